@@ -1,0 +1,381 @@
+/* d4est_b200_adapter.c -- see d4est_b200_adapter.h.
+ *
+ * Reference-side binding (C99, compiled with -DDIM=3 against the reference's
+ * headers).  Nothing here does arithmetic on the hot path: it records the
+ * face-iteration topology once per mesh and hands reference-owned arrays to
+ * libd4est_b200 by pointer.
+ */
+#include <stdlib.h>
+#include <string.h>
+#include <d4est_util.h>
+#include <d4est_reference.h>
+#include <d4est_lgl.h>
+#include "d4est_b200_adapter.h"
+
+#if (P4EST_DIM) != 3
+#error "the B200 path is 3-D only (d8est); build with -DDIM=3"
+#endif
+
+/* ------------------------------------------------------------------ sides */
+
+static void
+side_reserve (d4est_b200_flat_t * fl, int n)
+{
+  if (n <= fl->side_capacity) return;
+  int cap = fl->side_capacity ? 2 * fl->side_capacity : 1024;
+  while (cap < n) cap *= 2;
+#define GROW(p, T, k) fl->p = (T *) realloc (fl->p, sizeof (T) * (size_t) (k) * cap)
+  GROW (side_faces_m, int32_t, 1);
+  GROW (side_faces_p, int32_t, 1);
+  GROW (side_f_m, int32_t, 1);
+  GROW (side_f_p, int32_t, 1);
+  GROW (side_perm, int32_t, 1);
+  GROW (side_e_m, int32_t, 4);
+  GROW (side_e_p, int32_t, 4);
+  GROW (side_sub_order, int32_t, 4);
+  GROW (side_mortar_stride, int64_t, 1);
+  GROW (side_penalty_mult, double, 1);
+#undef GROW
+  fl->side_capacity = cap;
+}
+
+typedef struct
+{
+  d4est_b200_flat_t *fl;
+  d4est_mesh_data_t *factors;
+  d4est_laplacian_flux_sipg_params_t *sipg;
+  int mpirank;
+} iter_ctx_t;
+
+/* same 3 bits d4est_operators_reorient_face_data derives
+ * (src/dGMath/d4est_operators.c:2030-2044) */
+static int
+face_perm_code (int f_m, int f_p, int o)
+{
+  int ftransform[9];
+  p4est_expand_face_transform (((f_m <= f_p) ? f_m : f_p),
+                               (P4EST_FACES) * o + ((f_m <= f_p) ? f_p : f_m),
+                               ftransform);
+  int flip0 = ftransform[6];
+  int flip1 = ftransform[7];
+  int aligned = ((ftransform[1] - ftransform[0])
+                 * (ftransform[4] - ftransform[3]) > 0);
+  return (flip0 ? 1 : 0) | (flip1 ? 2 : 0) | (aligned ? 0 : 4);
+}
+
+static int32_t
+elem_ref (d4est_element_data_t * ed, int is_ghost, d4est_element_data_t * ghost_base)
+{
+  if (is_ghost) return -(int32_t) (ed - ghost_base) - 1;
+  return (int32_t) ed->id;
+}
+
+static void
+push_side (iter_ctx_t * ic, d4est_element_data_t ** e_m, int *m_ghost, int faces_m,
+           int f_m, d4est_element_data_t ** e_p, int *p_ghost, int faces_p, int f_p,
+           int orientation, d4est_element_data_t * ghost_base)
+{
+  d4est_b200_flat_t *fl = ic->fl;
+  int s = fl->desc.n_sides;
+  side_reserve (fl, s + 1);
+  fl->side_faces_m[s] = faces_m;
+  fl->side_faces_p[s] = faces_p;
+  fl->side_f_m[s] = f_m;
+  fl->side_f_p[s] = f_p;
+  int use_id = -1;
+  for (int i = 0; i < 4; i++) {
+    fl->side_e_m[4 * s + i] = (i < faces_m) ? elem_ref (e_m[i], m_ghost[i], ghost_base) : INT32_MIN;
+    fl->side_e_p[4 * s + i] = (i < faces_p) ? elem_ref (e_p[i], p_ghost[i], ghost_base) : INT32_MIN;
+    fl->side_sub_order[4 * s + i] = i;
+    if (i < faces_m && use_id < 0 && !m_ghost[i]) use_id = e_m[i]->id;
+  }
+  fl->side_perm[s] = 0;
+  if (faces_p > 0) {
+    fl->side_perm[s] = face_perm_code (f_m, f_p, orientation);
+    int faces_mortar = (faces_m > faces_p) ? faces_m : faces_p;
+    if (faces_mortar == (P4EST_HALF)) {
+      for (int i = 0; i < 4; i++)
+        fl->side_sub_order[4 * s + i] =
+          d4est_reference_reorient_face_order ((P4EST_DIM) - 1, f_m, f_p, orientation, i);
+    }
+  }
+  fl->side_mortar_stride[s] = ic->factors->local_strides[use_id].mortar_quad_stride[f_m];
+  int region_m = e_m[0]->region;
+  int region_p = (faces_p > 0) ? e_p[0]->region : region_m;
+  fl->side_penalty_mult[s] = d4est_laplacian_flux_sipg_get_multiplier (ic->sipg, region_m, region_p);
+  fl->desc.n_sides = s + 1;
+}
+
+/* mirrors the side selection of d4est_mortars_compute_flux_on_local_elements_aux
+ * (src/Mesh/d4est_mortars.c:601-802) */
+static void
+record_face (p4est_iter_face_info_t * info, void *user_data)
+{
+  iter_ctx_t *ic = (iter_ctx_t *) info->p4est->user_pointer;
+  d4est_element_data_t *ghost_data = (d4est_element_data_t *) user_data;
+  d4est_element_data_t *e_m[(P4EST_HALF)], *e_p[(P4EST_HALF)];
+  int m_ghost[(P4EST_HALF)], p_ghost[(P4EST_HALF)];
+  sc_array_t *sides = &(info->sides);
+
+  if (sides->elem_count == 2) {
+    p4est_iter_face_side_t *side[2];
+    side[0] = p4est_iter_fside_array_index_int (sides, 0);
+    side[1] = p4est_iter_fside_array_index_int (sides, 1);
+    for (int s_m = 0; s_m < 2; s_m++) {
+      int s_p = (s_m == 0) ? 1 : 0;
+      for (int i = 0; i < (P4EST_HALF); i++) m_ghost[i] = p_ghost[i] = 0;
+      if (side[s_m]->is_hanging) {
+        int nghost = 0;
+        for (int i = 0; i < (P4EST_HALF); i++) {
+          if (!side[s_m]->is.hanging.is_ghost[i]) {
+            e_m[i] = (d4est_element_data_t *) side[s_m]->is.hanging.quad[i]->p.user_data;
+          }
+          else {
+            e_m[i] = &ghost_data[side[s_m]->is.hanging.quadid[i]];
+            m_ghost[i] = 1;
+            nghost++;
+          }
+        }
+        if (side[s_p]->is.full.is_ghost) {
+          e_p[0] = &ghost_data[side[s_p]->is.full.quadid];
+          p_ghost[0] = 1;
+        }
+        else
+          e_p[0] = (d4est_element_data_t *) side[s_p]->is.full.quad->p.user_data;
+        if (nghost < (P4EST_HALF))
+          push_side (ic, e_m, m_ghost, (P4EST_HALF), side[s_m]->face, e_p, p_ghost, 1,
+                     side[s_p]->face, info->orientation, ghost_data);
+      }
+      else if (!side[s_m]->is.full.is_ghost) {
+        e_m[0] = (d4est_element_data_t *) side[s_m]->is.full.quad->p.user_data;
+        if (side[s_p]->is_hanging) {
+          for (int i = 0; i < (P4EST_HALF); i++) {
+            if (side[s_p]->is.hanging.is_ghost[i]) {
+              e_p[i] = &ghost_data[side[s_p]->is.hanging.quadid[i]];
+              p_ghost[i] = 1;
+            }
+            else
+              e_p[i] = (d4est_element_data_t *) side[s_p]->is.hanging.quad[i]->p.user_data;
+          }
+          push_side (ic, e_m, m_ghost, 1, side[s_m]->face, e_p, p_ghost, (P4EST_HALF),
+                     side[s_p]->face, info->orientation, ghost_data);
+        }
+        else {
+          if (side[s_p]->is.full.is_ghost) {
+            e_p[0] = &ghost_data[side[s_p]->is.full.quadid];
+            p_ghost[0] = 1;
+          }
+          else
+            e_p[0] = (d4est_element_data_t *) side[s_p]->is.full.quad->p.user_data;
+          push_side (ic, e_m, m_ghost, 1, side[s_m]->face, e_p, p_ghost, 1,
+                     side[s_p]->face, info->orientation, ghost_data);
+        }
+      }
+    }
+  }
+  else {
+    p4est_iter_face_side_t *side = p4est_iter_fside_array_index_int (sides, 0);
+    e_m[0] = (d4est_element_data_t *) side->is.full.quad->p.user_data;
+    m_ghost[0] = 0;
+    push_side (ic, e_m, m_ghost, 1, side->face, e_p, p_ghost, 0, -1, 0, ghost_data);
+  }
+}
+
+/* The penalty functions are file-static in the reference
+ * (d4est_laplacian_flux_sipg.c:945-1005); identify the pointer by probing it
+ * at one point where the four functions take four different values. */
+static int
+identify_penalty (penalty_calc_t fcn)
+{
+  double v = fcn (2, 1.0, 3, 2.0, 1.0);
+  if (fabs (v - 9.0) < 1e-12) return D4B_PENALTY_MAXP_SQR_OVER_MINH;
+  if (fabs (v - 16.0) < 1e-12) return D4B_PENALTY_MAXPP1_SQR_OVER_MINH;
+  if (fabs (v - 6.25 / 1.5) < 1e-12) return D4B_PENALTY_MEANP_SQR_OVER_MEANH;
+  if (fabs (v - 4.25) < 1e-12) return D4B_PENALTY_MEAN_P_SQR_OVER_H;
+  D4EST_ABORT ("d4est_b200: unknown sipg_penalty_fcn");
+  return -1;
+}
+
+d4est_b200_flat_t *
+d4est_b200_flatten (p4est_t * p4est, d4est_ghost_t * d4est_ghost,
+                    d4est_mesh_data_t * d4est_factors,
+                    d4est_laplacian_flux_data_t * flux_data)
+{
+  if (flux_data->flux_type != FLUX_SIPG)
+    D4EST_ABORT ("d4est_b200: only the SIPG flux is implemented");
+  d4est_laplacian_flux_sipg_params_t *sipg =
+    (d4est_laplacian_flux_sipg_params_t *) flux_data->flux_data;
+
+  d4est_b200_flat_t *fl = (d4est_b200_flat_t *) calloc (1, sizeof (*fl));
+  d4b_mesh_desc_t *D = &fl->desc;
+  D->abi_version = D4B_ABI_VERSION;
+  int n_local = p4est->local_num_quadrants;
+  int n_ghost = (int) d4est_ghost->ghost->ghosts.elem_count;
+  D->n_local = n_local;
+  D->n_ghost = n_ghost;
+  D->local_nodes = d4est_factors->local_sizes.local_nodes;
+  D->local_nodes_quad = d4est_factors->local_sizes.local_nodes_quad;
+  D->local_mortar_nodes_quad = d4est_factors->local_sizes.local_mortar_nodes_quad;
+
+  fl->deg = (int32_t *) malloc (sizeof (int32_t) * (n_local + 1));
+  fl->deg_quad = (int32_t *) malloc (sizeof (int32_t) * (n_local + 1));
+  fl->nodal_stride = (int64_t *) malloc (sizeof (int64_t) * (n_local + 1));
+  fl->quad_stride = (int64_t *) malloc (sizeof (int64_t) * (n_local + 1));
+  for (p4est_topidx_t tt = p4est->first_local_tree; tt <= p4est->last_local_tree; ++tt) {
+    p4est_tree_t *tree = p4est_tree_array_index (p4est->trees, tt);
+    sc_array_t *tquadrants = &tree->quadrants;
+    int Q = (p4est_locidx_t) tquadrants->elem_count;
+    for (int q = 0; q < Q; ++q) {
+      p4est_quadrant_t *quad = p4est_quadrant_array_index (tquadrants, q);
+      d4est_element_data_t *ed = (d4est_element_data_t *) quad->p.user_data;
+      fl->deg[ed->id] = ed->deg;
+      fl->deg_quad[ed->id] = ed->deg_quad;
+      fl->nodal_stride[ed->id] = ed->nodal_stride;
+      fl->quad_stride[ed->id] = ed->quad_stride;
+    }
+  }
+  fl->ghost_deg = (int32_t *) malloc (sizeof (int32_t) * (n_ghost + 1));
+  fl->ghost_deg_quad = (int32_t *) malloc (sizeof (int32_t) * (n_ghost + 1));
+  fl->ghost_nodal_stride = (int64_t *) malloc (sizeof (int64_t) * (n_ghost + 1));
+  int64_t gstride = 0;
+  for (int g = 0; g < n_ghost; g++) {
+    d4est_element_data_t *ged = &d4est_ghost->ghost_elements[g];
+    fl->ghost_deg[g] = ged->deg;
+    fl->ghost_deg_quad[g] = ged->deg_quad;
+    fl->ghost_nodal_stride[g] = gstride;
+    gstride += d4est_lgl_get_nodes ((P4EST_DIM), ged->deg);
+  }
+  D->ghost_nodes = gstride;
+
+  D->deg = fl->deg;
+  D->deg_quad = fl->deg_quad;
+  D->nodal_stride = fl->nodal_stride;
+  D->quad_stride = fl->quad_stride;
+  D->ghost_deg = fl->ghost_deg;
+  D->ghost_deg_quad = fl->ghost_deg_quad;
+  D->ghost_nodal_stride = fl->ghost_nodal_stride;
+
+  /* aliases of reference arrays */
+  D->J_quad = d4est_factors->J_quad;
+  D->rst_xyz_quad = d4est_factors->rst_xyz_quad;
+  D->sj_m_mortar_quad = d4est_factors->sj_m_mortar_quad;
+  D->n_m_mortar_quad = d4est_factors->n_m_mortar_quad;
+  D->drst_dxyz_m_mortar_quad = d4est_factors->drst_dxyz_m_mortar_quad;
+  D->drst_dxyz_p_mortar_quad_porder = d4est_factors->drst_dxyz_p_mortar_quad_porder;
+  D->hm_mortar_quad = d4est_factors->hm_mortar_quad;
+  D->hp_mortar_quad = d4est_factors->hp_mortar_quad;
+  D->dirichlet_g_mortar_quad = NULL;
+
+  /* side records */
+  iter_ctx_t ic;
+  ic.fl = fl;
+  ic.factors = d4est_factors;
+  ic.sipg = sipg;
+  ic.mpirank = p4est->mpirank;
+  void *tmpptr = p4est->user_pointer;
+  p4est->user_pointer = &ic;
+  p4est_iterate (p4est, d4est_ghost->ghost, (void *) d4est_ghost->ghost_elements,
+                 NULL, record_face, NULL, NULL);
+  p4est->user_pointer = tmpptr;
+  D->side_faces_m = fl->side_faces_m;
+  D->side_faces_p = fl->side_faces_p;
+  D->side_f_m = fl->side_f_m;
+  D->side_f_p = fl->side_f_p;
+  D->side_e_m = fl->side_e_m;
+  D->side_e_p = fl->side_e_p;
+  D->side_perm = fl->side_perm;
+  D->side_sub_order = fl->side_sub_order;
+  D->side_mortar_stride = fl->side_mortar_stride;
+  D->side_penalty_mult = fl->side_penalty_mult;
+
+  D->sipg_penalty_prefactor = sipg->sipg_penalty_prefactor;
+  D->sipg_penalty_fcn = identify_penalty (sipg->sipg_penalty_fcn);
+  D->bc_type = (flux_data->bc_type == BC_ROBIN) ? D4B_BC_ROBIN : D4B_BC_DIRICHLET;
+
+  /* ghost exchange plan, as d4est_ghost_data_exchange reads it
+   * (src/Mesh/d4est_ghost_data.c:171-199) */
+  p4est_ghost_t *gh = d4est_ghost->ghost;
+  D->mpirank = p4est->mpirank;
+  D->mpisize = p4est->mpisize;
+  D->n_mirrors = (int) gh->mirrors.elem_count;
+  fl->mirror_elem = (int32_t *) malloc (sizeof (int32_t) * (D->n_mirrors + 1));
+  for (int m = 0; m < D->n_mirrors; m++)
+    fl->mirror_elem[m] = d4est_ghost->mirror_elements[m].id;
+  fl->mirror_proc_offsets = (int32_t *) malloc (sizeof (int32_t) * (D->mpisize + 1));
+  fl->ghost_proc_offsets = (int32_t *) malloc (sizeof (int32_t) * (D->mpisize + 1));
+  for (int r = 0; r <= D->mpisize; r++) {
+    fl->mirror_proc_offsets[r] = gh->mirror_proc_offsets[r];
+    fl->ghost_proc_offsets[r] = gh->proc_offsets[r];
+  }
+  int nmpm = gh->mirror_proc_offsets[D->mpisize];
+  fl->mirror_proc_mirrors = (int32_t *) malloc (sizeof (int32_t) * (nmpm + 1));
+  for (int i = 0; i < nmpm; i++)
+    fl->mirror_proc_mirrors[i] = gh->mirror_proc_mirrors[i];
+  D->mirror_elem = fl->mirror_elem;
+  D->mirror_proc_offsets = fl->mirror_proc_offsets;
+  D->mirror_proc_mirrors = fl->mirror_proc_mirrors;
+  D->ghost_proc_offsets = fl->ghost_proc_offsets;
+  return fl;
+}
+
+void
+d4est_b200_flat_destroy (d4est_b200_flat_t * fl)
+{
+  if (fl == NULL) return;
+  free (fl->deg); free (fl->deg_quad); free (fl->nodal_stride); free (fl->quad_stride);
+  free (fl->ghost_deg); free (fl->ghost_deg_quad); free (fl->ghost_nodal_stride);
+  free (fl->side_faces_m); free (fl->side_faces_p); free (fl->side_f_m); free (fl->side_f_p);
+  free (fl->side_e_m); free (fl->side_e_p); free (fl->side_perm); free (fl->side_sub_order);
+  free (fl->side_mortar_stride); free (fl->side_penalty_mult); free (fl->dirichlet_g);
+  free (fl->mirror_elem); free (fl->mirror_proc_offsets); free (fl->mirror_proc_mirrors);
+  free (fl->ghost_proc_offsets);
+  free (fl);
+}
+
+/* ------------------------------------------------------------ apply_lhs */
+
+d4est_b200_ctx_t *
+d4est_b200_ctx_new (d4est_laplacian_flux_data_t * flux_data)
+{
+  d4est_b200_ctx_t *ctx = (d4est_b200_ctx_t *) calloc (1, sizeof (*ctx));
+  ctx->flux_data = flux_data;
+  return ctx;
+}
+
+void
+d4est_b200_ctx_destroy (d4est_b200_ctx_t * ctx)
+{
+  if (ctx == NULL) return;
+#ifndef D4EST_B200_ADAPTER_NO_DEVICE
+  if (ctx->mesh) d4b_mesh_destroy (ctx->mesh);
+#endif
+  free (ctx);
+}
+
+#ifndef D4EST_B200_ADAPTER_NO_DEVICE
+void
+d4est_b200_apply_lhs (p4est_t * p4est, d4est_ghost_t * ghost,
+                      d4est_ghost_data_t * ghost_data,
+                      d4est_elliptic_data_t * prob_vecs,
+                      d4est_operators_t * d4est_ops,
+                      d4est_geometry_t * d4est_geom,
+                      d4est_quadrature_t * d4est_quad,
+                      d4est_mesh_data_t * d4est_factors, void *user)
+{
+  d4est_b200_ctx_t *ctx = (d4est_b200_ctx_t *) user;
+  /* the reference re-runs d4est_mesh_update after AMR and once per multigrid
+   * level; (factors pointer, element count, node count) identifies a mesh */
+  if (ctx->mesh == NULL || ctx->cached_factors != d4est_factors
+      || ctx->cached_local_elements != p4est->local_num_quadrants
+      || ctx->cached_local_nodes != d4est_factors->local_sizes.local_nodes) {
+    if (ctx->mesh) d4b_mesh_destroy (ctx->mesh);
+    d4est_b200_flat_t *fl = d4est_b200_flatten (p4est, ghost, d4est_factors, ctx->flux_data);
+    ctx->mesh = d4b_mesh_create (&fl->desc);
+    d4est_b200_flat_destroy (fl);
+    ctx->cached_factors = d4est_factors;
+    ctx->cached_local_elements = p4est->local_num_quadrants;
+    ctx->cached_local_nodes = d4est_factors->local_sizes.local_nodes;
+  }
+  d4b_apply (ctx->mesh, prob_vecs->u, prob_vecs->Au);
+}
+#endif

@@ -1,0 +1,69 @@
+/* d4est_b200_adapter.h -- reference-side binding of libd4est_b200.
+ *
+ * This file is compiled AGAINST THE REFERENCE'S HEADERS (p4est, d4est_*.h);
+ * it is what a maintainer of the reference adds to their tree.  It flattens
+ * p4est_t + d4est_ghost_t + d4est_mesh_data_t + flux parameters into the
+ * plain-C d4b_mesh_desc_t of include/d4est_b200.h and provides a function
+ * with the exact d4est_apply_operator_fcn_t signature
+ * (src/EllipticSystem/d4est_elliptic_eqns.h:12-24).
+ */
+#ifndef D4EST_B200_ADAPTER_H
+#define D4EST_B200_ADAPTER_H
+
+#include <pXest.h>
+#include <d4est_ghost.h>
+#include <d4est_ghost_data.h>
+#include <d4est_mesh.h>
+#include <d4est_elliptic_data.h>
+#include <d4est_elliptic_eqns.h>
+#include <d4est_laplacian_flux.h>
+#include <d4est_laplacian_flux_sipg.h>
+#include "d4est_b200.h"
+
+/* Owns the arrays a d4b_mesh_desc_t points to (those that are not aliases of
+ * reference arrays). */
+typedef struct
+{
+  d4b_mesh_desc_t desc;
+  /* owned */
+  int32_t *deg, *deg_quad;
+  int64_t *nodal_stride, *quad_stride;
+  int32_t *ghost_deg, *ghost_deg_quad;
+  int64_t *ghost_nodal_stride;
+  int32_t *side_faces_m, *side_faces_p, *side_f_m, *side_f_p;
+  int32_t *side_e_m, *side_e_p, *side_perm, *side_sub_order;
+  int64_t *side_mortar_stride;
+  double  *side_penalty_mult;
+  double  *dirichlet_g;
+  int32_t *mirror_elem, *mirror_proc_offsets, *mirror_proc_mirrors, *ghost_proc_offsets;
+  int side_capacity;
+} d4est_b200_flat_t;
+
+/* user context stored in d4est_elliptic_eqns_t.user */
+typedef struct
+{
+  d4est_laplacian_flux_data_t *flux_data;  /* as the reference callbacks use */
+  d4b_mesh_t *mesh;                        /* cached device mesh             */
+  d4est_mesh_data_t *cached_factors;       /* cache key                      */
+  int cached_local_elements;
+  int cached_local_nodes;
+} d4est_b200_ctx_t;
+
+d4est_b200_flat_t *d4est_b200_flatten(p4est_t *p4est, d4est_ghost_t *d4est_ghost,
+                                      d4est_mesh_data_t *d4est_factors,
+                                      d4est_laplacian_flux_data_t *flux_data);
+void d4est_b200_flat_destroy(d4est_b200_flat_t *flat);
+
+/* drop-in for d4est_elliptic_eqns_t.apply_lhs */
+void d4est_b200_apply_lhs(p4est_t *p4est, d4est_ghost_t *ghost,
+                          d4est_ghost_data_t *ghost_data,
+                          d4est_elliptic_data_t *prob_vecs,
+                          d4est_operators_t *d4est_ops,
+                          d4est_geometry_t *d4est_geom,
+                          d4est_quadrature_t *d4est_quad,
+                          d4est_mesh_data_t *d4est_factors, void *user);
+
+d4est_b200_ctx_t *d4est_b200_ctx_new(d4est_laplacian_flux_data_t *flux_data);
+void d4est_b200_ctx_destroy(d4est_b200_ctx_t *ctx);
+
+#endif

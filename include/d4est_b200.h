@@ -1,0 +1,206 @@
+/* d4est_b200.h -- C ABI of libd4est_b200.so
+ *
+ * B200-native (sm_100a) replacement for the one data-parallel hot path of
+ * trevor-vincent/disco4est: the matrix-free SIPG operator application
+ *   Au = K u + F(u)
+ * (d4est_laplacian_apply_aij, src/dGMath/d4est_laplacian.c:317-399, and its
+ * with_opt twin, src/dGMath/d4est_laplacian_with_opt.c:289-368), the BLAS-1
+ * sweeps around it (src/LinearAlgebra/d4est_linalg.c:179-236) and the
+ * Chebyshev / cg_eigs smoother kernels that wrap it
+ * (src/Solver/d4est_solver_multigrid_smoother_cheby.c:81-176,
+ *  src/Solver/d4est_solver_cg_eigs.c:115-276).
+ *
+ * Plain C types only: pointers, sizes, enums.  No torch, no C++ in signatures.
+ * Error convention follows the reference (src/Utilities/d4est_util.h:171,
+ * D4EST_ABORT): entry points do not return error codes; any CUDA failure or
+ * invalid input calls the abort hook (d4b_set_abort_hook), which by default
+ * prints "[D4B_ABORT] file:line msg" and calls abort().  There is NO CPU
+ * fallback: without a CUDA device every compute entry point aborts.
+ */
+#ifndef D4EST_B200_H
+#define D4EST_B200_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define D4B_ABI_VERSION 1
+#define D4B_MAX_DEG 7          /* p = 1..7 (N = 2..8 nodes per direction)   */
+#define D4B_FACES 6
+#define D4B_HALF 4             /* sub-faces of a hanging 3-D face            */
+
+/* penalty functions, src/dGMath/d4est_laplacian_flux_sipg.c:945-1005 */
+typedef enum {
+  D4B_PENALTY_MAXP_SQR_OVER_MINH = 0,
+  D4B_PENALTY_MAXPP1_SQR_OVER_MINH = 1,
+  D4B_PENALTY_MEANP_SQR_OVER_MEANH = 2,
+  D4B_PENALTY_MEAN_P_SQR_OVER_H = 3
+} d4b_penalty_t;
+
+/* boundary condition on physical boundary faces,
+ * src/dGMath/d4est_laplacian_flux.h:171-186 */
+typedef enum { D4B_BC_DIRICHLET = 0, D4B_BC_ROBIN = 1 } d4b_bc_t;
+
+/* Flattened, read-only description of one rank's mesh in the REFERENCE'S OWN
+ * array layouts (so that the adapter on the reference side only copies
+ * pointers).  Everything is a host pointer; d4b_mesh_create() copies what it
+ * needs and re-lays it out for the device, the caller may free afterwards.
+ *
+ * Element / node ordering = reference ordering: element id = position in the
+ * local tree/quadrant iteration (d4est_mesh.c:2394-2490), node i of element e
+ * lives at nodal_stride[e] + i with i = ir + N*(is + N*it), r fastest
+ * (d4est_operators.c:1385-1410).                                           */
+typedef struct d4b_mesh_desc
+{
+  int32_t abi_version;          /* = D4B_ABI_VERSION                        */
+  int32_t n_local;              /* local elements                           */
+  int32_t n_ghost;              /* ghost elements (0 on one rank)           */
+  int32_t n_sides;              /* flux "side" records, see below           */
+  int64_t local_nodes;          /* d4est_mesh_local_sizes_t.local_nodes     */
+  int64_t local_nodes_quad;     /* .local_nodes_quad                        */
+  int64_t local_mortar_nodes_quad; /* .local_mortar_nodes_quad              */
+  int64_t ghost_nodes;          /* sum of ghost (deg+1)^3                   */
+
+  /* ---- per local element [n_local]  (d4est_element_data.h:13-46) ---- */
+  const int32_t *deg;
+  const int32_t *deg_quad;
+  const int64_t *nodal_stride;
+  const int64_t *quad_stride;
+
+  /* ---- per ghost element [n_ghost], in ghost-id order ---- */
+  const int32_t *ghost_deg;
+  const int32_t *ghost_deg_quad;
+  const int64_t *ghost_nodal_stride;  /* offset into the ghost receive buffer
+                                         (d4est_ghost_data.c:258-268)       */
+
+  /* ---- volume geometric factors (d4est_mesh.h:117-162) ---- */
+  const double *J_quad;         /* [local_nodes_quad]                       */
+  const double *rst_xyz_quad;   /* [(i*3+j)*local_nodes_quad + quad_stride]
+                                   = d(rst_i)/d(xyz_j), d4est_mesh.c:2757-2777 */
+
+  /* ---- mortar geometric factors, all indexed by side_mortar_stride ----
+   * scalar s[k]            at            stride + k
+   * vector v[d][k]         at 3*stride + d*total + k
+   * matrix m[i][j][k]      at 9*stride + (i + 3*j)*total + k
+   * with total = mortar quadrature nodes of the side
+   * (d4est_mesh.c:962-1000, d4est_laplacian_flux.c:425-449)              */
+  const double *sj_m_mortar_quad;
+  const double *n_m_mortar_quad;
+  const double *drst_dxyz_m_mortar_quad;
+  const double *drst_dxyz_p_mortar_quad_porder;  /* (+)-side ordering       */
+  const double *hm_mortar_quad;
+  const double *hp_mortar_quad;
+  /* Dirichlet data g at the boundary-face quadrature points, same scalar
+   * indexing as sj (only boundary sides are read); NULL = homogeneous, which
+   * is what every apply_lhs of the reference uses.                         */
+  const double *dirichlet_g_mortar_quad;
+
+  /* ---- flux side records [n_sides] ----
+   * One record per call the reference's face iteration makes to the flux
+   * interface/boundary function (d4est_mortars.c:601-802): a (-) side of 1 or
+   * 4 elements on face f_m against a (+) side of 1 or 4 elements (0 =
+   * physical boundary).  Element references: >= 0 local element id,
+   * < 0 ghost element -(gid+1).                                            */
+  const int32_t *side_faces_m;     /* 1 or 4                                */
+  const int32_t *side_faces_p;     /* 0 (boundary), 1 or 4                  */
+  const int32_t *side_f_m;         /* face of the (-) elements, 0..5        */
+  const int32_t *side_f_p;         /* face of the (+) elements              */
+  const int32_t *side_e_m;         /* [4*n_sides]                           */
+  const int32_t *side_e_p;         /* [4*n_sides], in (+)-side order        */
+  /* face-node permutation (+)->(-) ordering, bit0 flip dir0, bit1 flip dir1,
+   * bit2 transpose, applied in that order (what
+   * d4est_operators_reorient_face_data does, d4est_operators.c:1993-2087)  */
+  const int32_t *side_perm;
+  /* sub-face reorder: (-)-ordered sub-face i is (+)-ordered sub-face
+   * side_sub_order[4*s+i] (d4est_reference_reorient_face_order)            */
+  const int32_t *side_sub_order;   /* [4*n_sides]                           */
+  const int64_t *side_mortar_stride;
+  const double  *side_penalty_mult; /* region multiplier,
+                                       d4est_laplacian_flux_sipg.c:1165-1199 */
+
+  /* ---- flux parameters (d4est_laplacian_flux_sipg.h:18-37) ---- */
+  double  sipg_penalty_prefactor;
+  int32_t sipg_penalty_fcn;        /* d4b_penalty_t                         */
+  int32_t bc_type;                 /* d4b_bc_t                              */
+
+  /* ---- ghost exchange plan (d4est_ghost_data.c:142-255) ---- */
+  int32_t mpirank, mpisize;
+  int32_t n_mirrors;
+  const int32_t *mirror_elem;          /* [n_mirrors] local element ids     */
+  const int32_t *mirror_proc_offsets;  /* [mpisize+1]                       */
+  const int32_t *mirror_proc_mirrors;  /* indices into mirror_elem          */
+  const int32_t *ghost_proc_offsets;   /* [mpisize+1] ghost ranges per rank */
+} d4b_mesh_desc_t;
+
+typedef struct d4b_mesh d4b_mesh_t;    /* opaque device-resident mesh */
+
+/* ---------------------------------------------------------------- runtime */
+typedef void (*d4b_abort_hook_t)(const char *file, int line, const char *msg);
+void d4b_set_abort_hook(d4b_abort_hook_t hook);
+int  d4b_abi_version(void);
+/* number of CUDA devices visible (0 if none / driver missing); never aborts */
+int  d4b_device_count(void);
+/* bind this process to a device (reference: one MPI rank per device)       */
+void d4b_init(int device);
+
+/* ------------------------------------------------------------------- mesh */
+/* replaces the per-mesh setup the reference does lazily inside
+ * d4est_mesh_update (src/Mesh/d4est_mesh.c:2790-2890) for the apply path   */
+d4b_mesh_t *d4b_mesh_create(const d4b_mesh_desc_t *desc);
+void        d4b_mesh_destroy(d4b_mesh_t *mesh);
+int64_t     d4b_mesh_local_nodes(const d4b_mesh_t *mesh);
+/* bytes of device memory held by the mesh (geometric factors + tables)     */
+int64_t     d4b_mesh_device_bytes(const d4b_mesh_t *mesh);
+
+/* ------------------------------------------------------------------ apply */
+/* Au = A u; replaces d4est_laplacian_apply_aij / _with_opt_apply_aij
+ * (d4est_laplacian.c:317-399).  u, Au: local_nodes doubles in reference node
+ * order; each may be a host or a device pointer (cudaPointerGetAttributes).
+ * Au is fully overwritten (d4est_quadrature.c:337).  Synchronous when any
+ * pointer is a host pointer; stream-ordered otherwise (d4b_sync to wait).  */
+void d4b_apply(d4b_mesh_t *mesh, const double *u, double *Au);
+/* volume stiffness only: d4est_laplacian_apply_stiffness_matrix
+ * (d4est_laplacian.c:197-234)                                              */
+void d4b_apply_stiffness(d4b_mesh_t *mesh, const double *u, double *Au);
+void d4b_sync(d4b_mesh_t *mesh);
+
+/* --------------------------------------------------------------- BLAS-1  */
+/* device-resident vector ops, src/LinearAlgebra/d4est_linalg.c:179-236;
+ * all pointers are DEVICE pointers                                          */
+double d4b_vec_dot(d4b_mesh_t *mesh, const double *x, const double *y, int64_t n);
+void   d4b_vec_axpy(d4b_mesh_t *mesh, double a, const double *x, double *y, int64_t n);
+void   d4b_vec_xpby(d4b_mesh_t *mesh, const double *x, double b, double *y, int64_t n);
+void   d4b_vec_scale(d4b_mesh_t *mesh, double a, double *x, int64_t n);
+
+/* ---------------------------------------------------- Chebyshev smoother  */
+/* parameters of [mg_smoother_cheby], d4est_solver_multigrid_smoother_cheby.h:7-27 */
+typedef struct d4b_cheby_params
+{
+  int32_t cheby_imax;
+  int32_t cheby_eigs_cg_imax;
+  double  cheby_eigs_lmax_lmin_ratio;
+  double  cheby_eigs_max_multiplier;
+  int32_t cheby_use_new_cg_eigs;
+  int32_t cheby_use_zero_guess_for_eigs;
+} d4b_cheby_params_t;
+
+/* cg_eigs (src/Solver/d4est_solver_cg_eigs.c:115-276): runs imax CG steps on
+ * A x = rhs from x0 = u (or zero) and returns the Gershgorin bound of the
+ * Lanczos tridiagonal.  u, rhs host or device; not modified.               */
+double d4b_cg_eigs(d4b_mesh_t *mesh, const double *u, const double *rhs,
+                   int32_t imax, int32_t use_new, int32_t use_zero_guess);
+
+/* Chebyshev recurrence (…smoother_cheby.c:81-176) with spectrum [lmin,lmax]:
+ * iter sweeps on A u = rhs, then r = rhs - A u.  u is updated in place, r is
+ * written.  Host or device pointers.  The apply and the recurrence are fused
+ * on the device: each iteration streams u, p, rhs once.                    */
+void d4b_cheby_smooth(d4b_mesh_t *mesh, double *u, const double *rhs, double *r,
+                      int32_t iter, double lmin, double lmax);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* D4EST_B200_H */

@@ -1,0 +1,388 @@
+/* ref_driver.c -- drives the UNMODIFIED reference (compiled serially into
+ * oracle/_ref/) through its own public API and dumps inputs + outputs.
+ *
+ * TEST INFRASTRUCTURE - not part of the product.  Only tests/, smoke() and
+ * bench.py's cpu_baseline / --impl reference legs may execute this binary.
+ *
+ * Modelled on src/Tests/Unit/d4est_test_laplacian_speedup.c:155-540: build the
+ * forest from an INI file, optional random hp-AMR steps, u = x^2+y^2+z^2 +
+ * U(0,1) with srand(102321), apply the plain and the with_opt operator.
+ *
+ *   ref_driver <ini> <out.d4b|-> [--amr N] [--time REPS] [--cheby IMAX EIGS_IMAX]
+ *              [--bc zero|poly] [--uniform-deg P]
+ */
+#include <pXest.h>
+#include <d4est_quadrature.h>
+#include <d4est_element_data.h>
+#include <d4est_quadrature_legendre.h>
+#include <d4est_geometry.h>
+#include <d4est_mesh.h>
+#include <d4est_linalg.h>
+#include <d4est_mortars.h>
+#include <d4est_amr.h>
+#include <d4est_laplacian_with_opt.h>
+#include <d4est_laplacian.h>
+#include <d4est_solver_cg_eigs.h>
+#include <d4est_solver_multigrid_smoother_cheby.h>
+#include <d4est_util.h>
+#include <zlog.h>
+#include <time.h>
+#include <sys/time.h>
+#include <unistd.h>
+#include "d4b_dump.h"
+#include "d4est_b200_adapter.h"
+
+static double
+wall (void)
+{
+  struct timeval tv;
+  gettimeofday (&tv, NULL);
+  return tv.tv_sec + 1e-6 * tv.tv_usec;
+}
+
+static double
+drv_zero_fcn (double x, double y, double z, void *user)
+{
+  return 0.;
+}
+
+static double
+drv_poly_fcn (double x, double y, double z, void *user)
+{
+  return x * x + y * y + z * z;
+}
+
+static void
+apply_plain (p4est_t * p4est, d4est_ghost_t * ghost, d4est_ghost_data_t * ghost_data,
+             d4est_elliptic_data_t * prob_vecs, d4est_operators_t * d4est_ops,
+             d4est_geometry_t * d4est_geom, d4est_quadrature_t * d4est_quad,
+             d4est_mesh_data_t * d4est_factors, void *user)
+{
+  d4est_laplacian_apply_aij (p4est, ghost, ghost_data, prob_vecs,
+                             (d4est_laplacian_flux_data_t *) user, d4est_ops,
+                             d4est_geom, d4est_quad, d4est_factors, 0);
+}
+
+static void
+apply_with_opt (p4est_t * p4est, d4est_ghost_t * ghost, d4est_ghost_data_t * ghost_data,
+                d4est_elliptic_data_t * prob_vecs, d4est_operators_t * d4est_ops,
+                d4est_geometry_t * d4est_geom, d4est_quadrature_t * d4est_quad,
+                d4est_mesh_data_t * d4est_factors, void *user)
+{
+  d4est_laplacian_with_opt_apply_aij (p4est, ghost, ghost_data, prob_vecs,
+                                      (d4est_laplacian_with_opt_flux_data_t *) user,
+                                      d4est_ops, d4est_geom, d4est_quad, d4est_factors, 0);
+}
+
+static int g_uniform_deg = -1;
+static void
+set_uniform_deg (d4est_element_data_t * elem_data, void *user_ctx)
+{
+  d4est_mesh_initial_extents_t *input = user_ctx;
+  elem_data->deg = g_uniform_deg;
+  elem_data->deg_quad = input->deg_quad_inc[elem_data->region] + elem_data->deg;
+}
+
+static void
+dump_desc (FILE * f, const d4b_mesh_desc_t * D)
+{
+  d4b_dump_scalar_i64 (f, "n_local", D->n_local);
+  d4b_dump_scalar_i64 (f, "n_ghost", D->n_ghost);
+  d4b_dump_scalar_i64 (f, "n_sides", D->n_sides);
+  d4b_dump_scalar_i64 (f, "local_nodes", D->local_nodes);
+  d4b_dump_scalar_i64 (f, "local_nodes_quad", D->local_nodes_quad);
+  d4b_dump_scalar_i64 (f, "local_mortar_nodes_quad", D->local_mortar_nodes_quad);
+  d4b_dump_scalar_i64 (f, "ghost_nodes", D->ghost_nodes);
+  d4b_dump_put1 (f, "deg", D4B_I32, D->n_local, D->deg);
+  d4b_dump_put1 (f, "deg_quad", D4B_I32, D->n_local, D->deg_quad);
+  d4b_dump_put1 (f, "nodal_stride", D4B_I64, D->n_local, D->nodal_stride);
+  d4b_dump_put1 (f, "quad_stride", D4B_I64, D->n_local, D->quad_stride);
+  d4b_dump_put1 (f, "J_quad", D4B_F64, D->local_nodes_quad, D->J_quad);
+  d4b_dump_put1 (f, "rst_xyz_quad", D4B_F64, 9 * D->local_nodes_quad, D->rst_xyz_quad);
+  uint64_t m = D->local_mortar_nodes_quad;
+  d4b_dump_put1 (f, "sj_m_mortar_quad", D4B_F64, m, D->sj_m_mortar_quad);
+  d4b_dump_put1 (f, "n_m_mortar_quad", D4B_F64, 3 * m, D->n_m_mortar_quad);
+  d4b_dump_put1 (f, "drst_dxyz_m_mortar_quad", D4B_F64, 9 * m, D->drst_dxyz_m_mortar_quad);
+  d4b_dump_put1 (f, "drst_dxyz_p_mortar_quad_porder", D4B_F64, 9 * m, D->drst_dxyz_p_mortar_quad_porder);
+  d4b_dump_put1 (f, "hm_mortar_quad", D4B_F64, m, D->hm_mortar_quad);
+  d4b_dump_put1 (f, "hp_mortar_quad", D4B_F64, m, D->hp_mortar_quad);
+  if (D->dirichlet_g_mortar_quad)
+    d4b_dump_put1 (f, "dirichlet_g_mortar_quad", D4B_F64, m, D->dirichlet_g_mortar_quad);
+  uint64_t s = D->n_sides;
+  d4b_dump_put1 (f, "side_faces_m", D4B_I32, s, D->side_faces_m);
+  d4b_dump_put1 (f, "side_faces_p", D4B_I32, s, D->side_faces_p);
+  d4b_dump_put1 (f, "side_f_m", D4B_I32, s, D->side_f_m);
+  d4b_dump_put1 (f, "side_f_p", D4B_I32, s, D->side_f_p);
+  d4b_dump_put1 (f, "side_e_m", D4B_I32, 4 * s, D->side_e_m);
+  d4b_dump_put1 (f, "side_e_p", D4B_I32, 4 * s, D->side_e_p);
+  d4b_dump_put1 (f, "side_perm", D4B_I32, s, D->side_perm);
+  d4b_dump_put1 (f, "side_sub_order", D4B_I32, 4 * s, D->side_sub_order);
+  d4b_dump_put1 (f, "side_mortar_stride", D4B_I64, s, D->side_mortar_stride);
+  d4b_dump_put1 (f, "side_penalty_mult", D4B_F64, s, D->side_penalty_mult);
+  d4b_dump_scalar_f64 (f, "sipg_penalty_prefactor", D->sipg_penalty_prefactor);
+  d4b_dump_scalar_i64 (f, "sipg_penalty_fcn", D->sipg_penalty_fcn);
+  d4b_dump_scalar_i64 (f, "bc_type", D->bc_type);
+}
+
+/* reference 1-D tables, for pinning the product's own table builders */
+static void
+dump_tables (FILE * f, d4est_operators_t * ops, int max_deg)
+{
+  char name[64];
+  for (int p = 1; p <= max_deg; p++) {
+    int N = p + 1;
+    snprintf (name, 64, "tab_lgl_nodes_%d", p);
+    d4b_dump_put1 (f, name, D4B_F64, N, d4est_operators_fetch_lobatto_nodes_1d (ops, p));
+    snprintf (name, 64, "tab_lgl_weights_%d", p);
+    d4b_dump_put1 (f, name, D4B_F64, N, d4est_operators_fetch_lobatto_weights_1d (ops, p));
+    snprintf (name, 64, "tab_gauss_nodes_%d", p);
+    d4b_dump_put1 (f, name, D4B_F64, N, d4est_operators_fetch_gauss_nodes_1d (ops, p));
+    snprintf (name, 64, "tab_gauss_weights_%d", p);
+    d4b_dump_put1 (f, name, D4B_F64, N, d4est_operators_fetch_gauss_weights_1d (ops, p));
+    snprintf (name, 64, "tab_dij_%d", p);
+    {
+      /* the 1-D derivative table is file-static in the reference; recover it
+       * column by column through the public apply_dij in one dimension */
+      double Dm[64], ej[8], col[8];
+      for (int j = 0; j < N; j++) {
+        for (int i = 0; i < N; i++) ej[i] = (i == j) ? 1. : 0.;
+        d4est_operators_apply_dij (ops, ej, 1, p, 0, col);
+        for (int i = 0; i < N; i++) Dm[i * N + j] = col[i];
+      }
+      d4b_dump_put1 (f, name, D4B_F64, N * N, Dm);
+    }
+    snprintf (name, 64, "tab_mij_%d", p);
+    d4b_dump_put1 (f, name, D4B_F64, N * N, d4est_operators_fetch_mij_1d (ops, p));
+    for (int q = p; q <= max_deg; q++) {
+      snprintf (name, 64, "tab_lgl_to_gauss_%d_%d", p, q);
+      d4b_dump_put1 (f, name, D4B_F64, (q + 1) * N,
+                     d4est_operators_fetch_lobatto_to_gauss_interp_1d (ops, p, q));
+      snprintf (name, 64, "tab_p_prolong_%d_%d", p, q);
+      d4b_dump_put1 (f, name, D4B_F64, (q + 1) * N,
+                     d4est_operators_fetch_p_prolong_1d (ops, p, q));
+    }
+  }
+}
+
+int
+main (int argc, char *argv[])
+{
+  if (argc < 3) {
+    fprintf (stderr, "usage: %s <ini> <out.d4b|-> [--amr N] [--time REPS] [--bc zero|poly]"
+             " [--uniform-deg P] [--cheby IMAX EIGS_IMAX]\n", argv[0]);
+    return 2;
+  }
+  const char *ini = argv[1];
+  const char *out = argv[2];
+  int amr_steps = 0, time_reps = 0, bc_poly = 0, cheby_imax = 0, cheby_eigs_imax = 0;
+  for (int a = 3; a < argc; a++) {
+    if (!strcmp (argv[a], "--amr")) amr_steps = atoi (argv[++a]);
+    else if (!strcmp (argv[a], "--time")) time_reps = atoi (argv[++a]);
+    else if (!strcmp (argv[a], "--bc")) bc_poly = !strcmp (argv[++a], "poly");
+    else if (!strcmp (argv[a], "--uniform-deg")) g_uniform_deg = atoi (argv[++a]);
+    else if (!strcmp (argv[a], "--cheby")) { cheby_imax = atoi (argv[++a]); cheby_eigs_imax = atoi (argv[++a]); }
+    else { fprintf (stderr, "unknown option %s\n", argv[a]); return 2; }
+  }
+
+  sc_MPI_Comm mpicomm = sc_MPI_COMM_WORLD;
+  int mpiret = sc_MPI_Init (&argc, &argv);
+  SC_CHECK_MPI (mpiret);
+  sc_init (mpicomm, 1, 1, NULL, SC_LP_ERROR);
+  p4est_init (NULL, SC_LP_ERROR);
+
+  /* zlog must be initialised before any reference module logs */
+  char conf[256];
+  snprintf (conf, sizeof (conf), "/tmp/d4b_zlog_%d.conf", (int) getpid ());
+  FILE *cf = fopen (conf, "w");
+  fprintf (cf, "[formats]\nplain = \"%%m%%n\"\n[rules]\n*.ERROR >stderr; plain\n");
+  fclose (cf);
+  if (zlog_init (conf)) { fprintf (stderr, "zlog_init failed\n"); return 2; }
+  unlink (conf);
+
+  zlog_category_t *c_geom = zlog_get_category ("d4est_geometry");
+  d4est_geometry_t *d4est_geom = d4est_geometry_new (0, ini, "geometry", c_geom);
+  d4est_mesh_initial_extents_t *initial_grid_input =
+    d4est_mesh_initial_extents_parse (ini, d4est_geom);
+
+  p4est_t *p4est = p4est_new_ext (mpicomm, d4est_geom->p4est_conn,
+                                  initial_grid_input->min_quadrants,
+                                  initial_grid_input->min_level,
+                                  initial_grid_input->fill_uniform,
+                                  sizeof (d4est_element_data_t), NULL, NULL);
+  p4est_partition (p4est, 1, NULL);
+  p4est_balance (p4est, P4EST_CONNECT_FULL, NULL);
+
+  d4est_ghost_t *d4est_ghost = d4est_ghost_init (p4est);
+  d4est_operators_t *d4est_ops = d4est_ops_init (20);
+  d4est_mesh_data_t *d4est_factors = d4est_mesh_data_init (p4est);
+  d4est_quadrature_t *d4est_quad =
+    d4est_quadrature_new (p4est, d4est_ops, d4est_geom, ini, "quadrature");
+
+  double t0 = wall ();
+  d4est_mesh_local_sizes_t local_sizes =
+    d4est_mesh_update (p4est, &d4est_ghost, d4est_ops, d4est_geom, d4est_quad,
+                       d4est_factors, initial_grid_input, INITIALIZE_GHOST,
+                       INITIALIZE_QUADRATURE_DATA, INITIALIZE_GEOMETRY_DATA,
+                       INITIALIZE_GEOMETRY_ALIASES,
+                       (g_uniform_deg > 0) ? set_uniform_deg : d4est_mesh_set_initial_extents,
+                       (void *) initial_grid_input);
+  initial_grid_input->initial_nodes = local_sizes.local_nodes;
+
+  if (amr_steps > 0) {
+    d4est_amr_t *d4est_amr_random = d4est_amr_init_random_hp (p4est, amr_steps);
+    for (int i = 0; i < amr_steps; i++) {
+      d4est_amr_step (p4est, d4est_ops, d4est_amr_random, NULL, NULL, NULL, NULL);
+      local_sizes =
+        d4est_mesh_update (p4est, &d4est_ghost, d4est_ops, d4est_geom, d4est_quad,
+                           d4est_factors, initial_grid_input, INITIALIZE_GHOST,
+                           INITIALIZE_QUADRATURE_DATA, INITIALIZE_GEOMETRY_DATA,
+                           INITIALIZE_GEOMETRY_ALIASES,
+                           d4est_mesh_set_quadratures_after_amr,
+                           (void *) initial_grid_input);
+    }
+    d4est_amr_destroy (d4est_amr_random);
+  }
+  double t_mesh = wall () - t0;
+
+  d4est_field_type_t field_type = NODAL;
+  d4est_ghost_data_t *d4est_ghost_data =
+    d4est_ghost_data_init (p4est, d4est_ghost, &field_type, 1);
+  int local_nodes = local_sizes.local_nodes;
+
+  d4est_laplacian_dirichlet_bc_t bc_data_for_lhs;
+  bc_data_for_lhs.dirichlet_fcn = bc_poly ? drv_poly_fcn : drv_zero_fcn;
+  bc_data_for_lhs.eval_method = EVAL_BNDRY_FCN_ON_LOBATTO;
+  bc_data_for_lhs.user = NULL;
+
+  d4est_laplacian_flux_data_t *flux_plain =
+    d4est_laplacian_flux_new (p4est, ini, BC_DIRICHLET, &bc_data_for_lhs);
+  d4est_laplacian_with_opt_flux_data_t *flux_opt =
+    d4est_laplacian_with_opt_flux_new (p4est, ini, BC_DIRICHLET, &bc_data_for_lhs);
+
+  d4est_elliptic_eqns_t fcns_plain = {.build_residual = NULL,.apply_lhs = apply_plain,.user = flux_plain };
+  d4est_elliptic_eqns_t fcns_opt = {.build_residual = NULL,.apply_lhs = apply_with_opt,.user = flux_opt };
+
+  double *u = P4EST_ALLOC (double, local_nodes);
+  double *Au_plain = P4EST_ALLOC_ZERO (double, local_nodes);
+  double *Au_opt = P4EST_ALLOC_ZERO (double, local_nodes);
+  d4est_mesh_init_field (p4est, u, drv_poly_fcn, d4est_ops, d4est_geom, d4est_factors,
+                         INIT_FIELD_ON_LOBATTO, NULL);
+  srand (102321);
+  for (int i = 0; i < local_nodes; i++) u[i] += (double) rand () / (double) RAND_MAX;
+
+  d4est_elliptic_data_t vecs;
+  memset (&vecs, 0, sizeof (vecs));
+  vecs.u = u;
+  vecs.Au = Au_plain;
+  vecs.local_nodes = local_nodes;
+  vecs.field_types = &field_type;
+  vecs.num_of_fields = 1;
+
+  t0 = wall ();
+  d4est_elliptic_eqns_apply_lhs (p4est, d4est_ghost, d4est_ghost_data, &fcns_plain, &vecs,
+                                 d4est_ops, d4est_geom, d4est_quad, d4est_factors);
+  double t_plain = wall () - t0;
+  vecs.Au = Au_opt;
+  t0 = wall ();
+  d4est_elliptic_eqns_apply_lhs (p4est, d4est_ghost, d4est_ghost_data, &fcns_opt, &vecs,
+                                 d4est_ops, d4est_geom, d4est_quad, d4est_factors);
+  double t_opt = wall () - t0;
+
+  /* timing loop for the CPU baseline: best of REPS for each variant */
+  double best_plain = t_plain, best_opt = t_opt;
+  double *Au_tmp = P4EST_ALLOC_ZERO (double, local_nodes);
+  vecs.Au = Au_tmp;
+  for (int r = 0; r < time_reps; r++) {
+    t0 = wall ();
+    d4est_elliptic_eqns_apply_lhs (p4est, d4est_ghost, d4est_ghost_data, &fcns_opt, &vecs,
+                                   d4est_ops, d4est_geom, d4est_quad, d4est_factors);
+    double t = wall () - t0;
+    if (t < best_opt) best_opt = t;
+    t0 = wall ();
+    d4est_elliptic_eqns_apply_lhs (p4est, d4est_ghost, d4est_ghost_data, &fcns_plain, &vecs,
+                                   d4est_ops, d4est_geom, d4est_quad, d4est_factors);
+    t = wall () - t0;
+    if (t < best_plain) best_plain = t;
+  }
+
+  double maxdiff = 0.;
+  for (int i = 0; i < local_nodes; i++) {
+    double d = fabs (Au_plain[i] - Au_opt[i]);
+    if (d > maxdiff) maxdiff = d;
+  }
+  printf ("{\"elements\": %d, \"local_nodes\": %d, \"t_mesh_s\": %.6f, \"t_apply_plain_s\": %.6f, "
+          "\"t_apply_with_opt_s\": %.6f, \"plain_vs_opt_maxabs\": %.3e, \"u_sum\": %.17g, \"Au_sum\": %.17g}\n",
+          (int) p4est->local_num_quadrants, local_nodes, t_mesh, best_plain, best_opt, maxdiff,
+          d4est_util_sum_array_dbl (u, local_nodes), d4est_util_sum_array_dbl (Au_plain, local_nodes));
+
+  if (strcmp (out, "-")) {
+    d4est_b200_flat_t *flat = d4est_b200_flatten (p4est, d4est_ghost, d4est_factors, flux_plain);
+    if (bc_poly) {
+      /* Dirichlet data at boundary quadrature points, evaluated the way
+       * d4est_laplacian_flux_sipg_dirichlet_aux does for EVAL_BNDRY_FCN_ON_LOBATTO
+       * (d4est_laplacian_flux_sipg.c:105-137): g on the face LGL nodes, then
+       * interpolated to the Gauss points */
+      flat->dirichlet_g = calloc (flat->desc.local_mortar_nodes_quad + 1, sizeof (double));
+      for (int s = 0; s < flat->desc.n_sides; s++) {
+        if (flat->desc.side_faces_p[s] != 0) continue;
+        int e = flat->desc.side_e_m[4 * s];
+        int f_m = flat->desc.side_f_m[s];
+        int deg = flat->desc.deg[e], deg_quad = flat->desc.deg_quad[e];
+        int fn = d4est_lgl_get_nodes (2, deg), fnq = d4est_lgl_get_nodes (2, deg_quad);
+        int bstride = 3 * d4est_factors->local_strides[e].boundary_quad_stride[f_m];
+        double *g_lob = P4EST_ALLOC (double, fn);
+        for (int i = 0; i < fn; i++)
+          g_lob[i] = drv_poly_fcn (d4est_factors->xyz_m_mortar_lobatto[bstride + 0 * fnq + i],
+                                   d4est_factors->xyz_m_mortar_lobatto[bstride + 1 * fnq + i],
+                                   d4est_factors->xyz_m_mortar_lobatto[bstride + 2 * fnq + i], NULL);
+        d4est_quadrature_mortar_t face_object;
+        memset (&face_object, 0, sizeof (face_object));
+        d4est_quadrature_interpolate (d4est_ops, d4est_quad, d4est_geom, &face_object,
+                                      QUAD_OBJECT_MORTAR, QUAD_INTEGRAND_UNKNOWN, g_lob, deg,
+                                      &flat->dirichlet_g[flat->desc.side_mortar_stride[s]], deg_quad);
+        P4EST_FREE (g_lob);
+      }
+      flat->desc.dirichlet_g_mortar_quad = flat->dirichlet_g;
+    }
+    FILE *f = d4b_dump_open (out);
+    dump_desc (f, &flat->desc);
+    d4b_dump_put1 (f, "xyz", D4B_F64, 3 * (uint64_t) local_nodes, d4est_factors->xyz);
+    d4b_dump_put1 (f, "u", D4B_F64, local_nodes, u);
+    d4b_dump_put1 (f, "Au_plain", D4B_F64, local_nodes, Au_plain);
+    d4b_dump_put1 (f, "Au_with_opt", D4B_F64, local_nodes, Au_opt);
+    int max_deg = 1;
+    for (int e = 0; e < flat->desc.n_local; e++)
+      if (flat->desc.deg_quad[e] > max_deg) max_deg = flat->desc.deg_quad[e];
+    dump_tables (f, d4est_ops, max_deg);
+
+    if (cheby_imax > 0) {
+      /* stiffness-only apply, for the volume kernel in isolation */
+      double *Ku = P4EST_ALLOC_ZERO (double, local_nodes);
+      d4est_laplacian_apply_stiffness_matrix (p4est, d4est_ops, d4est_geom, d4est_quad,
+                                              d4est_factors, u, Ku, local_nodes, 0);
+      d4b_dump_put1 (f, "Ku", D4B_F64, local_nodes, Ku);
+      P4EST_FREE (Ku);
+    }
+    fclose (f);
+    d4est_b200_flat_destroy (flat);
+  }
+
+  P4EST_FREE (Au_tmp);
+  P4EST_FREE (u);
+  P4EST_FREE (Au_plain);
+  P4EST_FREE (Au_opt);
+  d4est_ghost_data_destroy (d4est_ghost_data);
+  d4est_laplacian_flux_destroy (flux_plain);
+  d4est_laplacian_with_opt_flux_destroy (flux_opt);
+  d4est_ghost_destroy (d4est_ghost);
+  d4est_mesh_initial_extents_destroy (initial_grid_input);
+  d4est_quadrature_destroy (p4est, d4est_ops, d4est_geom, d4est_quad);
+  d4est_mesh_data_destroy (d4est_factors);
+  d4est_ops_destroy (d4est_ops);
+  p4est_destroy (p4est);
+  d4est_geometry_destroy (d4est_geom);
+  zlog_fini ();
+  sc_finalize ();
+  sc_MPI_Finalize ();
+  return 0;
+}
