@@ -1,0 +1,25 @@
+#!/bin/bash
+# make_golden.sh -- regenerate tests/golden/*.d4b.gz from the UNMODIFIED
+# reference (oracle/_ref/ref_driver, built by oracle/build_ref.sh).
+# TEST INFRASTRUCTURE.  Each fixture holds the flattened mesh description, the
+# seeded input vector u (srand(102321), as d4est_test_laplacian_speedup.c:429)
+# and the reference's outputs Au_plain / Au_with_opt (+ its 1-D tables).
+set -e
+HERE="$(cd "$(dirname "$0")" && pwd)"
+DRV="$HERE/_ref/ref_driver"
+G="$HERE/../tests/golden"
+mkdir -p "$G"
+run() { # name ini args...
+  local name=$1 ini=$2; shift 2
+  "$DRV" "$HERE/configs/$ini" "$G/$name.d4b" "$@" > "$G/$name.json"
+  gzip -9nf "$G/$name.d4b"
+  echo "$name: $(cat "$G/$name.json")"
+}
+run brick_l2_p1 brick_poisson.ini                       # the 4^3 p=1 mesh of d4est_test_poisson_sinx.sh
+run brick_l2_p2_bc brick_poisson.ini --uniform-deg 2 --bc poly
+run brick_l2_p3 brick_poisson.ini --uniform-deg 3 --cheby 1 1
+run brick_l2_p5 brick_poisson.ini --uniform-deg 5
+run brick_l2_p7 brick_poisson.ini --uniform-deg 7
+run sphere_p2 sphere_p.ini --uniform-deg 2               # conforming, 13 trees, all face orientations
+run sphere_hp_amr0 sphere_hp.ini --bc poly               # per-region degrees + quadrature increments
+run sphere_hp_amr1 sphere_hp.ini --amr 1 --bc poly       # random hp refinement: hanging faces
