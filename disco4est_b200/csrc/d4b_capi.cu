@@ -1,0 +1,79 @@
+// d4b_capi.cu -- extern "C" entry points of libd4est_b200 (include/d4est_b200.h).
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include "d4b_internal.h"
+
+namespace {
+d4b_abort_hook_t g_abort_hook = nullptr;
+}
+
+void d4b_abort_impl(const char *file, int line, const char *fmt, ...) {
+  char msg[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(msg, sizeof(msg), fmt, ap);
+  va_end(ap);
+  if (g_abort_hook) g_abort_hook(file, line, msg);
+  // reference convention: D4EST_ABORT -> SC_ABORT, never returns
+  // (src/Utilities/d4est_util.h:171)
+  fprintf(stderr, "[D4B_ABORT] %s:%d %s\n", file, line, msg);
+  fflush(stderr);
+  abort();
+}
+
+extern "C" void d4b_set_abort_hook(d4b_abort_hook_t hook) { g_abort_hook = hook; }
+extern "C" int d4b_abi_version(void) { return D4B_ABI_VERSION; }
+
+extern "C" int d4b_device_count(void) {
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+extern "C" void d4b_init(int device) {
+  D4B_CHECK(d4b_device_count() > 0, "d4b_init: no CUDA device (there is no CPU fallback)");
+  D4B_CUDA(cudaSetDevice(device));
+  D4B_CUDA(cudaFree(0));
+}
+
+namespace {
+bool is_device_ptr(const void *p) {
+  cudaPointerAttributes at;
+  cudaError_t e = cudaPointerGetAttributes(&at, p);
+  if (e != cudaSuccess) { cudaGetLastError(); return false; }
+  return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
+}
+
+void apply_impl(d4b_mesh *m, const double *u, double *Au, int stiffness_only) {
+  D4B_CHECK(m && u && Au, "d4b_apply: NULL argument");
+  D4B_CHECK(m->n_ghost == 0 || m->d_ughost, "d4b_apply: ghost buffer missing");
+  bool u_dev = is_device_ptr(u), Au_dev = is_device_ptr(Au);
+  const double *du = u;
+  double *dAu = Au;
+  size_t bytes = (size_t)m->local_nodes * sizeof(double);
+  if (!u_dev) {
+    D4B_CUDA(cudaMemcpyAsync(m->d_u_stage, u, bytes, cudaMemcpyHostToDevice, m->stream));
+    du = m->d_u_stage;
+  }
+  if (!Au_dev) dAu = m->d_Au_stage;
+  if (stiffness_only) {
+    d4b_launch_generic(m, du, dAu, 1);
+  } else {
+    d4b_launch_fast(m, du, dAu);
+    d4b_launch_generic(m, du, dAu, 0);
+  }
+  if (!Au_dev) D4B_CUDA(cudaMemcpyAsync(Au, dAu, bytes, cudaMemcpyDeviceToHost, m->stream));
+  if (!u_dev || !Au_dev) D4B_CUDA(cudaStreamSynchronize(m->stream));
+}
+}  // namespace
+
+extern "C" void d4b_apply(d4b_mesh_t *m, const double *u, double *Au) { apply_impl(m, u, Au, 0); }
+extern "C" void d4b_apply_stiffness(d4b_mesh_t *m, const double *u, double *Au) { apply_impl(m, u, Au, 1); }
+extern "C" void d4b_sync(d4b_mesh_t *m) { D4B_CUDA(cudaStreamSynchronize(m->stream)); }
+extern "C" void d4b_set_stream(d4b_mesh_t *m, void *cuda_stream) {
+  D4B_CUDA(cudaStreamSynchronize(m->stream));
+  if (m->own_stream) { cudaStreamDestroy(m->stream); m->own_stream = false; }
+  m->stream = (cudaStream_t)cuda_stream;
+}

@@ -1,0 +1,118 @@
+// d4b_internal.h -- internal declarations of libd4est_b200 (not installed).
+//
+// Device-resident mesh for the matrix-free SIPG apply.  See DESIGN.md for the
+// layout; include/d4est_b200.h is the public C ABI.
+#ifndef D4B_INTERNAL_H
+#define D4B_INTERNAL_H
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <vector>
+#include "d4est_b200.h"
+
+#define D4B_MAXN 8     // max LGL nodes per direction (deg <= 7)
+#define D4B_MAXNQ 12   // max Gauss nodes per direction handled by the generic kernel
+
+void d4b_abort_impl(const char *file, int line, const char *fmt, ...);
+#define D4B_ABORT(...) d4b_abort_impl(__FILE__, __LINE__, __VA_ARGS__)
+#define D4B_CHECK(cond, ...) do { if (!(cond)) D4B_ABORT(__VA_ARGS__); } while (0)
+#define D4B_CUDA(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) \
+    D4B_ABORT("CUDA error %s: %s", #call, cudaGetErrorString(e_)); } while (0)
+
+// ---- 1-D operator tables (host builders, d4b_tables.cpp) --------------------
+// Replace the lazily built tables of d4est_operators_t
+// (src/dGMath/d4est_operators.c:196-304, :411-438, :855-872, :944-1012).
+void d4b_tab_lobatto(int n, double *x, double *w);
+void d4b_tab_gauss(int n, double *x, double *w);
+// D[n x n] on LGL nodes, row-major
+void d4b_tab_deriv(int n, const double *x, double *D);
+// E[nq x n]: Lagrange basis on x[0..n) evaluated at y[0..nq)
+void d4b_tab_eval(int n, const double *x, int nq, const double *y, double *E);
+
+// Table block on the device: for every (deg, deg_q, half) the evaluation
+// matrix E and for every deg the derivative matrix; offsets in doubles.
+struct D4bTables {
+  // E index: ((deg-1)*D4B_MAXNQ + (deg_q-1))*3 + half -> offset of [nq x n]
+  int32_t e_off[D4B_MAXN * D4B_MAXNQ * 3];
+  int32_t d_off[D4B_MAXN];      // deg-1 -> offset of D [n x n]
+  int32_t w_off[D4B_MAXNQ];     // deg_q-1 -> offset of Gauss weights [nq]
+};
+
+// ---- fast-path element classes ----------------------------------------------
+// A "regular" element: deg_quad == deg, all six faces conforming against a
+// neighbour of the same degree (or a physical boundary), everything local.
+struct D4bFastClass {
+  int deg = 0;
+  int n_elem = 0;
+  int32_t *d_elem = nullptr;     // [n_elem] element ids
+};
+
+struct d4b_mesh {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = true;
+  int32_t n_local = 0, n_ghost = 0, n_sides = 0;
+  int64_t local_nodes = 0, local_nodes_quad = 0, mortar_nodes = 0, ghost_nodes = 0;
+  int max_deg = 0, max_deg_quad = 0;
+  int64_t device_bytes = 0;
+
+  // tables
+  D4bTables tab;                 // host copy of offsets
+  D4bTables *d_tab = nullptr;
+  double *d_tabdata = nullptr;
+
+  // per element
+  int32_t *d_deg = nullptr, *d_deg_quad = nullptr;
+  int64_t *d_nodal_stride = nullptr, *d_quad_stride = nullptr;
+  int32_t *d_ghost_deg = nullptr, *d_ghost_deg_quad = nullptr;
+  int64_t *d_ghost_nodal_stride = nullptr;
+  // volume metric: G[c][quad point], c = 0..5 <-> (00,01,02,11,12,22),
+  // G_{l'l} = w_r w_s w_t J sum_k rst[l][k] rst[l'][k]
+  double *d_G = nullptr;
+  // per element-face: flux side record and position inside it
+  int32_t *d_elem_side = nullptr;   // [6*n_local]
+  int32_t *d_elem_sub = nullptr;    // [6*n_local]
+  // side records
+  int32_t *d_side_faces_m = nullptr, *d_side_faces_p = nullptr, *d_side_f_m = nullptr,
+          *d_side_f_p = nullptr, *d_side_e_m = nullptr, *d_side_e_p = nullptr,
+          *d_side_perm = nullptr, *d_side_sub_order = nullptr;
+  int64_t *d_side_mortar_stride = nullptr;
+  // folded mortar data, 8 planes of mortar_nodes doubles, (-)-side ordering:
+  // 0..2 A_m[l] = sj sum_d n_d drst_m[l][d]   (x 1/2 on a big (-) side)
+  // 3..5 A_p[l] = sj sum_d n_d drst_p[l][d]   (x 1/2 on a big (+) side)
+  // 6    S     = sj sigma
+  // 7    g     Dirichlet data (boundary sides), 0 elsewhere
+  double *d_mortar = nullptr;
+
+  // ghost values (filled by the exchange)
+  double *d_ughost = nullptr;
+
+  // staging for host-pointer calls
+  double *d_u_stage = nullptr, *d_Au_stage = nullptr;
+  // scratch for reductions / smoother
+  double *d_red = nullptr;         // partial sums
+  double *h_red = nullptr;         // pinned
+  double *d_work[4] = {nullptr, nullptr, nullptr, nullptr};
+
+  // fast path
+  std::vector<D4bFastClass> fast;
+  int n_generic = 0;
+  int32_t *d_generic_elem = nullptr;   // elements handled by the generic kernel
+  // fast-path face data, see d4b_fast.cu
+  double *d_fast_face = nullptr;
+  int32_t *d_fast_nbr = nullptr;
+  int generic_smem = 0;
+};
+
+template <typename T>
+T *d4b_dev_alloc(d4b_mesh *m, size_t n);
+template <typename T>
+T *d4b_dev_upload(d4b_mesh *m, const T *h, size_t n);
+
+// kernels / launchers
+void d4b_launch_generic(d4b_mesh *m, const double *d_u, double *d_Au, int stiffness_only);
+void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *desc, const std::vector<double> &mortar,
+                    const std::vector<int32_t> &elem_side, std::vector<char> &is_fast);
+void d4b_launch_fast(d4b_mesh *m, const double *d_u, double *d_Au);
+
+#endif

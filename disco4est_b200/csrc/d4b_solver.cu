@@ -1,0 +1,218 @@
+// d4b_solver.cu -- device-resident BLAS-1, cg_eigs and the Chebyshev smoother.
+//
+// Replaces, for device-resident vectors:
+//   d4est_linalg_vec_axpy/xpby/scale/dot   src/LinearAlgebra/d4est_linalg.c:179-236
+//   cg_eigs                                src/Solver/d4est_solver_cg_eigs.c:115-276
+//   ..._smoother_cheby_iterate_aux         src/Solver/d4est_solver_multigrid_smoother_cheby.c:81-176
+// Reductions are deterministic: fixed grid, fixed-shape tree, no atomics.
+#include <cmath>
+#include "d4b_internal.h"
+
+namespace {
+
+constexpr int kRedBlocks = 592;    // 4 x 148 SMs
+constexpr int kRedThreads = 256;
+
+__global__ void __launch_bounds__(kRedThreads) dot_partial(const double *__restrict__ x,
+                                                           const double *__restrict__ y, int64_t n,
+                                                           double *__restrict__ part) {
+  __shared__ double sh[kRedThreads];
+  int64_t chunk = (n + gridDim.x - 1) / gridDim.x;
+  int64_t lo = (int64_t)blockIdx.x * chunk, hi = lo + chunk < n ? lo + chunk : n;
+  double s = 0.;
+  for (int64_t i = lo + threadIdx.x; i < hi; i += kRedThreads) s += x[i] * y[i];
+  sh[threadIdx.x] = s;
+  __syncthreads();
+  for (int w = kRedThreads / 2; w > 0; w >>= 1) {
+    if (threadIdx.x < w) sh[threadIdx.x] += sh[threadIdx.x + w];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) part[blockIdx.x] = sh[0];
+}
+
+__global__ void __launch_bounds__(1024) dot_final(const double *__restrict__ part, int np,
+                                                   double *__restrict__ out) {
+  __shared__ double sh[1024];
+  sh[threadIdx.x] = (threadIdx.x < np) ? part[threadIdx.x] : 0.;
+  __syncthreads();
+  for (int w = 512; w > 0; w >>= 1) {
+    if (threadIdx.x < w) sh[threadIdx.x] += sh[threadIdx.x + w];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *out = sh[0];
+}
+
+__global__ void axpy_k(double a, const double *__restrict__ x, double *__restrict__ y, int64_t n) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    y[i] += a * x[i];
+}
+// y = x + b y   (d4est_linalg_vec_xpby, d4est_linalg.c:200-215)
+__global__ void xpby_k(const double *__restrict__ x, double b, double *__restrict__ y, int64_t n) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    y[i] = x[i] + b * y[i];
+}
+__global__ void scale_k(double a, double *__restrict__ x, int64_t n) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    x[i] *= a;
+}
+// r = rhs - Au
+__global__ void residual_k(const double *__restrict__ rhs, const double *__restrict__ Au,
+                           double *__restrict__ r, int64_t n) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    r[i] = rhs[i] - Au[i];
+}
+// r = rhs - Au ; d = r   (cg_eigs start)
+__global__ void residual2_k(const double *__restrict__ rhs, const double *__restrict__ Au,
+                            double *__restrict__ r, double *__restrict__ d, int64_t n) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    double v = rhs[i] - Au[i];
+    r[i] = v; d[i] = v;
+  }
+}
+// CG update: u += alpha d ; r -= alpha Au
+__global__ void cg_update_k(double alpha, const double *__restrict__ d, const double *__restrict__ Au,
+                            double *__restrict__ u, double *__restrict__ r, int64_t n) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    u[i] += alpha * d[i];
+    r[i] -= alpha * Au[i];
+  }
+}
+// Chebyshev update: p = alpha (rhs - Au) + beta p ; u += p
+__global__ void cheby_update_k(double alpha, double beta, const double *__restrict__ rhs,
+                               const double *__restrict__ Au, double *__restrict__ p,
+                               double *__restrict__ u, int64_t n) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    double r = (rhs[i] - Au[i]) * alpha;
+    double pn = r + beta * p[i];
+    p[i] = pn;
+    u[i] += pn;
+  }
+}
+
+inline int grid_for(int64_t n) {
+  int64_t b = (n + 255) / 256;
+  return (int)(b < 148 * 8 ? (b > 0 ? b : 1) : 148 * 8);
+}
+
+double *work(d4b_mesh *m, int i) {
+  if (!m->d_work[i]) m->d_work[i] = d4b_dev_alloc<double>(m, (size_t)m->local_nodes);
+  return m->d_work[i];
+}
+
+bool is_dev(const void *p) {
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
+}
+
+}  // namespace
+
+extern "C" double d4b_vec_dot(d4b_mesh_t *m, const double *x, const double *y, int64_t n) {
+  dot_partial<<<kRedBlocks, kRedThreads, 0, m->stream>>>(x, y, n, m->d_red);
+  dot_final<<<1, 1024, 0, m->stream>>>(m->d_red, kRedBlocks, m->d_red + kRedBlocks);
+  D4B_CUDA(cudaMemcpyAsync(m->h_red, m->d_red + kRedBlocks, sizeof(double), cudaMemcpyDeviceToHost, m->stream));
+  D4B_CUDA(cudaStreamSynchronize(m->stream));
+  return m->h_red[0];
+}
+extern "C" void d4b_vec_axpy(d4b_mesh_t *m, double a, const double *x, double *y, int64_t n) {
+  axpy_k<<<grid_for(n), 256, 0, m->stream>>>(a, x, y, n);
+}
+extern "C" void d4b_vec_xpby(d4b_mesh_t *m, const double *x, double b, double *y, int64_t n) {
+  xpby_k<<<grid_for(n), 256, 0, m->stream>>>(x, b, y, n);
+}
+extern "C" void d4b_vec_scale(d4b_mesh_t *m, double a, double *x, int64_t n) {
+  scale_k<<<grid_for(n), 256, 0, m->stream>>>(a, x, n);
+}
+
+// Gershgorin bounds of the Lanczos tridiagonal, d4est_solver_cg_eigs.c:9-65
+static void gershgorin(int use_new, int i, int64_t n, double a0, double b0, double a1, double b1,
+                       double *mx) {
+  double diag, off;
+  if (!use_new) {
+    if (i != 0 && i < n - 1) { diag = 1. / a1 + b0 / a0; off = fabs(sqrt(b1) / a1) + fabs(sqrt(b0) / a0); }
+    else if (i == 0) { diag = 1. / a1; off = sqrt(b1) / a1; }
+    else { diag = 1. / a1 + b0 / a0; off = fabs(sqrt(b0) / a0); }
+  } else {
+    if (i != 0) { diag = 1. / a1 + b0 / a0; off = fabs(sqrt(b0) / a0); }
+    else { diag = 1. / a1; off = sqrt(b1) / a1; }
+  }
+  *mx = diag + off;
+}
+
+extern "C" double d4b_cg_eigs(d4b_mesh_t *m, double *u, const double *rhs, int32_t imax,
+                              int32_t use_new, int32_t use_zero_guess) {
+  const int64_t n = m->local_nodes;
+  const size_t bytes = (size_t)n * sizeof(double);
+  bool u_dev = is_dev(u), rhs_dev = is_dev(rhs);
+  double *du = u_dev ? u : work(m, 2);
+  const double *drhs = rhs;
+  if (!rhs_dev) {
+    D4B_CUDA(cudaMemcpyAsync(m->d_u_stage, rhs, bytes, cudaMemcpyHostToDevice, m->stream));
+    drhs = m->d_u_stage;
+  }
+  if (!u_dev) D4B_CUDA(cudaMemcpyAsync(du, u, bytes, cudaMemcpyHostToDevice, m->stream));
+  if (use_zero_guess) {
+    // the reference iterates on a scratch zero vector and leaves u untouched
+    // (d4est_solver_multigrid_smoother_cheby.c:281-305)
+    du = work(m, 3);
+    D4B_CUDA(cudaMemsetAsync(du, 0, bytes, m->stream));
+  }
+  double *Au = m->d_Au_stage, *d = work(m, 0), *r = work(m, 1);
+  const int g = grid_for(n);
+  d4b_apply(m, du, Au);
+  residual2_k<<<g, 256, 0, m->stream>>>(drhs, Au, r, d, n);
+  double delta_new = d4b_vec_dot(m, r, r, n);
+  double alpha = -1., beta = -1., bound = 0.;
+  for (int i = 0; i < imax; ++i) {
+    d4b_apply(m, d, Au);
+    double d_dot_Au = d4b_vec_dot(m, d, Au, n);
+    double alpha_old = alpha;
+    alpha = delta_new / d_dot_Au;
+    cg_update_k<<<g, 256, 0, m->stream>>>(alpha, d, Au, du, r, n);
+    double delta_old = delta_new;
+    delta_new = d4b_vec_dot(m, r, r, n);
+    double beta_old = beta;
+    beta = delta_new / delta_old;
+    xpby_k<<<g, 256, 0, m->stream>>>(r, beta, d, n);
+    double tmax;
+    gershgorin(use_new, i, n, alpha_old, beta_old, alpha, beta, &tmax);
+    bound = (i > 0) ? fmax(bound, tmax) : tmax;
+  }
+  if (!u_dev && !use_zero_guess)
+    D4B_CUDA(cudaMemcpyAsync(u, du, bytes, cudaMemcpyDeviceToHost, m->stream));
+  D4B_CUDA(cudaStreamSynchronize(m->stream));
+  return bound;
+}
+
+extern "C" void d4b_cheby_smooth(d4b_mesh_t *m, double *u, const double *rhs, double *r, int32_t iter,
+                                 double lmin, double lmax) {
+  const int64_t n = m->local_nodes;
+  const size_t bytes = (size_t)n * sizeof(double);
+  bool u_dev = is_dev(u), rhs_dev = is_dev(rhs), r_dev = is_dev(r);
+  double *du = u_dev ? u : work(m, 2);
+  const double *drhs = rhs;
+  if (!rhs_dev) {
+    D4B_CUDA(cudaMemcpyAsync(m->d_u_stage, rhs, bytes, cudaMemcpyHostToDevice, m->stream));
+    drhs = m->d_u_stage;
+  }
+  if (!u_dev) D4B_CUDA(cudaMemcpyAsync(du, u, bytes, cudaMemcpyHostToDevice, m->stream));
+  double *Au = m->d_Au_stage, *p = work(m, 0);
+  double *dr = r_dev ? r : work(m, 1);
+  const int g = grid_for(n);
+  const double d = (lmax + lmin) * .5, c = (lmax - lmin) * .5;
+  double alpha = 0., beta;
+  D4B_CUDA(cudaMemsetAsync(p, 0, bytes, m->stream));
+  for (int i = 0; i < iter; ++i) {
+    d4b_apply(m, du, Au);
+    if (i == 0) alpha = 1. / d;
+    else if (i == 1) alpha = 2. * d / (2 * d * d - c * c);
+    else alpha = 1. / (d - (alpha * c * c / 4.));
+    beta = alpha * d - 1.;
+    cheby_update_k<<<g, 256, 0, m->stream>>>(alpha, beta, drhs, Au, p, du, n);
+  }
+  d4b_apply(m, du, Au);
+  residual_k<<<g, 256, 0, m->stream>>>(drhs, Au, dr, n);
+  if (!u_dev) D4B_CUDA(cudaMemcpyAsync(u, du, bytes, cudaMemcpyDeviceToHost, m->stream));
+  if (!r_dev) D4B_CUDA(cudaMemcpyAsync(r, dr, bytes, cudaMemcpyDeviceToHost, m->stream));
+  if (!u_dev || !r_dev) D4B_CUDA(cudaStreamSynchronize(m->stream));
+}

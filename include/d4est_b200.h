@@ -166,6 +166,10 @@ void d4b_apply(d4b_mesh_t *mesh, const double *u, double *Au);
  * (d4est_laplacian.c:197-234)                                              */
 void d4b_apply_stiffness(d4b_mesh_t *mesh, const double *u, double *Au);
 void d4b_sync(d4b_mesh_t *mesh);
+/* run all work of this mesh on the caller's CUDA stream (a cudaStream_t passed
+ * as void*; NULL = the legacy default stream).  The library otherwise uses a
+ * private non-blocking stream.                                             */
+void d4b_set_stream(d4b_mesh_t *mesh, void *cuda_stream);
 
 /* --------------------------------------------------------------- BLAS-1  */
 /* device-resident vector ops, src/LinearAlgebra/d4est_linalg.c:179-236;
@@ -188,9 +192,12 @@ typedef struct d4b_cheby_params
 } d4b_cheby_params_t;
 
 /* cg_eigs (src/Solver/d4est_solver_cg_eigs.c:115-276): runs imax CG steps on
- * A x = rhs from x0 = u (or zero) and returns the Gershgorin bound of the
- * Lanczos tridiagonal.  u, rhs host or device; not modified.               */
-double d4b_cg_eigs(d4b_mesh_t *mesh, const double *u, const double *rhs,
+ * A x = rhs starting from x0 = u and returns the Gershgorin bound of the
+ * Lanczos tridiagonal.  As in the reference, u IS ADVANCED by those CG steps
+ * (cg_eigs works on vecs->u in place, :206) unless use_zero_guess is set, in
+ * which case a scratch zero vector is iterated and u is untouched
+ * (d4est_solver_multigrid_smoother_cheby.c:281-305).  u, rhs host or device. */
+double d4b_cg_eigs(d4b_mesh_t *mesh, double *u, const double *rhs,
                    int32_t imax, int32_t use_new, int32_t use_zero_guess);
 
 /* Chebyshev recurrence (…smoother_cheby.c:81-176) with spectrum [lmin,lmax]:
