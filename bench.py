@@ -1,0 +1,283 @@
+#!/usr/bin/env python
+"""bench.py -- GDOF/s of the matrix-free SIPG apply (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--level L] [--deg P]
+                  [--impl ours|reference] [--sweep]
+
+One "step" = one apply_lhs (Au = A u) over the whole mesh.  Workload at N=1:
+BASELINE.json configs[1], the unit-cube Poisson SIPG apply on 64^3 elements at
+p=3 (16.8 M DOF), synthetic mesh (disco4est_b200/brick.py), random input
+vector.  Inputs (134 MB vector + ~1.5 GB of geometric factors) are larger than
+the 126 MB L2, so no explicit L2 flush is needed between timed iterations.
+
+Prints ONE JSON line (rank 0).  `--impl reference` times the unmodified
+reference's CPU apply (oracle/_ref/ref_driver) on the host cores instead.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "GDOF/s of matrix-free SIPG apply (apply_lhs)"
+UNIT = "GDOF/s"
+REF_DRIVER = os.path.join(ROOT, "oracle", "_ref", "ref_driver")
+BRICK_INI = os.path.join(ROOT, "oracle", "configs", "brick_poisson.ini")
+
+
+def algorithmic_bytes_per_dof(p):
+    """8 (u) + 8 (Au) + 48 (6 metric comps) + 168/N (7 face doubles x 3 faces)."""
+    return 64.0 + 168.0 / (p + 1)
+
+
+def measured_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        return float(json.load(open(path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            parts = [x.strip() for x in ln.split(",")]
+            if len(parts) < 8:
+                continue
+            try:
+                sm.append(float(parts[0])); mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for nm, val in zip(names, parts[4:8]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None,
+                "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def run_ref_driver(level, deg, reps, out="-"):
+    """One run of the reference binary on a 2^level cube; returns its JSON line."""
+    ini = "/tmp/d4b_bench_%d_%d_%d.ini" % (os.getpid(), threading.get_ident(), level)
+    txt = open(BRICK_INI).read().replace("min_level = 2", "min_level = %d" % level)
+    open(ini, "w").write(txt)
+    res = subprocess.run([REF_DRIVER, ini, out, "--uniform-deg", str(deg), "--time", str(reps)],
+                         capture_output=True, text=True, check=True)
+    os.unlink(ini)
+    return json.loads(res.stdout.strip().splitlines()[-1])
+
+
+def cpu_baseline(deg):
+    """Reference CPU apply on ONE host core, bounded sample (about 10-20 s)."""
+    level = 4 if deg <= 3 else 3
+    if os.path.exists(REF_DRIVER):
+        r = run_ref_driver(level, deg, 2)
+        t = min(r["t_apply_plain_s"], r["t_apply_with_opt_s"])
+        return {"value": r["local_nodes"] / t / 1e9, "unit": UNIT, "cores": 1, "kind": "reference",
+                "sample": "unmodified reference d4est_laplacian[_with_opt]_apply_aij, %d^3-element unit cube p=%d "
+                          "(%d DOF), best of 3 applies of the faster variant, 1 core (serial build, no MPI)"
+                          % (1 << level, deg, r["local_nodes"])}
+    import numpy as np
+    import oracle_lib
+    from disco4est_b200.brick import brick_desc
+    A = brick_desc(level - 1, deg)
+    O = oracle_lib.Oracle(A)
+    u = np.random.default_rng(0).standard_normal(O.n)
+    t0 = time.perf_counter(); O.apply(u); t = time.perf_counter() - t0
+    return {"value": O.n / t / 1e9, "unit": UNIT, "cores": 1, "kind": "port",
+            "sample": "oracle/d4b_oracle C restatement, %d^3 cube p=%d, 1 apply, 1 core" % (1 << (level - 1), deg)}
+
+
+def bench_reference(args):
+    """--impl reference: the reference's CPU apply on all host cores.  The
+    serial build has no MPI, so C independent processes each apply the operator
+    on its own 16^3 (p<=3) / 8^3 cube: aggregate throughput, no halo exchange."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    deg, level = args.deg, (4 if args.deg <= 3 else 3)
+    if not os.path.exists(REF_DRIVER):
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/ref_driver not built"}))
+        return
+    cores = max(1, min(os.cpu_count() or 1, 64))
+    times, dof = [], None
+    for step in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
+        procs = []
+        import concurrent.futures as cf
+        with cf.ThreadPoolExecutor(cores) as ex:
+            rs = list(ex.map(lambda _: run_ref_driver(level, deg, 0), range(cores)))
+        dof = rs[0]["local_nodes"]
+        t_apply = max(min(r["t_apply_plain_s"], r["t_apply_with_opt_s"]) for r in rs)
+        if step >= args.warmup:
+            times.append(t_apply)
+    t = sum(times) / len(times)
+    v = cores * dof / t / 1e9
+    sample = ("%d independent serial processes of the unmodified reference, each one apply on a %d^3-element "
+              "unit cube p=%d (%d DOF); aggregate throughput, no halo exchange (MPI absent)"
+              % (cores, 1 << level, deg, dof))
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "unit-cube Poisson SIPG apply, p=%d (reference arm: bounded %d^3 sample per core)"
+                               % (deg, 1 << level)},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+def bench_ours(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    from disco4est_b200 import Mesh
+    from disco4est_b200.brick import brick_desc
+
+    level, deg = args.level, args.deg
+    A = brick_desc(level, deg)
+    mesh = Mesh(A, device=local_rank)
+    del A
+    n = mesh.n
+    stream = torch.cuda.current_stream()
+    mesh.set_stream(stream.cuda_stream)
+    g = torch.Generator(device=dev).manual_seed(102321 + rank)
+    u = torch.rand(n, dtype=torch.float64, device=dev, generator=g)
+    Au = torch.empty_like(u)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing (value) ----
+    for _ in range(max(args.warmup, 3)):
+        mesh.apply(u, Au)
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(stream)
+    for _ in range(args.steps):
+        mesh.apply(u, Au)
+    ev1.record(stream)
+    barrier()
+    t_dev = ev0.elapsed_time(ev1) * 1e-3 / args.steps
+    # ---- end to end through the C ABI with host buffers ----
+    hu = torch.empty(n, dtype=torch.float64).pin_memory()
+    hu.copy_(u.cpu())
+    hAu = torch.empty(n, dtype=torch.float64).pin_memory()
+    e2e_steps = max(2, min(args.steps, 10))
+    mesh.apply(hu.numpy(), hAu.numpy())
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        mesh.apply(hu.numpy(), hAu.numpy())   # H2D u, apply, D2H Au, synchronous
+    barrier()
+    t_e2e = (time.perf_counter() - t0) / e2e_steps
+    clocks = sampler.stop() if rank == 0 else None
+    checksum = float(hAu.sum())
+
+    tt = torch.tensor([t_dev, t_e2e], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    t_dev, t_e2e = float(tt[0]), float(tt[1])
+    total_dof = n * world
+    if rank == 0:
+        peak, peak_src = measured_peak()
+        bytes_launch = n * algorithmic_bytes_per_dof(deg)
+        achieved = bytes_launch / t_dev / 1e9
+        out = {
+            "metric": METRIC, "value": total_dof / t_dev / 1e9, "unit": UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": 1e3 * t_dev,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": "unit-cube Poisson SIPG apply, %d^3 elements per GPU, p=%d, deg_quad=p, "
+                                   "Gauss quadrature, SIPG prefactor 2 maxp_sqr_over_minh, homogeneous Dirichlet"
+                                   % (1 << level, deg),
+                       "dof_per_gpu": n, "l2": "inputs larger than L2 (no flush needed)",
+                       "fast_kernel_elements": mesh.fast_elements(), "checksum_Au": checksum},
+            "e2e": {"value": total_dof / t_e2e / 1e9, "unit": UNIT,
+                    "h2d_bytes_per_step": 8 * n, "d2h_bytes_per_step": 8 * n},
+            "gpu_launches": args.steps * (1 if mesh.fast_elements() == (1 << (3 * level)) else 2),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "bytes_per_dof": algorithmic_bytes_per_dof(deg)},
+            "clocks": clocks,
+        }
+        if world == 1 and not args.no_cpu:
+            out["cpu_baseline"] = cpu_baseline(deg)
+        print(json.dumps(out))
+    mesh.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--level", type=int, default=6, help="2^level elements per direction")
+    ap.add_argument("--deg", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        bench_reference(args)
+    else:
+        bench_ours(args)
+
+
+if __name__ == "__main__":
+    main()

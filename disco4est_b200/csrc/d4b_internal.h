@@ -99,8 +99,9 @@ struct d4b_mesh {
   int n_generic = 0;
   int32_t *d_generic_elem = nullptr;   // elements handled by the generic kernel
   // fast-path face data, see d4b_fast.cu
-  double *d_fast_face = nullptr;
-  int32_t *d_fast_nbr = nullptr;
+  int64_t *d_fast_S = nullptr;         // [6*n_local] mortar stride of (e,f)
+  int32_t *d_fast_nbr = nullptr;       // [6*n_local] neighbour element / -1
+  int32_t *d_fast_code = nullptr;      // [6*n_local] f_p | perm << 3
   int generic_smem = 0;
 };
 

@@ -279,7 +279,7 @@ extern "C" void d4b_mesh_destroy(d4b_mesh_t *m) {
                   m->d_side_e_m, m->d_side_e_p, m->d_side_perm, m->d_side_sub_order,
                   m->d_side_mortar_stride, m->d_mortar, m->d_ughost, m->d_u_stage, m->d_Au_stage,
                   m->d_red, m->d_work[0], m->d_work[1], m->d_work[2], m->d_work[3], m->d_generic_elem,
-                  m->d_fast_face, m->d_fast_nbr};
+                  m->d_fast_S, m->d_fast_nbr, m->d_fast_code};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   for (auto &c : m->fast)
@@ -291,3 +291,4 @@ extern "C" void d4b_mesh_destroy(d4b_mesh_t *m) {
 
 extern "C" int64_t d4b_mesh_local_nodes(const d4b_mesh_t *m) { return m->local_nodes; }
 extern "C" int64_t d4b_mesh_device_bytes(const d4b_mesh_t *m) { return m->device_bytes; }
+extern "C" int64_t d4b_mesh_fast_elements(const d4b_mesh_t *m) { return m->n_local - m->n_generic; }

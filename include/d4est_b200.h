@@ -154,6 +154,9 @@ void        d4b_mesh_destroy(d4b_mesh_t *mesh);
 int64_t     d4b_mesh_local_nodes(const d4b_mesh_t *mesh);
 /* bytes of device memory held by the mesh (geometric factors + tables)     */
 int64_t     d4b_mesh_device_bytes(const d4b_mesh_t *mesh);
+/* elements taken by the uniform-degree conforming kernel (the rest go through
+ * the general hp kernel); for reporting and tests                           */
+int64_t     d4b_mesh_fast_elements(const d4b_mesh_t *mesh);
 
 /* ------------------------------------------------------------------ apply */
 /* Au = A u; replaces d4est_laplacian_apply_aij / _with_opt_apply_aij

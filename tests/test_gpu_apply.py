@@ -89,3 +89,27 @@ def test_device_pointers_and_linearity(golden, meshes):
     Ah = np.zeros(m.n)
     m.apply(x.numpy(), Ah)
     assert np.array_equal(Ah, Ax.cpu().numpy())
+
+
+@pytest.mark.parametrize("case", ["brick_l2_p1", "brick_l2_p3", "brick_l2_p7", "sphere_p2"])
+def test_uniform_meshes_take_the_fast_kernel(golden, meshes, case):
+    A = golden(case)
+    m = meshes(case, A)
+    assert m.fast_elements() == int(A["n_local"][0])
+
+
+@pytest.mark.parametrize("case", ["brick_l2_p3", "sphere_p2", "sphere_hp_amr1"])
+def test_fast_and_general_kernels_agree(golden, case, monkeypatch):
+    from disco4est_b200 import Mesh
+
+    A = golden(case)
+    u = np.ascontiguousarray(A["u"])
+    m1 = Mesh(A)
+    monkeypatch.setenv("D4B_FORCE_GENERIC", "1")
+    m2 = Mesh(A)
+    monkeypatch.delenv("D4B_FORCE_GENERIC")
+    assert m2.fast_elements() == 0
+    a1, a2 = np.zeros_like(u), np.zeros_like(u)
+    m1.apply(u, a1); m2.apply(u, a2)
+    assert rel(a1, a2) < 1e-13
+    m1.close(); m2.close()
