@@ -58,10 +58,10 @@ template <int N>
 struct Cfg {
   static constexpr int NN = N * N;
   static constexpr int N3 = N * N * N;
-  static constexpr int THREADS = 256;
+  static constexpr int THREADS = (N == 7 || N == 6) ? 256 : 128;
   static constexpr int EPB = THREADS / NN;           // elements per CTA
-  // shared doubles per element: V0,V1,V2 + FT,NB,NB2,FR (each 12*NN)
-  static constexpr int SH_PER_ELEM = 3 * N3 + 4 * 12 * NN;
+  // shared doubles per element: V0,V1,V2 + FT (12*NN) + NB, NB2 (4*NN each)
+  static constexpr int SH_PER_ELEM = 3 * N3 + 20 * NN;
 };
 
 __device__ __forceinline__ int perm_xy(int n, int perm, int a, int b, int &xp, int &yp) {
@@ -73,7 +73,7 @@ __device__ __forceinline__ int perm_xy(int n, int perm, int a, int b, int &xp, i
 }
 
 template <int N>
-__global__ void __launch_bounds__(256) fast_apply_kernel(FastArgs a) {
+__global__ void __launch_bounds__(Cfg<N>::THREADS) fast_apply_kernel(FastArgs a) {
   using C = Cfg<N>;
   constexpr int NN = C::NN, N3 = C::N3;
   extern __shared__ double smem[];
@@ -86,12 +86,10 @@ __global__ void __launch_bounds__(256) fast_apply_kernel(FastArgs a) {
   double *V0 = smem + (size_t)(slot < C::EPB ? slot : 0) * C::SH_PER_ELEM;
   double *V1 = V0 + N3, *V2 = V1 + N3;
   double *FT = V2 + N3;            // [6][2][NN] own trace / normal derivative
-  double *NB = FT + 12 * NN;       // [6][2][NN] neighbour stage
-  double *NB2 = NB + 12 * NN;      // [6][2][NN] neighbour stage 2 / weighted tangential term2
-  double *FR = NB2 + 12 * NN;      // [6][2][NN] face results (value / normal-derivative coefficient)
+  double *NB = FT + 12 * NN;       // [2][2][NN] neighbour stage (one face pair)
+  double *NB2 = NB + 4 * NN;       // [2][2][NN] neighbour stage 2 / weighted tangential term2
   const int e = active ? a.elem[ei] : 0;
   const int64_t ns = active ? a.nodal_stride[e] : 0;
-  double rt[N];                    // t-orientation residual line, live across the face phase
 
   // ---- forward: uh = (I x I x I) u ------------------------------------------
   if (active) {
@@ -202,178 +200,181 @@ __global__ void __launch_bounds__(256) fast_apply_kernel(FastArgs a) {
       V2[idx] = G01 * gr + G11 * gs + G12 * gt;
       ft[c] = G02 * gr + G12 * gs + G22 * gt;
     }
+    // V0 becomes the residual accumulator (each thread owns its own c-line here)
 #pragma unroll
     for (int c = 0; c < N; ++c) {
       double s = 0.;
 #pragma unroll
       for (int i = 0; i < N; ++i) s += T.Dg[i][c] * ft[i];
-      rt[c] = s;
+      V0[lx + N * ly + NN * c] = s;
     }
   }
 
-  // ---- faces: neighbour stage A (normal lines from global memory) -----------
-  int nbr[6], code[6];
-  int64_t fS[6];
-  if (active) {
+  // ---- faces, one opposite pair (same normal direction) at a time -------------
+  // thread (lx, ly) is face Gauss point (lx, ly) of both faces of the pair
+#pragma unroll 1
+  for (int nd = 0; nd < 3; ++nd) {
+    int nbr[2] = {-1, -1}, code[2] = {0, 0};
+    int64_t fS[2] = {0, 0};
+    if (active) {   // stage A: neighbour normal lines from global memory
 #pragma unroll
-    for (int f = 0; f < 6; ++f) {
-      nbr[f] = a.face_nbr[6 * e + f];
-      code[f] = a.face_code[6 * e + f];
-      fS[f] = a.face_S[6 * e + f];
-      if (nbr[f] >= 0) {
-        int fp = code[f] & 7, ndp = fp >> 1, sp = fp & 1;
-        const double *up = a.u + a.nodal_stride[nbr[f]];
-        int base, stride;
-        if (ndp == 0) { base = N * lx + NN * ly; stride = 1; }
-        else if (ndp == 1) { base = lx + NN * ly; stride = N; }
-        else { base = lx + N * ly; stride = NN; }
-        double dn = 0., tr = 0.;
+      for (int sd = 0; sd < 2; ++sd) {
+        const int f = 2 * nd + sd;
+        nbr[sd] = a.face_nbr[6 * e + f];
+        code[sd] = a.face_code[6 * e + f];
+        fS[sd] = a.face_S[6 * e + f];
+        if (nbr[sd] >= 0) {
+          int fp = code[sd] & 7, ndp = fp >> 1, sp = fp & 1;
+          const double *up = a.u + a.nodal_stride[nbr[sd]];
+          int base, stride;
+          if (ndp == 0) { base = N * lx + NN * ly; stride = 1; }
+          else if (ndp == 1) { base = lx + NN * ly; stride = N; }
+          else { base = lx + N * ly; stride = NN; }
+          double dn = 0., tr = 0.;
 #pragma unroll
-        for (int l = 0; l < N; ++l) {
-          double val = up[base + l * stride];
-          dn += T.DL[sp][l] * val;
-          if (l == (sp ? N - 1 : 0)) tr = val;
+          for (int l = 0; l < N; ++l) {
+            double val = up[base + l * stride];
+            dn += T.DL[sp][l] * val;
+            if (l == (sp ? N - 1 : 0)) tr = val;
+          }
+          NB[(sd * 2 + 0) * NN + lt] = tr;
+          NB[(sd * 2 + 1) * NN + lt] = dn;
         }
-        NB[(f * 2 + 0) * NN + lt] = tr;
-        NB[(f * 2 + 1) * NN + lt] = dn;
       }
     }
-  }
-  __syncthreads();
-  if (active) {   // stage B: interpolate along face x
+    __syncthreads();
+    if (active) {   // stage B: interpolate along face x
 #pragma unroll
-    for (int f = 0; f < 6; ++f) {
-      if (nbr[f] < 0) continue;
+      for (int sd = 0; sd < 2; ++sd) {
+        if (nbr[sd] < 0) continue;
 #pragma unroll
-      for (int q = 0; q < 2; ++q) {
-        const double *row = NB + (f * 2 + q) * NN + N * ly;
-        double s = 0.;
+        for (int q = 0; q < 2; ++q) {
+          const double *row = NB + (sd * 2 + q) * NN + N * ly;
+          double s = 0.;
 #pragma unroll
-        for (int i = 0; i < N; ++i) s += T.I[lx][i] * row[i];
-        NB2[(f * 2 + q) * NN + lt] = s;
+          for (int i = 0; i < N; ++i) s += T.I[lx][i] * row[i];
+          NB2[(sd * 2 + q) * NN + lt] = s;
+        }
       }
     }
-  }
-  __syncthreads();
-  if (active) {   // stage C: interpolate along face y -> NB = (trace, normal derivative) at Gauss pts
+    __syncthreads();
+    if (active) {   // stage C: interpolate along face y
 #pragma unroll
-    for (int f = 0; f < 6; ++f) {
-      if (nbr[f] < 0) continue;
+      for (int sd = 0; sd < 2; ++sd) {
+        if (nbr[sd] < 0) continue;
 #pragma unroll
-      for (int q = 0; q < 2; ++q) {
-        const double *col = NB2 + (f * 2 + q) * NN + lx;
-        double s = 0.;
+        for (int q = 0; q < 2; ++q) {
+          const double *col = NB2 + (sd * 2 + q) * NN + lx;
+          double s = 0.;
 #pragma unroll
-        for (int i = 0; i < N; ++i) s += T.I[ly][i] * col[N * i];
-        NB[(f * 2 + q) * NN + lt] = s;
+          for (int i = 0; i < N; ++i) s += T.I[ly][i] * col[N * i];
+          NB[(sd * 2 + q) * NN + lt] = s;
+        }
       }
     }
-  }
-  __syncthreads();
-  if (active) {   // stage D: fluxes at my face Gauss point (lx, ly) of each face
-    const double wxy = T.w[lx] * T.w[ly];
-#pragma unroll
-    for (int f = 0; f < 6; ++f) {
-      const int nd = f >> 1;
+    __syncthreads();
+    double ve[2], vd[2];
+    if (active) {   // stage D: fluxes at my face Gauss point
+      const double wxy = T.w[lx] * T.w[ly];
       const int t1 = (nd == 0) ? 1 : 0, t2 = (nd == 2) ? 1 : 2;
-      const double *um_a = FT + (f * 2 + 0) * NN;
-      double um = um_a[lt], dmn = FT[(f * 2 + 1) * NN + lt];
-      double dm1 = 0., dm2 = 0.;
 #pragma unroll
-      for (int i = 0; i < N; ++i) {
-        dm1 += T.Dg[lx][i] * um_a[N * ly + i];
-        dm2 += T.Dg[ly][i] * um_a[N * i + lx];
-      }
-      const double *mo = a.mortar + fS[f] + lt;
-      double Am[3];
-      Am[0] = mo[0]; Am[1] = mo[a.MP]; Am[2] = mo[2 * a.MP];
-      double Fm = Am[nd] * dmn + Am[t1] * dm1 + Am[t2] * dm2;
-      double Ssig = mo[6 * a.MP];
-      double du, t13, c2;
-      if (nbr[f] >= 0) {
-        int fp = code[f] & 7, perm = code[f] >> 3;
-        int ndp = fp >> 1;
-        int t1p = (ndp == 0) ? 1 : 0, t2p = (ndp == 2) ? 1 : 2;
-        int xp, yp;
-        int kp = perm_xy(N, perm, lx, ly, xp, yp);
-        const double *up_a = NB + (f * 2 + 0) * NN;
-        double up = up_a[kp], dpn = NB[(f * 2 + 1) * NN + kp];
-        double dp1 = 0., dp2 = 0.;
+      for (int sd = 0; sd < 2; ++sd) {
+        const int f = 2 * nd + sd;
+        const double *um_a = FT + (f * 2 + 0) * NN;
+        double um = um_a[lt], dmn = FT[(f * 2 + 1) * NN + lt];
+        double dm1 = 0., dm2 = 0.;
 #pragma unroll
         for (int i = 0; i < N; ++i) {
-          dp1 += T.Dg[xp][i] * up_a[N * yp + i];
-          dp2 += T.Dg[yp][i] * up_a[N * i + xp];
+          dm1 += T.Dg[lx][i] * um_a[N * ly + i];
+          dm2 += T.Dg[ly][i] * um_a[N * i + lx];
         }
-        double Ap0 = mo[3 * a.MP], Ap1 = mo[4 * a.MP], Ap2 = mo[5 * a.MP];
-        double Apn = (ndp == 0) ? Ap0 : (ndp == 1) ? Ap1 : Ap2;
-        double Apt1 = (t1p == 0) ? Ap0 : Ap1, Apt2 = (t2p == 1) ? Ap1 : Ap2;
-        double Fp = Apn * dpn + Apt1 * dp1 + Apt2 * dp2;
-        du = um - up;
-        t13 = -.5 * (Fp + Fm) + Ssig * du;
-        c2 = -.5;
-      } else {
-        du = um - mo[7 * a.MP];
-        t13 = -Fm + Ssig * du;
-        c2 = -1.;
+        const double *mo = a.mortar + fS[sd] + lt;
+        double Am0 = mo[0], Am1 = mo[a.MP], Am2 = mo[2 * a.MP];
+        double Amn = (nd == 0) ? Am0 : (nd == 1) ? Am1 : Am2;
+        double Amt1 = (t1 == 0) ? Am0 : Am1, Amt2 = (t2 == 1) ? Am1 : Am2;
+        double Fm = Amn * dmn + Amt1 * dm1 + Amt2 * dm2;
+        double Ssig = mo[6 * a.MP];
+        double du, t13, c2;
+        if (nbr[sd] >= 0) {
+          int fp = code[sd] & 7, perm = code[sd] >> 3;
+          int ndp = fp >> 1;
+          int t1p = (ndp == 0) ? 1 : 0, t2p = (ndp == 2) ? 1 : 2;
+          int xp, yp;
+          int kp = perm_xy(N, perm, lx, ly, xp, yp);
+          const double *up_a = NB + (sd * 2 + 0) * NN;
+          double up = up_a[kp], dpn = NB[(sd * 2 + 1) * NN + kp];
+          double dp1 = 0., dp2 = 0.;
+#pragma unroll
+          for (int i = 0; i < N; ++i) {
+            dp1 += T.Dg[xp][i] * up_a[N * yp + i];
+            dp2 += T.Dg[yp][i] * up_a[N * i + xp];
+          }
+          double Ap0 = mo[3 * a.MP], Ap1 = mo[4 * a.MP], Ap2 = mo[5 * a.MP];
+          double Apn = (ndp == 0) ? Ap0 : (ndp == 1) ? Ap1 : Ap2;
+          double Apt1 = (t1p == 0) ? Ap0 : Ap1, Apt2 = (t2p == 1) ? Ap1 : Ap2;
+          double Fp = Apn * dpn + Apt1 * dp1 + Apt2 * dp2;
+          du = um - up;
+          t13 = -.5 * (Fp + Fm) + Ssig * du;
+          c2 = -.5;
+        } else {
+          du = um - mo[7 * a.MP];
+          t13 = -Fm + Ssig * du;
+          c2 = -1.;
+        }
+        double wdu = wxy * c2 * du;
+        ve[sd] = wxy * t13;
+        vd[sd] = Amn * wdu;
+        NB2[(sd * 2 + 0) * NN + lt] = Amt1 * wdu;
+        NB2[(sd * 2 + 1) * NN + lt] = Amt2 * wdu;
       }
-      double wdu = wxy * c2 * du;
-      FR[(f * 2 + 0) * NN + lt] = wxy * t13;
-      FR[(f * 2 + 1) * NN + lt] = Am[nd] * wdu;
-      NB2[(f * 2 + 0) * NN + lt] = Am[t1] * wdu;
-      NB2[(f * 2 + 1) * NN + lt] = Am[t2] * wdu;
     }
+    __syncthreads();
+    if (active) {   // stage E: transposed tangential derivatives, rank-1 update of the normal lines
+#pragma unroll
+      for (int sd = 0; sd < 2; ++sd) {
+        const double *w1 = NB2 + (sd * 2 + 0) * NN, *w2 = NB2 + (sd * 2 + 1) * NN;
+        double s = 0.;
+#pragma unroll
+        for (int i = 0; i < N; ++i) s += T.Dg[i][lx] * w1[N * ly + i] + T.Dg[i][ly] * w2[N * i + lx];
+        ve[sd] += s;
+      }
+      int base, stride;
+      if (nd == 0) { base = N * lx + NN * ly; stride = 1; }
+      else if (nd == 1) { base = lx + NN * ly; stride = N; }
+      else { base = lx + N * ly; stride = NN; }
+#pragma unroll
+      for (int l = 0; l < N; ++l)
+        V0[base + l * stride] += T.e[0][l] * ve[0] + T.d[0][l] * vd[0] + T.e[1][l] * ve[1] + T.d[1][l] * vd[1];
+    }
+    // the next pair's stage-A barrier orders these V0 updates and the NB2 reads
   }
   __syncthreads();
-  if (active) {   // stage E: transposed tangential derivatives of the weighted term2
-#pragma unroll
-    for (int f = 0; f < 6; ++f) {
-      const double *w1 = NB2 + (f * 2 + 0) * NN, *w2 = NB2 + (f * 2 + 1) * NN;
-      double s = 0.;
-#pragma unroll
-      for (int i = 0; i < N; ++i) s += T.Dg[i][lx] * w1[N * ly + i] + T.Dg[i][ly] * w2[N * i + lx];
-      FR[(f * 2 + 0) * NN + lt] += s;
-    }
-  }
-  // FR entries are written and read by the same thread below for faces 4/5
-  // (T-orientation); faces 0..3 are read after the next barriers.
 
   // ---- backward --------------------------------------------------------------
-  if (active) {   // T-orientation: rt + faces 4/5
-    double v4 = FR[(4 * 2 + 0) * NN + lt], d4 = FR[(4 * 2 + 1) * NN + lt];
-    double v5 = FR[(5 * 2 + 0) * NN + lt], d5 = FR[(5 * 2 + 1) * NN + lt];
-#pragma unroll
-    for (int c = 0; c < N; ++c)
-      V0[lx + N * ly + NN * c] = rt[c] + T.e[0][c] * v4 + T.d[0][c] * d4 + T.e[1][c] * v5 + T.d[1][c] * d5;
-  }
-  __syncthreads();
-  if (active) {   // S-orientation: + Dg^T F_s + faces 2/3
+  if (active) {   // S-orientation: + Dg^T F_s
     double fs[N];
 #pragma unroll
     for (int i = 0; i < N; ++i) fs[i] = V2[lx + N * i + NN * ly];
-    double v2 = FR[(2 * 2 + 0) * NN + lt], d2 = FR[(2 * 2 + 1) * NN + lt];
-    double v3 = FR[(3 * 2 + 0) * NN + lt], d3 = FR[(3 * 2 + 1) * NN + lt];
 #pragma unroll
     for (int b = 0; b < N; ++b) {
       double s = 0.;
 #pragma unroll
       for (int i = 0; i < N; ++i) s += T.Dg[i][b] * fs[i];
-      V0[lx + N * b + NN * ly] += s + T.e[0][b] * v2 + T.d[0][b] * d2 + T.e[1][b] * v3 + T.d[1][b] * d3;
+      V0[lx + N * b + NN * ly] += s;
     }
   }
   __syncthreads();
-  if (active) {   // R-orientation: + Dg^T F_r + faces 0/1, then I^T along a
+  if (active) {   // R-orientation: + Dg^T F_r, then I^T along a
     double fr[N], tot[N];
     double *p = V0 + N * lx + NN * ly;
 #pragma unroll
     for (int i = 0; i < N; ++i) fr[i] = V1[i + N * lx + NN * ly];
-    double v0 = FR[(0 * 2 + 0) * NN + lt], d0 = FR[(0 * 2 + 1) * NN + lt];
-    double v1 = FR[(1 * 2 + 0) * NN + lt], d1 = FR[(1 * 2 + 1) * NN + lt];
 #pragma unroll
     for (int i2 = 0; i2 < N; ++i2) {
       double s = 0.;
 #pragma unroll
       for (int i = 0; i < N; ++i) s += T.Dg[i][i2] * fr[i];
-      tot[i2] = p[i2] + s + T.e[0][i2] * v0 + T.d[0][i2] * d0 + T.e[1][i2] * v1 + T.d[1][i2] * d1;
+      tot[i2] = p[i2] + s;
     }
 #pragma unroll
     for (int i2 = 0; i2 < N; ++i2) {
