@@ -249,7 +249,7 @@ def bench_ours(args):
                        "fast_kernel_elements": mesh.fast_elements(), "checksum_Au": checksum},
             "e2e": {"value": total_dof / t_e2e / 1e9, "unit": UNIT,
                     "h2d_bytes_per_step": 8 * n, "d2h_bytes_per_step": 8 * n},
-            "gpu_launches": args.steps * (1 if mesh.fast_elements() == (1 << (3 * level)) else 2),
+            "gpu_launches": args.steps * mesh.launches_per_apply(),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                          "bytes_per_dof": algorithmic_bytes_per_dof(deg)},

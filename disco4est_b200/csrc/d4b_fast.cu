@@ -1,4 +1,4 @@
-// d4b_fast.cu -- uniform-degree conforming SIPG apply: the hot kernel.
+// d4b_fast.cu -- uniform-degree conforming SIPG apply: the hot kernels.
 //
 // Takes every element whose deg_quad == deg and whose six faces are physical
 // boundaries or conforming faces against a LOCAL neighbour of the SAME degree
@@ -9,21 +9,30 @@
 // and d4est_laplacian_flux_sipg_interface_aux d4est_laplacian_flux_sipg.c:494-814):
 //   * With Nq == N the element polynomial is carried in the Lagrange basis of
 //     the N^3 tensor Gauss points ("Gauss-collocated"): uh = (I x I x I) u with
-//     I = LGL->Gauss interpolation.  In that basis the reference-space gradient
-//     is three 1-D sweeps with the Gauss-basis derivative matrix Dg, the
-//     stiffness metric G acts point-wise, and a face trace / normal derivative
-//     at the face Gauss points is a 1-D contraction of each line normal to the
-//     face with the end-point vectors eL/eR (values) and dL/dR (derivatives).
-//     No 2-D face interpolation is needed on the element's own side.
+//     I = LGL->Gauss interpolation.  Kernel 1 (interp_kernel) writes uh for
+//     every element once per apply (a pure streaming pass, 16 B/DOF).
+//   * Kernel 2 (fast_apply_kernel) works entirely in that basis: the
+//     reference-space gradient is three 1-D sweeps with the Gauss-basis
+//     derivative matrix Dg, the stiffness metric G acts point-wise, and a face
+//     trace / normal derivative AT THE FACE GAUSS POINTS is a 1-D contraction
+//     of each line normal to the face with the end-point vectors e (values)
+//     and d (derivatives) -- for the element itself from registers, for the
+//     neighbour from its uh lines read straight from global memory (L2 hits).
+//     No 2-D face interpolation is needed on either side.
 //   * Residuals are accumulated in the same basis (face terms are rank-1
-//     updates along the normal lines) and mapped back once: Au = (I^T x I^T x I^T) rh.
+//     updates along the normal lines) and mapped back once:
+//     Au = (I^T x I^T x I^T) rh.
 //   * N^2 threads per element, each holding one line of N values in registers;
 //     the three line orientations are exchanged through shared memory.
-//   * The neighbour's side is evaluated from its nodal values read straight
-//     from global memory (L2 hits): normal line -> trace + normal derivative,
-//     2-D interpolation to the Gauss points, tangential derivatives there.
+//   * Face geometric data (7 doubles per face Gauss point: A_m[3], A_p[3],
+//     sj*sigma) is stored ONCE per face and shared by its two elements: the
+//     non-owning side reads it through the face permutation with the sign
+//     flipped (n_p sj_p = -n_m sj_m).  The set-up verifies that identity on the
+//     reference's own arrays and falls back to per-side records if it fails.
 // Each element's Au is written exactly once, no atomics (deterministic).
+#include <cmath>
 #include <cstring>
+#include <map>
 #include "d4b_internal.h"
 
 namespace {
@@ -33,24 +42,24 @@ struct FastTab {
   double Dg[8][8];   // derivative in the Gauss-point Lagrange basis, [point][basis]
   double e[2][8];    // Gauss basis evaluated at -1 / +1
   double d[2][8];    // Gauss basis derivative at -1 / +1
-  double DL[2][8];   // rows 0 and N-1 of the LGL derivative matrix
   double w[8];       // Gauss weights
 };
 
 __constant__ FastTab c_tab[9];   // indexed by N
 
+// code bits of an element face
+constexpr int kOwn = 1 << 6;     // this element owns the face record
+
 struct FastArgs {
   const int32_t *elem;          // [n_elem] element ids of this class
   int n_elem;
-  const int64_t *nodal_stride, *quad_stride;
-  const double *G;
-  int64_t LQ;
-  const double *mortar;
-  int64_t MP;
-  const int64_t *face_S;        // [6*n_local] mortar stride of (e,f)
-  const int32_t *face_nbr;      // [6*n_local] neighbour element or -1 (boundary)
-  const int32_t *face_code;     // [6*n_local] f_p | perm << 3
-  const double *u;
+  const int64_t *nodal_stride;
+  const double *FG;             // [n_elem][6][N^3] volume metric
+  const double *FF;             // face records, [7][N^2] each
+  const int64_t *face_rec;      // [6*n_elem] offset of the face record in FF
+  const int64_t *face_nbr;      // [6*n_elem] nodal offset of the neighbour or -1
+  const int32_t *face_code;     // [6*n_elem] f_p | perm << 3 | own << 6
+  const double *uh;             // Gauss-collocated input
   double *Au;
 };
 
@@ -60,56 +69,49 @@ struct Cfg {
   static constexpr int N3 = N * N * N;
   static constexpr int THREADS = (N == 7 || N == 6) ? 256 : 128;
   static constexpr int EPB = THREADS / NN;           // elements per CTA
-  // shared doubles per element: V0,V1,V2 + FT (12*NN) + NB, NB2 (4*NN each)
-  static constexpr int SH_PER_ELEM = 3 * N3 + 20 * NN;
+  // shared doubles per element: V0,V1,V2 + FT (12*NN) + NB (8*NN) + NB2 (4*NN)
+  static constexpr int SH_PER_ELEM = 3 * N3 + 24 * NN;
 };
 
-__device__ __forceinline__ int perm_xy(int n, int perm, int a, int b, int &xp, int &yp) {
+// my-order face point (a,b) -> neighbour-order (xp,yp); returns yp*n + xp
+__device__ __forceinline__ int perm_xy(int n, int perm, int a, int b) {
   int row = (perm & 4) ? a : b, col = (perm & 4) ? b : a;
   if (perm & 2) row = n - 1 - row;
   if (perm & 1) col = n - 1 - col;
-  xp = col; yp = row;
   return row * n + col;
 }
 
+// ---- kernel 1: uh = (I x I x I) u ---------------------------------------------
 template <int N>
-__global__ void __launch_bounds__(Cfg<N>::THREADS) fast_apply_kernel(FastArgs a) {
+__global__ void __launch_bounds__(Cfg<N>::THREADS) interp_kernel(const int32_t *__restrict__ elem, int n_elem,
+                                                                 const int64_t *__restrict__ nodal_stride,
+                                                                 const double *__restrict__ u,
+                                                                 double *__restrict__ uh) {
   using C = Cfg<N>;
   constexpr int NN = C::NN, N3 = C::N3;
-  extern __shared__ double smem[];
+  __shared__ double sm[C::EPB * N3];
   const FastTab &T = c_tab[N];
-  const int slot = threadIdx.x / NN;
-  const int lt = threadIdx.x % NN;
-  const int lx = lt % N, ly = lt / N;
+  const int slot = threadIdx.x / NN, lt = threadIdx.x % NN, lx = lt % N, ly = lt / N;
   const int ei = blockIdx.x * C::EPB + slot;
-  const bool active = (slot < C::EPB) && (ei < a.n_elem);
-  double *V0 = smem + (size_t)(slot < C::EPB ? slot : 0) * C::SH_PER_ELEM;
-  double *V1 = V0 + N3, *V2 = V1 + N3;
-  double *FT = V2 + N3;            // [6][2][NN] own trace / normal derivative
-  double *NB = FT + 12 * NN;       // [2][2][NN] neighbour stage (one face pair)
-  double *NB2 = NB + 4 * NN;       // [2][2][NN] neighbour stage 2 / weighted tangential term2
-  const int e = active ? a.elem[ei] : 0;
-  const int64_t ns = active ? a.nodal_stride[e] : 0;
-
-  // ---- forward: uh = (I x I x I) u ------------------------------------------
+  const bool active = (slot < C::EPB) && (ei < n_elem);
+  double *V = sm + (slot < C::EPB ? slot : 0) * N3;
+  const int64_t ns = active ? nodal_stride[elem[ei]] : 0;
   if (active) {
-    double ul[N], v[N];
+    double l[N];
 #pragma unroll
-    for (int c = 0; c < N; ++c) ul[c] = a.u[ns + lx + N * ly + NN * c];
+    for (int c = 0; c < N; ++c) l[c] = u[ns + lx + N * ly + NN * c];
 #pragma unroll
     for (int c2 = 0; c2 < N; ++c2) {
       double s = 0.;
 #pragma unroll
-      for (int c = 0; c < N; ++c) s += T.I[c2][c] * ul[c];
-      v[c2] = s;
+      for (int c = 0; c < N; ++c) s += T.I[c2][c] * l[c];
+      V[lx + N * ly + NN * c2] = s;
     }
-#pragma unroll
-    for (int c = 0; c < N; ++c) V0[lx + N * ly + NN * c] = v[c];
   }
   __syncthreads();
-  if (active) {   // R-orientation: (b, c) = (lx, ly), line along a
+  if (active) {
     double l[N], v[N];
-    double *p = V0 + N * lx + NN * ly;
+    double *p = V + N * lx + NN * ly;
 #pragma unroll
     for (int i = 0; i < N; ++i) l[i] = p[i];
 #pragma unroll
@@ -123,109 +125,169 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) fast_apply_kernel(FastArgs a)
     for (int i = 0; i < N; ++i) p[i] = v[i];
   }
   __syncthreads();
-  if (active) {   // S-orientation: (a, c) = (lx, ly), line along b
-    double l[N], uh[N], g[N];
-    double *p = V0 + lx + NN * ly;
+  if (active) {
+    double l[N], v[N];
+    double *p = V + lx + NN * ly;
 #pragma unroll
     for (int i = 0; i < N; ++i) l[i] = p[N * i];
-    double t2 = 0., n2 = 0., t3 = 0., n3 = 0.;
 #pragma unroll
     for (int i2 = 0; i2 < N; ++i2) {
       double s = 0.;
 #pragma unroll
       for (int i = 0; i < N; ++i) s += T.I[i2][i] * l[i];
-      uh[i2] = s;
-      t2 += T.e[0][i2] * s; n2 += T.d[0][i2] * s;
-      t3 += T.e[1][i2] * s; n3 += T.d[1][i2] * s;
+      v[i2] = s;
     }
 #pragma unroll
-    for (int i2 = 0; i2 < N; ++i2) {
-      double s = 0.;
-#pragma unroll
-      for (int i = 0; i < N; ++i) s += T.Dg[i2][i] * uh[i];
-      g[i2] = s;
-    }
-#pragma unroll
-    for (int i = 0; i < N; ++i) { p[N * i] = uh[i]; V2[lx + N * i + NN * ly] = g[i]; }
-    FT[(2 * 2 + 0) * NN + lt] = t2; FT[(2 * 2 + 1) * NN + lt] = n2;
-    FT[(3 * 2 + 0) * NN + lt] = t3; FT[(3 * 2 + 1) * NN + lt] = n3;
+    for (int i = 0; i < N; ++i) p[N * i] = v[i];
   }
   __syncthreads();
-  if (active) {   // R-orientation: gradient along a, faces 0/1
-    double uh[N];
-    const double *p = V0 + N * lx + NN * ly;
+  if (active) {
 #pragma unroll
-    for (int i = 0; i < N; ++i) uh[i] = p[i];
-    double t0 = 0., n0 = 0., t1 = 0., n1 = 0.;
-#pragma unroll
-    for (int i = 0; i < N; ++i) {
-      t0 += T.e[0][i] * uh[i]; n0 += T.d[0][i] * uh[i];
-      t1 += T.e[1][i] * uh[i]; n1 += T.d[1][i] * uh[i];
-    }
-#pragma unroll
-    for (int i2 = 0; i2 < N; ++i2) {
-      double s = 0.;
-#pragma unroll
-      for (int i = 0; i < N; ++i) s += T.Dg[i2][i] * uh[i];
-      V1[i2 + N * lx + NN * ly] = s;
-    }
-    FT[(0 * 2 + 0) * NN + lt] = t0; FT[(0 * 2 + 1) * NN + lt] = n0;
-    FT[(1 * 2 + 0) * NN + lt] = t1; FT[(1 * 2 + 1) * NN + lt] = n1;
+    for (int c = 0; c < N; ++c) uh[ns + lx + N * ly + NN * c] = V[lx + N * ly + NN * c];
   }
-  __syncthreads();
-  if (active) {   // T-orientation: (a, b) = (lx, ly): gradient along c, faces 4/5, metric
+}
+
+// ---- kernel 2: the apply in the Gauss basis ------------------------------------
+template <int N>
+__global__ void __launch_bounds__(Cfg<N>::THREADS) fast_apply_kernel(FastArgs a) {
+  using C = Cfg<N>;
+  constexpr int NN = C::NN, N3 = C::N3;
+  extern __shared__ double smem[];
+  const FastTab &T = c_tab[N];
+  const int slot = threadIdx.x / NN;
+  const int lt = threadIdx.x % NN;
+  const int lx = lt % N, ly = lt / N;
+  const int ei = blockIdx.x * C::EPB + slot;
+  const bool active = (slot < C::EPB) && (ei < a.n_elem);
+  double *V0 = smem + (size_t)(slot < C::EPB ? slot : 0) * C::SH_PER_ELEM;
+  double *V1 = V0 + N3, *V2 = V1 + N3;
+  double *FT = V2 + N3;            // [6][2][NN] own trace / normal derivative at face Gauss points
+  double *NB = FT + 12 * NN;       // [2][4][NN] neighbour: trace, normal, two tangential derivatives
+  double *NB2 = NB + 8 * NN;       // [2][2][NN] weighted tangential term2
+  const int64_t ns = active ? a.nodal_stride[a.elem[ei]] : 0;
+  double gt[N];
+
+  // ---- T-orientation (a,b) = (lx,ly): load uh, gradient along c, faces 4/5 ----
+  if (active) {
     double uh[N];
 #pragma unroll
-    for (int i = 0; i < N; ++i) uh[i] = V0[lx + N * ly + NN * i];
+    for (int c = 0; c < N; ++c) uh[c] = a.uh[ns + lx + N * ly + NN * c];
     double t4 = 0., n4 = 0., t5 = 0., n5 = 0.;
 #pragma unroll
     for (int i = 0; i < N; ++i) {
+      V0[lx + N * ly + NN * i] = uh[i];
       t4 += T.e[0][i] * uh[i]; n4 += T.d[0][i] * uh[i];
       t5 += T.e[1][i] * uh[i]; n5 += T.d[1][i] * uh[i];
     }
-    FT[(4 * 2 + 0) * NN + lt] = t4; FT[(4 * 2 + 1) * NN + lt] = n4;
-    FT[(5 * 2 + 0) * NN + lt] = t5; FT[(5 * 2 + 1) * NN + lt] = n5;
-    double ft[N];
-    const double *G = a.G + a.quad_stride[e] + lx + N * ly;
 #pragma unroll
     for (int c = 0; c < N; ++c) {
-      double gt = 0.;
+      double s = 0.;
 #pragma unroll
-      for (int i = 0; i < N; ++i) gt += T.Dg[c][i] * uh[i];
-      int idx = lx + N * ly + NN * c;
-      double gr = V1[idx], gs = V2[idx];
-      double G00 = G[NN * c], G01 = G[a.LQ + NN * c], G02 = G[2 * a.LQ + NN * c];
-      double G11 = G[3 * a.LQ + NN * c], G12 = G[4 * a.LQ + NN * c], G22 = G[5 * a.LQ + NN * c];
-      V1[idx] = G00 * gr + G01 * gs + G02 * gt;
-      V2[idx] = G01 * gr + G11 * gs + G12 * gt;
-      ft[c] = G02 * gr + G12 * gs + G22 * gt;
+      for (int i = 0; i < N; ++i) s += T.Dg[c][i] * uh[i];
+      gt[c] = s;
     }
-    // V0 becomes the residual accumulator (each thread owns its own c-line here)
+    FT[(4 * 2 + 0) * NN + lt] = t4; FT[(4 * 2 + 1) * NN + lt] = n4;
+    FT[(5 * 2 + 0) * NN + lt] = t5; FT[(5 * 2 + 1) * NN + lt] = n5;
+  }
+  __syncthreads();
+  if (active) {
+    {   // S-orientation: (a, c) = (lx, ly), line along b: gradient, faces 2/3
+      double uh[N];
+#pragma unroll
+      for (int i = 0; i < N; ++i) uh[i] = V0[lx + N * i + NN * ly];
+      double t2 = 0., n2 = 0., t3 = 0., n3 = 0.;
+#pragma unroll
+      for (int i = 0; i < N; ++i) {
+        t2 += T.e[0][i] * uh[i]; n2 += T.d[0][i] * uh[i];
+        t3 += T.e[1][i] * uh[i]; n3 += T.d[1][i] * uh[i];
+      }
+#pragma unroll
+      for (int i2 = 0; i2 < N; ++i2) {
+        double s = 0.;
+#pragma unroll
+        for (int i = 0; i < N; ++i) s += T.Dg[i2][i] * uh[i];
+        V2[lx + N * i2 + NN * ly] = s;
+      }
+      FT[(2 * 2 + 0) * NN + lt] = t2; FT[(2 * 2 + 1) * NN + lt] = n2;
+      FT[(3 * 2 + 0) * NN + lt] = t3; FT[(3 * 2 + 1) * NN + lt] = n3;
+    }
+    {   // R-orientation: (b, c) = (lx, ly), line along a: gradient, faces 0/1
+      double uh[N];
+      const double *p = V0 + N * lx + NN * ly;
+#pragma unroll
+      for (int i = 0; i < N; ++i) uh[i] = p[i];
+      double t0 = 0., n0 = 0., t1 = 0., n1 = 0.;
+#pragma unroll
+      for (int i = 0; i < N; ++i) {
+        t0 += T.e[0][i] * uh[i]; n0 += T.d[0][i] * uh[i];
+        t1 += T.e[1][i] * uh[i]; n1 += T.d[1][i] * uh[i];
+      }
+#pragma unroll
+      for (int i2 = 0; i2 < N; ++i2) {
+        double s = 0.;
+#pragma unroll
+        for (int i = 0; i < N; ++i) s += T.Dg[i2][i] * uh[i];
+        V1[i2 + N * lx + NN * ly] = s;
+      }
+      FT[(0 * 2 + 0) * NN + lt] = t0; FT[(0 * 2 + 1) * NN + lt] = n0;
+      FT[(1 * 2 + 0) * NN + lt] = t1; FT[(1 * 2 + 1) * NN + lt] = n1;
+    }
+  }
+  __syncthreads();
+  if (active) {   // T-orientation: metric, Dg^T along c; V0 becomes the residual accumulator
+    double ft[N];
+    const double *G = a.FG + (size_t)ei * (6 * N3) + lt;
+#pragma unroll
+    for (int c = 0; c < N; ++c) {
+      int idx = lt + NN * c;
+      double gr = V1[idx], gs = V2[idx];
+      double G00 = G[0 * N3 + NN * c], G01 = G[1 * N3 + NN * c], G02 = G[2 * N3 + NN * c];
+      double G11 = G[3 * N3 + NN * c], G12 = G[4 * N3 + NN * c], G22 = G[5 * N3 + NN * c];
+      V1[idx] = G00 * gr + G01 * gs + G02 * gt[c];
+      V2[idx] = G01 * gr + G11 * gs + G12 * gt[c];
+      ft[c] = G02 * gr + G12 * gs + G22 * gt[c];
+    }
 #pragma unroll
     for (int c = 0; c < N; ++c) {
       double s = 0.;
 #pragma unroll
       for (int i = 0; i < N; ++i) s += T.Dg[i][c] * ft[i];
-      V0[lx + N * ly + NN * c] = s;
+      V0[lt + NN * c] = s;
     }
   }
 
   // ---- faces, one opposite pair (same normal direction) at a time -------------
   // thread (lx, ly) is face Gauss point (lx, ly) of both faces of the pair
-#pragma unroll 1
+#pragma unroll
   for (int nd = 0; nd < 3; ++nd) {
-    int nbr[2] = {-1, -1}, code[2] = {0, 0};
-    int64_t fS[2] = {0, 0};
-    if (active) {   // stage A: neighbour normal lines from global memory
+    int code[2] = {0, 0};
+    bool interior[2] = {false, false};
+    double fd[2][7];   // face record values at my point: A_m[3], A_p[3], sj*sigma
+    double um[2], fm[2];
+    if (active) {
+      const int t1 = (nd == 0) ? 1 : 0, t2 = (nd == 2) ? 1 : 2;
 #pragma unroll
       for (int sd = 0; sd < 2; ++sd) {
         const int f = 2 * nd + sd;
-        nbr[sd] = a.face_nbr[6 * e + f];
-        code[sd] = a.face_code[6 * e + f];
-        fS[sd] = a.face_S[6 * e + f];
-        if (nbr[sd] >= 0) {
-          int fp = code[sd] & 7, ndp = fp >> 1, sp = fp & 1;
-          const double *up = a.u + a.nodal_stride[nbr[sd]];
+        const int64_t nb = a.face_nbr[6 * ei + f];
+        code[sd] = a.face_code[6 * ei + f];
+        interior[sd] = nb >= 0;
+        const double *rec = a.FF + a.face_rec[6 * ei + f];
+        const int perm = (code[sd] >> 3) & 7;
+        const bool own = code[sd] & kOwn;
+        // face record at my point; the non-owner reads through the permutation
+        // and swaps / negates the two metric triples
+        const int k = own ? lt : perm_xy(N, perm, lx, ly);
+#pragma unroll
+        for (int l = 0; l < 3; ++l) {
+          double x = rec[l * NN + k], y = rec[(3 + l) * NN + k];
+          fd[sd][l] = own ? x : -y;
+          fd[sd][3 + l] = own ? y : -x;
+        }
+        fd[sd][6] = rec[6 * NN + k];
+        if (interior[sd]) {   // neighbour normal line -> trace, normal derivative (its own order)
+          const int fp = code[sd] & 7, ndp = fp >> 1, sp = fp & 1;
+          const double *up = a.uh + nb;
           int base, stride;
           if (ndp == 0) { base = N * lx + NN * ly; stride = 1; }
           else if (ndp == 1) { base = lx + NN * ly; stride = N; }
@@ -234,102 +296,76 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) fast_apply_kernel(FastArgs a)
 #pragma unroll
           for (int l = 0; l < N; ++l) {
             double val = up[base + l * stride];
-            dn += T.DL[sp][l] * val;
-            if (l == (sp ? N - 1 : 0)) tr = val;
+            tr += T.e[sp][l] * val;
+            dn += T.d[sp][l] * val;
           }
-          NB[(sd * 2 + 0) * NN + lt] = tr;
-          NB[(sd * 2 + 1) * NN + lt] = dn;
+          NB[(sd * 4 + 0) * NN + lt] = tr;
+          NB[(sd * 4 + 1) * NN + lt] = dn;
         }
-      }
-    }
-    __syncthreads();
-    if (active) {   // stage B: interpolate along face x
-#pragma unroll
-      for (int sd = 0; sd < 2; ++sd) {
-        if (nbr[sd] < 0) continue;
-#pragma unroll
-        for (int q = 0; q < 2; ++q) {
-          const double *row = NB + (sd * 2 + q) * NN + N * ly;
-          double s = 0.;
-#pragma unroll
-          for (int i = 0; i < N; ++i) s += T.I[lx][i] * row[i];
-          NB2[(sd * 2 + q) * NN + lt] = s;
-        }
-      }
-    }
-    __syncthreads();
-    if (active) {   // stage C: interpolate along face y
-#pragma unroll
-      for (int sd = 0; sd < 2; ++sd) {
-        if (nbr[sd] < 0) continue;
-#pragma unroll
-        for (int q = 0; q < 2; ++q) {
-          const double *col = NB2 + (sd * 2 + q) * NN + lx;
-          double s = 0.;
-#pragma unroll
-          for (int i = 0; i < N; ++i) s += T.I[ly][i] * col[N * i];
-          NB[(sd * 2 + q) * NN + lt] = s;
-        }
-      }
-    }
-    __syncthreads();
-    double ve[2], vd[2];
-    if (active) {   // stage D: fluxes at my face Gauss point
-      const double wxy = T.w[lx] * T.w[ly];
-      const int t1 = (nd == 0) ? 1 : 0, t2 = (nd == 2) ? 1 : 2;
-#pragma unroll
-      for (int sd = 0; sd < 2; ++sd) {
-        const int f = 2 * nd + sd;
+        // own side
         const double *um_a = FT + (f * 2 + 0) * NN;
-        double um = um_a[lt], dmn = FT[(f * 2 + 1) * NN + lt];
+        double dmn = FT[(f * 2 + 1) * NN + lt];
         double dm1 = 0., dm2 = 0.;
 #pragma unroll
         for (int i = 0; i < N; ++i) {
           dm1 += T.Dg[lx][i] * um_a[N * ly + i];
           dm2 += T.Dg[ly][i] * um_a[N * i + lx];
         }
-        const double *mo = a.mortar + fS[sd] + lt;
-        double Am0 = mo[0], Am1 = mo[a.MP], Am2 = mo[2 * a.MP];
-        double Amn = (nd == 0) ? Am0 : (nd == 1) ? Am1 : Am2;
-        double Amt1 = (t1 == 0) ? Am0 : Am1, Amt2 = (t2 == 1) ? Am1 : Am2;
-        double Fm = Amn * dmn + Amt1 * dm1 + Amt2 * dm2;
-        double Ssig = mo[6 * a.MP];
-        double du, t13, c2;
-        if (nbr[sd] >= 0) {
-          int fp = code[sd] & 7, perm = code[sd] >> 3;
-          int ndp = fp >> 1;
-          int t1p = (ndp == 0) ? 1 : 0, t2p = (ndp == 2) ? 1 : 2;
-          int xp, yp;
-          int kp = perm_xy(N, perm, lx, ly, xp, yp);
-          const double *up_a = NB + (sd * 2 + 0) * NN;
-          double up = up_a[kp], dpn = NB[(sd * 2 + 1) * NN + kp];
-          double dp1 = 0., dp2 = 0.;
+        um[sd] = um_a[lt];
+        fm[sd] = fd[sd][nd] * dmn + fd[sd][t1] * dm1 + fd[sd][t2] * dm2;
+      }
+    }
+    __syncthreads();
+    if (active) {   // neighbour tangential derivatives at its own face point (lx, ly)
 #pragma unroll
-          for (int i = 0; i < N; ++i) {
-            dp1 += T.Dg[xp][i] * up_a[N * yp + i];
-            dp2 += T.Dg[yp][i] * up_a[N * i + xp];
-          }
-          double Ap0 = mo[3 * a.MP], Ap1 = mo[4 * a.MP], Ap2 = mo[5 * a.MP];
+      for (int sd = 0; sd < 2; ++sd) {
+        if (!interior[sd]) continue;
+        const double *tr = NB + (sd * 4 + 0) * NN;
+        double d1 = 0., d2 = 0.;
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+          d1 += T.Dg[lx][i] * tr[N * ly + i];
+          d2 += T.Dg[ly][i] * tr[N * i + lx];
+        }
+        NB[(sd * 4 + 2) * NN + lt] = d1;
+        NB[(sd * 4 + 3) * NN + lt] = d2;
+      }
+    }
+    __syncthreads();
+    double ve[2], vd[2];
+    if (active) {   // fluxes at my face Gauss point
+      const double wxy = T.w[lx] * T.w[ly];
+      const int t1 = (nd == 0) ? 1 : 0, t2 = (nd == 2) ? 1 : 2;
+#pragma unroll
+      for (int sd = 0; sd < 2; ++sd) {
+        double du, t13, c2;
+        if (interior[sd]) {
+          const int fp = code[sd] & 7, perm = (code[sd] >> 3) & 7;
+          const int ndp = fp >> 1;
+          const int kp = perm_xy(N, perm, lx, ly);
+          const double *nb = NB + (sd * 4) * NN + kp;
+          double up = nb[0], dpn = nb[NN], dp1 = nb[2 * NN], dp2 = nb[3 * NN];
+          double Ap0 = fd[sd][3], Ap1 = fd[sd][4], Ap2 = fd[sd][5];
           double Apn = (ndp == 0) ? Ap0 : (ndp == 1) ? Ap1 : Ap2;
-          double Apt1 = (t1p == 0) ? Ap0 : Ap1, Apt2 = (t2p == 1) ? Ap1 : Ap2;
+          double Apt1 = (ndp == 0) ? Ap1 : Ap0, Apt2 = (ndp == 2) ? Ap1 : Ap2;
           double Fp = Apn * dpn + Apt1 * dp1 + Apt2 * dp2;
-          du = um - up;
-          t13 = -.5 * (Fp + Fm) + Ssig * du;
+          du = um[sd] - up;
+          t13 = -.5 * (Fp + fm[sd]) + fd[sd][6] * du;
           c2 = -.5;
         } else {
-          du = um - mo[7 * a.MP];
-          t13 = -Fm + Ssig * du;
+          du = um[sd] - fd[sd][3];   // Dirichlet data g is stored in the A_p[0] slot
+          t13 = -fm[sd] + fd[sd][6] * du;
           c2 = -1.;
         }
         double wdu = wxy * c2 * du;
         ve[sd] = wxy * t13;
-        vd[sd] = Amn * wdu;
-        NB2[(sd * 2 + 0) * NN + lt] = Amt1 * wdu;
-        NB2[(sd * 2 + 1) * NN + lt] = Amt2 * wdu;
+        vd[sd] = fd[sd][nd] * wdu;
+        NB2[(sd * 2 + 0) * NN + lt] = fd[sd][t1] * wdu;
+        NB2[(sd * 2 + 1) * NN + lt] = fd[sd][t2] * wdu;
       }
     }
     __syncthreads();
-    if (active) {   // stage E: transposed tangential derivatives, rank-1 update of the normal lines
+    if (active) {   // transposed tangential derivatives, rank-1 update of the normal lines
 #pragma unroll
       for (int sd = 0; sd < 2; ++sd) {
         const double *w1 = NB2 + (sd * 2 + 0) * NN, *w2 = NB2 + (sd * 2 + 1) * NN;
@@ -346,7 +382,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) fast_apply_kernel(FastArgs a)
       for (int l = 0; l < N; ++l)
         V0[base + l * stride] += T.e[0][l] * ve[0] + T.d[0][l] * vd[0] + T.e[1][l] * ve[1] + T.d[1][l] * vd[1];
     }
-    // the next pair's stage-A barrier orders these V0 updates and the NB2 reads
+    // the barrier after the next pair's first stage orders these V0 updates and NB2 reads
   }
   __syncthreads();
 
@@ -402,28 +438,36 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) fast_apply_kernel(FastArgs a)
   if (active) {   // T-orientation: I^T along c, write Au
     double l[N];
 #pragma unroll
-    for (int i = 0; i < N; ++i) l[i] = V0[lx + N * ly + NN * i];
+    for (int i = 0; i < N; ++i) l[i] = V0[lt + NN * i];
 #pragma unroll
     for (int c = 0; c < N; ++c) {
       double s = 0.;
 #pragma unroll
       for (int i = 0; i < N; ++i) s += T.I[i][c] * l[i];
-      a.Au[ns + lx + N * ly + NN * c] = s;
+      a.Au[ns + lt + NN * c] = s;
     }
   }
 }
 
 template <int N>
-void launch_fast(d4b_mesh *m, const D4bFastClass &cls, const double *d_u, double *d_Au,
-                 const int64_t *face_S, const int32_t *face_nbr, const int32_t *face_code) {
+void launch_interp(d4b_mesh *m, const D4bFastClass &cls, const double *d_u) {
   using C = Cfg<N>;
+  if (cls.n_hat == 0) return;
+  int grid = (cls.n_hat + C::EPB - 1) / C::EPB;
+  interp_kernel<N><<<grid, C::THREADS, 0, m->stream>>>(cls.d_hat_elem, cls.n_hat, m->d_nodal_stride, d_u, m->d_uhat);
+  D4B_CUDA(cudaGetLastError());
+}
+
+template <int N>
+void launch_fast(d4b_mesh *m, const D4bFastClass &cls, double *d_Au) {
+  using C = Cfg<N>;
+  if (cls.n_elem == 0) return;
   FastArgs a;
   a.elem = cls.d_elem; a.n_elem = cls.n_elem;
-  a.nodal_stride = m->d_nodal_stride; a.quad_stride = m->d_quad_stride;
-  a.G = m->d_G; a.LQ = m->local_nodes_quad;
-  a.mortar = m->d_mortar; a.MP = m->mortar_nodes;
-  a.face_S = face_S; a.face_nbr = face_nbr; a.face_code = face_code;
-  a.u = d_u; a.Au = d_Au;
+  a.nodal_stride = m->d_nodal_stride;
+  a.FG = cls.d_FG; a.FF = m->d_fast_FF;
+  a.face_rec = cls.d_face_rec; a.face_nbr = cls.d_face_nbr; a.face_code = cls.d_face_code;
+  a.uh = m->d_uhat; a.Au = d_Au;
   size_t smem = (size_t)C::EPB * C::SH_PER_ELEM * sizeof(double);
   static bool configured = false;
   if (!configured) {
@@ -437,10 +481,9 @@ void launch_fast(d4b_mesh *m, const D4bFastClass &cls, const double *d_u, double
 
 void build_fast_tab(int N, FastTab &T) {
   memset(&T, 0, sizeof(T));
-  double xl[8], wl[8], xg[8], wg[8], D[64], E[64], ends[2] = {-1., 1.};
+  double xl[8], wl[8], xg[8], wg[8], E[64], ends[2] = {-1., 1.};
   d4b_tab_lobatto(N, xl, wl);
   d4b_tab_gauss(N, xg, wg);
-  d4b_tab_deriv(N, xl, D);
   d4b_tab_eval(N, xl, N, xg, E);
   for (int i = 0; i < N; ++i)
     for (int j = 0; j < N; ++j) T.I[i][j] = E[i * N + j];
@@ -452,72 +495,167 @@ void build_fast_tab(int N, FastTab &T) {
   d4b_tab_eval(N, xg, 2, ends, Ee);
   for (int s = 0; s < 2; ++s)
     for (int j = 0; j < N; ++j) T.e[s][j] = Ee[s * N + j];
-  // derivative of the Gauss basis at +-1: d/dx of the interpolant = sum_k e[k] * Dg[k][j]
-  // holds only inside the basis; use the exact relation psi_j'(x) = sum_k psi_k(x) Dg[k][j]
+  // psi_j'(x) = sum_k psi_k(x) Dg[k][j] (psi_j' has degree N-2, exact in the basis)
   for (int s = 0; s < 2; ++s)
     for (int j = 0; j < N; ++j) {
       double v = 0.;
       for (int k = 0; k < N; ++k) v += T.e[s][k] * Dg[k * N + j];
       T.d[s][j] = v;
     }
-  for (int j = 0; j < N; ++j) { T.DL[0][j] = D[j]; T.DL[1][j] = D[(N - 1) * N + j]; T.w[j] = wg[j]; }
+  for (int j = 0; j < N; ++j) T.w[j] = wg[j];
+}
+
+inline int perm_index_host(int n, int perm, int a, int b) {
+  int row = (perm & 4) ? a : b, col = (perm & 4) ? b : a;
+  if (perm & 2) row = n - 1 - row;
+  if (perm & 1) col = n - 1 - col;
+  return row * n + col;
 }
 
 }  // namespace
 
-void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<double> &,
-                    const std::vector<int32_t> &elem_side, std::vector<char> &is_fast) {
+void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<double> &mortar,
+                    const std::vector<double> &G, const std::vector<int32_t> &elem_side,
+                    std::vector<char> &is_fast) {
   const int E = d->n_local;
-  std::vector<int64_t> face_S((size_t)6 * E, 0);
-  std::vector<int32_t> face_nbr((size_t)6 * E, -1), face_code((size_t)6 * E, 0);
-  std::vector<std::vector<int32_t>> by_deg(D4B_MAX_DEG + 1);
+  const int64_t MP = d->local_mortar_nodes_quad, LQ = d->local_nodes_quad;
+  std::vector<std::vector<int32_t>> by_deg(D4B_MAX_DEG + 1), hat_by_deg(D4B_MAX_DEG + 1);
   for (int e = 0; e < E; ++e) {
+    if (d->deg_quad[e] == d->deg[e]) hat_by_deg[d->deg[e]].push_back(e);
     bool ok = (d->deg_quad[e] == d->deg[e]);
     for (int f = 0; f < 6 && ok; ++f) {
       int s = elem_side[6 * e + f];
       if (d->side_faces_m[s] != 1 || d->side_faces_p[s] > 1) { ok = false; break; }
-      face_S[6 * e + f] = d->side_mortar_stride[s];
       if (d->side_faces_p[s] == 1) {
         int32_t ep = d->side_e_p[4 * s];
         if (ep < 0 || d->deg[ep] != d->deg[e] || d->deg_quad[ep] != d->deg_quad[e]) { ok = false; break; }
-        face_nbr[6 * e + f] = ep;
-        face_code[6 * e + f] = d->side_f_p[s] | (d->side_perm[s] << 3);
       }
     }
     if (ok) { is_fast[e] = 1; by_deg[d->deg[e]].push_back(e); }
   }
+  bool any = false;
+  for (int p = 1; p <= D4B_MAX_DEG; ++p) any = any || !by_deg[p].empty();
+  if (!any) return;
+
+  // ---- face records, one per face, shared by both sides when consistent
+  std::vector<double> FF;
+  std::map<int64_t, int64_t> rec_of;   // key of the owning (element, face) -> record offset
+  auto write_record = [&](int s, int NN, bool boundary) -> int64_t {
+    int64_t off = (int64_t)FF.size();
+    FF.resize(FF.size() + (size_t)7 * NN);
+    int64_t S = d->side_mortar_stride[s];
+    for (int q = 0; q < 7; ++q)
+      for (int k = 0; k < NN; ++k) FF[off + q * NN + k] = mortar[(size_t)q * MP + S + k];
+    if (boundary)
+      for (int k = 0; k < NN; ++k) FF[off + 3 * NN + k] = mortar[(size_t)7 * MP + S + k];   // g
+    return off;
+  };
   FastTab tabs[9];
   memset(tabs, 0, sizeof(tabs));
-  bool any = false;
+  int64_t n_shared = 0, n_split = 0;
   for (int p = 1; p <= D4B_MAX_DEG; ++p) {
     if (by_deg[p].empty()) continue;
-    any = true;
-    build_fast_tab(p + 1, tabs[p + 1]);
+    const int N = p + 1, NN = N * N, N3 = N * NN;
+    build_fast_tab(N, tabs[N]);
     D4bFastClass c;
     c.deg = p;
-    c.n_elem = (int)by_deg[p].size();
-    c.d_elem = d4b_dev_upload<int32_t>(m, by_deg[p].data(), by_deg[p].size());
+    c.n_hat = (int)hat_by_deg[p].size();
+    c.d_hat_elem = d4b_dev_upload<int32_t>(m, hat_by_deg[p].data(), hat_by_deg[p].size());
+    const std::vector<int32_t> &els = by_deg[p];
+    c.n_elem = (int)els.size();
+    std::vector<int64_t> face_rec((size_t)6 * els.size()), face_nbr((size_t)6 * els.size(), -1);
+    std::vector<int32_t> face_code((size_t)6 * els.size(), 0);
+    std::vector<double> FG((size_t)6 * N3 * els.size());
+    for (size_t i = 0; i < els.size(); ++i) {
+      const int e = els[i];
+      const int64_t qs = d->quad_stride[e];
+      for (int cpl = 0; cpl < 6; ++cpl)
+        for (int k = 0; k < N3; ++k) FG[(i * 6 + cpl) * N3 + k] = G[(size_t)cpl * LQ + qs + k];
+      for (int f = 0; f < 6; ++f) {
+        const int s = elem_side[6 * e + f];
+        const size_t fi = 6 * i + f;
+        if (d->side_faces_p[s] == 0) {
+          face_rec[fi] = write_record(s, NN, true);
+          face_code[fi] = kOwn;
+          continue;
+        }
+        const int32_t ep = d->side_e_p[4 * s];
+        const int fp = d->side_f_p[s], perm = d->side_perm[s];
+        face_nbr[fi] = d->nodal_stride[ep];
+        const int64_t mykey = (int64_t)e * 6 + f, okey = (int64_t)ep * 6 + fp;
+        const int s2 = elem_side[6 * ep + fp];
+        bool i_own = mykey < okey;
+        int64_t off;
+        if (i_own) {
+          auto it = rec_of.find(mykey);
+          off = (it != rec_of.end()) ? it->second : (rec_of[mykey] = write_record(s, NN, false));
+        } else {
+          // the record of the other side serves this side if
+          // A_m(mine)[k] == -A_p(theirs)[pi(k)], A_p(mine)[k] == -A_m(theirs)[pi(k)], S equal
+          const int64_t S1 = d->side_mortar_stride[s], S2 = d->side_mortar_stride[s2];
+          double scale = 0., err = 0.;
+          for (int k = 0; k < NN; ++k) {
+            int kp = perm_index_host(N, perm, k % N, k / N);
+            for (int l = 0; l < 3; ++l) {
+              double am = mortar[(size_t)l * MP + S1 + k], ap = mortar[(size_t)(3 + l) * MP + S1 + k];
+              double oam = mortar[(size_t)l * MP + S2 + kp], oap = mortar[(size_t)(3 + l) * MP + S2 + kp];
+              scale = fmax(scale, fmax(fabs(am), fabs(ap)));
+              err = fmax(err, fmax(fabs(am + oap), fabs(ap + oam)));
+            }
+            double sg = mortar[(size_t)6 * MP + S1 + k], osg = mortar[(size_t)6 * MP + S2 + kp];
+            scale = fmax(scale, fabs(sg));
+            err = fmax(err, fabs(sg - osg));
+          }
+          if (err <= 1e-12 * scale) {
+            auto it = rec_of.find(okey);
+            off = (it != rec_of.end()) ? it->second : (rec_of[okey] = write_record(s2, NN, false));
+            ++n_shared;
+          } else {
+            off = write_record(s, NN, false);
+            i_own = true;
+            ++n_split;
+          }
+        }
+        face_rec[fi] = off;
+        face_code[fi] = fp | (perm << 3) | (i_own ? kOwn : 0);
+      }
+    }
+    c.d_elem = d4b_dev_upload<int32_t>(m, els.data(), els.size());
+    c.d_FG = d4b_dev_upload<double>(m, FG.data(), FG.size());
+    c.d_face_rec = d4b_dev_upload<int64_t>(m, face_rec.data(), face_rec.size());
+    c.d_face_nbr = d4b_dev_upload<int64_t>(m, face_nbr.data(), face_nbr.size());
+    c.d_face_code = d4b_dev_upload<int32_t>(m, face_code.data(), face_code.size());
     m->fast.push_back(c);
+    D4B_CUDA(cudaMemcpyToSymbol(c_tab, &tabs[N], sizeof(FastTab), (size_t)N * sizeof(FastTab)));
   }
-  if (!any) return;
-  for (int p = 1; p <= D4B_MAX_DEG; ++p)
-    if (!by_deg[p].empty())
-      D4B_CUDA(cudaMemcpyToSymbol(c_tab, &tabs[p + 1], sizeof(FastTab), (size_t)(p + 1) * sizeof(FastTab)));
-  m->d_fast_S = d4b_dev_upload<int64_t>(m, face_S.data(), face_S.size());
-  m->d_fast_nbr = d4b_dev_upload<int32_t>(m, face_nbr.data(), face_nbr.size());
-  m->d_fast_code = d4b_dev_upload<int32_t>(m, face_code.data(), face_code.size());
+  m->n_face_shared = n_shared;
+  m->n_face_split = n_split;
+  m->d_fast_FF = d4b_dev_upload<double>(m, FF.data(), FF.size());
+  m->d_uhat = d4b_dev_alloc<double>(m, (size_t)d->local_nodes);
 }
 
 void d4b_launch_fast(d4b_mesh *m, const double *d_u, double *d_Au) {
   for (const D4bFastClass &c : m->fast) {
     switch (c.deg + 1) {
-      case 2: launch_fast<2>(m, c, d_u, d_Au, m->d_fast_S, m->d_fast_nbr, m->d_fast_code); break;
-      case 3: launch_fast<3>(m, c, d_u, d_Au, m->d_fast_S, m->d_fast_nbr, m->d_fast_code); break;
-      case 4: launch_fast<4>(m, c, d_u, d_Au, m->d_fast_S, m->d_fast_nbr, m->d_fast_code); break;
-      case 5: launch_fast<5>(m, c, d_u, d_Au, m->d_fast_S, m->d_fast_nbr, m->d_fast_code); break;
-      case 6: launch_fast<6>(m, c, d_u, d_Au, m->d_fast_S, m->d_fast_nbr, m->d_fast_code); break;
-      case 7: launch_fast<7>(m, c, d_u, d_Au, m->d_fast_S, m->d_fast_nbr, m->d_fast_code); break;
-      case 8: launch_fast<8>(m, c, d_u, d_Au, m->d_fast_S, m->d_fast_nbr, m->d_fast_code); break;
+      case 2: launch_interp<2>(m, c, d_u); break;
+      case 3: launch_interp<3>(m, c, d_u); break;
+      case 4: launch_interp<4>(m, c, d_u); break;
+      case 5: launch_interp<5>(m, c, d_u); break;
+      case 6: launch_interp<6>(m, c, d_u); break;
+      case 7: launch_interp<7>(m, c, d_u); break;
+      case 8: launch_interp<8>(m, c, d_u); break;
+      default: D4B_ABORT("fast path: unsupported degree %d", c.deg);
+    }
+  }
+  for (const D4bFastClass &c : m->fast) {
+    switch (c.deg + 1) {
+      case 2: launch_fast<2>(m, c, d_Au); break;
+      case 3: launch_fast<3>(m, c, d_Au); break;
+      case 4: launch_fast<4>(m, c, d_Au); break;
+      case 5: launch_fast<5>(m, c, d_Au); break;
+      case 6: launch_fast<6>(m, c, d_Au); break;
+      case 7: launch_fast<7>(m, c, d_Au); break;
+      case 8: launch_fast<8>(m, c, d_Au); break;
       default: D4B_ABORT("fast path: unsupported degree %d", c.deg);
     }
   }

@@ -43,8 +43,14 @@ struct D4bTables {
 // neighbour of the same degree (or a physical boundary), everything local.
 struct D4bFastClass {
   int deg = 0;
-  int n_elem = 0;
+  int n_elem = 0;                // elements taken by the fast kernel
   int32_t *d_elem = nullptr;     // [n_elem] element ids
+  int n_hat = 0;                 // elements of this degree with deg_quad == deg (uh is computed for all)
+  int32_t *d_hat_elem = nullptr;
+  double *d_FG = nullptr;        // [n_elem][6][N^3] volume metric
+  int64_t *d_face_rec = nullptr; // [6*n_elem] face record offset
+  int64_t *d_face_nbr = nullptr; // [6*n_elem] neighbour nodal offset / -1
+  int32_t *d_face_code = nullptr;
 };
 
 struct d4b_mesh {
@@ -99,9 +105,9 @@ struct d4b_mesh {
   int n_generic = 0;
   int32_t *d_generic_elem = nullptr;   // elements handled by the generic kernel
   // fast-path face data, see d4b_fast.cu
-  int64_t *d_fast_S = nullptr;         // [6*n_local] mortar stride of (e,f)
-  int32_t *d_fast_nbr = nullptr;       // [6*n_local] neighbour element / -1
-  int32_t *d_fast_code = nullptr;      // [6*n_local] f_p | perm << 3
+  double *d_fast_FF = nullptr;         // face records [7][N^2], one per face (d4b_fast.cu)
+  double *d_uhat = nullptr;            // Gauss-collocated copy of the input vector
+  int64_t n_face_shared = 0, n_face_split = 0;
   int generic_smem = 0;
 };
 
@@ -113,7 +119,8 @@ T *d4b_dev_upload(d4b_mesh *m, const T *h, size_t n);
 // kernels / launchers
 void d4b_launch_generic(d4b_mesh *m, const double *d_u, double *d_Au, int stiffness_only);
 void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *desc, const std::vector<double> &mortar,
-                    const std::vector<int32_t> &elem_side, std::vector<char> &is_fast);
+                    const std::vector<double> &G, const std::vector<int32_t> &elem_side,
+                    std::vector<char> &is_fast);
 void d4b_launch_fast(d4b_mesh *m, const double *d_u, double *d_Au);
 
 #endif

@@ -132,9 +132,9 @@ extern "C" d4b_mesh_t *d4b_mesh_create(const d4b_mesh_desc_t *d) {
   m->d_ughost = d4b_dev_alloc<double>(m, (size_t)d->ghost_nodes);
 
   // ---- volume metric G = w J (rst_xyz)(rst_xyz)^T, six symmetric planes
+  std::vector<double> G((size_t)6 * d->local_nodes_quad);
   {
     const int64_t LQ = d->local_nodes_quad;
-    std::vector<double> G((size_t)6 * LQ);
     std::vector<double> xg(D4B_MAXNQ), wg(D4B_MAXNQ);
     int cur_q = -1;
     for (int e = 0; e < E; ++e) {
@@ -249,7 +249,7 @@ extern "C" d4b_mesh_t *d4b_mesh_create(const d4b_mesh_desc_t *d) {
   // generic kernel.  D4B_FORCE_GENERIC=1 sends everything to the generic kernel.
   std::vector<char> is_fast(E, 0);
   const char *force = getenv("D4B_FORCE_GENERIC");
-  if (!(force && force[0] == '1')) d4b_fast_setup(m, d, mortar, elem_side, is_fast);
+  if (!(force && force[0] == '1')) d4b_fast_setup(m, d, mortar, G, elem_side, is_fast);
   std::vector<int32_t> generic;
   for (int e = 0; e < E; ++e)
     if (!is_fast[e]) generic.push_back(e);
@@ -279,11 +279,14 @@ extern "C" void d4b_mesh_destroy(d4b_mesh_t *m) {
                   m->d_side_e_m, m->d_side_e_p, m->d_side_perm, m->d_side_sub_order,
                   m->d_side_mortar_stride, m->d_mortar, m->d_ughost, m->d_u_stage, m->d_Au_stage,
                   m->d_red, m->d_work[0], m->d_work[1], m->d_work[2], m->d_work[3], m->d_generic_elem,
-                  m->d_fast_S, m->d_fast_nbr, m->d_fast_code};
+                  m->d_fast_FF, m->d_uhat};
   for (void *p : ptrs)
     if (p) cudaFree(p);
-  for (auto &c : m->fast)
-    if (c.d_elem) cudaFree(c.d_elem);
+  for (auto &c : m->fast) {
+    void *cp[] = {c.d_elem, c.d_hat_elem, c.d_FG, c.d_face_rec, c.d_face_nbr, c.d_face_code};
+    for (void *p : cp)
+      if (p) cudaFree(p);
+  }
   if (m->h_red) cudaFreeHost(m->h_red);
   if (m->own_stream) cudaStreamDestroy(m->stream);
   delete m;
@@ -292,3 +295,8 @@ extern "C" void d4b_mesh_destroy(d4b_mesh_t *m) {
 extern "C" int64_t d4b_mesh_local_nodes(const d4b_mesh_t *m) { return m->local_nodes; }
 extern "C" int64_t d4b_mesh_device_bytes(const d4b_mesh_t *m) { return m->device_bytes; }
 extern "C" int64_t d4b_mesh_fast_elements(const d4b_mesh_t *m) { return m->n_local - m->n_generic; }
+extern "C" int32_t d4b_mesh_launches_per_apply(const d4b_mesh_t *m) {
+  int n = (m->n_generic > 0 || m->fast.empty()) ? 1 : 0;
+  for (const auto &c : m->fast) n += (c.n_hat > 0) + (c.n_elem > 0);
+  return n;
+}
