@@ -31,6 +31,8 @@
 //     reference's own arrays and falls back to per-side records if it fails.
 // Each element's Au is written exactly once, no atomics (deterministic).
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include "d4b_internal.h"
@@ -81,6 +83,14 @@ __device__ __forceinline__ int perm_xy(int n, int perm, int a, int b) {
   return row * n + col;
 }
 
+// bank-conflict-free placement of the N^3 block for the three line orientations
+template <int N>
+__device__ __forceinline__ int vix(int a, int b, int c) {
+  if (N == 4) return 16 * c + ((a + 4 * b) ^ (5 * c));
+  if (N == 8) return 64 * c + 8 * (b ^ (c & 1)) + (a ^ b);
+  return a + N * b + N * N * c;
+}
+
 // ---- kernel 1: uh = (I x I x I) u ---------------------------------------------
 template <int N>
 __global__ void __launch_bounds__(Cfg<N>::THREADS) interp_kernel(const int32_t *__restrict__ elem, int n_elem,
@@ -105,45 +115,34 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) interp_kernel(const int32_t *
       double s = 0.;
 #pragma unroll
       for (int c = 0; c < N; ++c) s += T.I[c2][c] * l[c];
-      V[lx + N * ly + NN * c2] = s;
+      V[vix<N>(lx, ly, c2)] = s;
     }
   }
   __syncthreads();
-  if (active) {
-    double l[N], v[N];
-    double *p = V + N * lx + NN * ly;
+  if (active) {   // (b,c) = (lx,ly), line along a
+    double l[N];
 #pragma unroll
-    for (int i = 0; i < N; ++i) l[i] = p[i];
+    for (int i = 0; i < N; ++i) l[i] = V[vix<N>(i, lx, ly)];
 #pragma unroll
     for (int i2 = 0; i2 < N; ++i2) {
       double s = 0.;
 #pragma unroll
       for (int i = 0; i < N; ++i) s += T.I[i2][i] * l[i];
-      v[i2] = s;
+      V[vix<N>(i2, lx, ly)] = s;
     }
-#pragma unroll
-    for (int i = 0; i < N; ++i) p[i] = v[i];
   }
   __syncthreads();
-  if (active) {
-    double l[N], v[N];
-    double *p = V + lx + NN * ly;
+  if (active) {   // (a,c) = (lx,ly), line along b; the result goes straight out
+    double l[N];
 #pragma unroll
-    for (int i = 0; i < N; ++i) l[i] = p[N * i];
+    for (int i = 0; i < N; ++i) l[i] = V[vix<N>(lx, i, ly)];
 #pragma unroll
     for (int i2 = 0; i2 < N; ++i2) {
       double s = 0.;
 #pragma unroll
       for (int i = 0; i < N; ++i) s += T.I[i2][i] * l[i];
-      v[i2] = s;
+      uh[ns + lx + N * i2 + NN * ly] = s;
     }
-#pragma unroll
-    for (int i = 0; i < N; ++i) p[N * i] = v[i];
-  }
-  __syncthreads();
-  if (active) {
-#pragma unroll
-    for (int c = 0; c < N; ++c) uh[ns + lx + N * ly + NN * c] = V[lx + N * ly + NN * c];
   }
 }
 
@@ -449,6 +448,29 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) fast_apply_kernel(FastArgs a)
   }
 }
 
+#include "d4b_flat_kernel.cuh"
+
+template <int N>
+void launch_flat(d4b_mesh *m, const D4bFastClass &cls, double *d_Au) {
+  using C = FlatCfg<N>;
+  if (cls.n_elem == 0) return;
+  FlatArgs a;
+  a.elem = cls.d_elem; a.n_elem = cls.n_elem;
+  a.nodal_stride = m->d_nodal_stride;
+  a.FG = cls.d_FG; a.FF3 = m->d_flat_FF;
+  a.meta = static_cast<const FaceMeta *>(cls.d_face_meta);
+  a.uh = m->d_uhat; a.Au = d_Au;
+  size_t smem = (size_t)C::EPB * C::SH_PER_ELEM * sizeof(double);
+  static bool configured = false;
+  if (!configured) {
+    D4B_CUDA(cudaFuncSetAttribute(flat_apply_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = true;
+  }
+  int grid = (cls.n_elem + C::EPB - 1) / C::EPB;
+  flat_apply_kernel<N><<<grid, C::THREADS, smem, m->stream>>>(a);
+  D4B_CUDA(cudaGetLastError());
+}
+
 template <int N>
 void launch_interp(d4b_mesh *m, const D4bFastClass &cls, const double *d_u) {
   using C = Cfg<N>;
@@ -536,10 +558,32 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
   bool any = false;
   for (int p = 1; p <= D4B_MAX_DEG; ++p) any = any || !by_deg[p].empty();
   if (!any) return;
+  const bool allow_flat = !(getenv("D4B_NO_FLAT") && atoi(getenv("D4B_NO_FLAT")) != 0);
+
+  // a face is tangential-free when A_m[l] (l != its normal direction) and
+  // A_p[l] (l != the neighbour's normal direction) vanish at every face point
+  auto face_is_flat = [&](int s, int NN) -> bool {
+    const int64_t S = d->side_mortar_stride[s];
+    const int nd = d->side_f_m[s] >> 1;
+    for (int l = 0; l < 3; ++l) {
+      if (l == nd) continue;
+      for (int k = 0; k < NN; ++k)
+        if (mortar[(size_t)l * MP + S + k] != 0.) return false;
+    }
+    if (d->side_faces_p[s] == 1) {
+      const int ndp = d->side_f_p[s] >> 1;
+      for (int l = 0; l < 3; ++l) {
+        if (l == ndp) continue;
+        for (int k = 0; k < NN; ++k)
+          if (mortar[(size_t)(3 + l) * MP + S + k] != 0.) return false;
+      }
+    }
+    return true;
+  };
 
   // ---- face records, one per face, shared by both sides when consistent
-  std::vector<double> FF;
-  std::map<int64_t, int64_t> rec_of;   // key of the owning (element, face) -> record offset
+  std::vector<double> FF, FF3;
+  std::map<int64_t, int64_t> rec_of, rec3_of;   // key of the owning (element, face) -> record
   auto write_record = [&](int s, int NN, bool boundary) -> int64_t {
     int64_t off = (int64_t)FF.size();
     FF.resize(FF.size() + (size_t)7 * NN);
@@ -550,6 +594,39 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
       for (int k = 0; k < NN; ++k) FF[off + 3 * NN + k] = mortar[(size_t)7 * MP + S + k];   // g
     return off;
   };
+  auto write_record3 = [&](int s, int NN, bool boundary) -> int64_t {
+    int64_t idx = (int64_t)(FF3.size() / ((size_t)3 * NN));
+    size_t off = FF3.size();
+    FF3.resize(off + (size_t)3 * NN);
+    const int64_t S = d->side_mortar_stride[s];
+    const int nd = d->side_f_m[s] >> 1, ndp = boundary ? 0 : (d->side_f_p[s] >> 1);
+    for (int k = 0; k < NN; ++k) {
+      FF3[off + k] = mortar[(size_t)nd * MP + S + k];
+      FF3[off + NN + k] = boundary ? mortar[(size_t)7 * MP + S + k] : mortar[(size_t)(3 + ndp) * MP + S + k];
+      FF3[off + 2 * NN + k] = mortar[(size_t)6 * MP + S + k];
+    }
+    return idx;
+  };
+  // can side s use the record written from the other side s2?
+  auto consistent = [&](int s, int s2, int N, int perm) -> bool {
+    const int NN = N * N;
+    const int64_t S1 = d->side_mortar_stride[s], S2 = d->side_mortar_stride[s2];
+    double scale = 0., err = 0.;
+    for (int k = 0; k < NN; ++k) {
+      int kp = perm_index_host(N, perm, k % N, k / N);
+      for (int l = 0; l < 3; ++l) {
+        double am = mortar[(size_t)l * MP + S1 + k], ap = mortar[(size_t)(3 + l) * MP + S1 + k];
+        double oam = mortar[(size_t)l * MP + S2 + kp], oap = mortar[(size_t)(3 + l) * MP + S2 + kp];
+        scale = fmax(scale, fmax(fabs(am), fabs(ap)));
+        err = fmax(err, fmax(fabs(am + oap), fabs(ap + oam)));
+      }
+      double sg = mortar[(size_t)6 * MP + S1 + k], osg = mortar[(size_t)6 * MP + S2 + kp];
+      scale = fmax(scale, fabs(sg));
+      err = fmax(err, fabs(sg - osg));
+    }
+    return err <= 1e-12 * scale;
+  };
+
   FastTab tabs[9];
   memset(tabs, 0, sizeof(tabs));
   int64_t n_shared = 0, n_split = 0;
@@ -557,80 +634,93 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
     if (by_deg[p].empty()) continue;
     const int N = p + 1, NN = N * N, N3 = N * NN;
     build_fast_tab(N, tabs[N]);
-    D4bFastClass c;
-    c.deg = p;
-    c.n_hat = (int)hat_by_deg[p].size();
-    c.d_hat_elem = d4b_dev_upload<int32_t>(m, hat_by_deg[p].data(), hat_by_deg[p].size());
-    const std::vector<int32_t> &els = by_deg[p];
-    c.n_elem = (int)els.size();
-    std::vector<int64_t> face_rec((size_t)6 * els.size()), face_nbr((size_t)6 * els.size(), -1);
-    std::vector<int32_t> face_code((size_t)6 * els.size(), 0);
-    std::vector<double> FG((size_t)6 * N3 * els.size());
-    for (size_t i = 0; i < els.size(); ++i) {
-      const int e = els[i];
-      const int64_t qs = d->quad_stride[e];
-      for (int cpl = 0; cpl < 6; ++cpl)
-        for (int k = 0; k < N3; ++k) FG[(i * 6 + cpl) * N3 + k] = G[(size_t)cpl * LQ + qs + k];
-      for (int f = 0; f < 6; ++f) {
-        const int s = elem_side[6 * e + f];
-        const size_t fi = 6 * i + f;
-        if (d->side_faces_p[s] == 0) {
-          face_rec[fi] = write_record(s, NN, true);
-          face_code[fi] = kOwn;
-          continue;
-        }
-        const int32_t ep = d->side_e_p[4 * s];
-        const int fp = d->side_f_p[s], perm = d->side_perm[s];
-        face_nbr[fi] = d->nodal_stride[ep];
-        const int64_t mykey = (int64_t)e * 6 + f, okey = (int64_t)ep * 6 + fp;
-        const int s2 = elem_side[6 * ep + fp];
-        bool i_own = mykey < okey;
-        int64_t off;
-        if (i_own) {
-          auto it = rec_of.find(mykey);
-          off = (it != rec_of.end()) ? it->second : (rec_of[mykey] = write_record(s, NN, false));
-        } else {
-          // the record of the other side serves this side if
-          // A_m(mine)[k] == -A_p(theirs)[pi(k)], A_p(mine)[k] == -A_m(theirs)[pi(k)], S equal
-          const int64_t S1 = d->side_mortar_stride[s], S2 = d->side_mortar_stride[s2];
-          double scale = 0., err = 0.;
-          for (int k = 0; k < NN; ++k) {
-            int kp = perm_index_host(N, perm, k % N, k / N);
-            for (int l = 0; l < 3; ++l) {
-              double am = mortar[(size_t)l * MP + S1 + k], ap = mortar[(size_t)(3 + l) * MP + S1 + k];
-              double oam = mortar[(size_t)l * MP + S2 + kp], oap = mortar[(size_t)(3 + l) * MP + S2 + kp];
-              scale = fmax(scale, fmax(fabs(am), fabs(ap)));
-              err = fmax(err, fmax(fabs(am + oap), fabs(ap + oam)));
-            }
-            double sg = mortar[(size_t)6 * MP + S1 + k], osg = mortar[(size_t)6 * MP + S2 + kp];
-            scale = fmax(scale, fabs(sg));
-            err = fmax(err, fabs(sg - osg));
+    D4B_CUDA(cudaMemcpyToSymbol(c_tab, &tabs[N], sizeof(FastTab), (size_t)N * sizeof(FastTab)));
+    std::vector<int32_t> els_kind[2];
+    for (int e : by_deg[p]) {
+      bool flat = allow_flat;
+      for (int f = 0; f < 6 && flat; ++f) flat = face_is_flat(elem_side[6 * e + f], NN);
+      els_kind[flat ? 1 : 0].push_back(e);
+    }
+    bool hat_done = false;
+    for (int kind = 0; kind < 2; ++kind) {
+      const std::vector<int32_t> &els = els_kind[kind];
+      if (els.empty()) continue;
+      D4bFastClass c;
+      c.deg = p;
+      c.kind = kind;
+      if (!hat_done) {
+        c.n_hat = (int)hat_by_deg[p].size();
+        c.d_hat_elem = d4b_dev_upload<int32_t>(m, hat_by_deg[p].data(), hat_by_deg[p].size());
+        hat_done = true;
+      }
+      c.n_elem = (int)els.size();
+      std::vector<int64_t> face_rec((size_t)6 * els.size()), face_nbr((size_t)6 * els.size(), -1);
+      std::vector<int32_t> face_code((size_t)6 * els.size(), 0);
+      std::vector<double> FG((size_t)6 * N3 * els.size());
+      for (size_t i = 0; i < els.size(); ++i) {
+        const int e = els[i];
+        const int64_t qs = d->quad_stride[e];
+        for (int cpl = 0; cpl < 6; ++cpl)
+          for (int k = 0; k < N3; ++k) FG[(i * 6 + cpl) * N3 + k] = G[(size_t)cpl * LQ + qs + k];
+        for (int f = 0; f < 6; ++f) {
+          const int s = elem_side[6 * e + f];
+          const size_t fi = 6 * i + f;
+          if (d->side_faces_p[s] == 0) {
+            face_rec[fi] = kind ? write_record3(s, NN, true) : write_record(s, NN, true);
+            face_code[fi] = kOwn;
+            continue;
           }
-          if (err <= 1e-12 * scale) {
-            auto it = rec_of.find(okey);
-            off = (it != rec_of.end()) ? it->second : (rec_of[okey] = write_record(s2, NN, false));
+          const int32_t ep = d->side_e_p[4 * s];
+          const int fp = d->side_f_p[s], perm = d->side_perm[s];
+          face_nbr[fi] = d->nodal_stride[ep];
+          const int64_t mykey = (int64_t)e * 6 + f, okey = (int64_t)ep * 6 + fp;
+          const int s2 = elem_side[6 * ep + fp];
+          std::map<int64_t, int64_t> &recs = kind ? rec3_of : rec_of;
+          bool i_own = mykey < okey;
+          int64_t off;
+          if (i_own) {
+            auto it = recs.find(mykey);
+            off = (it != recs.end()) ? it->second
+                                     : (recs[mykey] = kind ? write_record3(s, NN, false) : write_record(s, NN, false));
+          } else if (consistent(s, s2, N, perm)) {
+            auto it = recs.find(okey);
+            off = (it != recs.end()) ? it->second
+                                     : (recs[okey] = kind ? write_record3(s2, NN, false) : write_record(s2, NN, false));
             ++n_shared;
           } else {
-            off = write_record(s, NN, false);
+            off = kind ? write_record3(s, NN, false) : write_record(s, NN, false);
             i_own = true;
             ++n_split;
           }
+          face_rec[fi] = off;
+          face_code[fi] = fp | (perm << 3) | (i_own ? kOwn : 0);
         }
-        face_rec[fi] = off;
-        face_code[fi] = fp | (perm << 3) | (i_own ? kOwn : 0);
       }
+      c.d_elem = d4b_dev_upload<int32_t>(m, els.data(), els.size());
+      c.d_FG = d4b_dev_upload<double>(m, FG.data(), FG.size());
+      if (kind == 0) {
+        c.d_face_rec = d4b_dev_upload<int64_t>(m, face_rec.data(), face_rec.size());
+        c.d_face_nbr = d4b_dev_upload<int64_t>(m, face_nbr.data(), face_nbr.size());
+        c.d_face_code = d4b_dev_upload<int32_t>(m, face_code.data(), face_code.size());
+      } else {
+        std::vector<FaceMeta> meta(face_rec.size());
+        for (size_t j = 0; j < meta.size(); ++j) {
+          D4B_CHECK(face_rec[j] < INT32_MAX, "fast path: too many face records");
+          meta[j].nbr = face_nbr[j];
+          meta[j].rec = (int32_t)face_rec[j];
+          meta[j].code = face_code[j];
+        }
+        static_assert(sizeof(FaceMeta) == 16, "FaceMeta layout");
+        c.d_face_meta = d4b_dev_upload<int64_t>(m, reinterpret_cast<const int64_t *>(meta.data()), meta.size() * 2);
+        m->n_flat_elem += c.n_elem;
+      }
+      m->fast.push_back(c);
     }
-    c.d_elem = d4b_dev_upload<int32_t>(m, els.data(), els.size());
-    c.d_FG = d4b_dev_upload<double>(m, FG.data(), FG.size());
-    c.d_face_rec = d4b_dev_upload<int64_t>(m, face_rec.data(), face_rec.size());
-    c.d_face_nbr = d4b_dev_upload<int64_t>(m, face_nbr.data(), face_nbr.size());
-    c.d_face_code = d4b_dev_upload<int32_t>(m, face_code.data(), face_code.size());
-    m->fast.push_back(c);
-    D4B_CUDA(cudaMemcpyToSymbol(c_tab, &tabs[N], sizeof(FastTab), (size_t)N * sizeof(FastTab)));
   }
   m->n_face_shared = n_shared;
   m->n_face_split = n_split;
-  m->d_fast_FF = d4b_dev_upload<double>(m, FF.data(), FF.size());
+  if (!FF.empty()) m->d_fast_FF = d4b_dev_upload<double>(m, FF.data(), FF.size());
+  if (!FF3.empty()) m->d_flat_FF = d4b_dev_upload<double>(m, FF3.data(), FF3.size());
   m->d_uhat = d4b_dev_alloc<double>(m, (size_t)d->local_nodes);
 }
 
@@ -648,15 +738,11 @@ void d4b_launch_fast(d4b_mesh *m, const double *d_u, double *d_Au) {
     }
   }
   for (const D4bFastClass &c : m->fast) {
+#define D4B_CASE(n) case n: if (c.kind) launch_flat<n>(m, c, d_Au); else launch_fast<n>(m, c, d_Au); break;
     switch (c.deg + 1) {
-      case 2: launch_fast<2>(m, c, d_Au); break;
-      case 3: launch_fast<3>(m, c, d_Au); break;
-      case 4: launch_fast<4>(m, c, d_Au); break;
-      case 5: launch_fast<5>(m, c, d_Au); break;
-      case 6: launch_fast<6>(m, c, d_Au); break;
-      case 7: launch_fast<7>(m, c, d_Au); break;
-      case 8: launch_fast<8>(m, c, d_Au); break;
+      D4B_CASE(2) D4B_CASE(3) D4B_CASE(4) D4B_CASE(5) D4B_CASE(6) D4B_CASE(7) D4B_CASE(8)
       default: D4B_ABORT("fast path: unsupported degree %d", c.deg);
     }
+#undef D4B_CASE
   }
 }

@@ -1,0 +1,269 @@
+// d4b_flat_kernel.cuh -- the apply for elements whose six faces are
+// "tangential-free": on every face Gauss point the folded face metric
+// A[l] = sj sum_d n_d drst[l][d] vanishes for the two directions l tangential
+// to the face, on both sides (exactly, tested at set-up).  Axis-aligned bricks
+// and any mesh whose grid lines meet the faces orthogonally are of this kind.
+// Then the SIPG face terms (d4est_laplacian_flux_sipg.c:494-814) need only
+// traces and NORMAL derivatives, both of which are 1-D contractions of the
+// line normal to the face, which the thread owning face Gauss point (x,y)
+// already holds in registers (own side) or reads from the neighbour's uh
+// (other side).  The face work therefore fuses into the three line
+// orientations of the volume sweep and needs no shared-memory exchange:
+//
+//   forward  T/S/R: line -> gradient component, traces of the two faces normal
+//                   to the line, neighbour traces, fluxes (kept per thread)
+//   pointwise     : stiffness metric G
+//   backward T/S/R: Dg^T of the flux line + rank-1 lifting of both faces
+//   I^T x I^T x I^T back to the LGL basis, one store of Au.
+//
+// Included by d4b_fast.cu (shares its constant tables and helpers).
+
+struct FaceMeta {     // 16 bytes per element face
+  int64_t nbr;        // offset of the neighbour's uh block, -1 on the boundary
+  int32_t rec;        // record index into FF3 (records of 3 planes [NN])
+  int32_t code;       // f_p | perm << 3 | own << 6
+};
+
+struct FlatArgs {
+  const int32_t *elem;
+  int n_elem;
+  const int64_t *nodal_stride;
+  const double *FG;             // [n_elem][6][N^3]
+  const double *FF3;            // compact face records: A_m[n], A_p[n] (g on the boundary), sj*sigma
+  const FaceMeta *meta;         // [6*n_elem]
+  const double *uh;
+  double *Au;
+};
+
+template <int N>
+struct FlatCfg {
+  static constexpr int NN = N * N, N3 = N * N * N;
+  static constexpr int THREADS = Cfg<N>::THREADS;
+  static constexpr int EPB = THREADS / NN;
+  // V0,V1,V2 + per-thread face results [6][2][NN] + 6 face metas (2 doubles each)
+  static constexpr int SH_PER_ELEM = 3 * N3 + 12 * NN + 12;
+};
+
+// flux of one face at this thread's face Gauss point (x, y) (my face ordering)
+template <int N>
+__device__ __forceinline__ void flat_face(const FlatArgs &a, const FastTab &T, const FaceMeta &fm, int x, int y,
+                                          double trm, double dnm, double wxy, double &ve, double &vd) {
+  constexpr int NN = N * N;
+  const int code = fm.code, perm = (code >> 3) & 7;
+  const bool own = code & kOwn;
+  int row = (perm & 4) ? x : y, col = (perm & 4) ? y : x;
+  if (perm & 2) row = N - 1 - row;
+  if (perm & 1) col = N - 1 - col;
+  const int k = own ? (x + N * y) : (col + N * row);
+  const double *r = a.FF3 + (size_t)fm.rec * (3 * NN) + k;
+  const double r0 = r[0], r1 = r[NN], S = r[2 * NN];
+  const double Amn = own ? r0 : -r1;
+  if (fm.nbr >= 0) {
+    const double Apn = own ? r1 : -r0;
+    const int fp = code & 7, ndp = fp >> 1, sp = fp & 1;
+    const double *up = a.uh + fm.nbr;
+    int base, stride;
+    if (ndp == 0) { base = N * col + NN * row; stride = 1; }
+    else if (ndp == 1) { base = col + NN * row; stride = N; }
+    else { base = col + N * row; stride = NN; }
+    double trp = 0., dnp = 0.;
+#pragma unroll
+    for (int l = 0; l < N; ++l) {
+      double v = up[base + l * stride];
+      trp += T.e[sp][l] * v;
+      dnp += T.d[sp][l] * v;
+    }
+    const double du = trm - trp;
+    ve = wxy * (-.5 * (Amn * dnm + Apn * dnp) + S * du);
+    vd = wxy * (-.5 * Amn * du);
+  } else {
+    const double du = trm - r1;   // Dirichlet data in the A_p slot
+    ve = wxy * (-Amn * dnm + S * du);
+    vd = wxy * (-Amn * du);
+  }
+}
+
+template <int N>
+__global__ void __launch_bounds__(FlatCfg<N>::THREADS) flat_apply_kernel(FlatArgs a) {
+  using C = FlatCfg<N>;
+  constexpr int NN = C::NN, N3 = C::N3;
+  extern __shared__ double smem[];
+  const FastTab &T = c_tab[N];
+  const int slot = threadIdx.x / NN;
+  const int lt = threadIdx.x % NN;
+  const int lx = lt % N, ly = lt / N;
+  const int ei = blockIdx.x * C::EPB + slot;
+  const bool active = (slot < C::EPB) && (ei < a.n_elem);
+  double *V0 = smem + (size_t)(slot < C::EPB ? slot : 0) * C::SH_PER_ELEM;
+  double *V1 = V0 + N3, *V2 = V1 + N3;
+  double *FB = V2 + N3;                                   // [6][2][NN], thread-private columns
+  FaceMeta *META = reinterpret_cast<FaceMeta *>(FB + 12 * NN);
+  const int64_t ns = active ? a.nodal_stride[a.elem[ei]] : 0;
+  const double wxy = T.w[lx] * T.w[ly];
+  double gt[N];
+  double tr4 = 0., dn4 = 0., tr5 = 0., dn5 = 0.;
+
+  // ---- T-orientation (a,b) = (lx,ly), line along c ----
+  if (active) {
+    double uh[N];
+#pragma unroll
+    for (int c = 0; c < N; ++c) uh[c] = a.uh[ns + lt + NN * c];
+    for (int j = lt; j < 6; j += NN) META[j] = a.meta[6 * (size_t)ei + j];
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+      V0[vix<N>(lx, ly, i)] = uh[i];
+      tr4 += T.e[0][i] * uh[i]; dn4 += T.d[0][i] * uh[i];
+      tr5 += T.e[1][i] * uh[i]; dn5 += T.d[1][i] * uh[i];
+    }
+#pragma unroll
+    for (int c = 0; c < N; ++c) {
+      double s = 0.;
+#pragma unroll
+      for (int i = 0; i < N; ++i) s += T.Dg[c][i] * uh[i];
+      gt[c] = s;
+    }
+  }
+  __syncthreads();
+  if (active) {
+    {   // faces 4/5 (normal c), face point (a,b)
+      double ve, vd;
+      flat_face<N>(a, T, META[4], lx, ly, tr4, dn4, wxy, ve, vd);
+      FB[(4 * 2 + 0) * NN + lt] = ve; FB[(4 * 2 + 1) * NN + lt] = vd;
+      flat_face<N>(a, T, META[5], lx, ly, tr5, dn5, wxy, ve, vd);
+      FB[(5 * 2 + 0) * NN + lt] = ve; FB[(5 * 2 + 1) * NN + lt] = vd;
+    }
+    {   // S-orientation: (a,c) = (lx,ly), line along b: gradient, faces 2/3
+      double uh[N];
+#pragma unroll
+      for (int i = 0; i < N; ++i) uh[i] = V0[vix<N>(lx, i, ly)];
+      double t2 = 0., n2 = 0., t3 = 0., n3 = 0.;
+#pragma unroll
+      for (int i = 0; i < N; ++i) {
+        t2 += T.e[0][i] * uh[i]; n2 += T.d[0][i] * uh[i];
+        t3 += T.e[1][i] * uh[i]; n3 += T.d[1][i] * uh[i];
+      }
+#pragma unroll
+      for (int i2 = 0; i2 < N; ++i2) {
+        double s = 0.;
+#pragma unroll
+        for (int i = 0; i < N; ++i) s += T.Dg[i2][i] * uh[i];
+        V2[vix<N>(lx, i2, ly)] = s;
+      }
+      double ve, vd;
+      flat_face<N>(a, T, META[2], lx, ly, t2, n2, wxy, ve, vd);
+      FB[(2 * 2 + 0) * NN + lt] = ve; FB[(2 * 2 + 1) * NN + lt] = vd;
+      flat_face<N>(a, T, META[3], lx, ly, t3, n3, wxy, ve, vd);
+      FB[(3 * 2 + 0) * NN + lt] = ve; FB[(3 * 2 + 1) * NN + lt] = vd;
+    }
+    {   // R-orientation: (b,c) = (lx,ly), line along a: gradient, faces 0/1
+      double uh[N];
+#pragma unroll
+      for (int i = 0; i < N; ++i) uh[i] = V0[vix<N>(i, lx, ly)];
+      double t0 = 0., n0 = 0., t1 = 0., n1 = 0.;
+#pragma unroll
+      for (int i = 0; i < N; ++i) {
+        t0 += T.e[0][i] * uh[i]; n0 += T.d[0][i] * uh[i];
+        t1 += T.e[1][i] * uh[i]; n1 += T.d[1][i] * uh[i];
+      }
+#pragma unroll
+      for (int i2 = 0; i2 < N; ++i2) {
+        double s = 0.;
+#pragma unroll
+        for (int i = 0; i < N; ++i) s += T.Dg[i2][i] * uh[i];
+        V1[vix<N>(i2, lx, ly)] = s;
+      }
+      double ve, vd;
+      flat_face<N>(a, T, META[0], lx, ly, t0, n0, wxy, ve, vd);
+      FB[(0 * 2 + 0) * NN + lt] = ve; FB[(0 * 2 + 1) * NN + lt] = vd;
+      flat_face<N>(a, T, META[1], lx, ly, t1, n1, wxy, ve, vd);
+      FB[(1 * 2 + 0) * NN + lt] = ve; FB[(1 * 2 + 1) * NN + lt] = vd;
+    }
+  }
+  __syncthreads();
+  if (active) {   // T-orientation: metric, Dg^T along c + faces 4/5; V0 becomes the residual
+    double ft[N];
+    const double *G = a.FG + (size_t)ei * (6 * N3) + lt;
+#pragma unroll
+    for (int c = 0; c < N; ++c) {
+      const int idx = vix<N>(lx, ly, c);
+      double gr = V1[idx], gs = V2[idx];
+      double G00 = G[0 * N3 + NN * c], G01 = G[1 * N3 + NN * c], G02 = G[2 * N3 + NN * c];
+      double G11 = G[3 * N3 + NN * c], G12 = G[4 * N3 + NN * c], G22 = G[5 * N3 + NN * c];
+      V1[idx] = G00 * gr + G01 * gs + G02 * gt[c];
+      V2[idx] = G01 * gr + G11 * gs + G12 * gt[c];
+      ft[c] = G02 * gr + G12 * gs + G22 * gt[c];
+    }
+    const double ve0 = FB[(4 * 2 + 0) * NN + lt], vd0 = FB[(4 * 2 + 1) * NN + lt];
+    const double ve1 = FB[(5 * 2 + 0) * NN + lt], vd1 = FB[(5 * 2 + 1) * NN + lt];
+#pragma unroll
+    for (int c = 0; c < N; ++c) {
+      double s = T.e[0][c] * ve0 + T.d[0][c] * vd0 + T.e[1][c] * ve1 + T.d[1][c] * vd1;
+#pragma unroll
+      for (int i = 0; i < N; ++i) s += T.Dg[i][c] * ft[i];
+      V0[vix<N>(lx, ly, c)] = s;
+    }
+  }
+  __syncthreads();
+  if (active) {   // S-orientation: + Dg^T F_s + faces 2/3
+    double fs[N];
+#pragma unroll
+    for (int i = 0; i < N; ++i) fs[i] = V2[vix<N>(lx, i, ly)];
+    const double ve0 = FB[(2 * 2 + 0) * NN + lt], vd0 = FB[(2 * 2 + 1) * NN + lt];
+    const double ve1 = FB[(3 * 2 + 0) * NN + lt], vd1 = FB[(3 * 2 + 1) * NN + lt];
+#pragma unroll
+    for (int b = 0; b < N; ++b) {
+      double s = T.e[0][b] * ve0 + T.d[0][b] * vd0 + T.e[1][b] * ve1 + T.d[1][b] * vd1;
+#pragma unroll
+      for (int i = 0; i < N; ++i) s += T.Dg[i][b] * fs[i];
+      V0[vix<N>(lx, b, ly)] += s;
+    }
+  }
+  __syncthreads();
+  if (active) {   // R-orientation: + Dg^T F_r + faces 0/1, then I^T along a
+    double fr[N], tot[N];
+#pragma unroll
+    for (int i = 0; i < N; ++i) fr[i] = V1[vix<N>(i, lx, ly)];
+    const double ve0 = FB[(0 * 2 + 0) * NN + lt], vd0 = FB[(0 * 2 + 1) * NN + lt];
+    const double ve1 = FB[(1 * 2 + 0) * NN + lt], vd1 = FB[(1 * 2 + 1) * NN + lt];
+#pragma unroll
+    for (int i2 = 0; i2 < N; ++i2) {
+      double s = T.e[0][i2] * ve0 + T.d[0][i2] * vd0 + T.e[1][i2] * ve1 + T.d[1][i2] * vd1;
+#pragma unroll
+      for (int i = 0; i < N; ++i) s += T.Dg[i][i2] * fr[i];
+      tot[i2] = V0[vix<N>(i2, lx, ly)] + s;
+    }
+#pragma unroll
+    for (int i2 = 0; i2 < N; ++i2) {
+      double s = 0.;
+#pragma unroll
+      for (int i = 0; i < N; ++i) s += T.I[i][i2] * tot[i];
+      V0[vix<N>(i2, lx, ly)] = s;
+    }
+  }
+  __syncthreads();
+  if (active) {   // S-orientation: I^T along b
+    double l[N];
+#pragma unroll
+    for (int i = 0; i < N; ++i) l[i] = V0[vix<N>(lx, i, ly)];
+#pragma unroll
+    for (int i2 = 0; i2 < N; ++i2) {
+      double s = 0.;
+#pragma unroll
+      for (int i = 0; i < N; ++i) s += T.I[i][i2] * l[i];
+      V0[vix<N>(lx, i2, ly)] = s;
+    }
+  }
+  __syncthreads();
+  if (active) {   // T-orientation: I^T along c, write Au
+    double l[N];
+#pragma unroll
+    for (int i = 0; i < N; ++i) l[i] = V0[vix<N>(lx, ly, i)];
+#pragma unroll
+    for (int c = 0; c < N; ++c) {
+      double s = 0.;
+#pragma unroll
+      for (int i = 0; i < N; ++i) s += T.I[i][c] * l[i];
+      a.Au[ns + lt + NN * c] = s;
+    }
+  }
+}

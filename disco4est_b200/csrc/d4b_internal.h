@@ -51,6 +51,8 @@ struct D4bFastClass {
   int64_t *d_face_rec = nullptr; // [6*n_elem] face record offset
   int64_t *d_face_nbr = nullptr; // [6*n_elem] neighbour nodal offset / -1
   int32_t *d_face_code = nullptr;
+  int kind = 0;                  // 0: general conforming kernel, 1: tangential-free faces (d4b_flat_kernel.cuh)
+  void *d_face_meta = nullptr;   // kind 1: [6*n_elem] packed face descriptors
 };
 
 struct d4b_mesh {
@@ -107,6 +109,8 @@ struct d4b_mesh {
   // fast-path face data, see d4b_fast.cu
   double *d_fast_FF = nullptr;         // face records [7][N^2], one per face (d4b_fast.cu)
   double *d_uhat = nullptr;            // Gauss-collocated copy of the input vector
+  double *d_flat_FF = nullptr;         // compact face records [3][N^2] of the tangential-free class
+  int64_t n_flat_elem = 0;
   int64_t n_face_shared = 0, n_face_split = 0;
   int generic_smem = 0;
 };

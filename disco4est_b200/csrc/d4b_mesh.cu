@@ -295,6 +295,7 @@ extern "C" void d4b_mesh_destroy(d4b_mesh_t *m) {
 extern "C" int64_t d4b_mesh_local_nodes(const d4b_mesh_t *m) { return m->local_nodes; }
 extern "C" int64_t d4b_mesh_device_bytes(const d4b_mesh_t *m) { return m->device_bytes; }
 extern "C" int64_t d4b_mesh_fast_elements(const d4b_mesh_t *m) { return m->n_local - m->n_generic; }
+extern "C" int64_t d4b_mesh_flat_elements(const d4b_mesh_t *m) { return m->n_flat_elem; }
 extern "C" int32_t d4b_mesh_launches_per_apply(const d4b_mesh_t *m) {
   int n = (m->n_generic > 0 || m->fast.empty()) ? 1 : 0;
   for (const auto &c : m->fast) n += (c.n_hat > 0) + (c.n_elem > 0);

@@ -157,6 +157,8 @@ int64_t     d4b_mesh_device_bytes(const d4b_mesh_t *mesh);
 /* elements taken by the uniform-degree conforming kernel (the rest go through
  * the general hp kernel); for reporting and tests                           */
 int64_t     d4b_mesh_fast_elements(const d4b_mesh_t *mesh);
+/* of those, elements whose six faces carry no tangential metric terms */
+int64_t     d4b_mesh_flat_elements(const d4b_mesh_t *mesh);
 /* CUDA kernels one d4b_apply launches on this mesh (for launch accounting)  */
 int32_t     d4b_mesh_launches_per_apply(const d4b_mesh_t *mesh);
 

@@ -113,3 +113,55 @@ def test_fast_and_general_kernels_agree(golden, case, monkeypatch):
     m1.apply(u, a1); m2.apply(u, a2)
     assert rel(a1, a2) < 1e-13
     m1.close(); m2.close()
+
+
+@pytest.mark.parametrize("case", ["brick_l2_p1", "brick_l2_p2_bc", "brick_l2_p3", "brick_l2_p5", "brick_l2_p7"])
+def test_brick_takes_the_tangential_free_kernel(golden, meshes, case):
+    """Axis-aligned faces have no tangential metric terms: every element of
+    the reference's brick fixtures must run in flat_apply_kernel."""
+    A = golden(case)
+    m = meshes(case, A)
+    assert m.flat_elements() == int(A["n_local"][0])
+
+
+def test_curved_mesh_does_not_take_the_tangential_free_kernel(golden, meshes):
+    A = golden("sphere_p2")
+    m = meshes("sphere_p2", A)
+    assert m.flat_elements() < int(A["n_local"][0])
+
+
+@pytest.mark.parametrize("case", ["brick_l2_p1", "brick_l2_p2_bc", "brick_l2_p3", "brick_l2_p5", "brick_l2_p7"])
+def test_flat_and_general_fast_kernels_agree(golden, case, monkeypatch):
+    from disco4est_b200 import Mesh
+
+    A = golden(case)
+    u = np.ascontiguousarray(A["u"])
+    m1 = Mesh(A)
+    monkeypatch.setenv("D4B_NO_FLAT", "1")
+    m2 = Mesh(A)
+    monkeypatch.delenv("D4B_NO_FLAT")
+    assert m2.flat_elements() == 0 and m2.fast_elements() == m1.fast_elements()
+    a1, a2 = np.zeros_like(u), np.zeros_like(u)
+    m1.apply(u, a1); m2.apply(u, a2)
+    assert rel(a1, a2) < 1e-13
+    assert rel(a1, A["Au_with_opt"]) < 1e-12
+    m1.close(); m2.close()
+
+
+@pytest.mark.parametrize("p", [1, 2, 3, 4, 5, 6, 7])
+def test_flat_kernel_all_degrees_against_oracle(p):
+    """Synthetic 4^3 brick (disco4est_b200.brick) at every supported degree."""
+    from disco4est_b200 import Mesh
+    from disco4est_b200.brick import brick_desc
+    from oracle_lib import Oracle
+
+    A = brick_desc(2, p)
+    rng = np.random.default_rng(p)
+    u = rng.standard_normal(A["local_nodes"])
+    m = Mesh(A)
+    assert m.flat_elements() == A["n_local"]
+    au = np.zeros_like(u)
+    m.apply(u, au)
+    ref = Oracle(A).apply(u)
+    assert rel(au, ref) < 1e-12
+    m.close()
