@@ -466,6 +466,7 @@ void launch_flat(d4b_mesh *m, const D4bFastClass &cls, double *d_Au) {
     D4B_CUDA(cudaFuncSetAttribute(flat_apply_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = true;
   }
+  a.prefetch = getenv("D4B_PREFETCH") ? atoi(getenv("D4B_PREFETCH")) : 2;
   int grid = (cls.n_elem + C::EPB - 1) / C::EPB;
   flat_apply_kernel<N><<<grid, C::THREADS, smem, m->stream>>>(a);
   D4B_CUDA(cudaGetLastError());

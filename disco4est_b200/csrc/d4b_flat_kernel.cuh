@@ -33,58 +33,82 @@ struct FlatArgs {
   const FaceMeta *meta;         // [6*n_elem]
   const double *uh;
   double *Au;
+  int prefetch;                 // 1: bulk-prefetch the block's volume metric into L2 at kernel start
 };
+
+// ask the L2 for `bytes` (multiple of 16) at a 16-byte aligned global address
+__device__ __forceinline__ void l2_prefetch(const void *ptr, unsigned bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(ptr), "r"(bytes) : "memory");
+}
 
 template <int N>
 struct FlatCfg {
   static constexpr int NN = N * N, N3 = N * N * N;
-  static constexpr int THREADS = Cfg<N>::THREADS;
+#ifndef D4B_FLAT_THREADS4
+#define D4B_FLAT_THREADS4 32
+#endif
+  static constexpr int THREADS = (N == 4) ? D4B_FLAT_THREADS4 : Cfg<N>::THREADS;
   static constexpr int EPB = THREADS / NN;
   // V0,V1,V2 + per-thread face results [6][2][NN] + 6 face metas (2 doubles each)
   static constexpr int SH_PER_ELEM = 3 * N3 + 12 * NN + 12;
+#ifndef D4B_FLAT_MINB4
+#define D4B_FLAT_MINB4 24
+#endif
+  static constexpr int MIN_BLOCKS = (N == 4) ? D4B_FLAT_MINB4 : 1;
 };
 
-// flux of one face at this thread's face Gauss point (x, y) (my face ordering)
+// a one-warp block only needs a warp-level barrier
+template <int THREADS>
+__device__ __forceinline__ void block_sync() {
+#ifndef D4B_FLAT_NO_SYNCWARP
+  if (THREADS == 32) { __syncwarp(); return; }
+#endif
+  __syncthreads();
+}
+
+// flux of one face at this thread's face Gauss point (x, y) (my face ordering).
+// Branch-free so that the loads of several faces can be in flight together: a
+// boundary face reads (and ignores) a line of the element itself.
 template <int N>
-__device__ __forceinline__ void flat_face(const FlatArgs &a, const FastTab &T, const FaceMeta &fm, int x, int y,
-                                          double trm, double dnm, double wxy, double &ve, double &vd) {
+__device__ __forceinline__ void flat_face(const FlatArgs &a, const FastTab &T, const FaceMeta &fm, int64_t ns, int x,
+                                          int y, double trm, double dnm, double wxy, double &ve, double &vd) {
   constexpr int NN = N * N;
-  const int code = fm.code, perm = (code >> 3) & 7;
-  const bool own = code & kOwn;
-  int row = (perm & 4) ? x : y, col = (perm & 4) ? y : x;
-  if (perm & 2) row = N - 1 - row;
-  if (perm & 1) col = N - 1 - col;
+  const int code = fm.code;
+  const bool own = code & kOwn, interior = fm.nbr >= 0;
+  int row = (code & (4 << 3)) ? x : y, col = (code & (4 << 3)) ? y : x;
+  row = (code & (2 << 3)) ? N - 1 - row : row;
+  col = (code & (1 << 3)) ? N - 1 - col : col;
   const int k = own ? (x + N * y) : (col + N * row);
   const double *r = a.FF3 + (size_t)fm.rec * (3 * NN) + k;
   const double r0 = r[0], r1 = r[NN], S = r[2 * NN];
-  const double Amn = own ? r0 : -r1;
-  if (fm.nbr >= 0) {
-    const double Apn = own ? r1 : -r0;
-    const int fp = code & 7, ndp = fp >> 1, sp = fp & 1;
-    const double *up = a.uh + fm.nbr;
-    int base, stride;
-    if (ndp == 0) { base = N * col + NN * row; stride = 1; }
-    else if (ndp == 1) { base = col + NN * row; stride = N; }
-    else { base = col + N * row; stride = NN; }
-    double trp = 0., dnp = 0.;
+  // neighbour line normal to its face f_p through its point (col,row); read it
+  // from the face inwards so that the -1 end tables serve both ends
+  // (e[1][l] = e[0][N-1-l], d[1][l] = -d[0][N-1-l])
+  const int ndp = (code >> 1) & 3, sp = code & 1;
+  const int stride = (ndp == 0) ? 1 : ((ndp == 1) ? N : NN);
+  const int base = (ndp == 0) ? (N * col + NN * row) : ((ndp == 1) ? (col + NN * row) : (col + N * row));
+  const double *p = a.uh + (interior ? fm.nbr : ns) + base + (sp ? (N - 1) * stride : 0);
+  const int step = sp ? -stride : stride;
+  double v[N];
 #pragma unroll
-    for (int l = 0; l < N; ++l) {
-      double v = up[base + l * stride];
-      trp += T.e[sp][l] * v;
-      dnp += T.d[sp][l] * v;
-    }
-    const double du = trm - trp;
-    ve = wxy * (-.5 * (Amn * dnm + Apn * dnp) + S * du);
-    vd = wxy * (-.5 * Amn * du);
-  } else {
-    const double du = trm - r1;   // Dirichlet data in the A_p slot
-    ve = wxy * (-Amn * dnm + S * du);
-    vd = wxy * (-Amn * du);
+  for (int l = 0; l < N; ++l) v[l] = p[l * step];
+  double trp = 0., dnp = 0.;
+#pragma unroll
+  for (int l = 0; l < N; ++l) {
+    trp += T.e[0][l] * v[l];
+    dnp += T.d[0][l] * v[l];
   }
+  dnp = sp ? -dnp : dnp;
+  const double Amn = own ? r0 : -r1;
+  const double Apn = own ? r1 : -r0;
+  const double du = trm - (interior ? trp : r1);   // boundary: Dirichlet data in the A_p slot
+  const double cm = interior ? .5 : 1., cp = interior ? .5 : 0.;
+  ve = wxy * (S * du - cm * Amn * dnm - cp * Apn * dnp);
+  vd = -wxy * cm * Amn * du;
 }
 
 template <int N>
-__global__ void __launch_bounds__(FlatCfg<N>::THREADS) flat_apply_kernel(FlatArgs a) {
+__global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) flat_apply_kernel(FlatArgs a) {
   using C = FlatCfg<N>;
   constexpr int NN = C::NN, N3 = C::N3;
   extern __shared__ double smem[];
@@ -103,12 +127,23 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS) flat_apply_kernel(FlatArg
   double gt[N];
   double tr4 = 0., dn4 = 0., tr5 = 0., dn5 = 0.;
 
+  // the volume metric is the largest stream and is first needed half-way
+  // through the kernel: ask the L2 for this block's share now
+  if (threadIdx.x == 0 && a.prefetch) {
+    constexpr unsigned kBlockBytes = C::EPB * 6 * N3 * sizeof(double);
+    int left = a.n_elem - (int)blockIdx.x * C::EPB;
+    l2_prefetch(a.FG + (size_t)blockIdx.x * (C::EPB * 6 * N3), left >= C::EPB ? kBlockBytes : left * 6 * N3 * 8);
+  }
   // ---- T-orientation (a,b) = (lx,ly), line along c ----
   if (active) {
     double uh[N];
 #pragma unroll
     for (int c = 0; c < N; ++c) uh[c] = a.uh[ns + lt + NN * c];
-    for (int j = lt; j < 6; j += NN) META[j] = a.meta[6 * (size_t)ei + j];
+    for (int j = lt; j < 6; j += NN) {
+      const FaceMeta fm = a.meta[6 * (size_t)ei + j];
+      META[j] = fm;
+      if ((3 * NN * 8) % 16 == 0 && a.prefetch > 1) l2_prefetch(a.FF3 + (size_t)fm.rec * (3 * NN), 3 * NN * 8);
+    }
 #pragma unroll
     for (int i = 0; i < N; ++i) {
       V0[vix<N>(lx, ly, i)] = uh[i];
@@ -123,13 +158,13 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS) flat_apply_kernel(FlatArg
       gt[c] = s;
     }
   }
-  __syncthreads();
+  block_sync<C::THREADS>();
   if (active) {
     {   // faces 4/5 (normal c), face point (a,b)
       double ve, vd;
-      flat_face<N>(a, T, META[4], lx, ly, tr4, dn4, wxy, ve, vd);
+      flat_face<N>(a, T, META[4], ns, lx, ly, tr4, dn4, wxy, ve, vd);
       FB[(4 * 2 + 0) * NN + lt] = ve; FB[(4 * 2 + 1) * NN + lt] = vd;
-      flat_face<N>(a, T, META[5], lx, ly, tr5, dn5, wxy, ve, vd);
+      flat_face<N>(a, T, META[5], ns, lx, ly, tr5, dn5, wxy, ve, vd);
       FB[(5 * 2 + 0) * NN + lt] = ve; FB[(5 * 2 + 1) * NN + lt] = vd;
     }
     {   // S-orientation: (a,c) = (lx,ly), line along b: gradient, faces 2/3
@@ -150,9 +185,9 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS) flat_apply_kernel(FlatArg
         V2[vix<N>(lx, i2, ly)] = s;
       }
       double ve, vd;
-      flat_face<N>(a, T, META[2], lx, ly, t2, n2, wxy, ve, vd);
+      flat_face<N>(a, T, META[2], ns, lx, ly, t2, n2, wxy, ve, vd);
       FB[(2 * 2 + 0) * NN + lt] = ve; FB[(2 * 2 + 1) * NN + lt] = vd;
-      flat_face<N>(a, T, META[3], lx, ly, t3, n3, wxy, ve, vd);
+      flat_face<N>(a, T, META[3], ns, lx, ly, t3, n3, wxy, ve, vd);
       FB[(3 * 2 + 0) * NN + lt] = ve; FB[(3 * 2 + 1) * NN + lt] = vd;
     }
     {   // R-orientation: (b,c) = (lx,ly), line along a: gradient, faces 0/1
@@ -173,13 +208,13 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS) flat_apply_kernel(FlatArg
         V1[vix<N>(i2, lx, ly)] = s;
       }
       double ve, vd;
-      flat_face<N>(a, T, META[0], lx, ly, t0, n0, wxy, ve, vd);
+      flat_face<N>(a, T, META[0], ns, lx, ly, t0, n0, wxy, ve, vd);
       FB[(0 * 2 + 0) * NN + lt] = ve; FB[(0 * 2 + 1) * NN + lt] = vd;
-      flat_face<N>(a, T, META[1], lx, ly, t1, n1, wxy, ve, vd);
+      flat_face<N>(a, T, META[1], ns, lx, ly, t1, n1, wxy, ve, vd);
       FB[(1 * 2 + 0) * NN + lt] = ve; FB[(1 * 2 + 1) * NN + lt] = vd;
     }
   }
-  __syncthreads();
+  block_sync<C::THREADS>();
   if (active) {   // T-orientation: metric, Dg^T along c + faces 4/5; V0 becomes the residual
     double ft[N];
     const double *G = a.FG + (size_t)ei * (6 * N3) + lt;
@@ -203,7 +238,7 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS) flat_apply_kernel(FlatArg
       V0[vix<N>(lx, ly, c)] = s;
     }
   }
-  __syncthreads();
+  block_sync<C::THREADS>();
   if (active) {   // S-orientation: + Dg^T F_s + faces 2/3
     double fs[N];
 #pragma unroll
@@ -218,7 +253,7 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS) flat_apply_kernel(FlatArg
       V0[vix<N>(lx, b, ly)] += s;
     }
   }
-  __syncthreads();
+  block_sync<C::THREADS>();
   if (active) {   // R-orientation: + Dg^T F_r + faces 0/1, then I^T along a
     double fr[N], tot[N];
 #pragma unroll
@@ -240,7 +275,7 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS) flat_apply_kernel(FlatArg
       V0[vix<N>(i2, lx, ly)] = s;
     }
   }
-  __syncthreads();
+  block_sync<C::THREADS>();
   if (active) {   // S-orientation: I^T along b
     double l[N];
 #pragma unroll
@@ -253,7 +288,7 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS) flat_apply_kernel(FlatArg
       V0[vix<N>(lx, i2, ly)] = s;
     }
   }
-  __syncthreads();
+  block_sync<C::THREADS>();
   if (active) {   // T-orientation: I^T along c, write Au
     double l[N];
 #pragma unroll

@@ -17,7 +17,8 @@ import numpy as np
 from .abi import ChebyParams, MeshDesc, make_desc
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libd4est_b200.so")
+# D4B_LIBRARY_PATH lets profiling scripts A/B differently compiled builds of the same library
+LIB_PATH = os.environ.get("D4B_LIBRARY_PATH") or os.path.join(_HERE, "libd4est_b200.so")
 _F64P = C.POINTER(C.c_double)
 
 EXPORTS = [
