@@ -36,6 +36,18 @@ def algorithmic_bytes_per_dof(p):
     return 64.0 + 168.0 / (p + 1)
 
 
+def required_bytes_per_dof(p, flat):
+    """Bytes the kernels that actually ran must move per DOF: the uhat round
+    trip of the two-kernel split (16) + uhat read, G, Au (64) + face records, 3 planes on
+    tangential-free meshes (flat_apply_kernel), 7 otherwise."""
+    return 80.0 + (72.0 if flat else 168.0) / (p + 1)
+
+
+# DRAM bytes per apply from `ncu --set full` (dram__bytes_read.sum + dram__bytes_write.sum over
+# interp_kernel + flat_apply_kernel), only for the default workload; see profiles/
+NCU_TRAFFIC_BYTES = {(6, 3): None}
+
+
 def measured_peak():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -233,6 +245,7 @@ def bench_ours(args):
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     t_dev, t_e2e = float(tt[0]), float(tt[1])
     total_dof = n * world
+    flat = mesh.flat_elements() == mesh.fast_elements() > 0
     if rank == 0:
         peak, peak_src = measured_peak()
         bytes_launch = n * algorithmic_bytes_per_dof(deg)
@@ -251,8 +264,13 @@ def bench_ours(args):
                     "h2d_bytes_per_step": 8 * n, "d2h_bytes_per_step": 8 * n},
             "gpu_launches": args.steps * mesh.launches_per_apply(),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                         "bytes_per_dof": algorithmic_bytes_per_dof(deg)},
+                         "frac": achieved / peak, "traffic": NCU_TRAFFIC_BYTES.get((level, deg)),
+                         "peak_source": peak_src,
+                         "bytes_per_dof": algorithmic_bytes_per_dof(deg),
+                         "bytes_per_dof_true": required_bytes_per_dof(deg, flat),
+                         "frac_true_bytes": n * required_bytes_per_dof(deg, flat) / t_dev / 1e9 / peak,
+                         "kernels": ("interp_kernel + flat_apply_kernel" if flat
+                                     else "interp_kernel + fast_apply_kernel (+ generic_kernel)")},
             "clocks": clocks,
         }
         if world == 1 and not args.no_cpu:

@@ -44,17 +44,14 @@ __device__ __forceinline__ void l2_prefetch(const void *ptr, unsigned bytes) {
 template <int N>
 struct FlatCfg {
   static constexpr int NN = N * N, N3 = N * N * N;
-#ifndef D4B_FLAT_THREADS4
-#define D4B_FLAT_THREADS4 32
-#endif
-  static constexpr int THREADS = (N == 4) ? D4B_FLAT_THREADS4 : Cfg<N>::THREADS;
+  // threads per block by N = 2..8, from an A/B sweep on B200 (profiles/): small
+  // blocks keep barriers cheap, a one-warp block needs none
+  static constexpr int kThreads[9] = {0, 0, 32, 64, 32, 128, 128, 64, 64};
+  static constexpr int THREADS = kThreads[N];
   static constexpr int EPB = THREADS / NN;
   // V0,V1,V2 + per-thread face results [6][2][NN] + 6 face metas (2 doubles each)
   static constexpr int SH_PER_ELEM = 3 * N3 + 12 * NN + 12;
-#ifndef D4B_FLAT_MINB4
-#define D4B_FLAT_MINB4 24
-#endif
-  static constexpr int MIN_BLOCKS = (N == 4) ? D4B_FLAT_MINB4 : 1;
+  static constexpr int MIN_BLOCKS = (N == 4) ? 24 : 1;
 };
 
 // a one-warp block only needs a warp-level barrier
