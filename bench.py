@@ -192,10 +192,17 @@ def bench_ours(args):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     from disco4est_b200 import Mesh
-    from disco4est_b200.brick import brick_desc
+    from disco4est_b200.brick import brick_desc, trees_for_world
+    from disco4est_b200.runtime import comm_init_from_torch, comm_destroy
 
     level, deg = args.level, args.deg
-    A = brick_desc(level, deg)
+    # weak scaling: one 2^level-cubed tree per rank (p4est brick connectivity), halo exchange
+    # between neighbouring trees inside every apply
+    trees = trees_for_world(world)
+    if world > 1:
+        comm_init_from_torch(local_rank)
+    A = brick_desc(level, deg, rank=rank, world=world, trees=trees)
+    n_ghost = int(A["n_ghost"])
     mesh = Mesh(A, device=local_rank)
     del A
     n = mesh.n
@@ -258,7 +265,10 @@ def bench_ours(args):
             "config": {"workload": "unit-cube Poisson SIPG apply, %d^3 elements per GPU, p=%d, deg_quad=p, "
                                    "Gauss quadrature, SIPG prefactor 2 maxp_sqr_over_minh, homogeneous Dirichlet"
                                    % (1 << level, deg),
-                       "dof_per_gpu": n, "l2": "inputs larger than L2 (no flush needed)",
+                       "dof_per_gpu": n, "trees": list(trees), "ghost_elements_rank0": n_ghost,
+                       "halo": ("none (one rank)" if world == 1 else
+                                "NCCL send/recv of mirror elements inside every apply, overlapped with interior elements"),
+                       "l2": "inputs larger than L2 (no flush needed)",
                        "fast_kernel_elements": mesh.fast_elements(), "checksum_Au": checksum},
             "e2e": {"value": total_dof / t_e2e / 1e9, "unit": UNIT,
                     "h2d_bytes_per_step": 8 * n, "d2h_bytes_per_step": 8 * n},
@@ -278,6 +288,7 @@ def bench_ours(args):
         print(json.dumps(out))
     mesh.close()
     if world > 1:
+        comm_destroy()
         dist.destroy_process_group()
 
 

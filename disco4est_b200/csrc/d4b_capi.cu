@@ -61,7 +61,11 @@ void apply_impl(d4b_mesh *m, const double *u, double *Au, int stiffness_only) {
   if (stiffness_only) {
     d4b_launch_generic(m, du, dAu, 1);
   } else {
-    d4b_launch_fast(m, du, dAu);
+    // halo exchange on the communication stream while interior elements run
+    d4b_comm_exchange_begin(m, du);
+    d4b_launch_fast(m, du, dAu, 0);
+    d4b_comm_exchange_wait(m);
+    d4b_launch_fast(m, du, dAu, 1);
     d4b_launch_generic(m, du, dAu, 0);
   }
   if (!Au_dev) D4B_CUDA(cudaMemcpyAsync(Au, dAu, bytes, cudaMemcpyDeviceToHost, m->stream));

@@ -34,6 +34,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
 #include <map>
 #include "d4b_internal.h"
 
@@ -54,6 +55,7 @@ constexpr int kOwn = 1 << 6;     // this element owns the face record
 
 struct FastArgs {
   const int32_t *elem;          // [n_elem] element ids of this class
+  int first;                    // this launch covers class positions [first, n_elem)
   int n_elem;
   const int64_t *nodal_stride;
   const double *FG;             // [n_elem][6][N^3] volume metric
@@ -156,7 +158,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) fast_apply_kernel(FastArgs a)
   const int slot = threadIdx.x / NN;
   const int lt = threadIdx.x % NN;
   const int lx = lt % N, ly = lt / N;
-  const int ei = blockIdx.x * C::EPB + slot;
+  const int ei = a.first + blockIdx.x * C::EPB + slot;
   const bool active = (slot < C::EPB) && (ei < a.n_elem);
   double *V0 = smem + (size_t)(slot < C::EPB ? slot : 0) * C::SH_PER_ELEM;
   double *V1 = V0 + N3, *V2 = V1 + N3;
@@ -451,11 +453,11 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) fast_apply_kernel(FastArgs a)
 #include "d4b_flat_kernel.cuh"
 
 template <int N>
-void launch_flat(d4b_mesh *m, const D4bFastClass &cls, double *d_Au) {
+void launch_flat(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, int last) {
   using C = FlatCfg<N>;
-  if (cls.n_elem == 0) return;
+  if (last <= first) return;
   FlatArgs a;
-  a.elem = cls.d_elem; a.n_elem = cls.n_elem;
+  a.elem = cls.d_elem; a.first = first; a.n_elem = last;
   a.nodal_stride = m->d_nodal_stride;
   a.FG = cls.d_FG; a.FF3 = m->d_flat_FF;
   a.meta = static_cast<const FaceMeta *>(cls.d_face_meta);
@@ -467,26 +469,33 @@ void launch_flat(d4b_mesh *m, const D4bFastClass &cls, double *d_Au) {
     configured = true;
   }
   a.prefetch = getenv("D4B_PREFETCH") ? atoi(getenv("D4B_PREFETCH")) : 2;
-  int grid = (cls.n_elem + C::EPB - 1) / C::EPB;
+  int grid = (last - first + C::EPB - 1) / C::EPB;
   flat_apply_kernel<N><<<grid, C::THREADS, smem, m->stream>>>(a);
   D4B_CUDA(cudaGetLastError());
 }
 
 template <int N>
-void launch_interp(d4b_mesh *m, const D4bFastClass &cls, const double *d_u) {
+void launch_interp(d4b_mesh *m, const D4bFastClass &cls, const double *d_u, int phase) {
   using C = Cfg<N>;
-  if (cls.n_hat == 0) return;
-  int grid = (cls.n_hat + C::EPB - 1) / C::EPB;
-  interp_kernel<N><<<grid, C::THREADS, 0, m->stream>>>(cls.d_hat_elem, cls.n_hat, m->d_nodal_stride, d_u, m->d_uhat);
+  if (phase == 0) {   // local elements
+    if (cls.n_hat == 0) return;
+    int grid = (cls.n_hat + C::EPB - 1) / C::EPB;
+    interp_kernel<N><<<grid, C::THREADS, 0, m->stream>>>(cls.d_hat_elem, cls.n_hat, m->d_nodal_stride, d_u, m->d_uhat);
+  } else {            // ghost elements, from the receive buffer to the tail of uhat
+    if (cls.n_ghost_hat == 0) return;
+    int grid = (cls.n_ghost_hat + C::EPB - 1) / C::EPB;
+    interp_kernel<N><<<grid, C::THREADS, 0, m->stream>>>(cls.d_ghost_hat, cls.n_ghost_hat, m->d_ghost_nodal_stride,
+                                                        m->d_ughost, m->d_uhat + m->local_nodes);
+  }
   D4B_CUDA(cudaGetLastError());
 }
 
 template <int N>
-void launch_fast(d4b_mesh *m, const D4bFastClass &cls, double *d_Au) {
+void launch_fast(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, int last) {
   using C = Cfg<N>;
-  if (cls.n_elem == 0) return;
+  if (last <= first) return;
   FastArgs a;
-  a.elem = cls.d_elem; a.n_elem = cls.n_elem;
+  a.elem = cls.d_elem; a.first = first; a.n_elem = last;
   a.nodal_stride = m->d_nodal_stride;
   a.FG = cls.d_FG; a.FF = m->d_fast_FF;
   a.face_rec = cls.d_face_rec; a.face_nbr = cls.d_face_nbr; a.face_code = cls.d_face_code;
@@ -497,7 +506,7 @@ void launch_fast(d4b_mesh *m, const D4bFastClass &cls, double *d_Au) {
     D4B_CUDA(cudaFuncSetAttribute(fast_apply_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = true;
   }
-  int grid = (cls.n_elem + C::EPB - 1) / C::EPB;
+  int grid = (last - first + C::EPB - 1) / C::EPB;
   fast_apply_kernel<N><<<grid, C::THREADS, smem, m->stream>>>(a);
   D4B_CUDA(cudaGetLastError());
 }
@@ -551,7 +560,9 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
       if (d->side_faces_m[s] != 1 || d->side_faces_p[s] > 1) { ok = false; break; }
       if (d->side_faces_p[s] == 1) {
         int32_t ep = d->side_e_p[4 * s];
-        if (ep < 0 || d->deg[ep] != d->deg[e] || d->deg_quad[ep] != d->deg_quad[e]) { ok = false; break; }
+        const int dp = ep >= 0 ? d->deg[ep] : d->ghost_deg[-ep - 1];
+        const int dqp = ep >= 0 ? d->deg_quad[ep] : d->ghost_deg_quad[-ep - 1];
+        if (dp != d->deg[e] || dqp != d->deg_quad[e]) { ok = false; break; }
       }
     }
     if (ok) { is_fast[e] = 1; by_deg[d->deg[e]].push_back(e); }
@@ -642,6 +653,23 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
       for (int f = 0; f < 6 && flat; ++f) flat = face_is_flat(elem_side[6 * e + f], NN);
       els_kind[flat ? 1 : 0].push_back(e);
     }
+    // elements without a ghost neighbour first: they run while the halo is in flight
+    auto touches_ghost = [&](int e) {
+      for (int f = 0; f < 6; ++f) {
+        const int s = elem_side[6 * e + f];
+        if (d->side_faces_p[s] == 1 && d->side_e_p[4 * s] < 0) return true;
+      }
+      return false;
+    };
+    int n_interior_kind[2] = {0, 0};
+    for (int kind = 0; kind < 2; ++kind) {
+      auto mid = std::stable_partition(els_kind[kind].begin(), els_kind[kind].end(),
+                                       [&](int e) { return !touches_ghost(e); });
+      n_interior_kind[kind] = (int)(mid - els_kind[kind].begin());
+    }
+    std::vector<int32_t> ghost_hat;
+    for (int g = 0; g < d->n_ghost; ++g)
+      if (d->ghost_deg[g] == p && d->ghost_deg_quad[g] == p) ghost_hat.push_back(g);
     bool hat_done = false;
     for (int kind = 0; kind < 2; ++kind) {
       const std::vector<int32_t> &els = els_kind[kind];
@@ -652,9 +680,12 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
       if (!hat_done) {
         c.n_hat = (int)hat_by_deg[p].size();
         c.d_hat_elem = d4b_dev_upload<int32_t>(m, hat_by_deg[p].data(), hat_by_deg[p].size());
+        c.n_ghost_hat = (int)ghost_hat.size();
+        c.d_ghost_hat = d4b_dev_upload<int32_t>(m, ghost_hat.data(), ghost_hat.size());
         hat_done = true;
       }
       c.n_elem = (int)els.size();
+      c.n_interior = n_interior_kind[kind];
       std::vector<int64_t> face_rec((size_t)6 * els.size()), face_nbr((size_t)6 * els.size(), -1);
       std::vector<int32_t> face_code((size_t)6 * els.size(), 0);
       std::vector<double> FG((size_t)6 * N3 * els.size());
@@ -673,6 +704,12 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
           }
           const int32_t ep = d->side_e_p[4 * s];
           const int fp = d->side_f_p[s], perm = d->side_perm[s];
+          if (ep < 0) {   // ghost neighbour: its uh lives behind the local block; this side owns the record
+            face_nbr[fi] = d->local_nodes + d->ghost_nodal_stride[-ep - 1];
+            face_rec[fi] = kind ? write_record3(s, NN, false) : write_record(s, NN, false);
+            face_code[fi] = fp | (perm << 3) | kOwn;
+            continue;
+          }
           face_nbr[fi] = d->nodal_stride[ep];
           const int64_t mykey = (int64_t)e * 6 + f, okey = (int64_t)ep * 6 + fp;
           const int s2 = elem_side[6 * ep + fp];
@@ -722,24 +759,21 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
   m->n_face_split = n_split;
   if (!FF.empty()) m->d_fast_FF = d4b_dev_upload<double>(m, FF.data(), FF.size());
   if (!FF3.empty()) m->d_flat_FF = d4b_dev_upload<double>(m, FF3.data(), FF3.size());
-  m->d_uhat = d4b_dev_alloc<double>(m, (size_t)d->local_nodes);
+  m->d_uhat = d4b_dev_alloc<double>(m, (size_t)(d->local_nodes + d->ghost_nodes));
 }
 
-void d4b_launch_fast(d4b_mesh *m, const double *d_u, double *d_Au) {
+void d4b_launch_fast(d4b_mesh *m, const double *d_u, double *d_Au, int phase) {
   for (const D4bFastClass &c : m->fast) {
+#define D4B_CASE(n) case n: launch_interp<n>(m, c, d_u, phase); break;
     switch (c.deg + 1) {
-      case 2: launch_interp<2>(m, c, d_u); break;
-      case 3: launch_interp<3>(m, c, d_u); break;
-      case 4: launch_interp<4>(m, c, d_u); break;
-      case 5: launch_interp<5>(m, c, d_u); break;
-      case 6: launch_interp<6>(m, c, d_u); break;
-      case 7: launch_interp<7>(m, c, d_u); break;
-      case 8: launch_interp<8>(m, c, d_u); break;
+      D4B_CASE(2) D4B_CASE(3) D4B_CASE(4) D4B_CASE(5) D4B_CASE(6) D4B_CASE(7) D4B_CASE(8)
       default: D4B_ABORT("fast path: unsupported degree %d", c.deg);
     }
+#undef D4B_CASE
   }
   for (const D4bFastClass &c : m->fast) {
-#define D4B_CASE(n) case n: if (c.kind) launch_flat<n>(m, c, d_Au); else launch_fast<n>(m, c, d_Au); break;
+    const int first = phase == 0 ? 0 : c.n_interior, last = phase == 0 ? c.n_interior : c.n_elem;
+#define D4B_CASE(n) case n: if (c.kind) launch_flat<n>(m, c, d_Au, first, last); else launch_fast<n>(m, c, d_Au, first, last); break;
     switch (c.deg + 1) {
       D4B_CASE(2) D4B_CASE(3) D4B_CASE(4) D4B_CASE(5) D4B_CASE(6) D4B_CASE(7) D4B_CASE(8)
       default: D4B_ABORT("fast path: unsupported degree %d", c.deg);

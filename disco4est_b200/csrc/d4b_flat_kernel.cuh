@@ -26,6 +26,7 @@ struct FaceMeta {     // 16 bytes per element face
 
 struct FlatArgs {
   const int32_t *elem;
+  int first;                    // this launch covers class positions [first, n_elem)
   int n_elem;
   const int64_t *nodal_stride;
   const double *FG;             // [n_elem][6][N^3]
@@ -113,7 +114,7 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) f
   const int slot = threadIdx.x / NN;
   const int lt = threadIdx.x % NN;
   const int lx = lt % N, ly = lt / N;
-  const int ei = blockIdx.x * C::EPB + slot;
+  const int ei = a.first + blockIdx.x * C::EPB + slot;
   const bool active = (slot < C::EPB) && (ei < a.n_elem);
   double *V0 = smem + (size_t)(slot < C::EPB ? slot : 0) * C::SH_PER_ELEM;
   double *V1 = V0 + N3, *V2 = V1 + N3;
@@ -128,8 +129,8 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) f
   // through the kernel: ask the L2 for this block's share now
   if (threadIdx.x == 0 && a.prefetch) {
     constexpr unsigned kBlockBytes = C::EPB * 6 * N3 * sizeof(double);
-    int left = a.n_elem - (int)blockIdx.x * C::EPB;
-    l2_prefetch(a.FG + (size_t)blockIdx.x * (C::EPB * 6 * N3), left >= C::EPB ? kBlockBytes : left * 6 * N3 * 8);
+    const int e0 = a.first + (int)blockIdx.x * C::EPB, left = a.n_elem - e0;
+    l2_prefetch(a.FG + (size_t)e0 * (6 * N3), left >= C::EPB ? kBlockBytes : left * 6 * N3 * 8);
   }
   // ---- T-orientation (a,b) = (lx,ly), line along c ----
   if (active) {

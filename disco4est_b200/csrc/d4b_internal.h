@@ -44,6 +44,9 @@ struct D4bTables {
 struct D4bFastClass {
   int deg = 0;
   int n_elem = 0;                // elements taken by the fast kernel
+  int n_interior = 0;            // the first n_interior of them have no ghost neighbour
+  int n_ghost_hat = 0;           // ghost elements of this degree whose uh the class needs
+  int32_t *d_ghost_hat = nullptr;
   int32_t *d_elem = nullptr;     // [n_elem] element ids
   int n_hat = 0;                 // elements of this degree with deg_quad == deg (uh is computed for all)
   int32_t *d_hat_elem = nullptr;
@@ -53,6 +56,13 @@ struct D4bFastClass {
   int32_t *d_face_code = nullptr;
   int kind = 0;                  // 0: general conforming kernel, 1: tangential-free faces (d4b_flat_kernel.cuh)
   void *d_face_meta = nullptr;   // kind 1: [6*n_elem] packed face descriptors
+};
+
+// halo exchange with one neighbour rank; offsets / counts in doubles
+struct D4bPeer {
+  int rank = 0;
+  int64_t send_off = 0, send_cnt = 0;   // into d_sendbuf
+  int64_t recv_off = 0, recv_cnt = 0;   // into d_ughost
 };
 
 struct d4b_mesh {
@@ -94,6 +104,15 @@ struct d4b_mesh {
 
   // ghost values (filled by the exchange)
   double *d_ughost = nullptr;
+  // exchange plan (d4b_comm.cu)
+  int mpirank = 0, mpisize = 1;
+  std::vector<D4bPeer> peers;
+  int32_t n_send_elems = 0;
+  int64_t *d_send_src = nullptr, *d_send_dst = nullptr;
+  int32_t *d_send_cnt = nullptr;
+  double *d_sendbuf = nullptr;
+  cudaStream_t comm_stream = nullptr;
+  cudaEvent_t ev_packed = nullptr, ev_recv = nullptr;
 
   // staging for host-pointer calls
   double *d_u_stage = nullptr, *d_Au_stage = nullptr;
@@ -125,6 +144,15 @@ void d4b_launch_generic(d4b_mesh *m, const double *d_u, double *d_Au, int stiffn
 void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *desc, const std::vector<double> &mortar,
                     const std::vector<double> &G, const std::vector<int32_t> &elem_side,
                     std::vector<char> &is_fast);
-void d4b_launch_fast(d4b_mesh *m, const double *d_u, double *d_Au);
+// phase 0: uh of local elements + interior elements; phase 1 (after the halo
+// exchange): uh of ghost elements + elements with a ghost neighbour
+void d4b_launch_fast(d4b_mesh *m, const double *d_u, double *d_Au, int phase);
+
+// halo exchange (d4b_comm.cu)
+void d4b_comm_setup(d4b_mesh *m, const d4b_mesh_desc_t *d);
+void d4b_comm_teardown(d4b_mesh *m);
+void d4b_comm_exchange_begin(d4b_mesh *m, const double *d_u);
+void d4b_comm_exchange_wait(d4b_mesh *m);
+void d4b_comm_allreduce_sum(d4b_mesh *m, double *d_x, int n);
 
 #endif

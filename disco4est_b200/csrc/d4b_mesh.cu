@@ -130,6 +130,7 @@ extern "C" d4b_mesh_t *d4b_mesh_create(const d4b_mesh_desc_t *d) {
   m->d_ghost_deg_quad = d4b_dev_upload<int32_t>(m, d->ghost_deg_quad, d->n_ghost);
   m->d_ghost_nodal_stride = d4b_dev_upload<int64_t>(m, d->ghost_nodal_stride, d->n_ghost);
   m->d_ughost = d4b_dev_alloc<double>(m, (size_t)d->ghost_nodes);
+  d4b_comm_setup(m, d);
 
   // ---- volume metric G = w J (rst_xyz)(rst_xyz)^T, six symmetric planes
   std::vector<double> G((size_t)6 * d->local_nodes_quad);
@@ -279,15 +280,18 @@ extern "C" void d4b_mesh_destroy(d4b_mesh_t *m) {
                   m->d_side_e_m, m->d_side_e_p, m->d_side_perm, m->d_side_sub_order,
                   m->d_side_mortar_stride, m->d_mortar, m->d_ughost, m->d_u_stage, m->d_Au_stage,
                   m->d_red, m->d_work[0], m->d_work[1], m->d_work[2], m->d_work[3], m->d_generic_elem,
-                  m->d_fast_FF, m->d_uhat};
+                  m->d_fast_FF, m->d_uhat, m->d_flat_FF, m->d_send_src, m->d_send_dst, m->d_send_cnt,
+                  m->d_sendbuf};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   for (auto &c : m->fast) {
-    void *cp[] = {c.d_elem, c.d_hat_elem, c.d_FG, c.d_face_rec, c.d_face_nbr, c.d_face_code};
+    void *cp[] = {c.d_elem, c.d_hat_elem, c.d_FG, c.d_face_rec, c.d_face_nbr, c.d_face_code, c.d_face_meta,
+                  c.d_ghost_hat};
     for (void *p : cp)
       if (p) cudaFree(p);
   }
   if (m->h_red) cudaFreeHost(m->h_red);
+  d4b_comm_teardown(m);
   if (m->own_stream) cudaStreamDestroy(m->stream);
   delete m;
 }
@@ -298,6 +302,8 @@ extern "C" int64_t d4b_mesh_fast_elements(const d4b_mesh_t *m) { return m->n_loc
 extern "C" int64_t d4b_mesh_flat_elements(const d4b_mesh_t *m) { return m->n_flat_elem; }
 extern "C" int32_t d4b_mesh_launches_per_apply(const d4b_mesh_t *m) {
   int n = (m->n_generic > 0 || m->fast.empty()) ? 1 : 0;
-  for (const auto &c : m->fast) n += (c.n_hat > 0) + (c.n_elem > 0);
+  for (const auto &c : m->fast)
+    n += (c.n_hat > 0) + (c.n_interior > 0) + (c.n_ghost_hat > 0) + (c.n_elem > c.n_interior);
+  if (m->n_send_elems > 0) n += 1;   // pack kernel
   return n;
 }

@@ -110,6 +110,7 @@ bool is_dev(const void *p) {
 extern "C" double d4b_vec_dot(d4b_mesh_t *m, const double *x, const double *y, int64_t n) {
   dot_partial<<<kRedBlocks, kRedThreads, 0, m->stream>>>(x, y, n, m->d_red);
   dot_final<<<1, 1024, 0, m->stream>>>(m->d_red, kRedBlocks, m->d_red + kRedBlocks);
+  d4b_comm_allreduce_sum(m, m->d_red + kRedBlocks, 1);   // sc_allreduce of the reference; no-op on one rank
   D4B_CUDA(cudaMemcpyAsync(m->h_red, m->d_red + kRedBlocks, sizeof(double), cudaMemcpyDeviceToHost, m->stream));
   D4B_CUDA(cudaStreamSynchronize(m->stream));
   return m->h_red[0];

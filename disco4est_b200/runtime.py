@@ -27,6 +27,7 @@ EXPORTS = [
     "d4b_apply", "d4b_apply_stiffness", "d4b_sync", "d4b_set_stream",
     "d4b_vec_dot", "d4b_vec_axpy", "d4b_vec_xpby", "d4b_vec_scale",
     "d4b_cg_eigs", "d4b_cheby_smooth",
+    "d4b_comm_get_unique_id", "d4b_comm_init", "d4b_comm_destroy", "d4b_comm_size", "d4b_comm_rank",
 ]
 
 _lib = None
@@ -72,8 +73,40 @@ def load_library():
     L.d4b_cg_eigs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32]
     L.d4b_cheby_smooth.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32,
                                    C.c_double, C.c_double]
+    L.d4b_comm_get_unique_id.argtypes = [C.c_void_p]
+    L.d4b_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int]
+    L.d4b_comm_size.restype = C.c_int
+    L.d4b_comm_rank.restype = C.c_int
     _lib = L
     return L
+
+
+COMM_ID_BYTES = 128
+
+
+def comm_init_from_torch(device):
+    """Create the library's NCCL communicator for the ranks of the default
+    torch.distributed group: rank 0 draws the id, torch broadcasts its bytes."""
+    import torch
+    import torch.distributed as dist
+
+    L = load_library()
+    rank, world = dist.get_rank(), dist.get_world_size()
+    L.d4b_init(device)
+    buf = C.create_string_buffer(COMM_ID_BYTES)
+    if rank == 0:
+        L.d4b_comm_get_unique_id(buf)
+    backend = dist.get_backend()
+    t = torch.frombuffer(bytearray(buf.raw), dtype=torch.uint8).clone()
+    if backend == "nccl":
+        t = t.cuda(device)
+    dist.broadcast(t, src=0)
+    raw = bytes(t.cpu().numpy().tobytes())
+    L.d4b_comm_init(C.create_string_buffer(raw, COMM_ID_BYTES), rank, world)
+
+
+def comm_destroy():
+    load_library().d4b_comm_destroy()
 
 
 def _ptr(x):

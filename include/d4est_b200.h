@@ -146,6 +146,22 @@ int  d4b_device_count(void);
 /* bind this process to a device (reference: one MPI rank per device)       */
 void d4b_init(int device);
 
+/* ------------------------------------------------------------------- ranks */
+/* One process per GPU.  Replaces p4est->mpicomm for this path: the halo
+ * exchange (d4est_ghost_data_exchange, src/Mesh/d4est_ghost_data.c:142-255)
+ * and the scalar reductions (sc_allreduce, src/Solver/d4est_solver_cg_eigs.c:181-245)
+ * run over NCCL.  Rank 0 obtains an id, the caller broadcasts its
+ * D4B_COMM_ID_BYTES bytes with its own transport (MPI_Bcast in the reference,
+ * torch.distributed in the harness), every rank calls d4b_comm_init, then
+ * creates meshes whose desc carries mpirank/mpisize and the exchange plan.
+ * Single-rank users call none of these and need no NCCL.                    */
+#define D4B_COMM_ID_BYTES 128
+void d4b_comm_get_unique_id(void *id_out);
+void d4b_comm_init(const void *id, int rank, int size);
+void d4b_comm_destroy(void);
+int  d4b_comm_size(void);
+int  d4b_comm_rank(void);
+
 /* ------------------------------------------------------------------- mesh */
 /* replaces the per-mesh setup the reference does lazily inside
  * d4est_mesh_update (src/Mesh/d4est_mesh.c:2790-2890) for the apply path   */
