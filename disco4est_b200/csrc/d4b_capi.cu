@@ -46,6 +46,19 @@ bool is_device_ptr(const void *p) {
   return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
 }
 
+}  // namespace
+
+void d4b_apply_device(d4b_mesh *m, const double *du, double *dAu) {
+  D4B_CHECK(m->epi.mode == 0 || m->n_generic == 0, "fused epilogue on a mesh with general-kernel elements");
+  // halo exchange on the communication stream while interior elements run
+  d4b_comm_exchange_begin(m, du);
+  d4b_launch_fast(m, du, dAu, 0);
+  d4b_comm_exchange_wait(m);
+  d4b_launch_fast(m, du, dAu, 1);
+  d4b_launch_generic(m, du, dAu, 0);
+}
+
+namespace {
 void apply_impl(d4b_mesh *m, const double *u, double *Au, int stiffness_only) {
   D4B_CHECK(m && u && Au, "d4b_apply: NULL argument");
   D4B_CHECK(m->n_ghost == 0 || m->d_ughost, "d4b_apply: ghost buffer missing");
@@ -61,12 +74,8 @@ void apply_impl(d4b_mesh *m, const double *u, double *Au, int stiffness_only) {
   if (stiffness_only) {
     d4b_launch_generic(m, du, dAu, 1);
   } else {
-    // halo exchange on the communication stream while interior elements run
-    d4b_comm_exchange_begin(m, du);
-    d4b_launch_fast(m, du, dAu, 0);
-    d4b_comm_exchange_wait(m);
-    d4b_launch_fast(m, du, dAu, 1);
-    d4b_launch_generic(m, du, dAu, 0);
+    m->epi = D4bEpilogue();
+    d4b_apply_device(m, du, dAu);
   }
   if (!Au_dev) D4B_CUDA(cudaMemcpyAsync(Au, dAu, bytes, cudaMemcpyDeviceToHost, m->stream));
   if (!u_dev || !Au_dev) D4B_CUDA(cudaStreamSynchronize(m->stream));

@@ -53,6 +53,16 @@ __constant__ FastTab c_tab[9];   // indexed by N
 // code bits of an element face
 constexpr int kOwn = 1 << 6;     // this element owns the face record
 
+// what to do with a finished entry of A u (D4bEpilogue, d4b_internal.h)
+__device__ __forceinline__ void store_result(const D4bEpilogue &e, double *Au, int64_t i, double s) {
+  if (e.mode == 0) { Au[i] = s; return; }
+  if (e.mode == 2) { Au[i] = e.rhs[i] - s; return; }
+  const double r = (e.rhs[i] - s) * e.alpha;
+  const double pn = r + e.beta * e.p[i];
+  e.p[i] = pn;
+  e.u[i] += pn;
+}
+
 struct FastArgs {
   const int32_t *elem;          // [n_elem] element ids of this class
   int first;                    // this launch covers class positions [first, n_elem)
@@ -65,6 +75,7 @@ struct FastArgs {
   const int32_t *face_code;     // [6*n_elem] f_p | perm << 3 | own << 6
   const double *uh;             // Gauss-collocated input
   double *Au;
+  D4bEpilogue epi;
 };
 
 template <int N>
@@ -445,7 +456,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) fast_apply_kernel(FastArgs a)
       double s = 0.;
 #pragma unroll
       for (int i = 0; i < N; ++i) s += T.I[i][c] * l[i];
-      a.Au[ns + lt + NN * c] = s;
+      store_result(a.epi, a.Au, ns + lt + NN * c, s);
     }
   }
 }
@@ -461,7 +472,7 @@ void launch_flat(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, 
   a.nodal_stride = m->d_nodal_stride;
   a.FG = cls.d_FG; a.FF3 = m->d_flat_FF;
   a.meta = static_cast<const FaceMeta *>(cls.d_face_meta);
-  a.uh = m->d_uhat; a.Au = d_Au;
+  a.uh = m->d_uhat; a.Au = d_Au; a.epi = m->epi;
   size_t smem = (size_t)C::EPB * C::SH_PER_ELEM * sizeof(double);
   static bool configured = false;
   if (!configured) {
@@ -499,7 +510,7 @@ void launch_fast(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, 
   a.nodal_stride = m->d_nodal_stride;
   a.FG = cls.d_FG; a.FF = m->d_fast_FF;
   a.face_rec = cls.d_face_rec; a.face_nbr = cls.d_face_nbr; a.face_code = cls.d_face_code;
-  a.uh = m->d_uhat; a.Au = d_Au;
+  a.uh = m->d_uhat; a.Au = d_Au; a.epi = m->epi;
   size_t smem = (size_t)C::EPB * C::SH_PER_ELEM * sizeof(double);
   static bool configured = false;
   if (!configured) {

@@ -34,12 +34,18 @@ struct FlatArgs {
   const FaceMeta *meta;         // [6*n_elem]
   const double *uh;
   double *Au;
+  D4bEpilogue epi;
   int prefetch;                 // 1: bulk-prefetch the block's volume metric into L2 at kernel start
 };
 
 // ask the L2 for `bytes` (multiple of 16) at a 16-byte aligned global address
 __device__ __forceinline__ void l2_prefetch(const void *ptr, unsigned bytes) {
   asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(ptr), "r"(bytes) : "memory");
+}
+
+// per-line L2 prefetch (no alignment requirement)
+__device__ __forceinline__ void l2_prefetch_line(const void *ptr) {
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(ptr));
 }
 
 template <int N>
@@ -131,6 +137,15 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) f
     constexpr unsigned kBlockBytes = C::EPB * 6 * N3 * sizeof(double);
     const int e0 = a.first + (int)blockIdx.x * C::EPB, left = a.n_elem - e0;
     l2_prefetch(a.FG + (size_t)e0 * (6 * N3), left >= C::EPB ? kBlockBytes : left * 6 * N3 * 8);
+  }
+  // fused smoother: its three operand streams are only touched by the very last
+  // phase; have them in L2 by then
+  if (active && a.epi.mode == 1 && a.prefetch) {
+    for (int off = lt * 16; off < N3; off += NN * 16) {
+      l2_prefetch_line(a.epi.rhs + ns + off);
+      l2_prefetch_line(a.epi.p + ns + off);
+      l2_prefetch_line(a.epi.u + ns + off);
+    }
   }
   // ---- T-orientation (a,b) = (lx,ly), line along c ----
   if (active) {
@@ -296,7 +311,7 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) f
       double s = 0.;
 #pragma unroll
       for (int i = 0; i < N; ++i) s += T.I[i][c] * l[i];
-      a.Au[ns + lt + NN * c] = s;
+      store_result(a.epi, a.Au, ns + lt + NN * c, s);
     }
   }
 }

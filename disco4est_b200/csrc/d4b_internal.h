@@ -58,6 +58,19 @@ struct D4bFastClass {
   void *d_face_meta = nullptr;   // kind 1: [6*n_elem] packed face descriptors
 };
 
+// what the fast kernels do with a finished value s = (A u)[i] (fused smoother,
+// d4est_solver_multigrid_smoother_cheby.c:130-152):
+//   mode 0: Au[i] = s
+//   mode 1: r = alpha (rhs[i] - s); p[i] = r + beta p[i]; u[i] += p[i]   (u is updated in place:
+//           the kernels read the Gauss-collocated copy uhat, never u)
+//   mode 2: Au[i] = rhs[i] - s
+struct D4bEpilogue {
+  int mode = 0;
+  const double *rhs = nullptr;
+  double *p = nullptr, *u = nullptr;
+  double alpha = 0., beta = 0.;
+};
+
 // halo exchange with one neighbour rank; offsets / counts in doubles
 struct D4bPeer {
   int rank = 0;
@@ -132,6 +145,7 @@ struct d4b_mesh {
   int64_t n_flat_elem = 0;
   int64_t n_face_shared = 0, n_face_split = 0;
   int generic_smem = 0;
+  D4bEpilogue epi;                     // epilogue of the next fast-kernel launches
 };
 
 template <typename T>
@@ -141,6 +155,8 @@ T *d4b_dev_upload(d4b_mesh *m, const T *h, size_t n);
 
 // kernels / launchers
 void d4b_launch_generic(d4b_mesh *m, const double *d_u, double *d_Au, int stiffness_only);
+// the whole apply on device pointers (halo exchange, fast kernels with m->epi, generic kernel)
+void d4b_apply_device(d4b_mesh *m, const double *d_u, double *d_Au);
 void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *desc, const std::vector<double> &mortar,
                     const std::vector<double> &G, const std::vector<int32_t> &elem_side,
                     std::vector<char> &is_fast);

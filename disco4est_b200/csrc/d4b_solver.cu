@@ -6,6 +6,7 @@
 //   ..._smoother_cheby_iterate_aux         src/Solver/d4est_solver_multigrid_smoother_cheby.c:81-176
 // Reductions are deterministic: fixed grid, fixed-shape tree, no atomics.
 #include <cmath>
+#include <cstdlib>
 #include "d4b_internal.h"
 
 namespace {
@@ -203,16 +204,33 @@ extern "C" void d4b_cheby_smooth(d4b_mesh_t *m, double *u, const double *rhs, do
   const double d = (lmax + lmin) * .5, c = (lmax - lmin) * .5;
   double alpha = 0., beta;
   D4B_CUDA(cudaMemsetAsync(p, 0, bytes, m->stream));
+  // every element in a fast kernel: the recurrence runs in the apply's epilogue
+  // (u updated in place, no Au vector); otherwise apply + one vector kernel
+  const char *nf = getenv("D4B_NO_FUSED_CHEBY");
+  const bool fused = m->n_generic == 0 && !m->fast.empty() && !(nf && nf[0] == '1');
   for (int i = 0; i < iter; ++i) {
-    d4b_apply(m, du, Au);
     if (i == 0) alpha = 1. / d;
     else if (i == 1) alpha = 2. * d / (2 * d * d - c * c);
     else alpha = 1. / (d - (alpha * c * c / 4.));
     beta = alpha * d - 1.;
-    cheby_update_k<<<g, 256, 0, m->stream>>>(alpha, beta, drhs, Au, p, du, n);
+    if (fused) {
+      m->epi.mode = 1; m->epi.rhs = drhs; m->epi.p = p; m->epi.u = du;
+      m->epi.alpha = alpha; m->epi.beta = beta;
+      d4b_apply_device(m, du, nullptr);
+    } else {
+      d4b_apply(m, du, Au);
+      cheby_update_k<<<g, 256, 0, m->stream>>>(alpha, beta, drhs, Au, p, du, n);
+    }
   }
-  d4b_apply(m, du, Au);
-  residual_k<<<g, 256, 0, m->stream>>>(drhs, Au, dr, n);
+  if (fused) {
+    m->epi = D4bEpilogue();
+    m->epi.mode = 2; m->epi.rhs = drhs;
+    d4b_apply_device(m, du, dr);
+    m->epi = D4bEpilogue();
+  } else {
+    d4b_apply(m, du, Au);
+    residual_k<<<g, 256, 0, m->stream>>>(drhs, Au, dr, n);
+  }
   if (!u_dev) D4B_CUDA(cudaMemcpyAsync(u, du, bytes, cudaMemcpyDeviceToHost, m->stream));
   if (!r_dev) D4B_CUDA(cudaMemcpyAsync(r, dr, bytes, cudaMemcpyDeviceToHost, m->stream));
   if (!u_dev || !r_dev) D4B_CUDA(cudaStreamSynchronize(m->stream));

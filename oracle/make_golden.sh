@@ -17,9 +17,10 @@ run() { # name ini args...
 }
 run brick_l2_p1 brick_poisson.ini                       # the 4^3 p=1 mesh of d4est_test_poisson_sinx.sh
 run brick_l2_p2_bc brick_poisson.ini --uniform-deg 2 --bc poly
-run brick_l2_p3 brick_poisson.ini --uniform-deg 3 --cheby 1 1
+run brick_l2_p3 brick_poisson.ini --uniform-deg 3 --cheby 15 15   # + cg_eigs / Chebyshev smoother outputs
 run brick_l2_p5 brick_poisson.ini --uniform-deg 5
 run brick_l2_p7 brick_poisson.ini --uniform-deg 7
-run sphere_p2 sphere_p.ini --uniform-deg 2               # conforming, 13 trees, all face orientations
+run sphere_p2 sphere_p.ini --uniform-deg 2 --cheby 8 10 # conforming, 13 trees, all face orientations; smoother outputs
 run sphere_hp_amr0 sphere_hp.ini --bc poly               # per-region degrees + quadrature increments
 run sphere_hp_amr1 sphere_hp.ini --amr 1 --bc poly       # random hp refinement: hanging faces
+run sphere_hp_amr1_zero sphere_hp.ini --amr 1 --cheby 8 10  # hanging faces, homogeneous BC, smoother outputs

@@ -362,6 +362,41 @@ main (int argc, char *argv[])
                                               d4est_factors, u, Ku, local_nodes, 0);
       d4b_dump_put1 (f, "Ku", D4B_F64, local_nodes, Ku);
       P4EST_FREE (Ku);
+
+      /* the smoother exactly as d4est_solver_multigrid_smoother_cheby does it
+       * (src/Solver/d4est_solver_multigrid_smoother_cheby.c:264-376): cg_eigs
+       * from the current guess (which advances the guess in place), lmax = bound,
+       * lmin = lmax / ratio, then cheby_imax iterations leaving u and r = rhs - A u.
+       * Problem: rhs = A u_seeded (homogeneous operator), initial guess u_seeded / 2. */
+      if (!bc_poly) {
+        const double ratio = 30.;
+        double *cu = P4EST_ALLOC (double, local_nodes);
+        double *cAu = P4EST_ALLOC_ZERO (double, local_nodes);
+        double *cr = P4EST_ALLOC_ZERO (double, local_nodes);
+        d4est_elliptic_data_t cv = vecs;
+        cv.u = cu; cv.Au = cAu; cv.rhs = Au_plain;
+        double eig_new = -1., eig_old = -1.;
+        for (int i = 0; i < local_nodes; i++) cu[i] = .5 * u[i];
+        cg_eigs (p4est, &cv, &fcns_plain, d4est_ghost, d4est_ghost_data, d4est_ops, d4est_geom,
+                 d4est_quad, d4est_factors, cheby_eigs_imax, 0, 1, &eig_new);
+        for (int i = 0; i < local_nodes; i++) cu[i] = .5 * u[i];
+        cg_eigs (p4est, &cv, &fcns_plain, d4est_ghost, d4est_ghost_data, d4est_ops, d4est_geom,
+                 d4est_quad, d4est_factors, cheby_eigs_imax, 0, 0, &eig_old);
+        d4b_dump_put1 (f, "cheby_rhs", D4B_F64, local_nodes, Au_plain);
+        d4b_dump_put1 (f, "cheby_eig_new", D4B_F64, 1, &eig_new);
+        d4b_dump_put1 (f, "cheby_eig_old", D4B_F64, 1, &eig_old);
+        d4b_dump_put1 (f, "cheby_u_after_eigs", D4B_F64, local_nodes, cu);
+        double lmax = eig_old, lmin = lmax / ratio;
+        d4est_solver_multigrid_smoother_cheby_iterate_aux (p4est, d4est_ops, d4est_geom, d4est_quad,
+                                                           d4est_factors, d4est_ghost, d4est_ghost_data,
+                                                           &cv, &fcns_plain, cr, cheby_imax, lmin, lmax,
+                                                           0, 0, 1);
+        double params[4] = { (double) cheby_imax, (double) cheby_eigs_imax, ratio, lmax };
+        d4b_dump_put1 (f, "cheby_params", D4B_F64, 4, params);
+        d4b_dump_put1 (f, "cheby_u", D4B_F64, local_nodes, cu);
+        d4b_dump_put1 (f, "cheby_r", D4B_F64, local_nodes, cr);
+        P4EST_FREE (cu); P4EST_FREE (cAu); P4EST_FREE (cr);
+      }
     }
     fclose (f);
     d4est_b200_flat_destroy (flat);

@@ -1,0 +1,79 @@
+"""cg_eigs + Chebyshev smoother against the outputs of the unmodified reference
+(tests/golden/*: cheby_* records written by oracle/ref_driver.c --cheby)."""
+import numpy as np
+import pytest
+
+from oracle_lib import Oracle
+from solver_ref import cg_eigs, cheby
+
+CASES = ["brick_l2_p3", "sphere_p2", "sphere_hp_amr1_zero"]
+
+
+def rel(a, b):
+    return np.linalg.norm(a - b) / np.linalg.norm(b)
+
+
+def problem(A):
+    imax, eigs_imax, ratio, lmax = (float(x) for x in A["cheby_params"])
+    return int(imax), int(eigs_imax), ratio, lmax, np.ascontiguousarray(A["cheby_rhs"]), 0.5 * A["u"]
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_restatement_matches_reference(golden, case):
+    """pins tests/solver_ref.py (and the oracle apply under it) to the reference"""
+    A = golden(case)
+    imax, eigs_imax, ratio, lmax, rhs, u0 = problem(A)
+    orc = Oracle(A)
+    e_new, _ = cg_eigs(orc.apply, u0, rhs, eigs_imax, use_new=1)
+    e_old, u1 = cg_eigs(orc.apply, u0, rhs, eigs_imax, use_new=0)
+    assert abs(e_new - A["cheby_eig_new"][0]) <= 1e-10 * e_new
+    assert abs(e_old - A["cheby_eig_old"][0]) <= 1e-10 * e_old
+    assert e_old == pytest.approx(lmax, rel=1e-10)
+    assert rel(u1, A["cheby_u_after_eigs"]) < 1e-10
+    u2, r2 = cheby(orc.apply, A["cheby_u_after_eigs"], rhs, imax, lmax / ratio, lmax)
+    assert rel(u2, A["cheby_u"]) < 1e-11
+    assert rel(r2, A["cheby_r"]) < 1e-10
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", CASES)
+def test_gpu_cg_eigs_and_cheby_match_reference(golden, case):
+    from disco4est_b200 import Mesh
+
+    A = golden(case)
+    imax, eigs_imax, ratio, lmax, rhs, u0 = problem(A)
+    m = Mesh(A)
+    u = u0.copy()
+    e_new = m.cg_eigs(u, rhs, eigs_imax, use_new=1)
+    assert abs(e_new - A["cheby_eig_new"][0]) <= 1e-10 * e_new
+    u = u0.copy()
+    e_old = m.cg_eigs(u, rhs, eigs_imax, use_new=0)
+    assert abs(e_old - A["cheby_eig_old"][0]) <= 1e-10 * e_old
+    assert rel(u, A["cheby_u_after_eigs"]) < 1e-10       # the estimate advances u in place, like the reference
+    # zero-guess variant leaves u alone
+    u_keep = u0.copy()
+    m.cg_eigs(u_keep, rhs, eigs_imax, use_new=0, use_zero_guess=1)
+    assert np.array_equal(u_keep, u0)
+    u = np.ascontiguousarray(A["cheby_u_after_eigs"]).copy()
+    r = np.zeros_like(u)
+    m.cheby_smooth(u, rhs, r, imax, e_old / ratio, e_old)
+    assert rel(u, A["cheby_u"]) < 1e-11
+    assert rel(r, A["cheby_r"]) < 1e-10
+    m.close()
+
+
+@pytest.mark.gpu
+def test_gpu_cheby_device_pointers(golden):
+    import torch
+    from disco4est_b200 import Mesh
+
+    A = golden("brick_l2_p3")
+    imax, eigs_imax, ratio, lmax, rhs, u0 = problem(A)
+    m = Mesh(A)
+    u = torch.from_numpy(np.ascontiguousarray(A["cheby_u_after_eigs"])).cuda()
+    r = torch.zeros_like(u)
+    m.cheby_smooth(u, torch.from_numpy(rhs).cuda(), r, imax, lmax / ratio, lmax)
+    m.sync()
+    assert rel(u.cpu().numpy(), A["cheby_u"]) < 1e-11
+    assert rel(r.cpu().numpy(), A["cheby_r"]) < 1e-10
+    m.close()
