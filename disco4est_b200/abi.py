@@ -80,6 +80,28 @@ class ChebyParams(C.Structure):
         ("cheby_eigs_max_multiplier", C.c_double),
         ("cheby_use_new_cg_eigs", C.c_int32),
         ("cheby_use_zero_guess_for_eigs", C.c_int32),
+        ("cheby_eigs_reuse_fromdownvcycle", C.c_int32),
+        ("cheby_eigs_reuse_fromlastvcycle", C.c_int32),
+    ]
+
+
+class MgDesc(C.Structure):
+    """d4b_mg_desc_t"""
+
+    _fields_ = [
+        ("n_levels", C.c_int32),
+        ("meshes", C.POINTER(C.c_void_p)),
+        ("child_first", C.POINTER(_I32P)),
+        ("child_count", C.POINTER(_I32P)),
+        ("vcycle_imax", C.c_int32),
+        ("vcycle_rtol", C.c_double),
+        ("vcycle_atol", C.c_double),
+        ("smoother", ChebyParams),
+        ("bottom_solver", C.c_int32),
+        ("bottom_iter", C.c_int32),
+        ("bottom_rtol", C.c_double),
+        ("bottom_atol", C.c_double),
+        ("bottom_cheby", ChebyParams),
     ]
 
 

@@ -205,3 +205,20 @@ def brick_xyz(level, p, rank=0, world=1, trees=(1, 1, 1)):
     Z = iz[:, None, None, None] * h + x1[None, :, None, None]
     X, Y, Z = np.broadcast_arrays(X, Y, Z)
     return np.stack([X.reshape(-1), Y.reshape(-1), Z.reshape(-1)])
+
+
+def brick_hierarchy(level, p, rank=0, world=1, trees=(1, 1, 1), **kw):
+    """h-multigrid hierarchy of the brick, coarsest (one element per tree) first, as the
+    reference builds it with p4est_coarsen_ext (d4est_solver_multigrid.c:984): every
+    coarse element is the parent of the 8 consecutive (z-order) fine elements
+    8e..8e+7; the degree stays p (coarse degree = min of the children,
+    callbacks.h:51-76).  Needs one tree per rank when world > 1 so that families and
+    their parents share a rank at every level.  Returns (descs, transfers) with
+    transfers[l] = (child_first, child_count) between level l and l+1."""
+    assert world == 1 or world == trees[0] * trees[1] * trees[2], "multi-rank hierarchy: one tree per rank"
+    descs = [brick_desc(l, p, rank=rank, world=world, trees=trees, **kw) for l in range(level + 1)]
+    transfers = []
+    for l in range(level):
+        E = descs[l]["n_local"]
+        transfers.append((8 * np.arange(E, dtype=np.int32), np.full(E, 8, np.int32)))
+    return descs, transfers

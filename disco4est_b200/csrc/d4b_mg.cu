@@ -1,0 +1,435 @@
+// d4b_mg.cu -- device-resident multigrid V-cycle over a caller-described
+// hierarchy of meshes (include/d4est_b200.h, "multigrid").
+//
+// Follows d4est_solver_multigrid_vcycle (src/Solver/d4est_solver_multigrid.c:751-1349):
+//   down, level top..1 : u_l = 0 below the top; smooth -> r_l = rhs_l - A u_l;
+//                        rhs_{l-1} = P^T r_l            (callbacks.h:110-203)
+//   bottom             : u_0 = 0; bottom solver
+//   up, level 0..top-1 : u_{l+1} += P u_l; smooth       (callbacks.h:237-329, :1250)
+// with the Chebyshev smoother of d4est_solver_multigrid_smoother_cheby.c:222-376
+// (eigenvalue re-use rules included) and the CG / Chebyshev bottom solvers.
+// All level vectors stay in HBM; the only host traffic is the scalars of the
+// dot products that steer CG and the stopping tests.
+#include <cmath>
+#include <cstring>
+#include "d4b_internal.h"
+
+struct d4b_mg {
+  int n_levels = 0;
+  std::vector<d4b_mesh *> mesh;
+  std::vector<int32_t *> d_child_first, d_child_count;   // [n_levels-1]
+  std::vector<double *> d_u, d_rhs, d_r;                 // per level (top: only d_r; u/rhs are the caller's)
+  double *d_top_u = nullptr, *d_top_rhs = nullptr;       // staging for host-pointer calls
+  double *d_P = nullptr;                                 // 1-D prolongation tables
+  int32_t *d_P_off = nullptr;                            // ((degH-1)*7 + (degh-1))*3 + half -> offset
+  d4b_mg_desc_t prm;
+  std::vector<double> eigs;
+  double bottom_eig = 0.;
+  int vcycle_num_finished = 0;
+};
+
+namespace {
+
+bool is_dev(const void *p) {
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
+}
+
+constexpr int kMaxN = D4B_MAXN;
+
+// One block per coarse element.  dir = 0: fine[child] (+)= P_c coarse;  dir = 1: coarse = sum_c P_c^T fine[child]
+// (children in z-order, summed in that order like d4est_operators_apply_hp_prolong_transpose).
+__global__ void __launch_bounds__(128) transfer_kernel(int dir, int accumulate, int n_coarse,
+                                                       const int32_t *__restrict__ child_first,
+                                                       const int32_t *__restrict__ child_count,
+                                                       const int32_t *__restrict__ deg_c,
+                                                       const int64_t *__restrict__ stride_c,
+                                                       const int32_t *__restrict__ deg_f,
+                                                       const int64_t *__restrict__ stride_f,
+                                                       const double *__restrict__ P, const int32_t *__restrict__ P_off,
+                                                       const double *__restrict__ in, double *__restrict__ out) {
+  __shared__ double sA[kMaxN * kMaxN * kMaxN], sB[kMaxN * kMaxN * kMaxN], sAcc[kMaxN * kMaxN * kMaxN];
+  const int e = blockIdx.x;
+  if (e >= n_coarse) return;
+  const int nH = deg_c[e] + 1, nH3 = nH * nH * nH;
+  const int64_t sH = stride_c[e];
+  const int first = child_first[e], count = child_count[e];
+  if (dir == 0) {
+    for (int i = threadIdx.x; i < nH3; i += blockDim.x) sAcc[i] = in[sH + i];
+  } else {
+    for (int i = threadIdx.x; i < nH3; i += blockDim.x) sAcc[i] = 0.;
+  }
+  __syncthreads();
+  for (int c = 0; c < count; ++c) {
+    const int ef = first + c;
+    const int nh = deg_f[ef] + 1;
+    const int64_t sh = stride_f[ef];
+    const int hx = count == 1 ? 0 : 1 + (c & 1), hy = count == 1 ? 0 : 1 + ((c >> 1) & 1),
+              hz = count == 1 ? 0 : 1 + ((c >> 2) & 1);
+    const int tb = ((nH - 2) * 7 + (nh - 2)) * 3;
+    const double *Px = P + P_off[tb + hx], *Py = P + P_off[tb + hy], *Pz = P + P_off[tb + hz];   // [nh x nH]
+    if (dir == 0) {
+      // x: [nH,nH,nH] -> [nH,nH,nh]
+      for (int o = threadIdx.x; o < nH * nH * nh; o += blockDim.x) {
+        int i2 = o % nh, jk = o / nh;
+        double s = 0.;
+        for (int i = 0; i < nH; ++i) s += Px[i2 * nH + i] * sAcc[jk * nH + i];
+        sA[o] = s;
+      }
+      __syncthreads();
+      // y: [nH,nH,nh] -> [nH,nh,nh]
+      for (int o = threadIdx.x; o < nH * nh * nh; o += blockDim.x) {
+        int i2 = o % nh, j2 = (o / nh) % nh, k = o / (nh * nh);
+        double s = 0.;
+        for (int j = 0; j < nH; ++j) s += Py[j2 * nH + j] * sA[(k * nH + j) * nh + i2];
+        sB[o] = s;
+      }
+      __syncthreads();
+      // z: [nH,nh,nh] -> [nh,nh,nh]
+      for (int o = threadIdx.x; o < nh * nh * nh; o += blockDim.x) {
+        int ij = o % (nh * nh), k2 = o / (nh * nh);
+        double s = 0.;
+        for (int k = 0; k < nH; ++k) s += Pz[k2 * nH + k] * sB[k * nh * nh + ij];
+        if (accumulate) out[sh + o] += s; else out[sh + o] = s;
+      }
+      __syncthreads();
+    } else {
+      for (int i = threadIdx.x; i < nh * nh * nh; i += blockDim.x) sA[i] = in[sh + i];
+      __syncthreads();
+      // x^T: [nh,nh,nh] -> [nh,nh,nH]
+      for (int o = threadIdx.x; o < nh * nh * nH; o += blockDim.x) {
+        int i = o % nH, jk = o / nH;
+        double s = 0.;
+        for (int i2 = 0; i2 < nh; ++i2) s += Px[i2 * nH + i] * sA[jk * nh + i2];
+        sB[o] = s;
+      }
+      __syncthreads();
+      // y^T: [nh,nh,nH] -> [nh,nH,nH]
+      for (int o = threadIdx.x; o < nh * nH * nH; o += blockDim.x) {
+        int i = o % nH, j = (o / nH) % nH, k2 = o / (nH * nH);
+        double s = 0.;
+        for (int j2 = 0; j2 < nh; ++j2) s += Py[j2 * nH + j] * sB[(k2 * nh + j2) * nH + i];
+        sA[o] = s;
+      }
+      __syncthreads();
+      // z^T: [nh,nH,nH] -> [nH,nH,nH], added to the parent
+      for (int o = threadIdx.x; o < nH3; o += blockDim.x) {
+        int ij = o % (nH * nH), k = o / (nH * nH);
+        double s = 0.;
+        for (int k2 = 0; k2 < nh; ++k2) s += Pz[k2 * nH + k] * sA[k2 * nH * nH + ij];
+        sAcc[o] += s;
+      }
+      __syncthreads();
+    }
+  }
+  if (dir == 1)
+    for (int i = threadIdx.x; i < nH3; i += blockDim.x) out[sH + i] = sAcc[i];
+}
+
+void transfer(d4b_mg *g, int dir, int accumulate, int lc, const double *in, double *out) {
+  d4b_mesh *mc = g->mesh[lc], *mf = g->mesh[lc + 1];
+  transfer_kernel<<<mc->n_local, 128, 0, mf->stream>>>(dir, accumulate, mc->n_local, g->d_child_first[lc],
+                                                       g->d_child_count[lc], mc->d_deg, mc->d_nodal_stride,
+                                                       mf->d_deg, mf->d_nodal_stride, g->d_P, g->d_P_off, in, out);
+  D4B_CUDA(cudaGetLastError());
+}
+
+__global__ void copy2_k(const double *__restrict__ a, double *__restrict__ b, int64_t n) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    b[i] = a[i];
+}
+__global__ void resid_k(const double *__restrict__ rhs, const double *__restrict__ Au, double *__restrict__ r,
+                        int64_t n) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    r[i] = rhs[i] - Au[i];
+}
+__global__ void resid_init_k(const double *__restrict__ rhs, const double *__restrict__ Au, double *__restrict__ r,
+                             double *__restrict__ d, int64_t n) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    double v = rhs[i] - Au[i];
+    r[i] = v; d[i] = v;
+  }
+}
+__global__ void cg_step_k(double alpha, const double *__restrict__ d, const double *__restrict__ Au,
+                          double *__restrict__ u, double *__restrict__ r, int64_t n) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    u[i] += alpha * d[i];
+    r[i] -= alpha * Au[i];
+  }
+}
+__global__ void xpby_k(const double *__restrict__ x, double b, double *__restrict__ y, int64_t n) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    y[i] = x[i] + b * y[i];
+}
+int grid_for(int64_t n) {
+  int64_t b = (n + 255) / 256;
+  return (int)(b < 148 * 8 ? (b > 0 ? b : 1) : 148 * 8);
+}
+
+// Chebyshev smoother of one level, d4est_solver_multigrid_smoother_cheby.c:264-376
+void smooth(d4b_mg *g, int level, double *u, const double *rhs, double *r, bool compute_eigs) {
+  const d4b_cheby_params_t &c = g->prm.smoother;
+  d4b_mesh *m = g->mesh[level];
+  if (compute_eigs) {
+    // with a zero guess the estimate runs on a scratch vector and u is untouched (:281-305)
+    double e = d4b_cg_eigs(m, u, rhs, c.cheby_eigs_cg_imax, c.cheby_use_new_cg_eigs, c.cheby_use_zero_guess_for_eigs);
+    g->eigs[level] = e * c.cheby_eigs_max_multiplier;
+  }
+  // (:322-349 re-runs cg_eigs on a zero vector into a dummy when the estimate is
+  //  re-used with the zero-guess option; it changes no state and is skipped here)
+  const double lmax = g->eigs[level], lmin = lmax / c.cheby_eigs_lmax_lmin_ratio;
+  d4b_cheby_smooth(m, u, rhs, r, c.cheby_imax, lmin, lmax);
+}
+
+// d4est_solver_multigrid_bottom_solver_cg.c:48-200
+void bottom_cg(d4b_mg *g, double *u, const double *rhs, double *r) {
+  d4b_mesh *m = g->mesh[0];
+  const int64_t n = m->local_nodes;
+  const int gr = grid_for(n);
+  double *Au = m->d_Au_stage;
+  if (!m->d_work[3]) m->d_work[3] = d4b_dev_alloc<double>(m, (size_t)n);
+  double *d = m->d_work[3];
+  d4b_apply(m, u, Au);
+  resid_init_k<<<gr, 256, 0, m->stream>>>(rhs, Au, r, d, n);
+  double delta_new = d4b_vec_dot(m, r, r, n);
+  const double delta_0 = delta_new, rtol = g->prm.bottom_rtol, atol = g->prm.bottom_atol;
+  for (int i = 0; i < g->prm.bottom_iter && (delta_new > atol * atol + delta_0 * rtol * rtol); ++i) {
+    d4b_apply(m, d, Au);
+    const double d_dot_Au = d4b_vec_dot(m, d, Au, n);
+    const double alpha = delta_new / d_dot_Au;
+    cg_step_k<<<gr, 256, 0, m->stream>>>(alpha, d, Au, u, r, n);
+    const double delta_old = delta_new;
+    delta_new = d4b_vec_dot(m, r, r, n);
+    xpby_k<<<gr, 256, 0, m->stream>>>(r, delta_new / delta_old, d, n);
+  }
+}
+
+// d4est_solver_multigrid_bottom_solver_cheby.c:60-115
+void bottom_cheby(d4b_mg *g, double *u, const double *rhs, double *r) {
+  const d4b_cheby_params_t &c = g->prm.bottom_cheby;
+  d4b_mesh *m = g->mesh[0];
+  g->bottom_eig = d4b_cg_eigs(m, u, rhs, c.cheby_eigs_cg_imax, c.cheby_use_new_cg_eigs, 0) * c.cheby_eigs_max_multiplier;
+  d4b_cheby_smooth(m, u, rhs, r, c.cheby_imax, g->bottom_eig / c.cheby_eigs_lmax_lmin_ratio, g->bottom_eig);
+}
+
+// one V-cycle on device pointers; returns the global squared residual of the top level
+double vcycle_device(d4b_mg *g, double *u_top, const double *rhs_top) {
+  const int top = g->n_levels - 1;
+  const d4b_cheby_params_t &c = g->prm.smoother;
+  const int vc = g->vcycle_num_finished;
+  // ..._smoother_cheby_update (:222-262): decided at PRE_V for the whole down leg,
+  // at UPV_PRE_SMOOTH for every smoothing of the up leg
+  const bool eigs_down = !(c.cheby_eigs_reuse_fromlastvcycle == 1 && vc != 0);
+  const bool eigs_up = !(c.cheby_eigs_reuse_fromdownvcycle == 1 || (c.cheby_eigs_reuse_fromlastvcycle == 1 && vc != 0));
+  D4B_CHECK(!(c.cheby_use_zero_guess_for_eigs == 1 && c.cheby_eigs_reuse_fromdownvcycle != 1),
+            "cheby_use_zero_guess_for_eigs = 1 needs cheby_eigs_reuse_fromdownvcycle = 1 "
+            "(d4est_solver_multigrid_smoother_cheby.c:315-320)");
+  for (int l = top; l > 0; --l) {
+    d4b_mesh *m = g->mesh[l];
+    double *u = (l == top) ? u_top : g->d_u[l];
+    const double *rhs = (l == top) ? rhs_top : g->d_rhs[l];
+    if (l != top) D4B_CUDA(cudaMemsetAsync(u, 0, (size_t)m->local_nodes * sizeof(double), m->stream));
+    smooth(g, l, u, rhs, g->d_r[l], eigs_down);
+    // restricted residual is the coarse right-hand side
+    D4B_CUDA(cudaStreamSynchronize(m->stream));   // levels may use different streams
+    transfer(g, 1, 0, l - 1, g->d_r[l], g->d_rhs[l - 1]);
+    D4B_CUDA(cudaStreamSynchronize(m->stream));
+  }
+  {
+    d4b_mesh *m = g->mesh[0];
+    D4B_CUDA(cudaMemsetAsync(g->d_u[0], 0, (size_t)m->local_nodes * sizeof(double), m->stream));
+    if (g->prm.bottom_solver == 0) bottom_cg(g, g->d_u[0], g->d_rhs[0], g->d_r[0]);
+    else bottom_cheby(g, g->d_u[0], g->d_rhs[0], g->d_r[0]);
+    D4B_CUDA(cudaStreamSynchronize(m->stream));
+  }
+  for (int l = 0; l < top; ++l) {
+    const int f = l + 1;
+    d4b_mesh *m = g->mesh[f];
+    double *u = (f == top) ? u_top : g->d_u[f];
+    const double *rhs = (f == top) ? rhs_top : g->d_rhs[f];
+    transfer(g, 0, 1, l, g->d_u[l], u);   // u_fine += P u_coarse
+    smooth(g, f, u, rhs, g->d_r[f], eigs_up);
+    D4B_CUDA(cudaStreamSynchronize(m->stream));
+  }
+  d4b_mesh *mt = g->mesh[top];
+  return d4b_vec_dot(mt, g->d_r[top], g->d_r[top], mt->local_nodes);
+}
+
+struct TopVectors {
+  double *u = nullptr;
+  const double *rhs = nullptr;
+  bool u_dev = true;
+};
+
+TopVectors stage_in(d4b_mg *g, double *u, const double *rhs) {
+  d4b_mesh *mt = g->mesh[g->n_levels - 1];
+  const size_t bytes = (size_t)mt->local_nodes * sizeof(double);
+  TopVectors t;
+  t.u_dev = is_dev(u);
+  if (t.u_dev) t.u = u;
+  else {
+    if (!g->d_top_u) g->d_top_u = d4b_dev_alloc<double>(mt, (size_t)mt->local_nodes);
+    D4B_CUDA(cudaMemcpyAsync(g->d_top_u, u, bytes, cudaMemcpyHostToDevice, mt->stream));
+    t.u = g->d_top_u;
+  }
+  if (is_dev(rhs)) t.rhs = rhs;
+  else {
+    if (!g->d_top_rhs) g->d_top_rhs = d4b_dev_alloc<double>(mt, (size_t)mt->local_nodes);
+    D4B_CUDA(cudaMemcpyAsync(g->d_top_rhs, rhs, bytes, cudaMemcpyHostToDevice, mt->stream));
+    t.rhs = g->d_top_rhs;
+  }
+  return t;
+}
+
+void stage_out(d4b_mg *g, const TopVectors &t, double *u) {
+  d4b_mesh *mt = g->mesh[g->n_levels - 1];
+  if (!t.u_dev)
+    D4B_CUDA(cudaMemcpyAsync(u, t.u, (size_t)mt->local_nodes * sizeof(double), cudaMemcpyDeviceToHost, mt->stream));
+  D4B_CUDA(cudaStreamSynchronize(mt->stream));
+}
+
+}  // namespace
+
+extern "C" d4b_mg_t *d4b_mg_create(const d4b_mg_desc_t *desc) {
+  D4B_CHECK(desc && desc->n_levels >= 2, "d4b_mg_create: needs at least two levels (d4est_solver_multigrid.c:1434)");
+  d4b_mg *g = new d4b_mg();
+  g->n_levels = desc->n_levels;
+  g->prm = *desc;
+  g->eigs.assign(desc->n_levels, 0.);
+  for (int l = 0; l < desc->n_levels; ++l) {
+    D4B_CHECK(desc->meshes[l], "d4b_mg_create: level %d has no mesh", l);
+    g->mesh.push_back(desc->meshes[l]);
+  }
+  g->prm.meshes = nullptr; g->prm.child_first = nullptr; g->prm.child_count = nullptr;
+  const int top = desc->n_levels - 1;
+  // transfer maps, validated: every fine element has exactly one parent, in order
+  for (int l = 0; l < top; ++l) {
+    d4b_mesh *mc = g->mesh[l], *mf = g->mesh[l + 1];
+    int next = 0;
+    for (int e = 0; e < mc->n_local; ++e) {
+      const int cnt = desc->child_count[l][e];
+      D4B_CHECK(cnt == 1 || cnt == 8, "level %d element %d: child count %d", l, e, cnt);
+      D4B_CHECK(desc->child_first[l][e] == next, "level %d element %d: children are not consecutive", l, e);
+      next += cnt;
+    }
+    D4B_CHECK(next == mf->n_local, "level %d: children cover %d of %d fine elements", l, next, mf->n_local);
+    g->d_child_first.push_back(d4b_dev_upload<int32_t>(mc, desc->child_first[l], mc->n_local));
+    g->d_child_count.push_back(d4b_dev_upload<int32_t>(mc, desc->child_count[l], mc->n_local));
+  }
+  for (int l = 0; l <= top; ++l) {
+    d4b_mesh *m = g->mesh[l];
+    g->d_r.push_back(d4b_dev_alloc<double>(m, (size_t)m->local_nodes));
+    g->d_u.push_back(l < top ? d4b_dev_alloc<double>(m, (size_t)m->local_nodes) : nullptr);
+    g->d_rhs.push_back(l < top ? d4b_dev_alloc<double>(m, (size_t)m->local_nodes) : nullptr);
+  }
+  // 1-D prolongation tables for degH <= degh: Lagrange basis on LGL(degH) evaluated at the
+  // LGL(degh) nodes of the whole interval (half 0, build_p_prolong_1d d4est_operators.c:995-1012)
+  // or of the lower / upper half (half 1, 2, build_hp_prolong_1d :944-993)
+  std::vector<double> P;
+  std::vector<int32_t> off(7 * 7 * 3, -1);
+  for (int dH = 1; dH <= D4B_MAX_DEG; ++dH)
+    for (int dh = dH; dh <= D4B_MAX_DEG; ++dh) {
+      const int nH = dH + 1, nh = dh + 1;
+      double xH[kMaxN], wH[kMaxN], xh[kMaxN], wh[kMaxN], y[kMaxN], E[kMaxN * kMaxN];
+      d4b_tab_lobatto(nH, xH, wH);
+      d4b_tab_lobatto(nh, xh, wh);
+      for (int half = 0; half < 3; ++half) {
+        for (int i = 0; i < nh; ++i) y[i] = half == 0 ? xh[i] : (half == 1 ? 0.5 * (xh[i] - 1.) : 0.5 * (xh[i] + 1.));
+        d4b_tab_eval(nH, xH, nh, y, E);
+        if (half == 0 && dH == dh)   // the reference copies instead of multiplying (:1115-1118)
+          for (int i = 0; i < nh; ++i)
+            for (int j = 0; j < nH; ++j) E[i * nH + j] = (i == j) ? 1. : 0.;
+        off[((dH - 1) * 7 + (dh - 1)) * 3 + half] = (int32_t)P.size();
+        P.insert(P.end(), E, E + nh * nH);
+      }
+    }
+  g->d_P = d4b_dev_upload<double>(g->mesh[top], P.data(), P.size());
+  g->d_P_off = d4b_dev_upload<int32_t>(g->mesh[top], off.data(), off.size());
+  // a coarse element is never of higher degree than its children
+  return g;
+}
+
+extern "C" void d4b_mg_destroy(d4b_mg_t *g) {
+  if (!g) return;
+  for (d4b_mesh *m : g->mesh) cudaStreamSynchronize(m->stream);
+  for (auto p : g->d_child_first) cudaFree(p);
+  for (auto p : g->d_child_count) cudaFree(p);
+  for (auto p : g->d_u) if (p) cudaFree(p);
+  for (auto p : g->d_rhs) if (p) cudaFree(p);
+  for (auto p : g->d_r) if (p) cudaFree(p);
+  if (g->d_top_u) cudaFree(g->d_top_u);
+  if (g->d_top_rhs) cudaFree(g->d_top_rhs);
+  cudaFree(g->d_P); cudaFree(g->d_P_off);
+  delete g;
+}
+
+extern "C" double d4b_mg_vcycle(d4b_mg_t *g, double *u, const double *rhs) {
+  TopVectors t = stage_in(g, u, rhs);
+  double r2 = vcycle_device(g, t.u, t.rhs);
+  g->vcycle_num_finished++;
+  stage_out(g, t, u);
+  return r2;
+}
+
+extern "C" int32_t d4b_mg_solve(d4b_mg_t *g, double *u, const double *rhs, double *r2_history) {
+  TopVectors t = stage_in(g, u, rhs);
+  d4b_mesh *mt = g->mesh[g->n_levels - 1];
+  const int64_t n = mt->local_nodes;
+  // initial residual, d4est_solver_multigrid_compute_residual (:1351-1418)
+  double *Au = mt->d_Au_stage;
+  d4b_apply(mt, t.u, Au);
+  resid_k<<<grid_for(n), 256, 0, mt->stream>>>(t.rhs, Au, g->d_r[g->n_levels - 1], n);
+  double r2 = d4b_vec_dot(mt, g->d_r[g->n_levels - 1], g->d_r[g->n_levels - 1], n);
+  double r2_last = r2;
+  const double stoptol = g->prm.vcycle_rtol * g->prm.vcycle_rtol * r2 + g->prm.vcycle_atol * g->prm.vcycle_atol;
+  if (r2_history) r2_history[0] = r2;
+  g->vcycle_num_finished = 0;
+  while (g->vcycle_num_finished < g->prm.vcycle_imax && r2 > stoptol) {
+    // the smoother's final residual IS rhs - A u of the new iterate: no extra apply
+    r2 = vcycle_device(g, t.u, t.rhs);
+    g->vcycle_num_finished++;
+    if (r2_history) r2_history[g->vcycle_num_finished] = r2;
+    if (sqrt(r2 / r2_last) >= .99) break;
+    r2_last = r2;
+  }
+  stage_out(g, t, u);
+  return g->vcycle_num_finished;
+}
+
+extern "C" void d4b_mg_get_eigs(const d4b_mg_t *g, double *eigs_out) {
+  for (int l = 0; l < g->n_levels; ++l) eigs_out[l] = g->eigs[l];
+}
+
+namespace {
+void transfer_any(d4b_mg *g, int dir, int lc, const double *in, double *out) {
+  D4B_CHECK(lc >= 0 && lc < g->n_levels - 1, "transfer: coarse level %d out of range", lc);
+  d4b_mesh *m_in = dir == 0 ? g->mesh[lc] : g->mesh[lc + 1];
+  d4b_mesh *m_out = dir == 0 ? g->mesh[lc + 1] : g->mesh[lc];
+  cudaStream_t s = g->mesh[lc + 1]->stream;
+  const double *din = in;
+  double *dout = out, *tmp_in = nullptr, *tmp_out = nullptr;
+  if (!is_dev(in)) {
+    D4B_CUDA(cudaMalloc(&tmp_in, (size_t)m_in->local_nodes * sizeof(double)));
+    D4B_CUDA(cudaMemcpyAsync(tmp_in, in, (size_t)m_in->local_nodes * sizeof(double), cudaMemcpyHostToDevice, s));
+    din = tmp_in;
+  }
+  if (!is_dev(out)) {
+    D4B_CUDA(cudaMalloc(&tmp_out, (size_t)m_out->local_nodes * sizeof(double)));
+    dout = tmp_out;
+  }
+  transfer(g, dir, 0, lc, din, dout);
+  if (tmp_out)
+    D4B_CUDA(cudaMemcpyAsync(out, tmp_out, (size_t)m_out->local_nodes * sizeof(double), cudaMemcpyDeviceToHost, s));
+  D4B_CUDA(cudaStreamSynchronize(s));
+  if (tmp_in) cudaFree(tmp_in);
+  if (tmp_out) cudaFree(tmp_out);
+}
+}  // namespace
+
+extern "C" void d4b_mg_restrict(d4b_mg_t *g, int32_t lc, const double *fine, double *coarse) {
+  transfer_any(g, 1, lc, fine, coarse);
+}
+extern "C" void d4b_mg_prolong(d4b_mg_t *g, int32_t lc, const double *coarse, double *fine) {
+  transfer_any(g, 0, lc, coarse, fine);
+}

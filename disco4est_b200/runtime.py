@@ -14,12 +14,13 @@ import os
 
 import numpy as np
 
-from .abi import ChebyParams, MeshDesc, make_desc
+from .abi import ChebyParams, MeshDesc, MgDesc, make_desc
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 # D4B_LIBRARY_PATH lets profiling scripts A/B differently compiled builds of the same library
 LIB_PATH = os.environ.get("D4B_LIBRARY_PATH") or os.path.join(_HERE, "libd4est_b200.so")
 _F64P = C.POINTER(C.c_double)
+_I32P_T = C.POINTER(C.c_int32)
 
 EXPORTS = [
     "d4b_set_abort_hook", "d4b_abi_version", "d4b_device_count", "d4b_init",
@@ -27,6 +28,8 @@ EXPORTS = [
     "d4b_apply", "d4b_apply_stiffness", "d4b_sync", "d4b_set_stream",
     "d4b_vec_dot", "d4b_vec_axpy", "d4b_vec_xpby", "d4b_vec_scale",
     "d4b_cg_eigs", "d4b_cheby_smooth",
+    "d4b_mg_create", "d4b_mg_destroy", "d4b_mg_vcycle", "d4b_mg_solve", "d4b_mg_get_eigs", "d4b_mg_restrict",
+    "d4b_mg_prolong",
     "d4b_comm_get_unique_id", "d4b_comm_init", "d4b_comm_destroy", "d4b_comm_size", "d4b_comm_rank",
 ]
 
@@ -73,12 +76,87 @@ def load_library():
     L.d4b_cg_eigs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32]
     L.d4b_cheby_smooth.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32,
                                    C.c_double, C.c_double]
+    L.d4b_mg_create.restype = C.c_void_p
+    L.d4b_mg_create.argtypes = [C.POINTER(MgDesc)]
+    L.d4b_mg_destroy.argtypes = [C.c_void_p]
+    L.d4b_mg_vcycle.restype = C.c_double
+    L.d4b_mg_vcycle.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    L.d4b_mg_solve.restype = C.c_int32
+    L.d4b_mg_solve.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.d4b_mg_get_eigs.argtypes = [C.c_void_p, C.c_void_p]
+    L.d4b_mg_restrict.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]
+    L.d4b_mg_prolong.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]
     L.d4b_comm_get_unique_id.argtypes = [C.c_void_p]
     L.d4b_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int]
     L.d4b_comm_size.restype = C.c_int
     L.d4b_comm_rank.restype = C.c_int
     _lib = L
     return L
+
+
+def cheby_params(imax, eigs_cg_imax, ratio=30.0, multiplier=1.0, use_new=0, zero_guess=0, reuse_down=0, reuse_last=0):
+    return ChebyParams(imax, eigs_cg_imax, ratio, multiplier, use_new, zero_guess, reuse_down, reuse_last)
+
+
+class Multigrid:
+    """Device-resident V-cycle (d4b_mg_t) over `meshes` (coarsest first) and, per
+    coarse level, (child_first, child_count) int32 arrays."""
+
+    def __init__(self, meshes, transfers, smoother, vcycle_imax=1, vcycle_rtol=1e-9, vcycle_atol=0.0,
+                 bottom_solver="cg", bottom_iter=100, bottom_rtol=1e-10, bottom_atol=0.0, bottom_cheby=None):
+        L = load_library()
+        self.L, self.meshes = L, meshes
+        n = len(meshes)
+        d = MgDesc()
+        d.n_levels = n
+        self._mesh_arr = (C.c_void_p * n)(*[m.h for m in meshes])
+        d.meshes = C.cast(self._mesh_arr, C.POINTER(C.c_void_p))
+        self._keep = []
+        firsts, counts = (_I32P_T * (n - 1))(), (_I32P_T * (n - 1))()
+        for l, (cf, cc) in enumerate(transfers):
+            cf = np.ascontiguousarray(cf, dtype=np.int32); cc = np.ascontiguousarray(cc, dtype=np.int32)
+            self._keep += [cf, cc]
+            firsts[l] = cf.ctypes.data_as(_I32P_T); counts[l] = cc.ctypes.data_as(_I32P_T)
+        self._firsts, self._counts = firsts, counts
+        d.child_first = C.cast(firsts, C.POINTER(_I32P_T)); d.child_count = C.cast(counts, C.POINTER(_I32P_T))
+        d.vcycle_imax, d.vcycle_rtol, d.vcycle_atol = vcycle_imax, vcycle_rtol, vcycle_atol
+        d.smoother = smoother
+        d.bottom_solver = 0 if bottom_solver == "cg" else 1
+        d.bottom_iter, d.bottom_rtol, d.bottom_atol = bottom_iter, bottom_rtol, bottom_atol
+        d.bottom_cheby = bottom_cheby if bottom_cheby is not None else smoother
+        self.desc = d
+        self.vcycle_imax = vcycle_imax
+        self.h = L.d4b_mg_create(C.byref(d))
+
+    def vcycle(self, u, rhs):
+        return float(self.L.d4b_mg_vcycle(self.h, _ptr(u), _ptr(rhs)))
+
+    def solve(self, u, rhs):
+        hist = np.zeros(self.vcycle_imax + 1)
+        n = int(self.L.d4b_mg_solve(self.h, _ptr(u), _ptr(rhs), hist.ctypes.data))
+        return n, hist[: n + 1]
+
+    def eigs(self):
+        e = np.zeros(len(self.meshes))
+        self.L.d4b_mg_get_eigs(self.h, e.ctypes.data)
+        return e
+
+    def restrict(self, coarse_level, fine, coarse):
+        self.L.d4b_mg_restrict(self.h, coarse_level, _ptr(fine), _ptr(coarse))
+
+    def prolong(self, coarse_level, coarse, fine):
+        self.L.d4b_mg_prolong(self.h, coarse_level, _ptr(coarse), _ptr(fine))
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.d4b_mg_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 COMM_ID_BYTES = 128

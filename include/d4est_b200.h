@@ -212,6 +212,8 @@ typedef struct d4b_cheby_params
   double  cheby_eigs_max_multiplier;
   int32_t cheby_use_new_cg_eigs;
   int32_t cheby_use_zero_guess_for_eigs;
+  int32_t cheby_eigs_reuse_fromdownvcycle;
+  int32_t cheby_eigs_reuse_fromlastvcycle;
 } d4b_cheby_params_t;
 
 /* cg_eigs (src/Solver/d4est_solver_cg_eigs.c:115-276): runs imax CG steps on
@@ -229,6 +231,58 @@ double d4b_cg_eigs(d4b_mesh_t *mesh, double *u, const double *rhs,
  * on the device: each iteration streams u, p, rhs once.                    */
 void d4b_cheby_smooth(d4b_mesh_t *mesh, double *u, const double *rhs, double *r,
                       int32_t iter, double lmin, double lmax);
+
+/* ------------------------------------------------------------- multigrid  */
+/* Device-resident V-cycle, replaces d4est_solver_multigrid_vcycle / _solve
+ * (src/Solver/d4est_solver_multigrid.c:751-1349, :1420-1506) for a hierarchy
+ * the caller describes level by level.  Level numbering follows the
+ * reference: level 0 is the coarsest, n_levels-1 the finest ("toplevel").
+ * The reference creates level l-1 from level l with p4est_coarsen_ext +
+ * p4est_balance_ext and records, per coarse element, which fine elements it
+ * came from (d4est_solver_multigrid_refine_data_t, d4est_solver_multigrid.h:12-18,
+ * callbacks.h:23-108); a family is contiguous in the fine element order, so
+ * that record is (first child, child count):
+ *   count 8: h-coarsened family in z-order, coarse degree = min of the children
+ *            -> restriction = apply_hp_prolong_transpose, prolongation = apply_hp_prolong
+ *   count 1: same element (possibly lower degree: p-coarsening, or an element
+ *            re-split by the balance step)
+ *            -> apply_p_prolong_transpose / apply_p_prolong (d4est_operators.c:1091-1132, :1689-1749) */
+typedef struct d4b_mg_desc
+{
+  int32_t n_levels;
+  d4b_mesh_t *const *meshes;             /* [n_levels], coarsest first; not owned  */
+  const int32_t *const *child_first;     /* [n_levels-1][n_local of level l]: first element of level l+1 */
+  const int32_t *const *child_count;     /* [n_levels-1][n_local of level l]: 1 or 8 */
+  /* [multigrid] section, d4est_solver_multigrid.c:392-405 */
+  int32_t vcycle_imax;
+  double  vcycle_rtol, vcycle_atol;
+  /* [mg_smoother_cheby] */
+  d4b_cheby_params_t smoother;
+  /* bottom solver: 0 = mg_bottom_solver_cg (…bottom_solver_cg.c:48-200),
+   *                1 = mg_bottom_solver_cheby (…bottom_solver_cheby.c:60-115)  */
+  int32_t bottom_solver;
+  int32_t bottom_iter;
+  double  bottom_rtol, bottom_atol;
+  d4b_cheby_params_t bottom_cheby;
+} d4b_mg_desc_t;
+
+typedef struct d4b_mg d4b_mg_t;
+d4b_mg_t *d4b_mg_create(const d4b_mg_desc_t *desc);
+void      d4b_mg_destroy(d4b_mg_t *mg);
+/* one V-cycle on A u = rhs of the finest level (u updated in place; host or
+ * device pointers); returns the global |rhs - A u|^2 after it                */
+double    d4b_mg_vcycle(d4b_mg_t *mg, double *u, const double *rhs);
+/* d4est_solver_multigrid_solve: V-cycles until vcycle_imax, the residual
+ * tolerance, or stagnation (sqrt(r2/r2_last) >= 0.99).  Returns the number of
+ * V-cycles; r2_history (may be NULL) receives the initial and every
+ * subsequent global squared residual, [vcycle_imax + 1].                     */
+int32_t   d4b_mg_solve(d4b_mg_t *mg, double *u, const double *rhs, double *r2_history);
+/* largest-eigenvalue estimates the smoother used last, [n_levels]           */
+void      d4b_mg_get_eigs(const d4b_mg_t *mg, double *eigs_out);
+/* inter-grid transfer alone (tests): coarse level l <- / -> fine level l+1;
+ * device or host pointers                                                    */
+void      d4b_mg_restrict(d4b_mg_t *mg, int32_t coarse_level, const double *fine, double *coarse);
+void      d4b_mg_prolong(d4b_mg_t *mg, int32_t coarse_level, const double *coarse, double *fine);
 
 #ifdef __cplusplus
 }

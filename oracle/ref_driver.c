@@ -8,7 +8,7 @@
  * forest from an INI file, optional random hp-AMR steps, u = x^2+y^2+z^2 +
  * U(0,1) with srand(102321), apply the plain and the with_opt operator.
  *
- *   ref_driver <ini> <out.d4b|-> [--amr N] [--time REPS] [--cheby IMAX EIGS_IMAX]
+ *   ref_driver <ini> <out.d4b|-> [--amr N] [--time REPS] [--cheby IMAX EIGS_IMAX] [--mg VCYCLES]
  *              [--bc zero|poly] [--uniform-deg P]
  */
 #include <pXest.h>
@@ -24,6 +24,7 @@
 #include <d4est_laplacian.h>
 #include <d4est_solver_cg_eigs.h>
 #include <d4est_solver_multigrid_smoother_cheby.h>
+#include <d4est_solver_multigrid.h>
 #include <d4est_util.h>
 #include <zlog.h>
 #include <time.h>
@@ -169,18 +170,19 @@ main (int argc, char *argv[])
 {
   if (argc < 3) {
     fprintf (stderr, "usage: %s <ini> <out.d4b|-> [--amr N] [--time REPS] [--bc zero|poly]"
-             " [--uniform-deg P] [--cheby IMAX EIGS_IMAX]\n", argv[0]);
+             " [--uniform-deg P] [--cheby IMAX EIGS_IMAX] [--mg VCYCLES]\n", argv[0]);
     return 2;
   }
   const char *ini = argv[1];
   const char *out = argv[2];
-  int amr_steps = 0, time_reps = 0, bc_poly = 0, cheby_imax = 0, cheby_eigs_imax = 0;
+  int amr_steps = 0, time_reps = 0, bc_poly = 0, cheby_imax = 0, cheby_eigs_imax = 0, mg_vcycles = 0;
   for (int a = 3; a < argc; a++) {
     if (!strcmp (argv[a], "--amr")) amr_steps = atoi (argv[++a]);
     else if (!strcmp (argv[a], "--time")) time_reps = atoi (argv[++a]);
     else if (!strcmp (argv[a], "--bc")) bc_poly = !strcmp (argv[++a], "poly");
     else if (!strcmp (argv[a], "--uniform-deg")) g_uniform_deg = atoi (argv[++a]);
     else if (!strcmp (argv[a], "--cheby")) { cheby_imax = atoi (argv[++a]); cheby_eigs_imax = atoi (argv[++a]); }
+    else if (!strcmp (argv[a], "--mg")) { mg_vcycles = atoi (argv[++a]); }
     else { fprintf (stderr, "unknown option %s\n", argv[a]); return 2; }
   }
 
@@ -397,6 +399,48 @@ main (int argc, char *argv[])
         d4b_dump_put1 (f, "cheby_r", D4B_F64, local_nodes, cr);
         P4EST_FREE (cu); P4EST_FREE (cAu); P4EST_FREE (cr);
       }
+    }
+
+    /* the reference's multigrid solve (src/Solver/d4est_solver_multigrid.c:1420-1506), one
+     * V-cycle per call so that the residual and the iterate after every V-cycle can be
+     * recorded.  rhs = A u_seeded, initial guess 0, parameters from the [multigrid],
+     * [mg_smoother_cheby], [mg_bottom_solver_cg] sections of the ini file. */
+    if (mg_vcycles > 0 && !bc_poly) {
+      d4est_solver_multigrid_t *mg_data =
+        d4est_solver_multigrid_data_init (p4est, d4est_ops, d4est_geom, d4est_quad, &d4est_ghost,
+                                          &d4est_ghost_data, d4est_factors, initial_grid_input, ini);
+      double *mu = P4EST_ALLOC_ZERO (double, local_nodes);
+      double *mAu = P4EST_ALLOC_ZERO (double, local_nodes);
+      double *r2 = P4EST_ALLOC_ZERO (double, mg_vcycles + 1);
+      double *u_hist = P4EST_ALLOC_ZERO (double, (size_t) mg_vcycles * local_nodes);
+      d4est_elliptic_data_t mv = vecs;
+      mv.u = mu; mv.Au = mAu; mv.rhs = Au_plain;
+      double t_mg = 0.;
+      for (int k = 0; k < mg_vcycles; k++) {
+        double t1 = wall ();
+        d4est_solver_multigrid_solve (p4est, &mv, &fcns_plain, mg_data);
+        t_mg += wall () - t1;
+        if (k == 0) r2[0] = mg_data->vcycle_r2_global_last;   /* initial residual (only while no break) */
+        r2[k + 1] = mg_data->vcycle_r2_global_current;
+        memcpy (u_hist + (size_t) k * local_nodes, mu, sizeof (double) * local_nodes);
+      }
+      /* initial residual with u = 0 is |rhs|^2 */
+      r2[0] = d4est_linalg_vec_dot (Au_plain, Au_plain, local_nodes);
+      d4est_solver_multigrid_smoother_cheby_t *cheby = mg_data->smoother->user;
+      double levels = (double) mg_data->num_of_levels;
+      d4b_dump_put1 (f, "mg_rhs", D4B_F64, local_nodes, Au_plain);
+      d4b_dump_put1 (f, "mg_num_levels", D4B_F64, 1, &levels);
+      d4b_dump_put1 (f, "mg_r2", D4B_F64, mg_vcycles + 1, r2);
+      d4b_dump_put1 (f, "mg_u_hist", D4B_F64, (uint64_t) mg_vcycles * local_nodes, u_hist);
+      d4b_dump_put1 (f, "mg_eigs_last", D4B_F64, mg_data->num_of_levels, cheby->eigs);
+      double prm[5] = { (double) cheby->cheby_imax, (double) cheby->cheby_eigs_cg_imax,
+                        cheby->cheby_eigs_lmax_lmin_ratio, cheby->cheby_eigs_max_multiplier,
+                        (double) cheby->cheby_use_new_cg_eigs };
+      d4b_dump_put1 (f, "mg_cheby_params", D4B_F64, 5, prm);
+      printf ("{\"mg_levels\": %d, \"mg_vcycles\": %d, \"t_mg_s\": %.6f, \"r2_first\": %.6e, \"r2_last\": %.6e}\n",
+              mg_data->num_of_levels, mg_vcycles, t_mg, r2[0], r2[mg_vcycles]);
+      P4EST_FREE (mu); P4EST_FREE (mAu); P4EST_FREE (r2); P4EST_FREE (u_hist);
+      d4est_solver_multigrid_data_destroy (mg_data);
     }
     fclose (f);
     d4est_b200_flat_destroy (flat);

@@ -76,3 +76,105 @@ def cheby(apply, u, rhs, iters, lmin, lmax):
         p = alpha * r + beta * p
         u += p
     return u, rhs - apply(u)
+
+
+# ---- multigrid -------------------------------------------------------------------
+def lgl_nodes(N):
+    from disco4est_b200.brick import lgl_nodes as f
+    return f(N)
+
+
+def prolong_1d(degH, degh, half):
+    """[nh x nH] Lagrange basis on LGL(degH) at the LGL(degh) nodes of the whole
+    interval (half 0: build_p_prolong_1d, d4est_operators.c:995-1012) or of its lower /
+    upper half (half 1, 2: build_hp_prolong_1d :944-993)."""
+    xH, xh = lgl_nodes(degH + 1), lgl_nodes(degh + 1)
+    y = xh if half == 0 else (0.5 * (xh - 1.0) if half == 1 else 0.5 * (xh + 1.0))
+    if half == 0 and degH == degh:
+        return np.eye(degh + 1)
+    P = np.ones((degh + 1, degH + 1))
+    for j in range(degH + 1):
+        for k in range(degH + 1):
+            if k != j:
+                P[:, j] *= (y - xH[k]) / (xH[j] - xH[k])
+    return P
+
+
+def prolong_3d(degH, degh, child, count):
+    h = (0, 0, 0) if count == 1 else (1 + (child & 1), 1 + ((child >> 1) & 1), 1 + ((child >> 2) & 1))
+    return np.kron(prolong_1d(degH, degh, h[2]), np.kron(prolong_1d(degH, degh, h[1]), prolong_1d(degH, degh, h[0])))
+
+
+class Transfer:
+    """coarse level <-> fine level, (child_first, child_count) per coarse element
+    (d4est_solver_multigrid_callbacks.h:110-203 restriction, :237-329 prolongation)."""
+
+    def __init__(self, coarse, fine, child_first, child_count):
+        self.c, self.f, self.first, self.count = coarse, fine, child_first, child_count
+
+    def _blocks(self):
+        for e in range(int(self.c["n_local"])):
+            dH = int(self.c["deg"][e]); sH = int(self.c["nodal_stride"][e])
+            for ch in range(int(self.count[e])):
+                ef = int(self.first[e]) + ch
+                dh = int(self.f["deg"][ef]); sh = int(self.f["nodal_stride"][ef])
+                yield sH, (dH + 1) ** 3, sh, (dh + 1) ** 3, prolong_3d(dH, dh, ch, int(self.count[e]))
+
+    def restrict(self, fine):
+        out = np.zeros(int(self.c["local_nodes"]))
+        for sH, nH, sh, nh, P in self._blocks():
+            out[sH:sH + nH] += P.T @ fine[sh:sh + nh]
+        return out
+
+    def prolong(self, coarse):
+        out = np.zeros(int(self.f["local_nodes"]))
+        for sH, nH, sh, nh, P in self._blocks():
+            out[sh:sh + nh] = P @ coarse[sH:sH + nH]
+        return out
+
+
+def bottom_cg(apply, rhs, imax, rtol, atol):
+    """d4est_solver_multigrid_bottom_solver_cg.c:48-200, zero initial guess"""
+    u = np.zeros_like(rhs)
+    r = rhs - apply(u)
+    d = r.copy()
+    delta_new = float(r @ r)
+    delta_0 = delta_new
+    i = 0
+    while i < imax and delta_new > atol * atol + delta_0 * rtol * rtol:
+        Ad = apply(d)
+        alpha = delta_new / float(d @ Ad)
+        u += alpha * d
+        r -= alpha * Ad
+        delta_old = delta_new
+        delta_new = float(r @ r)
+        d = r + (delta_new / delta_old) * d
+        i += 1
+    return u, i
+
+
+def vcycle(applies, transfers, u, rhs, cheby_imax, eigs_imax, ratio, mult=1.0, use_new=0,
+           bottom=(100, 1e-10, 0.0)):
+    """One V-cycle, d4est_solver_multigrid.c:751-1349 (eigenvalues recomputed on both legs).
+    applies[l], transfers[l] (between l and l+1), coarsest first.  Returns (u, r2, eigs)."""
+    top = len(applies) - 1
+    us, rhss, eigs = [None] * (top + 1), [None] * (top + 1), [0.0] * (top + 1)
+    us[top], rhss[top] = u.copy(), rhs
+    r = None
+
+    def smooth(l):
+        e, us[l] = cg_eigs(applies[l], us[l], rhss[l], eigs_imax, use_new)
+        eigs[l] = e * mult
+        us[l], rr = cheby(applies[l], us[l], rhss[l], cheby_imax, eigs[l] / ratio, eigs[l])
+        return rr
+
+    for l in range(top, 0, -1):
+        if l != top:
+            us[l] = np.zeros_like(rhss[l])
+        r = smooth(l)
+        rhss[l - 1] = transfers[l - 1].restrict(r)
+    us[0], _ = bottom_cg(applies[0], rhss[0], *bottom)
+    for l in range(0, top):
+        us[l + 1] = us[l + 1] + transfers[l].prolong(us[l])
+        r = smooth(l + 1)
+    return us[top], float(r @ r), eigs
