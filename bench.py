@@ -15,6 +15,7 @@ reference's CPU apply (oracle/_ref/ref_driver) on the host cores instead.
 """
 import argparse
 import json
+import math
 import os
 import subprocess
 import sys
@@ -179,6 +180,52 @@ def bench_reference(args):
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 
 
+def bench_vcycle(top_mesh, level, deg, rank, world, trees, torch, dev, cycles=3):
+    """V-cycle seconds per iteration: h-multigrid down to one element per tree, Chebyshev(15)
+    smoother with lambda_max from 15 CG steps recomputed on both legs, Chebyshev bottom
+    solver (the [multigrid] settings of src/Problems/ConstantDensityStar/options.input),
+    rhs = random, zero initial guess.  Whole-job seconds, max over ranks."""
+    import torch.distributed as dist
+    from disco4est_b200 import Mesh
+    from disco4est_b200.brick import brick_hierarchy
+    from disco4est_b200.runtime import Multigrid, cheby_params
+
+    descs, transfers = brick_hierarchy(level, deg, rank=rank, world=world, trees=trees)
+    meshes = [Mesh(d, device=dev.index) for d in descs[:-1]] + [top_mesh]
+    nodes = [int(d["local_nodes"]) for d in descs]
+    del descs
+    sm = cheby_params(15, 15, 30.0, 1.0)
+    mg = Multigrid(meshes, transfers, sm, vcycle_imax=1, bottom_solver="cheby", bottom_cheby=cheby_params(15, 30, 30.0, 1.0))
+    n = top_mesh.n
+    g = torch.Generator(device=dev).manual_seed(4242 + rank)
+    rhs = torch.rand(n, dtype=torch.float64, device=dev, generator=g)
+    u = torch.zeros_like(rhs)
+    r2 = [float(rhs.dot(rhs))]
+    mg.vcycle(u, rhs)                      # warm-up (also allocates level work space)
+    u.zero_()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(cycles):
+        r2.append(mg.vcycle(u, rhs))       # every V-cycle ends with a host-visible residual norm
+    torch.cuda.synchronize()
+    t = (time.perf_counter() - t0) / cycles
+    tt = torch.tensor([t], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    # fine-level applies per V-cycle: 2 legs x [(1 + 15) cg_eigs + (15 + 1) Chebyshev]
+    out = {"seconds_per_vcycle": float(tt[0]), "levels": len(meshes), "nodes_per_level_rank0": nodes,
+           "fine_applies_per_vcycle": 64, "smoother": "cheby_imax=15 cheby_eigs_cg_imax=15 ratio=30, eigs recomputed on both legs",
+           "bottom_solver": "mg_bottom_solver_cheby imax=15 eigs_cg_imax=30",
+           "residual_reduction_per_vcycle": [math.sqrt(r2[i + 1] / r2[i]) for i in range(cycles)],
+           "timing": "wall clock around %d V-cycles after one warm-up, synchronised, max over ranks" % cycles}
+    mg.close()
+    for m in meshes[:-1]:
+        m.close()
+    return out
+
+
 def bench_ours(args):
     import numpy as np
     import torch
@@ -285,6 +332,13 @@ def bench_ours(args):
         }
         if world == 1 and not args.no_cpu:
             out["cpu_baseline"] = cpu_baseline(deg)
+    # second metric of BASELINE.json: seconds per multigrid V-cycle
+    vc = None
+    if not args.no_vcycle:
+        vc = bench_vcycle(mesh, level, deg, rank, world, trees, torch, dev)
+    if rank == 0:
+        if vc is not None:
+            out["vcycle"] = vc
         print(json.dumps(out))
     mesh.close()
     if world > 1:
@@ -301,6 +355,7 @@ def main():
     ap.add_argument("--deg", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-vcycle", action="store_true", help="skip the V-cycle metric")
     args = ap.parse_args()
     if args.impl == "reference":
         bench_reference(args)
