@@ -141,8 +141,56 @@ static void gershgorin(int use_new, int i, int64_t n, double a0, double b0, doub
   *mx = diag + off;
 }
 
+// cg_eigs keeps its scalars on the device: kernel i reads alpha_i = delta_i / (d.Ad)_i and
+// beta_i = delta_{i+1} / delta_i from the slots earlier reductions filled, so the whole
+// estimate is enqueued without a host round trip; the Gershgorin bounds are evaluated on the
+// host from the 2 imax + 1 scalars at the end.
+constexpr int kScalOff = 1024, kMaxCgIter = 500;   // d_red: [0,1024) partial sums, then delta[], dAd[]
+
+void dot_to(d4b_mesh *m, const double *x, const double *y, int64_t n, double *d_out) {
+  dot_partial<<<kRedBlocks, kRedThreads, 0, m->stream>>>(x, y, n, m->d_red);
+  dot_final<<<1, 1024, 0, m->stream>>>(m->d_red, kRedBlocks, d_out);
+  d4b_comm_allreduce_sum(m, d_out, 1);
+}
+
+// u += alpha d ; r -= alpha Ad with alpha = *delta / *dAd ; block partials of r.r
+__global__ void __launch_bounds__(kRedThreads) cg_update_dot_k(const double *__restrict__ delta,
+                                                               const double *__restrict__ dAd,
+                                                               const double *__restrict__ d,
+                                                               const double *__restrict__ Ad, double *__restrict__ u,
+                                                               double *__restrict__ r, int64_t n,
+                                                               double *__restrict__ part) {
+  __shared__ double sh[kRedThreads];
+  const double alpha = *delta / *dAd;
+  int64_t chunk = (n + gridDim.x - 1) / gridDim.x;
+  int64_t lo = (int64_t)blockIdx.x * chunk, hi = lo + chunk < n ? lo + chunk : n;
+  double s = 0.;
+  for (int64_t i = lo + threadIdx.x; i < hi; i += kRedThreads) {
+    u[i] += alpha * d[i];
+    const double ri = r[i] - alpha * Ad[i];
+    r[i] = ri;
+    s += ri * ri;
+  }
+  sh[threadIdx.x] = s;
+  __syncthreads();
+  for (int w = kRedThreads / 2; w > 0; w >>= 1) {
+    if (threadIdx.x < w) sh[threadIdx.x] += sh[threadIdx.x + w];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) part[blockIdx.x] = sh[0];
+}
+
+// d = r + beta d with beta = *delta_new / *delta_old
+__global__ void xpby_dev_k(const double *__restrict__ r, const double *__restrict__ delta_new,
+                           const double *__restrict__ delta_old, double *__restrict__ d, int64_t n) {
+  const double beta = *delta_new / *delta_old;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    d[i] = r[i] + beta * d[i];
+}
+
 extern "C" double d4b_cg_eigs(d4b_mesh_t *m, double *u, const double *rhs, int32_t imax,
                               int32_t use_new, int32_t use_zero_guess) {
+  D4B_CHECK(imax >= 1 && imax <= kMaxCgIter, "d4b_cg_eigs: imax %d out of range", imax);
   const int64_t n = m->local_nodes;
   const size_t bytes = (size_t)n * sizeof(double);
   bool u_dev = is_dev(u), rhs_dev = is_dev(rhs);
@@ -160,29 +208,34 @@ extern "C" double d4b_cg_eigs(d4b_mesh_t *m, double *u, const double *rhs, int32
     D4B_CUDA(cudaMemsetAsync(du, 0, bytes, m->stream));
   }
   double *Au = m->d_Au_stage, *d = work(m, 0), *r = work(m, 1);
+  double *delta = m->d_red + kScalOff, *dAd = delta + kMaxCgIter + 1;
   const int g = grid_for(n);
   d4b_apply(m, du, Au);
   residual2_k<<<g, 256, 0, m->stream>>>(drhs, Au, r, d, n);
-  double delta_new = d4b_vec_dot(m, r, r, n);
-  double alpha = -1., beta = -1., bound = 0.;
+  dot_to(m, r, r, n, delta);
   for (int i = 0; i < imax; ++i) {
     d4b_apply(m, d, Au);
-    double d_dot_Au = d4b_vec_dot(m, d, Au, n);
-    double alpha_old = alpha;
-    alpha = delta_new / d_dot_Au;
-    cg_update_k<<<g, 256, 0, m->stream>>>(alpha, d, Au, du, r, n);
-    double delta_old = delta_new;
-    delta_new = d4b_vec_dot(m, r, r, n);
-    double beta_old = beta;
-    beta = delta_new / delta_old;
-    xpby_k<<<g, 256, 0, m->stream>>>(r, beta, d, n);
+    dot_to(m, d, Au, n, dAd + i);
+    cg_update_dot_k<<<kRedBlocks, kRedThreads, 0, m->stream>>>(delta + i, dAd + i, d, Au, du, r, n, m->d_red);
+    dot_final<<<1, 1024, 0, m->stream>>>(m->d_red, kRedBlocks, delta + i + 1);
+    d4b_comm_allreduce_sum(m, delta + i + 1, 1);
+    xpby_dev_k<<<g, 256, 0, m->stream>>>(r, delta + i + 1, delta + i, d, n);
+  }
+  D4B_CUDA(cudaMemcpyAsync(m->h_red, delta, (size_t)(2 * kMaxCgIter + 2) * sizeof(double), cudaMemcpyDeviceToHost,
+                           m->stream));
+  if (!u_dev && !use_zero_guess)
+    D4B_CUDA(cudaMemcpyAsync(u, du, bytes, cudaMemcpyDeviceToHost, m->stream));
+  D4B_CUDA(cudaStreamSynchronize(m->stream));
+  const double *h_delta = m->h_red, *h_dAd = m->h_red + kMaxCgIter + 1;
+  double alpha = -1., beta = -1., bound = 0.;
+  for (int i = 0; i < imax; ++i) {
+    const double alpha_old = alpha, beta_old = beta;
+    alpha = h_delta[i] / h_dAd[i];
+    beta = h_delta[i + 1] / h_delta[i];
     double tmax;
     gershgorin(use_new, i, n, alpha_old, beta_old, alpha, beta, &tmax);
     bound = (i > 0) ? fmax(bound, tmax) : tmax;
   }
-  if (!u_dev && !use_zero_guess)
-    D4B_CUDA(cudaMemcpyAsync(u, du, bytes, cudaMemcpyDeviceToHost, m->stream));
-  D4B_CUDA(cudaStreamSynchronize(m->stream));
   return bound;
 }
 
