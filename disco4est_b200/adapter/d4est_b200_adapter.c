@@ -347,12 +347,49 @@ d4est_b200_ctx_destroy (d4est_b200_ctx_t * ctx)
 {
   if (ctx == NULL) return;
 #ifndef D4EST_B200_ADAPTER_NO_DEVICE
-  if (ctx->mesh) d4b_mesh_destroy (ctx->mesh);
+  for (int i = 0; i < D4EST_B200_CACHE; i++)
+    if (ctx->cache[i].mesh) d4b_mesh_destroy (ctx->cache[i].mesh);
 #endif
   free (ctx);
 }
 
 #ifndef D4EST_B200_ADAPTER_NO_DEVICE
+d4b_mesh_t *
+d4est_b200_get_mesh (d4est_b200_ctx_t * ctx, p4est_t * p4est, d4est_ghost_t * ghost,
+                     d4est_mesh_data_t * d4est_factors)
+{
+  const int ne = p4est->local_num_quadrants, nn = d4est_factors->local_sizes.local_nodes;
+  int victim = 0;
+  ctx->clock++;
+  for (int i = 0; i < D4EST_B200_CACHE; i++) {
+    d4est_b200_cached_mesh_t *c = &ctx->cache[i];
+    if (c->mesh && c->factors == d4est_factors && c->local_elements == ne && c->local_nodes == nn) {
+      c->stamp = ctx->clock;
+      return c->mesh;
+    }
+  }
+  /* first free slot, else the least recently used one */
+  victim = -1;
+  for (int i = 0; i < D4EST_B200_CACHE && victim < 0; i++)
+    if (ctx->cache[i].mesh == NULL) victim = i;
+  if (victim < 0) {
+    victim = 0;
+    for (int i = 1; i < D4EST_B200_CACHE; i++)
+      if (ctx->cache[i].stamp < ctx->cache[victim].stamp) victim = i;
+    d4b_mesh_destroy (ctx->cache[victim].mesh);
+  }
+  d4est_b200_flat_t *fl = d4est_b200_flatten (p4est, ghost, d4est_factors, ctx->flux_data);
+  d4est_b200_cached_mesh_t *c = &ctx->cache[victim];
+  c->mesh = d4b_mesh_create (&fl->desc);
+  d4est_b200_flat_destroy (fl);
+  c->factors = d4est_factors;
+  c->local_elements = ne;
+  c->local_nodes = nn;
+  c->stamp = ctx->clock;
+  ctx->uploads++;
+  return c->mesh;
+}
+
 void
 d4est_b200_apply_lhs (p4est_t * p4est, d4est_ghost_t * ghost,
                       d4est_ghost_data_t * ghost_data,
@@ -363,19 +400,8 @@ d4est_b200_apply_lhs (p4est_t * p4est, d4est_ghost_t * ghost,
                       d4est_mesh_data_t * d4est_factors, void *user)
 {
   d4est_b200_ctx_t *ctx = (d4est_b200_ctx_t *) user;
-  /* the reference re-runs d4est_mesh_update after AMR and once per multigrid
-   * level; (factors pointer, element count, node count) identifies a mesh */
-  if (ctx->mesh == NULL || ctx->cached_factors != d4est_factors
-      || ctx->cached_local_elements != p4est->local_num_quadrants
-      || ctx->cached_local_nodes != d4est_factors->local_sizes.local_nodes) {
-    if (ctx->mesh) d4b_mesh_destroy (ctx->mesh);
-    d4est_b200_flat_t *fl = d4est_b200_flatten (p4est, ghost, d4est_factors, ctx->flux_data);
-    ctx->mesh = d4b_mesh_create (&fl->desc);
-    d4est_b200_flat_destroy (fl);
-    ctx->cached_factors = d4est_factors;
-    ctx->cached_local_elements = p4est->local_num_quadrants;
-    ctx->cached_local_nodes = d4est_factors->local_sizes.local_nodes;
-  }
-  d4b_apply (ctx->mesh, prob_vecs->u, prob_vecs->Au);
+  d4b_mesh_t *mesh = d4est_b200_get_mesh (ctx, p4est, ghost, d4est_factors);
+  ctx->applies++;
+  d4b_apply (mesh, prob_vecs->u, prob_vecs->Au);
 }
 #endif

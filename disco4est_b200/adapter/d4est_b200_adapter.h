@@ -39,15 +39,32 @@ typedef struct
   int side_capacity;
 } d4est_b200_flat_t;
 
+/* One uploaded mesh.  The reference re-runs d4est_mesh_update after AMR and keeps
+ * one d4est_mesh_data_t per multigrid level alive for the whole solve
+ * (d4est_solver_multigrid_element_data_updater.c:89-205), so (factors pointer,
+ * element count, node count) identifies a mesh and a small cache makes every
+ * level a one-time upload.                                                    */
+#define D4EST_B200_CACHE 16
+typedef struct
+{
+  d4b_mesh_t *mesh;
+  d4est_mesh_data_t *factors;
+  int local_elements, local_nodes;
+  unsigned long stamp;                     /* last use, for eviction         */
+} d4est_b200_cached_mesh_t;
+
 /* user context stored in d4est_elliptic_eqns_t.user */
 typedef struct
 {
   d4est_laplacian_flux_data_t *flux_data;  /* as the reference callbacks use */
-  d4b_mesh_t *mesh;                        /* cached device mesh             */
-  d4est_mesh_data_t *cached_factors;       /* cache key                      */
-  int cached_local_elements;
-  int cached_local_nodes;
+  d4est_b200_cached_mesh_t cache[D4EST_B200_CACHE];
+  unsigned long clock;
+  long uploads, applies;                   /* statistics                     */
 } d4est_b200_ctx_t;
+
+/* the device mesh for the reference's current mesh (uploads it on first use) */
+d4b_mesh_t *d4est_b200_get_mesh(d4est_b200_ctx_t *ctx, p4est_t *p4est, d4est_ghost_t *ghost,
+                                d4est_mesh_data_t *d4est_factors);
 
 d4est_b200_flat_t *d4est_b200_flatten(p4est_t *p4est, d4est_ghost_t *d4est_ghost,
                                       d4est_mesh_data_t *d4est_factors,

@@ -88,6 +88,10 @@ emit $HERE/refbuild/ref_stubs.c obj/d8/ref_stubs.o "$DFLAGS"
 emit $HERE/../disco4est_b200/adapter/d4est_b200_adapter.c obj/d8/d4est_b200_adapter.o \
      "$DFLAGS -DD4EST_B200_ADAPTER_NO_DEVICE -I$HERE/../include -I$HERE/../disco4est_b200/adapter"
 emit $HERE/ref_driver.c obj/d8/ref_driver.o "$DFLAGS -I$HERE -I$HERE/../include -I$HERE/../disco4est_b200/adapter"
+# device-linked variant: the same driver and adapter with the C ABI library behind them
+emit $HERE/../disco4est_b200/adapter/d4est_b200_adapter.c obj/d8/d4est_b200_adapter_dev.o \
+     "$DFLAGS -I$HERE/../include -I$HERE/../disco4est_b200/adapter"
+emit $HERE/ref_driver.c obj/d8/ref_driver_dev.o "$DFLAGS -DD4B_WITH_DEVICE -I$HERE -I$HERE/../include -I$HERE/../disco4est_b200/adapter"
 
 if [ -s "$CMDS" ]; then
   echo "build_ref.sh: compiling $(wc -l < "$CMDS") files"
@@ -98,3 +102,10 @@ for s in $D8SRCS; do D8OBJS="$D8OBJS obj/d8/$(basename $s .c).o"; done
 gcc -o "$OUT/ref_driver" obj/d8/ref_driver.o obj/d8/d4est_b200_adapter.o $D8OBJS \
     obj/d8/miniblas.o obj/d8/ref_stubs.o obj/p4/*.o obj/sc/*.o obj/zlog/*.o -lm -lpthread
 echo "build_ref.sh: built $OUT/ref_driver"
+if [ -f "$HERE/../disco4est_b200/libd4est_b200.so" ]; then
+  gcc -o "$OUT/ref_driver_b200" obj/d8/ref_driver_dev.o obj/d8/d4est_b200_adapter_dev.o $D8OBJS \
+      obj/d8/miniblas.o obj/d8/ref_stubs.o obj/p4/*.o obj/sc/*.o obj/zlog/*.o \
+      -L"$HERE/../disco4est_b200" -ld4est_b200 -Wl,-rpath,'$ORIGIN/../../disco4est_b200' \
+      -Wl,--allow-shlib-undefined -lm -lpthread
+  echo "build_ref.sh: built $OUT/ref_driver_b200 (reference + libd4est_b200.so; runs on a GPU box only)"
+fi

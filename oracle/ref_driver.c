@@ -175,7 +175,7 @@ main (int argc, char *argv[])
   }
   const char *ini = argv[1];
   const char *out = argv[2];
-  int amr_steps = 0, time_reps = 0, bc_poly = 0, cheby_imax = 0, cheby_eigs_imax = 0, mg_vcycles = 0;
+  int amr_steps = 0, time_reps = 0, bc_poly = 0, cheby_imax = 0, cheby_eigs_imax = 0, mg_vcycles = 0, use_b200 = 0;
   for (int a = 3; a < argc; a++) {
     if (!strcmp (argv[a], "--amr")) amr_steps = atoi (argv[++a]);
     else if (!strcmp (argv[a], "--time")) time_reps = atoi (argv[++a]);
@@ -183,6 +183,7 @@ main (int argc, char *argv[])
     else if (!strcmp (argv[a], "--uniform-deg")) g_uniform_deg = atoi (argv[++a]);
     else if (!strcmp (argv[a], "--cheby")) { cheby_imax = atoi (argv[++a]); cheby_eigs_imax = atoi (argv[++a]); }
     else if (!strcmp (argv[a], "--mg")) { mg_vcycles = atoi (argv[++a]); }
+    else if (!strcmp (argv[a], "--b200")) { use_b200 = 1; }
     else { fprintf (stderr, "unknown option %s\n", argv[a]); return 2; }
   }
 
@@ -316,6 +317,76 @@ main (int argc, char *argv[])
           "\"t_apply_with_opt_s\": %.6f, \"plain_vs_opt_maxabs\": %.3e, \"u_sum\": %.17g, \"Au_sum\": %.17g}\n",
           (int) p4est->local_num_quadrants, local_nodes, t_mesh, best_plain, best_opt, maxdiff,
           d4est_util_sum_array_dbl (u, local_nodes), d4est_util_sum_array_dbl (Au_plain, local_nodes));
+
+#ifdef D4B_WITH_DEVICE
+  /* DROP-IN CHECK (ref_driver_b200 only, needs a GPU): the reference's own code calls
+   * eqns->apply_lhs = d4est_b200_apply_lhs instead of d4est_laplacian_apply_aij --
+   * once directly, then from inside its UNMODIFIED multigrid solver (smoother,
+   * cg_eigs, bottom CG all call apply_lhs through the same function pointer). */
+  if (use_b200 && !bc_poly) {
+    d4est_b200_ctx_t *bctx = d4est_b200_ctx_new (flux_plain);
+    d4est_elliptic_eqns_t fcns_b200 = {.build_residual = NULL,.apply_lhs = d4est_b200_apply_lhs,.user = bctx };
+    double *Au_b = P4EST_ALLOC_ZERO (double, local_nodes);
+    vecs.Au = Au_b;
+    d4est_elliptic_eqns_apply_lhs (p4est, d4est_ghost, d4est_ghost_data, &fcns_b200, &vecs,
+                                   d4est_ops, d4est_geom, d4est_quad, d4est_factors);
+    double t1 = wall ();
+    for (int r = 0; r < 5; r++)
+      d4est_elliptic_eqns_apply_lhs (p4est, d4est_ghost, d4est_ghost_data, &fcns_b200, &vecs,
+                                     d4est_ops, d4est_geom, d4est_quad, d4est_factors);
+    double t_b200 = (wall () - t1) / 5.;
+    double num = 0., den = 0.;
+    for (int i = 0; i < local_nodes; i++) {
+      num += (Au_b[i] - Au_plain[i]) * (Au_b[i] - Au_plain[i]);
+      den += Au_plain[i] * Au_plain[i];
+    }
+    printf ("{\"b200_apply_rel_l2\": %.3e, \"t_apply_b200_host_vectors_s\": %.6f, \"t_apply_reference_s\": %.6f}\n",
+            sqrt (num / den), t_b200, best_plain < best_opt ? best_plain : best_opt);
+    if (mg_vcycles > 0) {
+      double r2s[2][64], tsolve[2];
+      double *usol[2];
+      for (int which = 0; which < 2; which++) {   /* 0: stock apply_lhs, 1: B200 apply_lhs */
+        d4est_solver_multigrid_t *mg_data =
+          d4est_solver_multigrid_data_init (p4est, d4est_ops, d4est_geom, d4est_quad, &d4est_ghost,
+                                            &d4est_ghost_data, d4est_factors, initial_grid_input, ini);
+        usol[which] = P4EST_ALLOC_ZERO (double, local_nodes);
+        double *mAu = P4EST_ALLOC_ZERO (double, local_nodes);
+        d4est_elliptic_data_t mv = vecs;
+        mv.u = usol[which]; mv.Au = mAu; mv.rhs = Au_plain;
+        double t2 = wall ();
+        for (int k = 0; k < mg_vcycles && k < 63; k++) {
+          d4est_solver_multigrid_solve (p4est, &mv, which ? &fcns_b200 : &fcns_plain, mg_data);
+          r2s[which][k] = mg_data->vcycle_r2_global_current;
+        }
+        tsolve[which] = wall () - t2;
+        P4EST_FREE (mAu);
+        d4est_solver_multigrid_data_destroy (mg_data);
+      }
+      double worst = 0., unum = 0., uden = 0.;
+      for (int k = 0; k < mg_vcycles && k < 63; k++) {
+        double rr = fabs (r2s[0][k] - r2s[1][k]) / r2s[0][k];
+        if (rr > worst && r2s[0][k] > 1e-20 * r2s[0][0]) worst = rr;
+      }
+      for (int i = 0; i < local_nodes; i++) {
+        unum += (usol[0][i] - usol[1][i]) * (usol[0][i] - usol[1][i]);
+        uden += usol[0][i] * usol[0][i];
+      }
+      printf ("{\"mg_vcycles\": %d, \"r2_reference\": [", mg_vcycles);
+      for (int k = 0; k < mg_vcycles && k < 63; k++) printf ("%s%.6e", k ? ", " : "", r2s[0][k]);
+      printf ("], \"r2_b200_apply\": [");
+      for (int k = 0; k < mg_vcycles && k < 63; k++) printf ("%s%.6e", k ? ", " : "", r2s[1][k]);
+      printf ("], \"r2_worst_rel_diff\": %.3e, \"u_rel_l2_diff\": %.3e, \"t_mg_reference_s\": %.4f, "
+              "\"t_mg_b200_apply_s\": %.4f, \"device_mesh_uploads\": %ld, \"b200_applies\": %ld}\n",
+              worst, sqrt (unum / uden), tsolve[0], tsolve[1], bctx->uploads, bctx->applies);
+      P4EST_FREE (usol[0]); P4EST_FREE (usol[1]);
+    }
+    vecs.Au = Au_tmp;
+    P4EST_FREE (Au_b);
+    d4est_b200_ctx_destroy (bctx);
+  }
+#else
+  if (use_b200) { fprintf (stderr, "--b200 needs the device-linked build (ref_driver_b200)\n"); return 2; }
+#endif
 
   if (strcmp (out, "-")) {
     d4est_b200_flat_t *flat = d4est_b200_flatten (p4est, d4est_ghost, d4est_factors, flux_plain);
