@@ -404,4 +404,46 @@ d4est_b200_apply_lhs (p4est_t * p4est, d4est_ghost_t * ghost,
   ctx->applies++;
   d4b_apply (mesh, prob_vecs->u, prob_vecs->Au);
 }
+
+/* ------------------------------------------------------------ smoother */
+#include <d4est_solver_multigrid_smoother_cheby.h>
+
+/* one context per process is enough for the reference's single-threaded solvers */
+static d4est_b200_ctx_t *d4est_b200_smoother_ctx = NULL;
+
+static void
+d4est_b200_smoother_cheby_smooth (p4est_t * p4est, d4est_elliptic_data_t * vecs,
+                                  d4est_elliptic_eqns_t * fcns, double *r, int level)
+{
+  d4est_solver_multigrid_t *mg_data = (d4est_solver_multigrid_t *) p4est->user_pointer;
+  d4est_solver_multigrid_smoother_cheby_t *cheby = mg_data->smoother->user;
+  d4est_solver_multigrid_element_data_updater_t *updater = mg_data->elem_data_updater;
+  d4b_mesh_t *mesh = d4est_b200_get_mesh (d4est_b200_smoother_ctx, p4est, updater->current_d4est_ghost,
+                                          updater->current_d4est_factors);
+  /* same decisions as d4est_solver_multigrid_smoother_cheby (:264-376); the flag
+   * cheby_eigs_compute is maintained by the reference's own update callback (:222-262) */
+  if (cheby->cheby_eigs_compute) {
+    cheby->eigs[level] = d4b_cg_eigs (mesh, vecs->u, vecs->rhs, cheby->cheby_eigs_cg_imax,
+                                      cheby->cheby_use_new_cg_eigs, cheby->cheby_use_zero_guess_for_eigs);
+    cheby->eigs[level] *= cheby->cheby_eigs_max_multiplier;
+  }
+  if (cheby->cheby_use_zero_guess_for_eigs == 1 && cheby->cheby_eigs_reuse_fromdownvcycle != 1) {
+    D4EST_ABORT ("If you set cheby_use_zero_guess_for_eigs == 1, please set cheby_eigs_reuse_fromdownvcycle = 1");
+  }
+  const double lmax = cheby->eigs[level];
+  const double lmin = lmax / cheby->cheby_eigs_lmax_lmin_ratio;
+  d4b_cheby_smooth (mesh, vecs->u, vecs->rhs, r, cheby->cheby_imax, lmin, lmax);
+}
+
+d4est_solver_multigrid_smoother_t *
+d4est_b200_smoother_cheby_init (p4est_t * p4est, int num_of_levels, const char *input_file,
+                                d4est_b200_ctx_t * ctx)
+{
+  /* the reference's factory parses [mg_smoother_cheby] and installs its update callback */
+  d4est_solver_multigrid_smoother_t *smoother =
+    d4est_solver_multigrid_smoother_cheby_init (p4est, num_of_levels, input_file);
+  smoother->smooth = d4est_b200_smoother_cheby_smooth;
+  d4est_b200_smoother_ctx = ctx;
+  return smoother;
+}
 #endif

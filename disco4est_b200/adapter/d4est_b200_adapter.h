@@ -18,6 +18,7 @@
 #include <d4est_elliptic_eqns.h>
 #include <d4est_laplacian_flux.h>
 #include <d4est_laplacian_flux_sipg.h>
+#include <d4est_solver_multigrid.h>
 #include "d4est_b200.h"
 
 /* Owns the arrays a d4b_mesh_desc_t points to (those that are not aliases of
@@ -82,5 +83,20 @@ void d4est_b200_apply_lhs(p4est_t *p4est, d4est_ghost_t *ghost,
 
 d4est_b200_ctx_t *d4est_b200_ctx_new(d4est_laplacian_flux_data_t *flux_data);
 void d4est_b200_ctx_destroy(d4est_b200_ctx_t *ctx);
+
+/* Second entry point: the multigrid smoother.  Same factory signature, INI section
+ * ([mg_smoother_cheby]) and behaviour as d4est_solver_multigrid_smoother_cheby_init
+ * (src/Solver/d4est_solver_multigrid_smoother_cheby.c:20-63, :264-376, :378-430) plus the
+ * context: `smooth` runs cg_eigs and the Chebyshev recurrence on the device (vectors cross
+ * PCIe once per smoothing instead of once per apply) and leaves vecs->u and r = rhs - A u
+ * exactly like the reference.  The operator is the SIPG Laplacian of ctx->flux_data: only
+ * valid where fcns->apply_lhs is d4est_laplacian[_with_opt]_apply_aij.  Install with
+ *   mg_data->smoother = d4est_b200_smoother_cheby_init(p4est, mg_data->num_of_levels, ini, ctx);
+ * (what d4est_solver_multigrid_set_smoother does for "mg_smoother_cheby",
+ * d4est_solver_multigrid.c:429-474); destroy with the reference's
+ * d4est_solver_multigrid_smoother_cheby_destroy.                                        */
+d4est_solver_multigrid_smoother_t *d4est_b200_smoother_cheby_init(p4est_t *p4est, int num_of_levels,
+                                                                  const char *input_file,
+                                                                  d4est_b200_ctx_t *ctx);
 
 #endif

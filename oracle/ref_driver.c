@@ -343,12 +343,18 @@ main (int argc, char *argv[])
     printf ("{\"b200_apply_rel_l2\": %.3e, \"t_apply_b200_host_vectors_s\": %.6f, \"t_apply_reference_s\": %.6f}\n",
             sqrt (num / den), t_b200, best_plain < best_opt ? best_plain : best_opt);
     if (mg_vcycles > 0) {
-      double r2s[2][64], tsolve[2];
-      double *usol[2];
-      for (int which = 0; which < 2; which++) {   /* 0: stock apply_lhs, 1: B200 apply_lhs */
+      double r2s[3][64], tsolve[3];
+      double *usol[3];
+      /* 0: stock apply_lhs, 1: B200 apply_lhs under the reference's smoother,
+       * 2: B200 smoother (d4est_b200_smoother_cheby_init) + B200 apply_lhs for the rest */
+      for (int which = 0; which < 3; which++) {
         d4est_solver_multigrid_t *mg_data =
           d4est_solver_multigrid_data_init (p4est, d4est_ops, d4est_geom, d4est_quad, &d4est_ghost,
                                             &d4est_ghost_data, d4est_factors, initial_grid_input, ini);
+        if (which == 2) {
+          d4est_solver_multigrid_smoother_cheby_destroy (mg_data->smoother);
+          mg_data->smoother = d4est_b200_smoother_cheby_init (p4est, mg_data->num_of_levels, ini, bctx);
+        }
         usol[which] = P4EST_ALLOC_ZERO (double, local_nodes);
         double *mAu = P4EST_ALLOC_ZERO (double, local_nodes);
         d4est_elliptic_data_t mv = vecs;
@@ -362,13 +368,16 @@ main (int argc, char *argv[])
         P4EST_FREE (mAu);
         d4est_solver_multigrid_data_destroy (mg_data);
       }
-      double worst = 0., unum = 0., uden = 0.;
+      double worst = 0., unum = 0., uden = 0., worst2 = 0., unum2 = 0.;
       for (int k = 0; k < mg_vcycles && k < 63; k++) {
         double rr = fabs (r2s[0][k] - r2s[1][k]) / r2s[0][k];
         if (rr > worst && r2s[0][k] > 1e-20 * r2s[0][0]) worst = rr;
+        rr = fabs (r2s[0][k] - r2s[2][k]) / r2s[0][k];
+        if (rr > worst2 && r2s[0][k] > 1e-20 * r2s[0][0]) worst2 = rr;
       }
       for (int i = 0; i < local_nodes; i++) {
         unum += (usol[0][i] - usol[1][i]) * (usol[0][i] - usol[1][i]);
+        unum2 += (usol[0][i] - usol[2][i]) * (usol[0][i] - usol[2][i]);
         uden += usol[0][i] * usol[0][i];
       }
       printf ("{\"mg_vcycles\": %d, \"r2_reference\": [", mg_vcycles);
@@ -376,9 +385,11 @@ main (int argc, char *argv[])
       printf ("], \"r2_b200_apply\": [");
       for (int k = 0; k < mg_vcycles && k < 63; k++) printf ("%s%.6e", k ? ", " : "", r2s[1][k]);
       printf ("], \"r2_worst_rel_diff\": %.3e, \"u_rel_l2_diff\": %.3e, \"t_mg_reference_s\": %.4f, "
-              "\"t_mg_b200_apply_s\": %.4f, \"device_mesh_uploads\": %ld, \"b200_applies\": %ld}\n",
-              worst, sqrt (unum / uden), tsolve[0], tsolve[1], bctx->uploads, bctx->applies);
-      P4EST_FREE (usol[0]); P4EST_FREE (usol[1]);
+              "\"t_mg_b200_apply_s\": %.4f, \"device_mesh_uploads\": %ld, \"b200_applies\": %ld, "
+              "\"smoother_r2_worst_rel_diff\": %.3e, \"smoother_u_rel_l2_diff\": %.3e, \"t_mg_b200_smoother_s\": %.4f}\n",
+              worst, sqrt (unum / uden), tsolve[0], tsolve[1], bctx->uploads, bctx->applies,
+              worst2, sqrt (unum2 / uden), tsolve[2]);
+      P4EST_FREE (usol[0]); P4EST_FREE (usol[1]); P4EST_FREE (usol[2]);
     }
     vecs.Au = Au_tmp;
     P4EST_FREE (Au_b);

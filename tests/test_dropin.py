@@ -43,3 +43,11 @@ def test_reference_multigrid_driving_our_apply():
     assert res["device_mesh_uploads"] == 3          # one upload per multigrid level, cached afterwards
     for a, b in zip(res["r2_reference"], res["r2_b200_apply"]):
         assert abs(a - b) <= 1e-6 * a
+
+
+def test_reference_multigrid_with_our_smoother_entry():
+    """d4est_b200_smoother_cheby_init installed as mg_data->smoother of the reference's solver"""
+    lines = run("brick_poisson_mg.ini", "--uniform-deg", "3", "--mg", "4")
+    res = [l for l in lines if "smoother_u_rel_l2_diff" in l][0]
+    assert res["smoother_u_rel_l2_diff"] < 1e-10
+    assert res["smoother_r2_worst_rel_diff"] < 1e-5
