@@ -50,11 +50,24 @@ bool is_device_ptr(const void *p) {
 
 void d4b_apply_device(d4b_mesh *m, const double *du, double *dAu) {
   D4B_CHECK(m->epi.mode == 0 || m->n_generic == 0, "fused epilogue on a mesh with general-kernel elements");
-  // halo exchange on the communication stream while interior elements run
-  d4b_comm_exchange_begin(m, du);
-  d4b_launch_fast(m, du, dAu, 0);
-  d4b_comm_exchange_wait(m);
-  d4b_launch_fast(m, du, dAu, 1);
+  if (m->mpisize == 1) {
+    d4b_launch_fast(m, du, dAu, 0);
+    d4b_launch_fast(m, du, dAu, 1);
+  } else {
+    // compute stream:  pack | uh(local) | interior elements ............ | join
+    // halo stream   :       wait pack | send/recv | wait uh(local) | uh(ghosts) | boundary elements
+    d4b_comm_exchange_begin(m, du);
+    d4b_launch_fast(m, du, dAu, 0);
+    D4B_CUDA(cudaEventRecord(m->ev_interp, m->stream));
+    d4b_launch_fast(m, du, dAu, 1);
+    cudaStream_t compute = m->stream;
+    m->stream = m->comm_stream;
+    D4B_CUDA(cudaStreamWaitEvent(m->comm_stream, m->ev_interp, 0));
+    d4b_launch_fast(m, du, dAu, 2);
+    D4B_CUDA(cudaEventRecord(m->ev_boundary, m->comm_stream));
+    m->stream = compute;
+    D4B_CUDA(cudaStreamWaitEvent(m->stream, m->ev_boundary, 0));
+  }
   d4b_launch_generic(m, du, dAu, 0);
 }
 

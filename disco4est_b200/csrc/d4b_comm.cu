@@ -137,7 +137,13 @@ void d4b_comm_setup(d4b_mesh *m, const d4b_mesh_desc_t *d) {
   m->d_send_dst = d4b_dev_upload<int64_t>(m, dst.data(), dst.size());
   m->d_send_cnt = d4b_dev_upload<int32_t>(m, cnt.data(), cnt.size());
   m->d_sendbuf = d4b_dev_alloc<double>(m, (size_t)send_total);
-  D4B_CUDA(cudaStreamCreateWithFlags(&m->comm_stream, cudaStreamNonBlocking));
+  // highest priority: the halo and the few elements that wait for it are scheduled into
+  // the SM slots the interior launch frees, instead of queueing behind it
+  int prio_lo = 0, prio_hi = 0;
+  D4B_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+  D4B_CUDA(cudaStreamCreateWithPriority(&m->comm_stream, cudaStreamNonBlocking, prio_hi));
+  D4B_CUDA(cudaEventCreateWithFlags(&m->ev_interp, cudaEventDisableTiming));
+  D4B_CUDA(cudaEventCreateWithFlags(&m->ev_boundary, cudaEventDisableTiming));
   D4B_CUDA(cudaEventCreateWithFlags(&m->ev_packed, cudaEventDisableTiming));
   D4B_CUDA(cudaEventCreateWithFlags(&m->ev_recv, cudaEventDisableTiming));
 }
@@ -146,6 +152,8 @@ void d4b_comm_teardown(d4b_mesh *m) {
   if (m->comm_stream) cudaStreamDestroy(m->comm_stream);
   if (m->ev_packed) cudaEventDestroy(m->ev_packed);
   if (m->ev_recv) cudaEventDestroy(m->ev_recv);
+  if (m->ev_interp) cudaEventDestroy(m->ev_interp);
+  if (m->ev_boundary) cudaEventDestroy(m->ev_boundary);
 }
 
 // pack on the compute stream, exchange on the communication stream; the caller

@@ -773,17 +773,24 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
   m->d_uhat = d4b_dev_alloc<double>(m, (size_t)(d->local_nodes + d->ghost_nodes));
 }
 
-void d4b_launch_fast(d4b_mesh *m, const double *d_u, double *d_Au, int phase) {
-  for (const D4bFastClass &c : m->fast) {
+// part 0: uh of the local elements; part 1: elements without a ghost neighbour;
+// part 2 (after the halo arrived): uh of the ghost elements + elements with a ghost neighbour.
+// Launches go to m->stream (d4b_apply_device points it at the high-priority halo stream for part 2).
+void d4b_launch_fast(d4b_mesh *m, const double *d_u, double *d_Au, int part) {
+  if (part != 1) {
+    const int phase = part == 0 ? 0 : 1;
+    for (const D4bFastClass &c : m->fast) {
 #define D4B_CASE(n) case n: launch_interp<n>(m, c, d_u, phase); break;
-    switch (c.deg + 1) {
-      D4B_CASE(2) D4B_CASE(3) D4B_CASE(4) D4B_CASE(5) D4B_CASE(6) D4B_CASE(7) D4B_CASE(8)
-      default: D4B_ABORT("fast path: unsupported degree %d", c.deg);
-    }
+      switch (c.deg + 1) {
+        D4B_CASE(2) D4B_CASE(3) D4B_CASE(4) D4B_CASE(5) D4B_CASE(6) D4B_CASE(7) D4B_CASE(8)
+        default: D4B_ABORT("fast path: unsupported degree %d", c.deg);
+      }
 #undef D4B_CASE
+    }
   }
+  if (part == 0) return;
   for (const D4bFastClass &c : m->fast) {
-    const int first = phase == 0 ? 0 : c.n_interior, last = phase == 0 ? c.n_interior : c.n_elem;
+    const int first = part == 1 ? 0 : c.n_interior, last = part == 1 ? c.n_interior : c.n_elem;
 #define D4B_CASE(n) case n: if (c.kind) launch_flat<n>(m, c, d_Au, first, last); else launch_fast<n>(m, c, d_Au, first, last); break;
     switch (c.deg + 1) {
       D4B_CASE(2) D4B_CASE(3) D4B_CASE(4) D4B_CASE(5) D4B_CASE(6) D4B_CASE(7) D4B_CASE(8)

@@ -125,7 +125,7 @@ struct d4b_mesh {
   int32_t *d_send_cnt = nullptr;
   double *d_sendbuf = nullptr;
   cudaStream_t comm_stream = nullptr;
-  cudaEvent_t ev_packed = nullptr, ev_recv = nullptr;
+  cudaEvent_t ev_packed = nullptr, ev_recv = nullptr, ev_interp = nullptr, ev_boundary = nullptr;
 
   // staging for host-pointer calls
   double *d_u_stage = nullptr, *d_Au_stage = nullptr;
@@ -160,9 +160,9 @@ void d4b_apply_device(d4b_mesh *m, const double *d_u, double *d_Au);
 void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *desc, const std::vector<double> &mortar,
                     const std::vector<double> &G, const std::vector<int32_t> &elem_side,
                     std::vector<char> &is_fast);
-// phase 0: uh of local elements + interior elements; phase 1 (after the halo
-// exchange): uh of ghost elements + elements with a ghost neighbour
-void d4b_launch_fast(d4b_mesh *m, const double *d_u, double *d_Au, int phase);
+// part 0: uh of local elements; 1: interior elements; 2 (after the halo exchange): uh of
+// ghost elements + elements with a ghost neighbour
+void d4b_launch_fast(d4b_mesh *m, const double *d_u, double *d_Au, int part);
 
 // halo exchange (d4b_comm.cu)
 void d4b_comm_setup(d4b_mesh *m, const d4b_mesh_desc_t *d);
