@@ -46,7 +46,7 @@ def required_bytes_per_dof(p, flat):
 
 # DRAM bytes per apply from `ncu --set full` (dram__bytes_read.sum + dram__bytes_write.sum over
 # interp_kernel + flat_apply_kernel), only for the default workload; see profiles/
-NCU_TRAFFIC_BYTES = {(6, 3): None}
+NCU_TRAFFIC_BYTES = {(6, 3): 1.656e9}   # profiles/r01_ncu_full_flat_p3_64cube.txt
 
 
 def measured_peak():
