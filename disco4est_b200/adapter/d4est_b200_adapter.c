@@ -446,4 +446,203 @@ d4est_b200_smoother_cheby_init (p4est_t * p4est, int num_of_levels, const char *
   d4est_b200_smoother_ctx = ctx;
   return smoother;
 }
+
+/* ------------------------------------------------------- preconditioner */
+#include <d4est_solver_multigrid_bottom_solver_cg.h>
+#include <d4est_solver_multigrid_bottom_solver_cheby.h>
+
+static d4est_b200_pc_multigrid_data_t *d4est_b200_pc_recording = NULL;
+
+static void
+d4est_b200_pc_record_level (p4est_t * p4est, int level, double *r, int local_nodes)
+{
+  d4est_b200_pc_multigrid_data_t *pcd = d4est_b200_pc_recording;
+  d4est_solver_multigrid_t *mg_data = (d4est_solver_multigrid_t *) p4est->user_pointer;
+  d4est_solver_multigrid_element_data_updater_t *updater = mg_data->elem_data_updater;
+  if (pcd->level_mesh[level] == NULL) {     /* down leg; the up leg revisits the same meshes */
+    pcd->level_mesh[level] = d4est_b200_get_mesh (pcd->ctx, p4est, updater->current_d4est_ghost,
+                                                  updater->current_d4est_factors);
+    pcd->level_elements[level] = p4est->local_num_quadrants;
+  }
+  /* zero residual -> zero coarse right-hand sides, zero corrections: u is left as it was */
+  memset (r, 0, sizeof (double) * (size_t) local_nodes);
+}
+
+static void
+d4est_b200_pc_record_smooth (p4est_t * p4est, d4est_elliptic_data_t * vecs,
+                             d4est_elliptic_eqns_t * fcns, double *r, int level)
+{
+  d4est_b200_pc_record_level (p4est, level, r, vecs->local_nodes);
+}
+
+static void
+d4est_b200_pc_record_bottom (p4est_t * p4est, d4est_elliptic_data_t * vecs,
+                             d4est_elliptic_eqns_t * fcns, double *r)
+{
+  d4est_b200_pc_record_level (p4est, 0, r, vecs->local_nodes);
+}
+
+static void
+d4est_b200_pc_no_update (p4est_t * p4est, int level, d4est_elliptic_data_t * vecs)
+{
+}
+
+static void
+d4est_b200_pc_drop_hierarchy (d4est_b200_pc_multigrid_data_t * pcd)
+{
+  if (pcd->mg) d4b_mg_destroy (pcd->mg);
+  pcd->mg = NULL;
+  for (int l = 0; l < D4EST_B200_MAX_LEVELS; l++) pcd->level_mesh[l] = NULL;
+}
+
+/* one recording V-cycle of the reference, then d4b_mg_create from what it left behind */
+static void
+d4est_b200_pc_build_hierarchy (d4est_b200_pc_multigrid_data_t * pcd, p4est_t * p4est,
+                               d4est_elliptic_data_t * vecs, d4est_elliptic_eqns_t * fcns)
+{
+  d4est_solver_multigrid_t *mg_data = pcd->mg_data;
+  const int nl = mg_data->num_of_levels, top = nl - 1;
+  if (nl < 2 || nl > D4EST_B200_MAX_LEVELS) D4EST_ABORT ("d4est_b200_pc_multigrid: unsupported number of levels");
+  if (strcmp (mg_data->smoother_name, "mg_smoother_cheby")) D4EST_ABORT ("d4est_b200_pc_multigrid needs mg_smoother_cheby");
+  d4est_b200_pc_drop_hierarchy (pcd);
+
+  d4est_solver_multigrid_smoother_fcn_t smooth0 = mg_data->smoother->smooth;
+  d4est_solver_multigrid_update_callback_fcn_t supdate0 = mg_data->smoother->update;
+  d4est_solver_multigrid_bottom_solver_fcn_t solve0 = mg_data->bottom_solver->solve;
+  d4est_solver_multigrid_update_callback_fcn_t bupdate0 = mg_data->bottom_solver->update;
+  const int imax0 = mg_data->vcycle_imax;
+  mg_data->smoother->smooth = d4est_b200_pc_record_smooth;
+  mg_data->smoother->update = d4est_b200_pc_no_update;
+  mg_data->bottom_solver->solve = d4est_b200_pc_record_bottom;
+  if (bupdate0) mg_data->bottom_solver->update = d4est_b200_pc_no_update;
+  mg_data->vcycle_imax = 1;
+  d4est_b200_pc_recording = pcd;
+  d4est_solver_multigrid_solve (p4est, vecs, fcns, mg_data);
+  d4est_b200_pc_recording = NULL;
+  mg_data->smoother->smooth = smooth0;
+  mg_data->smoother->update = supdate0;
+  mg_data->bottom_solver->solve = solve0;
+  mg_data->bottom_solver->update = bupdate0;
+  mg_data->vcycle_imax = imax0;
+
+  /* families: the records of level l's coarsening follow those of level l+1's
+   * (mg_data->stride bookkeeping, d4est_solver_multigrid.c:975-1046) */
+  int32_t *first[D4EST_B200_MAX_LEVELS], *count[D4EST_B200_MAX_LEVELS];
+  const d4est_solver_multigrid_refine_data_t *cgr = mg_data->coarse_grid_refinement;
+  int rec = 0;
+  for (int l = top - 1; l >= 0; l--) {
+    if (pcd->level_mesh[l] == NULL || pcd->level_mesh[l + 1] == NULL)
+      D4EST_ABORT ("d4est_b200_pc_multigrid: the recording V-cycle did not visit every level");
+    const int n_fine = pcd->level_elements[l + 1], n_coarse = pcd->level_elements[l];
+    first[l] = (int32_t *) malloc (sizeof (int32_t) * (n_coarse + 8));
+    count[l] = (int32_t *) malloc (sizeof (int32_t) * (n_coarse + 8));
+    int consumed = 0, ce = 0;
+    while (consumed < n_fine && ce < n_coarse) {
+      const int h = cgr[rec++].hrefine;
+      if (h == 1) { first[l][ce] = consumed; count[l][ce] = (P4EST_CHILDREN); ce++; consumed += (P4EST_CHILDREN); }
+      else if (h == 0) { first[l][ce] = consumed; count[l][ce] = 1; ce++; consumed++; }
+      else                                  /* coarsened, then re-split by the 2:1 balance: eight 1:1 copies */
+        for (int i = 0; i < (P4EST_CHILDREN); i++) { first[l][ce] = consumed; count[l][ce] = 1; ce++; consumed++; }
+    }
+    if (consumed != n_fine || ce != n_coarse) D4EST_ABORT ("d4est_b200_pc_multigrid: refinement records do not match the level sizes");
+  }
+
+  d4b_mg_desc_t D;
+  memset (&D, 0, sizeof (D));
+  D.n_levels = nl;
+  D.meshes = pcd->level_mesh;
+  D.child_first = (const int32_t * const *) first;
+  D.child_count = (const int32_t * const *) count;
+  D.vcycle_imax = mg_data->vcycle_imax;
+  D.vcycle_rtol = mg_data->vcycle_rtol;
+  D.vcycle_atol = mg_data->vcycle_atol;
+  const d4est_solver_multigrid_smoother_cheby_t *ch = mg_data->smoother->user;
+  D.smoother.cheby_imax = ch->cheby_imax;
+  D.smoother.cheby_eigs_cg_imax = ch->cheby_eigs_cg_imax;
+  D.smoother.cheby_eigs_lmax_lmin_ratio = ch->cheby_eigs_lmax_lmin_ratio;
+  D.smoother.cheby_eigs_max_multiplier = ch->cheby_eigs_max_multiplier;
+  D.smoother.cheby_use_new_cg_eigs = ch->cheby_use_new_cg_eigs;
+  D.smoother.cheby_use_zero_guess_for_eigs = ch->cheby_use_zero_guess_for_eigs;
+  D.smoother.cheby_eigs_reuse_fromdownvcycle = ch->cheby_eigs_reuse_fromdownvcycle;
+  D.smoother.cheby_eigs_reuse_fromlastvcycle = ch->cheby_eigs_reuse_fromlastvcycle;
+  if (!strcmp (mg_data->bottom_solver_name, "mg_bottom_solver_cg")) {
+    const d4est_solver_multigrid_bottom_solver_cg_t *b = mg_data->bottom_solver->user;
+    D.bottom_solver = 0;
+    D.bottom_iter = b->bottom_imax;
+    D.bottom_rtol = b->bottom_rtol;
+    D.bottom_atol = b->bottom_atol;
+  }
+  else if (!strcmp (mg_data->bottom_solver_name, "mg_bottom_solver_cheby")) {
+    const d4est_solver_multigrid_bottom_solver_cheby_t *b = mg_data->bottom_solver->user;
+    D.bottom_solver = 1;
+    D.bottom_cheby.cheby_imax = b->cheby_imax;
+    D.bottom_cheby.cheby_eigs_cg_imax = b->cheby_eigs_cg_imax;
+    D.bottom_cheby.cheby_eigs_lmax_lmin_ratio = b->cheby_eigs_lmax_lmin_ratio;
+    D.bottom_cheby.cheby_eigs_max_multiplier = b->cheby_eigs_max_multiplier;
+    D.bottom_cheby.cheby_use_new_cg_eigs = b->cheby_use_new_cg_eigs;
+  }
+  else
+    D4EST_ABORT ("d4est_b200_pc_multigrid needs mg_bottom_solver_cg or mg_bottom_solver_cheby");
+  pcd->mg = d4b_mg_create (&D);
+  for (int l = 0; l < top; l++) { free (first[l]); free (count[l]); }
+  pcd->n_levels = nl;
+  pcd->top_elements = p4est->local_num_quadrants;
+  pcd->top_nodes = vecs->local_nodes;
+  pcd->builds++;
+}
+
+static void
+d4est_b200_pc_multigrid_apply (d4est_krylov_pc_t * kpc, double *xp, double *yp)
+{
+  d4est_b200_pc_multigrid_data_t *pcd = kpc->pc_data;
+  krylov_ctx_t *kct = kpc->pc_ctx;
+  const int local_nodes = kct->vecs->local_nodes;
+  /* zero initial guess, d4est_krylov_pc_multigrid.c:52 */
+  memset (yp, 0, sizeof (double) * (size_t) local_nodes);
+  if (pcd->mg == NULL || pcd->top_elements != kct->p4est->local_num_quadrants || pcd->top_nodes != local_nodes) {
+    double *Au = P4EST_ALLOC (double, local_nodes);
+    d4est_elliptic_data_t mg_prob_vecs;
+    d4est_elliptic_data_copy_ptrs (kct->vecs, &mg_prob_vecs);
+    mg_prob_vecs.u = yp;
+    mg_prob_vecs.rhs = xp;
+    mg_prob_vecs.Au = Au;
+    d4est_b200_pc_build_hierarchy (pcd, kct->p4est, &mg_prob_vecs, kct->fcns);
+    P4EST_FREE (Au);
+  }
+  pcd->vcycles += d4b_mg_solve (pcd->mg, yp, xp, NULL);
+  pcd->applies++;
+}
+
+static void
+d4est_b200_pc_multigrid_setup (d4est_krylov_pc_t * kpc)
+{
+  /* "Operator is changing" (d4est_krylov_pc_multigrid.c:8-26): rebuild on the next apply */
+  d4est_b200_pc_multigrid_data_t *pcd = kpc->pc_data;
+  d4est_b200_pc_drop_hierarchy (pcd);
+  if (pcd->user_setup_fcn != NULL) pcd->user_setup_fcn (kpc);
+}
+
+d4est_krylov_pc_t *
+d4est_b200_pc_multigrid_create (d4est_solver_multigrid_t * mg_data, d4est_b200_ctx_t * ctx,
+                                void (*user_setup_fcn) (d4est_krylov_pc_t *))
+{
+  d4est_krylov_pc_t *pc = P4EST_ALLOC (d4est_krylov_pc_t, 1);
+  d4est_b200_pc_multigrid_data_t *pcd = P4EST_ALLOC_ZERO (d4est_b200_pc_multigrid_data_t, 1);
+  pcd->mg_data = mg_data;
+  pcd->ctx = ctx;
+  pcd->user_setup_fcn = user_setup_fcn;
+  pc->pc_apply = d4est_b200_pc_multigrid_apply;
+  pc->pc_setup = d4est_b200_pc_multigrid_setup;
+  pc->pc_data = pcd;
+  pc->pc_ctx = NULL;
+  return pc;
+}
+
+void
+d4est_b200_pc_multigrid_destroy (d4est_krylov_pc_t * kpc)
+{
+  d4est_b200_pc_drop_hierarchy ((d4est_b200_pc_multigrid_data_t *) kpc->pc_data);
+  P4EST_FREE (kpc->pc_data);
+  P4EST_FREE (kpc);
+}
 #endif

@@ -19,6 +19,7 @@
 #include <d4est_laplacian_flux.h>
 #include <d4est_laplacian_flux_sipg.h>
 #include <d4est_solver_multigrid.h>
+#include <d4est_krylov_pc.h>
 #include "d4est_b200.h"
 
 /* Owns the arrays a d4b_mesh_desc_t points to (those that are not aliases of
@@ -45,7 +46,7 @@ typedef struct
  * (d4est_solver_multigrid_element_data_updater.c:89-205), so (factors pointer,
  * element count, node count) identifies a mesh and a small cache makes every
  * level a one-time upload.                                                    */
-#define D4EST_B200_CACHE 16
+#define D4EST_B200_CACHE 32
 typedef struct
 {
   d4b_mesh_t *mesh;
@@ -98,5 +99,41 @@ void d4est_b200_ctx_destroy(d4est_b200_ctx_t *ctx);
 d4est_solver_multigrid_smoother_t *d4est_b200_smoother_cheby_init(p4est_t *p4est, int num_of_levels,
                                                                   const char *input_file,
                                                                   d4est_b200_ctx_t *ctx);
+
+/* Third entry point: the whole multigrid preconditioner, device-resident.  Same role and
+ * call convention as d4est_krylov_pc_multigrid_create (src/Solver/d4est_krylov_pc_multigrid.c:82-100):
+ * the returned d4est_krylov_pc_t is handed to the Krylov solver, which calls
+ * pc_apply(kpc, x, y) with host arrays (d4est_krylov_pc.h:69-89).  pc_apply does what
+ * d4est_krylov_pc_multigrid_apply does -- y = 0, then d4est_solver_multigrid_solve on
+ * A y = x with mg_data's vcycle_imax / rtol / atol, [mg_smoother_cheby] and bottom-solver
+ * settings -- but as H2D(x), V-cycles on the device (d4b_mg_solve), D2H(y).
+ *
+ * The level hierarchy is taken from the reference itself: on the first apply (and again
+ * after pc_setup signalled a changed operator, or when the top mesh changed) ONE V-cycle of
+ * the unmodified d4est_solver_multigrid_solve is run with a recording smoother / bottom
+ * solver that do no arithmetic.  It walks the reference's own coarsen / balance / mesh-update
+ * sequence, so every level's d4est_mesh_data_t is uploaded through d4est_b200_get_mesh and
+ * mg_data->coarse_grid_refinement afterwards holds, per level, which coarse element came from
+ * which fine elements (hrefine 0 / 1 / 2, d4est_solver_multigrid.h:12-18).
+ * Valid where fcns->apply_lhs is the SIPG Laplacian of ctx->flux_data and the smoother is
+ * mg_smoother_cheby with mg_bottom_solver_cg or mg_bottom_solver_cheby.                  */
+#define D4EST_B200_MAX_LEVELS 32
+typedef struct
+{
+  d4est_solver_multigrid_t *mg_data;
+  d4est_b200_ctx_t *ctx;
+  void (*user_setup_fcn) (d4est_krylov_pc_t *);
+  d4b_mg_t *mg;                            /* NULL until the first apply     */
+  int n_levels;
+  d4b_mesh_t *level_mesh[D4EST_B200_MAX_LEVELS];
+  int level_elements[D4EST_B200_MAX_LEVELS];
+  int top_elements, top_nodes;
+  long builds, applies, vcycles;           /* statistics                     */
+} d4est_b200_pc_multigrid_data_t;
+
+d4est_krylov_pc_t *d4est_b200_pc_multigrid_create (d4est_solver_multigrid_t * mg_data,
+                                                   d4est_b200_ctx_t * ctx,
+                                                   void (*user_setup_fcn) (d4est_krylov_pc_t *));
+void d4est_b200_pc_multigrid_destroy (d4est_krylov_pc_t * kpc);
 
 #endif

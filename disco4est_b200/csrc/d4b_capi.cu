@@ -97,6 +97,77 @@ void apply_impl(d4b_mesh *m, const double *u, double *Au, int stiffness_only) {
 
 extern "C" void d4b_apply(d4b_mesh_t *m, const double *u, double *Au) { apply_impl(m, u, Au, 0); }
 extern "C" void d4b_apply_stiffness(d4b_mesh_t *m, const double *u, double *Au) { apply_impl(m, u, Au, 1); }
+// ---- volume quadrature operators ------------------------------------------------------
+namespace {
+// device view of a host-or-device array of n doubles (temporary device copy for host data)
+struct DevIn {
+  const double *p = nullptr;
+  double *tmp = nullptr;
+  DevIn(d4b_mesh *m, const double *x, int64_t n) {
+    if (!x) return;
+    if (is_device_ptr(x)) { p = x; return; }
+    D4B_CUDA(cudaMalloc(&tmp, (size_t)n * sizeof(double)));
+    D4B_CUDA(cudaMemcpyAsync(tmp, x, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, m->stream));
+    p = tmp;
+  }
+  ~DevIn() { if (tmp) cudaFree(tmp); }
+};
+struct DevOut {
+  double *p = nullptr, *tmp = nullptr, *host = nullptr;
+  int64_t n = 0;
+  DevOut(d4b_mesh *, double *x, int64_t n_) : n(n_) {
+    if (is_device_ptr(x)) { p = x; return; }
+    D4B_CUDA(cudaMalloc(&tmp, (size_t)n * sizeof(double)));
+    p = tmp; host = x;
+  }
+  void finish(d4b_mesh *m) {
+    if (tmp) D4B_CUDA(cudaMemcpyAsync(host, tmp, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, m->stream));
+    if (tmp) D4B_CUDA(cudaStreamSynchronize(m->stream));
+  }
+  ~DevOut() { if (tmp) cudaFree(tmp); }
+};
+}  // namespace
+
+extern "C" void d4b_interp_to_quad(d4b_mesh_t *m, const double *u, double *u_quad) {
+  D4B_CHECK(m && u && u_quad, "d4b_interp_to_quad: NULL argument");
+  DevIn in(m, u, m->local_nodes);
+  DevOut out(m, u_quad, m->local_nodes_quad);
+  d4b_launch_quad_op(m, 0, in.p, nullptr, out.p);
+  out.finish(m);
+  if (in.tmp) D4B_CUDA(cudaStreamSynchronize(m->stream));
+}
+
+extern "C" void d4b_apply_galerkin(d4b_mesh_t *m, const double *in_quad, const double *jac_quad, double *out) {
+  D4B_CHECK(m && in_quad && out, "d4b_apply_galerkin: NULL argument");
+  DevIn in(m, in_quad, m->local_nodes_quad), jac(m, jac_quad, m->local_nodes_quad);
+  DevOut o(m, out, m->local_nodes);
+  d4b_launch_quad_op(m, 1, in.p, jac.p, o.p);
+  o.finish(m);
+  if (in.tmp || jac.tmp) D4B_CUDA(cudaStreamSynchronize(m->stream));
+}
+
+extern "C" void d4b_apply_mass(d4b_mesh_t *m, const double *x, const double *jac_quad, double *out) {
+  D4B_CHECK(m && x && jac_quad && out, "d4b_apply_mass: NULL argument");
+  DevIn in(m, x, m->local_nodes), jac(m, jac_quad, m->local_nodes_quad);
+  DevOut o(m, out, m->local_nodes);
+  d4b_launch_quad_op(m, 2, in.p, jac.p, o.p);
+  o.finish(m);
+  if (in.tmp || jac.tmp) D4B_CUDA(cudaStreamSynchronize(m->stream));
+}
+
+extern "C" void d4b_mesh_set_mass_diag(d4b_mesh_t *m, const double *jac_quad) {
+  D4B_CHECK(m, "d4b_mesh_set_mass_diag: NULL mesh");
+  D4B_CUDA(cudaStreamSynchronize(m->stream));
+  if (!jac_quad) {
+    if (m->d_W) { cudaFree(m->d_W); m->d_W = nullptr; m->device_bytes -= m->local_nodes_quad * (int64_t)sizeof(double); }
+    return;
+  }
+  if (!m->d_W) m->d_W = d4b_dev_alloc<double>(m, (size_t)m->local_nodes_quad);
+  DevIn jac(m, jac_quad, m->local_nodes_quad);
+  d4b_launch_quad_op(m, 3, nullptr, jac.p, m->d_W);
+  D4B_CUDA(cudaStreamSynchronize(m->stream));
+}
+
 extern "C" void d4b_sync(d4b_mesh_t *m) { D4B_CUDA(cudaStreamSynchronize(m->stream)); }
 extern "C" void d4b_set_stream(d4b_mesh_t *m, void *cuda_stream) {
   D4B_CUDA(cudaStreamSynchronize(m->stream));

@@ -54,11 +54,20 @@ __constant__ FastTab c_tab[9];   // indexed by N
 constexpr int kOwn = 1 << 6;     // this element owns the face record
 
 // what to do with a finished entry of A u (D4bEpilogue, d4b_internal.h)
-__device__ __forceinline__ void store_result(const D4bEpilogue &e, double *Au, int64_t i, double s) {
+struct EpiCoef { double alpha, beta; };
+// the recurrence coefficients of this launch: kernel arguments, or -- when the spectrum
+// estimate never left the device (d4b_solver.cu) -- a pair in device memory
+__device__ __forceinline__ EpiCoef epi_coef(const D4bEpilogue &e) {
+  EpiCoef c;
+  if (e.mode == 1 && e.coef) { c.alpha = e.coef[0]; c.beta = e.coef[1]; }
+  else { c.alpha = e.alpha; c.beta = e.beta; }
+  return c;
+}
+__device__ __forceinline__ void store_result(const D4bEpilogue &e, const EpiCoef &c, double *Au, int64_t i, double s) {
   if (e.mode == 0) { Au[i] = s; return; }
   if (e.mode == 2) { Au[i] = e.rhs[i] - s; return; }
-  const double r = (e.rhs[i] - s) * e.alpha;
-  const double pn = r + e.beta * e.p[i];
+  const double r = (e.rhs[i] - s) * c.alpha;
+  const double pn = r + c.beta * e.p[i];
   e.p[i] = pn;
   e.u[i] += pn;
 }
@@ -76,6 +85,8 @@ struct FastArgs {
   const double *uh;             // Gauss-collocated input
   double *Au;
   D4bEpilogue epi;
+  const double *W;              // MASS kernels: weighted diagonal at the quadrature points (d4b_mesh_set_mass_diag)
+  const int64_t *quad_stride;
 };
 
 template <int N>
@@ -160,7 +171,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) interp_kernel(const int32_t *
 }
 
 // ---- kernel 2: the apply in the Gauss basis ------------------------------------
-template <int N>
+template <int N, bool MASS>
 __global__ void __launch_bounds__(Cfg<N>::THREADS) fast_apply_kernel(FastArgs a) {
   using C = Cfg<N>;
   constexpr int NN = C::NN, N3 = C::N3;
@@ -259,9 +270,11 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) fast_apply_kernel(FastArgs a)
       V2[idx] = G01 * gr + G11 * gs + G12 * gt[c];
       ft[c] = G02 * gr + G12 * gs + G22 * gt[c];
     }
+    // mass-type diagonal: in the Gauss basis V^T diag(W) V u is point-wise, r += W uh
+    const double *Wd = MASS ? a.W + a.quad_stride[a.elem[ei]] + lt : nullptr;
 #pragma unroll
     for (int c = 0; c < N; ++c) {
-      double s = 0.;
+      double s = MASS ? Wd[NN * c] * V0[lt + NN * c] : 0.;
 #pragma unroll
       for (int i = 0; i < N; ++i) s += T.Dg[i][c] * ft[i];
       V0[lt + NN * c] = s;
@@ -449,6 +462,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) fast_apply_kernel(FastArgs a)
   __syncthreads();
   if (active) {   // T-orientation: I^T along c, write Au
     double l[N];
+    const EpiCoef ec = epi_coef(a.epi);
 #pragma unroll
     for (int i = 0; i < N; ++i) l[i] = V0[lt + NN * i];
 #pragma unroll
@@ -456,7 +470,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) fast_apply_kernel(FastArgs a)
       double s = 0.;
 #pragma unroll
       for (int i = 0; i < N; ++i) s += T.I[i][c] * l[i];
-      store_result(a.epi, a.Au, ns + lt + NN * c, s);
+      store_result(a.epi, ec, a.Au, ns + lt + NN * c, s);
     }
   }
 }
@@ -474,14 +488,17 @@ void launch_flat(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, 
   a.meta = static_cast<const FaceMeta *>(cls.d_face_meta);
   a.uh = m->d_uhat; a.Au = d_Au; a.epi = m->epi;
   size_t smem = (size_t)C::EPB * C::SH_PER_ELEM * sizeof(double);
+  a.W = m->d_W; a.quad_stride = m->d_quad_stride;
   static bool configured = false;
   if (!configured) {
-    D4B_CUDA(cudaFuncSetAttribute(flat_apply_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    D4B_CUDA(cudaFuncSetAttribute(flat_apply_kernel<N, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    D4B_CUDA(cudaFuncSetAttribute(flat_apply_kernel<N, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = true;
   }
   a.prefetch = getenv("D4B_PREFETCH") ? atoi(getenv("D4B_PREFETCH")) : 2;
   int grid = (last - first + C::EPB - 1) / C::EPB;
-  flat_apply_kernel<N><<<grid, C::THREADS, smem, m->stream>>>(a);
+  if (m->d_W) flat_apply_kernel<N, true><<<grid, C::THREADS, smem, m->stream>>>(a);
+  else flat_apply_kernel<N, false><<<grid, C::THREADS, smem, m->stream>>>(a);
   D4B_CUDA(cudaGetLastError());
 }
 
@@ -512,13 +529,16 @@ void launch_fast(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, 
   a.face_rec = cls.d_face_rec; a.face_nbr = cls.d_face_nbr; a.face_code = cls.d_face_code;
   a.uh = m->d_uhat; a.Au = d_Au; a.epi = m->epi;
   size_t smem = (size_t)C::EPB * C::SH_PER_ELEM * sizeof(double);
+  a.W = m->d_W; a.quad_stride = m->d_quad_stride;
   static bool configured = false;
   if (!configured) {
-    D4B_CUDA(cudaFuncSetAttribute(fast_apply_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    D4B_CUDA(cudaFuncSetAttribute(fast_apply_kernel<N, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    D4B_CUDA(cudaFuncSetAttribute(fast_apply_kernel<N, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = true;
   }
   int grid = (last - first + C::EPB - 1) / C::EPB;
-  fast_apply_kernel<N><<<grid, C::THREADS, smem, m->stream>>>(a);
+  if (m->d_W) fast_apply_kernel<N, true><<<grid, C::THREADS, smem, m->stream>>>(a);
+  else fast_apply_kernel<N, false><<<grid, C::THREADS, smem, m->stream>>>(a);
   D4B_CUDA(cudaGetLastError());
 }
 

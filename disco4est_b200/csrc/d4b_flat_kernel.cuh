@@ -36,6 +36,8 @@ struct FlatArgs {
   double *Au;
   D4bEpilogue epi;
   int prefetch;                 // 1: bulk-prefetch the block's volume metric into L2 at kernel start
+  const double *W;              // MASS kernels: weighted diagonal at the quadrature points (d4b_mesh_set_mass_diag)
+  const int64_t *quad_stride;
 };
 
 // ask the L2 for `bytes` (multiple of 16) at a 16-byte aligned global address
@@ -136,7 +138,7 @@ __device__ __forceinline__ void flat_face(const FlatArgs &a, const FastTab &T, c
   vd = -wxy * cm * Amn * du;
 }
 
-template <int N>
+template <int N, bool MASS>
 __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) flat_apply_kernel(FlatArgs a) {
   using C = FlatCfg<N>;
   constexpr int NN = C::NN, N3 = C::N3;
@@ -268,9 +270,12 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) f
     }
     const double ve0 = FB[(4 * 2 + 0) * NN + lt], vd0 = FB[(4 * 2 + 1) * NN + lt];
     const double ve1 = FB[(5 * 2 + 0) * NN + lt], vd1 = FB[(5 * 2 + 1) * NN + lt];
+    // mass-type diagonal: in the Gauss basis V^T diag(W) V u is point-wise, r += W uh
+    const double *Wd = MASS ? a.W + a.quad_stride[a.elem[ei]] + lt : nullptr;
 #pragma unroll
     for (int c = 0; c < N; ++c) {
       double s = T.e[0][c] * ve0 + T.d[0][c] * vd0 + T.e[1][c] * ve1 + T.d[1][c] * vd1;
+      if (MASS) s += Wd[NN * c] * V0[vix<N>(lx, ly, c)];
 #pragma unroll
       for (int i = 0; i < N; ++i) s += T.Dg[i][c] * ft[i];
       V0[vix<N>(lx, ly, c)] = s;
@@ -329,6 +334,7 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) f
   block_sync<C::THREADS>();
   if (active) {   // T-orientation: I^T along c, write Au
     double l[N];
+    const EpiCoef ec = epi_coef(a.epi);
 #pragma unroll
     for (int i = 0; i < N; ++i) l[i] = V0[vix<N>(lx, ly, i)];
 #pragma unroll
@@ -336,7 +342,7 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) f
       double s = 0.;
 #pragma unroll
       for (int i = 0; i < N; ++i) s += T.I[i][c] * l[i];
-      store_result(a.epi, a.Au, ns + lt + NN * c, s);
+      store_result(a.epi, ec, a.Au, ns + lt + NN * c, s);
     }
   }
 }

@@ -25,6 +25,7 @@ struct GenericArgs {
   const int32_t *ghost_deg, *ghost_deg_quad;
   const int64_t *ghost_nodal_stride;
   const double *G;
+  const double *W;              // optional weighted diagonal at the quadrature points, or NULL
   int64_t local_nodes_quad;
   const int32_t *elem_side, *elem_sub;
   const int32_t *side_faces_m, *side_faces_p, *side_f_m, *side_f_p, *side_e_m, *side_e_p,
@@ -177,6 +178,22 @@ __global__ void __launch_bounds__(128) generic_apply_kernel(GenericArgs a) {
     __syncthreads();
   }
 
+  // ---- mass-type diagonal: + V^T diag(W) V u (d4est_quadrature_apply_mass_matrix with
+  // jac := J f, d4est_quadrature.c:385-477, as apply_fofufofvlilj calls it :593-774)
+  if (a.W && !a.stiffness_only) {
+    const double *W = a.W + a.quad_stride[e];
+    sweep3(s_t1, s_u, E, N, 1, Nq, N, 0, N, N, N);
+    sweep3(s_t2, s_t1, E, N, 1, Nq, N, 1, Nq, N, N);
+    sweep3(s_g, s_t2, E, N, 1, Nq, N, 2, Nq, Nq, N);
+    for (int k = threadIdx.x; k < q3; k += blockDim.x) s_g[k] *= W[k];
+    __syncthreads();
+    sweep3(s_t2, s_g, E, 1, N, N, Nq, 2, Nq, Nq, Nq);
+    sweep3(s_t1, s_t2, E, 1, N, N, Nq, 1, Nq, Nq, N);
+    sweep3(s_a, s_t1, E, 1, N, N, Nq, 0, Nq, N, N);
+    for (int i = threadIdx.x; i < n3; i += blockDim.x) s_out[i] += s_a[i];
+    __syncthreads();
+  }
+
   // ---- faces
   if (!a.stiffness_only) {
     // scratch carved from the volume buffers (all free now)
@@ -299,7 +316,79 @@ __global__ void __launch_bounds__(128) generic_apply_kernel(GenericArgs a) {
   for (int i = threadIdx.x; i < n3; i += blockDim.x) oe[i] = s_out[i];
 }
 
+// ---- volume quadrature operators, one CTA per element, any (deg, deg_quad) ----------
+//   mode 0: out_quad = V in                      d4est_quadrature_interpolate            d4est_quadrature.c:966-1016
+//   mode 1: out = V^T (w jac in_quad)            d4est_quadrature_apply_galerkin_integral :142-213
+//   mode 2: out = V^T diag(w jac) V in           d4est_quadrature_apply_mass_matrix       :385-477
+//   mode 3: out_quad = w jac                     (set-up of the fused diagonal)
+struct QuadArgs {
+  const D4bTables *tab;
+  const double *tabdata;
+  const int32_t *deg, *deg_quad;
+  const int64_t *nodal_stride, *quad_stride;
+  int mode, mQ;
+  const double *in, *jac;
+  double *out;
+};
+
+__global__ void __launch_bounds__(128) quad_ops_kernel(QuadArgs a) {
+  extern __shared__ double smem[];
+  const int e = blockIdx.x;
+  const int p = a.deg[e], q = a.deg_quad[e];
+  const int N = p + 1, Nq = q + 1, n3 = N * N * N, q3 = Nq * Nq * Nq;
+  const int64_t ns = a.nodal_stride[e], qs = a.quad_stride[e];
+  const int m3 = a.mQ * a.mQ * a.mQ;
+  double *s0 = smem, *s1 = s0 + m3, *s2 = s1 + m3;
+  const double *E = a.tabdata + a.tab->e_off[((p - 1) * D4B_MAXNQ + (q - 1)) * 3];
+  const double *w = a.tabdata + a.tab->w_off[q - 1];
+  if (a.mode == 3) {
+    for (int k = threadIdx.x; k < q3; k += blockDim.x) {
+      const int ia = k % Nq, ib = (k / Nq) % Nq, ic = k / (Nq * Nq);
+      a.out[qs + k] = w[ic] * w[ib] * w[ia] * a.jac[qs + k];
+    }
+    return;
+  }
+  if (a.mode == 0 || a.mode == 2) {
+    for (int i = threadIdx.x; i < n3; i += blockDim.x) s0[i] = a.in[ns + i];
+    __syncthreads();
+    sweep3(s1, s0, E, N, 1, Nq, N, 0, N, N, N);
+    sweep3(s2, s1, E, N, 1, Nq, N, 1, Nq, N, N);
+    sweep3(s0, s2, E, N, 1, Nq, N, 2, Nq, Nq, N);
+    if (a.mode == 0) {
+      for (int k = threadIdx.x; k < q3; k += blockDim.x) a.out[qs + k] = s0[k];
+      return;
+    }
+  } else {
+    for (int k = threadIdx.x; k < q3; k += blockDim.x) s0[k] = a.in[qs + k];
+    __syncthreads();
+  }
+  for (int k = threadIdx.x; k < q3; k += blockDim.x) {
+    const int ia = k % Nq, ib = (k / Nq) % Nq, ic = k / (Nq * Nq);
+    s0[k] *= w[ic] * w[ib] * w[ia] * (a.jac ? a.jac[qs + k] : 1.);
+  }
+  __syncthreads();
+  sweep3(s1, s0, E, 1, N, N, Nq, 2, Nq, Nq, Nq);
+  sweep3(s2, s1, E, 1, N, N, Nq, 1, Nq, Nq, N);
+  sweep3(s0, s2, E, 1, N, N, Nq, 0, Nq, N, N);
+  for (int i = threadIdx.x; i < n3; i += blockDim.x) a.out[ns + i] = s0[i];
+}
+
 }  // namespace
+
+void d4b_launch_quad_op(d4b_mesh *m, int mode, const double *d_in, const double *d_jac, double *d_out) {
+  if (m->n_local == 0) return;
+  QuadArgs a;
+  a.tab = m->d_tab; a.tabdata = m->d_tabdata;
+  a.deg = m->d_deg; a.deg_quad = m->d_deg_quad;
+  a.nodal_stride = m->d_nodal_stride; a.quad_stride = m->d_quad_stride;
+  a.mode = mode;
+  a.mQ = m->max_deg_quad > m->max_deg ? m->max_deg_quad + 1 : m->max_deg + 1;
+  a.in = d_in; a.jac = d_jac; a.out = d_out;
+  const size_t smem = (size_t)3 * a.mQ * a.mQ * a.mQ * sizeof(double);
+  D4B_CHECK(smem <= 48 * 1024, "quadrature operators: %zu bytes of shared memory", smem);
+  quad_ops_kernel<<<m->n_local, 128, smem, m->stream>>>(a);
+  D4B_CUDA(cudaGetLastError());
+}
 
 void d4b_launch_generic(d4b_mesh *m, const double *d_u, double *d_Au, int stiffness_only) {
   bool force_all = (stiffness_only != 0) || (m->fast.empty());
@@ -311,7 +400,7 @@ void d4b_launch_generic(d4b_mesh *m, const double *d_u, double *d_Au, int stiffn
   a.nodal_stride = m->d_nodal_stride; a.quad_stride = m->d_quad_stride;
   a.ghost_deg = m->d_ghost_deg; a.ghost_deg_quad = m->d_ghost_deg_quad;
   a.ghost_nodal_stride = m->d_ghost_nodal_stride;
-  a.G = m->d_G; a.local_nodes_quad = m->local_nodes_quad;
+  a.G = m->d_G; a.W = m->d_W; a.local_nodes_quad = m->local_nodes_quad;
   a.elem_side = m->d_elem_side; a.elem_sub = m->d_elem_sub;
   a.side_faces_m = m->d_side_faces_m; a.side_faces_p = m->d_side_faces_p;
   a.side_f_m = m->d_side_f_m; a.side_f_p = m->d_side_f_p;

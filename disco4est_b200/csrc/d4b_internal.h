@@ -69,6 +69,7 @@ struct D4bEpilogue {
   const double *rhs = nullptr;
   double *p = nullptr, *u = nullptr;
   double alpha = 0., beta = 0.;
+  const double *coef = nullptr;   // mode 1: {alpha, beta} in device memory instead of the two arguments
 };
 
 // halo exchange with one neighbour rank; offsets / counts in doubles
@@ -100,6 +101,9 @@ struct d4b_mesh {
   // volume metric: G[c][quad point], c = 0..5 <-> (00,01,02,11,12,22),
   // G_{l'l} = w_r w_s w_t J sum_k rst[l][k] rst[l'][k]
   double *d_G = nullptr;
+  // optional mass-type diagonal W = w_r w_s w_t jac at the quadrature points (d4b_mesh_set_mass_diag):
+  // every apply adds V^T diag(W) V u
+  double *d_W = nullptr;
   // per element-face: flux side record and position inside it
   int32_t *d_elem_side = nullptr;   // [6*n_local]
   int32_t *d_elem_sub = nullptr;    // [6*n_local]
@@ -155,6 +159,9 @@ T *d4b_dev_upload(d4b_mesh *m, const T *h, size_t n);
 
 // kernels / launchers
 void d4b_launch_generic(d4b_mesh *m, const double *d_u, double *d_Au, int stiffness_only);
+// volume quadrature operators on device pointers (d4b_generic.cu): mode 0 interpolate,
+// 1 Galerkin integral, 2 mass matrix, 3 out_quad = w jac
+void d4b_launch_quad_op(d4b_mesh *m, int mode, const double *d_in, const double *d_jac, double *d_out);
 // the whole apply on device pointers (halo exchange, fast kernels with m->epi, generic kernel)
 void d4b_apply_device(d4b_mesh *m, const double *d_u, double *d_Au);
 void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *desc, const std::vector<double> &mortar,
@@ -163,6 +170,14 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *desc, const std::vector<
 // part 0: uh of local elements; 1: interior elements; 2 (after the halo exchange): uh of
 // ghost elements + elements with a ghost neighbour
 void d4b_launch_fast(d4b_mesh *m, const double *d_u, double *d_Au, int part);
+
+// One smoothing of a multigrid level on device vectors (cg_eigs estimate when asked,
+// Chebyshev sweeps, r = rhs - A u), enqueued without any host synchronisation; the estimate
+// stays on the device and is re-used by later calls with compute_eigs == false (d4b_solver.cu)
+// d_eig: one double of device memory owned by the caller (the level's estimate)
+void d4b_smooth_async(d4b_mesh *m, double *du, const double *drhs, double *dr, const d4b_cheby_params_t &c,
+                      bool compute_eigs, double *d_eig);
+void d4b_dot_async(d4b_mesh *m, const double *x, const double *y, int64_t n, double *d_out);
 
 // halo exchange (d4b_comm.cu)
 void d4b_comm_setup(d4b_mesh *m, const d4b_mesh_desc_t *d);

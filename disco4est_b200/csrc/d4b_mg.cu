@@ -23,8 +23,9 @@ struct d4b_mg {
   double *d_P = nullptr;                                 // 1-D prolongation tables
   int32_t *d_P_off = nullptr;                            // ((degH-1)*7 + (degh-1))*3 + half -> offset
   d4b_mg_desc_t prm;
-  std::vector<double> eigs;
-  double bottom_eig = 0.;
+  double *d_eigs = nullptr;      // [n_levels + 1] smoother estimates per level, then the bottom solver's
+  double *d_scal = nullptr;      // bottom CG scalars (BcgScal)
+  double *h_scal = nullptr;      // pinned
   int vcycle_num_finished = 0;
 };
 
@@ -135,10 +136,6 @@ void transfer(d4b_mg *g, int dir, int accumulate, int lc, const double *in, doub
   D4B_CUDA(cudaGetLastError());
 }
 
-__global__ void copy2_k(const double *__restrict__ a, double *__restrict__ b, int64_t n) {
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-    b[i] = a[i];
-}
 __global__ void resid_k(const double *__restrict__ rhs, const double *__restrict__ Au, double *__restrict__ r,
                         int64_t n) {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
@@ -151,38 +148,56 @@ __global__ void resid_init_k(const double *__restrict__ rhs, const double *__res
     r[i] = v; d[i] = v;
   }
 }
-__global__ void cg_step_k(double alpha, const double *__restrict__ d, const double *__restrict__ Au,
-                          double *__restrict__ u, double *__restrict__ r, int64_t n) {
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-    u[i] += alpha * d[i];
-    r[i] -= alpha * Au[i];
-  }
-}
-__global__ void xpby_k(const double *__restrict__ x, double b, double *__restrict__ y, int64_t n) {
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-    y[i] = x[i] + b * y[i];
-}
 int grid_for(int64_t n) {
   int64_t b = (n + 255) / 256;
   return (int)(b < 148 * 8 ? (b > 0 ? b : 1) : 148 * 8);
 }
 
-// Chebyshev smoother of one level, d4est_solver_multigrid_smoother_cheby.c:264-376
+// Chebyshev smoother of one level, d4est_solver_multigrid_smoother_cheby.c:264-376; the
+// estimate of the level lives in g->d_eigs[level] and never visits the host
 void smooth(d4b_mg *g, int level, double *u, const double *rhs, double *r, bool compute_eigs) {
-  const d4b_cheby_params_t &c = g->prm.smoother;
-  d4b_mesh *m = g->mesh[level];
-  if (compute_eigs) {
-    // with a zero guess the estimate runs on a scratch vector and u is untouched (:281-305)
-    double e = d4b_cg_eigs(m, u, rhs, c.cheby_eigs_cg_imax, c.cheby_use_new_cg_eigs, c.cheby_use_zero_guess_for_eigs);
-    g->eigs[level] = e * c.cheby_eigs_max_multiplier;
-  }
-  // (:322-349 re-runs cg_eigs on a zero vector into a dummy when the estimate is
-  //  re-used with the zero-guess option; it changes no state and is skipped here)
-  const double lmax = g->eigs[level], lmin = lmax / c.cheby_eigs_lmax_lmin_ratio;
-  d4b_cheby_smooth(m, u, rhs, r, c.cheby_imax, lmin, lmax);
+  d4b_smooth_async(g->mesh[level], u, rhs, r, g->prm.smoother, compute_eigs, g->d_eigs + level);
 }
 
-// d4est_solver_multigrid_bottom_solver_cg.c:48-200
+// Bottom CG, d4est_solver_multigrid_bottom_solver_cg.c:48-200.  Its stopping test
+// (delta_new > atol^2 + delta_0 rtol^2, :118) is evaluated on the device: every iteration is
+// enqueued behind a `done` flag the vector kernels honour, and the host only looks at the
+// flag once per chunk of iterations.  Same arithmetic and same iteration count as the
+// reference loop.
+struct BcgScal { double delta_new, dAd, delta_0, alpha, beta, rr; int32_t done, iters; };
+constexpr int kBcgChunk = 16;
+
+__global__ void bcg_begin_k(BcgScal *s, double atol, double rtol, int imax) {
+  s->delta_new = s->rr; s->delta_0 = s->rr; s->iters = 0;
+  s->done = !(imax > 0 && s->delta_new > atol * atol + s->delta_0 * rtol * rtol);
+}
+__global__ void bcg_alpha_k(BcgScal *s) { if (!s->done) s->alpha = s->delta_new / s->dAd; }
+__global__ void bcg_beta_k(BcgScal *s, double atol, double rtol, int imax) {
+  if (s->done) return;
+  s->beta = s->rr / s->delta_new;
+  s->delta_new = s->rr;
+  s->iters++;
+  s->done = !(s->iters < imax && s->delta_new > atol * atol + s->delta_0 * rtol * rtol);
+  if (s->done) s->done = 2;   // finished by this iteration: its d-update still runs, like the reference's
+}
+__global__ void bcg_step_k(const BcgScal *__restrict__ s, const double *__restrict__ d, const double *__restrict__ Au,
+                           double *__restrict__ u, double *__restrict__ r, int64_t n) {
+  if (s->done) return;
+  const double alpha = s->alpha;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    u[i] += alpha * d[i];
+    r[i] -= alpha * Au[i];
+  }
+}
+__global__ void bcg_xpby_k(const BcgScal *__restrict__ s, const double *__restrict__ r, double *__restrict__ d,
+                           int64_t n) {
+  if (s->done == 1) return;
+  const double beta = s->beta;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    d[i] = r[i] + beta * d[i];
+}
+__global__ void bcg_settle_k(BcgScal *s) { if (s->done == 2) s->done = 1; }
+
 void bottom_cg(d4b_mg *g, double *u, const double *rhs, double *r) {
   d4b_mesh *m = g->mesh[0];
   const int64_t n = m->local_nodes;
@@ -190,30 +205,43 @@ void bottom_cg(d4b_mg *g, double *u, const double *rhs, double *r) {
   double *Au = m->d_Au_stage;
   if (!m->d_work[3]) m->d_work[3] = d4b_dev_alloc<double>(m, (size_t)n);
   double *d = m->d_work[3];
+  BcgScal *s = reinterpret_cast<BcgScal *>(g->d_scal);
+  const double rtol = g->prm.bottom_rtol, atol = g->prm.bottom_atol;
+  const int imax = g->prm.bottom_iter;
   d4b_apply(m, u, Au);
   resid_init_k<<<gr, 256, 0, m->stream>>>(rhs, Au, r, d, n);
-  double delta_new = d4b_vec_dot(m, r, r, n);
-  const double delta_0 = delta_new, rtol = g->prm.bottom_rtol, atol = g->prm.bottom_atol;
-  for (int i = 0; i < g->prm.bottom_iter && (delta_new > atol * atol + delta_0 * rtol * rtol); ++i) {
-    d4b_apply(m, d, Au);
-    const double d_dot_Au = d4b_vec_dot(m, d, Au, n);
-    const double alpha = delta_new / d_dot_Au;
-    cg_step_k<<<gr, 256, 0, m->stream>>>(alpha, d, Au, u, r, n);
-    const double delta_old = delta_new;
-    delta_new = d4b_vec_dot(m, r, r, n);
-    xpby_k<<<gr, 256, 0, m->stream>>>(r, delta_new / delta_old, d, n);
+  d4b_dot_async(m, r, r, n, &s->rr);
+  bcg_begin_k<<<1, 1, 0, m->stream>>>(s, atol, rtol, imax);
+  for (int i0 = 0; i0 < imax; i0 += kBcgChunk) {
+    for (int i = i0; i < imax && i < i0 + kBcgChunk; ++i) {
+      d4b_apply(m, d, Au);
+      d4b_dot_async(m, d, Au, n, &s->dAd);
+      bcg_alpha_k<<<1, 1, 0, m->stream>>>(s);
+      bcg_step_k<<<gr, 256, 0, m->stream>>>(s, d, Au, u, r, n);
+      d4b_dot_async(m, r, r, n, &s->rr);
+      bcg_beta_k<<<1, 1, 0, m->stream>>>(s, atol, rtol, imax);
+      bcg_xpby_k<<<gr, 256, 0, m->stream>>>(s, r, d, n);
+      bcg_settle_k<<<1, 1, 0, m->stream>>>(s);
+    }
+    BcgScal *h = reinterpret_cast<BcgScal *>(g->h_scal);
+    D4B_CUDA(cudaMemcpyAsync(h, s, sizeof(BcgScal), cudaMemcpyDeviceToHost, m->stream));
+    D4B_CUDA(cudaStreamSynchronize(m->stream));
+    if (h->done) break;
   }
 }
 
 // d4est_solver_multigrid_bottom_solver_cheby.c:60-115
 void bottom_cheby(d4b_mg *g, double *u, const double *rhs, double *r) {
-  const d4b_cheby_params_t &c = g->prm.bottom_cheby;
-  d4b_mesh *m = g->mesh[0];
-  g->bottom_eig = d4b_cg_eigs(m, u, rhs, c.cheby_eigs_cg_imax, c.cheby_use_new_cg_eigs, 0) * c.cheby_eigs_max_multiplier;
-  d4b_cheby_smooth(m, u, rhs, r, c.cheby_imax, g->bottom_eig / c.cheby_eigs_lmax_lmin_ratio, g->bottom_eig);
+  d4b_cheby_params_t c = g->prm.bottom_cheby;
+  c.cheby_use_zero_guess_for_eigs = 0;
+  d4b_smooth_async(g->mesh[0], u, rhs, r, c, true, g->d_eigs + g->n_levels);
 }
 
-// one V-cycle on device pointers; returns the global squared residual of the top level
+// one V-cycle on device pointers; returns the global squared residual of the top level.
+// Everything between the first smoother kernel and the final residual norm is enqueued on
+// one stream without a host synchronisation (a CG bottom solver polls its flag once per
+// kBcgChunk iterations): while the fine level runs, the host is already queueing the coarse
+// levels, so their launch latencies are hidden.
 double vcycle_device(d4b_mg *g, double *u_top, const double *rhs_top) {
   const int top = g->n_levels - 1;
   const d4b_cheby_params_t &c = g->prm.smoother;
@@ -225,35 +253,40 @@ double vcycle_device(d4b_mg *g, double *u_top, const double *rhs_top) {
   D4B_CHECK(!(c.cheby_use_zero_guess_for_eigs == 1 && c.cheby_eigs_reuse_fromdownvcycle != 1),
             "cheby_use_zero_guess_for_eigs = 1 needs cheby_eigs_reuse_fromdownvcycle = 1 "
             "(d4est_solver_multigrid_smoother_cheby.c:315-320)");
+  // all levels on the top level's stream for the duration of the cycle
+  cudaStream_t s = g->mesh[top]->stream;
+  std::vector<cudaStream_t> saved(g->n_levels);
+  for (int l = 0; l <= top; ++l) {
+    saved[l] = g->mesh[l]->stream;
+    if (saved[l] != s) D4B_CUDA(cudaStreamSynchronize(saved[l]));
+    g->mesh[l]->stream = s;
+  }
   for (int l = top; l > 0; --l) {
     d4b_mesh *m = g->mesh[l];
     double *u = (l == top) ? u_top : g->d_u[l];
     const double *rhs = (l == top) ? rhs_top : g->d_rhs[l];
-    if (l != top) D4B_CUDA(cudaMemsetAsync(u, 0, (size_t)m->local_nodes * sizeof(double), m->stream));
+    if (l != top) D4B_CUDA(cudaMemsetAsync(u, 0, (size_t)m->local_nodes * sizeof(double), s));
     smooth(g, l, u, rhs, g->d_r[l], eigs_down);
     // restricted residual is the coarse right-hand side
-    D4B_CUDA(cudaStreamSynchronize(m->stream));   // levels may use different streams
     transfer(g, 1, 0, l - 1, g->d_r[l], g->d_rhs[l - 1]);
-    D4B_CUDA(cudaStreamSynchronize(m->stream));
   }
   {
     d4b_mesh *m = g->mesh[0];
-    D4B_CUDA(cudaMemsetAsync(g->d_u[0], 0, (size_t)m->local_nodes * sizeof(double), m->stream));
+    D4B_CUDA(cudaMemsetAsync(g->d_u[0], 0, (size_t)m->local_nodes * sizeof(double), s));
     if (g->prm.bottom_solver == 0) bottom_cg(g, g->d_u[0], g->d_rhs[0], g->d_r[0]);
     else bottom_cheby(g, g->d_u[0], g->d_rhs[0], g->d_r[0]);
-    D4B_CUDA(cudaStreamSynchronize(m->stream));
   }
   for (int l = 0; l < top; ++l) {
     const int f = l + 1;
-    d4b_mesh *m = g->mesh[f];
     double *u = (f == top) ? u_top : g->d_u[f];
     const double *rhs = (f == top) ? rhs_top : g->d_rhs[f];
     transfer(g, 0, 1, l, g->d_u[l], u);   // u_fine += P u_coarse
     smooth(g, f, u, rhs, g->d_r[f], eigs_up);
-    D4B_CUDA(cudaStreamSynchronize(m->stream));
   }
   d4b_mesh *mt = g->mesh[top];
-  return d4b_vec_dot(mt, g->d_r[top], g->d_r[top], mt->local_nodes);
+  const double r2 = d4b_vec_dot(mt, g->d_r[top], g->d_r[top], mt->local_nodes);   // synchronises
+  for (int l = 0; l <= top; ++l) g->mesh[l]->stream = saved[l];
+  return r2;
 }
 
 struct TopVectors {
@@ -296,7 +329,15 @@ extern "C" d4b_mg_t *d4b_mg_create(const d4b_mg_desc_t *desc) {
   d4b_mg *g = new d4b_mg();
   g->n_levels = desc->n_levels;
   g->prm = *desc;
-  g->eigs.assign(desc->n_levels, 0.);
+  {
+    d4b_mesh *mt = desc->meshes[desc->n_levels - 1];
+    D4B_CHECK(mt, "d4b_mg_create: the top level has no mesh");
+    g->d_eigs = d4b_dev_alloc<double>(mt, (size_t)desc->n_levels + 1);
+    g->d_scal = d4b_dev_alloc<double>(mt, 16);
+    D4B_CUDA(cudaMemset(g->d_eigs, 0, ((size_t)desc->n_levels + 1) * sizeof(double)));
+    D4B_CUDA(cudaMemset(g->d_scal, 0, 16 * sizeof(double)));
+    D4B_CUDA(cudaMallocHost(&g->h_scal, 64 * sizeof(double)));
+  }
   for (int l = 0; l < desc->n_levels; ++l) {
     D4B_CHECK(desc->meshes[l], "d4b_mg_create: level %d has no mesh", l);
     g->mesh.push_back(desc->meshes[l]);
@@ -361,6 +402,7 @@ extern "C" void d4b_mg_destroy(d4b_mg_t *g) {
   if (g->d_top_u) cudaFree(g->d_top_u);
   if (g->d_top_rhs) cudaFree(g->d_top_rhs);
   cudaFree(g->d_P); cudaFree(g->d_P_off);
+  cudaFree(g->d_eigs); cudaFree(g->d_scal); cudaFreeHost(g->h_scal);
   delete g;
 }
 
@@ -398,7 +440,7 @@ extern "C" int32_t d4b_mg_solve(d4b_mg_t *g, double *u, const double *rhs, doubl
 }
 
 extern "C" void d4b_mg_get_eigs(const d4b_mg_t *g, double *eigs_out) {
-  for (int l = 0; l < g->n_levels; ++l) eigs_out[l] = g->eigs[l];
+  D4B_CUDA(cudaMemcpy(eigs_out, g->d_eigs, (size_t)g->n_levels * sizeof(double), cudaMemcpyDeviceToHost));
 }
 
 namespace {

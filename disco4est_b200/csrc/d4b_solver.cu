@@ -7,6 +7,7 @@
 // Reductions are deterministic: fixed grid, fixed-shape tree, no atomics.
 #include <cmath>
 #include <cstdlib>
+#include <vector>
 #include "d4b_internal.h"
 
 namespace {
@@ -70,14 +71,6 @@ __global__ void residual2_k(const double *__restrict__ rhs, const double *__rest
     r[i] = v; d[i] = v;
   }
 }
-// CG update: u += alpha d ; r -= alpha Au
-__global__ void cg_update_k(double alpha, const double *__restrict__ d, const double *__restrict__ Au,
-                            double *__restrict__ u, double *__restrict__ r, int64_t n) {
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-    u[i] += alpha * d[i];
-    r[i] -= alpha * Au[i];
-  }
-}
 // Chebyshev update: p = alpha (rhs - Au) + beta p ; u += p
 __global__ void cheby_update_k(double alpha, double beta, const double *__restrict__ rhs,
                                const double *__restrict__ Au, double *__restrict__ p,
@@ -126,26 +119,60 @@ extern "C" void d4b_vec_scale(d4b_mesh_t *m, double a, double *x, int64_t n) {
   scale_k<<<grid_for(n), 256, 0, m->stream>>>(a, x, n);
 }
 
-// Gershgorin bounds of the Lanczos tridiagonal, d4est_solver_cg_eigs.c:9-65
-static void gershgorin(int use_new, int i, int64_t n, double a0, double b0, double a1, double b1,
-                       double *mx) {
+namespace {
+
+// Gershgorin bounds of the Lanczos tridiagonal, d4est_solver_cg_eigs.c:9-65.  Runs on the
+// device (one thread) so that the estimate never has to visit the host; the explicitly
+// rounded intrinsics keep nvcc from contracting into FMAs, i.e. the result is the one the
+// reference's scalar code produces from the same dot products.
+__device__ double gershgorin(int use_new, int i, int64_t n, double a0, double b0, double a1, double b1) {
   double diag, off;
   if (!use_new) {
-    if (i != 0 && i < n - 1) { diag = 1. / a1 + b0 / a0; off = fabs(sqrt(b1) / a1) + fabs(sqrt(b0) / a0); }
+    if (i != 0 && i < n - 1) { diag = __dadd_rn(1. / a1, b0 / a0); off = __dadd_rn(fabs(sqrt(b1) / a1), fabs(sqrt(b0) / a0)); }
     else if (i == 0) { diag = 1. / a1; off = sqrt(b1) / a1; }
-    else { diag = 1. / a1 + b0 / a0; off = fabs(sqrt(b0) / a0); }
+    else { diag = __dadd_rn(1. / a1, b0 / a0); off = fabs(sqrt(b0) / a0); }
   } else {
-    if (i != 0) { diag = 1. / a1 + b0 / a0; off = fabs(sqrt(b0) / a0); }
+    if (i != 0) { diag = __dadd_rn(1. / a1, b0 / a0); off = fabs(sqrt(b0) / a0); }
     else { diag = 1. / a1; off = sqrt(b1) / a1; }
   }
-  *mx = diag + off;
+  return __dadd_rn(diag, off);
 }
 
-// cg_eigs keeps its scalars on the device: kernel i reads alpha_i = delta_i / (d.Ad)_i and
-// beta_i = delta_{i+1} / delta_i from the slots earlier reductions filled, so the whole
-// estimate is enqueued without a host round trip; the Gershgorin bounds are evaluated on the
-// host from the 2 imax + 1 scalars at the end.
-constexpr int kScalOff = 1024, kMaxCgIter = 500;   // d_red: [0,1024) partial sums, then delta[], dAd[]
+// d_red layout: [0,1024) partial sums | delta[kMaxCgIter+1] | dAd[kMaxCgIter+1] | eig | coef[2*kMaxCheby]
+constexpr int kScalOff = 1024, kMaxCgIter = 500;
+constexpr int kEigOff = kScalOff + 2 * (kMaxCgIter + 1) + 2, kCoefOff = kEigOff + 2, kMaxCheby = 500;
+static_assert(kCoefOff + 2 * kMaxCheby <= 4096, "d_red is 4096 doubles (d4b_mesh.cu)");
+
+// One thread: (imax > 0) the bound of cg_eigs from its CG scalars, times `mult`, into *eig;
+// then the Chebyshev coefficients {alpha_i, beta_i} for the spectrum [*eig / ratio, *eig]
+// (d4est_solver_multigrid_smoother_cheby.c:100-128) into coef[2 i], coef[2 i + 1].
+__global__ void eig_plan_k(const double *__restrict__ delta, const double *__restrict__ dAd, int imax, int use_new,
+                           int64_t n, double mult, double ratio, int iter, double *__restrict__ eig,
+                           double *__restrict__ coef) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  if (imax > 0) {
+    double alpha = -1., beta = -1., bound = 0.;
+    for (int i = 0; i < imax; ++i) {
+      const double alpha_old = alpha, beta_old = beta;
+      alpha = delta[i] / dAd[i];
+      beta = delta[i + 1] / delta[i];
+      const double t = gershgorin(use_new, i, n, alpha_old, beta_old, alpha, beta);
+      bound = (i > 0) ? fmax(bound, t) : t;
+    }
+    *eig = __dmul_rn(bound, mult);
+  }
+  const double lmax = *eig, lmin = lmax / ratio;
+  const double d = __dmul_rn(__dadd_rn(lmax, lmin), .5), c = __dmul_rn(__dadd_rn(lmax, -lmin), .5);
+  const double cc = __dmul_rn(c, c);
+  double alpha = 0.;
+  for (int i = 0; i < iter; ++i) {
+    if (i == 0) alpha = 1. / d;
+    else if (i == 1) alpha = __dmul_rn(2., d) / __dadd_rn(__dmul_rn(__dmul_rn(2., d), d), -cc);
+    else alpha = 1. / __dadd_rn(d, -(__dmul_rn(alpha, cc) / 4.));
+    coef[2 * i] = alpha;
+    coef[2 * i + 1] = __dadd_rn(__dmul_rn(alpha, d), -1.);
+  }
+}
 
 void dot_to(d4b_mesh *m, const double *x, const double *y, int64_t n, double *d_out) {
   dot_partial<<<kRedBlocks, kRedThreads, 0, m->stream>>>(x, y, n, m->d_red);
@@ -187,25 +214,30 @@ __global__ void xpby_dev_k(const double *__restrict__ r, const double *__restric
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     d[i] = r[i] + beta * d[i];
 }
-
-extern "C" double d4b_cg_eigs(d4b_mesh_t *m, double *u, const double *rhs, int32_t imax,
-                              int32_t use_new, int32_t use_zero_guess) {
-  D4B_CHECK(imax >= 1 && imax <= kMaxCgIter, "d4b_cg_eigs: imax %d out of range", imax);
-  const int64_t n = m->local_nodes;
-  const size_t bytes = (size_t)n * sizeof(double);
-  bool u_dev = is_dev(u), rhs_dev = is_dev(rhs);
-  double *du = u_dev ? u : work(m, 2);
-  const double *drhs = rhs;
-  if (!rhs_dev) {
-    D4B_CUDA(cudaMemcpyAsync(m->d_u_stage, rhs, bytes, cudaMemcpyHostToDevice, m->stream));
-    drhs = m->d_u_stage;
+// Chebyshev update with the coefficients in device memory
+__global__ void cheby_update_dev_k(const double *__restrict__ coef, const double *__restrict__ rhs,
+                                   const double *__restrict__ Au, double *__restrict__ p,
+                                   double *__restrict__ u, int64_t n) {
+  const double alpha = coef[0], beta = coef[1];
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    double r = (rhs[i] - Au[i]) * alpha;
+    double pn = r + beta * p[i];
+    p[i] = pn;
+    u[i] += pn;
   }
-  if (!u_dev) D4B_CUDA(cudaMemcpyAsync(du, u, bytes, cudaMemcpyHostToDevice, m->stream));
+}
+
+// cg_eigs on device vectors, enqueued without a host round trip: kernel i reads
+// alpha_i = delta_i / (d.Ad)_i and beta_i = delta_{i+1} / delta_i from the slots earlier
+// reductions filled.  Leaves delta[0..imax], dAd[0..imax) in d_red.
+void cg_eigs_enqueue(d4b_mesh *m, double *du, const double *drhs, int imax, int use_zero_guess) {
+  D4B_CHECK(imax >= 1 && imax <= kMaxCgIter, "cg_eigs: imax %d out of range", imax);
+  const int64_t n = m->local_nodes;
   if (use_zero_guess) {
     // the reference iterates on a scratch zero vector and leaves u untouched
     // (d4est_solver_multigrid_smoother_cheby.c:281-305)
     du = work(m, 3);
-    D4B_CUDA(cudaMemsetAsync(du, 0, bytes, m->stream));
+    D4B_CUDA(cudaMemsetAsync(du, 0, (size_t)n * sizeof(double), m->stream));
   }
   double *Au = m->d_Au_stage, *d = work(m, 0), *r = work(m, 1);
   double *delta = m->d_red + kScalOff, *dAd = delta + kMaxCgIter + 1;
@@ -221,58 +253,31 @@ extern "C" double d4b_cg_eigs(d4b_mesh_t *m, double *u, const double *rhs, int32
     d4b_comm_allreduce_sum(m, delta + i + 1, 1);
     xpby_dev_k<<<g, 256, 0, m->stream>>>(r, delta + i + 1, delta + i, d, n);
   }
-  D4B_CUDA(cudaMemcpyAsync(m->h_red, delta, (size_t)(2 * kMaxCgIter + 2) * sizeof(double), cudaMemcpyDeviceToHost,
-                           m->stream));
-  if (!u_dev && !use_zero_guess)
-    D4B_CUDA(cudaMemcpyAsync(u, du, bytes, cudaMemcpyDeviceToHost, m->stream));
-  D4B_CUDA(cudaStreamSynchronize(m->stream));
-  const double *h_delta = m->h_red, *h_dAd = m->h_red + kMaxCgIter + 1;
-  double alpha = -1., beta = -1., bound = 0.;
-  for (int i = 0; i < imax; ++i) {
-    const double alpha_old = alpha, beta_old = beta;
-    alpha = h_delta[i] / h_dAd[i];
-    beta = h_delta[i + 1] / h_delta[i];
-    double tmax;
-    gershgorin(use_new, i, n, alpha_old, beta_old, alpha, beta, &tmax);
-    bound = (i > 0) ? fmax(bound, tmax) : tmax;
-  }
-  return bound;
 }
 
-extern "C" void d4b_cheby_smooth(d4b_mesh_t *m, double *u, const double *rhs, double *r, int32_t iter,
-                                 double lmin, double lmax) {
+// Chebyshev recurrence on device vectors.  Coefficients: host arrays (alpha/beta as kernel
+// arguments) or, when d_coef is given, pairs in device memory.
+void cheby_enqueue(d4b_mesh *m, double *du, const double *drhs, double *dr, int iter, const double *h_alpha,
+                   const double *h_beta, const double *d_coef) {
   const int64_t n = m->local_nodes;
-  const size_t bytes = (size_t)n * sizeof(double);
-  bool u_dev = is_dev(u), rhs_dev = is_dev(rhs), r_dev = is_dev(r);
-  double *du = u_dev ? u : work(m, 2);
-  const double *drhs = rhs;
-  if (!rhs_dev) {
-    D4B_CUDA(cudaMemcpyAsync(m->d_u_stage, rhs, bytes, cudaMemcpyHostToDevice, m->stream));
-    drhs = m->d_u_stage;
-  }
-  if (!u_dev) D4B_CUDA(cudaMemcpyAsync(du, u, bytes, cudaMemcpyHostToDevice, m->stream));
-  double *Au = m->d_Au_stage, *p = work(m, 0);
-  double *dr = r_dev ? r : work(m, 1);
   const int g = grid_for(n);
-  const double d = (lmax + lmin) * .5, c = (lmax - lmin) * .5;
-  double alpha = 0., beta;
-  D4B_CUDA(cudaMemsetAsync(p, 0, bytes, m->stream));
+  double *Au = m->d_Au_stage, *p = work(m, 0);
+  D4B_CUDA(cudaMemsetAsync(p, 0, (size_t)n * sizeof(double), m->stream));
   // every element in a fast kernel: the recurrence runs in the apply's epilogue
   // (u updated in place, no Au vector); otherwise apply + one vector kernel
   const char *nf = getenv("D4B_NO_FUSED_CHEBY");
   const bool fused = m->n_generic == 0 && !m->fast.empty() && !(nf && nf[0] == '1');
   for (int i = 0; i < iter; ++i) {
-    if (i == 0) alpha = 1. / d;
-    else if (i == 1) alpha = 2. * d / (2 * d * d - c * c);
-    else alpha = 1. / (d - (alpha * c * c / 4.));
-    beta = alpha * d - 1.;
     if (fused) {
+      m->epi = D4bEpilogue();
       m->epi.mode = 1; m->epi.rhs = drhs; m->epi.p = p; m->epi.u = du;
-      m->epi.alpha = alpha; m->epi.beta = beta;
+      if (d_coef) m->epi.coef = d_coef + 2 * i;
+      else { m->epi.alpha = h_alpha[i]; m->epi.beta = h_beta[i]; }
       d4b_apply_device(m, du, nullptr);
     } else {
       d4b_apply(m, du, Au);
-      cheby_update_k<<<g, 256, 0, m->stream>>>(alpha, beta, drhs, Au, p, du, n);
+      if (d_coef) cheby_update_dev_k<<<g, 256, 0, m->stream>>>(d_coef + 2 * i, drhs, Au, p, du, n);
+      else cheby_update_k<<<g, 256, 0, m->stream>>>(h_alpha[i], h_beta[i], drhs, Au, p, du, n);
     }
   }
   if (fused) {
@@ -284,6 +289,81 @@ extern "C" void d4b_cheby_smooth(d4b_mesh_t *m, double *u, const double *rhs, do
     d4b_apply(m, du, Au);
     residual_k<<<g, 256, 0, m->stream>>>(drhs, Au, dr, n);
   }
+}
+
+}  // namespace
+
+// One smoothing of a multigrid level (d4est_solver_multigrid_smoother_cheby.c:264-376) on
+// device vectors, stream-ordered from the first kernel to the last: the spectrum estimate,
+// its multiplier and the recurrence coefficients stay in device memory (m->d_red).
+void d4b_smooth_async(d4b_mesh *m, double *du, const double *drhs, double *dr, const d4b_cheby_params_t &c,
+                      bool compute_eigs, double *d_eig) {
+  D4B_CHECK(c.cheby_imax >= 0 && c.cheby_imax <= kMaxCheby, "cheby_imax %d out of range", c.cheby_imax);
+  // with a zero guess the estimate runs on a scratch vector and u is untouched (:281-305)
+  if (compute_eigs) cg_eigs_enqueue(m, du, drhs, c.cheby_eigs_cg_imax, c.cheby_use_zero_guess_for_eigs);
+  // (:322-349 re-runs cg_eigs on a zero vector into a dummy when the estimate is
+  //  re-used with the zero-guess option; it changes no state and is skipped here)
+  double *delta = m->d_red + kScalOff, *dAd = delta + kMaxCgIter + 1;
+  eig_plan_k<<<1, 32, 0, m->stream>>>(delta, dAd, compute_eigs ? c.cheby_eigs_cg_imax : 0, c.cheby_use_new_cg_eigs,
+                                      m->local_nodes, c.cheby_eigs_max_multiplier, c.cheby_eigs_lmax_lmin_ratio,
+                                      c.cheby_imax, d_eig, m->d_red + kCoefOff);
+  cheby_enqueue(m, du, drhs, dr, c.cheby_imax, nullptr, nullptr, m->d_red + kCoefOff);
+}
+
+// global dot product into a device scalar, stream-ordered
+void d4b_dot_async(d4b_mesh *m, const double *x, const double *y, int64_t n, double *d_out) { dot_to(m, x, y, n, d_out); }
+
+static double d4b_smooth_eig(d4b_mesh *m) {
+  D4B_CUDA(cudaMemcpyAsync(m->h_red, m->d_red + kEigOff, sizeof(double), cudaMemcpyDeviceToHost, m->stream));
+  D4B_CUDA(cudaStreamSynchronize(m->stream));
+  return m->h_red[0];
+}
+
+extern "C" double d4b_cg_eigs(d4b_mesh_t *m, double *u, const double *rhs, int32_t imax,
+                              int32_t use_new, int32_t use_zero_guess) {
+  const int64_t n = m->local_nodes;
+  const size_t bytes = (size_t)n * sizeof(double);
+  bool u_dev = is_dev(u), rhs_dev = is_dev(rhs);
+  double *du = u_dev ? u : work(m, 2);
+  const double *drhs = rhs;
+  if (!rhs_dev) {
+    D4B_CUDA(cudaMemcpyAsync(m->d_u_stage, rhs, bytes, cudaMemcpyHostToDevice, m->stream));
+    drhs = m->d_u_stage;
+  }
+  if (!u_dev) D4B_CUDA(cudaMemcpyAsync(du, u, bytes, cudaMemcpyHostToDevice, m->stream));
+  cg_eigs_enqueue(m, du, drhs, imax, use_zero_guess);
+  double *delta = m->d_red + kScalOff, *dAd = delta + kMaxCgIter + 1;
+  eig_plan_k<<<1, 32, 0, m->stream>>>(delta, dAd, imax, use_new, n, 1., 1., 0, m->d_red + kEigOff,
+                                      m->d_red + kCoefOff);
+  if (!u_dev && !use_zero_guess)
+    D4B_CUDA(cudaMemcpyAsync(u, du, bytes, cudaMemcpyDeviceToHost, m->stream));
+  return d4b_smooth_eig(m);
+}
+
+extern "C" void d4b_cheby_smooth(d4b_mesh_t *m, double *u, const double *rhs, double *r, int32_t iter,
+                                 double lmin, double lmax) {
+  D4B_CHECK(iter >= 0 && iter <= kMaxCheby, "d4b_cheby_smooth: iter %d out of range", iter);
+  const int64_t n = m->local_nodes;
+  const size_t bytes = (size_t)n * sizeof(double);
+  bool u_dev = is_dev(u), rhs_dev = is_dev(rhs), r_dev = is_dev(r);
+  double *du = u_dev ? u : work(m, 2);
+  const double *drhs = rhs;
+  if (!rhs_dev) {
+    D4B_CUDA(cudaMemcpyAsync(m->d_u_stage, rhs, bytes, cudaMemcpyHostToDevice, m->stream));
+    drhs = m->d_u_stage;
+  }
+  if (!u_dev) D4B_CUDA(cudaMemcpyAsync(du, u, bytes, cudaMemcpyHostToDevice, m->stream));
+  double *dr = r_dev ? r : work(m, 1);
+  const double d = (lmax + lmin) * .5, c = (lmax - lmin) * .5;
+  std::vector<double> al(iter + 1), be(iter + 1);
+  double alpha = 0.;
+  for (int i = 0; i < iter; ++i) {
+    if (i == 0) alpha = 1. / d;
+    else if (i == 1) alpha = 2. * d / (2 * d * d - c * c);
+    else alpha = 1. / (d - (alpha * c * c / 4.));
+    al[i] = alpha; be[i] = alpha * d - 1.;
+  }
+  cheby_enqueue(m, du, drhs, dr, iter, al.data(), be.data(), nullptr);
   if (!u_dev) D4B_CUDA(cudaMemcpyAsync(u, du, bytes, cudaMemcpyDeviceToHost, m->stream));
   if (!r_dev) D4B_CUDA(cudaMemcpyAsync(r, dr, bytes, cudaMemcpyDeviceToHost, m->stream));
   if (!u_dev || !r_dev) D4B_CUDA(cudaStreamSynchronize(m->stream));

@@ -26,6 +26,7 @@ EXPORTS = [
     "d4b_set_abort_hook", "d4b_abi_version", "d4b_device_count", "d4b_init",
     "d4b_mesh_create", "d4b_mesh_destroy", "d4b_mesh_local_nodes", "d4b_mesh_device_bytes", "d4b_mesh_fast_elements", "d4b_mesh_flat_elements", "d4b_mesh_launches_per_apply",
     "d4b_apply", "d4b_apply_stiffness", "d4b_sync", "d4b_set_stream",
+    "d4b_interp_to_quad", "d4b_apply_galerkin", "d4b_apply_mass", "d4b_mesh_set_mass_diag",
     "d4b_vec_dot", "d4b_vec_axpy", "d4b_vec_xpby", "d4b_vec_scale",
     "d4b_cg_eigs", "d4b_cheby_smooth",
     "d4b_mg_create", "d4b_mg_destroy", "d4b_mg_vcycle", "d4b_mg_solve", "d4b_mg_get_eigs", "d4b_mg_restrict",
@@ -66,6 +67,10 @@ def load_library():
         fn.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         fn.restype = None
     L.d4b_sync.argtypes = [C.c_void_p]
+    L.d4b_interp_to_quad.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    L.d4b_apply_galerkin.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.d4b_apply_mass.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.d4b_mesh_set_mass_diag.argtypes = [C.c_void_p, C.c_void_p]
     L.d4b_set_stream.argtypes = [C.c_void_p, C.c_void_p]
     L.d4b_vec_dot.restype = C.c_double
     L.d4b_vec_dot.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]
@@ -233,6 +238,21 @@ class Mesh:
 
     def sync(self):
         self.L.d4b_sync(self.h)
+
+    # volume quadrature operators (d4est_quadrature_interpolate / apply_galerkin_integral /
+    # apply_mass_matrix, src/Quadrature/d4est_quadrature.c:966-1016, :142-213, :385-477)
+    def interp_to_quad(self, u, u_quad):
+        self.L.d4b_interp_to_quad(self.h, _ptr(u), _ptr(u_quad))
+
+    def apply_galerkin(self, in_quad, jac_quad, out):
+        self.L.d4b_apply_galerkin(self.h, _ptr(in_quad), None if jac_quad is None else _ptr(jac_quad), _ptr(out))
+
+    def apply_mass(self, x, jac_quad, out):
+        self.L.d4b_apply_mass(self.h, _ptr(x), _ptr(jac_quad), _ptr(out))
+
+    def set_mass_diag(self, jac_quad):
+        """every later apply adds V^T diag(w jac_quad) V u (None removes the term)"""
+        self.L.d4b_mesh_set_mass_diag(self.h, None if jac_quad is None else _ptr(jac_quad))
 
     def dot(self, x, y):
         return float(self.L.d4b_vec_dot(self.h, _ptr(x), _ptr(y), self.n))

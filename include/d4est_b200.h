@@ -189,6 +189,34 @@ void d4b_apply(d4b_mesh_t *mesh, const double *u, double *Au);
  * (d4est_laplacian.c:197-234)                                              */
 void d4b_apply_stiffness(d4b_mesh_t *mesh, const double *u, double *Au);
 void d4b_sync(d4b_mesh_t *mesh);
+
+/* ------------------------------------------- volume quadrature operators */
+/* On every local element, LGL(deg) <-> Gauss(deg_quad); V = the 3-D interpolation matrix,
+ * w = the tensor Gauss weights.  Nodal arrays have local_nodes entries (reference node
+ * order), *_quad arrays local_nodes_quad entries at quad_stride[e] + k.  Host or device
+ * pointers; synchronous when any is a host pointer.
+ *   d4b_interp_to_quad : u_quad = V u                   d4est_quadrature_interpolate
+ *                                                        (src/Quadrature/d4est_quadrature.c:966-1016)
+ *   d4b_apply_galerkin : out = V^T (w jac_quad in_quad)  d4est_quadrature_apply_galerkin_integral (:142-213);
+ *                                                        jac_quad may be NULL (= 1)
+ *   d4b_apply_mass     : out = V^T diag(w jac_quad) V x  d4est_quadrature_apply_mass_matrix (:385-477)
+ * With jac_quad = J these are the reference's operators; with jac_quad = J f(x, V u0) --
+ * f evaluated by the caller through its own d4est_xyzu_fcn_t -- d4b_apply_mass is the
+ * Newton-linearised mass-type term of d4est_quadrature_apply_fofufofvlilj (QUAD_APPLY_MATRIX,
+ * :593-774) and d4b_apply_galerkin(mesh, f_quad, J, out) the residual term of
+ * d4est_quadrature_apply_fofufofvlj (:776-936).                                           */
+void d4b_interp_to_quad(d4b_mesh_t *mesh, const double *u, double *u_quad);
+void d4b_apply_galerkin(d4b_mesh_t *mesh, const double *in_quad, const double *jac_quad, double *out);
+void d4b_apply_mass(d4b_mesh_t *mesh, const double *x, const double *jac_quad, double *out);
+/* Fuse a mass-type diagonal into the operator: after this call every d4b_apply (and the
+ * smoother, cg_eigs and V-cycle built on it) computes
+ *   Au = A u + V^T diag(w jac_quad) V u,
+ * i.e. the Jacobian apply of the reference's nonlinear problems (SIPG Laplacian +
+ * d4est_quadrature_apply_fofufofvlilj term, e.g. constant_density_star_apply_jac,
+ * src/Problems/ConstantDensityStar/constant_density_star_fcns.h:528-600) in one pass: the
+ * kernels add W * u at the Gauss points, 8 more bytes per quadrature point.  jac_quad is
+ * copied (host or device); NULL removes the term.  d4b_apply_stiffness is unaffected.     */
+void d4b_mesh_set_mass_diag(d4b_mesh_t *mesh, const double *jac_quad);
 /* run all work of this mesh on the caller's CUDA stream (a cudaStream_t passed
  * as void*; NULL = the legacy default stream).  The library otherwise uses a
  * private non-blocking stream.                                             */

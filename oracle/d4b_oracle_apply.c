@@ -83,6 +83,56 @@ d4bo_apply_stiffness (d4bo_ctx_t * c, const double *u, double *Au)
   }
 }
 
+/* ------------------------------------------------------ volume quadrature ops */
+
+/* u_quad = (V x V x V) u on every element, LGL(deg) -> Gauss(deg_quad)
+ * (d4est_quadrature_interpolate, src/Quadrature/d4est_quadrature.c:966-1016) */
+void
+d4bo_interp_to_quad (d4bo_ctx_t * c, const double *u, double *u_quad)
+{
+  const d4b_mesh_desc_t *d = &c->d;
+  for (int e = 0; e < d->n_local; e++) {
+    int N = d->deg[e] + 1, Nq = d->deg_quad[e] + 1;
+    pair_tab_t *pt = get_pair (c, d->deg[e], d->deg_quad[e]);
+    kron3 (u_quad + d->quad_stride[e], pt->E[0], pt->E[0], pt->E[0], u + d->nodal_stride[e], Nq, N, Nq, N, Nq, N);
+  }
+}
+
+/* out = V^T (w . jac . in_quad)
+ * (d4est_quadrature_apply_galerkin_integral, d4est_quadrature.c:142-213) */
+void
+d4bo_apply_galerkin (d4bo_ctx_t * c, const double *in_quad, const double *jac_quad, double *out)
+{
+  const d4b_mesh_desc_t *d = &c->d;
+  for (int e = 0; e < d->n_local; e++) {
+    int N = d->deg[e] + 1, Nq = d->deg_quad[e] + 1, q3 = Nq * Nq * Nq;
+    pair_tab_t *pt = get_pair (c, d->deg[e], d->deg_quad[e]);
+    const double *w = get_gw (c, d->deg_quad[e]);
+    int64_t qs = d->quad_stride[e];
+    double *wji = (double *) malloc (sizeof (double) * q3);
+    for (int kk = 0; kk < q3; kk++) {
+      int a = kk % Nq, b = (kk / Nq) % Nq, cc = kk / (Nq * Nq);
+      wji[kk] = w[cc] * w[b] * w[a] * (jac_quad ? jac_quad[qs + kk] : 1.) * in_quad[qs + kk];
+    }
+    kron3 (out + d->nodal_stride[e], pt->ET[0], pt->ET[0], pt->ET[0], wji, N, Nq, N, Nq, N, Nq);
+    free (wji);
+  }
+}
+
+/* out = V^T diag(w jac) V in: the mass matrix for jac = J
+ * (d4est_quadrature_apply_mass_matrix, d4est_quadrature.c:385-477) and, for
+ * jac = J f(x, V u0), the Newton-linearised mass-type term of
+ * d4est_quadrature_apply_fofufofvlilj (QUAD_APPLY_MATRIX, :593-774) */
+void
+d4bo_apply_mass (d4bo_ctx_t * c, const double *in, const double *jac_quad, double *out)
+{
+  const d4b_mesh_desc_t *d = &c->d;
+  double *in_quad = (double *) malloc (sizeof (double) * (d->local_nodes_quad + 1));
+  d4bo_interp_to_quad (c, in, in_quad);
+  d4bo_apply_galerkin (c, in_quad, jac_quad, out);
+  free (in_quad);
+}
+
 /* --------------------------------------------------------------- face tools */
 
 /* face f -> normal direction f/2, side f%2; face nodes ordered by the two

@@ -4,6 +4,8 @@
 # TEST INFRASTRUCTURE.  Each fixture holds the flattened mesh description, the
 # seeded input vector u (srand(102321), as d4est_test_laplacian_speedup.c:429)
 # and the reference's outputs Au_plain / Au_with_opt (+ its 1-D tables).
+# --quad adds the reference's volume quadrature operators (interpolate, Galerkin
+# integral, mass matrix, fofufofvlj / fofufofvlilj with a star-like f).
 set -e
 HERE="$(cd "$(dirname "$0")" && pwd)"
 DRV="$HERE/_ref/ref_driver"
@@ -17,11 +19,11 @@ run() { # name ini args...
 }
 run brick_l2_p1 brick_poisson.ini                       # the 4^3 p=1 mesh of d4est_test_poisson_sinx.sh
 run brick_l2_p2_bc brick_poisson.ini --uniform-deg 2 --bc poly
-run brick_l2_p3 brick_poisson.ini --uniform-deg 3 --cheby 15 15   # + cg_eigs / Chebyshev smoother outputs
+run brick_l2_p3 brick_poisson.ini --uniform-deg 3 --cheby 15 15 --quad   # + volume quadrature operators; + cg_eigs / Chebyshev smoother outputs
 run brick_l2_p5 brick_poisson.ini --uniform-deg 5
 run brick_l2_p7 brick_poisson.ini --uniform-deg 7
-run sphere_p2 sphere_p.ini --uniform-deg 2 --cheby 8 10 # conforming, 13 trees, all face orientations; smoother outputs
+run sphere_p2 sphere_p.ini --uniform-deg 2 --cheby 8 10 --quad # conforming, 13 trees, all face orientations; smoother outputs
 run sphere_hp_amr0 sphere_hp.ini --bc poly               # per-region degrees + quadrature increments
 run sphere_hp_amr1 sphere_hp.ini --amr 1 --bc poly       # random hp refinement: hanging faces
-run sphere_hp_amr1_zero sphere_hp.ini --amr 1 --cheby 8 10  # hanging faces, homogeneous BC, smoother outputs
+run sphere_hp_amr1_zero sphere_hp.ini --amr 1 --cheby 8 10 --quad  # hanging faces, homogeneous BC, smoother outputs
 run brick_mg_l2_p2 brick_poisson_mg.ini --uniform-deg 2 --mg 4   # + the reference multigrid: residual and iterate after each of 4 V-cycles

@@ -25,6 +25,7 @@
 #include <d4est_solver_cg_eigs.h>
 #include <d4est_solver_multigrid_smoother_cheby.h>
 #include <d4est_solver_multigrid.h>
+#include <d4est_krylov_pc_multigrid.h>
 #include <d4est_util.h>
 #include <zlog.h>
 #include <time.h>
@@ -165,6 +166,27 @@ dump_tables (FILE * f, d4est_operators_t * ops, int max_deg)
   }
 }
 
+/* mass-type nonlinearities of the kind the shipped problems use (ConstantDensityStar:
+ * residual -2 pi rho (1+u)^5, Jacobian -10 pi rho (1+u)^4 with rho a step in radius,
+ * src/Problems/ConstantDensityStar/constant_density_star_fcns.h:64-139) */
+static double
+star_like_rho (double x, double y, double z)
+{
+  return (x * x + y * y + z * z < 1.44) ? 0.3 : 0.02;
+}
+
+static double
+star_like_jac_fcn (double x, double y, double z, double u, void *user)
+{
+  return -10. * M_PI * star_like_rho (x, y, z) * (1. + u) * (1. + u) * (1. + u) * (1. + u);
+}
+
+static double
+star_like_res_fcn (double x, double y, double z, double u, void *user)
+{
+  return -2. * M_PI * star_like_rho (x, y, z) * (1. + u) * (1. + u) * (1. + u) * (1. + u) * (1. + u);
+}
+
 int
 main (int argc, char *argv[])
 {
@@ -176,6 +198,7 @@ main (int argc, char *argv[])
   const char *ini = argv[1];
   const char *out = argv[2];
   int amr_steps = 0, time_reps = 0, bc_poly = 0, cheby_imax = 0, cheby_eigs_imax = 0, mg_vcycles = 0, use_b200 = 0;
+  int dump_quad = 0;
   for (int a = 3; a < argc; a++) {
     if (!strcmp (argv[a], "--amr")) amr_steps = atoi (argv[++a]);
     else if (!strcmp (argv[a], "--time")) time_reps = atoi (argv[++a]);
@@ -183,6 +206,7 @@ main (int argc, char *argv[])
     else if (!strcmp (argv[a], "--uniform-deg")) g_uniform_deg = atoi (argv[++a]);
     else if (!strcmp (argv[a], "--cheby")) { cheby_imax = atoi (argv[++a]); cheby_eigs_imax = atoi (argv[++a]); }
     else if (!strcmp (argv[a], "--mg")) { mg_vcycles = atoi (argv[++a]); }
+    else if (!strcmp (argv[a], "--quad")) { dump_quad = 1; }
     else if (!strcmp (argv[a], "--b200")) { use_b200 = 1; }
     else { fprintf (stderr, "unknown option %s\n", argv[a]); return 2; }
   }
@@ -390,6 +414,59 @@ main (int argc, char *argv[])
               worst, sqrt (unum / uden), tsolve[0], tsolve[1], bctx->uploads, bctx->applies,
               worst2, sqrt (unum2 / uden), tsolve[2]);
       P4EST_FREE (usol[0]); P4EST_FREE (usol[1]); P4EST_FREE (usol[2]);
+
+      /* third entry point: the whole preconditioner.  y = PC(x) through the reference's
+       * d4est_krylov_pc_multigrid (stock apply_lhs) against d4est_b200_pc_multigrid_create,
+       * both called the way the Krylov wrapper calls them (pc->pc_apply (pc, x, y),
+       * src/Solver/d4est_krylov_pc.h:69-89) with vcycle_imax = --mg. */
+      {
+        double *ypc[2];
+        double tpc[2] = { 0., 0. }, tpc_first = 0.;
+        long pc_builds = 0, pc_vcycles = 0;
+        int ref_vcycles = 0;
+        for (int which = 0; which < 2; which++) {
+          d4est_solver_multigrid_t *mg_data =
+            d4est_solver_multigrid_data_init (p4est, d4est_ops, d4est_geom, d4est_quad, &d4est_ghost,
+                                              &d4est_ghost_data, d4est_factors, initial_grid_input, ini);
+          mg_data->vcycle_imax = mg_vcycles;
+          ypc[which] = P4EST_ALLOC_ZERO (double, local_nodes);
+          d4est_elliptic_data_t kv = vecs;
+          krylov_ctx_t kct;
+          memset (&kct, 0, sizeof (kct));
+          kct.p4est = p4est;
+          kct.vecs = &kv;
+          kct.fcns = which ? &fcns_b200 : &fcns_plain;
+          d4est_krylov_pc_t *pc = which ? d4est_b200_pc_multigrid_create (mg_data, bctx, NULL)
+                                        : d4est_krylov_pc_multigrid_create (mg_data, NULL);
+          pc->pc_ctx = &kct;
+          double t3 = wall ();
+          pc->pc_apply (pc, Au_plain, ypc[which]);
+          tpc_first = wall () - t3;
+          if (which) {                       /* second call: hierarchy already on the device */
+            t3 = wall ();
+            pc->pc_apply (pc, Au_plain, ypc[which]);
+            tpc[1] = wall () - t3;
+            d4est_b200_pc_multigrid_data_t *pcd = pc->pc_data;
+            pc_builds = pcd->builds; pc_vcycles = pcd->vcycles / pcd->applies;
+            d4est_b200_pc_multigrid_destroy (pc);
+          }
+          else {
+            tpc[0] = tpc_first;
+            ref_vcycles = mg_data->vcycle_num_finished;
+            d4est_krylov_pc_multigrid_destroy (pc);
+          }
+          d4est_solver_multigrid_data_destroy (mg_data);
+        }
+        double pnum = 0., pden = 0.;
+        for (int i = 0; i < local_nodes; i++) {
+          pnum += (ypc[0][i] - ypc[1][i]) * (ypc[0][i] - ypc[1][i]);
+          pden += ypc[0][i] * ypc[0][i];
+        }
+        printf ("{\"pc_vcycles_reference\": %d, \"pc_vcycles_b200\": %ld, \"pc_y_rel_l2_diff\": %.3e, "
+                "\"t_pc_reference_s\": %.4f, \"t_pc_b200_s\": %.4f, \"pc_hierarchy_builds\": %ld}\n",
+                ref_vcycles, pc_vcycles, sqrt (pnum / pden), tpc[0], tpc[1], pc_builds);
+        P4EST_FREE (ypc[0]); P4EST_FREE (ypc[1]);
+      }
     }
     vecs.Au = Au_tmp;
     P4EST_FREE (Au_b);
@@ -438,6 +515,72 @@ main (int argc, char *argv[])
     for (int e = 0; e < flat->desc.n_local; e++)
       if (flat->desc.deg_quad[e] > max_deg) max_deg = flat->desc.deg_quad[e];
     dump_tables (f, d4est_ops, max_deg);
+
+    if (dump_quad) {
+      /* volume quadrature operators of the reference, element by element the way the
+       * problem files call them (src/Problems/ConstantDensityStar/constant_density_star_fcns.h:352-440,
+       * :528-600): interpolation to the quadrature points, Galerkin integral, mass matrix, and
+       * the Newton-linearised mass-type term V^T diag(w J f(x, V u0)) V u of
+       * d4est_quadrature_apply_fofufofvlilj with a ConstantDensityStar-like f. */
+      const int64_t lnq = d4est_factors->local_sizes.local_nodes_quad;
+      double *q_interp = P4EST_ALLOC_ZERO (double, lnq);
+      double *q_jf = P4EST_ALLOC_ZERO (double, lnq);
+      double *q_galerkin = P4EST_ALLOC_ZERO (double, local_nodes);
+      double *q_mass = P4EST_ALLOC_ZERO (double, local_nodes);
+      double *q_jacterm = P4EST_ALLOC_ZERO (double, local_nodes);
+      double *q_resterm = P4EST_ALLOC_ZERO (double, local_nodes);
+      double *u0 = P4EST_ALLOC (double, local_nodes);
+      for (int i = 0; i < local_nodes; i++) u0[i] = 0.1 * u[i] - 0.05;
+      for (p4est_topidx_t tt = p4est->first_local_tree; tt <= p4est->last_local_tree; ++tt) {
+        p4est_tree_t *tree = p4est_tree_array_index (p4est->trees, tt);
+        sc_array_t *tquadrants = &tree->quadrants;
+        for (int q = 0; q < (int) tquadrants->elem_count; ++q) {
+          p4est_quadrant_t *quad = p4est_quadrant_array_index (tquadrants, q);
+          d4est_element_data_t *ed = quad->p.user_data;
+          d4est_quadrature_volume_t mo;
+          mo.dq = ed->dq; mo.tree = ed->tree; mo.element_id = ed->id;
+          mo.q[0] = ed->q[0]; mo.q[1] = ed->q[1]; mo.q[2] = ed->q[2];
+          double *J_quad = d4est_mesh_get_jacobian_on_quadrature_points (d4est_factors, ed);
+          d4est_mesh_data_on_element_t md = d4est_mesh_data_on_element (d4est_factors, ed);
+          const int nq3 = d4est_lgl_get_nodes ((P4EST_DIM), ed->deg_quad);
+          d4est_quadrature_interpolate (d4est_ops, d4est_quad, d4est_geom, &mo, QUAD_OBJECT_VOLUME,
+                                        QUAD_INTEGRAND_UNKNOWN, &u[ed->nodal_stride], ed->deg,
+                                        &q_interp[ed->quad_stride], ed->deg_quad);
+          d4est_quadrature_apply_galerkin_integral (d4est_ops, d4est_geom, d4est_quad, &mo, QUAD_OBJECT_VOLUME,
+                                                    QUAD_INTEGRAND_UNKNOWN, &q_interp[ed->quad_stride], ed->deg,
+                                                    J_quad, ed->deg_quad, &q_galerkin[ed->nodal_stride]);
+          d4est_quadrature_apply_mass_matrix (d4est_ops, d4est_geom, d4est_quad, &mo, QUAD_OBJECT_VOLUME,
+                                              QUAD_INTEGRAND_UNKNOWN, &u[ed->nodal_stride], ed->deg, J_quad,
+                                              ed->deg_quad, &q_mass[ed->nodal_stride]);
+          d4est_quadrature_apply_fofufofvlilj (d4est_ops, d4est_geom, d4est_quad, &mo, QUAD_OBJECT_VOLUME,
+                                               QUAD_INTEGRAND_UNKNOWN, &u[ed->nodal_stride], &u0[ed->nodal_stride],
+                                               NULL, ed->deg, md.xyz_quad, J_quad, ed->deg_quad,
+                                               &q_jacterm[ed->nodal_stride], star_like_jac_fcn, NULL, NULL, NULL,
+                                               QUAD_APPLY_MATRIX, 0, NULL);
+          d4est_quadrature_apply_fofufofvlj (d4est_ops, d4est_geom, d4est_quad, &mo, QUAD_OBJECT_VOLUME,
+                                             QUAD_INTEGRAND_UNKNOWN, &u0[ed->nodal_stride], NULL, ed->deg, J_quad,
+                                             md.xyz_quad, ed->deg_quad, &q_resterm[ed->nodal_stride],
+                                             star_like_res_fcn, NULL, NULL, NULL, 0, NULL);
+          /* J f(x, V u0) at the quadrature points: what a caller hands to d4b_mesh_set_mass_diag */
+          double *u0q = P4EST_ALLOC (double, nq3);
+          d4est_quadrature_interpolate (d4est_ops, d4est_quad, d4est_geom, &mo, QUAD_OBJECT_VOLUME,
+                                        QUAD_INTEGRAND_UNKNOWN, &u0[ed->nodal_stride], ed->deg, u0q, ed->deg_quad);
+          for (int k = 0; k < nq3; k++)
+            q_jf[ed->quad_stride + k] = J_quad[k] * star_like_jac_fcn (md.xyz_quad[0][k], md.xyz_quad[1][k],
+                                                                       md.xyz_quad[2][k], u0q[k], NULL);
+          P4EST_FREE (u0q);
+        }
+      }
+      d4b_dump_put1 (f, "q_u0", D4B_F64, local_nodes, u0);
+      d4b_dump_put1 (f, "q_interp", D4B_F64, lnq, q_interp);
+      d4b_dump_put1 (f, "q_galerkin", D4B_F64, local_nodes, q_galerkin);
+      d4b_dump_put1 (f, "q_mass", D4B_F64, local_nodes, q_mass);
+      d4b_dump_put1 (f, "q_jf", D4B_F64, lnq, q_jf);
+      d4b_dump_put1 (f, "q_jacterm", D4B_F64, local_nodes, q_jacterm);
+      d4b_dump_put1 (f, "q_resterm", D4B_F64, local_nodes, q_resterm);
+      P4EST_FREE (q_interp); P4EST_FREE (q_jf); P4EST_FREE (q_galerkin); P4EST_FREE (q_mass);
+      P4EST_FREE (q_jacterm); P4EST_FREE (q_resterm); P4EST_FREE (u0);
+    }
 
     if (cheby_imax > 0) {
       /* stiffness-only apply, for the volume kernel in isolation */

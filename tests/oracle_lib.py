@@ -31,6 +31,9 @@ def lib():
         fn.argtypes = [C.c_void_p, _F64P, _F64P]
     L.d4bo_apply.argtypes = [C.c_void_p, _F64P, _F64P, _F64P]
     L.d4bo_apply_flux.argtypes = [C.c_void_p, _F64P, _F64P, _F64P]
+    L.d4bo_interp_to_quad.argtypes = [C.c_void_p, _F64P, _F64P]
+    L.d4bo_apply_galerkin.argtypes = [C.c_void_p, _F64P, _F64P, _F64P]
+    L.d4bo_apply_mass.argtypes = [C.c_void_p, _F64P, _F64P, _F64P]
     L.d4bo_gauss.argtypes = [C.c_int, _F64P, _F64P]
     L.d4bo_lobatto.argtypes = [C.c_int, _F64P, _F64P]
     L.d4bo_dij.argtypes = [C.c_int, _F64P]
@@ -61,6 +64,26 @@ class Oracle:
         Au = np.zeros(self.n)
         self.L.d4bo_apply_stiffness(self.ctx, _p(u), _p(Au))
         return Au
+
+    def interp_to_quad(self, u):
+        u = np.ascontiguousarray(u, dtype=np.float64)
+        uq = np.zeros(int(self.desc.local_nodes_quad))
+        self.L.d4bo_interp_to_quad(self.ctx, _p(u), _p(uq))
+        return uq
+
+    def apply_galerkin(self, in_quad, jac_quad=None):
+        in_quad = np.ascontiguousarray(in_quad, dtype=np.float64)
+        jac_quad = None if jac_quad is None else np.ascontiguousarray(jac_quad, dtype=np.float64)
+        out = np.zeros(self.n)
+        self.L.d4bo_apply_galerkin(self.ctx, _p(in_quad), _p(jac_quad), _p(out))
+        return out
+
+    def apply_mass(self, x, jac_quad):
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        jac_quad = np.ascontiguousarray(jac_quad, dtype=np.float64)
+        out = np.zeros(self.n)
+        self.L.d4bo_apply_mass(self.ctx, _p(x), _p(jac_quad), _p(out))
+        return out
 
     def close(self):
         if self.ctx:
