@@ -405,6 +405,47 @@ d4est_b200_apply_lhs (p4est_t * p4est, d4est_ghost_t * ghost,
   d4b_apply (mesh, prob_vecs->u, prob_vecs->Au);
 }
 
+/* ------------------------------------------------------------ mass term */
+void
+d4est_b200_set_mass_term (d4est_b200_ctx_t * ctx, p4est_t * p4est, d4est_ghost_t * ghost,
+                          d4est_operators_t * d4est_ops, d4est_geometry_t * d4est_geom,
+                          d4est_quadrature_t * d4est_quad, d4est_mesh_data_t * d4est_factors,
+                          double *u0, d4est_xyzu_fcn_t f, void *f_ctx)
+{
+  d4b_mesh_t *mesh = d4est_b200_get_mesh (ctx, p4est, ghost, d4est_factors);
+  if (f == NULL) { d4b_mesh_set_mass_diag (mesh, NULL); return; }
+  double *jf = (double *) malloc (sizeof (double) * (d4est_factors->local_sizes.local_nodes_quad + 1));
+  for (p4est_topidx_t tt = p4est->first_local_tree; tt <= p4est->last_local_tree; ++tt) {
+    p4est_tree_t *tree = p4est_tree_array_index (p4est->trees, tt);
+    sc_array_t *tquadrants = &tree->quadrants;
+    for (size_t q = 0; q < tquadrants->elem_count; ++q) {
+      p4est_quadrant_t *quad = p4est_quadrant_array_index (tquadrants, q);
+      d4est_element_data_t *ed = (d4est_element_data_t *) quad->p.user_data;
+      d4est_quadrature_volume_t mo;
+      mo.dq = ed->dq; mo.tree = ed->tree; mo.element_id = ed->id;
+      mo.q[0] = ed->q[0]; mo.q[1] = ed->q[1];
+#if (P4EST_DIM)==3
+      mo.q[2] = ed->q[2];
+#endif
+      double *J_quad = d4est_mesh_get_jacobian_on_quadrature_points (d4est_factors, ed);
+      d4est_mesh_data_on_element_t md = d4est_mesh_data_on_element (d4est_factors, ed);
+      const int nq = d4est_lgl_get_nodes ((P4EST_DIM), ed->deg_quad);
+      double *out = jf + ed->quad_stride;
+      /* u0 at the quadrature points, then J f as d4est_quadrature.c:660-680 forms it */
+      d4est_quadrature_interpolate (d4est_ops, d4est_quad, d4est_geom, &mo, QUAD_OBJECT_VOLUME,
+                                    QUAD_INTEGRAND_UNKNOWN, &u0[ed->nodal_stride], ed->deg, out, ed->deg_quad);
+      for (int k = 0; k < nq; k++)
+        out[k] = J_quad[k] * f (md.xyz_quad[0][k], md.xyz_quad[1][k],
+#if (P4EST_DIM)==3
+                                md.xyz_quad[2][k],
+#endif
+                                out[k], f_ctx);
+    }
+  }
+  d4b_mesh_set_mass_diag (mesh, jf);
+  free (jf);
+}
+
 /* ------------------------------------------------------------ smoother */
 #include <d4est_solver_multigrid_smoother_cheby.h>
 

@@ -20,6 +20,8 @@
 #include <d4est_laplacian_flux_sipg.h>
 #include <d4est_solver_multigrid.h>
 #include <d4est_krylov_pc.h>
+#include <d4est_quadrature.h>
+#include <d4est_xyz_functions.h>
 #include "d4est_b200.h"
 
 /* Owns the arrays a d4b_mesh_desc_t points to (those that are not aliases of
@@ -99,6 +101,19 @@ void d4est_b200_ctx_destroy(d4est_b200_ctx_t *ctx);
 d4est_solver_multigrid_smoother_t *d4est_b200_smoother_cheby_init(p4est_t *p4est, int num_of_levels,
                                                                   const char *input_file,
                                                                   d4est_b200_ctx_t *ctx);
+
+/* Mass-type term of the nonlinear problems' Jacobians.  The reference adds,
+ * element by element, d4est_quadrature_apply_fofufofvlilj (vec = u, u = u0, fofu_fcn = f,
+ * QUAD_APPLY_MATRIX) to the Laplacian apply (e.g. constant_density_star_apply_jac,
+ * src/Problems/ConstantDensityStar/constant_density_star_fcns.h:528-600).  This call evaluates
+ * J f(x, V u0) at the quadrature points with the caller's own d4est_xyzu_fcn_t -- once per
+ * Newton linearisation -- and fuses it into the device operator of the current mesh, so that
+ * d4est_b200_apply_lhs, the smoother and the preconditioner then apply the whole Jacobian
+ * in one pass.  f == NULL removes the term.                                             */
+void d4est_b200_set_mass_term (d4est_b200_ctx_t * ctx, p4est_t * p4est, d4est_ghost_t * ghost,
+                               d4est_operators_t * d4est_ops, d4est_geometry_t * d4est_geom,
+                               d4est_quadrature_t * d4est_quad, d4est_mesh_data_t * d4est_factors,
+                               double *u0, d4est_xyzu_fcn_t f, void *f_ctx);
 
 /* Third entry point: the whole multigrid preconditioner, device-resident.  Same role and
  * call convention as d4est_krylov_pc_multigrid_create (src/Solver/d4est_krylov_pc_multigrid.c:82-100):

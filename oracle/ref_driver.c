@@ -366,6 +366,47 @@ main (int argc, char *argv[])
     }
     printf ("{\"b200_apply_rel_l2\": %.3e, \"t_apply_b200_host_vectors_s\": %.6f, \"t_apply_reference_s\": %.6f}\n",
             sqrt (num / den), t_b200, best_plain < best_opt ? best_plain : best_opt);
+    {
+      /* Jacobian apply of a nonlinear problem: Laplacian + mass-type term.  Reference: the
+       * problem files' loop over d4est_quadrature_apply_fofufofvlilj added to apply_aij
+       * (constant_density_star_fcns.h:528-600); ours: d4est_b200_set_mass_term, then the same
+       * apply_lhs callback as before. */
+      double *u0 = P4EST_ALLOC (double, local_nodes);
+      double *term = P4EST_ALLOC_ZERO (double, local_nodes);
+      for (int i = 0; i < local_nodes; i++) u0[i] = 0.1 * u[i] - 0.05;
+      for (p4est_topidx_t tt = p4est->first_local_tree; tt <= p4est->last_local_tree; ++tt) {
+        p4est_tree_t *tree = p4est_tree_array_index (p4est->trees, tt);
+        sc_array_t *tquadrants = &tree->quadrants;
+        for (int q = 0; q < (int) tquadrants->elem_count; ++q) {
+          p4est_quadrant_t *quad = p4est_quadrant_array_index (tquadrants, q);
+          d4est_element_data_t *ed = quad->p.user_data;
+          d4est_quadrature_volume_t mo;
+          mo.dq = ed->dq; mo.tree = ed->tree; mo.element_id = ed->id;
+          mo.q[0] = ed->q[0]; mo.q[1] = ed->q[1]; mo.q[2] = ed->q[2];
+          double *J_quad = d4est_mesh_get_jacobian_on_quadrature_points (d4est_factors, ed);
+          d4est_mesh_data_on_element_t md = d4est_mesh_data_on_element (d4est_factors, ed);
+          d4est_quadrature_apply_fofufofvlilj (d4est_ops, d4est_geom, d4est_quad, &mo, QUAD_OBJECT_VOLUME,
+                                               QUAD_INTEGRAND_UNKNOWN, &u[ed->nodal_stride], &u0[ed->nodal_stride],
+                                               NULL, ed->deg, md.xyz_quad, J_quad, ed->deg_quad,
+                                               &term[ed->nodal_stride], star_like_jac_fcn, NULL, NULL, NULL,
+                                               QUAD_APPLY_MATRIX, 0, NULL);
+        }
+      }
+      d4est_b200_set_mass_term (bctx, p4est, d4est_ghost, d4est_ops, d4est_geom, d4est_quad, d4est_factors,
+                                u0, star_like_jac_fcn, NULL);
+      d4est_elliptic_eqns_apply_lhs (p4est, d4est_ghost, d4est_ghost_data, &fcns_b200, &vecs,
+                                     d4est_ops, d4est_geom, d4est_quad, d4est_factors);
+      double jn = 0., jd = 0.;
+      for (int i = 0; i < local_nodes; i++) {
+        const double want = Au_plain[i] + term[i];
+        jn += (Au_b[i] - want) * (Au_b[i] - want);
+        jd += want * want;
+      }
+      printf ("{\"b200_jacobian_apply_rel_l2\": %.3e}\n", sqrt (jn / jd));
+      d4est_b200_set_mass_term (bctx, p4est, d4est_ghost, d4est_ops, d4est_geom, d4est_quad, d4est_factors,
+                                NULL, NULL, NULL);
+      P4EST_FREE (u0); P4EST_FREE (term);
+    }
     if (mg_vcycles > 0) {
       double r2s[3][64], tsolve[3];
       double *usol[3];

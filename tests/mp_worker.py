@@ -1,7 +1,9 @@
 """Worker for the multi-rank tests (launched by tests/test_multi_rank.py, one process per rank).
 
-mode "gloo": CPU.  Every rank builds its part of a partitioned brick
-(disco4est_b200.brick), exchanges mirror -> ghost nodal values exactly as the
+Mesh: a synthetic brick ("<level> <p>") or a reference fixture split by
+disco4est_b200.partition ("golden:<case> 0": hp meshes with hanging faces, curved trees).
+
+mode "gloo": CPU.  Every rank builds its part of the partitioned mesh, exchanges mirror -> ghost nodal values exactly as the
 exchange plan of the mesh description says (what d4est_ghost_data_exchange
 does, src/Mesh/d4est_ghost_data.c:142-255) with gloo send/recv, applies the
 ORACLE with those ghosts, and rank 0 compares the gathered result with the
@@ -26,11 +28,16 @@ def n3_of(p):
     return (p + 1) ** 3
 
 
+def _i(x):
+    """fixture scalars are stored as 1-element arrays"""
+    return int(np.asarray(x).reshape(-1)[0])
+
+
 def exchange_host(A, ul, dist, torch):
     """mirror -> ghost exchange by the plan in A, nodal values, host buffers."""
     rank, world = A["mpirank"], A["mpisize"]
-    n3 = n3_of(int(A["deg"][0]))
-    ug = np.zeros(max(int(A["ghost_nodes"]), 1))
+    ug = np.zeros(max(_i(A["ghost_nodes"]), 1))
+    gend = np.concatenate([A["ghost_nodal_stride"], [_i(A["ghost_nodes"])]]).astype(np.int64)
     reqs, keep = [], []
     for q in range(world):
         if q == rank:
@@ -38,14 +45,13 @@ def exchange_host(A, ul, dist, torch):
         m0, m1 = A["mirror_proc_offsets"][q], A["mirror_proc_offsets"][q + 1]
         if m1 > m0:
             els = A["mirror_elem"][A["mirror_proc_mirrors"][m0:m1]]
-            buf = np.concatenate([ul[A["nodal_stride"][e]:A["nodal_stride"][e] + n3] for e in els])
+            buf = np.concatenate([ul[A["nodal_stride"][e]:A["nodal_stride"][e] + n3_of(int(A["deg"][e]))] for e in els])
             t = torch.from_numpy(np.ascontiguousarray(buf))
             keep.append(t)
             reqs.append(dist.isend(t, q))
         g0, g1 = A["ghost_proc_offsets"][q], A["ghost_proc_offsets"][q + 1]
         if g1 > g0:
-            lo = int(A["ghost_nodal_stride"][g0])
-            t = torch.from_numpy(ug[lo:lo + (g1 - g0) * n3])
+            t = torch.from_numpy(ug[int(gend[g0]):int(gend[g1])])
             reqs.append(dist.irecv(t, q))
     for r in reqs:
         r.wait()
@@ -53,7 +59,7 @@ def exchange_host(A, ul, dist, torch):
 
 
 def main():
-    mode, level, p = sys.argv[1], int(sys.argv[2]), int(sys.argv[3])
+    mode, mesh_arg, p = sys.argv[1], sys.argv[2], int(sys.argv[3])
     import torch
     import torch.distributed as dist
     from disco4est_b200.brick import brick_desc, partition_offsets, trees_for_world
@@ -65,18 +71,32 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", rank))
     else:
         dist.init_process_group("gloo")
-    trees = trees_for_world(world)
-    full = brick_desc(level, p, trees=trees)
-    n3 = n3_of(p)
-    u = np.random.default_rng(7).standard_normal(full["local_nodes"])
-    offs = partition_offsets(full["n_local"], world) * n3
+    if mesh_arg.startswith("golden:"):
+        import d4bio
+        from disco4est_b200.partition import partition_desc
+
+        full = d4bio.load(os.path.join(HERE, "golden", mesh_arg[7:] + ".d4b.gz"))
+        eoffs = partition_offsets(_i(full["n_local"]), world)
+        nend = np.concatenate([full["nodal_stride"], [_i(full["local_nodes"])]]).astype(np.int64)
+        offs = nend[eoffs]
+        A = partition_desc(full, rank, world)
+        gid = A["ghost_global_id"]
+        ghost_want = [(int(nend[g]), int(nend[g + 1])) for g in gid]
+    else:
+        level = int(mesh_arg)
+        trees = trees_for_world(world)
+        full = brick_desc(level, p, trees=trees)
+        n3 = n3_of(p)
+        offs = partition_offsets(full["n_local"], world) * n3
+        A = brick_desc(level, p, rank=rank, world=world, trees=trees)
+        ghost_want = [(int(g) * n3, (int(g) + 1) * n3) for g in A["ghost_global_id"]]
+    u = np.random.default_rng(7).standard_normal(_i(full["local_nodes"]))
     ul = np.ascontiguousarray(u[offs[rank]:offs[rank + 1]])
-    A = brick_desc(level, p, rank=rank, world=world, trees=trees)
 
     if mode == "gloo":
         ug = exchange_host(A, ul, dist, torch)
         # the exchange delivered exactly the neighbours' values
-        want = np.concatenate([u[g * n3:(g + 1) * n3] for g in A["ghost_global_id"]])
+        want = np.concatenate([u[a:b] for a, b in ghost_want]) if ghost_want else np.zeros(0)
         assert np.array_equal(ug[:want.size], want)
         au = Oracle(A).apply(ul, ug)
         local_dot = float(ul @ au)
@@ -89,7 +109,8 @@ def main():
 
         comm_init_from_torch(rank)
         m = Mesh(A, device=rank)
-        assert m.fast_elements() == A["n_local"], "every brick element must take a fast kernel, ghosts included"
+        if not mesh_arg.startswith("golden:"):
+            assert m.fast_elements() == A["n_local"], "every brick element must take a fast kernel, ghosts included"
         au = np.zeros_like(ul)
         m.apply(ul, au)
         # device-pointer path + all-reduced dot
@@ -102,19 +123,22 @@ def main():
         m.close()
         comm_destroy()
 
-    gathered = [torch.zeros(int(offs[r + 1] - offs[r]), dtype=torch.float64) for r in range(world)] if rank == 0 else None
+    # gloo's gather wants equal sizes: pad to the largest rank, trim on rank 0
+    sizes = [int(offs[r + 1] - offs[r]) for r in range(world)]
+    padded = np.zeros(max(sizes))
+    padded[:au.size] = au
+    gathered = [torch.zeros(max(sizes), dtype=torch.float64) for r in range(world)] if rank == 0 else None
     if mode == "nccl":
-        # gather through the host with a gloo side group (sizes may differ per rank)
-        side = dist.new_group(backend="gloo")
-        dist.gather(torch.from_numpy(au), gathered, dst=0, group=side)
+        side = dist.new_group(backend="gloo")   # gather through the host
+        dist.gather(torch.from_numpy(padded), gathered, dst=0, group=side)
     else:
-        dist.gather(torch.from_numpy(au), gathered, dst=0)
+        dist.gather(torch.from_numpy(padded), gathered, dst=0)
     if rank == 0:
-        got = np.concatenate([g.numpy() for g in gathered])
+        got = np.concatenate([g.numpy()[:sizes[r]] for r, g in enumerate(gathered)])
         ref = Oracle(full).apply(u)
         err = np.linalg.norm(got - ref) / np.linalg.norm(ref)
         derr = abs(gdot - float(u @ ref)) / abs(float(u @ ref))
-        print("MP_RESULT mode=%s world=%d rel_err=%.3e dot_err=%.3e" % (mode, world, err, derr), flush=True)
+        print("MP_RESULT mode=%s mesh=%s world=%d rel_err=%.3e dot_err=%.3e" % (mode, mesh_arg, world, err, derr), flush=True)
         assert err < 1e-12 and derr < 1e-12
     dist.barrier()
     dist.destroy_process_group()

@@ -35,6 +35,14 @@ def test_apply_lhs_callback_inside_the_reference(ini, args):
     assert res["b200_apply_rel_l2"] < 1e-12
 
 
+@pytest.mark.parametrize("ini,args", [("brick_poisson.ini", ["--uniform-deg", "3"]), ("sphere_hp.ini", ["--amr", "1"])])
+def test_jacobian_apply_with_mass_term_inside_the_reference(ini, args):
+    """d4est_b200_set_mass_term + apply_lhs against apply_aij + the reference's fofufofvlilj loop"""
+    lines = run(ini, *args)
+    res = [l for l in lines if "b200_jacobian_apply_rel_l2" in l][0]
+    assert res["b200_jacobian_apply_rel_l2"] < 1e-12
+
+
 def test_reference_multigrid_driving_our_apply():
     lines = run("brick_poisson_mg.ini", "--uniform-deg", "3", "--mg", "4")
     res = [l for l in lines if "r2_b200_apply" in l][0]

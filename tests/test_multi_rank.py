@@ -22,6 +22,7 @@ def free_port():
 
 
 def run_ranks(mode, world, level, p, timeout=600):
+    """level: brick refinement level, or "golden:<case>" for a partitioned reference fixture"""
     port = free_port()
     procs = []
     for r in range(world):
@@ -57,3 +58,19 @@ def test_two_gpu_apply_matches_oracle(level, p):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     run_ranks("nccl", 2, level, p)
+
+
+@pytest.mark.parametrize("world,case", [(2, "sphere_hp_amr1_zero"), (3, "sphere_hp_amr1_zero"), (2, "sphere_p2")])
+def test_partitioned_hp_mesh_gloo(world, case):
+    """BASELINE config 4 in small: curved cubed sphere, hp-adapted, hanging faces across rank boundaries"""
+    run_ranks("gloo", world, "golden:" + case, 0)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", ["sphere_hp_amr1_zero", "sphere_p2"])
+def test_two_gpu_hp_mesh_matches_oracle(case):
+    import torch
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    run_ranks("nccl", 2, "golden:" + case, 0)
