@@ -657,9 +657,11 @@ d4est_b200_pc_multigrid_apply (d4est_krylov_pc_t * kpc, double *xp, double *yp)
 static void
 d4est_b200_pc_multigrid_setup (d4est_krylov_pc_t * kpc)
 {
-  /* "Operator is changing" (d4est_krylov_pc_multigrid.c:8-26): rebuild on the next apply */
+  /* like d4est_krylov_pc_multigrid_setup (d4est_krylov_pc_multigrid.c:8-26): only the user's
+   * hook runs.  The reference's FCG calls this before EVERY pc_apply
+   * (d4est_solver_fcg_improved.c:206-210); the device hierarchy depends on the meshes alone and
+   * is rebuilt by pc_apply when the top mesh changed, so there is nothing to drop here. */
   d4est_b200_pc_multigrid_data_t *pcd = kpc->pc_data;
-  d4est_b200_pc_drop_hierarchy (pcd);
   if (pcd->user_setup_fcn != NULL) pcd->user_setup_fcn (kpc);
 }
 

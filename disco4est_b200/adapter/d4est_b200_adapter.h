@@ -124,7 +124,7 @@ void d4est_b200_set_mass_term (d4est_b200_ctx_t * ctx, p4est_t * p4est, d4est_gh
  * settings -- but as H2D(x), V-cycles on the device (d4b_mg_solve), D2H(y).
  *
  * The level hierarchy is taken from the reference itself: on the first apply (and again
- * after pc_setup signalled a changed operator, or when the top mesh changed) ONE V-cycle of
+ * when the top mesh changed) ONE V-cycle of
  * the unmodified d4est_solver_multigrid_solve is run with a recording smoother / bottom
  * solver that do no arithmetic.  It walks the reference's own coarsen / balance / mesh-update
  * sequence, so every level's d4est_mesh_data_t is uploaded through d4est_b200_get_mesh and

@@ -179,6 +179,11 @@ void d4b_smooth_async(d4b_mesh *m, double *du, const double *drhs, double *dr, c
                       bool compute_eigs, double *d_eig);
 void d4b_dot_async(d4b_mesh *m, const double *x, const double *y, int64_t n, double *d_out);
 
+// CG on device vectors with the stopping test on the device (d4b_krylov.cu); returns iterations
+int d4b_cg_run(d4b_mesh *m, double *u, const double *rhs, double *r, double *d, int imax, double rtol, double atol,
+               double *d_scal, double *h_scal);
+d4b_mesh *d4b_mg_top_mesh(d4b_mg_t *g);
+
 // halo exchange (d4b_comm.cu)
 void d4b_comm_setup(d4b_mesh *m, const d4b_mesh_desc_t *d);
 void d4b_comm_teardown(d4b_mesh *m);

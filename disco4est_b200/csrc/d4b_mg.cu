@@ -141,13 +141,6 @@ __global__ void resid_k(const double *__restrict__ rhs, const double *__restrict
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     r[i] = rhs[i] - Au[i];
 }
-__global__ void resid_init_k(const double *__restrict__ rhs, const double *__restrict__ Au, double *__restrict__ r,
-                             double *__restrict__ d, int64_t n) {
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-    double v = rhs[i] - Au[i];
-    r[i] = v; d[i] = v;
-  }
-}
 int grid_for(int64_t n) {
   int64_t b = (n + 255) / 256;
   return (int)(b < 148 * 8 ? (b > 0 ? b : 1) : 148 * 8);
@@ -159,75 +152,13 @@ void smooth(d4b_mg *g, int level, double *u, const double *rhs, double *r, bool 
   d4b_smooth_async(g->mesh[level], u, rhs, r, g->prm.smoother, compute_eigs, g->d_eigs + level);
 }
 
-// Bottom CG, d4est_solver_multigrid_bottom_solver_cg.c:48-200.  Its stopping test
-// (delta_new > atol^2 + delta_0 rtol^2, :118) is evaluated on the device: every iteration is
-// enqueued behind a `done` flag the vector kernels honour, and the host only looks at the
-// flag once per chunk of iterations.  Same arithmetic and same iteration count as the
-// reference loop.
-struct BcgScal { double delta_new, dAd, delta_0, alpha, beta, rr; int32_t done, iters; };
-constexpr int kBcgChunk = 16;
-
-__global__ void bcg_begin_k(BcgScal *s, double atol, double rtol, int imax) {
-  s->delta_new = s->rr; s->delta_0 = s->rr; s->iters = 0;
-  s->done = !(imax > 0 && s->delta_new > atol * atol + s->delta_0 * rtol * rtol);
-}
-__global__ void bcg_alpha_k(BcgScal *s) { if (!s->done) s->alpha = s->delta_new / s->dAd; }
-__global__ void bcg_beta_k(BcgScal *s, double atol, double rtol, int imax) {
-  if (s->done) return;
-  s->beta = s->rr / s->delta_new;
-  s->delta_new = s->rr;
-  s->iters++;
-  s->done = !(s->iters < imax && s->delta_new > atol * atol + s->delta_0 * rtol * rtol);
-  if (s->done) s->done = 2;   // finished by this iteration: its d-update still runs, like the reference's
-}
-__global__ void bcg_step_k(const BcgScal *__restrict__ s, const double *__restrict__ d, const double *__restrict__ Au,
-                           double *__restrict__ u, double *__restrict__ r, int64_t n) {
-  if (s->done) return;
-  const double alpha = s->alpha;
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-    u[i] += alpha * d[i];
-    r[i] -= alpha * Au[i];
-  }
-}
-__global__ void bcg_xpby_k(const BcgScal *__restrict__ s, const double *__restrict__ r, double *__restrict__ d,
-                           int64_t n) {
-  if (s->done == 1) return;
-  const double beta = s->beta;
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-    d[i] = r[i] + beta * d[i];
-}
-__global__ void bcg_settle_k(BcgScal *s) { if (s->done == 2) s->done = 1; }
-
+// Bottom CG, d4est_solver_multigrid_bottom_solver_cg.c:48-200: the loop of d4est_solver_cg.c,
+// stopping test on the device (d4b_krylov.cu)
 void bottom_cg(d4b_mg *g, double *u, const double *rhs, double *r) {
   d4b_mesh *m = g->mesh[0];
-  const int64_t n = m->local_nodes;
-  const int gr = grid_for(n);
-  double *Au = m->d_Au_stage;
-  if (!m->d_work[3]) m->d_work[3] = d4b_dev_alloc<double>(m, (size_t)n);
-  double *d = m->d_work[3];
-  BcgScal *s = reinterpret_cast<BcgScal *>(g->d_scal);
-  const double rtol = g->prm.bottom_rtol, atol = g->prm.bottom_atol;
-  const int imax = g->prm.bottom_iter;
-  d4b_apply(m, u, Au);
-  resid_init_k<<<gr, 256, 0, m->stream>>>(rhs, Au, r, d, n);
-  d4b_dot_async(m, r, r, n, &s->rr);
-  bcg_begin_k<<<1, 1, 0, m->stream>>>(s, atol, rtol, imax);
-  for (int i0 = 0; i0 < imax; i0 += kBcgChunk) {
-    for (int i = i0; i < imax && i < i0 + kBcgChunk; ++i) {
-      d4b_apply(m, d, Au);
-      d4b_dot_async(m, d, Au, n, &s->dAd);
-      bcg_alpha_k<<<1, 1, 0, m->stream>>>(s);
-      bcg_step_k<<<gr, 256, 0, m->stream>>>(s, d, Au, u, r, n);
-      d4b_dot_async(m, r, r, n, &s->rr);
-      bcg_beta_k<<<1, 1, 0, m->stream>>>(s, atol, rtol, imax);
-      bcg_xpby_k<<<gr, 256, 0, m->stream>>>(s, r, d, n);
-      bcg_settle_k<<<1, 1, 0, m->stream>>>(s);
-    }
-    BcgScal *h = reinterpret_cast<BcgScal *>(g->h_scal);
-    D4B_CUDA(cudaMemcpyAsync(h, s, sizeof(BcgScal), cudaMemcpyDeviceToHost, m->stream));
-    D4B_CUDA(cudaStreamSynchronize(m->stream));
-    if (h->done) break;
-  }
+  if (!m->d_work[3]) m->d_work[3] = d4b_dev_alloc<double>(m, (size_t)m->local_nodes);
+  d4b_cg_run(m, u, rhs, r, m->d_work[3], g->prm.bottom_iter, g->prm.bottom_rtol, g->prm.bottom_atol, g->d_scal,
+             g->h_scal);
 }
 
 // d4est_solver_multigrid_bottom_solver_cheby.c:60-115
@@ -390,6 +321,8 @@ extern "C" d4b_mg_t *d4b_mg_create(const d4b_mg_desc_t *desc) {
   // a coarse element is never of higher degree than its children
   return g;
 }
+
+d4b_mesh *d4b_mg_top_mesh(d4b_mg *g) { return g->mesh[g->n_levels - 1]; }
 
 extern "C" void d4b_mg_destroy(d4b_mg_t *g) {
   if (!g) return;

@@ -31,6 +31,7 @@ EXPORTS = [
     "d4b_cg_eigs", "d4b_cheby_smooth",
     "d4b_mg_create", "d4b_mg_destroy", "d4b_mg_vcycle", "d4b_mg_solve", "d4b_mg_get_eigs", "d4b_mg_restrict",
     "d4b_mg_prolong",
+    "d4b_cg_solve", "d4b_fcg_solve",
     "d4b_comm_get_unique_id", "d4b_comm_init", "d4b_comm_destroy", "d4b_comm_size", "d4b_comm_rank",
 ]
 
@@ -91,6 +92,11 @@ def load_library():
     L.d4b_mg_get_eigs.argtypes = [C.c_void_p, C.c_void_p]
     L.d4b_mg_restrict.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]
     L.d4b_mg_prolong.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]
+    L.d4b_cg_solve.restype = C.c_int32
+    L.d4b_cg_solve.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_double, C.c_double]
+    L.d4b_fcg_solve.restype = C.c_int32
+    L.d4b_fcg_solve.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_double, C.c_double,
+                                C.c_int32, C.c_void_p]
     L.d4b_comm_get_unique_id.argtypes = [C.c_void_p]
     L.d4b_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int]
     L.d4b_comm_size.restype = C.c_int
@@ -259,6 +265,19 @@ class Mesh:
 
     def cg_eigs(self, u, rhs, imax, use_new=0, use_zero_guess=0):
         return float(self.L.d4b_cg_eigs(self.h, _ptr(u), _ptr(rhs), imax, use_new, use_zero_guess))
+
+    def cg_solve(self, u, rhs, imax, rtol, atol=0.0):
+        """d4est_solver_cg_solve on the device; returns the iteration count"""
+        return int(self.L.d4b_cg_solve(self.h, _ptr(u), _ptr(rhs), imax, rtol, atol))
+
+    def fcg_solve(self, u, rhs, imax, rtol, atol=0.0, pc=None, textbook=False):
+        """d4est_solver_fcg_solve on the device (pc: a Multigrid whose finest mesh is this one, or None);
+        returns (iterations, |r_k|^2 at the start of every iteration).  textbook=False reproduces the
+        reference's executed arithmetic (see include/d4est_b200.h), True the recurrence of its comments."""
+        hist = np.zeros(max(imax, 1))
+        its = int(self.L.d4b_fcg_solve(self.h, pc.h if pc is not None else None, _ptr(u), _ptr(rhs), imax, rtol, atol,
+                                       1 if textbook else 0, hist.ctypes.data))
+        return its, hist[:its]
 
     def cheby_smooth(self, u, rhs, r, iters, lmin, lmax):
         self.L.d4b_cheby_smooth(self.h, _ptr(u), _ptr(rhs), _ptr(r), iters, lmin, lmax)

@@ -312,6 +312,29 @@ void      d4b_mg_get_eigs(const d4b_mg_t *mg, double *eigs_out);
 void      d4b_mg_restrict(d4b_mg_t *mg, int32_t coarse_level, const double *fine, double *coarse);
 void      d4b_mg_prolong(d4b_mg_t *mg, int32_t coarse_level, const double *coarse, double *fine);
 
+/* ----------------------------------------------------------- outer Krylov */
+/* Device-resident versions of the reference's in-house Krylov solvers (the PETSc KSP wrappers
+ * stay on the host and reach the device through apply_lhs / pc_apply).  u: initial guess in,
+ * solution out; host or device pointers; return value = iterations performed.
+ *
+ * d4b_cg_solve:  d4est_solver_cg_solve (src/Solver/d4est_solver_cg.c:75-197), unpreconditioned CG,
+ *   runs while i < imax and |r|^2 > atol^2 + |r_0|^2 rtol^2.
+ * d4b_fcg_solve: d4est_solver_fcg_solve (src/Solver/d4est_solver_fcg_improved.c:103-346), flexible
+ *   CG with tol = atol + rtol |r_0|; pc = the V-cycle hierarchy whose finest mesh is `mesh`
+ *   (each application = d4est_krylov_pc_multigrid_apply: zero guess, d4b_mg_solve), or NULL
+ *   for the identity (do_not_use_preconditioner = 1).  r2_history (may be NULL) receives
+ *   |r_k|^2 at the start of every iteration, [imax].
+ *   flags = 0 reproduces what the reference executes: its direction updates are written
+ *   d4est_linalg_vec_axpyeqz(c, d, v, d) (:260-262) and axpyeqz copies y into z before adding c x
+ *   (src/LinearAlgebra/d4est_linalg.c:217-221), so with z aliasing x they yield d_k = (1 + c) v_k,
+ *   q_k = (1 + c) w_k.  Iterates and iteration counts match the reference only with that
+ *   arithmetic.  D4B_FCG_TEXTBOOK selects the recurrence the reference's comments state
+ *   (d_k = v_k + c d_{k-1}, Notay & Napov).                                               */
+#define D4B_FCG_TEXTBOOK 1
+int32_t d4b_cg_solve(d4b_mesh_t *mesh, double *u, const double *rhs, int32_t imax, double rtol, double atol);
+int32_t d4b_fcg_solve(d4b_mesh_t *mesh, d4b_mg_t *pc, double *u, const double *rhs, int32_t imax,
+                      double rtol, double atol, int32_t flags, double *r2_history);
+
 #ifdef __cplusplus
 }
 #endif

@@ -26,6 +26,8 @@
 #include <d4est_solver_multigrid_smoother_cheby.h>
 #include <d4est_solver_multigrid.h>
 #include <d4est_krylov_pc_multigrid.h>
+#include <d4est_solver_fcg_improved.h>
+#include <d4est_solver_cg.h>
 #include <d4est_util.h>
 #include <zlog.h>
 #include <time.h>
@@ -166,6 +168,33 @@ dump_tables (FILE * f, d4est_operators_t * ops, int max_deg)
   }
 }
 
+/* the reference's in-house Krylov solvers report progress through zlog only: count their
+ * iterations and record the residual norms by wrapping the callbacks they are handed */
+static d4est_krylov_pc_apply_fcn_t fcg_inner_pc_apply;
+static int fcg_pc_calls, fcg_nodes;
+static double fcg_r2_hist[512];
+
+static void
+fcg_counting_pc_apply (d4est_krylov_pc_t * kpc, double *x, double *y)
+{
+  if (fcg_pc_calls < 512) fcg_r2_hist[fcg_pc_calls] = d4est_linalg_vec_dot (x, x, fcg_nodes);
+  fcg_pc_calls++;
+  fcg_inner_pc_apply (kpc, x, y);
+}
+
+static d4est_apply_operator_fcn_t cg_inner_apply_lhs;
+static int cg_apply_calls;
+
+static void
+cg_counting_apply_lhs (p4est_t * p4est, d4est_ghost_t * ghost, d4est_ghost_data_t * ghost_data,
+                       d4est_elliptic_data_t * prob_vecs, d4est_operators_t * d4est_ops,
+                       d4est_geometry_t * d4est_geom, d4est_quadrature_t * d4est_quad,
+                       d4est_mesh_data_t * d4est_factors, void *user)
+{
+  cg_apply_calls++;
+  cg_inner_apply_lhs (p4est, ghost, ghost_data, prob_vecs, d4est_ops, d4est_geom, d4est_quad, d4est_factors, user);
+}
+
 /* mass-type nonlinearities of the kind the shipped problems use (ConstantDensityStar:
  * residual -2 pi rho (1+u)^5, Jacobian -10 pi rho (1+u)^4 with rho a step in radius,
  * src/Problems/ConstantDensityStar/constant_density_star_fcns.h:64-139) */
@@ -198,7 +227,7 @@ main (int argc, char *argv[])
   const char *ini = argv[1];
   const char *out = argv[2];
   int amr_steps = 0, time_reps = 0, bc_poly = 0, cheby_imax = 0, cheby_eigs_imax = 0, mg_vcycles = 0, use_b200 = 0;
-  int dump_quad = 0;
+  int dump_quad = 0, fcg_imax = 0;
   for (int a = 3; a < argc; a++) {
     if (!strcmp (argv[a], "--amr")) amr_steps = atoi (argv[++a]);
     else if (!strcmp (argv[a], "--time")) time_reps = atoi (argv[++a]);
@@ -207,6 +236,7 @@ main (int argc, char *argv[])
     else if (!strcmp (argv[a], "--cheby")) { cheby_imax = atoi (argv[++a]); cheby_eigs_imax = atoi (argv[++a]); }
     else if (!strcmp (argv[a], "--mg")) { mg_vcycles = atoi (argv[++a]); }
     else if (!strcmp (argv[a], "--quad")) { dump_quad = 1; }
+    else if (!strcmp (argv[a], "--fcg")) { fcg_imax = atoi (argv[++a]); }
     else if (!strcmp (argv[a], "--b200")) { use_b200 = 1; }
     else { fprintf (stderr, "unknown option %s\n", argv[a]); return 2; }
   }
@@ -508,6 +538,48 @@ main (int argc, char *argv[])
                 ref_vcycles, pc_vcycles, sqrt (pnum / pden), tpc[0], tpc[1], pc_builds);
         P4EST_FREE (ypc[0]); P4EST_FREE (ypc[1]);
       }
+
+      /* the reference's own Krylov solver (d4est_solver_fcg_solve, unmodified) driving the two
+       * preconditioners: iteration counts and solutions must agree */
+      if (fcg_imax > 0) {
+        int its[2];
+        double tf[2], *fus[2];
+        for (int which = 0; which < 2; which++) {
+          d4est_solver_multigrid_t *mg_data =
+            d4est_solver_multigrid_data_init (p4est, d4est_ops, d4est_geom, d4est_quad, &d4est_ghost,
+                                              &d4est_ghost_data, d4est_factors, initial_grid_input, ini);
+          d4est_krylov_pc_t *pc = which ? d4est_b200_pc_multigrid_create (mg_data, bctx, NULL)
+                                        : d4est_krylov_pc_multigrid_create (mg_data, NULL);
+          fcg_inner_pc_apply = pc->pc_apply;
+          pc->pc_apply = fcg_counting_pc_apply;
+          fcg_pc_calls = 0; fcg_nodes = local_nodes;
+          d4est_solver_fcg_params_t fp;
+          memset (&fp, 0, sizeof (fp));
+          fp.imax = fcg_imax; fp.rtol = 1e-10; fp.atol = 0.;
+          fus[which] = P4EST_ALLOC_ZERO (double, local_nodes);
+          double *fAu = P4EST_ALLOC_ZERO (double, local_nodes);
+          d4est_elliptic_data_t fv = vecs;
+          fv.u = fus[which]; fv.Au = fAu; fv.rhs = Au_plain;
+          double t4 = wall ();
+          d4est_solver_fcg_solve (p4est, &fv, which ? &fcns_b200 : &fcns_plain, &d4est_ghost, &d4est_ghost_data,
+                                  d4est_ops, d4est_geom, d4est_quad, d4est_factors, &fp, pc, -1, -1);
+          tf[which] = wall () - t4;
+          its[which] = fcg_pc_calls;
+          pc->pc_apply = fcg_inner_pc_apply;
+          if (which) d4est_b200_pc_multigrid_destroy (pc); else d4est_krylov_pc_multigrid_destroy (pc);
+          P4EST_FREE (fAu);
+          d4est_solver_multigrid_data_destroy (mg_data);
+        }
+        double fn = 0., fd = 0.;
+        for (int i = 0; i < local_nodes; i++) {
+          fn += (fus[0][i] - fus[1][i]) * (fus[0][i] - fus[1][i]);
+          fd += fus[0][i] * fus[0][i];
+        }
+        printf ("{\"fcg_iters_reference\": %d, \"fcg_iters_b200_pc\": %d, \"fcg_u_rel_l2_diff\": %.3e, "
+                "\"t_fcg_reference_s\": %.4f, \"t_fcg_b200_pc_s\": %.4f}\n",
+                its[0], its[1], sqrt (fn / fd), tf[0], tf[1]);
+        P4EST_FREE (fus[0]); P4EST_FREE (fus[1]);
+      }
     }
     vecs.Au = Au_tmp;
     P4EST_FREE (Au_b);
@@ -706,6 +778,63 @@ main (int argc, char *argv[])
       printf ("{\"mg_levels\": %d, \"mg_vcycles\": %d, \"t_mg_s\": %.6f, \"r2_first\": %.6e, \"r2_last\": %.6e}\n",
               mg_data->num_of_levels, mg_vcycles, t_mg, r2[0], r2[mg_vcycles]);
       P4EST_FREE (mu); P4EST_FREE (mAu); P4EST_FREE (r2); P4EST_FREE (u_hist);
+      d4est_solver_multigrid_data_destroy (mg_data);
+    }
+    /* the reference's in-house Krylov solvers on A u = rhs (rhs = A u_seeded, u0 = 0):
+     * d4est_solver_fcg_solve (src/Solver/d4est_solver_fcg_improved.c:103-346) preconditioned
+     * with its multigrid (d4est_krylov_pc_multigrid, one V-cycle per application as the ini
+     * file says), and the unpreconditioned d4est_solver_cg_solve (src/Solver/d4est_solver_cg.c:75-197) */
+    if (fcg_imax > 0 && !bc_poly) {
+      d4est_solver_multigrid_t *mg_data =
+        d4est_solver_multigrid_data_init (p4est, d4est_ops, d4est_geom, d4est_quad, &d4est_ghost,
+                                          &d4est_ghost_data, d4est_factors, initial_grid_input, ini);
+      d4est_krylov_pc_t *pc = d4est_krylov_pc_multigrid_create (mg_data, NULL);
+      fcg_inner_pc_apply = pc->pc_apply;
+      pc->pc_apply = fcg_counting_pc_apply;
+      fcg_pc_calls = 0; fcg_nodes = local_nodes;
+      d4est_solver_fcg_params_t fp;
+      memset (&fp, 0, sizeof (fp));
+      fp.imax = fcg_imax; fp.rtol = 1e-10; fp.atol = 0.; fp.do_not_use_preconditioner = 0;
+      fp.checkpoint_every_n_krylov_its = 0;
+      double *fu = P4EST_ALLOC_ZERO (double, local_nodes);
+      double *fAu = P4EST_ALLOC_ZERO (double, local_nodes);
+      d4est_elliptic_data_t fv = vecs;
+      fv.u = fu; fv.Au = fAu; fv.rhs = Au_plain;
+      double t1 = wall ();
+      d4est_solver_fcg_solve (p4est, &fv, &fcns_plain, &d4est_ghost, &d4est_ghost_data, d4est_ops, d4est_geom,
+                              d4est_quad, d4est_factors, &fp, pc, -1, -1);
+      double t_fcg = wall () - t1;
+      double fprm[4] = { (double) fp.imax, fp.rtol, fp.atol, (double) fcg_pc_calls };
+      d4b_dump_put1 (f, "fcg_params", D4B_F64, 4, fprm);
+      d4b_dump_put1 (f, "fcg_u", D4B_F64, local_nodes, fu);
+      d4b_dump_put1 (f, "fcg_r2", D4B_F64, fcg_pc_calls < 512 ? fcg_pc_calls : 512, fcg_r2_hist);
+      /* same, identity preconditioner */
+      const int pc_its = fcg_pc_calls;
+      fp.do_not_use_preconditioner = 1;
+      cg_inner_apply_lhs = fcns_plain.apply_lhs; cg_apply_calls = 0;
+      d4est_elliptic_eqns_t fcns_count = fcns_plain;
+      fcns_count.apply_lhs = cg_counting_apply_lhs;
+      memset (fu, 0, sizeof (double) * local_nodes);
+      d4est_solver_fcg_solve (p4est, &fv, &fcns_count, &d4est_ghost, &d4est_ghost_data, d4est_ops, d4est_geom,
+                              d4est_quad, d4est_factors, &fp, NULL, -1, -1);
+      double nopc_its = (double) (cg_apply_calls - 1);
+      d4b_dump_put1 (f, "fcg_nopc_iters", D4B_F64, 1, &nopc_its);
+      d4b_dump_put1 (f, "fcg_nopc_u", D4B_F64, local_nodes, fu);
+      /* plain CG */
+      d4est_solver_cg_params_t cp;
+      memset (&cp, 0, sizeof (cp));
+      cp.iter = 10 * fcg_imax; cp.rtol = 1e-10; cp.atol = 0.; cp.monitor = 0;
+      cg_apply_calls = 0;
+      memset (fu, 0, sizeof (double) * local_nodes);
+      d4est_solver_cg_solve (p4est, &fv, &fcns_count, &d4est_ghost, &d4est_ghost_data, d4est_ops, d4est_geom,
+                             d4est_quad, d4est_factors, &cp, NULL);
+      double cprm[4] = { (double) cp.iter, cp.rtol, cp.atol, (double) (cg_apply_calls - 1) };
+      d4b_dump_put1 (f, "cg_params", D4B_F64, 4, cprm);
+      d4b_dump_put1 (f, "cg_u", D4B_F64, local_nodes, fu);
+      printf ("{\"fcg_mg_iters\": %d, \"fcg_nopc_iters\": %d, \"cg_iters\": %d, \"t_fcg_mg_s\": %.4f}\n",
+              pc_its, (int) nopc_its, cg_apply_calls - 1, t_fcg);
+      P4EST_FREE (fu); P4EST_FREE (fAu);
+      d4est_krylov_pc_multigrid_destroy (pc);
       d4est_solver_multigrid_data_destroy (mg_data);
     }
     fclose (f);

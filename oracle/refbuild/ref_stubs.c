@@ -19,6 +19,7 @@ STUB (d4est_solver_multigrid_bottom_solver_krylov_petsc_destroy)
 STUB (d4est_geometry_cubed_sphere_vtk_new)
 STUB (d4est_amr_smooth_pred_init)
 STUB (mpsort_mpi)
+STUB (d4est_checkpoint_save)
 
 double
 d4est_power_method ()

@@ -178,3 +178,59 @@ def vcycle(applies, transfers, u, rhs, cheby_imax, eigs_imax, ratio, mult=1.0, u
         us[l + 1] = us[l + 1] + transfers[l].prolong(us[l])
         r = smooth(l + 1)
     return us[top], float(r @ r), eigs
+
+
+# ---- outer Krylov ----------------------------------------------------------------
+def cg(apply, u, rhs, imax, rtol, atol=0.0):
+    """d4est_solver_cg_solve (src/Solver/d4est_solver_cg.c:75-197); returns (u, iterations)"""
+    u = u.copy()
+    r = rhs - apply(u)
+    d = r.copy()
+    delta_new = float(r @ r)
+    delta_0 = delta_new
+    its = 0
+    while its < imax and delta_new > atol * atol + delta_0 * rtol * rtol:
+        Ad = apply(d)
+        alpha = delta_new / float(d @ Ad)
+        u += alpha * d
+        r -= alpha * Ad
+        delta_old = delta_new
+        delta_new = float(r @ r)
+        d = r + (delta_new / delta_old) * d
+        its += 1
+    return u, its
+
+
+def fcg(apply, pc, u, rhs, imax, rtol, atol=0.0, textbook=False):
+    """d4est_solver_fcg_solve (src/Solver/d4est_solver_fcg_improved.c:103-346): flexible CG, truncation 1.
+    pc(r) -> v or None for the identity.  Returns (u, iterations, [|r_k|^2 at the start of iteration k]).
+
+    What the reference EXECUTES differs from the recurrence its comments state: the direction updates
+    are written d4est_linalg_vec_axpyeqz(c, d, v, d) (:260-262), and axpyeqz copies y into z before
+    adding c x (src/LinearAlgebra/d4est_linalg.c:217-221) -- with z aliasing x that yields
+    d_k = (1 + c) v_k and q_k = (1 + c) w_k, not v_k + c d_{k-1}.  Parity means reproducing that
+    (textbook=False); textbook=True is the recurrence of the comments (Notay & Napov)."""
+    u = u.copy()
+    r = rhs - apply(u)
+    tol = atol + rtol * np.sqrt(float(r @ r))
+    hist = []
+    rho = 0.0
+    d = q = None
+    for k in range(imax):
+        hist.append(float(r @ r))
+        v = pc(r) if pc is not None else r.copy()
+        w = apply(v)
+        alpha, beta = float(v @ r), float(v @ w)
+        if k > 0:
+            gamma, rr = float(v @ q), float(r @ r)
+            c = -gamma / rho
+            d = v + c * (d if textbook else v)
+            q = w + c * (q if textbook else w)
+            rho = beta - gamma * gamma / rho
+        else:
+            rho, d, q = beta, v.copy(), w.copy()
+        u += (alpha / rho) * d
+        r -= (alpha / rho) * q
+        if k > 0 and np.sqrt(rr) <= tol:
+            break
+    return u, len(hist), hist

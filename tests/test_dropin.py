@@ -72,3 +72,12 @@ def test_reference_preconditioner_slot(ini, args):
     assert res["pc_vcycles_b200"] == res["pc_vcycles_reference"]
     assert res["pc_y_rel_l2_diff"] < 1e-9
     assert res["pc_hierarchy_builds"] == 1
+
+
+def test_reference_fcg_with_our_preconditioner():
+    """the UNMODIFIED d4est_solver_fcg_solve with pc = d4est_b200_pc_multigrid_create and
+    apply_lhs = d4est_b200_apply_lhs: same Krylov iteration count and solution as the stock run"""
+    lines = run("brick_poisson_mg.ini", "--uniform-deg", "2", "--mg", "1", "--fcg", "30")
+    res = [l for l in lines if "fcg_iters_b200_pc" in l][0]
+    assert res["fcg_iters_b200_pc"] == res["fcg_iters_reference"]
+    assert res["fcg_u_rel_l2_diff"] < 1e-9

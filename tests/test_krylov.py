@@ -1,0 +1,111 @@
+"""Outer Krylov loops: the reference's in-house CG and multigrid-preconditioned
+flexible CG, device-resident.  tests/golden/brick_mg_l2_p2 holds the iterates and iteration counts of
+the UNMODIFIED d4est_solver_fcg_solve / d4est_solver_cg_solve (oracle/ref_driver.c --fcg)."""
+import numpy as np
+import pytest
+
+from oracle_lib import Oracle
+from solver_ref import Transfer, cg, fcg, vcycle
+
+CASE = "brick_mg_l2_p2"
+
+
+def rel(a, b):
+    return np.linalg.norm(a - b) / np.linalg.norm(b)
+
+
+def hierarchy(A):
+    from disco4est_b200.brick import brick_hierarchy
+
+    return brick_hierarchy(2, int(A["deg"][0]))
+
+
+def test_restatement_matches_reference_krylov(golden):
+    """pins tests/solver_ref.py:cg / fcg (on the pinned oracle apply and V-cycle) to the reference"""
+    A = golden(CASE)
+    O = Oracle(A)
+    rhs = np.ascontiguousarray(A["mg_rhs"])
+    imax, rtol, atol, its_ref = A["cg_params"]
+    u, its = cg(O.apply, np.zeros(rhs.size), rhs, int(imax), rtol, atol)
+    assert its == int(its_ref)
+    assert rel(u, A["cg_u"]) < 1e-9
+    imax, rtol, atol, its_ref = A["fcg_params"]
+    u, its, _ = fcg(O.apply, None, np.zeros(rhs.size), rhs, int(imax), rtol, atol)
+    assert its == int(A["fcg_nopc_iters"][0])
+    assert rel(u, A["fcg_nopc_u"]) < 1e-9
+    # multigrid-preconditioned: one V-cycle from a zero guess per application
+    descs, transfers = hierarchy(A)
+    orcs = [Oracle(d) for d in descs]
+    trs = [Transfer(descs[l], descs[l + 1], *transfers[l]) for l in range(len(descs) - 1)]
+    cimax, eimax, ratio, mult, use_new = (float(x) for x in A["mg_cheby_params"])
+
+    def pc(r):
+        return vcycle([o.apply for o in orcs], trs, np.zeros(r.size), r, int(cimax), int(eimax), ratio, mult, int(use_new))[0]
+
+    u, its, hist = fcg(O.apply, pc, np.zeros(rhs.size), rhs, int(imax), rtol, atol)
+    assert its == int(its_ref) == len(A["fcg_r2"])
+    assert np.allclose(hist, A["fcg_r2"], rtol=1e-5)
+    assert rel(u, A["fcg_u"]) < 1e-9
+
+
+@pytest.fixture()
+def gpu_case(golden):
+    from disco4est_b200 import Mesh
+    from disco4est_b200.runtime import Multigrid, cheby_params
+
+    A = golden(CASE)
+    descs, transfers = hierarchy(A)
+    meshes = [Mesh(d) for d in descs]
+    cimax, eimax, ratio, mult, use_new = (float(x) for x in A["mg_cheby_params"])
+    mg = Multigrid(meshes, transfers, cheby_params(int(cimax), int(eimax), ratio, mult, int(use_new)), vcycle_imax=1,
+                   vcycle_rtol=1e-15)
+    yield A, meshes[-1], mg
+    mg.close()
+    for m in meshes:
+        m.close()
+
+
+@pytest.mark.gpu
+def test_gpu_cg_matches_reference(gpu_case):
+    A, mesh, _ = gpu_case
+    rhs = np.ascontiguousarray(A["mg_rhs"])
+    imax, rtol, atol, its_ref = A["cg_params"]
+    u = np.zeros(rhs.size)
+    its = mesh.cg_solve(u, rhs, int(imax), rtol, atol)
+    assert its == int(its_ref)
+    assert rel(u, A["cg_u"]) < 1e-9
+    # iteration cap is honoured exactly
+    u2 = np.zeros(rhs.size)
+    assert mesh.cg_solve(u2, rhs, 7, rtol, atol) == 7
+
+
+@pytest.mark.gpu
+def test_gpu_fcg_matches_reference(gpu_case):
+    A, mesh, mg = gpu_case
+    rhs = np.ascontiguousarray(A["mg_rhs"])
+    imax, rtol, atol, its_ref = A["fcg_params"]
+    # identity preconditioner (do_not_use_preconditioner = 1)
+    u = np.zeros(rhs.size)
+    its, _ = mesh.fcg_solve(u, rhs, int(imax), rtol, atol)
+    assert its == int(A["fcg_nopc_iters"][0])
+    assert rel(u, A["fcg_nopc_u"]) < 1e-9
+    # device V-cycle as the preconditioner: same iteration count, residual history and iterate
+    u = np.zeros(rhs.size)
+    its, hist = mesh.fcg_solve(u, rhs, int(imax), rtol, atol, pc=mg)
+    assert its == int(its_ref)
+    assert np.allclose(hist, A["fcg_r2"], rtol=1e-5)
+    assert rel(u, A["fcg_u"]) < 1e-9
+    # the recurrence of the reference's comments (D4B_FCG_TEXTBOOK) converges where the executed one stalls
+    O = Oracle(A)
+    u = np.zeros(rhs.size)
+    its, _ = mesh.fcg_solve(u, rhs, 200, rtol, atol, textbook=True)
+    u_want, its_want, _ = fcg(O.apply, None, np.zeros(rhs.size), rhs, 200, rtol, atol, textbook=True)
+    assert abs(its - its_want) <= 1 and rel(u, u_want) < 1e-8
+    u = np.zeros(rhs.size)
+    # device pointers: same bits
+    import torch
+
+    its, _ = mesh.fcg_solve(u, rhs, int(imax), rtol, atol, pc=mg)
+    du = torch.zeros(rhs.size, dtype=torch.float64, device="cuda")
+    its2, _ = mesh.fcg_solve(du, torch.from_numpy(rhs).cuda(), int(imax), rtol, atol, pc=mg)
+    assert its2 == its and np.array_equal(du.cpu().numpy(), u)
