@@ -55,12 +55,20 @@ struct FlatCfg {
   static constexpr int NN = N * N, N3 = N * N * N;
   // threads per block by N = 2..8, from an A/B sweep on B200 (profiles/): small
   // blocks keep barriers cheap, a one-warp block needs none
-  static constexpr int kThreads[9] = {0, 0, 32, 64, 32, 128, 128, 64, 64};
+  // (D4B_FLAT_THREADS / D4B_FLAT_MINB: compile-time overrides for those sweeps, profiles/build_variants.sh)
+#ifndef D4B_FLAT_THREADS
+#define D4B_FLAT_THREADS {0, 0, 32, 64, 32, 128, 128, 64, 64}
+#endif
+#ifndef D4B_FLAT_MINB
+#define D4B_FLAT_MINB {0, 0, 1, 1, 24, 1, 1, 1, 1}
+#endif
+  static constexpr int kThreads[9] = D4B_FLAT_THREADS;
+  static constexpr int kMinBlocks[9] = D4B_FLAT_MINB;   // resident blocks per SM the register budget is cut for
   static constexpr int THREADS = kThreads[N];
   static constexpr int EPB = THREADS / NN;
   // V0,V1,V2 + per-thread face results [6][2][NN] + 6 face metas (2 doubles each)
   static constexpr int SH_PER_ELEM = 3 * N3 + 12 * NN + 12;
-  static constexpr int MIN_BLOCKS = (N == 4) ? 24 : 1;
+  static constexpr int MIN_BLOCKS = kMinBlocks[N];
 };
 
 // a one-warp block only needs a warp-level barrier
