@@ -72,6 +72,60 @@ class MeshDesc(C.Structure):
     ]
 
 
+class GeomDesc(C.Structure):
+    """d4b_geom_desc_t"""
+
+    _fields_ = [
+        ("geom_type", C.c_int32),
+        ("face_h_type", C.c_int32),
+        ("compactify_inner_shell", C.c_int32),
+        ("compactify_outer_shell", C.c_int32),
+        ("X0", C.c_double), ("X1", C.c_double), ("Y0", C.c_double), ("Y1", C.c_double),
+        ("Z0", C.c_double), ("Z1", C.c_double),
+        ("R0", C.c_double), ("R1", C.c_double), ("R2", C.c_double),
+        ("elem_tree", _I32P), ("elem_q", _I32P), ("elem_dq", _I32P),
+        ("ghost_tree", _I32P), ("ghost_q", _I32P), ("ghost_dq", _I32P),
+    ]
+
+
+GEOM_ARRAY_FIELDS = ["xyz", "J_quad", "rst_xyz_quad", "sj_m_mortar_quad", "n_m_mortar_quad",
+                     "drst_dxyz_m_mortar_quad", "drst_dxyz_p_mortar_quad_porder", "hm_mortar_quad", "hp_mortar_quad"]
+
+
+class GeomArrays(C.Structure):
+    """d4b_geom_arrays_t (addresses; host or device)"""
+
+    _fields_ = [(name, C.c_void_p) for name in GEOM_ARRAY_FIELDS]
+
+
+GEOM_TYPE = {"brick": 0, "cubed_sphere": 1}
+FACE_H = {"j_div_sj_quad": 0, "j_div_sj_min_lobatto": 1, "j_div_sj_mean_lobatto": 2, "j_div_sj_max_lobatto": 3,
+          "tree_h": 4, "volume_div_area": 5}
+
+
+def make_geom_desc(g):
+    """GeomDesc from a dict: geom_type / face_h_type (names or numbers), the map parameters and the
+    element positions elem_tree, elem_q, elem_dq (+ ghost_*).  Returns (desc, keepalive)."""
+    d = GeomDesc()
+    keep = []
+    gt, fh = g["geom_type"], g["face_h_type"]
+    d.geom_type = GEOM_TYPE[gt] if isinstance(gt, str) else int(np.asarray(gt).reshape(-1)[0])
+    d.face_h_type = FACE_H[fh] if isinstance(fh, str) else int(np.asarray(fh).reshape(-1)[0])
+    for name, typ in GeomDesc._fields_:
+        if name in ("geom_type", "face_h_type") or name not in g or g[name] is None:
+            continue
+        if typ is _I32P:
+            a = np.ascontiguousarray(g[name], dtype=np.int32).reshape(-1)
+            if a.size == 0:
+                a = np.zeros(1, np.int32)
+            keep.append(a)
+            setattr(d, name, a.ctypes.data_as(_I32P))
+        else:
+            v = np.asarray(g[name]).reshape(-1)[0]
+            setattr(d, name, float(v) if typ is C.c_double else int(v))
+    return d, keep
+
+
 class ChebyParams(C.Structure):
     _fields_ = [
         ("cheby_imax", C.c_int32),

@@ -1,0 +1,514 @@
+// d4b_geom.cu -- geometric factors generated on the device.
+//
+// Replaces, for the analytic tree maps, the geometry half of d4est_mesh_data_compute
+// (src/Mesh/d4est_mesh.c:2543-2755: J_quad, rst_xyz_quad, xyz), the element size
+// parameters (d4est_mesh.c:1620-1830: volume, face area, J/sj statistics on the LGL
+// nodes) and d4est_mesh_compute_mortar_quadrature_quantities (d4est_mesh.c:481-1140 with
+// d4est_mortars_compute_geometric_data_on_mortar_aux, src/Mesh/d4est_mortars.c:10-277:
+// sj, n, drst_dxyz on both sides of every mortar, hm, hp).
+//
+// One thread per quadrature point: it evaluates dX/d(rst) of the tree map, the determinant,
+// the inverse (cofactor formulas of d4est_geometry.c:877-1030) and stores the reference's
+// SoA planes -- a streaming kernel bound by the HBM writes (10 doubles per volume point,
+// 24 per mortar point).  The map derivatives are differentiated by hand from the maps
+// X(a,b,c) (d4est_geometry_brick.c:60-110, d4est_geometry_cubed_sphere.c:127-167, :315-400);
+// the reference evaluates machine-generated closed forms of the same derivatives
+// (d4est_geometry_cubed_sphere.c:847-1370), so the two agree to round-off, not bit for bit.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <vector>
+#include "d4b_internal.h"
+
+namespace {
+
+constexpr double kRoot = 1073741824.0;   // P8EST_ROOT_LEN = 2^30
+constexpr double kPi4 = 0.78539816339744830962;
+
+struct GeomP {
+  int type, face_h, ci, co;
+  double X0, X1, Y0, Y1, Z0, Z1, R0, R1, R2, Cl;
+};
+
+struct GeomTab {
+  double gx[D4B_MAXNQ][D4B_MAXNQ];   // gx[deg_quad][k] Gauss nodes
+  double lx[D4B_MAXN][D4B_MAXN];     // lx[deg][k] LGL nodes
+  double lw[D4B_MAXN][D4B_MAXN];     // LGL weights
+};
+__constant__ GeomTab c_gt;
+
+struct ElemPos { int tree, q[3], dq; };
+
+// radius law of a shell and its c-derivative (c in [1,2]); compactified: R = m/(c - t)
+__device__ __forceinline__ void shell_radius(double Ra, double Rb, int compactify, double c, double &R, double &Rc) {
+  if (compactify) {
+    const double m = 1. / ((1. / Rb) - (1. / Ra));
+    const double t = (Ra - 2. * Rb) / (Ra - Rb);
+    R = m / (c - t);
+    Rc = -m / ((c - t) * (c - t));
+  } else {
+    R = Ra * (2. - c) + Rb * (c - 1.);
+    Rc = Rb - Ra;
+  }
+}
+
+__device__ __forceinline__ void rotate_rows(int tree, const double top[3][3], double out[3][3]) {
+  // xyz of wedge (tree % 6) from the "top" wedge frame, d4est_geometry_cubed_sphere.c:372-399
+  int src[3]; double sg[3];
+  switch (tree % 6) {
+    case 0: src[0] = 0; sg[0] = 1; src[1] = 2; sg[1] = -1; src[2] = 1; sg[2] = 1; break;
+    case 1: src[0] = 0; sg[0] = 1; src[1] = 1; sg[1] = 1; src[2] = 2; sg[2] = 1; break;
+    case 2: src[0] = 0; sg[0] = 1; src[1] = 2; sg[1] = 1; src[2] = 1; sg[2] = -1; break;
+    case 3: src[0] = 2; sg[0] = 1; src[1] = 0; sg[1] = -1; src[2] = 1; sg[2] = -1; break;
+    case 4: src[0] = 1; sg[0] = -1; src[1] = 0; sg[1] = -1; src[2] = 2; sg[2] = -1; break;
+    default: src[0] = 2; sg[0] = -1; src[1] = 0; sg[1] = -1; src[2] = 1; sg[2] = 1; break;
+  }
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int d = 0; d < 3; ++d) out[i][d] = sg[i] * top[src[i]][d];
+}
+
+// X and dX/d(rst) at reference point rst of the element at (tree, q, dq).
+// want_x: also fill x[3].
+__device__ void geom_map(const GeomP &P, const ElemPos &e, const double rst[3], double dx[3][3], double *x) {
+  const double h = (double)e.dq / kRoot;   // element width in tree coordinates [0,1]
+  double tc[3];
+#pragma unroll
+  for (int d = 0; d < 3; ++d) tc[d] = (double)e.q[d] / kRoot + h * .5 * (rst[d] + 1.);
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j) dx[i][j] = 0.;
+  if (P.type == D4B_GEOM_BRICK) {
+    dx[0][0] = (P.X1 - P.X0) * h * .5;
+    dx[1][1] = (P.Y1 - P.Y0) * h * .5;
+    dx[2][2] = (P.Z1 - P.Z0) * h * .5;
+    if (x) {
+      x[0] = (P.X1 - P.X0) * tc[0] + P.X0;
+      x[1] = (P.Y1 - P.Y0) * tc[1] + P.Y0;
+      x[2] = (P.Z1 - P.Z0) * tc[2] + P.Z0;
+    }
+    return;
+  }
+  // cubed sphere: vertex space (a,b) in [-1,1]^2, c in [1,2]; centre cube [-1,1]^3
+  if (e.tree == 12) {
+    dx[0][0] = dx[1][1] = dx[2][2] = P.Cl * h;
+    if (x)
+      for (int d = 0; d < 3; ++d) x[d] = (2. * tc[d] - 1.) * P.Cl;
+    return;
+  }
+  const double a = 2. * tc[0] - 1., b = 2. * tc[1] - 1., c = tc[2] + 1.;
+  const double da = h, db = h, dc = .5 * h;   // d(a,b,c)/d(r,s,t)
+  const double T = tan(a * kPi4), U = tan(b * kPi4);
+  const double Tp = kPi4 * (1. + T * T), Up = kPi4 * (1. + U * U);
+  double top[3][3], xt[3];
+  if (e.tree < 6) {
+    // outer shell: (X,Y,Z) = q (T, U, 1), q = R(c) / sqrt(T^2 + U^2 + 1)
+    double R, Rc;
+    shell_radius(P.R1, P.R2, P.co, c, R, Rc);
+    const double rho2 = T * T + U * U + 1., irho = 1. / sqrt(rho2), irho3 = irho / rho2;
+    top[0][0] = R * (U * U + 1.) * irho3 * Tp * da;
+    top[0][1] = -R * T * U * irho3 * Up * db;
+    top[0][2] = T * Rc * irho * dc;
+    top[1][0] = -R * T * U * irho3 * Tp * da;
+    top[1][1] = R * (T * T + 1.) * irho3 * Up * db;
+    top[1][2] = U * Rc * irho * dc;
+    top[2][0] = -R * T * irho3 * Tp * da;
+    top[2][1] = -R * U * irho3 * Up * db;
+    top[2][2] = Rc * irho * dc;
+    const double q = R * irho;
+    xt[0] = q * T; xt[1] = q * U; xt[2] = q;
+  } else {
+    // inner shell: blends the cube face (w = 0) into the sphere (w = 1), w = c - 1:
+    // x = (1-w) a + w T, y = (1-w) b + w U, q = R(c) / sqrt(3 - 2w + w (T^2 + U^2))
+    double R, Rc;
+    shell_radius(P.R0, P.R1, P.ci, c, R, Rc);
+    const double w = c - 1.;
+    const double xx = (1. - w) * a + w * T, yy = (1. - w) * b + w * U;
+    const double x_a = (1. - w) + w * Tp, x_c = T - a, y_b = (1. - w) + w * Up, y_c = U - b;
+    const double S = 3. - 2. * w + w * (T * T + U * U);
+    const double S_a = 2. * w * T * Tp, S_b = 2. * w * U * Up, S_c = -2. + T * T + U * U;
+    const double isig = 1. / sqrt(S), isig3 = isig / S;
+    const double q = R * isig;
+    const double q_a = -.5 * R * S_a * isig3, q_b = -.5 * R * S_b * isig3, q_c = Rc * isig - .5 * R * S_c * isig3;
+    top[0][0] = (q_a * xx + q * x_a) * da;
+    top[0][1] = q_b * xx * db;
+    top[0][2] = (q_c * xx + q * x_c) * dc;
+    top[1][0] = q_a * yy * da;
+    top[1][1] = (q_b * yy + q * y_b) * db;
+    top[1][2] = (q_c * yy + q * y_c) * dc;
+    top[2][0] = q_a * da;
+    top[2][1] = q_b * db;
+    top[2][2] = q_c * dc;
+    xt[0] = q * xx; xt[1] = q * yy; xt[2] = q;
+  }
+  rotate_rows(e.tree, top, dx);
+  if (x) {
+    double xr[3][3], xi[3][3] = {{xt[0], 0, 0}, {xt[1], 0, 0}, {xt[2], 0, 0}};
+    rotate_rows(e.tree, xi, xr);
+    x[0] = xr[0][0]; x[1] = xr[1][0]; x[2] = xr[2][0];
+  }
+}
+
+// determinant and cofactors: cof[i][j] = J * d(rst_i)/d(xyz_j)   (d4est_geometry.c:877-1030)
+__device__ __forceinline__ double cofactors(const double dx[3][3], double cof[3][3]) {
+  const double xr = dx[0][0], xs = dx[0][1], xt = dx[0][2];
+  const double yr = dx[1][0], ys = dx[1][1], yt = dx[1][2];
+  const double zr = dx[2][0], zs = dx[2][1], zt = dx[2][2];
+  cof[0][0] = (ys * zt - zs * yt);
+  cof[0][1] = -(xs * zt - zs * xt);
+  cof[0][2] = (xs * yt - ys * xt);
+  cof[1][0] = -(yr * zt - zr * yt);
+  cof[1][1] = (xr * zt - zr * xt);
+  cof[1][2] = -(xr * yt - yr * xt);
+  cof[2][0] = (yr * zs - zr * ys);
+  cof[2][1] = -(xr * zs - zr * xs);
+  cof[2][2] = (xr * ys - yr * xs);
+  return xr * (ys * zt - zs * yt) - yr * (xs * zt - zs * xt) + zr * (xs * yt - ys * xt);
+}
+
+struct GeomArgs {
+  GeomP P;
+  int n_local, n_ghost, n_sides;
+  int64_t local_nodes, LQ, MP;
+  const int32_t *deg, *deg_quad, *ghost_deg, *ghost_deg_quad;
+  const int64_t *nodal_stride, *quad_stride;
+  const int32_t *tree, *q, *dq, *gtree, *gq, *gdq;
+  const int32_t *faces_m, *faces_p, *f_m, *f_p, *e_m, *e_p, *perm, *sub;
+  const int64_t *mstride;
+  // element sizes [n_local + n_ghost] / [..][6]
+  double *vol, *area, *jmin, *jmean, *jmax;
+  // outputs
+  double *xyz, *J, *rst_xyz, *sj, *n, *drm, *drp, *hm, *hp;
+};
+
+__device__ __forceinline__ ElemPos elem_pos(const GeomArgs &A, int32_t ref) {
+  ElemPos e;
+  if (ref >= 0) {
+    e.tree = A.tree[ref]; e.dq = A.dq[ref];
+    e.q[0] = A.q[3 * ref]; e.q[1] = A.q[3 * ref + 1]; e.q[2] = A.q[3 * ref + 2];
+  } else {
+    const int g = -ref - 1;
+    e.tree = A.gtree[g]; e.dq = A.gdq[g];
+    e.q[0] = A.gq[3 * g]; e.q[1] = A.gq[3 * g + 1]; e.q[2] = A.gq[3 * g + 2];
+  }
+  return e;
+}
+
+// ---- volume points: one block per element ----------------------------------
+__global__ void geom_volume_kernel(GeomArgs A) {
+  const int e = blockIdx.x;
+  const ElemPos pos = elem_pos(A, e);
+  if (A.J) {
+    const int dq = A.deg_quad[e], nq = dq + 1, n3 = nq * nq * nq;
+    const int64_t qs = A.quad_stride[e];
+    for (int k = threadIdx.x; k < n3; k += blockDim.x) {
+      const double rst[3] = {c_gt.gx[dq][k % nq], c_gt.gx[dq][(k / nq) % nq], c_gt.gx[dq][k / (nq * nq)]};
+      double dx[3][3], cof[3][3];
+      geom_map(A.P, pos, rst, dx, nullptr);
+      const double J = cofactors(dx, cof);
+      A.J[qs + k] = J;
+      if (A.rst_xyz)
+#pragma unroll
+        for (int i = 0; i < 3; ++i)
+#pragma unroll
+          for (int j = 0; j < 3; ++j) A.rst_xyz[(int64_t)(i * 3 + j) * A.LQ + qs + k] = cof[i][j] / J;
+    }
+  }
+  if (A.xyz) {
+    const int dg = A.deg[e], n = dg + 1, n3 = n * n * n;
+    const int64_t ns = A.nodal_stride[e];
+    for (int k = threadIdx.x; k < n3; k += blockDim.x) {
+      const double rst[3] = {c_gt.lx[dg][k % n], c_gt.lx[dg][(k / n) % n], c_gt.lx[dg][k / (n * n)]};
+      double dx[3][3], x[3];
+      geom_map(A.P, pos, rst, dx, x);
+      for (int d = 0; d < 3; ++d) A.xyz[(int64_t)d * A.local_nodes + ns + k] = x[d];
+    }
+  }
+}
+
+__device__ __forceinline__ void face_rst(int f, double ra, double rb, double rst[3]) {
+  // d4est_geometry_get_face_info (d4est_geometry.c:1378-1415): a = lower tangential direction
+  const int c = f >> 1, a = (c == 0) ? 1 : 0, b = (c == 2) ? 1 : 2;
+  rst[a] = ra; rst[b] = rb; rst[c] = (f & 1) ? 1. : -1.;
+}
+
+// ---- element sizes on the LGL nodes (d4est_mesh.c:1620-1830): thread per (element, item)
+// item 0: volume = sum w J; items 1..6: face f: area = sum w sj, min / mean / max of J/sj
+__global__ void geom_size_kernel(GeomArgs A) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int Et = A.n_local + A.n_ghost;
+  if (t >= (int64_t)Et * 7) return;
+  const int el = (int)(t / 7), item = (int)(t % 7);
+  const int32_t ref = el < A.n_local ? el : -(el - A.n_local) - 1;
+  const ElemPos pos = elem_pos(A, ref);
+  const int dg = el < A.n_local ? A.deg[el] : A.ghost_deg[el - A.n_local], n = dg + 1;
+  double dx[3][3], cof[3][3];
+  if (item == 0) {
+    double v = 0.;
+    for (int k = 0; k < n * n * n; ++k) {
+      const int i0 = k % n, i1 = (k / n) % n, i2 = k / (n * n);
+      const double rst[3] = {c_gt.lx[dg][i0], c_gt.lx[dg][i1], c_gt.lx[dg][i2]};
+      geom_map(A.P, pos, rst, dx, nullptr);
+      v += c_gt.lw[dg][i0] * c_gt.lw[dg][i1] * c_gt.lw[dg][i2] * cofactors(dx, cof);
+    }
+    A.vol[el] = v;
+    return;
+  }
+  const int f = item - 1, i0 = f >> 1;
+  double ar = 0., mn = 1e300, mx = -1e300, sum = 0.;
+  for (int k = 0; k < n * n; ++k) {
+    double rst[3];
+    face_rst(f, c_gt.lx[dg][k % n], c_gt.lx[dg][k / n], rst);
+    geom_map(A.P, pos, rst, dx, nullptr);
+    const double J = cofactors(dx, cof);
+    const double sj = sqrt(cof[i0][0] * cof[i0][0] + cof[i0][1] * cof[i0][1] + cof[i0][2] * cof[i0][2]);
+    ar += c_gt.lw[dg][k % n] * c_gt.lw[dg][k / n] * sj;
+    const double r = J / sj;
+    mn = fmin(mn, r); mx = fmax(mx, r);
+    if (k > 0) sum += r;   // d4est_util_mean_dbl_array (src/Utilities/d4est_util.c:678-685) skips entry 0
+  }
+  A.area[(int64_t)el * 6 + f] = ar;
+  A.jmin[(int64_t)el * 6 + f] = mn;
+  A.jmax[(int64_t)el * 6 + f] = mx;
+  A.jmean[(int64_t)el * 6 + f] = sum / (double)(n * n);
+}
+
+// (+)-ordered linear index of the (-)-ordered face point (a,b), see d4b_generic.cu
+__device__ __forceinline__ int perm_index_g(int n, int perm, int a, int b) {
+  int row = (perm & 4) ? a : b, col = (perm & 4) ? b : a;
+  if (perm & 2) row = n - 1 - row;
+  if (perm & 1) col = n - 1 - col;
+  return row * n + col;
+}
+
+// element whose face carries mortar sub-face c of a side that starts at element e0
+// (d4est_mortars_compute_qcoords_on_mortar, d4est_mortars.c:419-470): the sub-face's own
+// element when the side has as many faces as the mortar, else the virtual child of e0
+__device__ __forceinline__ ElemPos mortar_elem(const ElemPos &e0, int faces_side, int faces_mortar, int f, int c) {
+  ElemPos r = e0;
+  if (faces_mortar == 1) return r;
+  const int nd = f >> 1, ta = (nd == 0) ? 1 : 0, tb = (nd == 2) ? 1 : 2;
+  const bool hanging = faces_side != faces_mortar;
+  const int step = hanging ? e0.dq / 2 : e0.dq;
+  if (hanging) {
+    r.dq = e0.dq / 2;
+    if (f & 1) r.q[nd] += e0.dq / 2;
+  }
+  r.q[ta] += (c & 1) * step;
+  r.q[tb] += ((c >> 1) & 1) * step;
+  return r;
+}
+
+__device__ __forceinline__ int ref_degq(const GeomArgs &A, int32_t r) {
+  return r >= 0 ? A.deg_quad[r] : A.ghost_deg_quad[-r - 1];
+}
+
+__device__ __forceinline__ double side_h(const GeomArgs &A, int32_t ref, int f, double jdsj, int dq0) {
+  const int64_t el = ref >= 0 ? ref : (int64_t)A.n_local + (-ref - 1);
+  switch (A.P.face_h) {
+    case D4B_FACE_H_J_DIV_SJ_QUAD: return jdsj;
+    case D4B_FACE_H_TREE_H: return (double)dq0 / kRoot;
+    case D4B_FACE_H_VOLUME_DIV_AREA: return A.vol[el] / A.area[el * 6 + f];
+    case D4B_FACE_H_J_DIV_SJ_MIN_LOBATTO: return A.jmin[el * 6 + f];
+    case D4B_FACE_H_J_DIV_SJ_MEAN_LOBATTO: return A.jmean[el * 6 + f];
+    default: return A.jmax[el * 6 + f];
+  }
+}
+
+// ---- mortar points: one block per flux side ---------------------------------
+__global__ void geom_mortar_kernel(GeomArgs A) {
+  const int s = blockIdx.x;
+  const int faces_m = A.faces_m[s], faces_p = A.faces_p[s], f_m = A.f_m[s], f_p = A.f_p[s], perm = A.perm[s];
+  const int M = faces_m > faces_p ? faces_m : faces_p;
+  const int32_t *e_m = A.e_m + 4 * s, *e_p = A.e_p + 4 * s, *sub = A.sub + 4 * s;
+  const int64_t S = A.mstride[s];
+  int nq[4], off[4], offp[4], nqp[4], T = 0;
+  int32_t em[4], ep[4];
+  for (int i = 0; i < M; ++i) {
+    em[i] = e_m[faces_m == 4 ? i : 0];
+    ep[i] = faces_p ? e_p[faces_p == 4 ? sub[i] : 0] : 0;
+    int q = ref_degq(A, em[i]);
+    if (faces_p) q = max(q, ref_degq(A, ep[i]));
+    nq[i] = q + 1;
+    off[i] = T;
+    T += nq[i] * nq[i];
+  }
+  for (int i = 0; i < M; ++i) nqp[M == 4 ? sub[i] : i] = nq[i] * nq[i];
+  for (int j = 0, acc = 0; j < M; ++j) { offp[j] = acc; acc += nqp[j]; }
+  const ElemPos m0 = elem_pos(A, e_m[0]);
+  ElemPos p0 = m0;
+  if (faces_p) p0 = elem_pos(A, e_p[0]);
+  const int i0m = f_m >> 1, i0p = f_p >> 1;
+  const double sgm = (f_m & 1) ? 1. : -1.;
+  for (int i = 0; i < M; ++i) {
+    const int n1 = nq[i], dqd = n1 - 1;
+    const ElemPos me = mortar_elem(m0, faces_m, M, f_m, i);
+    const int j = (M == 4) ? sub[i] : 0;
+    ElemPos pe = p0;
+    if (faces_p) pe = mortar_elem(p0, faces_p, M, f_p, j);
+    for (int k = threadIdx.x; k < n1 * n1; k += blockDim.x) {
+      double rst[3], dx[3][3], cof[3][3];
+      face_rst(f_m, c_gt.gx[dqd][k % n1], c_gt.gx[dqd][k / n1], rst);
+      geom_map(A.P, me, rst, dx, nullptr);
+      const double J = cofactors(dx, cof);
+      double nsj[3], sj = 0.;
+      for (int d = 0; d < 3; ++d) { nsj[d] = sgm * cof[i0m][d]; sj += nsj[d] * nsj[d]; }
+      sj = sqrt(sj);
+      const int64_t ks = S + off[i] + k;
+      if (A.sj) A.sj[ks] = sj;
+      if (A.n)
+        for (int d = 0; d < 3; ++d) A.n[3 * S + (int64_t)d * T + off[i] + k] = nsj[d] / sj;
+      if (A.drm)
+        for (int a = 0; a < 3; ++a)
+          for (int l = 0; l < 3; ++l) A.drm[9 * S + (int64_t)(l + 3 * a) * T + off[i] + k] = cof[l][a] / J;
+      if (A.hm) A.hm[ks] = side_h(A, em[i], f_m, J / sj, m0.dq);
+      if (faces_p) {
+        const int kp = perm_index_g(n1, perm, k % n1, k / n1);
+        face_rst(f_p, c_gt.gx[dqd][kp % n1], c_gt.gx[dqd][kp / n1], rst);
+        geom_map(A.P, pe, rst, dx, nullptr);
+        const double Jp = cofactors(dx, cof);
+        if (A.drp)
+          for (int a = 0; a < 3; ++a)
+            for (int l = 0; l < 3; ++l)
+              A.drp[9 * S + (int64_t)(l + 3 * a) * T + offp[j] + kp] = cof[l][a] / Jp;
+        if (A.hp) {
+          const double sjp = sqrt(cof[i0p][0] * cof[i0p][0] + cof[i0p][1] * cof[i0p][1] + cof[i0p][2] * cof[i0p][2]);
+          A.hp[ks] = side_h(A, ep[i], f_p, Jp / sjp, p0.dq);
+        }
+      } else {
+        if (A.hp) A.hp[ks] = 0.;
+        if (A.drp)
+          for (int a = 0; a < 9; ++a) A.drp[9 * S + (int64_t)a * T + off[i] + k] = 0.;
+      }
+    }
+  }
+}
+
+bool is_device_ptr(const void *p) {
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
+}
+
+struct DevBuf {
+  std::vector<void *> owned;
+  template <typename T>
+  T *up(const T *h, size_t n) {
+    T *p = nullptr;
+    D4B_CUDA(cudaMalloc(&p, std::max<size_t>(n, 1) * sizeof(T)));
+    if (n && h) D4B_CUDA(cudaMemcpy(p, h, n * sizeof(T), cudaMemcpyHostToDevice));
+    owned.push_back(p);
+    return p;
+  }
+  ~DevBuf() { for (void *p : owned) cudaFree(p); }
+};
+
+void upload_tables() {
+  static bool done = false;
+  if (done) return;
+  GeomTab t;
+  memset(&t, 0, sizeof(t));
+  std::vector<double> x(D4B_MAXNQ), w(D4B_MAXNQ);
+  for (int dq = 1; dq < D4B_MAXNQ; ++dq) {
+    d4b_tab_gauss(dq + 1, x.data(), w.data());
+    for (int k = 0; k <= dq; ++k) t.gx[dq][k] = x[k];
+  }
+  for (int dg = 1; dg < D4B_MAXN; ++dg) {
+    d4b_tab_lobatto(dg + 1, x.data(), w.data());
+    for (int k = 0; k <= dg; ++k) { t.lx[dg][k] = x[k]; t.lw[dg][k] = w[k]; }
+  }
+  D4B_CUDA(cudaMemcpyToSymbol(c_gt, &t, sizeof(t)));
+  done = true;
+}
+
+}  // namespace
+
+extern "C" void d4b_geom_compute(const d4b_mesh_desc_t *d, const d4b_geom_desc_t *g, const d4b_geom_arrays_t *out) {
+  D4B_CHECK(d && g && out, "d4b_geom_compute: NULL argument");
+  D4B_CHECK(d4b_device_count() > 0, "d4b_geom_compute: no CUDA device (there is no CPU fallback)");
+  D4B_CHECK(g->geom_type == D4B_GEOM_BRICK || g->geom_type == D4B_GEOM_CUBED_SPHERE,
+            "d4b_geom_compute: unknown geometry type %d", g->geom_type);
+  D4B_CHECK(g->face_h_type >= D4B_FACE_H_J_DIV_SJ_QUAD && g->face_h_type <= D4B_FACE_H_VOLUME_DIV_AREA,
+            "d4b_geom_compute: face_h_type %d is not supported", g->face_h_type);
+  D4B_CHECK(g->elem_tree && g->elem_q && g->elem_dq, "d4b_geom_compute: element positions missing");
+  D4B_CHECK(d->n_ghost == 0 || (g->ghost_tree && g->ghost_q && g->ghost_dq), "d4b_geom_compute: ghost positions missing");
+  upload_tables();
+  const int E = d->n_local, Gh = d->n_ghost, Ns = d->n_sides;
+  for (int e = 0; e < E; ++e)
+    D4B_CHECK(d->deg[e] >= 1 && d->deg[e] <= D4B_MAX_DEG && d->deg_quad[e] >= d->deg[e] && d->deg_quad[e] < D4B_MAXNQ,
+              "d4b_geom_compute: element %d: deg %d / deg_quad %d out of range", e, d->deg[e], d->deg_quad[e]);
+  DevBuf B;
+  GeomArgs A;
+  memset(&A, 0, sizeof(A));
+  A.P.type = g->geom_type; A.P.face_h = g->face_h_type;
+  A.P.ci = g->compactify_inner_shell; A.P.co = g->compactify_outer_shell;
+  A.P.X0 = g->X0; A.P.X1 = g->X1; A.P.Y0 = g->Y0; A.P.Y1 = g->Y1; A.P.Z0 = g->Z0; A.P.Z1 = g->Z1;
+  A.P.R0 = g->R0; A.P.R1 = g->R1; A.P.R2 = g->R2; A.P.Cl = g->R0 / sqrt(3.);
+  A.n_local = E; A.n_ghost = Gh; A.n_sides = Ns;
+  A.local_nodes = d->local_nodes; A.LQ = d->local_nodes_quad; A.MP = d->local_mortar_nodes_quad;
+  A.deg = B.up(d->deg, E); A.deg_quad = B.up(d->deg_quad, E);
+  A.ghost_deg = B.up(d->ghost_deg, Gh); A.ghost_deg_quad = B.up(d->ghost_deg_quad, Gh);
+  A.nodal_stride = B.up(d->nodal_stride, E); A.quad_stride = B.up(d->quad_stride, E);
+  A.tree = B.up(g->elem_tree, E); A.q = B.up(g->elem_q, (size_t)3 * E); A.dq = B.up(g->elem_dq, E);
+  A.gtree = B.up(g->ghost_tree, Gh); A.gq = B.up(g->ghost_q, (size_t)3 * Gh); A.gdq = B.up(g->ghost_dq, Gh);
+  A.faces_m = B.up(d->side_faces_m, Ns); A.faces_p = B.up(d->side_faces_p, Ns);
+  A.f_m = B.up(d->side_f_m, Ns); A.f_p = B.up(d->side_f_p, Ns);
+  A.e_m = B.up(d->side_e_m, (size_t)4 * Ns); A.e_p = B.up(d->side_e_p, (size_t)4 * Ns);
+  A.perm = B.up(d->side_perm, Ns); A.sub = B.up(d->side_sub_order, (size_t)4 * Ns);
+  A.mstride = B.up(d->side_mortar_stride, Ns);
+
+  // outputs: write straight into device pointers, stage host pointers
+  struct Out { double *user; double **slot; size_t n; };
+  const size_t LN = (size_t)d->local_nodes, LQ = (size_t)d->local_nodes_quad, MP = (size_t)d->local_mortar_nodes_quad;
+  Out outs[] = {{out->xyz, &A.xyz, 3 * LN}, {out->J_quad, &A.J, LQ}, {out->rst_xyz_quad, &A.rst_xyz, 9 * LQ},
+                {out->sj_m_mortar_quad, &A.sj, MP}, {out->n_m_mortar_quad, &A.n, 3 * MP},
+                {out->drst_dxyz_m_mortar_quad, &A.drm, 9 * MP}, {out->drst_dxyz_p_mortar_quad_porder, &A.drp, 9 * MP},
+                {out->hm_mortar_quad, &A.hm, MP}, {out->hp_mortar_quad, &A.hp, MP}};
+  for (Out &o : outs) {
+    if (!o.user) continue;
+    *o.slot = is_device_ptr(o.user) ? o.user : B.up<double>(nullptr, o.n);
+  }
+  if (A.rst_xyz && !A.J) A.J = B.up<double>(nullptr, LQ);
+  const bool want_mortar = A.sj || A.n || A.drm || A.drp || A.hm || A.hp;
+  const bool need_sizes = (A.hm || A.hp) && g->face_h_type != D4B_FACE_H_J_DIV_SJ_QUAD && g->face_h_type != D4B_FACE_H_TREE_H;
+  if (need_sizes) {
+    const size_t Et = (size_t)E + Gh;
+    A.vol = B.up<double>(nullptr, Et); A.area = B.up<double>(nullptr, 6 * Et);
+    A.jmin = B.up<double>(nullptr, 6 * Et); A.jmean = B.up<double>(nullptr, 6 * Et); A.jmax = B.up<double>(nullptr, 6 * Et);
+    const int64_t nt = (int64_t)Et * 7;
+    geom_size_kernel<<<(unsigned)((nt + 127) / 128), 128>>>(A);
+    D4B_CUDA(cudaGetLastError());
+  }
+  if ((A.J || A.xyz) && E > 0) {
+    geom_volume_kernel<<<E, 64>>>(A);
+    D4B_CUDA(cudaGetLastError());
+  }
+  if (want_mortar && Ns > 0) {
+    geom_mortar_kernel<<<Ns, 64>>>(A);
+    D4B_CUDA(cudaGetLastError());
+  }
+  D4B_CUDA(cudaDeviceSynchronize());
+  for (Out &o : outs)
+    if (o.user && *o.slot != o.user) D4B_CUDA(cudaMemcpy(o.user, *o.slot, o.n * sizeof(double), cudaMemcpyDeviceToHost));
+}
+
+extern "C" d4b_mesh_t *d4b_mesh_create_with_geometry(const d4b_mesh_desc_t *topo, const d4b_geom_desc_t *geom) {
+  D4B_CHECK(topo && geom, "d4b_mesh_create_with_geometry: NULL argument");
+  const size_t LQ = (size_t)topo->local_nodes_quad, MP = (size_t)topo->local_mortar_nodes_quad;
+  std::vector<double> J(LQ), rst(9 * LQ), sj(MP), n(3 * MP), drm(9 * MP), drp(9 * MP), hm(MP), hp(MP);
+  d4b_geom_arrays_t out;
+  memset(&out, 0, sizeof(out));
+  out.J_quad = J.data(); out.rst_xyz_quad = rst.data();
+  out.sj_m_mortar_quad = sj.data(); out.n_m_mortar_quad = n.data();
+  out.drst_dxyz_m_mortar_quad = drm.data(); out.drst_dxyz_p_mortar_quad_porder = drp.data();
+  out.hm_mortar_quad = hm.data(); out.hp_mortar_quad = hp.data();
+  d4b_geom_compute(topo, geom, &out);
+  d4b_mesh_desc_t d = *topo;
+  d.J_quad = J.data(); d.rst_xyz_quad = rst.data();
+  d.sj_m_mortar_quad = sj.data(); d.n_m_mortar_quad = n.data();
+  d.drst_dxyz_m_mortar_quad = drm.data(); d.drst_dxyz_p_mortar_quad_porder = drp.data();
+  d.hm_mortar_quad = hm.data(); d.hp_mortar_quad = hp.data();
+  return d4b_mesh_create(&d);
+}

@@ -14,7 +14,7 @@ import os
 
 import numpy as np
 
-from .abi import ChebyParams, MeshDesc, MgDesc, make_desc
+from .abi import GEOM_ARRAY_FIELDS, ChebyParams, GeomArrays, GeomDesc, MeshDesc, MgDesc, make_desc, make_geom_desc
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 # D4B_LIBRARY_PATH lets profiling scripts A/B differently compiled builds of the same library
@@ -24,6 +24,7 @@ _I32P_T = C.POINTER(C.c_int32)
 
 EXPORTS = [
     "d4b_set_abort_hook", "d4b_abi_version", "d4b_device_count", "d4b_init",
+    "d4b_geom_compute", "d4b_mesh_create_with_geometry",
     "d4b_mesh_create", "d4b_mesh_destroy", "d4b_mesh_local_nodes", "d4b_mesh_device_bytes", "d4b_mesh_fast_elements", "d4b_mesh_flat_elements", "d4b_mesh_launches_per_apply",
     "d4b_apply", "d4b_apply_stiffness", "d4b_sync", "d4b_set_stream",
     "d4b_interp_to_quad", "d4b_apply_galerkin", "d4b_apply_mass", "d4b_mesh_set_mass_diag",
@@ -54,6 +55,10 @@ def load_library():
     L.d4b_mesh_create.restype = C.c_void_p
     L.d4b_mesh_create.argtypes = [C.POINTER(MeshDesc)]
     L.d4b_mesh_destroy.argtypes = [C.c_void_p]
+    L.d4b_geom_compute.argtypes = [C.POINTER(MeshDesc), C.POINTER(GeomDesc), C.POINTER(GeomArrays)]
+    L.d4b_geom_compute.restype = None
+    L.d4b_mesh_create_with_geometry.restype = C.c_void_p
+    L.d4b_mesh_create_with_geometry.argtypes = [C.POINTER(MeshDesc), C.POINTER(GeomDesc)]
     L.d4b_mesh_local_nodes.restype = C.c_int64
     L.d4b_mesh_local_nodes.argtypes = [C.c_void_p]
     L.d4b_mesh_device_bytes.restype = C.c_int64
@@ -208,17 +213,52 @@ def _ptr(x):
     return x.data_ptr()
 
 
-class Mesh:
-    """Device-resident mesh (d4b_mesh_t)."""
+def geom_compute(arrays, geom, want=None, device=0, out=None):
+    """d4b_geom_compute: geometric factors of the mesh whose topology is `arrays` (the geometric
+    arrays in it are ignored) for the map `geom` (dict, see abi.make_geom_desc).  Returns a dict of
+    numpy arrays for the names in `want` (default: all), or fills the torch / numpy buffers in `out`."""
+    L = load_library()
+    if L.d4b_device_count() <= 0:
+        raise RuntimeError("no CUDA device visible: the B200 path has no CPU fallback")
+    L.d4b_init(device)
+    desc, keep = make_desc({k: v for k, v in arrays.items() if k not in GEOM_ARRAY_FIELDS})
+    gd, gkeep = make_geom_desc(geom)
+    ln, lq, mp = int(desc.local_nodes), int(desc.local_nodes_quad), int(desc.local_mortar_nodes_quad)
+    sizes = {"xyz": 3 * ln, "J_quad": lq, "rst_xyz_quad": 9 * lq, "sj_m_mortar_quad": mp, "n_m_mortar_quad": 3 * mp,
+             "drst_dxyz_m_mortar_quad": 9 * mp, "drst_dxyz_p_mortar_quad_porder": 9 * mp, "hm_mortar_quad": mp,
+             "hp_mortar_quad": mp}
+    ga = GeomArrays()
+    res = {}
+    if out is None:
+        for name in (want or GEOM_ARRAY_FIELDS):
+            res[name] = np.zeros(sizes[name])
+            setattr(ga, name, res[name].ctypes.data)
+    else:
+        for name, buf in out.items():
+            setattr(ga, name, _ptr(buf))
+        res = out
+    L.d4b_geom_compute(C.byref(desc), C.byref(gd), C.byref(ga))
+    return res
 
-    def __init__(self, arrays, device=0):
+
+class Mesh:
+    """Device-resident mesh (d4b_mesh_t).  With `geom` (dict, abi.make_geom_desc) the geometric
+    factors are generated on the device (d4b_mesh_create_with_geometry) and `arrays` only needs the
+    topology."""
+
+    def __init__(self, arrays, device=0, geom=None):
         L = load_library()
         if L.d4b_device_count() <= 0:
             raise RuntimeError("no CUDA device visible: the B200 path has no CPU fallback")
         L.d4b_init(device)
         self.L = L
-        self.desc, self._keep = make_desc(arrays)
-        self.h = L.d4b_mesh_create(C.byref(self.desc))
+        if geom is not None:
+            self.desc, self._keep = make_desc({k: v for k, v in arrays.items() if k not in GEOM_ARRAY_FIELDS})
+            self.gdesc, self._gkeep = make_geom_desc(geom)
+            self.h = L.d4b_mesh_create_with_geometry(C.byref(self.desc), C.byref(self.gdesc))
+        else:
+            self.desc, self._keep = make_desc(arrays)
+            self.h = L.d4b_mesh_create(C.byref(self.desc))
         self.n = int(L.d4b_mesh_local_nodes(self.h))
 
     def set_stream(self, cuda_stream_handle):

@@ -178,6 +178,64 @@ int64_t     d4b_mesh_flat_elements(const d4b_mesh_t *mesh);
 /* CUDA kernels one d4b_apply launches on this mesh (for launch accounting)  */
 int32_t     d4b_mesh_launches_per_apply(const d4b_mesh_t *mesh);
 
+/* --------------------------------------------- geometric factors on device */
+/* Replaces the geometry half of d4est_mesh_data_compute (src/Mesh/d4est_mesh.c:2543-2755)
+ * and d4est_mesh_compute_mortar_quadrature_quantities (:481-1140,
+ * d4est_mortars_compute_geometric_data_on_mortar_aux, src/Mesh/d4est_mortars.c:10-277) for
+ * the analytic maps ([geometry] DX_compute_method = analytic, JAC_compute_method =
+ * numerical): every volume and mortar quadrature point evaluates dX/drst of the tree map
+ * in a CUDA thread, inverts it and writes the reference's arrays.  The derivatives are our
+ * own differentiation of the maps X (d4est_geometry_brick.c, d4est_geometry_cubed_sphere.c:
+ * 127-167, :315-400), not the reference's generated expressions.                        */
+typedef enum {
+  D4B_GEOM_BRICK = 0,          /* [geometry] name = brick: one tree, [X0,X1]x[Y0,Y1]x[Z0,Z1]       */
+  D4B_GEOM_CUBED_SPHERE = 1    /* name = cubed_sphere: 13 trees (p8est_connectivity_new_sphere):
+                                  0-5 outer shell R1..R2, 6-11 inner shell R0..R1, 12 centre cube */
+} d4b_geom_type_t;
+
+/* d4est_mesh_face_h_t, same numeric values (src/Mesh/d4est_mesh.h:32-42) */
+typedef enum {
+  D4B_FACE_H_J_DIV_SJ_QUAD = 0,
+  D4B_FACE_H_J_DIV_SJ_MIN_LOBATTO = 1,
+  D4B_FACE_H_J_DIV_SJ_MEAN_LOBATTO = 2,
+  D4B_FACE_H_J_DIV_SJ_MAX_LOBATTO = 3,
+  D4B_FACE_H_TREE_H = 4,
+  D4B_FACE_H_VOLUME_DIV_AREA = 5
+} d4b_face_h_t;
+
+#define D4B_ROOT_LEN_LOG2 30   /* P8EST_MAXLEVEL: quadrant coordinates live in [0, 2^30) */
+
+typedef struct d4b_geom_desc
+{
+  int32_t geom_type;                  /* d4b_geom_type_t                                   */
+  int32_t face_h_type;                /* d4b_face_h_t                                      */
+  int32_t compactify_inner_shell, compactify_outer_shell;
+  double  X0, X1, Y0, Y1, Z0, Z1;     /* brick extents (d4est_geometry_brick_attr_t)       */
+  double  R0, R1, R2;                 /* cubed sphere radii (…cubed_sphere_attr_t)         */
+  /* p4est position of every local / ghost element (d4est_element_data_t.tree, q, dq)      */
+  const int32_t *elem_tree;           /* [n_local]                                         */
+  const int32_t *elem_q;              /* [3*n_local]                                       */
+  const int32_t *elem_dq;             /* [n_local]                                         */
+  const int32_t *ghost_tree, *ghost_q, *ghost_dq;
+} d4b_geom_desc_t;
+
+/* outputs in the reference's layouts (see d4b_mesh_desc_t); each pointer may be a host
+ * pointer, a device pointer, or NULL (not wanted)                                        */
+typedef struct d4b_geom_arrays
+{
+  double *xyz;                        /* [3*local_nodes]: d*local_nodes + nodal_stride + i */
+  double *J_quad, *rst_xyz_quad;
+  double *sj_m_mortar_quad, *n_m_mortar_quad;
+  double *drst_dxyz_m_mortar_quad, *drst_dxyz_p_mortar_quad_porder;
+  double *hm_mortar_quad, *hp_mortar_quad;
+} d4b_geom_arrays_t;
+
+/* `topo` supplies sizes, degrees, strides and side records; its geometric arrays are not read */
+void d4b_geom_compute(const d4b_mesh_desc_t *topo, const d4b_geom_desc_t *geom,
+                      const d4b_geom_arrays_t *out);
+/* d4b_mesh_create with the geometric factors generated on the device instead of uploaded */
+d4b_mesh_t *d4b_mesh_create_with_geometry(const d4b_mesh_desc_t *topo, const d4b_geom_desc_t *geom);
+
 /* ------------------------------------------------------------------ apply */
 /* Au = A u; replaces d4est_laplacian_apply_aij / _with_opt_apply_aij
  * (d4est_laplacian.c:317-399).  u, Au: local_nodes doubles in reference node

@@ -16,6 +16,8 @@
 #include <d4est_element_data.h>
 #include <d4est_quadrature_legendre.h>
 #include <d4est_geometry.h>
+#include <d4est_geometry_brick.h>
+#include <d4est_geometry_cubed_sphere.h>
 #include <d4est_mesh.h>
 #include <d4est_linalg.h>
 #include <d4est_mortars.h>
@@ -228,6 +230,7 @@ main (int argc, char *argv[])
   const char *out = argv[2];
   int amr_steps = 0, time_reps = 0, bc_poly = 0, cheby_imax = 0, cheby_eigs_imax = 0, mg_vcycles = 0, use_b200 = 0;
   int dump_quad = 0, fcg_imax = 0;
+  const char *geom_out = NULL;
   for (int a = 3; a < argc; a++) {
     if (!strcmp (argv[a], "--amr")) amr_steps = atoi (argv[++a]);
     else if (!strcmp (argv[a], "--time")) time_reps = atoi (argv[++a]);
@@ -238,6 +241,7 @@ main (int argc, char *argv[])
     else if (!strcmp (argv[a], "--quad")) { dump_quad = 1; }
     else if (!strcmp (argv[a], "--fcg")) { fcg_imax = atoi (argv[++a]); }
     else if (!strcmp (argv[a], "--b200")) { use_b200 = 1; }
+    else if (!strcmp (argv[a], "--geom")) { geom_out = argv[++a]; }
     else { fprintf (stderr, "unknown option %s\n", argv[a]); return 2; }
   }
 
@@ -839,6 +843,64 @@ main (int argc, char *argv[])
     }
     fclose (f);
     d4est_b200_flat_destroy (flat);
+  }
+
+  if (geom_out) {
+    /* sidecar for the device geometry generator (d4b_geom_compute): where every element sits
+     * in the forest, the parameters of the map, and -- recomputed by the reference's own
+     * d4est_mesh_compute_mortar_quadrature_quantities at the very end of the run, when nothing
+     * else reads them any more -- hm / hp under every face_h_type the generator supports. */
+    FILE *gf = d4b_dump_open (geom_out);
+    int nl = p4est->local_num_quadrants;
+    int32_t *et = P4EST_ALLOC (int32_t, nl), *eq = P4EST_ALLOC (int32_t, 3 * nl), *edq = P4EST_ALLOC (int32_t, nl);
+    for (p4est_topidx_t tt = p4est->first_local_tree; tt <= p4est->last_local_tree; ++tt) {
+      p4est_tree_t *tree = p4est_tree_array_index (p4est->trees, tt);
+      sc_array_t *tquadrants = &tree->quadrants;
+      for (int qq = 0; qq < (int) tquadrants->elem_count; ++qq) {
+        p4est_quadrant_t *quad = p4est_quadrant_array_index (tquadrants, qq);
+        d4est_element_data_t *ed = (d4est_element_data_t *) (quad->p.user_data);
+        et[ed->id] = ed->tree; edq[ed->id] = ed->dq;
+        for (int d = 0; d < 3; d++) eq[3 * ed->id + d] = ed->q[d];
+      }
+    }
+    d4b_dump_put1 (gf, "elem_tree", D4B_I32, nl, et);
+    d4b_dump_put1 (gf, "elem_q", D4B_I32, 3 * (uint64_t) nl, eq);
+    d4b_dump_put1 (gf, "elem_dq", D4B_I32, nl, edq);
+    P4EST_FREE (et); P4EST_FREE (eq); P4EST_FREE (edq);
+    double prm[9] = { 0 };
+    int gtype = -1;
+    if (d4est_geom->geom_type == GEOM_BRICK) {
+      d4est_geometry_brick_attr_t *b = d4est_geom->user;
+      gtype = 0;
+      prm[0] = b->X0; prm[1] = b->X1; prm[2] = b->Y0; prm[3] = b->Y1; prm[4] = b->Z0; prm[5] = b->Z1;
+    }
+    else if (d4est_geom->geom_type == GEOM_CUBED_SPHERE_13TREE) {
+      d4est_geometry_cubed_sphere_attr_t *sp = d4est_geom->user;
+      gtype = 1;
+      prm[0] = sp->R0; prm[1] = sp->R1; prm[2] = sp->R2;
+      prm[3] = sp->compactify_inner_shell; prm[4] = sp->compactify_outer_shell;
+    }
+    d4b_dump_scalar_i64 (gf, "geom_type", gtype);
+    d4b_dump_put1 (gf, "geom_params", D4B_F64, 9, prm);
+    d4b_dump_scalar_i64 (gf, "face_h_type", initial_grid_input->face_h_type);
+    d4b_dump_scalar_i64 (gf, "root_len", P4EST_ROOT_LEN);
+    uint64_t m = d4est_factors->local_sizes.local_mortar_nodes_quad;
+    static const d4est_mesh_face_h_t types[] = { FACE_H_EQ_J_DIV_SJ_QUAD, FACE_H_EQ_J_DIV_SJ_MIN_LOBATTO,
+      FACE_H_EQ_J_DIV_SJ_MEAN_LOBATTO, FACE_H_EQ_J_DIV_SJ_MAX_LOBATTO, FACE_H_EQ_TREE_H, FACE_H_EQ_VOLUME_DIV_AREA };
+    for (int t = 0; t < 6; t++) {
+      char name[64];
+      memset (d4est_factors->hm_mortar_quad, 0, sizeof (double) * m);
+      memset (d4est_factors->hp_mortar_quad, 0, sizeof (double) * m);
+      d4est_factors->aux_mortar_quad_stride = 0;
+      d4est_factors->aux_boundary_quad_stride = 0;
+      d4est_mesh_compute_mortar_quadrature_quantities (p4est, d4est_ghost, d4est_ops, d4est_geom, d4est_quad,
+                                                       d4est_factors, types[t]);
+      snprintf (name, sizeof (name), "hm_type%d", (int) types[t]);
+      d4b_dump_put1 (gf, name, D4B_F64, m, d4est_factors->hm_mortar_quad);
+      snprintf (name, sizeof (name), "hp_type%d", (int) types[t]);
+      d4b_dump_put1 (gf, name, D4B_F64, m, d4est_factors->hp_mortar_quad);
+    }
+    fclose (gf);
   }
 
   P4EST_FREE (Au_tmp);
