@@ -226,6 +226,71 @@ def bench_vcycle(top_mesh, level, deg, rank, world, trees, torch, dev, cycles=3)
     return out
 
 
+def bench_sphere(args, rank, world, local_rank, torch, dist, dev):
+    """BASELINE.json configs[3] in synthetic form: the 13-tree cubed sphere (curved elements, all
+    inter-tree face orientations), every tree refined to --sphere-level, split over the ranks
+    along the Morton curve like p4est (strong scaling: the mesh is fixed).  Geometric factors
+    are generated on the device.  Two meshes: uniform degree (curved conforming kernel) and a
+    seeded random degree 1..deg per element (hp kernel).  GDOF/s of one apply each."""
+    import numpy as np
+
+    from disco4est_b200 import Mesh
+    from disco4est_b200.partition import partition_desc
+    from disco4est_b200.sphere import partition_geom, sphere_desc
+
+    out = {}
+    for name, kw, lvl in (("uniform_p", dict(p=args.deg), args.sphere_level),
+                          ("random_hp", dict(pmax=args.deg), max(args.sphere_level - 1, 1))):
+        t0 = time.perf_counter()
+        A, g = sphere_desc(lvl, **kw)
+        E = int(A["n_local"])
+        total_dof = int(A["local_nodes"])
+        if world > 1:
+            B = partition_desc(A, rank, world)
+            g = partition_geom(g, B, rank, world, E)
+            A = B
+        t1 = time.perf_counter()
+        mesh = Mesh(A, device=local_rank, geom=g)
+        t2 = time.perf_counter()
+        del A, g
+        n = mesh.n
+        stream = torch.cuda.current_stream()
+        mesh.set_stream(stream.cuda_stream)
+        gen = torch.Generator(device=dev).manual_seed(4242 + rank)
+        u = torch.rand(n, dtype=torch.float64, device=dev, generator=gen)
+        Au = torch.empty_like(u)
+        for _ in range(3):
+            mesh.apply(u, Au)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        steps = max(args.steps // 2, 5)
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record(stream)
+        for _ in range(steps):
+            mesh.apply(u, Au)
+        ev1.record(stream)
+        torch.cuda.synchronize()
+        tt = torch.tensor([ev0.elapsed_time(ev1) * 1e-3 / steps], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        t = float(tt[0])
+        out[name] = {"GDOF_per_s": total_dof / t / 1e9, "ms_per_apply": 1e3 * t, "level": lvl, "elements": E,
+                     "dof": total_dof, "fast_kernel_elements_rank0": mesh.fast_elements(),
+                     "flat_kernel_elements_rank0": mesh.flat_elements(),
+                     "launches_per_apply": mesh.launches_per_apply(),
+                     "frac_of_hbm_roofline": total_dof * algorithmic_bytes_per_dof(args.deg) / t / 1e9 / world / measured_peak()[0]
+                     if name == "uniform_p" else None,
+                     "setup_s": {"topology_numpy": t1 - t0, "device_geometry_and_mesh": t2 - t1},
+                     "checksum_Au": float(Au.sum())}
+        mesh.close()
+        del u, Au
+    out["scaling"] = "strong (fixed mesh split over the ranks)"
+    out["workload"] = ("13-tree cubed sphere R = 1, 2, 3, SIPG prefactor 2 maxp_sqr_over_minh, face_h = J/sj, "
+                       "deg_quad = deg, geometric factors generated on the device")
+    return out
+
+
 def bench_ours(args):
     import numpy as np
     import torch
@@ -339,11 +404,17 @@ def bench_ours(args):
     vc = None
     if not args.no_vcycle:
         vc = bench_vcycle(mesh, level, deg, rank, world, trees, torch, dev)
+    mesh.close()
+    del mesh, u, Au
+    sp = None
+    if not args.no_sphere:
+        sp = bench_sphere(args, rank, world, local_rank, torch, dist, dev)
     if rank == 0:
         if vc is not None:
             out["vcycle"] = vc
+        if sp is not None:
+            out["cubed_sphere"] = sp
         print(json.dumps(out))
-    mesh.close()
     if world > 1:
         comm_destroy()
         dist.destroy_process_group()
@@ -359,6 +430,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-vcycle", action="store_true", help="skip the V-cycle metric")
+    ap.add_argument("--no-sphere", action="store_true", help="skip the cubed-sphere applies")
+    ap.add_argument("--sphere-level", type=int, default=4, help="refinement level of each of the 13 sphere trees")
     args = ap.parse_args()
     if args.impl == "reference":
         bench_reference(args)

@@ -109,8 +109,9 @@ def partition_desc(A, rank, world, offsets=None):
     B["deg_quad"] = np.ascontiguousarray(A["deg_quad"][start:end]).astype(np.int32)
     B["nodal_stride"] = np.ascontiguousarray(nodal[start:end] - node0)
     B["quad_stride"] = np.ascontiguousarray(quad[start:end] - q0)
-    B["J_quad"] = np.ascontiguousarray(A["J_quad"][q0:q1])
-    B["rst_xyz_quad"] = np.ascontiguousarray(np.asarray(A["rst_xyz_quad"]).reshape(9, LQ)[:, q0:q1]).reshape(-1)
+    if A.get("J_quad") is not None:   # absent when the factors are generated on the device (sphere.py)
+        B["J_quad"] = np.ascontiguousarray(A["J_quad"][q0:q1])
+        B["rst_xyz_quad"] = np.ascontiguousarray(np.asarray(A["rst_xyz_quad"]).reshape(9, LQ)[:, q0:q1]).reshape(-1)
 
     B["ghost_deg"] = deg[ghost_gid].astype(np.int32)
     B["ghost_deg_quad"] = deg_quad[ghost_gid].astype(np.int32)

@@ -17,6 +17,16 @@ run() { # name ini args...
   gzip -9nf "$G/$name.d4b"
   echo "$name: $(cat "$G/$name.json")"
 }
+geom() { # name ini args...: sidecar for the device geometry generator (element positions, map
+  # parameters, hm/hp under every face_h_type); the main dump of the same run is discarded
+  local name=$1 ini=$2; shift 2
+  "$DRV" "$HERE/configs/$ini" /tmp/d4b_geom_$$.d4b "$@" --geom "$G/$name.geom.d4b" > /dev/null
+  rm -f /tmp/d4b_geom_$$.d4b
+  gzip -9nf "$G/$name.geom.d4b"
+}
+geom brick_l2_p3 brick_poisson.ini --uniform-deg 3
+geom sphere_p2 sphere_p.ini --uniform-deg 2
+geom sphere_hp_amr1 sphere_hp.ini --amr 1 --bc poly
 run brick_l2_p1 brick_poisson.ini                       # the 4^3 p=1 mesh of d4est_test_poisson_sinx.sh
 run brick_l2_p2_bc brick_poisson.ini --uniform-deg 2 --bc poly
 run brick_l2_p3 brick_poisson.ini --uniform-deg 3 --cheby 15 15 --quad   # + volume quadrature operators; + cg_eigs / Chebyshev smoother outputs

@@ -22,7 +22,7 @@ for r in range(rounds):
     for v in variants:
         env = dict(os.environ); env.update({k: x for k, x in v})
         out = subprocess.run([sys.executable, "bench.py", "--level", str(level), "--deg", str(deg), "--steps", "30",
-                              "--warmup", "5", "--no-cpu", "--no-vcycle"], env=env, capture_output=True, text=True).stdout
+                              "--warmup", "5", "--no-cpu", "--no-vcycle", "--no-sphere"], env=env, capture_output=True, text=True).stdout
         j = json.loads(out.strip().splitlines()[-1])
         res[v].append(j["ms_per_step"])
 for v, ms in res.items():

@@ -4,7 +4,7 @@ out=${1:-gpurun_out/sweep.jsonl}
 : > $out
 for d in 1 2 3 4 5 6 7; do
   lvl=6; if [ $d -ge 4 ]; then lvl=5; fi
-  python bench.py --level $lvl --deg $d --steps 20 --warmup 5 --no-cpu --no-vcycle 2>/dev/null | tail -1 >> $out
+  python bench.py --level $lvl --deg $d --steps 20 --warmup 5 --no-cpu --no-vcycle --no-sphere 2>/dev/null | tail -1 >> $out
 done
 python - "$out" <<'PY'
 import json, sys
