@@ -502,6 +502,68 @@ void launch_flat(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, 
   D4B_CUDA(cudaGetLastError());
 }
 
+#include "d4b_hp_kernel.cuh"
+
+template <int N>
+void launch_hp(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, int last) {
+  if (last <= first) return;
+  HpArgs a;
+  a.elem = cls.d_elem; a.first = first; a.n_elem = last;
+  a.deg = m->d_deg; a.ghost_deg = m->d_ghost_deg;
+  a.nodal_stride = m->d_nodal_stride; a.quad_stride = m->d_quad_stride;
+  a.ghost_nodal_stride = m->d_ghost_nodal_stride;
+  a.G = m->d_G; a.LQ = m->local_nodes_quad; a.W = m->d_W;
+  a.elem_side = m->d_elem_side; a.elem_sub = m->d_elem_sub;
+  a.side_faces_m = m->d_side_faces_m; a.side_faces_p = m->d_side_faces_p; a.side_f_p = m->d_side_f_p;
+  a.side_e_m = m->d_side_e_m; a.side_e_p = m->d_side_e_p; a.side_perm = m->d_side_perm;
+  a.side_sub_order = m->d_side_sub_order; a.side_mortar_stride = m->d_side_mortar_stride;
+  a.mortar = m->d_mortar; a.MP = m->mortar_nodes;
+  a.uh = m->d_uhat; a.local_nodes = m->local_nodes; a.Au = d_Au; a.epi = m->epi;
+  a.tabs = static_cast<const HpTabs *>(m->d_hp_tabs); a.tabdata = m->d_hp_tabdata;
+  a.mM = m->max_deg + 1;
+  a.smem_doubles = hp_smem_doubles<N>(a.mM);
+  const size_t per_warp = (size_t)a.smem_doubles * sizeof(double);
+  int warps = (int)((200 * 1024) / per_warp);
+  warps = warps < 1 ? 1 : warps > 4 ? 4 : warps;
+  const size_t smem = per_warp * warps;
+  static size_t configured = 48 * 1024;
+  if (smem > configured) {
+    D4B_CUDA(cudaFuncSetAttribute(hp_apply_kernel<N, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    D4B_CUDA(cudaFuncSetAttribute(hp_apply_kernel<N, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = smem;
+  }
+  const int grid = (last - first + warps - 1) / warps;
+  if (m->d_W) hp_apply_kernel<N, true><<<grid, 32 * warps, smem, m->stream>>>(a);
+  else hp_apply_kernel<N, false><<<grid, 32 * warps, smem, m->stream>>>(a);
+  D4B_CUDA(cudaGetLastError());
+}
+
+void build_hp_tabs(d4b_mesh *m) {
+  HpTabs T;
+  memset(&T, 0xff, sizeof(T));
+  std::vector<double> data;
+  double xg[8][8], wg[8];
+  for (int n = 2; n <= 8; ++n) d4b_tab_gauss(n, xg[n - 1], wg);
+  for (int n = 2; n <= 8; ++n) {
+    std::vector<double> D(n * n);
+    d4b_tab_deriv(n, xg[n - 1], D.data());
+    T.dg_off[n] = (int32_t)data.size();
+    data.insert(data.end(), D.begin(), D.end());
+    for (int mt = n; mt <= 8; ++mt)
+      for (int half = 0; half < 3; ++half) {
+        double y[8];
+        for (int k = 0; k < mt; ++k)
+          y[k] = (half == 0) ? xg[mt - 1][k] : (half == 1) ? .5 * (xg[mt - 1][k] - 1.) : .5 * (xg[mt - 1][k] + 1.);
+        std::vector<double> E(mt * n);
+        d4b_tab_eval(n, xg[n - 1], mt, y, E.data());
+        T.t_off[n][mt][half] = (int32_t)data.size();
+        data.insert(data.end(), E.begin(), E.end());
+      }
+  }
+  m->d_hp_tabdata = d4b_dev_upload<double>(m, data.data(), data.size());
+  m->d_hp_tabs = d4b_dev_upload<int32_t>(m, (const int32_t *)&T, sizeof(T) / sizeof(int32_t));
+}
+
 template <int N>
 void launch_interp(d4b_mesh *m, const D4bFastClass &cls, const double *d_u, int phase) {
   using C = Cfg<N>;
@@ -598,9 +660,28 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
     }
     if (ok) { is_fast[e] = 1; by_deg[d->deg[e]].push_back(e); }
   }
-  bool any = false;
+  // hp-irregular elements the mortar kernel (d4b_hp_kernel.cuh) takes: collocated quadrature on the
+  // element and on every element of its six flux sides; D4B_NO_HP=1 leaves them to the general kernel
+  std::vector<std::vector<int32_t>> hp_by_deg(D4B_MAX_DEG + 1);
+  const bool allow_hp = !(getenv("D4B_NO_HP") && atoi(getenv("D4B_NO_HP")) != 0);
+  auto collocated = [&](int32_t r) {
+    return r >= 0 ? d->deg_quad[r] == d->deg[r] : d->ghost_deg_quad[-r - 1] == d->ghost_deg[-r - 1];
+  };
+  bool any_hp = false;
+  for (int e = 0; e < E && allow_hp; ++e) {
+    if (is_fast[e] || d->deg_quad[e] != d->deg[e]) continue;
+    bool ok = true;
+    for (int f = 0; f < 6 && ok; ++f) {
+      const int s = elem_side[6 * e + f];
+      for (int i = 0; i < d->side_faces_m[s] && ok; ++i) ok = collocated(d->side_e_m[4 * s + i]);
+      for (int i = 0; i < d->side_faces_p[s] && ok; ++i) ok = collocated(d->side_e_p[4 * s + i]);
+    }
+    if (ok) { is_fast[e] = 1; hp_by_deg[d->deg[e]].push_back(e); any_hp = true; }
+  }
+  bool any = any_hp;
   for (int p = 1; p <= D4B_MAX_DEG; ++p) any = any || !by_deg[p].empty();
   if (!any) return;
+  if (any_hp) build_hp_tabs(m);
   const bool allow_flat = !(getenv("D4B_NO_FLAT") && atoi(getenv("D4B_NO_FLAT")) != 0);
 
   // a face is tangential-free when A_m[l] (l != its normal direction) and
@@ -674,7 +755,12 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
   memset(tabs, 0, sizeof(tabs));
   int64_t n_shared = 0, n_split = 0;
   for (int p = 1; p <= D4B_MAX_DEG; ++p) {
-    if (by_deg[p].empty()) continue;
+    std::vector<int32_t> ghost_hat_p;
+    for (int g = 0; g < d->n_ghost; ++g)
+      if (d->ghost_deg[g] == p && d->ghost_deg_quad[g] == p) ghost_hat_p.push_back(g);
+    // with hp elements around, every collocated element may be somebody's neighbour: its uh is needed
+    const bool hat_needed = any_hp && (!hat_by_deg[p].empty() || !ghost_hat_p.empty());
+    if (by_deg[p].empty() && hp_by_deg[p].empty() && !hat_needed) continue;
     const int N = p + 1, NN = N * N, N3 = N * NN;
     build_fast_tab(N, tabs[N]);
     D4B_CUDA(cudaMemcpyToSymbol(c_tab, &tabs[N], sizeof(FastTab), (size_t)N * sizeof(FastTab)));
@@ -698,9 +784,7 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
                                        [&](int e) { return !touches_ghost(e); });
       n_interior_kind[kind] = (int)(mid - els_kind[kind].begin());
     }
-    std::vector<int32_t> ghost_hat;
-    for (int g = 0; g < d->n_ghost; ++g)
-      if (d->ghost_deg[g] == p && d->ghost_deg_quad[g] == p) ghost_hat.push_back(g);
+    const std::vector<int32_t> &ghost_hat = ghost_hat_p;
     bool hat_done = false;
     for (int kind = 0; kind < 2; ++kind) {
       const std::vector<int32_t> &els = els_kind[kind];
@@ -785,6 +869,33 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
       }
       m->fast.push_back(c);
     }
+    if (!hp_by_deg[p].empty() || !hat_done) {   // the mortar-kernel class (possibly empty: it then only carries uh)
+      std::vector<int32_t> els = hp_by_deg[p];
+      auto side_touches_ghost = [&](int e) {
+        for (int f = 0; f < 6; ++f) {
+          const int s = elem_side[6 * e + f];
+          for (int i = 0; i < d->side_faces_m[s]; ++i) if (d->side_e_m[4 * s + i] < 0) return true;
+          for (int i = 0; i < d->side_faces_p[s]; ++i) if (d->side_e_p[4 * s + i] < 0) return true;
+        }
+        return false;
+      };
+      auto mid = std::stable_partition(els.begin(), els.end(), [&](int e) { return !side_touches_ghost(e); });
+      D4bFastClass c;
+      c.deg = p;
+      c.kind = 2;
+      if (!hat_done) {
+        c.n_hat = (int)hat_by_deg[p].size();
+        c.d_hat_elem = d4b_dev_upload<int32_t>(m, hat_by_deg[p].data(), hat_by_deg[p].size());
+        c.n_ghost_hat = (int)ghost_hat.size();
+        c.d_ghost_hat = d4b_dev_upload<int32_t>(m, ghost_hat.data(), ghost_hat.size());
+        hat_done = true;
+      }
+      c.n_elem = (int)els.size();
+      c.n_interior = (int)(mid - els.begin());
+      c.d_elem = d4b_dev_upload<int32_t>(m, els.data(), els.size());
+      m->n_hp_elem += c.n_elem;
+      m->fast.push_back(c);
+    }
   }
   m->n_face_shared = n_shared;
   m->n_face_split = n_split;
@@ -811,7 +922,7 @@ void d4b_launch_fast(d4b_mesh *m, const double *d_u, double *d_Au, int part) {
   if (part == 0) return;
   for (const D4bFastClass &c : m->fast) {
     const int first = part == 1 ? 0 : c.n_interior, last = part == 1 ? c.n_interior : c.n_elem;
-#define D4B_CASE(n) case n: if (c.kind) launch_flat<n>(m, c, d_Au, first, last); else launch_fast<n>(m, c, d_Au, first, last); break;
+#define D4B_CASE(n) case n: if (c.kind == 2) launch_hp<n>(m, c, d_Au, first, last); else if (c.kind) launch_flat<n>(m, c, d_Au, first, last); else launch_fast<n>(m, c, d_Au, first, last); break;
     switch (c.deg + 1) {
       D4B_CASE(2) D4B_CASE(3) D4B_CASE(4) D4B_CASE(5) D4B_CASE(6) D4B_CASE(7) D4B_CASE(8)
       default: D4B_ABORT("fast path: unsupported degree %d", c.deg);

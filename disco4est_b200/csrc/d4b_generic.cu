@@ -39,6 +39,7 @@ struct GenericArgs {
   int n_elem;
   int stiffness_only;
   int maxN, maxNq;
+  int smem_doubles;             // shared memory of one warp (element), in doubles
 };
 
 __device__ __forceinline__ const double *tabE(const GenericArgs &a, int deg, int deg_q, int half) {
@@ -47,13 +48,21 @@ __device__ __forceinline__ const double *tabE(const GenericArgs &a, int deg, int
 
 // out[(c*nb + b)*nra + ar] = sum_l A(ar,l) in[(c*nb + b)*nca + l]   (dir 0)
 // generic single-direction sweep on a 3-index array; A(row,col) = A[row*sr + col*sc]
+// TPB = cooperating threads: 32 (one warp per element, apply kernel) or the whole CTA (quadrature operators)
+template <bool WARP>
+__device__ __forceinline__ void group_sync() {
+  if (WARP) __syncwarp(); else __syncthreads();
+}
+
+template <bool WARP>
 __device__ void sweep3(double *out, const double *in, const double *A, int sr, int sc,
                        int nrow, int ncol, int dir, int d0, int d1, int d2) {
+  const int tid = WARP ? (threadIdx.x & 31) : threadIdx.x, nth = WARP ? 32 : blockDim.x;
   // input dims (d0,d1,d2) with d[dir] == ncol; output same with d[dir] = nrow
   int o0 = (dir == 0) ? nrow : d0, o1 = (dir == 1) ? nrow : d1, o2 = (dir == 2) ? nrow : d2;
   int total = o0 * o1 * o2;
   int istride = (dir == 0) ? 1 : (dir == 1) ? d0 : d0 * d1;
-  for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
+  for (int idx = tid; idx < total; idx += nth) {
     int i0 = idx % o0, i1 = (idx / o0) % o1, i2 = idx / (o0 * o1);
     int row = (dir == 0) ? i0 : (dir == 1) ? i1 : i2;
     int base = ((dir == 0) ? 0 : i0) + d0 * (((dir == 1) ? 0 : i1) + d1 * ((dir == 2) ? 0 : i2));
@@ -61,16 +70,17 @@ __device__ void sweep3(double *out, const double *in, const double *A, int sr, i
     for (int l = 0; l < ncol; ++l) s += A[row * sr + l * sc] * in[base + l * istride];
     out[idx] = s;
   }
-  __syncthreads();
+  group_sync<WARP>();
 }
 
 // 2-D: out[b*nra + a] = sum_l A(a,l) in[b*nca + l] (dir 0) or along b (dir 1)
 __device__ void sweep2(double *out, const double *in, const double *A, int sr, int sc,
                        int nrow, int ncol, int dir, int d0, int d1) {
+  const int tid = threadIdx.x & 31, nth = 32;
   int o0 = (dir == 0) ? nrow : d0, o1 = (dir == 1) ? nrow : d1;
   int total = o0 * o1;
   int istride = (dir == 0) ? 1 : d0;
-  for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
+  for (int idx = tid; idx < total; idx += nth) {
     int i0 = idx % o0, i1 = idx / o0;
     int row = (dir == 0) ? i0 : i1;
     int base = ((dir == 0) ? 0 : i0) + d0 * ((dir == 1) ? 0 : i1);
@@ -78,7 +88,7 @@ __device__ void sweep2(double *out, const double *in, const double *A, int sr, i
     for (int l = 0; l < ncol; ++l) s += A[row * sr + l * sc] * in[base + l * istride];
     out[idx] = s;
   }
-  __syncthreads();
+  __syncwarp();
 }
 
 __device__ __forceinline__ int vol_index(int N, int f, int a, int b, int n) {
@@ -102,12 +112,13 @@ __device__ __forceinline__ int perm_index(int n, int perm, int a, int b) {
 // tr, t2d: scratch of N*N and N*nq doubles.
 __device__ void traces_on_mortar(const GenericArgs &a, const double *v, int deg, int f, int dq,
                                  int hx, int hy, double *out, int ostride, double *tr, double *t2d) {
+  const int lane = threadIdx.x & 31;
   int N = deg + 1, Nq = dq + 1;
   const double *D = a.tabdata + a.tab->d_off[deg - 1];
   const double *Ex = tabE(a, deg, dq, hx), *Ey = tabE(a, deg, dq, hy);
   int n = (f & 1) ? N - 1 : 0;
   for (int q = 0; q < 4; ++q) {
-    for (int idx = threadIdx.x; idx < N * N; idx += blockDim.x) {
+    for (int idx = lane; idx < N * N; idx += 32) {
       int fa = idx % N, fb = idx / N;
       int vi = vol_index(N, f, fa, fb, n);
       double s;
@@ -122,15 +133,21 @@ __device__ void traces_on_mortar(const GenericArgs &a, const double *v, int deg,
       }
       tr[idx] = s;
     }
-    __syncthreads();
+    __syncwarp();
     sweep2(t2d, tr, Ex, N, 1, Nq, N, 0, N, N);
     sweep2(out + q * ostride, t2d, Ey, N, 1, Nq, N, 1, Nq, N);
   }
 }
 
-__global__ void __launch_bounds__(128) generic_apply_kernel(GenericArgs a) {
-  extern __shared__ double smem[];
-  int e = a.elem_list ? a.elem_list[blockIdx.x] : blockIdx.x;
+// one warp per element, kWarps elements per CTA; warps never synchronise with each other
+constexpr int kMaxWarps = 4;
+__global__ void __launch_bounds__(32 * kMaxWarps) generic_apply_kernel(GenericArgs a) {
+  extern __shared__ double smem_all[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int slot = blockIdx.x * (blockDim.x >> 5) + warp;
+  if (slot >= a.n_elem) return;
+  double *smem = smem_all + (size_t)warp * a.smem_doubles;
+  int e = a.elem_list ? a.elem_list[slot] : slot;
   int p = a.deg[e], q = a.deg_quad[e];
   int N = p + 1, Nq = q + 1, n3 = N * N * N, q3 = Nq * Nq * Nq;
   int mN = a.maxN, mQ = a.maxNq;
@@ -144,20 +161,20 @@ __global__ void __launch_bounds__(128) generic_apply_kernel(GenericArgs a) {
   const double *ue = a.u + a.nodal_stride[e];
   const double *D = a.tabdata + a.tab->d_off[p - 1];
   const double *E = tabE(a, p, q, 0);
-  for (int i = threadIdx.x; i < n3; i += blockDim.x) { s_u[i] = ue[i]; s_out[i] = 0.; }
-  __syncthreads();
+  for (int i = lane; i < n3; i += 32) { s_u[i] = ue[i]; s_out[i] = 0.; }
+  __syncwarp();
 
   // ---- volume: sum_{l',l} D_l'^T V^T G_{l'l} V D_l u
   for (int l = 0; l < 3; ++l) {
-    sweep3(s_a, s_u, D, N, 1, N, N, l, N, N, N);
-    sweep3(s_t1, s_a, E, N, 1, Nq, N, 0, N, N, N);
-    sweep3(s_t2, s_t1, E, N, 1, Nq, N, 1, Nq, N, N);
-    sweep3(s_g + l * q3, s_t2, E, N, 1, Nq, N, 2, Nq, Nq, N);
+    sweep3<true>(s_a, s_u, D, N, 1, N, N, l, N, N, N);
+    sweep3<true>(s_t1, s_a, E, N, 1, Nq, N, 0, N, N, N);
+    sweep3<true>(s_t2, s_t1, E, N, 1, Nq, N, 1, Nq, N, N);
+    sweep3<true>(s_g + l * q3, s_t2, E, N, 1, Nq, N, 2, Nq, Nq, N);
   }
   {
     const double *G = a.G + a.quad_stride[e];
     int64_t LQ = a.local_nodes_quad;
-    for (int k = threadIdx.x; k < q3; k += blockDim.x) {
+    for (int k = lane; k < q3; k += 32) {
       double g0 = s_g[k], g1 = s_g[q3 + k], g2 = s_g[2 * q3 + k];
       double G00 = G[k], G01 = G[LQ + k], G02 = G[2 * LQ + k], G11 = G[3 * LQ + k],
              G12 = G[4 * LQ + k], G22 = G[5 * LQ + k];
@@ -165,33 +182,33 @@ __global__ void __launch_bounds__(128) generic_apply_kernel(GenericArgs a) {
       s_g[q3 + k] = G01 * g0 + G11 * g1 + G12 * g2;
       s_g[2 * q3 + k] = G02 * g0 + G12 * g1 + G22 * g2;
     }
-    __syncthreads();
+    __syncwarp();
   }
   for (int lp = 0; lp < 3; ++lp) {
     // V^T: E transposed -> A(row=a, col=l) = E[l*N + a]
-    sweep3(s_t2, s_g + lp * q3, E, 1, N, N, Nq, 2, Nq, Nq, Nq);
-    sweep3(s_t1, s_t2, E, 1, N, N, Nq, 1, Nq, Nq, N);
-    sweep3(s_a, s_t1, E, 1, N, N, Nq, 0, Nq, N, N);
+    sweep3<true>(s_t2, s_g + lp * q3, E, 1, N, N, Nq, 2, Nq, Nq, Nq);
+    sweep3<true>(s_t1, s_t2, E, 1, N, N, Nq, 1, Nq, Nq, N);
+    sweep3<true>(s_a, s_t1, E, 1, N, N, Nq, 0, Nq, N, N);
     // D_l'^T
-    sweep3(s_t1, s_a, D, 1, N, N, N, lp, N, N, N);
-    for (int i = threadIdx.x; i < n3; i += blockDim.x) s_out[i] += s_t1[i];
-    __syncthreads();
+    sweep3<true>(s_t1, s_a, D, 1, N, N, N, lp, N, N, N);
+    for (int i = lane; i < n3; i += 32) s_out[i] += s_t1[i];
+    __syncwarp();
   }
 
   // ---- mass-type diagonal: + V^T diag(W) V u (d4est_quadrature_apply_mass_matrix with
   // jac := J f, d4est_quadrature.c:385-477, as apply_fofufofvlilj calls it :593-774)
   if (a.W && !a.stiffness_only) {
     const double *W = a.W + a.quad_stride[e];
-    sweep3(s_t1, s_u, E, N, 1, Nq, N, 0, N, N, N);
-    sweep3(s_t2, s_t1, E, N, 1, Nq, N, 1, Nq, N, N);
-    sweep3(s_g, s_t2, E, N, 1, Nq, N, 2, Nq, Nq, N);
-    for (int k = threadIdx.x; k < q3; k += blockDim.x) s_g[k] *= W[k];
-    __syncthreads();
-    sweep3(s_t2, s_g, E, 1, N, N, Nq, 2, Nq, Nq, Nq);
-    sweep3(s_t1, s_t2, E, 1, N, N, Nq, 1, Nq, Nq, N);
-    sweep3(s_a, s_t1, E, 1, N, N, Nq, 0, Nq, N, N);
-    for (int i = threadIdx.x; i < n3; i += blockDim.x) s_out[i] += s_a[i];
-    __syncthreads();
+    sweep3<true>(s_t1, s_u, E, N, 1, Nq, N, 0, N, N, N);
+    sweep3<true>(s_t2, s_t1, E, N, 1, Nq, N, 1, Nq, N, N);
+    sweep3<true>(s_g, s_t2, E, N, 1, Nq, N, 2, Nq, Nq, N);
+    for (int k = lane; k < q3; k += 32) s_g[k] *= W[k];
+    __syncwarp();
+    sweep3<true>(s_t2, s_g, E, 1, N, N, Nq, 2, Nq, Nq, Nq);
+    sweep3<true>(s_t1, s_t2, E, 1, N, N, Nq, 1, Nq, Nq, N);
+    sweep3<true>(s_a, s_t1, E, 1, N, N, Nq, 0, Nq, N, N);
+    for (int i = lane; i < n3; i += 32) s_out[i] += s_a[i];
+    __syncwarp();
   }
 
   // ---- faces
@@ -232,7 +249,7 @@ __global__ void __launch_bounds__(128) generic_apply_kernel(GenericArgs a) {
           const double *mo = a.mortar + S + off;
           int64_t MP = a.mortar_nodes;
           if (faces_p == 0) {
-            for (int k = threadIdx.x; k < nq2; k += blockDim.x) {
+            for (int k = lane; k < nq2; k += 32) {
               double du = s_m[k] - mo[7 * MP + k];
               double Am0 = mo[k], Am1 = mo[MP + k], Am2 = mo[2 * MP + k];
               double t1 = -(Am0 * s_m[mQ * mQ + k] + Am1 * s_m[2 * mQ * mQ + k] + Am2 * s_m[3 * mQ * mQ + k]);
@@ -241,7 +258,7 @@ __global__ void __launch_bounds__(128) generic_apply_kernel(GenericArgs a) {
               s_t[2 * mQ * mQ + k] = -Am1 * du;
               s_t[3 * mQ * mQ + k] = -Am2 * du;
             }
-            __syncthreads();
+            __syncwarp();
           } else {
             int j = (M == 4) ? sub[i] : 0;
             int hxp = p_big ? 1 + (j & 1) : 0, hyp = p_big ? 1 + (j >> 1) : 0;
@@ -249,7 +266,7 @@ __global__ void __launch_bounds__(128) generic_apply_kernel(GenericArgs a) {
             const double *vp = (ep_i >= 0) ? a.u + a.nodal_stride[ep_i]
                                            : a.ughost + a.ghost_nodal_stride[-ep_i - 1];
             traces_on_mortar(a, vp, deg_p, f_p, dq, hxp, hyp, s_p, mQ * mQ, s_tr, s_2d);
-            for (int k = threadIdx.x; k < nq2; k += blockDim.x) {
+            for (int k = lane; k < nq2; k += 32) {
               int kp = perm_index(nq, perm, k % nq, k / nq);
               double du = s_m[k] - s_p[kp];
               double Am0 = mo[k], Am1 = mo[MP + k], Am2 = mo[2 * MP + k];
@@ -261,7 +278,7 @@ __global__ void __launch_bounds__(128) generic_apply_kernel(GenericArgs a) {
               s_t[2 * mQ * mQ + k] = -.5 * Am1 * du;
               s_t[3 * mQ * mQ + k] = -.5 * Am2 * du;
             }
-            __syncthreads();
+            __syncwarp();
           }
           // test: E^T (w (x) w . t), lift, D_l^T for the term2 components
           const double *w = a.tabdata + a.tab->w_off[dq - 1];
@@ -269,19 +286,19 @@ __global__ void __launch_bounds__(128) generic_apply_kernel(GenericArgs a) {
           int n = (f & 1) ? N - 1 : 0;
           for (int c = 0; c < 4; ++c) {
             double *t = s_t + c * mQ * mQ;
-            for (int k = threadIdx.x; k < nq2; k += blockDim.x) t[k] *= w[k % nq] * w[k / nq];
-            __syncthreads();
+            for (int k = lane; k < nq2; k += 32) t[k] *= w[k % nq] * w[k / nq];
+            __syncwarp();
             sweep2(s_2d, t, Ey, 1, N, N, nq, 1, nq, nq);      // [N x nq] rows b
             sweep2(s_r, s_2d, Ex, 1, N, N, nq, 0, nq, N);     // [N x N]
             if (c == 0) {
-              for (int idx = threadIdx.x; idx < N * N; idx += blockDim.x)
+              for (int idx = lane; idx < N * N; idx += 32)
                 s_out[vol_index(N, f, idx % N, idx / N, n)] += s_r[idx];
             } else {
               int l = c - 1;
               int stride = (l == 0) ? 1 : (l == 1) ? N : N * N;
               if (l == (f >> 1)) {
                 // normal direction: every volume node receives one contribution
-                for (int v = threadIdx.x; v < n3; v += blockDim.x) {
+                for (int v = lane; v < n3; v += 32) {
                   int i_l = (l == 0) ? v % N : (l == 1) ? (v / N) % N : v / (N * N);
                   int vface = v + (n - i_l) * stride;   // node on the face in the same line
                   int i0 = vface % N, i1 = (vface / N) % N, i2 = vface / (N * N);
@@ -290,7 +307,7 @@ __global__ void __launch_bounds__(128) generic_apply_kernel(GenericArgs a) {
                 }
               } else {
                 // tangential: stays on the face
-                for (int idx = threadIdx.x; idx < N * N; idx += blockDim.x) {
+                for (int idx = lane; idx < N * N; idx += 32) {
                   int fa = idx % N, fb = idx / N;
                   int v = vol_index(N, f, fa, fb, n);
                   int i_l = (l == 0) ? v % N : (l == 1) ? (v / N) % N : v / (N * N);
@@ -305,7 +322,7 @@ __global__ void __launch_bounds__(128) generic_apply_kernel(GenericArgs a) {
                 }
               }
             }
-            __syncthreads();
+            __syncwarp();
           }
         }
         off += nq2;
@@ -313,7 +330,7 @@ __global__ void __launch_bounds__(128) generic_apply_kernel(GenericArgs a) {
     }
   }
   double *oe = a.Au + a.nodal_stride[e];
-  for (int i = threadIdx.x; i < n3; i += blockDim.x) oe[i] = s_out[i];
+  for (int i = lane; i < n3; i += 32) oe[i] = s_out[i];
 }
 
 // ---- volume quadrature operators, one CTA per element, any (deg, deg_quad) ----------
@@ -351,9 +368,9 @@ __global__ void __launch_bounds__(128) quad_ops_kernel(QuadArgs a) {
   if (a.mode == 0 || a.mode == 2) {
     for (int i = threadIdx.x; i < n3; i += blockDim.x) s0[i] = a.in[ns + i];
     __syncthreads();
-    sweep3(s1, s0, E, N, 1, Nq, N, 0, N, N, N);
-    sweep3(s2, s1, E, N, 1, Nq, N, 1, Nq, N, N);
-    sweep3(s0, s2, E, N, 1, Nq, N, 2, Nq, Nq, N);
+    sweep3<false>(s1, s0, E, N, 1, Nq, N, 0, N, N, N);
+    sweep3<false>(s2, s1, E, N, 1, Nq, N, 1, Nq, N, N);
+    sweep3<false>(s0, s2, E, N, 1, Nq, N, 2, Nq, Nq, N);
     if (a.mode == 0) {
       for (int k = threadIdx.x; k < q3; k += blockDim.x) a.out[qs + k] = s0[k];
       return;
@@ -367,9 +384,9 @@ __global__ void __launch_bounds__(128) quad_ops_kernel(QuadArgs a) {
     s0[k] *= w[ic] * w[ib] * w[ia] * (a.jac ? a.jac[qs + k] : 1.);
   }
   __syncthreads();
-  sweep3(s1, s0, E, 1, N, N, Nq, 2, Nq, Nq, Nq);
-  sweep3(s2, s1, E, 1, N, N, Nq, 1, Nq, Nq, N);
-  sweep3(s0, s2, E, 1, N, N, Nq, 0, Nq, N, N);
+  sweep3<false>(s1, s0, E, 1, N, N, Nq, 2, Nq, Nq, Nq);
+  sweep3<false>(s2, s1, E, 1, N, N, Nq, 1, Nq, Nq, N);
+  sweep3<false>(s0, s2, E, 1, N, N, Nq, 0, Nq, N, N);
   for (int i = threadIdx.x; i < n3; i += blockDim.x) a.out[ns + i] = s0[i];
 }
 
@@ -389,6 +406,8 @@ void d4b_launch_quad_op(d4b_mesh *m, int mode, const double *d_in, const double 
   quad_ops_kernel<<<m->n_local, 128, smem, m->stream>>>(a);
   D4B_CUDA(cudaGetLastError());
 }
+
+void d4b_generic_configure(int smem_bytes);
 
 void d4b_launch_generic(d4b_mesh *m, const double *d_u, double *d_Au, int stiffness_only) {
   bool force_all = (stiffness_only != 0) || (m->fast.empty());
@@ -413,7 +432,13 @@ void d4b_launch_generic(d4b_mesh *m, const double *d_u, double *d_Au, int stiffn
   a.n_elem = n_elem;
   a.stiffness_only = stiffness_only;
   a.maxN = m->max_deg + 1; a.maxNq = m->max_deg_quad + 1;
-  generic_apply_kernel<<<n_elem, 128, m->generic_smem, m->stream>>>(a);
+  // as many elements (warps) per CTA as the shared memory of an SM allows, at most kMaxWarps
+  const int per_warp = m->generic_smem;
+  int warps = (200 * 1024) / per_warp;
+  warps = warps < 1 ? 1 : warps > kMaxWarps ? kMaxWarps : warps;
+  a.smem_doubles = per_warp / (int)sizeof(double);
+  d4b_generic_configure(per_warp * warps);
+  generic_apply_kernel<<<(n_elem + warps - 1) / warps, 32 * warps, (size_t)per_warp * warps, m->stream>>>(a);
   D4B_CUDA(cudaGetLastError());
 }
 
@@ -423,7 +448,7 @@ int d4b_generic_smem_bytes(int maxN, int maxNq) {
   size_t face = (size_t)12 * maxNq * maxNq;     // s_m, s_p, s_t inside the s_g region
   size_t g = (size_t)3 * maxNq * maxNq * maxNq;
   if (face > g) d += face - g;
-  return (int)(d * sizeof(double));
+  return (int)(d * sizeof(double));   // per warp (= per element in flight)
 }
 
 void d4b_generic_configure(int smem_bytes) {

@@ -54,7 +54,8 @@ struct D4bFastClass {
   int64_t *d_face_rec = nullptr; // [6*n_elem] face record offset
   int64_t *d_face_nbr = nullptr; // [6*n_elem] neighbour nodal offset / -1
   int32_t *d_face_code = nullptr;
-  int kind = 0;                  // 0: general conforming kernel, 1: tangential-free faces (d4b_flat_kernel.cuh)
+  int kind = 0;                  // 0: general conforming kernel, 1: tangential-free faces (d4b_flat_kernel.cuh),
+                                 // 2: hp mortar kernel (d4b_hp_kernel.cuh)
   void *d_face_meta = nullptr;   // kind 1: [6*n_elem] packed face descriptors
 };
 
@@ -147,6 +148,9 @@ struct d4b_mesh {
   double *d_uhat = nullptr;            // Gauss-collocated copy of the input vector
   double *d_flat_FF = nullptr;         // compact face records [3][N^2] of the tangential-free class
   int64_t n_flat_elem = 0;
+  int64_t n_hp_elem = 0;               // elements of the mortar kernel (d4b_hp_kernel.cuh)
+  void *d_hp_tabs = nullptr;           // its table offsets / data
+  double *d_hp_tabdata = nullptr;
   int64_t n_face_shared = 0, n_face_split = 0;
   int generic_smem = 0;
   D4bEpilogue epi;                     // epilogue of the next fast-kernel launches

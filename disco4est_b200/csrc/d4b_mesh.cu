@@ -254,6 +254,10 @@ extern "C" d4b_mesh_t *d4b_mesh_create(const d4b_mesh_desc_t *d) {
   std::vector<int32_t> generic;
   for (int e = 0; e < E; ++e)
     if (!is_fast[e]) generic.push_back(e);
+  // elements of equal degree next to each other: the warps of a CTA then carry equal work
+  std::stable_sort(generic.begin(), generic.end(), [&](int x, int y) {
+    return d->deg_quad[x] != d->deg_quad[y] ? d->deg_quad[x] < d->deg_quad[y] : d->deg[x] < d->deg[y];
+  });
   m->n_generic = (int)generic.size();
   m->d_generic_elem = d4b_dev_upload<int32_t>(m, generic.data(), generic.size());
   if (m->n_generic > 0 || true) {
@@ -280,7 +284,7 @@ extern "C" void d4b_mesh_destroy(d4b_mesh_t *m) {
                   m->d_side_e_m, m->d_side_e_p, m->d_side_perm, m->d_side_sub_order,
                   m->d_side_mortar_stride, m->d_mortar, m->d_ughost, m->d_u_stage, m->d_Au_stage,
                   m->d_red, m->d_work[0], m->d_work[1], m->d_work[2], m->d_work[3], m->d_generic_elem,
-                  m->d_fast_FF, m->d_uhat, m->d_flat_FF, m->d_send_src, m->d_send_dst, m->d_send_cnt,
+                  m->d_fast_FF, m->d_uhat, m->d_flat_FF, m->d_hp_tabs, m->d_hp_tabdata, m->d_send_src, m->d_send_dst, m->d_send_cnt,
                   m->d_sendbuf, m->d_W};
   for (void *p : ptrs)
     if (p) cudaFree(p);
@@ -300,6 +304,7 @@ extern "C" int64_t d4b_mesh_local_nodes(const d4b_mesh_t *m) { return m->local_n
 extern "C" int64_t d4b_mesh_device_bytes(const d4b_mesh_t *m) { return m->device_bytes; }
 extern "C" int64_t d4b_mesh_fast_elements(const d4b_mesh_t *m) { return m->n_local - m->n_generic; }
 extern "C" int64_t d4b_mesh_flat_elements(const d4b_mesh_t *m) { return m->n_flat_elem; }
+extern "C" int64_t d4b_mesh_hp_elements(const d4b_mesh_t *m) { return m->n_hp_elem; }
 extern "C" int32_t d4b_mesh_launches_per_apply(const d4b_mesh_t *m) {
   int n = (m->n_generic > 0 || m->fast.empty()) ? 1 : 0;
   for (const auto &c : m->fast)

@@ -175,6 +175,9 @@ int64_t     d4b_mesh_device_bytes(const d4b_mesh_t *mesh);
 int64_t     d4b_mesh_fast_elements(const d4b_mesh_t *mesh);
 /* of those, elements whose six faces carry no tangential metric terms */
 int64_t     d4b_mesh_flat_elements(const d4b_mesh_t *mesh);
+/* elements taken by the hp mortar kernel: collocated quadrature (deg_quad == deg) on the element
+ * and its face neighbours, faces between unequal degrees and / or hanging faces             */
+int64_t     d4b_mesh_hp_elements(const d4b_mesh_t *mesh);
 /* CUDA kernels one d4b_apply launches on this mesh (for launch accounting)  */
 int32_t     d4b_mesh_launches_per_apply(const d4b_mesh_t *mesh);
 

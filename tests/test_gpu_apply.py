@@ -98,7 +98,28 @@ def test_uniform_meshes_take_the_fast_kernel(golden, meshes, case):
     assert m.fast_elements() == int(A["n_local"][0])
 
 
-@pytest.mark.parametrize("case", ["brick_l2_p3", "sphere_p2", "sphere_hp_amr1"])
+def test_hp_mortar_kernel_takes_the_collocated_hp_mesh(golden, monkeypatch):
+    """random hp refinement with deg_quad = deg (hanging faces both ways, unequal degrees, all
+    orientations): every element runs in fast_apply_kernel or hp_apply_kernel, the general kernel
+    gets nothing, and the result equals the general kernel's and the reference's"""
+    from disco4est_b200 import Mesh
+
+    A = golden("sphere_p_amr1")
+    u = np.ascontiguousarray(A["u"])
+    m1 = Mesh(A)
+    assert m1.hp_elements() > 0 and m1.fast_elements() == int(A["n_local"][0])
+    monkeypatch.setenv("D4B_NO_HP", "1")
+    m2 = Mesh(A)
+    monkeypatch.delenv("D4B_NO_HP")
+    assert m2.hp_elements() == 0 and m2.fast_elements() < m1.fast_elements()
+    a1, a2 = np.zeros_like(u), np.zeros_like(u)
+    m1.apply(u, a1); m2.apply(u, a2)
+    m1.close(); m2.close()
+    assert rel(a1, a2) < 1e-13
+    assert rel(a1, A["Au_plain"]) < TOL
+
+
+@pytest.mark.parametrize("case", ["brick_l2_p3", "sphere_p2", "sphere_hp_amr1", "sphere_p_amr1"])
 def test_fast_and_general_kernels_agree(golden, case, monkeypatch):
     from disco4est_b200 import Mesh
 

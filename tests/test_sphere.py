@@ -127,3 +127,14 @@ def test_properties_at_depth(kw):
     finally:
         del os.environ["D4B_FORCE_GENERIC"]
     assert np.linalg.norm(Ag - Au) < 1e-12 * np.linalg.norm(Au)
+
+
+@pytest.mark.gpu
+def test_random_hp_sphere_runs_in_the_hp_kernel():
+    from disco4est_b200 import Mesh
+    from disco4est_b200.sphere import sphere_desc
+
+    B, g = sphere_desc(2, pmax=5)
+    m = Mesh(B, geom=g)
+    assert m.fast_elements() == B["n_local"] and m.hp_elements() > 0.9 * B["n_local"]
+    m.close()
