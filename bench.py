@@ -240,7 +240,7 @@ def bench_sphere(args, rank, world, local_rank, torch, dist, dev):
 
     out = {}
     for name, kw, lvl in (("uniform_p", dict(p=args.deg), args.sphere_level),
-                          ("random_hp", dict(pmax=args.deg), max(args.sphere_level - 1, 1))):
+                          ("random_hp", dict(pmax=args.deg), args.sphere_level)):
         t0 = time.perf_counter()
         A, g = sphere_desc(lvl, **kw)
         E = int(A["n_local"])
@@ -431,7 +431,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-vcycle", action="store_true", help="skip the V-cycle metric")
     ap.add_argument("--no-sphere", action="store_true", help="skip the cubed-sphere applies")
-    ap.add_argument("--sphere-level", type=int, default=4, help="refinement level of each of the 13 sphere trees")
+    ap.add_argument("--sphere-level", type=int, default=5, help="refinement level of each of the 13 sphere trees")
     args = ap.parse_args()
     if args.impl == "reference":
         bench_reference(args)
