@@ -87,6 +87,7 @@ struct FastArgs {
   D4bEpilogue epi;
   const double *W;              // MASS kernels: weighted diagonal at the quadrature points (d4b_mesh_set_mass_diag)
   const int64_t *quad_stride;
+  int prefetch;                 // L2 prefetch of the block's volume metric and face records at kernel start
 };
 
 template <int N>
@@ -95,9 +96,35 @@ struct Cfg {
   static constexpr int N3 = N * N * N;
   static constexpr int THREADS = (N == 7 || N == 6) ? 256 : 128;
   static constexpr int EPB = THREADS / NN;           // elements per CTA
+};
+
+// launch geometry of fast_apply_kernel by N = 2..8 (D4B_FAST_THREADS / D4B_FAST_MINB: compile-time
+// overrides for A/B sweeps, profiles/build_variants.sh); a one-warp block synchronises with __syncwarp
+#ifndef D4B_FAST_THREADS
+#define D4B_FAST_THREADS {0, 0, 128, 128, 32, 128, 256, 256, 128}
+#endif
+#ifndef D4B_FAST_MINB
+#define D4B_FAST_MINB {0, 0, 1, 1, 20, 1, 1, 1, 1}
+#endif
+template <int N>
+struct CurvedCfg {
+  static constexpr int NN = N * N, N3 = N * N * N;
+  static constexpr int kThreads[9] = D4B_FAST_THREADS;
+  static constexpr int kMinBlocks[9] = D4B_FAST_MINB;
+  static constexpr int THREADS = kThreads[N];
+  static constexpr int MIN_BLOCKS = kMinBlocks[N];
+  static constexpr int EPB = THREADS / NN;
   // shared doubles per element: V0,V1,V2 + FT (12*NN) + NB (8*NN) + NB2 (4*NN)
   static constexpr int SH_PER_ELEM = 3 * N3 + 24 * NN;
 };
+template <int THREADS>
+__device__ __forceinline__ void curved_sync() {
+  if (THREADS == 32) { __syncwarp(); return; }
+  __syncthreads();
+}
+__device__ __forceinline__ void l2_prefetch_bulk(const void *ptr, unsigned bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(ptr), "r"(bytes) : "memory");
+}
 
 // my-order face point (a,b) -> neighbour-order (xp,yp); returns yp*n + xp
 __device__ __forceinline__ int perm_xy(int n, int perm, int a, int b) {
@@ -172,8 +199,8 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) interp_kernel(const int32_t *
 
 // ---- kernel 2: the apply in the Gauss basis ------------------------------------
 template <int N, bool MASS>
-__global__ void __launch_bounds__(Cfg<N>::THREADS) fast_apply_kernel(FastArgs a) {
-  using C = Cfg<N>;
+__global__ void __launch_bounds__(CurvedCfg<N>::THREADS, CurvedCfg<N>::MIN_BLOCKS) fast_apply_kernel(FastArgs a) {
+  using C = CurvedCfg<N>;
   constexpr int NN = C::NN, N3 = C::N3;
   extern __shared__ double smem[];
   const FastTab &T = c_tab[N];
@@ -189,6 +216,19 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) fast_apply_kernel(FastArgs a)
   double *NB2 = NB + 8 * NN;       // [2][2][NN] weighted tangential term2
   const int64_t ns = active ? a.nodal_stride[a.elem[ei]] : 0;
   double gt[N];
+  // the volume metric and the face records are first needed after the forward sweeps: ask the L2 now
+  if (a.prefetch) {
+    if (threadIdx.x == 0) {
+      constexpr unsigned kBlockBytes = C::EPB * 6 * N3 * sizeof(double);
+      const int e0 = a.first + (int)blockIdx.x * C::EPB, left = a.n_elem - e0;
+      l2_prefetch_bulk(a.FG + (size_t)e0 * (6 * N3), left >= C::EPB ? kBlockBytes : left * 6 * N3 * 8);
+    }
+    if (active) {
+      constexpr int L = (7 * NN * 8 + 127) / 128;   // 128-byte lines of one face record
+      for (int idx = lt; idx < 6 * L; idx += NN)
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(a.FF + a.face_rec[6 * ei + idx / L] + (idx % L) * 16));
+    }
+  }
 
   // ---- T-orientation (a,b) = (lx,ly): load uh, gradient along c, faces 4/5 ----
   if (active) {
@@ -198,7 +238,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) fast_apply_kernel(FastArgs a)
     double t4 = 0., n4 = 0., t5 = 0., n5 = 0.;
 #pragma unroll
     for (int i = 0; i < N; ++i) {
-      V0[lx + N * ly + NN * i] = uh[i];
+      V0[vix<N>(lx, ly, i)] = uh[i];
       t4 += T.e[0][i] * uh[i]; n4 += T.d[0][i] * uh[i];
       t5 += T.e[1][i] * uh[i]; n5 += T.d[1][i] * uh[i];
     }
@@ -212,12 +252,12 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) fast_apply_kernel(FastArgs a)
     FT[(4 * 2 + 0) * NN + lt] = t4; FT[(4 * 2 + 1) * NN + lt] = n4;
     FT[(5 * 2 + 0) * NN + lt] = t5; FT[(5 * 2 + 1) * NN + lt] = n5;
   }
-  __syncthreads();
+  curved_sync<C::THREADS>();
   if (active) {
     {   // S-orientation: (a, c) = (lx, ly), line along b: gradient, faces 2/3
       double uh[N];
 #pragma unroll
-      for (int i = 0; i < N; ++i) uh[i] = V0[lx + N * i + NN * ly];
+      for (int i = 0; i < N; ++i) uh[i] = V0[vix<N>(lx, i, ly)];
       double t2 = 0., n2 = 0., t3 = 0., n3 = 0.;
 #pragma unroll
       for (int i = 0; i < N; ++i) {
@@ -229,16 +269,15 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) fast_apply_kernel(FastArgs a)
         double s = 0.;
 #pragma unroll
         for (int i = 0; i < N; ++i) s += T.Dg[i2][i] * uh[i];
-        V2[lx + N * i2 + NN * ly] = s;
+        V2[vix<N>(lx, i2, ly)] = s;
       }
       FT[(2 * 2 + 0) * NN + lt] = t2; FT[(2 * 2 + 1) * NN + lt] = n2;
       FT[(3 * 2 + 0) * NN + lt] = t3; FT[(3 * 2 + 1) * NN + lt] = n3;
     }
     {   // R-orientation: (b, c) = (lx, ly), line along a: gradient, faces 0/1
       double uh[N];
-      const double *p = V0 + N * lx + NN * ly;
 #pragma unroll
-      for (int i = 0; i < N; ++i) uh[i] = p[i];
+      for (int i = 0; i < N; ++i) uh[i] = V0[vix<N>(i, lx, ly)];
       double t0 = 0., n0 = 0., t1 = 0., n1 = 0.;
 #pragma unroll
       for (int i = 0; i < N; ++i) {
@@ -250,19 +289,19 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) fast_apply_kernel(FastArgs a)
         double s = 0.;
 #pragma unroll
         for (int i = 0; i < N; ++i) s += T.Dg[i2][i] * uh[i];
-        V1[i2 + N * lx + NN * ly] = s;
+        V1[vix<N>(i2, lx, ly)] = s;
       }
       FT[(0 * 2 + 0) * NN + lt] = t0; FT[(0 * 2 + 1) * NN + lt] = n0;
       FT[(1 * 2 + 0) * NN + lt] = t1; FT[(1 * 2 + 1) * NN + lt] = n1;
     }
   }
-  __syncthreads();
+  curved_sync<C::THREADS>();
   if (active) {   // T-orientation: metric, Dg^T along c; V0 becomes the residual accumulator
     double ft[N];
     const double *G = a.FG + (size_t)ei * (6 * N3) + lt;
 #pragma unroll
     for (int c = 0; c < N; ++c) {
-      int idx = lt + NN * c;
+      const int idx = vix<N>(lx, ly, c);
       double gr = V1[idx], gs = V2[idx];
       double G00 = G[0 * N3 + NN * c], G01 = G[1 * N3 + NN * c], G02 = G[2 * N3 + NN * c];
       double G11 = G[3 * N3 + NN * c], G12 = G[4 * N3 + NN * c], G22 = G[5 * N3 + NN * c];
@@ -274,10 +313,10 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) fast_apply_kernel(FastArgs a)
     const double *Wd = MASS ? a.W + a.quad_stride[a.elem[ei]] + lt : nullptr;
 #pragma unroll
     for (int c = 0; c < N; ++c) {
-      double s = MASS ? Wd[NN * c] * V0[lt + NN * c] : 0.;
+      double s = MASS ? Wd[NN * c] * V0[vix<N>(lx, ly, c)] : 0.;
 #pragma unroll
       for (int i = 0; i < N; ++i) s += T.Dg[i][c] * ft[i];
-      V0[lt + NN * c] = s;
+      V0[vix<N>(lx, ly, c)] = s;
     }
   }
 
@@ -340,7 +379,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) fast_apply_kernel(FastArgs a)
         fm[sd] = fd[sd][nd] * dmn + fd[sd][t1] * dm1 + fd[sd][t2] * dm2;
       }
     }
-    __syncthreads();
+    curved_sync<C::THREADS>();
     if (active) {   // neighbour tangential derivatives at its own face point (lx, ly)
 #pragma unroll
       for (int sd = 0; sd < 2; ++sd) {
@@ -356,7 +395,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) fast_apply_kernel(FastArgs a)
         NB[(sd * 4 + 3) * NN + lt] = d2;
       }
     }
-    __syncthreads();
+    curved_sync<C::THREADS>();
     double ve[2], vd[2];
     if (active) {   // fluxes at my face Gauss point
       const double wxy = T.w[lx] * T.w[ly];
@@ -389,7 +428,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) fast_apply_kernel(FastArgs a)
         NB2[(sd * 2 + 1) * NN + lt] = fd[sd][t2] * wdu;
       }
     }
-    __syncthreads();
+    curved_sync<C::THREADS>();
     if (active) {   // transposed tangential derivatives, rank-1 update of the normal lines
 #pragma unroll
       for (int sd = 0; sd < 2; ++sd) {
@@ -399,72 +438,68 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) fast_apply_kernel(FastArgs a)
         for (int i = 0; i < N; ++i) s += T.Dg[i][lx] * w1[N * ly + i] + T.Dg[i][ly] * w2[N * i + lx];
         ve[sd] += s;
       }
-      int base, stride;
-      if (nd == 0) { base = N * lx + NN * ly; stride = 1; }
-      else if (nd == 1) { base = lx + NN * ly; stride = N; }
-      else { base = lx + N * ly; stride = NN; }
 #pragma unroll
-      for (int l = 0; l < N; ++l)
-        V0[base + l * stride] += T.e[0][l] * ve[0] + T.d[0][l] * vd[0] + T.e[1][l] * ve[1] + T.d[1][l] * vd[1];
+      for (int l = 0; l < N; ++l) {
+        const int v = (nd == 0) ? vix<N>(l, lx, ly) : (nd == 1) ? vix<N>(lx, l, ly) : vix<N>(lx, ly, l);
+        V0[v] += T.e[0][l] * ve[0] + T.d[0][l] * vd[0] + T.e[1][l] * ve[1] + T.d[1][l] * vd[1];
+      }
     }
     // the barrier after the next pair's first stage orders these V0 updates and NB2 reads
   }
-  __syncthreads();
+  curved_sync<C::THREADS>();
 
   // ---- backward --------------------------------------------------------------
   if (active) {   // S-orientation: + Dg^T F_s
     double fs[N];
 #pragma unroll
-    for (int i = 0; i < N; ++i) fs[i] = V2[lx + N * i + NN * ly];
+    for (int i = 0; i < N; ++i) fs[i] = V2[vix<N>(lx, i, ly)];
 #pragma unroll
     for (int b = 0; b < N; ++b) {
       double s = 0.;
 #pragma unroll
       for (int i = 0; i < N; ++i) s += T.Dg[i][b] * fs[i];
-      V0[lx + N * b + NN * ly] += s;
+      V0[vix<N>(lx, b, ly)] += s;
     }
   }
-  __syncthreads();
+  curved_sync<C::THREADS>();
   if (active) {   // R-orientation: + Dg^T F_r, then I^T along a
     double fr[N], tot[N];
-    double *p = V0 + N * lx + NN * ly;
 #pragma unroll
-    for (int i = 0; i < N; ++i) fr[i] = V1[i + N * lx + NN * ly];
+    for (int i = 0; i < N; ++i) fr[i] = V1[vix<N>(i, lx, ly)];
 #pragma unroll
     for (int i2 = 0; i2 < N; ++i2) {
       double s = 0.;
 #pragma unroll
       for (int i = 0; i < N; ++i) s += T.Dg[i][i2] * fr[i];
-      tot[i2] = p[i2] + s;
+      tot[i2] = V0[vix<N>(i2, lx, ly)] + s;
     }
 #pragma unroll
     for (int i2 = 0; i2 < N; ++i2) {
       double s = 0.;
 #pragma unroll
       for (int i = 0; i < N; ++i) s += T.I[i][i2] * tot[i];
-      p[i2] = s;
+      V0[vix<N>(i2, lx, ly)] = s;
     }
   }
-  __syncthreads();
+  curved_sync<C::THREADS>();
   if (active) {   // S-orientation: I^T along b
     double l[N];
-    double *p = V0 + lx + NN * ly;
 #pragma unroll
-    for (int i = 0; i < N; ++i) l[i] = p[N * i];
+    for (int i = 0; i < N; ++i) l[i] = V0[vix<N>(lx, i, ly)];
 #pragma unroll
     for (int i2 = 0; i2 < N; ++i2) {
       double s = 0.;
 #pragma unroll
       for (int i = 0; i < N; ++i) s += T.I[i][i2] * l[i];
-      p[N * i2] = s;
+      V0[vix<N>(lx, i2, ly)] = s;
     }
   }
-  __syncthreads();
+  curved_sync<C::THREADS>();
   if (active) {   // T-orientation: I^T along c, write Au
     double l[N];
     const EpiCoef ec = epi_coef(a.epi);
 #pragma unroll
-    for (int i = 0; i < N; ++i) l[i] = V0[lt + NN * i];
+    for (int i = 0; i < N; ++i) l[i] = V0[vix<N>(lx, ly, i)];
 #pragma unroll
     for (int c = 0; c < N; ++c) {
       double s = 0.;
@@ -582,7 +617,7 @@ void launch_interp(d4b_mesh *m, const D4bFastClass &cls, const double *d_u, int 
 
 template <int N>
 void launch_fast(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, int last) {
-  using C = Cfg<N>;
+  using C = CurvedCfg<N>;
   if (last <= first) return;
   FastArgs a;
   a.elem = cls.d_elem; a.first = first; a.n_elem = last;
@@ -598,6 +633,7 @@ void launch_fast(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, 
     D4B_CUDA(cudaFuncSetAttribute(fast_apply_kernel<N, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = true;
   }
+  a.prefetch = getenv("D4B_PREFETCH") ? atoi(getenv("D4B_PREFETCH")) : 1;
   int grid = (last - first + C::EPB - 1) / C::EPB;
   if (m->d_W) fast_apply_kernel<N, true><<<grid, C::THREADS, smem, m->stream>>>(a);
   else fast_apply_kernel<N, false><<<grid, C::THREADS, smem, m->stream>>>(a);
