@@ -299,10 +299,12 @@ def bench_ours(args):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    # only the JSON line belongs on stdout: NCCL prints its version banner there (at NCCL_DEBUG=VERSION
+    # and WARN alike), so everything else this process writes to fd 1 goes to stderr
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     if world > 1:
-        # NCCL_DEBUG=VERSION makes NCCL print its banner on stdout, where only the JSON line belongs
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
@@ -414,7 +416,8 @@ def bench_ours(args):
             out["vcycle"] = vc
         if sp is not None:
             out["cubed_sphere"] = sp
-        print(json.dumps(out))
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(out) + "\n").encode())
     if world > 1:
         comm_destroy()
         dist.destroy_process_group()

@@ -53,44 +53,75 @@ struct HpArgs {
 
 template <int N>
 __host__ __device__ constexpr int hp_smem_doubles(int mM) {
-  // V0..V3, FT[6][2][NN], OF[4][NN], RF[4][NN], NF/QM/QP/TT [4][mM^2] each, TMP [mM^2]
-  return 4 * N * N * N + 20 * N * N + 17 * mM * mM;
+  // V0..V3, FT[6][2][NN], OF[4][NN], RF[4][NN], NF/QM/QP/TT/TMP [4][mM^2] each
+  return 4 * N * N * N + 20 * N * N + 20 * mM * mM;
 }
 
-// out[M x M] = (Ty (x) Tx) in[n x n]; T* = [M][n] row-major in global memory; tmp: n*M doubles
-__device__ __forceinline__ void hp_interp2(double *out, const double *in, const double *Tx, const double *Ty, int n,
-                                           int M, double *tmp, int lane) {
-  for (int idx = lane; idx < n * M; idx += 32) {     // tmp[b*M + x] = sum_a Tx[x][a] in[b*n + a]
-    const int x = idx % M, b = idx / M;
-    double s = 0.;
-    for (int a = 0; a < n; ++a) s += __ldg(Tx + x * n + a) * in[b * n + a];
-    tmp[idx] = s;
+// idx / M for idx < 64, M <= 8 without an integer division
+__device__ __forceinline__ int hp_div(int idx, float inv) { return (int)(((float)idx + .5f) * inv); }
+
+// Four face arrays at once (u, d/dn, d/dt1, d/dt2): out[q][M x M] = (Ty (x) Tx) in[q][n x n].
+// T* = [M][n] row-major in global memory; tmp: 4*n*M doubles.  NC = n when it is known at
+// compile time (the element's own side), 0 otherwise (the neighbour's).
+template <int NC>
+__device__ __forceinline__ void hp_interp4(double *out, int ostride, const double *in, int istride, const double *Tx,
+                                           const double *Ty, int n_rt, int M, double *tmp, int lane) {
+  const int n = NC ? NC : n_rt, nM = n * M;
+  const float invM = 1.f / (float)M;
+  for (int idx = lane; idx < nM; idx += 32) {     // tmp[q][b*M + x] = sum_a Tx[x][a] in[q][b*n + a]
+    const int b = hp_div(idx, invM), x = idx - b * M;
+    double s0 = 0., s1 = 0., s2 = 0., s3 = 0.;
+    const double *row = in + b * n;
+#pragma unroll
+    for (int a = 0; a < (NC ? NC : 8); ++a) {
+      if (!NC && a >= n) break;
+      const double t = __ldg(Tx + x * n + a);
+      s0 += t * row[a]; s1 += t * row[istride + a]; s2 += t * row[2 * istride + a]; s3 += t * row[3 * istride + a];
+    }
+    tmp[idx] = s0; tmp[nM + idx] = s1; tmp[2 * nM + idx] = s2; tmp[3 * nM + idx] = s3;
   }
   __syncwarp();
-  for (int idx = lane; idx < M * M; idx += 32) {     // out[y*M + x] = sum_b Ty[y][b] tmp[b*M + x]
-    const int x = idx % M, y = idx / M;
-    double s = 0.;
-    for (int b = 0; b < n; ++b) s += __ldg(Ty + y * n + b) * tmp[b * M + x];
-    out[idx] = s;
+  for (int idx = lane; idx < M * M; idx += 32) {  // out[q][y*M + x] = sum_b Ty[y][b] tmp[q][b*M + x]
+    const int y = hp_div(idx, invM), x = idx - y * M;
+    double s0 = 0., s1 = 0., s2 = 0., s3 = 0.;
+#pragma unroll
+    for (int b = 0; b < (NC ? NC : 8); ++b) {
+      if (!NC && b >= n) break;
+      const double t = __ldg(Ty + y * n + b);
+      const double *c = tmp + b * M + x;
+      s0 += t * c[0]; s1 += t * c[nM]; s2 += t * c[2 * nM]; s3 += t * c[3 * nM];
+    }
+    out[idx] = s0; out[ostride + idx] = s1; out[2 * ostride + idx] = s2; out[3 * ostride + idx] = s3;
   }
   __syncwarp();
 }
 
-// out[n x n] += (Ty (x) Tx)^T in[M x M]
-__device__ __forceinline__ void hp_project2(double *out, const double *in, const double *Tx, const double *Ty, int n,
-                                            int M, double *tmp, int lane) {
-  for (int idx = lane; idx < M * n; idx += 32) {     // tmp[y*n + a] = sum_x Tx[x][a] in[y*M + x]
-    const int a = idx % n, y = idx / n;
-    double s = 0.;
-    for (int x = 0; x < M; ++x) s += __ldg(Tx + x * n + a) * in[y * M + x];
-    tmp[idx] = s;
+// out[q][n x n] += (Ty (x) Tx)^T in[q][M x M], q = 0..3; tmp: 4*M*n doubles
+template <int NC>
+__device__ __forceinline__ void hp_project4(double *out, int ostride, const double *in, int istride, const double *Tx,
+                                            const double *Ty, int M, double *tmp, int lane) {
+  constexpr int n = NC;
+  const int Mn = M * n;
+  for (int idx = lane; idx < Mn; idx += 32) {     // tmp[q][y*n + a] = sum_x Tx[x][a] in[q][y*M + x]
+    const int y = idx / n, a = idx - y * n;
+    double s0 = 0., s1 = 0., s2 = 0., s3 = 0.;
+    const double *row = in + y * M;
+    for (int x = 0; x < M; ++x) {
+      const double t = __ldg(Tx + x * n + a);
+      s0 += t * row[x]; s1 += t * row[istride + x]; s2 += t * row[2 * istride + x]; s3 += t * row[3 * istride + x];
+    }
+    tmp[idx] = s0; tmp[Mn + idx] = s1; tmp[2 * Mn + idx] = s2; tmp[3 * Mn + idx] = s3;
   }
   __syncwarp();
-  for (int idx = lane; idx < n * n; idx += 32) {     // out[b*n + a] += sum_y Ty[y][b] tmp[y*n + a]
-    const int a = idx % n, b = idx / n;
-    double s = 0.;
-    for (int y = 0; y < M; ++y) s += __ldg(Ty + y * n + b) * tmp[y * n + a];
-    out[idx] += s;
+  for (int idx = lane; idx < n * n; idx += 32) {  // out[q][b*n + a] += sum_y Ty[y][b] tmp[q][y*n + a]
+    const int b = idx / n, a = idx - b * n;
+    double s0 = 0., s1 = 0., s2 = 0., s3 = 0.;
+    for (int y = 0; y < M; ++y) {
+      const double t = __ldg(Ty + y * n + b);
+      const double *c = tmp + y * n + a;
+      s0 += t * c[0]; s1 += t * c[Mn]; s2 += t * c[2 * Mn]; s3 += t * c[3 * Mn];
+    }
+    out[idx] += s0; out[ostride + idx] += s1; out[2 * ostride + idx] += s2; out[3 * ostride + idx] += s3;
   }
   __syncwarp();
 }
@@ -115,7 +146,7 @@ __global__ void __launch_bounds__(128) hp_apply_kernel(HpArgs a) {
   double *QM = NF + 4 * mM2;     // [4][mM2]  own side at the mortar points
   double *QP = QM + 4 * mM2;     // [4][mM2]  neighbour at the mortar points, its order
   double *TT = QP + 4 * mM2;     // [4][mM2]  weighted fluxes
-  double *TMP = TT + 4 * mM2;    // [mM2]
+  double *TMP = TT + 4 * mM2;    // [4][mM2]
 
   // ---- lines along c: load uh, d/dt, faces 4/5
   for (int lt = lane; lt < NN; lt += 32) {
@@ -290,7 +321,7 @@ __global__ void __launch_bounds__(128) hp_apply_kernel(HpArgs a) {
         const double *qm = OF;
         int qms = NN;
         if (!own_id) {
-          for (int q = 0; q < 4; ++q) hp_interp2(QM + q * mM2, OF + q * NN, Tx, Ty, N, Mq, TMP, lane);
+          hp_interp4<N>(QM, mM2, OF, NN, Tx, Ty, N, Mq, TMP, lane);
           qm = QM; qms = mM2;
         }
         const double *qp = nullptr;
@@ -301,8 +332,9 @@ __global__ void __launch_bounds__(128) hp_apply_kernel(HpArgs a) {
           const int Np2 = Np * Np;
           const double *up = a.uh + ((ep_i >= 0) ? a.nodal_stride[ep_i] : a.local_nodes + a.ghost_nodal_stride[-ep_i - 1]);
           const FastTab &Tp = c_tab[Np];
+          const float invNp = 1.f / (float)Np;
           for (int kp = lane; kp < Np2; kp += 32) {
-            const int xp = kp % Np, yp = kp / Np;
+            const int yp = hp_div(kp, invNp), xp = kp - yp * Np;
             int base, stride;
             if (ndp == 0) { base = Np * xp + Np2 * yp; stride = 1; }
             else if (ndp == 1) { base = xp + Np2 * yp; stride = Np; }
@@ -319,7 +351,7 @@ __global__ void __launch_bounds__(128) hp_apply_kernel(HpArgs a) {
           __syncwarp();
           const double *Dp = a.tabdata + a.tabs->dg_off[Np];
           for (int kp = lane; kp < Np2; kp += 32) {
-            const int xp = kp % Np, yp = kp / Np;
+            const int yp = hp_div(kp, invNp), xp = kp - yp * Np;
             double d1 = 0., d2 = 0.;
             for (int l = 0; l < Np; ++l) {
               d1 += __ldg(Dp + xp * Np + l) * NF[Np * yp + l];
@@ -335,7 +367,7 @@ __global__ void __launch_bounds__(128) hp_apply_kernel(HpArgs a) {
             qp = NF;
           } else {
             const double *Txp = a.tabdata + a.tabs->t_off[Np][Mq][hxp], *Typ = a.tabdata + a.tabs->t_off[Np][Mq][hyp];
-            for (int q = 0; q < 4; ++q) hp_interp2(QP + q * mM2, NF + q * mM2, Txp, Typ, Np, Mq, TMP, lane);
+            hp_interp4<0>(QP, mM2, NF, mM2, Txp, Typ, Np, Mq, TMP, lane);
             qp = QP;
           }
         }
@@ -344,8 +376,9 @@ __global__ void __launch_bounds__(128) hp_apply_kernel(HpArgs a) {
           const double *mo = a.mortar + S + off;
           const FastTab &Tq = c_tab[Mq];
           const int t1p = (ndp == 0) ? 1 : 0, t2p = (ndp == 2) ? 1 : 2;
+          const float invMq = 1.f / (float)Mq;
           for (int k = lane; k < Mq2; k += 32) {
-            const int kx = k % Mq, ky = k / Mq;
+            const int ky = hp_div(k, invMq), kx = k - ky * Mq;
             const double Am[3] = {mo[k], mo[a.MP + k], mo[2 * a.MP + k]};
             const double Sg = mo[6 * a.MP + k];
             const double um = qm[k];
@@ -377,7 +410,7 @@ __global__ void __launch_bounds__(128) hp_apply_kernel(HpArgs a) {
             for (int lt = lane; lt < NN; lt += 32) RF[q * NN + lt] += TT[q * mM2 + lt];
           __syncwarp();
         } else {
-          for (int q = 0; q < 4; ++q) hp_project2(RF + q * NN, TT + q * mM2, Tx, Ty, N, Mq, TMP, lane);
+          hp_project4<N>(RF, NN, TT, mM2, Tx, Ty, Mq, TMP, lane);
         }
       }
       off += Mq2;
