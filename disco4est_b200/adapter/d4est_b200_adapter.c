@@ -353,6 +353,70 @@ d4est_b200_ctx_destroy (d4est_b200_ctx_t * ctx)
   free (ctx);
 }
 
+void
+d4est_b200_geom_desc_fill (d4b_geom_desc_t * g, p4est_t * p4est, d4est_ghost_t * ghost,
+                           d4est_geometry_t * d4est_geom, d4est_mesh_face_h_t face_h_type)
+{
+  memset (g, 0, sizeof (*g));
+  if (d4est_geom->DX_compute_method != GEOM_COMPUTE_ANALYTIC || d4est_geom->JAC_compute_method != GEOM_COMPUTE_NUMERICAL)
+    D4EST_ABORT ("d4est_b200: device geometry needs DX_compute_method = analytic, JAC_compute_method = numerical");
+  if (d4est_geom->geom_type == GEOM_BRICK) {
+    d4est_geometry_brick_attr_t *b = (d4est_geometry_brick_attr_t *) d4est_geom->user;
+    g->geom_type = D4B_GEOM_BRICK;
+    g->X0 = b->X0; g->X1 = b->X1; g->Y0 = b->Y0; g->Y1 = b->Y1; g->Z0 = b->Z0; g->Z1 = b->Z1;
+  }
+  else if (d4est_geom->geom_type == GEOM_CUBED_SPHERE_13TREE) {
+    d4est_geometry_cubed_sphere_attr_t *sp = (d4est_geometry_cubed_sphere_attr_t *) d4est_geom->user;
+    g->geom_type = D4B_GEOM_CUBED_SPHERE;
+    g->R0 = sp->R0; g->R1 = sp->R1; g->R2 = sp->R2;
+    g->compactify_inner_shell = sp->compactify_inner_shell;
+    g->compactify_outer_shell = sp->compactify_outer_shell;
+  }
+  else
+    D4EST_ABORT ("d4est_b200: device geometry supports the brick and the 13-tree cubed sphere");
+  g->face_h_type = (int32_t) face_h_type;   /* d4b_face_h_t mirrors d4est_mesh_face_h_t */
+  const int nl = p4est->local_num_quadrants, ng = (int) ghost->ghost->ghosts.elem_count;
+  int32_t *et = (int32_t *) malloc (sizeof (int32_t) * (nl > 0 ? nl : 1));
+  int32_t *eq = (int32_t *) malloc (sizeof (int32_t) * 3 * (nl > 0 ? nl : 1));
+  int32_t *ed_ = (int32_t *) malloc (sizeof (int32_t) * (nl > 0 ? nl : 1));
+  int32_t *gt = (int32_t *) malloc (sizeof (int32_t) * (ng > 0 ? ng : 1));
+  int32_t *gq = (int32_t *) malloc (sizeof (int32_t) * 3 * (ng > 0 ? ng : 1));
+  int32_t *gd = (int32_t *) malloc (sizeof (int32_t) * (ng > 0 ? ng : 1));
+  for (p4est_topidx_t tt = p4est->first_local_tree; tt <= p4est->last_local_tree; ++tt) {
+    p4est_tree_t *tree = p4est_tree_array_index (p4est->trees, tt);
+    sc_array_t *tquadrants = &tree->quadrants;
+    for (int qq = 0; qq < (int) tquadrants->elem_count; ++qq) {
+      p4est_quadrant_t *quad = p4est_quadrant_array_index (tquadrants, qq);
+      d4est_element_data_t *ed = (d4est_element_data_t *) (quad->p.user_data);
+      et[ed->id] = ed->tree; ed_[ed->id] = ed->dq;
+      for (int d = 0; d < 3; d++) eq[3 * ed->id + d] = ed->q[d];
+    }
+  }
+  for (int i = 0; i < ng; i++) {
+    d4est_element_data_t *ged = &ghost->ghost_elements[i];
+    gt[i] = ged->tree; gd[i] = ged->dq;
+    for (int d = 0; d < 3; d++) gq[3 * i + d] = ged->q[d];
+  }
+  g->elem_tree = et; g->elem_q = eq; g->elem_dq = ed_;
+  g->ghost_tree = gt; g->ghost_q = gq; g->ghost_dq = gd;
+}
+
+void
+d4est_b200_geom_desc_free (d4b_geom_desc_t * g)
+{
+  free ((void *) g->elem_tree); free ((void *) g->elem_q); free ((void *) g->elem_dq);
+  free ((void *) g->ghost_tree); free ((void *) g->ghost_q); free ((void *) g->ghost_dq);
+  memset (g, 0, sizeof (*g));
+}
+
+void
+d4est_b200_ctx_use_device_geometry (d4est_b200_ctx_t * ctx, d4est_geometry_t * d4est_geom,
+                                    d4est_mesh_face_h_t face_h_type)
+{
+  ctx->device_geom = d4est_geom;
+  ctx->device_face_h_type = (int) face_h_type;
+}
+
 #ifndef D4EST_B200_ADAPTER_NO_DEVICE
 d4b_mesh_t *
 d4est_b200_get_mesh (d4est_b200_ctx_t * ctx, p4est_t * p4est, d4est_ghost_t * ghost,
@@ -380,7 +444,14 @@ d4est_b200_get_mesh (d4est_b200_ctx_t * ctx, p4est_t * p4est, d4est_ghost_t * gh
   }
   d4est_b200_flat_t *fl = d4est_b200_flatten (p4est, ghost, d4est_factors, ctx->flux_data);
   d4est_b200_cached_mesh_t *c = &ctx->cache[victim];
-  c->mesh = d4b_mesh_create (&fl->desc);
+  if (ctx->device_geom) {
+    d4b_geom_desc_t gd;
+    d4est_b200_geom_desc_fill (&gd, p4est, ghost, ctx->device_geom, (d4est_mesh_face_h_t) ctx->device_face_h_type);
+    c->mesh = d4b_mesh_create_with_geometry (&fl->desc, &gd);
+    d4est_b200_geom_desc_free (&gd);
+  }
+  else
+    c->mesh = d4b_mesh_create (&fl->desc);
   d4est_b200_flat_destroy (fl);
   c->factors = d4est_factors;
   c->local_elements = ne;

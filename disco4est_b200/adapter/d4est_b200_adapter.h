@@ -22,6 +22,9 @@
 #include <d4est_krylov_pc.h>
 #include <d4est_quadrature.h>
 #include <d4est_xyz_functions.h>
+#include <d4est_geometry.h>
+#include <d4est_geometry_brick.h>
+#include <d4est_geometry_cubed_sphere.h>
 #include "d4est_b200.h"
 
 /* Owns the arrays a d4b_mesh_desc_t points to (those that are not aliases of
@@ -64,7 +67,25 @@ typedef struct
   d4est_b200_cached_mesh_t cache[D4EST_B200_CACHE];
   unsigned long clock;
   long uploads, applies;                   /* statistics                     */
+  /* device-generated geometric factors (d4est_b200_ctx_use_device_geometry) */
+  d4est_geometry_t *device_geom;
+  int device_face_h_type;
 } d4est_b200_ctx_t;
+
+/* Opt in to geometric factors generated on the device: from now on a mesh that is uploaded
+ * for this context takes J, rst_xyz and all mortar quantities from d4b_geom_compute (the map of
+ * d4est_geom evaluated at every quadrature point in a CUDA thread) instead of copying the
+ * arrays d4est_mesh_data_compute / d4est_mesh_compute_mortar_quadrature_quantities filled
+ * (src/Mesh/d4est_mesh.c:2543-2755, :481-1140); only the forest positions (tree, q, dq) and
+ * degrees of the local and ghost elements cross the bus.  Supported maps: brick, 13-tree cubed
+ * sphere with DX_compute_method = analytic, JAC_compute_method = numerical; aborts otherwise.
+ * face_h_type: the mesh's d4est_mesh_face_h_t (initial_extents->face_h_type).              */
+void d4est_b200_ctx_use_device_geometry (d4est_b200_ctx_t * ctx, d4est_geometry_t * d4est_geom,
+                                         d4est_mesh_face_h_t face_h_type);
+/* d4b_geom_desc_t of the reference's current forest; free with d4est_b200_geom_desc_free */
+void d4est_b200_geom_desc_fill (d4b_geom_desc_t * g, p4est_t * p4est, d4est_ghost_t * ghost,
+                                d4est_geometry_t * d4est_geom, d4est_mesh_face_h_t face_h_type);
+void d4est_b200_geom_desc_free (d4b_geom_desc_t * g);
 
 /* the device mesh for the reference's current mesh (uploads it on first use) */
 d4b_mesh_t *d4est_b200_get_mesh(d4est_b200_ctx_t *ctx, p4est_t *p4est, d4est_ghost_t *ghost,

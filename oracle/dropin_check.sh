@@ -9,11 +9,11 @@ export LD_LIBRARY_PATH=/usr/local/cuda/lib64:$LD_LIBRARY_PATH
 DRV="$HERE/_ref/ref_driver_b200"
 set -e
 echo "== brick 4^3 p=3, multigrid 4 V-cycles"
-"$DRV" "$HERE/configs/brick_poisson_mg.ini" - --uniform-deg 3 --mg 4 --fcg 30 --b200 | tail -4
+"$DRV" "$HERE/configs/brick_poisson_mg.ini" - --uniform-deg 3 --mg 4 --fcg 30 --b200 | tail -5
 echo "== brick 8^3 p=2, multigrid 3 V-cycles"
 sed 's/min_level = 2/min_level = 3/' "$HERE/configs/brick_poisson_mg.ini" > /tmp/d4b_mg_l3.ini
-"$DRV" /tmp/d4b_mg_l3.ini - --uniform-deg 2 --mg 3 --b200 | tail -2
+"$DRV" /tmp/d4b_mg_l3.ini - --uniform-deg 2 --mg 3 --b200 | tail -3
 echo "== cubed sphere, random hp AMR (hanging faces, all orientations): one apply"
-"$DRV" "$HERE/configs/sphere_hp.ini" - --amr 1 --b200 | tail -1
+"$DRV" "$HERE/configs/sphere_hp.ini" - --amr 1 --b200 | tail -2
 echo "== cubed sphere uniform p=2 (curved conforming kernel): one apply"
-"$DRV" "$HERE/configs/sphere_p.ini" - --uniform-deg 2 --b200 | tail -1
+"$DRV" "$HERE/configs/sphere_p.ini" - --uniform-deg 2 --b200 | tail -2

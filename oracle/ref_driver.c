@@ -401,6 +401,26 @@ main (int argc, char *argv[])
     printf ("{\"b200_apply_rel_l2\": %.3e, \"t_apply_b200_host_vectors_s\": %.6f, \"t_apply_reference_s\": %.6f}\n",
             sqrt (num / den), t_b200, best_plain < best_opt ? best_plain : best_opt);
     {
+      /* the same callback on a context that generates the geometric factors on the device
+       * (d4est_b200_ctx_use_device_geometry) instead of copying the reference's arrays */
+      d4est_b200_ctx_t *gctx = d4est_b200_ctx_new (flux_plain);
+      d4est_b200_ctx_use_device_geometry (gctx, d4est_geom, initial_grid_input->face_h_type);
+      d4est_elliptic_eqns_t fcns_g = {.build_residual = NULL,.apply_lhs = d4est_b200_apply_lhs,.user = gctx };
+      double *Au_g = P4EST_ALLOC_ZERO (double, local_nodes);
+      vecs.Au = Au_g;
+      d4est_elliptic_eqns_apply_lhs (p4est, d4est_ghost, d4est_ghost_data, &fcns_g, &vecs,
+                                     d4est_ops, d4est_geom, d4est_quad, d4est_factors);
+      double n2 = 0., d2 = 0.;
+      for (int i = 0; i < local_nodes; i++) {
+        n2 += (Au_g[i] - Au_plain[i]) * (Au_g[i] - Au_plain[i]);
+        d2 += Au_plain[i] * Au_plain[i];
+      }
+      printf ("{\"b200_device_geometry_apply_rel_l2\": %.3e}\n", sqrt (n2 / d2));
+      vecs.Au = Au_b;
+      P4EST_FREE (Au_g);
+      d4est_b200_ctx_destroy (gctx);
+    }
+    {
       /* Jacobian apply of a nonlinear problem: Laplacian + mass-type term.  Reference: the
        * problem files' loop over d4est_quadrature_apply_fofufofvlilj added to apply_aij
        * (constant_density_star_fcns.h:528-600); ours: d4est_b200_set_mass_term, then the same

@@ -35,6 +35,18 @@ def test_apply_lhs_callback_inside_the_reference(ini, args):
     assert res["b200_apply_rel_l2"] < 1e-12
 
 
+@pytest.mark.parametrize("ini,args", [("brick_poisson.ini", ["--uniform-deg", "3"]),
+                                      ("sphere_p.ini", ["--uniform-deg", "2"]),
+                                      ("sphere_p.ini", ["--amr", "1"]),
+                                      ("sphere_hp.ini", ["--amr", "1"])])
+def test_device_geometry_inside_the_reference(ini, args):
+    """d4est_b200_ctx_use_device_geometry: the adapter hands the forest positions of the reference's
+    elements to d4b_mesh_create_with_geometry; the operator equals d4est_laplacian_apply_aij"""
+    lines = run(ini, *args)
+    res = [l for l in lines if "b200_device_geometry_apply_rel_l2" in l][0]
+    assert res["b200_device_geometry_apply_rel_l2"] < 1e-12
+
+
 @pytest.mark.parametrize("ini,args", [("brick_poisson.ini", ["--uniform-deg", "3"]), ("sphere_hp.ini", ["--amr", "1"])])
 def test_jacobian_apply_with_mass_term_inside_the_reference(ini, args):
     """d4est_b200_set_mass_term + apply_lhs against apply_aij + the reference's fofufofvlilj loop"""
