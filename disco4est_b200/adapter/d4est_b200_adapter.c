@@ -354,6 +354,44 @@ d4est_b200_ctx_destroy (d4est_b200_ctx_t * ctx)
 }
 
 void
+d4est_b200_flat_eval_dirichlet (d4est_b200_flat_t * fl, d4est_operators_t * d4est_ops,
+                                d4est_geometry_t * d4est_geom, d4est_quadrature_t * d4est_quad,
+                                d4est_mesh_data_t * d4est_factors, d4est_laplacian_flux_data_t * flux_data)
+{
+  if (flux_data->bc_type != BC_DIRICHLET) return;
+  d4est_laplacian_dirichlet_bc_t *bc = (d4est_laplacian_dirichlet_bc_t *) flux_data->bc_data;
+  free (fl->dirichlet_g);
+  fl->dirichlet_g = (double *) calloc (fl->desc.local_mortar_nodes_quad + 1, sizeof (double));
+  for (int s = 0; s < fl->desc.n_sides; s++) {
+    if (fl->desc.side_faces_p[s] != 0) continue;
+    const int e = fl->desc.side_e_m[4 * s], f_m = fl->desc.side_f_m[s];
+    const int deg = fl->desc.deg[e], deg_quad = fl->desc.deg_quad[e];
+    const int fn = d4est_lgl_get_nodes ((P4EST_DIM) - 1, deg), fnq = d4est_lgl_get_nodes ((P4EST_DIM) - 1, deg_quad);
+    const int bstride = (P4EST_DIM) * d4est_factors->local_strides[e].boundary_quad_stride[f_m];
+    double *g = &fl->dirichlet_g[fl->desc.side_mortar_stride[s]];
+    if (bc->eval_method == EVAL_BNDRY_FCN_ON_QUAD) {
+      for (int i = 0; i < fnq; i++)
+        g[i] = bc->dirichlet_fcn (d4est_factors->xyz_m_mortar_quad[bstride + 0 * fnq + i],
+                                  d4est_factors->xyz_m_mortar_quad[bstride + 1 * fnq + i],
+                                  d4est_factors->xyz_m_mortar_quad[bstride + 2 * fnq + i], bc->user);
+    }
+    else {
+      double *g_lob = (double *) malloc (sizeof (double) * fn);
+      for (int i = 0; i < fn; i++)
+        g_lob[i] = bc->dirichlet_fcn (d4est_factors->xyz_m_mortar_lobatto[bstride + 0 * fnq + i],
+                                      d4est_factors->xyz_m_mortar_lobatto[bstride + 1 * fnq + i],
+                                      d4est_factors->xyz_m_mortar_lobatto[bstride + 2 * fnq + i], bc->user);
+      d4est_quadrature_mortar_t face_object;
+      memset (&face_object, 0, sizeof (face_object));
+      d4est_quadrature_interpolate (d4est_ops, d4est_quad, d4est_geom, &face_object, QUAD_OBJECT_MORTAR,
+                                    QUAD_INTEGRAND_UNKNOWN, g_lob, deg, g, deg_quad);
+      free (g_lob);
+    }
+  }
+  fl->desc.dirichlet_g_mortar_quad = fl->dirichlet_g;
+}
+
+void
 d4est_b200_geom_desc_fill (d4b_geom_desc_t * g, p4est_t * p4est, d4est_ghost_t * ghost,
                            d4est_geometry_t * d4est_geom, d4est_mesh_face_h_t face_h_type)
 {
@@ -444,6 +482,8 @@ d4est_b200_get_mesh (d4est_b200_ctx_t * ctx, p4est_t * p4est, d4est_ghost_t * gh
   }
   d4est_b200_flat_t *fl = d4est_b200_flatten (p4est, ghost, d4est_factors, ctx->flux_data);
   d4est_b200_cached_mesh_t *c = &ctx->cache[victim];
+  if (ctx->bc_ops)
+    d4est_b200_flat_eval_dirichlet (fl, ctx->bc_ops, ctx->bc_geom, ctx->bc_quad, d4est_factors, ctx->flux_data);
   if (ctx->device_geom) {
     d4b_geom_desc_t gd;
     d4est_b200_geom_desc_fill (&gd, p4est, ghost, ctx->device_geom, (d4est_mesh_face_h_t) ctx->device_face_h_type);
@@ -474,6 +514,31 @@ d4est_b200_apply_lhs (p4est_t * p4est, d4est_ghost_t * ghost,
   d4b_mesh_t *mesh = d4est_b200_get_mesh (ctx, p4est, ghost, d4est_factors);
   ctx->applies++;
   d4b_apply (mesh, prob_vecs->u, prob_vecs->Au);
+}
+
+/* ------------------------------------------------------------ right-hand side */
+void
+d4est_b200_build_rhs_with_strong_bc (d4est_b200_ctx_t * ctx, p4est_t * p4est, d4est_ghost_t * ghost,
+                                     d4est_ghost_data_t * ghost_data, d4est_operators_t * d4est_ops,
+                                     d4est_geometry_t * d4est_geom, d4est_quadrature_t * d4est_quad,
+                                     d4est_mesh_data_t * d4est_factors, d4est_elliptic_data_t * prob_vecs,
+                                     d4est_laplacian_flux_data_t * flux_fcn_data_for_build_rhs,
+                                     double *rhs, d4est_xyz_fcn_t problem_rhs_fcn,
+                                     d4est_mesh_init_field_option_t init_option, void *fcn_ctx, int which_field)
+{
+  (void) ghost_data; (void) prob_vecs; (void) which_field;
+  if (ctx->flux_data != flux_fcn_data_for_build_rhs)
+    D4EST_ABORT ("d4est_b200_build_rhs_with_strong_bc: the context was created from another flux data");
+  ctx->bc_ops = d4est_ops; ctx->bc_geom = d4est_geom; ctx->bc_quad = d4est_quad;
+  d4b_mesh_t *mesh = d4est_b200_get_mesh (ctx, p4est, ghost, d4est_factors);
+  const int on_quad = (init_option == INIT_FIELD_ON_QUAD);
+  if (!on_quad && init_option != INIT_FIELD_ON_LOBATTO) D4EST_ABORT ("Not a support init option");
+  const size_t nf = on_quad ? (size_t) d4est_factors->local_sizes.local_nodes_quad
+                            : (size_t) d4est_factors->local_sizes.local_nodes;
+  double *f = (double *) malloc (sizeof (double) * (nf + 1));
+  d4est_mesh_init_field (p4est, f, problem_rhs_fcn, d4est_ops, d4est_geom, d4est_factors, init_option, fcn_ctx);
+  d4b_build_rhs (mesh, f, on_quad, d4est_factors->J_quad, rhs);
+  free (f);
 }
 
 /* ------------------------------------------------------------ mass term */

@@ -70,7 +70,34 @@ typedef struct
   /* device-generated geometric factors (d4est_b200_ctx_use_device_geometry) */
   d4est_geometry_t *device_geom;
   int device_face_h_type;
+  /* set by d4est_b200_build_rhs_with_strong_bc: evaluate the Dirichlet function when a mesh is built */
+  d4est_operators_t *bc_ops;
+  d4est_geometry_t *bc_geom;
+  d4est_quadrature_t *bc_quad;
 } d4est_b200_ctx_t;
+
+/* Dirichlet data of flux_data->bc_data at the boundary-face quadrature points, evaluated the way
+ * d4est_laplacian_flux_sipg_dirichlet_aux does (src/dGMath/d4est_laplacian_flux_sipg.c:60-130):
+ * EVAL_BNDRY_FCN_ON_LOBATTO -- on the face LGL nodes (xyz_m_mortar_lobatto), then interpolated to
+ * the Gauss points; EVAL_BNDRY_FCN_ON_QUAD -- directly at xyz_m_mortar_quad.  Fills
+ * fl->dirichlet_g and points fl->desc.dirichlet_g_mortar_quad at it.                          */
+void d4est_b200_flat_eval_dirichlet (d4est_b200_flat_t * fl, d4est_operators_t * d4est_ops,
+                                     d4est_geometry_t * d4est_geom, d4est_quadrature_t * d4est_quad,
+                                     d4est_mesh_data_t * d4est_factors,
+                                     d4est_laplacian_flux_data_t * flux_data);
+
+/* drop-in for d4est_laplacian_build_rhs_with_strong_bc (src/dGMath/d4est_laplacian.c:15-140), same
+ * arguments: rhs = M f - A(0) on the device.  The mesh is built (and cached in ctx_for_rhs, a context
+ * created from flux_fcn_data_for_build_rhs) with that flux data's Dirichlet function evaluated at the
+ * boundary quadrature points; f is evaluated on the host through problem_rhs_fcn.            */
+void d4est_b200_build_rhs_with_strong_bc (d4est_b200_ctx_t * ctx_for_rhs, p4est_t * p4est, d4est_ghost_t * ghost,
+                                          d4est_ghost_data_t * ghost_data, d4est_operators_t * d4est_ops,
+                                          d4est_geometry_t * d4est_geom, d4est_quadrature_t * d4est_quad,
+                                          d4est_mesh_data_t * d4est_factors, d4est_elliptic_data_t * prob_vecs,
+                                          d4est_laplacian_flux_data_t * flux_fcn_data_for_build_rhs,
+                                          double *rhs, d4est_xyz_fcn_t problem_rhs_fcn,
+                                          d4est_mesh_init_field_option_t init_option, void *fcn_ctx,
+                                          int which_field);
 
 /* Opt in to geometric factors generated on the device: from now on a mesh that is uploaded
  * for this context takes J, rst_xyz and all mortar quantities from d4b_geom_compute (the map of

@@ -155,6 +155,21 @@ extern "C" void d4b_apply_mass(d4b_mesh_t *m, const double *x, const double *jac
   if (in.tmp || jac.tmp) D4B_CUDA(cudaStreamSynchronize(m->stream));
 }
 
+// rhs = M f - A(0), d4est_laplacian_build_rhs_with_strong_bc (src/dGMath/d4est_laplacian.c:15-140):
+// the operator applied to u = 0 leaves the inhomogeneous Dirichlet terms of the boundary faces
+extern "C" void d4b_build_rhs(d4b_mesh_t *m, const double *f, int32_t f_on_quad, const double *jac_quad, double *rhs) {
+  D4B_CHECK(m && f && jac_quad && rhs, "d4b_build_rhs: NULL argument");
+  DevIn in(m, f, f_on_quad ? m->local_nodes_quad : m->local_nodes), jac(m, jac_quad, m->local_nodes_quad);
+  DevOut o(m, rhs, m->local_nodes);
+  D4B_CUDA(cudaMemsetAsync(m->d_u_stage, 0, (size_t)m->local_nodes * sizeof(double), m->stream));
+  m->epi = D4bEpilogue();
+  d4b_apply_device(m, m->d_u_stage, m->d_Au_stage);
+  d4b_launch_quad_op(m, f_on_quad ? 1 : 2, in.p, jac.p, o.p);
+  d4b_vec_axpy(m, -1., m->d_Au_stage, o.p, m->local_nodes);
+  o.finish(m);
+  D4B_CUDA(cudaStreamSynchronize(m->stream));
+}
+
 extern "C" void d4b_mesh_set_mass_diag(d4b_mesh_t *m, const double *jac_quad) {
   D4B_CHECK(m, "d4b_mesh_set_mass_diag: NULL mesh");
   D4B_CUDA(cudaStreamSynchronize(m->stream));

@@ -27,7 +27,7 @@ EXPORTS = [
     "d4b_geom_compute", "d4b_mesh_create_with_geometry",
     "d4b_mesh_create", "d4b_mesh_destroy", "d4b_mesh_local_nodes", "d4b_mesh_device_bytes", "d4b_mesh_fast_elements", "d4b_mesh_flat_elements", "d4b_mesh_hp_elements", "d4b_mesh_launches_per_apply",
     "d4b_apply", "d4b_apply_stiffness", "d4b_sync", "d4b_set_stream",
-    "d4b_interp_to_quad", "d4b_apply_galerkin", "d4b_apply_mass", "d4b_mesh_set_mass_diag",
+    "d4b_interp_to_quad", "d4b_apply_galerkin", "d4b_apply_mass", "d4b_mesh_set_mass_diag", "d4b_build_rhs",
     "d4b_vec_dot", "d4b_vec_axpy", "d4b_vec_xpby", "d4b_vec_scale",
     "d4b_cg_eigs", "d4b_cheby_smooth",
     "d4b_mg_create", "d4b_mg_destroy", "d4b_mg_vcycle", "d4b_mg_solve", "d4b_mg_get_eigs", "d4b_mg_restrict",
@@ -79,6 +79,7 @@ def load_library():
     L.d4b_apply_galerkin.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     L.d4b_apply_mass.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     L.d4b_mesh_set_mass_diag.argtypes = [C.c_void_p, C.c_void_p]
+    L.d4b_build_rhs.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]
     L.d4b_set_stream.argtypes = [C.c_void_p, C.c_void_p]
     L.d4b_vec_dot.restype = C.c_double
     L.d4b_vec_dot.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]
@@ -300,6 +301,10 @@ class Mesh:
 
     def apply_mass(self, x, jac_quad, out):
         self.L.d4b_apply_mass(self.h, _ptr(x), _ptr(jac_quad), _ptr(out))
+
+    def build_rhs(self, f, jac_quad, rhs, on_quad=False):
+        """d4est_laplacian_build_rhs_with_strong_bc: rhs = M f - A(0) with the mesh's Dirichlet data"""
+        self.L.d4b_build_rhs(self.h, _ptr(f), 1 if on_quad else 0, _ptr(jac_quad), _ptr(rhs))
 
     def set_mass_diag(self, jac_quad):
         """every later apply adds V^T diag(w jac_quad) V u (None removes the term)"""

@@ -269,6 +269,14 @@ void d4b_sync(d4b_mesh_t *mesh);
 void d4b_interp_to_quad(d4b_mesh_t *mesh, const double *u, double *u_quad);
 void d4b_apply_galerkin(d4b_mesh_t *mesh, const double *in_quad, const double *jac_quad, double *out);
 void d4b_apply_mass(d4b_mesh_t *mesh, const double *x, const double *jac_quad, double *out);
+/* Right-hand side with strongly imposed boundary data, d4est_laplacian_build_rhs_with_strong_bc
+ * (src/dGMath/d4est_laplacian.c:15-140):  rhs = M f - A(0), where A(0) is the operator of `mesh`
+ * applied to u = 0 -- only the inhomogeneous Dirichlet terms of the boundary faces survive, so the
+ * mesh must have been created with the problem's boundary data in dirichlet_g_mortar_quad.
+ *   f_on_quad = 0 (INIT_FIELD_ON_LOBATTO): f at the LGL nodes, M f = V^T diag(w jac_quad) V f
+ *   f_on_quad = 1 (INIT_FIELD_ON_QUAD):    f at the quadrature points, M f = V^T (w jac_quad f)
+ * jac_quad = J_quad.  Host or device pointers.                                                   */
+void d4b_build_rhs(d4b_mesh_t *mesh, const double *f, int32_t f_on_quad, const double *jac_quad, double *rhs);
 /* Fuse a mass-type diagonal into the operator: after this call every d4b_apply (and the
  * smoother, cg_eigs and V-cycle built on it) computes
  *   Au = A u + V^T diag(w jac_quad) V u,

@@ -58,6 +58,14 @@ drv_poly_fcn (double x, double y, double z, void *user)
   return x * x + y * y + z * z;
 }
 
+/* right-hand-side density used for the build_rhs fixtures */
+static double
+drv_rhs_fcn (double x, double y, double z, void *user)
+{
+  (void) user;
+  return -6. + sin (x) * cos (2. * y) + z * z * x;
+}
+
 static void
 apply_plain (p4est_t * p4est, d4est_ghost_t * ghost, d4est_ghost_data_t * ghost_data,
              d4est_elliptic_data_t * prob_vecs, d4est_operators_t * d4est_ops,
@@ -609,39 +617,36 @@ main (int argc, char *argv[])
     P4EST_FREE (Au_b);
     d4est_b200_ctx_destroy (bctx);
   }
+  if (use_b200 && bc_poly) {
+    /* right-hand side with strong boundary data: the reference's builder against the drop-in */
+    d4est_b200_ctx_t *rctx = d4est_b200_ctx_new (flux_plain);
+    double worst = 0.;
+    for (int opt = 0; opt < 2; opt++) {
+      d4est_mesh_init_field_option_t io = opt ? INIT_FIELD_ON_QUAD : INIT_FIELD_ON_LOBATTO;
+      double *rhs_ref = P4EST_ALLOC_ZERO (double, local_nodes), *rhs_b = P4EST_ALLOC_ZERO (double, local_nodes);
+      d4est_laplacian_build_rhs_with_strong_bc (p4est, d4est_ghost, d4est_ghost_data, d4est_ops, d4est_geom, d4est_quad,
+                                                d4est_factors, &vecs, flux_plain, rhs_ref, drv_rhs_fcn, io, NULL, 0);
+      d4est_b200_build_rhs_with_strong_bc (rctx, p4est, d4est_ghost, d4est_ghost_data, d4est_ops, d4est_geom, d4est_quad,
+                                           d4est_factors, &vecs, flux_plain, rhs_b, drv_rhs_fcn, io, NULL, 0);
+      double num = 0., den = 0.;
+      for (int i = 0; i < local_nodes; i++) {
+        num += (rhs_b[i] - rhs_ref[i]) * (rhs_b[i] - rhs_ref[i]);
+        den += rhs_ref[i] * rhs_ref[i];
+      }
+      if (sqrt (num / den) > worst) worst = sqrt (num / den);
+      P4EST_FREE (rhs_ref); P4EST_FREE (rhs_b);
+    }
+    printf ("{\"b200_build_rhs_rel_l2\": %.3e}\n", worst);
+    d4est_b200_ctx_destroy (rctx);
+  }
 #else
   if (use_b200) { fprintf (stderr, "--b200 needs the device-linked build (ref_driver_b200)\n"); return 2; }
 #endif
 
   if (strcmp (out, "-")) {
     d4est_b200_flat_t *flat = d4est_b200_flatten (p4est, d4est_ghost, d4est_factors, flux_plain);
-    if (bc_poly) {
-      /* Dirichlet data at boundary quadrature points, evaluated the way
-       * d4est_laplacian_flux_sipg_dirichlet_aux does for EVAL_BNDRY_FCN_ON_LOBATTO
-       * (d4est_laplacian_flux_sipg.c:105-137): g on the face LGL nodes, then
-       * interpolated to the Gauss points */
-      flat->dirichlet_g = calloc (flat->desc.local_mortar_nodes_quad + 1, sizeof (double));
-      for (int s = 0; s < flat->desc.n_sides; s++) {
-        if (flat->desc.side_faces_p[s] != 0) continue;
-        int e = flat->desc.side_e_m[4 * s];
-        int f_m = flat->desc.side_f_m[s];
-        int deg = flat->desc.deg[e], deg_quad = flat->desc.deg_quad[e];
-        int fn = d4est_lgl_get_nodes (2, deg), fnq = d4est_lgl_get_nodes (2, deg_quad);
-        int bstride = 3 * d4est_factors->local_strides[e].boundary_quad_stride[f_m];
-        double *g_lob = P4EST_ALLOC (double, fn);
-        for (int i = 0; i < fn; i++)
-          g_lob[i] = drv_poly_fcn (d4est_factors->xyz_m_mortar_lobatto[bstride + 0 * fnq + i],
-                                   d4est_factors->xyz_m_mortar_lobatto[bstride + 1 * fnq + i],
-                                   d4est_factors->xyz_m_mortar_lobatto[bstride + 2 * fnq + i], NULL);
-        d4est_quadrature_mortar_t face_object;
-        memset (&face_object, 0, sizeof (face_object));
-        d4est_quadrature_interpolate (d4est_ops, d4est_quad, d4est_geom, &face_object,
-                                      QUAD_OBJECT_MORTAR, QUAD_INTEGRAND_UNKNOWN, g_lob, deg,
-                                      &flat->dirichlet_g[flat->desc.side_mortar_stride[s]], deg_quad);
-        P4EST_FREE (g_lob);
-      }
-      flat->desc.dirichlet_g_mortar_quad = flat->dirichlet_g;
-    }
+    if (bc_poly)
+      d4est_b200_flat_eval_dirichlet (flat, d4est_ops, d4est_geom, d4est_quad, d4est_factors, flux_plain);
     FILE *f = d4b_dump_open (out);
     dump_desc (f, &flat->desc);
     d4b_dump_put1 (f, "xyz", D4B_F64, 3 * (uint64_t) local_nodes, d4est_factors->xyz);
@@ -652,6 +657,26 @@ main (int argc, char *argv[])
     for (int e = 0; e < flat->desc.n_local; e++)
       if (flat->desc.deg_quad[e] > max_deg) max_deg = flat->desc.deg_quad[e];
     dump_tables (f, d4est_ops, max_deg);
+    if (bc_poly) {
+      /* d4est_laplacian_build_rhs_with_strong_bc of the reference with the fixture's Dirichlet data,
+       * f given on the LGL nodes and on the quadrature points (src/dGMath/d4est_laplacian.c:15-140) */
+      const int64_t lnq = d4est_factors->local_sizes.local_nodes_quad;
+      double *rhs_l = P4EST_ALLOC_ZERO (double, local_nodes), *rhs_q = P4EST_ALLOC_ZERO (double, local_nodes);
+      double *f_l = P4EST_ALLOC_ZERO (double, local_nodes), *f_q = P4EST_ALLOC_ZERO (double, lnq);
+      d4est_mesh_init_field (p4est, f_l, drv_rhs_fcn, d4est_ops, d4est_geom, d4est_factors, INIT_FIELD_ON_LOBATTO, NULL);
+      d4est_mesh_init_field (p4est, f_q, drv_rhs_fcn, d4est_ops, d4est_geom, d4est_factors, INIT_FIELD_ON_QUAD, NULL);
+      d4est_laplacian_build_rhs_with_strong_bc (p4est, d4est_ghost, d4est_ghost_data, d4est_ops, d4est_geom, d4est_quad,
+                                                d4est_factors, &vecs, flux_plain, rhs_l, drv_rhs_fcn,
+                                                INIT_FIELD_ON_LOBATTO, NULL, 0);
+      d4est_laplacian_build_rhs_with_strong_bc (p4est, d4est_ghost, d4est_ghost_data, d4est_ops, d4est_geom, d4est_quad,
+                                                d4est_factors, &vecs, flux_plain, rhs_q, drv_rhs_fcn,
+                                                INIT_FIELD_ON_QUAD, NULL, 0);
+      d4b_dump_put1 (f, "rhs_f_lobatto", D4B_F64, local_nodes, f_l);
+      d4b_dump_put1 (f, "rhs_f_quad", D4B_F64, lnq, f_q);
+      d4b_dump_put1 (f, "rhs_strong_bc_lobatto", D4B_F64, local_nodes, rhs_l);
+      d4b_dump_put1 (f, "rhs_strong_bc_quad", D4B_F64, local_nodes, rhs_q);
+      P4EST_FREE (rhs_l); P4EST_FREE (rhs_q); P4EST_FREE (f_l); P4EST_FREE (f_q);
+    }
 
     if (dump_quad) {
       /* volume quadrature operators of the reference, element by element the way the

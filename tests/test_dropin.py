@@ -47,6 +47,17 @@ def test_device_geometry_inside_the_reference(ini, args):
     assert res["b200_device_geometry_apply_rel_l2"] < 1e-12
 
 
+@pytest.mark.parametrize("ini,args", [("brick_poisson.ini", ["--uniform-deg", "2", "--bc", "poly"]),
+                                      ("sphere_p.ini", ["--amr", "1", "--bc", "poly"]),
+                                      ("sphere_hp.ini", ["--amr", "1", "--bc", "poly"])])
+def test_build_rhs_inside_the_reference(ini, args):
+    """d4est_b200_build_rhs_with_strong_bc against d4est_laplacian_build_rhs_with_strong_bc (same arguments),
+    f on the LGL nodes and on the quadrature points, Dirichlet data evaluated by the adapter"""
+    lines = run(ini, *args)
+    res = [l for l in lines if "b200_build_rhs_rel_l2" in l][0]
+    assert res["b200_build_rhs_rel_l2"] < 1e-12
+
+
 @pytest.mark.parametrize("ini,args", [("brick_poisson.ini", ["--uniform-deg", "3"]), ("sphere_hp.ini", ["--amr", "1"])])
 def test_jacobian_apply_with_mass_term_inside_the_reference(ini, args):
     """d4est_b200_set_mass_term + apply_lhs against apply_aij + the reference's fofufofvlilj loop"""
