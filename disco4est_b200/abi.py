@@ -126,6 +126,17 @@ def make_geom_desc(g):
     return d, keep
 
 
+class EstimatorDesc(C.Structure):
+    """d4b_estimator_desc_t (addresses; host or device)"""
+
+    _fields_ = [(n, C.c_void_p) for n in ("u", "residual", "jac_quad", "diam_volume", "sj_m_mortar_quad",
+                                          "hm_mortar_quad", "hp_mortar_quad", "dirichlet_g_mortar_quad")] + [
+        ("penalty_family", C.c_int32), ("penalty_prefactor", C.c_double)]
+
+
+EST_FAMILY = {"houston_maxp_minh": 0, "houston_max_p2_over_h": 1, "bi_maxp_minh": 2, "bi_max_p2_over_h": 3}
+
+
 class ChebyParams(C.Structure):
     _fields_ = [
         ("cheby_imax", C.c_int32),

@@ -353,13 +353,25 @@ d4est_b200_ctx_destroy (d4est_b200_ctx_t * ctx)
   free (ctx);
 }
 
+static void eval_dirichlet (d4est_b200_flat_t * fl, d4est_operators_t * d4est_ops, d4est_geometry_t * d4est_geom,
+                           d4est_quadrature_t * d4est_quad, d4est_mesh_data_t * d4est_factors,
+                           d4est_laplacian_dirichlet_bc_t * bc);
+
 void
 d4est_b200_flat_eval_dirichlet (d4est_b200_flat_t * fl, d4est_operators_t * d4est_ops,
                                 d4est_geometry_t * d4est_geom, d4est_quadrature_t * d4est_quad,
                                 d4est_mesh_data_t * d4est_factors, d4est_laplacian_flux_data_t * flux_data)
 {
   if (flux_data->bc_type != BC_DIRICHLET) return;
-  d4est_laplacian_dirichlet_bc_t *bc = (d4est_laplacian_dirichlet_bc_t *) flux_data->bc_data;
+  eval_dirichlet (fl, d4est_ops, d4est_geom, d4est_quad, d4est_factors,
+                  (d4est_laplacian_dirichlet_bc_t *) flux_data->bc_data);
+}
+
+static void
+eval_dirichlet (d4est_b200_flat_t * fl, d4est_operators_t * d4est_ops, d4est_geometry_t * d4est_geom,
+                d4est_quadrature_t * d4est_quad, d4est_mesh_data_t * d4est_factors,
+                d4est_laplacian_dirichlet_bc_t * bc)
+{
   free (fl->dirichlet_g);
   fl->dirichlet_g = (double *) calloc (fl->desc.local_mortar_nodes_quad + 1, sizeof (double));
   for (int s = 0; s < fl->desc.n_sides; s++) {
@@ -540,6 +552,69 @@ d4est_b200_build_rhs_with_strong_bc (d4est_b200_ctx_t * ctx, p4est_t * p4est, d4
   d4b_build_rhs (mesh, f, on_quad, d4est_factors->J_quad, rhs);
   free (f);
 }
+
+/* ------------------------------------------------------------ estimator */
+static int
+identify_estimator_family (d4est_estimator_bi_penalty_data_t * pd)
+{
+  /* values of the (gradu, u, u_dirichlet) callbacks at one point where the families differ */
+  const int dm = 2, dp = 3;
+  const double hm = 0.3, hp = 0.7, pre = 1.7;
+  const double g = pd->gradu_penalty_fcn (dm, hm, dp, hp, pre), u = pd->u_penalty_fcn (dm, hm, dp, hp, pre);
+  const double ud = pd->u_dirichlet_penalty_fcn (dm, hm, dp, hp, pre);
+  const double maxp = 3., minh = 0.3, max_hop = 0.7 / 3., max_p2h = 4. / 0.3;
+  const double fam[4][3] = {
+    {sqrt (.5 * minh / maxp), sqrt (.5 * pre * maxp * maxp / minh), sqrt (pre * maxp * maxp / minh)},
+    {sqrt (.5 * max_hop), sqrt (.5 * pre * max_p2h), sqrt (pre * max_p2h)},
+    {sqrt (minh / maxp), sqrt (pre * maxp * maxp / minh), sqrt (pre * maxp * maxp / minh)},
+    {sqrt (max_hop), sqrt (pre * max_p2h), sqrt (pre * max_p2h)}};
+  for (int f = 0; f < 4; f++)
+    if (fabs (g - fam[f][0]) < 1e-12 && fabs (u - fam[f][1]) < 1e-12 && fabs (ud - fam[f][2]) < 1e-12) return f;
+  D4EST_ABORT ("d4est_b200: unknown combination of estimator penalty callbacks");
+  return -1;
+}
+
+#ifndef D4EST_B200_ADAPTER_NO_DEVICE
+double *
+d4est_b200_estimator_bi_compute (d4est_b200_ctx_t * ctx, p4est_t * p4est,
+                                 d4est_elliptic_data_t * d4est_elliptic_data, d4est_elliptic_eqns_t * fcns,
+                                 d4est_estimator_bi_penalty_data_t penalty_data, d4est_xyz_fcn_t u_bndry_fcn,
+                                 void *bndry_ctx, d4est_ghost_t * d4est_ghost, d4est_ghost_data_t * d4est_ghost_data,
+                                 d4est_operators_t * d4est_ops, d4est_geometry_t * d4est_geom_for_residual,
+                                 d4est_mesh_data_t * d4est_factors_for_residual,
+                                 d4est_geometry_t * d4est_geom_for_integrals,
+                                 d4est_mesh_data_t * d4est_factors_for_integrals, d4est_quadrature_t * d4est_quad,
+                                 int which_field, double *estimator_vtk, double *estimator_vtk_per_face)
+{
+  (void) which_field;
+  const int nl = p4est->local_num_quadrants;
+  d4est_elliptic_eqns_build_residual (p4est, d4est_ghost, d4est_ghost_data, fcns, d4est_elliptic_data, d4est_ops,
+                                      d4est_geom_for_residual, d4est_quad, d4est_factors_for_residual);
+  d4b_mesh_t *mesh = d4est_b200_get_mesh (ctx, p4est, d4est_ghost, d4est_factors_for_integrals);
+  /* boundary data the way d4est_estimator_bi_dirichlet evaluates it: on the face LGL nodes, then interpolated */
+  d4est_b200_flat_t *fl = d4est_b200_flatten (p4est, d4est_ghost, d4est_factors_for_integrals, ctx->flux_data);
+  d4est_laplacian_dirichlet_bc_t bc;
+  bc.dirichlet_fcn = u_bndry_fcn; bc.user = bndry_ctx; bc.eval_method = EVAL_BNDRY_FCN_ON_LOBATTO;
+  eval_dirichlet (fl, d4est_ops, d4est_geom_for_integrals, d4est_quad, d4est_factors_for_integrals, &bc);
+  d4b_estimator_desc_t ed;
+  memset (&ed, 0, sizeof (ed));
+  ed.u = d4est_elliptic_data->u; ed.residual = d4est_elliptic_data->Au;
+  ed.jac_quad = d4est_factors_for_integrals->J_quad;
+  ed.diam_volume = d4est_factors_for_integrals->diam_volume;
+  ed.sj_m_mortar_quad = d4est_factors_for_integrals->sj_m_mortar_quad;
+  ed.hm_mortar_quad = d4est_factors_for_integrals->hm_mortar_quad;
+  ed.hp_mortar_quad = d4est_factors_for_integrals->hp_mortar_quad;
+  ed.dirichlet_g_mortar_quad = fl->dirichlet_g;
+  ed.penalty_family = identify_estimator_family (&penalty_data);
+  ed.penalty_prefactor = penalty_data.penalty_prefactor;
+  double *estimator = P4EST_ALLOC (double, nl);
+  d4b_estimator_bi (mesh, &ed, estimator, estimator_vtk);
+  if (estimator_vtk_per_face)
+    for (int i = 0; i < 18 * nl; i++) estimator_vtk_per_face[i] = 0.;
+  d4est_b200_flat_destroy (fl);
+  return estimator;
+}
+#endif
 
 /* ------------------------------------------------------------ mass term */
 void

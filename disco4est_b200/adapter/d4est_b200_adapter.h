@@ -25,6 +25,7 @@
 #include <d4est_geometry.h>
 #include <d4est_geometry_brick.h>
 #include <d4est_geometry_cubed_sphere.h>
+#include <d4est_estimator_bi.h>
 #include "d4est_b200.h"
 
 /* Owns the arrays a d4b_mesh_desc_t points to (those that are not aliases of
@@ -98,6 +99,25 @@ void d4est_b200_build_rhs_with_strong_bc (d4est_b200_ctx_t * ctx_for_rhs, p4est_
                                           double *rhs, d4est_xyz_fcn_t problem_rhs_fcn,
                                           d4est_mesh_init_field_option_t init_option, void *fcn_ctx,
                                           int which_field);
+
+/* drop-in for d4est_estimator_bi_compute (src/Estimators/d4est_estimator_bi.c:349-602), same arguments
+ * behind the context: runs the problem's build_residual callback (fcns->build_residual, which may
+ * itself be device-backed), then eta^2 of every local element on the device (d4b_estimator_bi).
+ * The three prefactor callbacks of penalty_data are identified by probing (they are static inline
+ * in d4est_estimator_bi.h); an unknown combination aborts.  Returns a P4EST_ALLOC'd array like
+ * the reference; estimator_vtk (may be NULL) receives the four parts, estimator_vtk_per_face is
+ * not filled (zeros).                                                                          */
+double *d4est_b200_estimator_bi_compute (d4est_b200_ctx_t * ctx, p4est_t * p4est,
+                                         d4est_elliptic_data_t * d4est_elliptic_data, d4est_elliptic_eqns_t * fcns,
+                                         d4est_estimator_bi_penalty_data_t penalty_data, d4est_xyz_fcn_t u_bndry_fcn,
+                                         void *bndry_ctx, d4est_ghost_t * d4est_ghost,
+                                         d4est_ghost_data_t * d4est_ghost_data, d4est_operators_t * d4est_ops,
+                                         d4est_geometry_t * d4est_geom_for_residual,
+                                         d4est_mesh_data_t * d4est_factors_for_residual,
+                                         d4est_geometry_t * d4est_geom_for_integrals,
+                                         d4est_mesh_data_t * d4est_factors_for_integrals,
+                                         d4est_quadrature_t * d4est_quad, int which_field, double *estimator_vtk,
+                                         double *estimator_vtk_per_face);
 
 /* Opt in to geometric factors generated on the device: from now on a mesh that is uploaded
  * for this context takes J, rst_xyz and all mortar quantities from d4b_geom_compute (the map of

@@ -2,6 +2,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
+#include <algorithm>
 #include "d4b_internal.h"
 
 namespace {
@@ -168,6 +169,36 @@ extern "C" void d4b_build_rhs(d4b_mesh_t *m, const double *f, int32_t f_on_quad,
   d4b_vec_axpy(m, -1., m->d_Au_stage, o.p, m->local_nodes);
   o.finish(m);
   D4B_CUDA(cudaStreamSynchronize(m->stream));
+}
+
+extern "C" void d4b_estimator_bi(d4b_mesh_t *m, const d4b_estimator_desc_t *d, double *eta2, double *terms) {
+  D4B_CHECK(m && d && eta2, "d4b_estimator_bi: NULL argument");
+  D4B_CHECK(d->u && d->residual && d->jac_quad && d->diam_volume && d->sj_m_mortar_quad && d->hm_mortar_quad &&
+            d->hp_mortar_quad, "d4b_estimator_bi: missing input array");
+  D4B_CHECK(d->penalty_family >= D4B_EST_HOUSTON_MAXP_MINH && d->penalty_family <= D4B_EST_BI_MAX_P2_OVER_H,
+            "d4b_estimator_bi: unknown penalty family %d", d->penalty_family);
+  DevIn u(m, d->u, m->local_nodes), r(m, d->residual, m->local_nodes), jac(m, d->jac_quad, m->local_nodes_quad);
+  DevIn diam(m, d->diam_volume, m->n_local), sj(m, d->sj_m_mortar_quad, m->mortar_nodes);
+  DevIn hm(m, d->hm_mortar_quad, m->mortar_nodes), hp(m, d->hp_mortar_quad, m->mortar_nodes);
+  DevIn g(m, d->dirichlet_g_mortar_quad, m->mortar_nodes);
+  DevOut o(m, eta2, m->n_local);
+  double *tp = nullptr, *ttmp = nullptr;
+  if (terms) {
+    if (is_device_ptr(terms)) tp = terms;
+    else { D4B_CUDA(cudaMalloc(&ttmp, (size_t)4 * std::max(m->n_local, 1) * sizeof(double))); tp = ttmp; }
+  }
+  if (m->mpisize > 1) {   // ghost values of u (d4est_ghost_data_exchange, d4est_estimator_bi.c:454)
+    d4b_comm_exchange_begin(m, u.p);
+    d4b_comm_exchange_wait(m);
+  }
+  d4b_launch_estimator(m, u.p, r.p, jac.p, diam.p, sj.p, hm.p, hp.p, g.p, d->penalty_family, d->penalty_prefactor,
+                       o.p, tp);
+  o.finish(m);
+  if (ttmp) {
+    D4B_CUDA(cudaMemcpyAsync(terms, ttmp, (size_t)4 * m->n_local * sizeof(double), cudaMemcpyDeviceToHost, m->stream));
+  }
+  D4B_CUDA(cudaStreamSynchronize(m->stream));
+  if (ttmp) cudaFree(ttmp);
 }
 
 extern "C" void d4b_mesh_set_mass_diag(d4b_mesh_t *m, const double *jac_quad) {

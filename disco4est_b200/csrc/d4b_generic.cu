@@ -333,6 +333,149 @@ __global__ void __launch_bounds__(32 * kMaxWarps) generic_apply_kernel(GenericAr
   for (int i = lane; i < n3; i += 32) oe[i] = s_out[i];
 }
 
+// ---- residual-based error estimator, d4est_estimator_bi_compute (src/Estimators/d4est_estimator_bi.c:349-602)
+// One warp per element:  eta2_e = h_e^2 / p_e^2 * r_e^T M_e r_e
+//   + sum over the mortars of the element's six flux sides of  w sj [ (c1 n.(grad u_m - grad u_p))^2 + (c2 (u_m - u_p))^2 ]
+//   (boundary: w sj (c_d (u_m - g))^2), c1 / c2 / c_d = the Houston et al. or "bi" prefactors of
+// d4est_estimator_bi.h:25-197.  n.grad u on either side comes from the folded mortar planes:
+// sj n.grad u_m = sum_l A_m[l] du_m/d(rst_l) (and the same with A_p for the (+) side).
+struct EstArgs {
+  GenericArgs g;
+  const double *r, *jac, *diam, *sj, *hm, *hp, *gbc;
+  int family;
+  double prefactor;
+  double *eta2, *terms;   // [n_local], [4*n_local] or NULL
+};
+
+__device__ __forceinline__ void est_prefactors(int family, int deg_m, double h_m, int deg_p, double h_p, double pre,
+                                               double &c_gradu, double &c_u, double &c_dir) {
+  const double max_p = (double)(deg_m > deg_p ? deg_m : deg_p), min_h = h_m < h_p ? h_m : h_p;
+  const double hop_m = h_m / (double)deg_m, hop_p = h_p / (double)deg_p, max_hop = hop_m > hop_p ? hop_m : hop_p;
+  const double p2h_m = (double)deg_m * (double)deg_m / h_m, p2h_p = (double)deg_p * (double)deg_p / h_p;
+  const double max_p2h = p2h_m > p2h_p ? p2h_m : p2h_p;
+  switch (family) {
+    case D4B_EST_HOUSTON_MAXP_MINH:
+      c_gradu = sqrt(.5 * min_h / max_p); c_u = sqrt(.5 * pre * max_p * max_p / min_h);
+      c_dir = sqrt(pre * max_p * max_p / min_h); break;
+    case D4B_EST_HOUSTON_MAX_P2_OVER_H:
+      c_gradu = sqrt(.5 * max_hop); c_u = sqrt(.5 * pre * max_p2h); c_dir = sqrt(pre * max_p2h); break;
+    case D4B_EST_BI_MAXP_MINH:
+      c_gradu = sqrt(min_h / max_p); c_u = sqrt(pre * max_p * max_p / min_h); c_dir = c_u; break;
+    default:   // D4B_EST_BI_MAX_P2_OVER_H
+      c_gradu = sqrt(max_hop); c_u = sqrt(pre * max_p2h); c_dir = c_u; break;
+  }
+}
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+__global__ void __launch_bounds__(32 * kMaxWarps) estimator_kernel(EstArgs ea) {
+  extern __shared__ double smem_all[];
+  const GenericArgs &a = ea.g;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int e = blockIdx.x * (blockDim.x >> 5) + warp;
+  if (e >= a.n_elem) return;
+  double *smem = smem_all + (size_t)warp * a.smem_doubles;
+  const int p = a.deg[e], q = a.deg_quad[e];
+  const int N = p + 1, Nq = q + 1, n3 = N * N * N, q3 = Nq * Nq * Nq;
+  const int mN = a.maxN, mQ = a.maxNq;
+  double *s_u = smem, *s_out = s_u + mN * mN * mN, *s_a = s_out + mN * mN * mN;
+  double *s_t1 = s_a + mN * mN * mN, *s_t2 = s_t1 + mN * mN * mQ, *s_g = s_t2 + mN * mQ * mQ;
+  const double *E = tabE(a, p, q, 0);
+  // ---- residual term: h^2 / p^2 * sum w J (V r)^2
+  for (int i = lane; i < n3; i += 32) s_u[i] = ea.r[a.nodal_stride[e] + i];
+  __syncwarp();
+  sweep3<true>(s_t1, s_u, E, N, 1, Nq, N, 0, N, N, N);
+  sweep3<true>(s_t2, s_t1, E, N, 1, Nq, N, 1, Nq, N, N);
+  sweep3<true>(s_g, s_t2, E, N, 1, Nq, N, 2, Nq, Nq, N);
+  double res = 0.;
+  {
+    const double *w = a.tabdata + a.tab->w_off[q - 1];
+    const double *J = ea.jac + a.quad_stride[e];
+    for (int k = lane; k < q3; k += 32)
+      res += w[k % Nq] * w[(k / Nq) % Nq] * w[k / (Nq * Nq)] * J[k] * s_g[k] * s_g[k];
+  }
+  res = warp_sum(res) * ea.diam[e] * ea.diam[e] / ((double)p * (double)p);
+  __syncwarp();
+  // ---- face terms
+  for (int i = lane; i < n3; i += 32) s_u[i] = a.u[a.nodal_stride[e] + i];
+  __syncwarp();
+  double je1 = 0., je2 = 0., jeb = 0.;
+  double *s_m = s_g, *s_p = s_m + 4 * mQ * mQ, *s_tr = s_t1, *s_2d = s_t2;
+  for (int f = 0; f < 6; ++f) {
+    const int s = a.elem_side[6 * e + f], my = a.elem_sub[6 * e + f];
+    const int faces_m = a.side_faces_m[s], faces_p = a.side_faces_p[s];
+    const int f_p = a.side_f_p[s], perm = a.side_perm[s];
+    const int M = faces_m > faces_p ? faces_m : faces_p;
+    const int32_t *e_p = a.side_e_p + 4 * s, *sub = a.side_sub_order + 4 * s, *e_m = a.side_e_m + 4 * s;
+    const int64_t S = a.side_mortar_stride[s];
+    const int m_big = (faces_m == 1 && M == 4), p_big = (faces_p == 1 && M == 4);
+    // the folded planes already carry the 1/2 of a hanging side (the reference halves dudx there,
+    // d4est_laplacian_flux.c:907-915): sum_l A[l] du/d(rst_l) = sj n.grad u on either side
+    int off = 0;
+    const int i_begin = (faces_m == 4) ? my : 0, i_end = (faces_m == 4) ? my + 1 : M;
+    for (int i = 0; i < M; ++i) {
+      const int32_t em_i = e_m[(faces_m == 4) ? i : 0];
+      int dq = (em_i >= 0) ? a.deg_quad[em_i] : a.ghost_deg_quad[-em_i - 1];
+      int32_t ep_i = 0;
+      if (faces_p) {
+        ep_i = e_p[(faces_p == 4) ? sub[i] : 0];
+        const int qp = (ep_i >= 0) ? a.deg_quad[ep_i] : a.ghost_deg_quad[-ep_i - 1];
+        if (qp > dq) dq = qp;
+      }
+      const int nq = dq + 1, nq2 = nq * nq;
+      if (i >= i_begin && i < i_end) {
+        const int hx = m_big ? 1 + (i & 1) : 0, hy = m_big ? 1 + (i >> 1) : 0;
+        traces_on_mortar(a, s_u, p, f, dq, hx, hy, s_m, mQ * mQ, s_tr, s_2d);
+        const double *mo = a.mortar + S + off;
+        const int64_t MP = a.mortar_nodes, ks0 = S + off;
+        const double *w = a.tabdata + a.tab->w_off[dq - 1];
+        int deg_p = p;
+        if (faces_p) {
+          const int j = (M == 4) ? sub[i] : 0;
+          const int hxp = p_big ? 1 + (j & 1) : 0, hyp = p_big ? 1 + (j >> 1) : 0;
+          deg_p = (ep_i >= 0) ? a.deg[ep_i] : a.ghost_deg[-ep_i - 1];
+          const double *vp = (ep_i >= 0) ? a.u + a.nodal_stride[ep_i] : a.ughost + a.ghost_nodal_stride[-ep_i - 1];
+          traces_on_mortar(a, vp, deg_p, f_p, dq, hxp, hyp, s_p, mQ * mQ, s_tr, s_2d);
+        }
+        for (int k = lane; k < nq2; k += 32) {
+          const double sj = ea.sj[ks0 + k], wk = w[k % nq] * w[k / nq];
+          const double h_m = ea.hm[ks0 + k];
+          double c1, c2, cd;
+          if (faces_p) {
+            est_prefactors(ea.family, p, h_m, deg_p, ea.hp[ks0 + k], ea.prefactor, c1, c2, cd);
+            const int kp = perm_index(nq, perm, k % nq, k / nq);
+            const double gm = (mo[k] * s_m[mQ * mQ + k] + mo[MP + k] * s_m[2 * mQ * mQ + k] +
+                               mo[2 * MP + k] * s_m[3 * mQ * mQ + k]) / sj;
+            const double gp = (mo[3 * MP + k] * s_p[mQ * mQ + kp] + mo[4 * MP + k] * s_p[2 * mQ * mQ + kp] +
+                               mo[5 * MP + k] * s_p[3 * mQ * mQ + kp]) / sj;
+            const double du = s_m[k] - s_p[kp];
+            je1 += wk * sj * c1 * c1 * (gm - gp) * (gm - gp);
+            je2 += wk * sj * c2 * c2 * du * du;
+          } else {
+            est_prefactors(ea.family, p, h_m, p, h_m, ea.prefactor, c1, c2, cd);
+            const double du = s_m[k] - (ea.gbc ? ea.gbc[ks0 + k] : 0.);
+            jeb += wk * sj * cd * cd * du * du;
+          }
+        }
+        __syncwarp();
+      }
+      off += nq2;
+    }
+  }
+  je1 = warp_sum(je1); je2 = warp_sum(je2); jeb = warp_sum(jeb);
+  if (lane == 0) {
+    ea.eta2[e] = res + je1 + je2 + jeb;
+    if (ea.terms) {
+      ea.terms[e] = res; ea.terms[a.n_elem + e] = je1;
+      ea.terms[2 * (int64_t)a.n_elem + e] = je2; ea.terms[3 * (int64_t)a.n_elem + e] = jeb;
+    }
+  }
+}
+
 // ---- volume quadrature operators, one CTA per element, any (deg, deg_quad) ----------
 //   mode 0: out_quad = V in                      d4est_quadrature_interpolate            d4est_quadrature.c:966-1016
 //   mode 1: out = V^T (w jac in_quad)            d4est_quadrature_apply_galerkin_integral :142-213
@@ -439,6 +582,43 @@ void d4b_launch_generic(d4b_mesh *m, const double *d_u, double *d_Au, int stiffn
   a.smem_doubles = per_warp / (int)sizeof(double);
   d4b_generic_configure(per_warp * warps);
   generic_apply_kernel<<<(n_elem + warps - 1) / warps, 32 * warps, (size_t)per_warp * warps, m->stream>>>(a);
+  D4B_CUDA(cudaGetLastError());
+}
+
+void d4b_launch_estimator(d4b_mesh *m, const double *d_u, const double *d_r, const double *d_jac, const double *d_diam,
+                          const double *d_sj, const double *d_hm, const double *d_hp, const double *d_g, int family,
+                          double prefactor, double *d_eta2, double *d_terms) {
+  if (m->n_local == 0) return;
+  EstArgs ea;
+  GenericArgs &a = ea.g;
+  a.tab = m->d_tab; a.tabdata = m->d_tabdata;
+  a.deg = m->d_deg; a.deg_quad = m->d_deg_quad;
+  a.nodal_stride = m->d_nodal_stride; a.quad_stride = m->d_quad_stride;
+  a.ghost_deg = m->d_ghost_deg; a.ghost_deg_quad = m->d_ghost_deg_quad;
+  a.ghost_nodal_stride = m->d_ghost_nodal_stride;
+  a.G = m->d_G; a.W = nullptr; a.local_nodes_quad = m->local_nodes_quad;
+  a.elem_side = m->d_elem_side; a.elem_sub = m->d_elem_sub;
+  a.side_faces_m = m->d_side_faces_m; a.side_faces_p = m->d_side_faces_p;
+  a.side_f_m = m->d_side_f_m; a.side_f_p = m->d_side_f_p;
+  a.side_e_m = m->d_side_e_m; a.side_e_p = m->d_side_e_p;
+  a.side_perm = m->d_side_perm; a.side_sub_order = m->d_side_sub_order;
+  a.side_mortar_stride = m->d_side_mortar_stride;
+  a.mortar = m->d_mortar; a.mortar_nodes = m->mortar_nodes;
+  a.u = d_u; a.ughost = m->d_ughost; a.Au = nullptr;
+  a.elem_list = nullptr; a.n_elem = m->n_local; a.stiffness_only = 0;
+  a.maxN = m->max_deg + 1; a.maxNq = m->max_deg_quad + 1;
+  const int per_warp = m->generic_smem;
+  int warps = (200 * 1024) / per_warp;
+  warps = warps < 1 ? 1 : warps > kMaxWarps ? kMaxWarps : warps;
+  a.smem_doubles = per_warp / (int)sizeof(double);
+  static int configured = 48 * 1024;
+  if (per_warp * warps > configured) {
+    D4B_CUDA(cudaFuncSetAttribute(estimator_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, per_warp * warps));
+    configured = per_warp * warps;
+  }
+  ea.r = d_r; ea.jac = d_jac; ea.diam = d_diam; ea.sj = d_sj; ea.hm = d_hm; ea.hp = d_hp; ea.gbc = d_g;
+  ea.family = family; ea.prefactor = prefactor; ea.eta2 = d_eta2; ea.terms = d_terms;
+  estimator_kernel<<<(m->n_local + warps - 1) / warps, 32 * warps, (size_t)per_warp * warps, m->stream>>>(ea);
   D4B_CUDA(cudaGetLastError());
 }
 

@@ -166,6 +166,10 @@ void d4b_launch_generic(d4b_mesh *m, const double *d_u, double *d_Au, int stiffn
 // volume quadrature operators on device pointers (d4b_generic.cu): mode 0 interpolate,
 // 1 Galerkin integral, 2 mass matrix, 3 out_quad = w jac
 void d4b_launch_quad_op(d4b_mesh *m, int mode, const double *d_in, const double *d_jac, double *d_out);
+// d4est_estimator_bi_compute on device pointers (d4b_generic.cu); ghost values of u must be in m->d_ughost
+void d4b_launch_estimator(d4b_mesh *m, const double *d_u, const double *d_r, const double *d_jac, const double *d_diam,
+                          const double *d_sj, const double *d_hm, const double *d_hp, const double *d_g, int family,
+                          double prefactor, double *d_eta2, double *d_terms);
 // the whole apply on device pointers (halo exchange, fast kernels with m->epi, generic kernel)
 void d4b_apply_device(d4b_mesh *m, const double *d_u, double *d_Au);
 void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *desc, const std::vector<double> &mortar,

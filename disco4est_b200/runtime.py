@@ -14,7 +14,7 @@ import os
 
 import numpy as np
 
-from .abi import GEOM_ARRAY_FIELDS, ChebyParams, GeomArrays, GeomDesc, MeshDesc, MgDesc, make_desc, make_geom_desc
+from .abi import EST_FAMILY, GEOM_ARRAY_FIELDS, ChebyParams, EstimatorDesc, GeomArrays, GeomDesc, MeshDesc, MgDesc, make_desc, make_geom_desc
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 # D4B_LIBRARY_PATH lets profiling scripts A/B differently compiled builds of the same library
@@ -27,7 +27,7 @@ EXPORTS = [
     "d4b_geom_compute", "d4b_mesh_create_with_geometry",
     "d4b_mesh_create", "d4b_mesh_destroy", "d4b_mesh_local_nodes", "d4b_mesh_device_bytes", "d4b_mesh_fast_elements", "d4b_mesh_flat_elements", "d4b_mesh_hp_elements", "d4b_mesh_launches_per_apply",
     "d4b_apply", "d4b_apply_stiffness", "d4b_sync", "d4b_set_stream",
-    "d4b_interp_to_quad", "d4b_apply_galerkin", "d4b_apply_mass", "d4b_mesh_set_mass_diag", "d4b_build_rhs",
+    "d4b_interp_to_quad", "d4b_apply_galerkin", "d4b_apply_mass", "d4b_mesh_set_mass_diag", "d4b_build_rhs", "d4b_estimator_bi",
     "d4b_vec_dot", "d4b_vec_axpy", "d4b_vec_xpby", "d4b_vec_scale",
     "d4b_cg_eigs", "d4b_cheby_smooth",
     "d4b_mg_create", "d4b_mg_destroy", "d4b_mg_vcycle", "d4b_mg_solve", "d4b_mg_get_eigs", "d4b_mg_restrict",
@@ -79,6 +79,7 @@ def load_library():
     L.d4b_apply_galerkin.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     L.d4b_apply_mass.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     L.d4b_mesh_set_mass_diag.argtypes = [C.c_void_p, C.c_void_p]
+    L.d4b_estimator_bi.argtypes = [C.c_void_p, C.POINTER(EstimatorDesc), C.c_void_p, C.c_void_p]
     L.d4b_build_rhs.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]
     L.d4b_set_stream.argtypes = [C.c_void_p, C.c_void_p]
     L.d4b_vec_dot.restype = C.c_double
@@ -305,6 +306,19 @@ class Mesh:
     def build_rhs(self, f, jac_quad, rhs, on_quad=False):
         """d4est_laplacian_build_rhs_with_strong_bc: rhs = M f - A(0) with the mesh's Dirichlet data"""
         self.L.d4b_build_rhs(self.h, _ptr(f), 1 if on_quad else 0, _ptr(jac_quad), _ptr(rhs))
+
+    def estimator_bi(self, u, residual, jac_quad, diam_volume, sj, hm, hp, prefactor, family="houston_maxp_minh",
+                     dirichlet_g=None, eta2=None, terms=None):
+        """d4est_estimator_bi_compute: eta^2 per local element (and, in `terms`, its four parts [4][n_local])"""
+        d = EstimatorDesc()
+        d.u, d.residual, d.jac_quad, d.diam_volume = _ptr(u), _ptr(residual), _ptr(jac_quad), _ptr(diam_volume)
+        d.sj_m_mortar_quad, d.hm_mortar_quad, d.hp_mortar_quad = _ptr(sj), _ptr(hm), _ptr(hp)
+        d.dirichlet_g_mortar_quad = None if dirichlet_g is None else _ptr(dirichlet_g)
+        d.penalty_family, d.penalty_prefactor = EST_FAMILY[family], float(prefactor)
+        if eta2 is None:
+            eta2 = np.zeros(int(self.desc.n_local))
+        self.L.d4b_estimator_bi(self.h, C.byref(d), _ptr(eta2), None if terms is None else _ptr(terms))
+        return eta2
 
     def set_mass_diag(self, jac_quad):
         """every later apply adds V^T diag(w jac_quad) V u (None removes the term)"""

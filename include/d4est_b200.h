@@ -277,6 +277,34 @@ void d4b_apply_mass(d4b_mesh_t *mesh, const double *x, const double *jac_quad, d
  *   f_on_quad = 1 (INIT_FIELD_ON_QUAD):    f at the quadrature points, M f = V^T (w jac_quad f)
  * jac_quad = J_quad.  Host or device pointers.                                                   */
 void d4b_build_rhs(d4b_mesh_t *mesh, const double *f, int32_t f_on_quad, const double *jac_quad, double *rhs);
+/* Residual-based a-posteriori error estimator, d4est_estimator_bi_compute
+ * (src/Estimators/d4est_estimator_bi.c:349-602): for every local element
+ *   eta2[e] = h_e^2 / p_e^2 |r|^2_{L2(e)}
+ *           + sum over its mortars of  int sj [ (c1 n.(grad u_m - grad u_p))^2 + (c2 (u_m - u_p))^2 ]
+ *           + on boundary faces        int sj (c_d (u_m - g))^2
+ * with the penalty prefactors of d4est_estimator_bi.h:25-197 (family below).  `residual` is what the
+ * problem's build_residual callback left in Au (nodal), diam_volume the reference's per-element size
+ * (d4est_mesh_data_t.diam_volume), sj / hm / hp its mortar arrays (the mesh does not keep them),
+ * dirichlet_g the boundary data at the boundary quadrature points (NULL = zero).  terms (may be
+ * NULL) receives the four parts like estimator_vtk: [4][n_local] = residual, Je1, Je2, Je2 boundary.
+ * All pointers host or device.                                                                  */
+typedef enum {
+  D4B_EST_HOUSTON_MAXP_MINH = 0,       /* houston_{gradu,u,u_dirichlet}_prefactor_maxp_minh   */
+  D4B_EST_HOUSTON_MAX_P2_OVER_H = 1,   /* houston_gradu_prefactor_max_h_over_p, houston_u[_dirichlet]_prefactor_max_p2_over_h */
+  D4B_EST_BI_MAXP_MINH = 2,            /* bi_gradu_prefactor_maxp_minh, bi_u_prefactor_conforming_maxp_minh */
+  D4B_EST_BI_MAX_P2_OVER_H = 3         /* bi_gradu_prefactor_max_h_over_p, bi_u_prefactor_conforming_max_p2_over_h */
+} d4b_estimator_penalty_t;
+typedef struct d4b_estimator_desc
+{
+  const double *u, *residual;                 /* [local_nodes] */
+  const double *jac_quad;                     /* [local_nodes_quad] J_quad */
+  const double *diam_volume;                  /* [n_local] */
+  const double *sj_m_mortar_quad, *hm_mortar_quad, *hp_mortar_quad;   /* [local_mortar_nodes_quad] */
+  const double *dirichlet_g_mortar_quad;      /* [local_mortar_nodes_quad] or NULL */
+  int32_t penalty_family;                     /* d4b_estimator_penalty_t */
+  double  penalty_prefactor;
+} d4b_estimator_desc_t;
+void d4b_estimator_bi(d4b_mesh_t *mesh, const d4b_estimator_desc_t *desc, double *eta2, double *terms);
 /* Fuse a mass-type diagonal into the operator: after this call every d4b_apply (and the
  * smoother, cg_eigs and V-cycle built on it) computes
  *   Au = A u + V^T diag(w jac_quad) V u,

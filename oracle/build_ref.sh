@@ -80,6 +80,7 @@ Solver/d4est_solver_multigrid_mesh_analyzer.c Solver/d4est_solver_multigrid_smoo
 Solver/d4est_solver_multigrid_smoother_none.c Solver/d4est_solver_multigrid_bottom_solver_reuse_smoother.c
 Solver/d4est_solver_cg_eigs.c Solver/d4est_krylov_pc_multigrid.c
 Solver/d4est_solver_fcg_improved.c Solver/d4est_solver_cg.c
+Estimators/d4est_estimator_bi.c
 "
 for s in $D8SRCS; do
   emit $REF/src/$s obj/d8/$(basename $s .c).o "$DFLAGS"

@@ -30,6 +30,7 @@
 #include <d4est_krylov_pc_multigrid.h>
 #include <d4est_solver_fcg_improved.h>
 #include <d4est_solver_cg.h>
+#include <d4est_estimator_bi.h>
 #include <d4est_util.h>
 #include <zlog.h>
 #include <time.h>
@@ -56,6 +57,18 @@ static double
 drv_poly_fcn (double x, double y, double z, void *user)
 {
   return x * x + y * y + z * z;
+}
+
+/* residual callback for the estimator fixture: Au <- rhs - A u, like poisson_build_residual */
+static void
+drv_build_residual (p4est_t * p4est, d4est_ghost_t * ghost, d4est_ghost_data_t * ghost_data,
+                    d4est_elliptic_data_t * prob_vecs, d4est_operators_t * d4est_ops,
+                    d4est_geometry_t * d4est_geom, d4est_quadrature_t * d4est_quad,
+                    d4est_mesh_data_t * d4est_factors, void *user)
+{
+  d4est_laplacian_apply_aij (p4est, ghost, ghost_data, prob_vecs, (d4est_laplacian_flux_data_t *) user, d4est_ops,
+                             d4est_geom, d4est_quad, d4est_factors, 0);
+  d4est_linalg_vec_xpby (prob_vecs->rhs, -1., prob_vecs->Au, prob_vecs->local_nodes);
 }
 
 /* right-hand-side density used for the build_rhs fixtures */
@@ -638,6 +651,44 @@ main (int argc, char *argv[])
     }
     printf ("{\"b200_build_rhs_rel_l2\": %.3e}\n", worst);
     d4est_b200_ctx_destroy (rctx);
+    {
+      /* estimator: the reference's d4est_estimator_bi_compute against the drop-in with the same arguments */
+      const int nl = p4est->local_num_quadrants;
+      double *rhs_e = P4EST_ALLOC_ZERO (double, local_nodes), *res = P4EST_ALLOC_ZERO (double, local_nodes);
+      d4est_laplacian_build_rhs_with_strong_bc (p4est, d4est_ghost, d4est_ghost_data, d4est_ops, d4est_geom, d4est_quad,
+                                                d4est_factors, &vecs, flux_plain, rhs_e, drv_rhs_fcn,
+                                                INIT_FIELD_ON_LOBATTO, NULL, 0);
+      d4est_elliptic_data_t ev = vecs;
+      ev.u = u; ev.Au = res; ev.rhs = rhs_e;
+      d4est_elliptic_eqns_t fcns_res = {.build_residual = drv_build_residual,.apply_lhs = apply_plain,.user = flux_plain };
+      d4est_estimator_bi_penalty_data_t pd;
+      memset (&pd, 0, sizeof (pd));
+      pd.u_penalty_fcn = houston_u_prefactor_maxp_minh;
+      pd.gradu_penalty_fcn = houston_gradu_prefactor_maxp_minh;
+      pd.u_dirichlet_penalty_fcn = houston_u_dirichlet_prefactor_maxp_minh;
+      pd.penalty_prefactor = ((d4est_laplacian_flux_sipg_params_t *) flux_plain->flux_data)->sipg_penalty_prefactor;
+      double *vtk = P4EST_ALLOC_ZERO (double, 4 * nl), *vtkf = P4EST_ALLOC_ZERO (double, 18 * nl);
+      double te = wall ();
+      double *eta_ref = d4est_estimator_bi_compute (p4est, &ev, &fcns_res, pd, drv_poly_fcn, NULL, d4est_ghost,
+                                                    d4est_ghost_data, d4est_ops, d4est_geom, d4est_factors, d4est_geom,
+                                                    d4est_factors, d4est_quad, 0, vtk, vtkf);
+      double t_ref = wall () - te;
+      d4est_b200_ctx_t *ectx = d4est_b200_ctx_new (flux_plain);
+      te = wall ();
+      double *eta_b = d4est_b200_estimator_bi_compute (ectx, p4est, &ev, &fcns_res, pd, drv_poly_fcn, NULL, d4est_ghost,
+                                                       d4est_ghost_data, d4est_ops, d4est_geom, d4est_factors, d4est_geom,
+                                                       d4est_factors, d4est_quad, 0, vtk, vtkf);
+      double t_b = wall () - te;
+      double w = 0., big = 0.;
+      for (int i = 0; i < nl; i++) {
+        if (fabs (eta_b[i] - eta_ref[i]) > w) w = fabs (eta_b[i] - eta_ref[i]);
+        if (fabs (eta_ref[i]) > big) big = fabs (eta_ref[i]);
+      }
+      printf ("{\"b200_estimator_rel_max\": %.3e, \"t_estimator_reference_s\": %.4f, \"t_estimator_b200_incl_upload_s\": %.4f}\n",
+              w / big, t_ref, t_b);
+      P4EST_FREE (eta_ref); P4EST_FREE (eta_b); P4EST_FREE (vtk); P4EST_FREE (vtkf); P4EST_FREE (rhs_e); P4EST_FREE (res);
+      d4est_b200_ctx_destroy (ectx);
+    }
   }
 #else
   if (use_b200) { fprintf (stderr, "--b200 needs the device-linked build (ref_driver_b200)\n"); return 2; }
@@ -675,6 +726,35 @@ main (int argc, char *argv[])
       d4b_dump_put1 (f, "rhs_f_quad", D4B_F64, lnq, f_q);
       d4b_dump_put1 (f, "rhs_strong_bc_lobatto", D4B_F64, local_nodes, rhs_l);
       d4b_dump_put1 (f, "rhs_strong_bc_quad", D4B_F64, local_nodes, rhs_q);
+      {
+        /* d4est_estimator_bi_compute of the reference (src/Estimators/d4est_estimator_bi.c:349-602) for
+         * the seeded u against rhs_l, with two prefactor families; estimator_vtk gives the four parts */
+        const int nl = p4est->local_num_quadrants;
+        double *res = P4EST_ALLOC_ZERO (double, local_nodes);
+        d4est_elliptic_data_t ev = vecs;
+        ev.u = u; ev.Au = res; ev.rhs = rhs_l;
+        d4est_elliptic_eqns_t fcns_res = {.build_residual = drv_build_residual,.apply_lhs = apply_plain,.user = flux_plain };
+        double pre = ((d4est_laplacian_flux_sipg_params_t *) flux_plain->flux_data)->sipg_penalty_prefactor;
+        for (int fam = 0; fam < 2; fam++) {
+          d4est_estimator_bi_penalty_data_t pd;
+          memset (&pd, 0, sizeof (pd));
+          pd.u_penalty_fcn = fam ? bi_u_prefactor_conforming_max_p2_over_h : houston_u_prefactor_maxp_minh;
+          pd.gradu_penalty_fcn = fam ? bi_gradu_prefactor_max_h_over_p : houston_gradu_prefactor_maxp_minh;
+          pd.u_dirichlet_penalty_fcn = fam ? bi_u_prefactor_conforming_max_p2_over_h : houston_u_dirichlet_prefactor_maxp_minh;
+          pd.penalty_prefactor = pre;
+          double *vtk = P4EST_ALLOC_ZERO (double, 4 * nl), *vtkf = P4EST_ALLOC_ZERO (double, 18 * nl);
+          double *eta2 = d4est_estimator_bi_compute (p4est, &ev, &fcns_res, pd, drv_poly_fcn, NULL, d4est_ghost,
+                                                     d4est_ghost_data, d4est_ops, d4est_geom, d4est_factors, d4est_geom,
+                                                     d4est_factors, d4est_quad, 0, vtk, vtkf);
+          d4b_dump_put1 (f, fam ? "est_eta2_bi_p2h" : "est_eta2_houston", D4B_F64, nl, eta2);
+          d4b_dump_put1 (f, fam ? "est_terms_bi_p2h" : "est_terms_houston", D4B_F64, 4 * (uint64_t) nl, vtk);
+          P4EST_FREE (eta2); P4EST_FREE (vtk); P4EST_FREE (vtkf);
+        }
+        d4b_dump_put1 (f, "est_residual", D4B_F64, local_nodes, res);
+        d4b_dump_put1 (f, "est_diam_volume", D4B_F64, nl, d4est_factors->diam_volume);
+        d4b_dump_scalar_f64 (f, "est_penalty_prefactor", pre);
+        P4EST_FREE (res);
+      }
       P4EST_FREE (rhs_l); P4EST_FREE (rhs_q); P4EST_FREE (f_l); P4EST_FREE (f_q);
     }
 

@@ -56,6 +56,9 @@ def test_build_rhs_inside_the_reference(ini, args):
     lines = run(ini, *args)
     res = [l for l in lines if "b200_build_rhs_rel_l2" in l][0]
     assert res["b200_build_rhs_rel_l2"] < 1e-12
+    # d4est_b200_estimator_bi_compute against d4est_estimator_bi_compute, same arguments
+    res = [l for l in lines if "b200_estimator_rel_max" in l][0]
+    assert res["b200_estimator_rel_max"] < 1e-11
 
 
 @pytest.mark.parametrize("ini,args", [("brick_poisson.ini", ["--uniform-deg", "3"]), ("sphere_hp.ini", ["--amr", "1"])])

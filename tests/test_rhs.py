@@ -58,3 +58,28 @@ def test_device_build_rhs_device_pointers(golden):
     m.build_rhs(f, J, rhs)
     assert rel(rhs.cpu().numpy(), A["rhs_strong_bc_lobatto"]) < TOL
     m.close()
+
+
+# ---------------------------------------------------------------- estimator (second half of f4)
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", CASES)
+@pytest.mark.parametrize("family,key", [("houston_maxp_minh", "houston"), ("bi_max_p2_over_h", "bi_p2h")])
+def test_device_estimator_matches_reference(golden, case, family, key):
+    """d4b_estimator_bi against d4est_estimator_bi_compute of the unmodified reference: eta^2 of every
+    element and its four parts (residual, Je1, Je2, boundary Je2), two prefactor families"""
+    from disco4est_b200 import Mesh
+
+    A = golden(case)
+    m = Mesh(A)
+    c = lambda k: np.ascontiguousarray(A[k])
+    nl = int(A["n_local"][0])
+    terms = np.zeros(4 * nl)
+    eta2 = m.estimator_bi(c("u"), c("est_residual"), c("J_quad"), c("est_diam_volume"), c("sj_m_mortar_quad"),
+                          c("hm_mortar_quad"), c("hp_mortar_quad"), float(A["est_penalty_prefactor"][0]), family=family,
+                          dirichlet_g=c("dirichlet_g_mortar_quad"), terms=terms)
+    m.close()
+    ref, ref_terms = A["est_eta2_" + key], A["est_terms_" + key].reshape(4, nl)
+    assert np.abs(eta2 - ref).max() < 1e-11 * np.abs(ref).max()
+    t = terms.reshape(4, nl)
+    for i in range(4):
+        assert np.abs(t[i] - ref_terms[i]).max() < 1e-11 * max(np.abs(ref_terms[i]).max(), 1e-300), i
