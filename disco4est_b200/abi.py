@@ -69,6 +69,8 @@ class MeshDesc(C.Structure):
         ("mirror_proc_offsets", _I32P),
         ("mirror_proc_mirrors", _I32P),
         ("ghost_proc_offsets", _I32P),
+        ("robin_coeff_mortar_quad", _F64P),
+        ("robin_rhs_mortar_quad", _F64P),
     ]
 
 

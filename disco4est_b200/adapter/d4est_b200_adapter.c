@@ -291,6 +291,40 @@ d4est_b200_flatten (p4est_t * p4est, d4est_ghost_t * d4est_ghost,
   D->sipg_penalty_prefactor = sipg->sipg_penalty_prefactor;
   D->sipg_penalty_fcn = identify_penalty (sipg->sipg_penalty_fcn);
   D->bc_type = (flux_data->bc_type == BC_ROBIN) ? D4B_BC_ROBIN : D4B_BC_DIRICHLET;
+  if (flux_data->bc_type == BC_ROBIN) {
+    /* the reference evaluates robin_coeff / robin_rhs at the boundary quadrature points inside every
+     * apply (d4est_laplacian_flux_sipg.c:385-410); they depend on the position only in every shipped
+     * problem (multi_puncture_fcns.h:772-804), so they are evaluated once per mesh here.  The
+     * callbacks also receive the boundary data of the face: position, normal and sj are provided. */
+    d4est_laplacian_robin_bc_t *bc = (d4est_laplacian_robin_bc_t *) flux_data->bc_data;
+    fl->robin_coeff = (double *) calloc (D->local_mortar_nodes_quad + 1, sizeof (double));
+    fl->robin_rhs = (double *) calloc (D->local_mortar_nodes_quad + 1, sizeof (double));
+    for (int s = 0; s < D->n_sides; s++) {
+      if (fl->side_faces_p[s] != 0) continue;
+      const int e = fl->side_e_m[4 * s], f_m = fl->side_f_m[s];
+      const int fnq = d4est_lgl_get_nodes ((P4EST_DIM) - 1, fl->deg_quad[e]);
+      const int64_t S = fl->side_mortar_stride[s];
+      const int bstride = (P4EST_DIM) * d4est_factors->local_strides[e].boundary_quad_stride[f_m];
+      d4est_laplacian_flux_boundary_data_t bd;
+      memset (&bd, 0, sizeof (bd));
+      bd.face_nodes_m_quad = fnq;
+      bd.deg_mortar_quad = fl->deg_quad[e];
+      bd.sj_on_f_m_quad = &d4est_factors->sj_m_mortar_quad[S];
+      bd.h_quad = &d4est_factors->hm_mortar_quad[S];
+      for (int d = 0; d < (P4EST_DIM); d++) {
+        bd.xyz_on_f_m_quad[d] = &d4est_factors->xyz_m_mortar_quad[bstride + d * fnq];
+        bd.xyz_on_f_m_lobatto[d] = &d4est_factors->xyz_m_mortar_lobatto[bstride + d * fnq];
+        bd.n_on_f_m_quad[d] = &d4est_factors->n_m_mortar_quad[(P4EST_DIM) * S + d * fnq];
+      }
+      for (int i = 0; i < fnq; i++) {
+        const double x = bd.xyz_on_f_m_quad[0][i], y = bd.xyz_on_f_m_quad[1][i], z = bd.xyz_on_f_m_quad[2][i];
+        fl->robin_coeff[S + i] = bc->robin_coeff (x, y, z, bc->user, &bd, i);
+        fl->robin_rhs[S + i] = bc->robin_rhs (x, y, z, bc->user, &bd, i);
+      }
+    }
+    D->robin_coeff_mortar_quad = fl->robin_coeff;
+    D->robin_rhs_mortar_quad = fl->robin_rhs;
+  }
 
   /* ghost exchange plan, as d4est_ghost_data_exchange reads it
    * (src/Mesh/d4est_ghost_data.c:171-199) */
@@ -327,6 +361,7 @@ d4est_b200_flat_destroy (d4est_b200_flat_t * fl)
   free (fl->side_faces_m); free (fl->side_faces_p); free (fl->side_f_m); free (fl->side_f_p);
   free (fl->side_e_m); free (fl->side_e_p); free (fl->side_perm); free (fl->side_sub_order);
   free (fl->side_mortar_stride); free (fl->side_penalty_mult); free (fl->dirichlet_g);
+  free (fl->robin_coeff); free (fl->robin_rhs);
   free (fl->mirror_elem); free (fl->mirror_proc_offsets); free (fl->mirror_proc_mirrors);
   free (fl->ghost_proc_offsets);
   free (fl);

@@ -43,6 +43,7 @@ typedef struct
   int64_t *side_mortar_stride;
   double  *side_penalty_mult;
   double  *dirichlet_g;
+  double  *robin_coeff, *robin_rhs;   /* BC_ROBIN: the two callbacks at the boundary quadrature points */
   int32_t *mirror_elem, *mirror_proc_offsets, *mirror_proc_mirrors, *ghost_proc_offsets;
   int side_capacity;
 } d4est_b200_flat_t;

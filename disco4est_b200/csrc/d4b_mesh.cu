@@ -99,7 +99,8 @@ extern "C" d4b_mesh_t *d4b_mesh_create(const d4b_mesh_desc_t *d) {
   D4B_CHECK(d->abi_version == D4B_ABI_VERSION, "d4b_mesh_create: ABI version %d, library has %d",
             d->abi_version, D4B_ABI_VERSION);
   D4B_CHECK(d4b_device_count() > 0, "d4b_mesh_create: no CUDA device (there is no CPU fallback)");
-  D4B_CHECK(d->bc_type == D4B_BC_DIRICHLET, "d4b_mesh_create: only Dirichlet boundaries are implemented");
+  D4B_CHECK(d->bc_type == D4B_BC_DIRICHLET || d->bc_type == D4B_BC_ROBIN, "d4b_mesh_create: unknown bc_type %d", d->bc_type);
+  D4B_CHECK(d->bc_type != D4B_BC_ROBIN || d->robin_coeff_mortar_quad, "d4b_mesh_create: Robin boundary without coefficients");
   d4b_mesh *m = new d4b_mesh();
   D4B_CUDA(cudaGetDevice(&m->device));
   D4B_CUDA(cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking));
@@ -227,6 +228,15 @@ extern "C" d4b_mesh_t *d4b_mesh_create(const d4b_mesh_desc_t *d) {
           double hp = d->hp_mortar_quad[ks];
           mortar[(size_t)6 * MP + ks] = sj * d->side_penalty_mult[s] *
               penalty(d->sipg_penalty_fcn, deg_m, hm, deg_p, hp, d->sipg_penalty_prefactor);
+        } else if (d->bc_type == D4B_BC_ROBIN) {
+          // sj (c u_m - q) = S (u_m - g) with S = sj c, g = q / c; no gradient term, no term2:
+          // the boundary branch of the kernels computes -sum A_m du_m + S (u_m - g) and -A_m (u_m - g)
+          const double c = d->robin_coeff_mortar_quad[ks];
+          const double q = d->robin_rhs_mortar_quad ? d->robin_rhs_mortar_quad[ks] : 0.;
+          D4B_CHECK(c != 0. || q == 0., "side %d: Robin coefficient 0 with a non-zero right-hand side", s);
+          for (int l = 0; l < 3; ++l) mortar[(size_t)l * MP + ks] = 0.;
+          mortar[(size_t)6 * MP + ks] = sj * c;
+          mortar[(size_t)7 * MP + ks] = (c != 0.) ? q / c : 0.;
         } else {
           mortar[(size_t)6 * MP + ks] = sj * d->side_penalty_mult[s] *
               penalty(d->sipg_penalty_fcn, deg_m, hm, deg_m, hm, d->sipg_penalty_prefactor);

@@ -21,7 +21,7 @@ from .brick import partition_offsets
 _SIDE_FIELDS = ("side_faces_m", "side_faces_p", "side_f_m", "side_f_p", "side_perm", "side_penalty_mult")
 _MORTAR_FIELDS = (("sj_m_mortar_quad", 1), ("n_m_mortar_quad", 3), ("drst_dxyz_m_mortar_quad", 9),
                   ("drst_dxyz_p_mortar_quad_porder", 9), ("hm_mortar_quad", 1), ("hp_mortar_quad", 1),
-                  ("dirichlet_g_mortar_quad", 1))
+                  ("dirichlet_g_mortar_quad", 1), ("robin_coeff_mortar_quad", 1), ("robin_rhs_mortar_quad", 1))
 
 
 def _i(x):

@@ -133,6 +133,16 @@ typedef struct d4b_mesh_desc
   const int32_t *mirror_proc_offsets;  /* [mpisize+1]                       */
   const int32_t *mirror_proc_mirrors;  /* indices into mirror_elem          */
   const int32_t *ghost_proc_offsets;   /* [mpisize+1] ghost ranges per rank */
+
+  /* ---- Robin boundary (bc_type = D4B_BC_ROBIN), d4est_laplacian_flux_sipg_robin_aux
+   * (src/dGMath/d4est_laplacian_flux_sipg.c:339-455): on a boundary face the operator adds
+   * V^T w sj (coeff u_m - rhs) and nothing else.  Both arrays use the scalar indexing of sj and
+   * hold the callbacks d4est_laplacian_robin_bc_t.robin_coeff / .robin_rhs evaluated at the
+   * boundary quadrature points (only boundary sides are read).  rhs may be NULL (= 0, what the
+   * Jacobian and residual of the two-puncture problems use, multi_puncture_fcns.h:790-804);
+   * a point with coeff = 0 and rhs != 0 is rejected.                                        */
+  const double *robin_coeff_mortar_quad;
+  const double *robin_rhs_mortar_quad;
 } d4b_mesh_desc_t;
 
 typedef struct d4b_mesh d4b_mesh_t;    /* opaque device-resident mesh */

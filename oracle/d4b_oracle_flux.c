@@ -116,6 +116,17 @@ d4bo_apply_flux (d4bo_ctx_t * c, const double *u, const double *ughost, double *
           dxm[j * FQ + k] = m_big ? .5 * g : g;
         }
       double t13[FQ], t2[3 * FQ];
+      if (faces_p == 0 && d->bc_type == D4B_BC_ROBIN) {
+        /* Robin boundary, d4est_laplacian_flux_sipg.c:339-455: sj (coeff u_m - rhs), tested and lifted */
+        const double *cf = d->robin_coeff_mortar_quad + S + off[i];
+        const double *rh = d->robin_rhs_mortar_quad ? d->robin_rhs_mortar_quad + S + off[i] : NULL;
+        for (int k = 0; k < nq2; k++) {
+          t13[k] = sj[k] * (cf[k] * um[k] - (rh ? rh[k] : 0.));
+          for (int l = 0; l < 3; l++) t2[l * FQ + k] = 0.;
+        }
+        test_and_lift (c, Au + d->nodal_stride[em[i]], deg_m, f_m, dqd[i], 0, 0, t13, t2, 1.);
+        continue;
+      }
       if (faces_p == 0) {
         /* Dirichlet boundary, d4est_laplacian_flux_sipg.c:86-137 */
         const double *g = d->dirichlet_g_mortar_quad ? d->dirichlet_g_mortar_quad + S + off[i] : NULL;

@@ -36,5 +36,7 @@ run sphere_p2 sphere_p.ini --uniform-deg 2 --cheby 8 10 --quad # conforming, 13 
 run sphere_hp_amr0 sphere_hp.ini --bc poly               # per-region degrees + quadrature increments
 run sphere_hp_amr1 sphere_hp.ini --amr 1 --bc poly       # random hp refinement: hanging faces
 run sphere_p_amr1 sphere_p.ini --amr 1 --bc poly           # random hp refinement with deg_quad = deg: the hp mortar kernel's mesh
+run brick_l2_p2_robin brick_poisson.ini --uniform-deg 2 --bc robin   # Robin boundary (coeff 1/|x|-like, non-zero rhs)
+run sphere_p_amr1_robin sphere_p.ini --amr 1 --bc robin               # Robin on the outer sphere, random hp refinement (two-puncture-like)
 run sphere_hp_amr1_zero sphere_hp.ini --amr 1 --cheby 8 10 --quad  # hanging faces, homogeneous BC, smoother outputs
 run brick_mg_l2_p2 brick_poisson_mg.ini --uniform-deg 2 --mg 4 --fcg 30   # + in-house FCG (multigrid-preconditioned and not) and CG: iterates, iteration counts; + the reference multigrid: residual and iterate after each of 4 V-cycles

@@ -59,6 +59,23 @@ drv_poly_fcn (double x, double y, double z, void *user)
   return x * x + y * y + z * z;
 }
 
+/* Robin boundary of the fixtures: coeff = 1 / |x| like multi_puncture_robin_coeff_sphere_fcn
+ * (src/Problems/TwoPunctures/multi_puncture_fcns.h:772-786, shifted so that it is finite on the
+ * brick), and a non-zero right-hand side so that both callbacks are exercised */
+static double
+drv_robin_coeff (double x, double y, double z, void *user, d4est_laplacian_flux_boundary_data_t * bd, int node)
+{
+  (void) user; (void) bd; (void) node;
+  return 1. / sqrt (x * x + y * y + z * z + .25);
+}
+
+static double
+drv_robin_rhs (double x, double y, double z, void *user, d4est_laplacian_flux_boundary_data_t * bd, int node)
+{
+  (void) user; (void) bd; (void) node;
+  return .3 * x - .2 * y * z;
+}
+
 /* residual callback for the estimator fixture: Au <- rhs - A u, like poisson_build_residual */
 static void
 drv_build_residual (p4est_t * p4est, d4est_ghost_t * ghost, d4est_ghost_data_t * ghost_data,
@@ -135,6 +152,10 @@ dump_desc (FILE * f, const d4b_mesh_desc_t * D)
   d4b_dump_put1 (f, "hp_mortar_quad", D4B_F64, m, D->hp_mortar_quad);
   if (D->dirichlet_g_mortar_quad)
     d4b_dump_put1 (f, "dirichlet_g_mortar_quad", D4B_F64, m, D->dirichlet_g_mortar_quad);
+  if (D->robin_coeff_mortar_quad) {
+    d4b_dump_put1 (f, "robin_coeff_mortar_quad", D4B_F64, m, D->robin_coeff_mortar_quad);
+    d4b_dump_put1 (f, "robin_rhs_mortar_quad", D4B_F64, m, D->robin_rhs_mortar_quad);
+  }
   uint64_t s = D->n_sides;
   d4b_dump_put1 (f, "side_faces_m", D4B_I32, s, D->side_faces_m);
   d4b_dump_put1 (f, "side_faces_p", D4B_I32, s, D->side_faces_p);
@@ -250,12 +271,12 @@ main (int argc, char *argv[])
   const char *ini = argv[1];
   const char *out = argv[2];
   int amr_steps = 0, time_reps = 0, bc_poly = 0, cheby_imax = 0, cheby_eigs_imax = 0, mg_vcycles = 0, use_b200 = 0;
-  int dump_quad = 0, fcg_imax = 0;
+  int dump_quad = 0, fcg_imax = 0, bc_robin = 0;
   const char *geom_out = NULL;
   for (int a = 3; a < argc; a++) {
     if (!strcmp (argv[a], "--amr")) amr_steps = atoi (argv[++a]);
     else if (!strcmp (argv[a], "--time")) time_reps = atoi (argv[++a]);
-    else if (!strcmp (argv[a], "--bc")) bc_poly = !strcmp (argv[++a], "poly");
+    else if (!strcmp (argv[a], "--bc")) { ++a; bc_poly = !strcmp (argv[a], "poly"); bc_robin = !strcmp (argv[a], "robin"); }
     else if (!strcmp (argv[a], "--uniform-deg")) g_uniform_deg = atoi (argv[++a]);
     else if (!strcmp (argv[a], "--cheby")) { cheby_imax = atoi (argv[++a]); cheby_eigs_imax = atoi (argv[++a]); }
     else if (!strcmp (argv[a], "--mg")) { mg_vcycles = atoi (argv[++a]); }
@@ -336,10 +357,21 @@ main (int argc, char *argv[])
   bc_data_for_lhs.eval_method = EVAL_BNDRY_FCN_ON_LOBATTO;
   bc_data_for_lhs.user = NULL;
 
-  d4est_laplacian_flux_data_t *flux_plain =
-    d4est_laplacian_flux_new (p4est, ini, BC_DIRICHLET, &bc_data_for_lhs);
-  d4est_laplacian_with_opt_flux_data_t *flux_opt =
-    d4est_laplacian_with_opt_flux_new (p4est, ini, BC_DIRICHLET, &bc_data_for_lhs);
+  d4est_laplacian_robin_bc_t bc_robin_data;
+  bc_robin_data.robin_coeff = drv_robin_coeff;
+  bc_robin_data.robin_rhs = drv_robin_rhs;
+  bc_robin_data.user = NULL;
+  d4est_laplacian_with_opt_robin_bc_t bc_robin_opt;
+  bc_robin_opt.robin_coeff = (d4est_laplacian_with_opt_mortar_xyz_fcn_t) drv_robin_coeff;
+  bc_robin_opt.robin_rhs = (d4est_laplacian_with_opt_mortar_xyz_fcn_t) drv_robin_rhs;
+  bc_robin_opt.user = NULL;
+
+  d4est_laplacian_flux_data_t *flux_plain = bc_robin
+    ? d4est_laplacian_flux_new (p4est, ini, BC_ROBIN, &bc_robin_data)
+    : d4est_laplacian_flux_new (p4est, ini, BC_DIRICHLET, &bc_data_for_lhs);
+  d4est_laplacian_with_opt_flux_data_t *flux_opt = bc_robin
+    ? d4est_laplacian_with_opt_flux_new (p4est, ini, BC_ROBIN, &bc_robin_opt)
+    : d4est_laplacian_with_opt_flux_new (p4est, ini, BC_DIRICHLET, &bc_data_for_lhs);
 
   d4est_elliptic_eqns_t fcns_plain = {.build_residual = NULL,.apply_lhs = apply_plain,.user = flux_plain };
   d4est_elliptic_eqns_t fcns_opt = {.build_residual = NULL,.apply_lhs = apply_with_opt,.user = flux_opt };

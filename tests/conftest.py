@@ -12,6 +12,7 @@ GOLDEN = os.path.join(ROOT, "tests", "golden")
 GOLDEN_CASES = [
     "brick_l2_p1", "brick_l2_p2_bc", "brick_l2_p3", "brick_l2_p5", "brick_l2_p7",
     "sphere_p2", "sphere_hp_amr0", "sphere_hp_amr1", "sphere_hp_amr1_zero", "sphere_p_amr1",
+    "brick_l2_p2_robin", "sphere_p_amr1_robin",
 ]
 
 

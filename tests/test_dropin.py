@@ -28,7 +28,9 @@ pytestmark = [pytest.mark.gpu, pytest.mark.skipif(not os.path.exists(DRV), reaso
 @pytest.mark.parametrize("ini,args", [("brick_poisson.ini", ["--uniform-deg", "3"]),
                                       ("sphere_p.ini", ["--uniform-deg", "2"]),
                                       ("sphere_hp.ini", []),
-                                      ("sphere_hp.ini", ["--amr", "1"])])
+                                      ("sphere_hp.ini", ["--amr", "1"]),
+                                      ("brick_poisson.ini", ["--uniform-deg", "2", "--bc", "robin"]),
+                                      ("sphere_p.ini", ["--amr", "1", "--bc", "robin"])])
 def test_apply_lhs_callback_inside_the_reference(ini, args):
     lines = run(ini, *args)
     res = [l for l in lines if "b200_apply_rel_l2" in l][0]

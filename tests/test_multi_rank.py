@@ -61,7 +61,7 @@ def test_two_gpu_apply_matches_oracle(level, p):
 
 
 @pytest.mark.parametrize("world,case", [(2, "sphere_hp_amr1_zero"), (3, "sphere_hp_amr1_zero"), (2, "sphere_p2"),
-                                        (3, "sphere_p_amr1")])
+                                        (3, "sphere_p_amr1"), (2, "sphere_p_amr1_robin")])
 def test_partitioned_hp_mesh_gloo(world, case):
     """BASELINE config 4 in small: curved cubed sphere, hp-adapted, hanging faces across rank boundaries"""
     run_ranks("gloo", world, "golden:" + case, 0)
