@@ -230,8 +230,10 @@ def bench_sphere(args, rank, world, local_rank, torch, dist, dev):
     """BASELINE.json configs[3] in synthetic form: the 13-tree cubed sphere (curved elements, all
     inter-tree face orientations), every tree refined to --sphere-level, split over the ranks
     along the Morton curve like p4est (strong scaling: the mesh is fixed).  Geometric factors
-    are generated on the device.  Two meshes: uniform degree (curved conforming kernel) and a
-    seeded random degree 1..deg per element (hp kernel).  GDOF/s of one apply each."""
+    are generated on the device.  Three meshes: uniform degree (curved conforming kernel); degree
+    graded radially, deg in the centre down to deg - 2 in the outermost layer (p-jumps on the layer
+    interfaces only: conforming + hp kernels); a seeded random degree 1..deg per element (every
+    face a p-jump, the hp kernel's worst case).  GDOF/s of one apply each."""
     import numpy as np
 
     from disco4est_b200 import Mesh
@@ -240,6 +242,7 @@ def bench_sphere(args, rank, world, local_rank, torch, dist, dev):
 
     out = {}
     for name, kw, lvl in (("uniform_p", dict(p=args.deg), args.sphere_level),
+                          ("graded_hp", dict(p=args.deg, graded=True), args.sphere_level),
                           ("random_hp", dict(pmax=args.deg), args.sphere_level)):
         t0 = time.perf_counter()
         A, g = sphere_desc(lvl, **kw)

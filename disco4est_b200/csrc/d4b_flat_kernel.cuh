@@ -60,7 +60,7 @@ struct FlatCfg {
 #define D4B_FLAT_THREADS {0, 0, 32, 64, 32, 128, 128, 64, 64}
 #endif
 #ifndef D4B_FLAT_MINB
-#define D4B_FLAT_MINB {0, 0, 1, 1, 24, 1, 1, 1, 1}
+#define D4B_FLAT_MINB {0, 0, 1, 12, 24, 5, 4, 1, 8}
 #endif
   static constexpr int kThreads[9] = D4B_FLAT_THREADS;
   static constexpr int kMinBlocks[9] = D4B_FLAT_MINB;   // resident blocks per SM the register budget is cut for

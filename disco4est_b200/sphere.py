@@ -56,10 +56,13 @@ def _perm_index(n, perm, a, b):
 
 
 def sphere_desc(level, p=3, pmax=None, seed=102321, prefactor=2.0, penalty_fcn=0, radii=(1.0, 2.0, 3.0),
-                compactify=(0, 0), face_h_type="j_div_sj_quad"):
+                compactify=(0, 0), face_h_type="j_div_sj_quad", graded=False):
     """(topology, geom): dicts for Mesh(topology, geom=geom) describing the whole 13-tree sphere on
     one rank (disco4est_b200.partition splits it).  pmax: draw every element's degree uniformly
-    from 1..pmax (seeded) instead of the uniform degree p."""
+    from 1..pmax (seeded) instead of the uniform degree p.  graded: degree p in the centre cube and
+    the inner shell, then decreasing outwards in radial layers of the outer shell down to
+    max(p - 2, 1) -- the kind of mesh p-adaptation of a centrally concentrated source produces
+    (ConstantDensityStar, two punctures): p-jumps only on the layer interfaces."""
     from scipy.spatial import cKDTree
 
     n = 1 << level
@@ -73,6 +76,10 @@ def sphere_desc(level, p=3, pmax=None, seed=102321, prefactor=2.0, penalty_fcn=0
         deg = np.random.default_rng(seed).integers(1, pmax + 1, size=E).astype(np.int64)
     else:
         deg = np.full(E, p, np.int64)
+    if graded:
+        outer = tree < 6
+        layer = (3 * iz) // n            # radial third of the outer shell (iz is the radial index there)
+        deg = np.where(outer, np.maximum(p - layer, max(p - 2, 1)), p).astype(np.int64)
 
     S = 6 * E
     f = np.tile(np.arange(6), E)

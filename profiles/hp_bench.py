@@ -12,10 +12,10 @@ from disco4est_b200.sphere import sphere_desc
 
 level = int(sys.argv[1]) if len(sys.argv) > 1 else 4
 deg = int(sys.argv[2]) if len(sys.argv) > 2 else 3
-modes = sys.argv[3:] or ["uniform", "hp"]
+modes = sys.argv[3:] or ["uniform", "hp"]  # also: graded
 dev = torch.device("cuda:0")
 for mode in modes:
-    kw = dict(pmax=deg) if mode == "hp" else dict(p=deg)
+    kw = dict(pmax=deg) if mode == "hp" else dict(p=deg, graded=True) if mode == "graded" else dict(p=deg)
     if mode == "generic":
         os.environ["D4B_FORCE_GENERIC"] = "1"
     A, g = sphere_desc(level, **kw)
