@@ -174,8 +174,10 @@ def bench_reference(args):
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "unit-cube Poisson SIPG apply, p=%d (reference arm: bounded %d^3 sample per core)"
-                               % (deg, 1 << level)},
+        "config": {"workload": "unit-cube Poisson SIPG apply, %d^3 elements per GPU, p=%d, deg_quad=p, "
+                               "Gauss quadrature, SIPG prefactor 2 maxp_sqr_over_minh, homogeneous Dirichlet"
+                               % (1 << args.level, deg),
+                   "sample": "bounded: %d^3 elements per core (cost per element is mesh-size independent)" % (1 << level)},
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 
