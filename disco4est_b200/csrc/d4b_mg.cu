@@ -12,6 +12,7 @@
 // dot products that steer CG and the stopping tests.
 #include <cmath>
 #include <cstring>
+#include <cstdlib>
 #include "d4b_internal.h"
 
 struct d4b_mg {
@@ -27,6 +28,18 @@ struct d4b_mg {
   double *d_scal = nullptr;      // bottom CG scalars (BcgScal)
   double *h_scal = nullptr;      // pinned
   int vcycle_num_finished = 0;
+  // CUDA graphs of whole V-cycles (one rank, Chebyshev bottom solver: the kernel sequence is then
+  // fixed and all its scalars live on the device).  Keyed by the caller's vectors and the two
+  // eigenvalue-reuse decisions; a key is captured the second time it is seen.
+  struct CycleGraph {
+    double *u = nullptr; const double *rhs = nullptr;
+    bool eigs_down = false, eigs_up = false;
+    int seen = 0;
+    cudaGraphExec_t exec = nullptr;
+  };
+  std::vector<CycleGraph> graphs;
+  double *d_r2 = nullptr;        // squared residual of the last cycle
+  cudaStream_t cap_stream = nullptr;
 };
 
 namespace {
@@ -192,30 +205,75 @@ double vcycle_device(d4b_mg *g, double *u_top, const double *rhs_top) {
     if (saved[l] != s) D4B_CUDA(cudaStreamSynchronize(saved[l]));
     g->mesh[l]->stream = s;
   }
-  for (int l = top; l > 0; --l) {
-    d4b_mesh *m = g->mesh[l];
-    double *u = (l == top) ? u_top : g->d_u[l];
-    const double *rhs = (l == top) ? rhs_top : g->d_rhs[l];
-    if (l != top) D4B_CUDA(cudaMemsetAsync(u, 0, (size_t)m->local_nodes * sizeof(double), s));
-    smooth(g, l, u, rhs, g->d_r[l], eigs_down);
-    // restricted residual is the coarse right-hand side
-    transfer(g, 1, 0, l - 1, g->d_r[l], g->d_rhs[l - 1]);
-  }
-  {
-    d4b_mesh *m = g->mesh[0];
-    D4B_CUDA(cudaMemsetAsync(g->d_u[0], 0, (size_t)m->local_nodes * sizeof(double), s));
-    if (g->prm.bottom_solver == 0) bottom_cg(g, g->d_u[0], g->d_rhs[0], g->d_r[0]);
-    else bottom_cheby(g, g->d_u[0], g->d_rhs[0], g->d_r[0]);
-  }
-  for (int l = 0; l < top; ++l) {
-    const int f = l + 1;
-    double *u = (f == top) ? u_top : g->d_u[f];
-    const double *rhs = (f == top) ? rhs_top : g->d_rhs[f];
-    transfer(g, 0, 1, l, g->d_u[l], u);   // u_fine += P u_coarse
-    smooth(g, f, u, rhs, g->d_r[f], eigs_up);
-  }
   d4b_mesh *mt = g->mesh[top];
-  const double r2 = d4b_vec_dot(mt, g->d_r[top], g->d_r[top], mt->local_nodes);   // synchronises
+  if (!g->d_r2) g->d_r2 = d4b_dev_alloc<double>(mt, 2);
+  auto enqueue = [&](cudaStream_t s) {
+    for (int l = top; l > 0; --l) {
+      d4b_mesh *m = g->mesh[l];
+      double *u = (l == top) ? u_top : g->d_u[l];
+      const double *rhs = (l == top) ? rhs_top : g->d_rhs[l];
+      if (l != top) D4B_CUDA(cudaMemsetAsync(u, 0, (size_t)m->local_nodes * sizeof(double), s));
+      smooth(g, l, u, rhs, g->d_r[l], eigs_down);
+      // restricted residual is the coarse right-hand side
+      transfer(g, 1, 0, l - 1, g->d_r[l], g->d_rhs[l - 1]);
+    }
+    {
+      d4b_mesh *m = g->mesh[0];
+      D4B_CUDA(cudaMemsetAsync(g->d_u[0], 0, (size_t)m->local_nodes * sizeof(double), s));
+      if (g->prm.bottom_solver == 0) bottom_cg(g, g->d_u[0], g->d_rhs[0], g->d_r[0]);
+      else bottom_cheby(g, g->d_u[0], g->d_rhs[0], g->d_r[0]);
+    }
+    for (int l = 0; l < top; ++l) {
+      const int f = l + 1;
+      double *u = (f == top) ? u_top : g->d_u[f];
+      const double *rhs = (f == top) ? rhs_top : g->d_rhs[f];
+      transfer(g, 0, 1, l, g->d_u[l], u);   // u_fine += P u_coarse
+      smooth(g, f, u, rhs, g->d_r[f], eigs_up);
+    }
+    d4b_dot_async(mt, g->d_r[top], g->d_r[top], mt->local_nodes, g->d_r2);
+  };
+  // graph replay: only when the sequence is static (no host polling, no second stream)
+  bool graphable = g->prm.bottom_solver == 1 && !(getenv("D4B_MG_GRAPH") && atoi(getenv("D4B_MG_GRAPH")) == 0);
+  for (int l = 0; l <= top && graphable; ++l) graphable = g->mesh[l]->mpisize == 1;
+  d4b_mg::CycleGraph *cg = nullptr;
+  if (graphable) {
+    for (auto &c2 : g->graphs)
+      if (c2.u == u_top && c2.rhs == rhs_top && c2.eigs_down == eigs_down && c2.eigs_up == eigs_up) cg = &c2;
+    if (!cg) {
+      if (g->graphs.size() >= 8) {   // vectors keep changing: stop caching
+        for (auto &c2 : g->graphs) if (c2.exec) cudaGraphExecDestroy(c2.exec);
+        g->graphs.clear();
+      }
+      g->graphs.emplace_back();
+      cg = &g->graphs.back();
+      cg->u = u_top; cg->rhs = rhs_top; cg->eigs_down = eigs_down; cg->eigs_up = eigs_up;
+    }
+  }
+  if (cg && cg->exec) {
+    D4B_CUDA(cudaGraphLaunch(cg->exec, s));
+  } else if (cg && cg->seen >= 1) {
+    // every lazy allocation and kernel attribute was set by the first, eager cycle with this key
+    // captured on a private stream (the caller's may be the legacy default stream, which cannot be
+    // captured), replayed on the caller's
+    cudaGraph_t graph = nullptr;
+    if (!g->cap_stream) D4B_CUDA(cudaStreamCreateWithFlags(&g->cap_stream, cudaStreamNonBlocking));
+    D4B_CUDA(cudaStreamSynchronize(s));
+    for (int l = 0; l <= top; ++l) g->mesh[l]->stream = g->cap_stream;
+    D4B_CUDA(cudaStreamBeginCapture(g->cap_stream, cudaStreamCaptureModeThreadLocal));
+    enqueue(g->cap_stream);
+    D4B_CUDA(cudaStreamEndCapture(g->cap_stream, &graph));
+    for (int l = 0; l <= top; ++l) g->mesh[l]->stream = s;
+    D4B_CUDA(cudaGraphInstantiate(&cg->exec, graph, 0));
+    D4B_CUDA(cudaGraphDestroy(graph));
+    D4B_CUDA(cudaGraphLaunch(cg->exec, s));
+  } else {
+    enqueue(s);
+  }
+  if (cg) cg->seen++;
+  double r2 = 0.;
+  D4B_CUDA(cudaMemcpyAsync(g->h_scal + 32, g->d_r2, sizeof(double), cudaMemcpyDeviceToHost, s));
+  D4B_CUDA(cudaStreamSynchronize(s));
+  r2 = g->h_scal[32];
   for (int l = 0; l <= top; ++l) g->mesh[l]->stream = saved[l];
   return r2;
 }
@@ -336,6 +394,9 @@ extern "C" void d4b_mg_destroy(d4b_mg_t *g) {
   if (g->d_top_rhs) cudaFree(g->d_top_rhs);
   cudaFree(g->d_P); cudaFree(g->d_P_off);
   cudaFree(g->d_eigs); cudaFree(g->d_scal); cudaFreeHost(g->h_scal);
+  for (auto &c : g->graphs) if (c.exec) cudaGraphExecDestroy(c.exec);
+  if (g->d_r2) cudaFree(g->d_r2);
+  if (g->cap_stream) cudaStreamDestroy(g->cap_stream);
   delete g;
 }
 
