@@ -204,6 +204,7 @@ extern "C" void d4b_estimator_bi(d4b_mesh_t *m, const d4b_estimator_desc_t *d, d
 extern "C" void d4b_mesh_set_mass_diag(d4b_mesh_t *m, const double *jac_quad) {
   D4B_CHECK(m, "d4b_mesh_set_mass_diag: NULL mesh");
   D4B_CUDA(cudaStreamSynchronize(m->stream));
+  m->config_epoch++;   // recorded V-cycle graphs of this mesh are stale
   if (!jac_quad) {
     if (m->d_W) { cudaFree(m->d_W); m->d_W = nullptr; m->device_bytes -= m->local_nodes_quad * (int64_t)sizeof(double); }
     return;

@@ -88,6 +88,7 @@ struct d4b_mesh {
   int64_t local_nodes = 0, local_nodes_quad = 0, mortar_nodes = 0, ghost_nodes = 0;
   int max_deg = 0, max_deg_quad = 0;
   int64_t device_bytes = 0;
+  int64_t config_epoch = 0;      // bumped whenever a later launch sequence would differ (d4b_mesh_set_mass_diag)
 
   // tables
   D4bTables tab;                 // host copy of offsets

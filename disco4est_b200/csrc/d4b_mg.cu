@@ -34,6 +34,7 @@ struct d4b_mg {
   struct CycleGraph {
     double *u = nullptr; const double *rhs = nullptr;
     bool eigs_down = false, eigs_up = false;
+    int64_t epoch = 0;             // sum of the levels' config_epoch when the key was created
     int seen = 0;
     cudaGraphExec_t exec = nullptr;
   };
@@ -236,9 +237,12 @@ double vcycle_device(d4b_mg *g, double *u_top, const double *rhs_top) {
   bool graphable = g->prm.bottom_solver == 1 && !(getenv("D4B_MG_GRAPH") && atoi(getenv("D4B_MG_GRAPH")) == 0);
   for (int l = 0; l <= top && graphable; ++l) graphable = g->mesh[l]->mpisize == 1;
   d4b_mg::CycleGraph *cg = nullptr;
+  int64_t epoch = 0;
+  for (int l = 0; l <= top; ++l) epoch += g->mesh[l]->config_epoch;
   if (graphable) {
     for (auto &c2 : g->graphs)
-      if (c2.u == u_top && c2.rhs == rhs_top && c2.eigs_down == eigs_down && c2.eigs_up == eigs_up) cg = &c2;
+      if (c2.u == u_top && c2.rhs == rhs_top && c2.eigs_down == eigs_down && c2.eigs_up == eigs_up &&
+          c2.epoch == epoch) cg = &c2;
     if (!cg) {
       if (g->graphs.size() >= 8) {   // vectors keep changing: stop caching
         for (auto &c2 : g->graphs) if (c2.exec) cudaGraphExecDestroy(c2.exec);
@@ -246,7 +250,7 @@ double vcycle_device(d4b_mg *g, double *u_top, const double *rhs_top) {
       }
       g->graphs.emplace_back();
       cg = &g->graphs.back();
-      cg->u = u_top; cg->rhs = rhs_top; cg->eigs_down = eigs_down; cg->eigs_up = eigs_up;
+      cg->u = u_top; cg->rhs = rhs_top; cg->eigs_down = eigs_down; cg->eigs_up = eigs_up; cg->epoch = epoch;
     }
   }
   if (cg && cg->exec) {

@@ -136,3 +136,41 @@ def test_gpu_solve_stops_like_the_reference(gpu_mg):
     n2, hist2 = mg.solve(du, torch.from_numpy(rhs).cuda())
     assert n2 == n and np.array_equal(du.cpu().numpy(), u)
     mg.close()
+
+
+@pytest.mark.gpu
+def test_graph_replay_equals_eager_cycles(monkeypatch):
+    """the recorded V-cycle (CUDA graph, Chebyshev bottom solver) reproduces the eagerly enqueued one
+    bit for bit, and a graph recorded before d4b_mesh_set_mass_diag is not replayed after it"""
+    import torch
+
+    from disco4est_b200 import Mesh
+    from disco4est_b200.brick import brick_hierarchy
+    from disco4est_b200.runtime import Multigrid, cheby_params
+
+    descs, transfers = brick_hierarchy(3, 2)
+    dev = torch.device("cuda:0")
+
+    def run(graph):
+        monkeypatch.setenv("D4B_MG_GRAPH", "1" if graph else "0")
+        meshes = [Mesh(d) for d in descs]
+        mg = Multigrid(meshes, transfers, cheby_params(6, 6), vcycle_imax=1, bottom_solver="cheby",
+                       bottom_cheby=cheby_params(6, 8))
+        n = meshes[-1].n
+        rhs = torch.rand(n, dtype=torch.float64, device=dev, generator=torch.Generator(device=dev).manual_seed(3))
+        u = torch.zeros_like(rhs)
+        r2 = [mg.vcycle(u, rhs) for _ in range(4)]       # eager, capture, replay, replay
+        jac = torch.full((int(descs[-1]["local_nodes_quad"]),), 0.7, dtype=torch.float64, device=dev)
+        meshes[-1].set_mass_diag(jac)                    # the operator changes: A + 0.7 M-like term
+        r2 += [mg.vcycle(u, rhs) for _ in range(3)]
+        out = u.cpu().numpy().copy()
+        mg.close()
+        for m in meshes:
+            m.close()
+        return r2, out
+
+    r2_g, u_g = run(True)
+    r2_e, u_e = run(False)
+    assert r2_g == r2_e
+    assert np.array_equal(u_g, u_e)
+    assert r2_g[4] != r2_g[3]
