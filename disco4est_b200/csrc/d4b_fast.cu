@@ -90,6 +90,23 @@ struct FastArgs {
   int prefetch;                 // L2 prefetch of the block's volume metric and face records at kernel start
 };
 
+// Placement of the N^3 block in shared memory for the three line orientations: an XOR swizzle for
+// N = 4, 8 (conflict-free), padded pitches for the other N (a search over pitches and the element
+// stride for the fewest 16-lane wavefronts, profiles/pad_search.py: N = 6 228 -> 162, N = 3 78 -> 57; flat kernel +2..3 % at p = 2, 4, 5).
+template <int N> struct VLay { static constexpr int P1 = N, P2 = N * N, PAD = 0; };
+template <> struct VLay<3> { static constexpr int P1 = 3, P2 = 18, PAD = 10; };
+template <> struct VLay<5> { static constexpr int P1 = 5, P2 = 25, PAD = 10; };
+template <> struct VLay<6> { static constexpr int P1 = 9, P2 = 54, PAD = 5; };
+// doubles one block occupies (largest index + 1)
+template <int N>
+struct VSize { static constexpr int value = (N == 4 || N == 8) ? N * N * N : (VLay<N>::P2 + VLay<N>::P1) * (N - 1) + N; };
+template <int N>
+__device__ __forceinline__ int vix(int a, int b, int c) {
+  if (N == 4) return 16 * c + ((a + 4 * b) ^ (5 * c));
+  if (N == 8) return 64 * c + 8 * (b ^ (c & 1)) + (a ^ b);
+  return a + VLay<N>::P1 * b + VLay<N>::P2 * c;
+}
+
 template <int N>
 struct Cfg {
   static constexpr int NN = N * N;
@@ -115,7 +132,8 @@ struct CurvedCfg {
   static constexpr int MIN_BLOCKS = kMinBlocks[N];
   static constexpr int EPB = THREADS / NN;
   // shared doubles per element: V0,V1,V2 + FT (12*NN) + NB (8*NN) + NB2 (4*NN)
-  static constexpr int SH_PER_ELEM = 3 * N3 + 24 * NN;
+  static constexpr int VS = VSize<N>::value;              // doubles of one swizzled / padded N^3 block
+  static constexpr int SH_PER_ELEM = 3 * VS + 24 * NN + VLay<N>::PAD;
 };
 template <int THREADS>
 __device__ __forceinline__ void curved_sync() {
@@ -134,13 +152,6 @@ __device__ __forceinline__ int perm_xy(int n, int perm, int a, int b) {
   return row * n + col;
 }
 
-// bank-conflict-free placement of the N^3 block for the three line orientations
-template <int N>
-__device__ __forceinline__ int vix(int a, int b, int c) {
-  if (N == 4) return 16 * c + ((a + 4 * b) ^ (5 * c));
-  if (N == 8) return 64 * c + 8 * (b ^ (c & 1)) + (a ^ b);
-  return a + N * b + N * N * c;
-}
 
 // ---- kernel 1: uh = (I x I x I) u ---------------------------------------------
 template <int N>
@@ -149,13 +160,13 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) interp_kernel(const int32_t *
                                                                  const double *__restrict__ u,
                                                                  double *__restrict__ uh) {
   using C = Cfg<N>;
-  constexpr int NN = C::NN, N3 = C::N3;
-  __shared__ double sm[C::EPB * N3];
+  constexpr int NN = C::NN;
+  __shared__ double sm[C::EPB * VSize<N>::value];
   const FastTab &T = c_tab[N];
   const int slot = threadIdx.x / NN, lt = threadIdx.x % NN, lx = lt % N, ly = lt / N;
   const int ei = blockIdx.x * C::EPB + slot;
   const bool active = (slot < C::EPB) && (ei < n_elem);
-  double *V = sm + (slot < C::EPB ? slot : 0) * N3;
+  double *V = sm + (slot < C::EPB ? slot : 0) * VSize<N>::value;
   const int64_t ns = active ? nodal_stride[elem[ei]] : 0;
   if (active) {
     double l[N];
@@ -210,8 +221,8 @@ __global__ void __launch_bounds__(CurvedCfg<N>::THREADS, CurvedCfg<N>::MIN_BLOCK
   const int ei = a.first + blockIdx.x * C::EPB + slot;
   const bool active = (slot < C::EPB) && (ei < a.n_elem);
   double *V0 = smem + (size_t)(slot < C::EPB ? slot : 0) * C::SH_PER_ELEM;
-  double *V1 = V0 + N3, *V2 = V1 + N3;
-  double *FT = V2 + N3;            // [6][2][NN] own trace / normal derivative at face Gauss points
+  double *V1 = V0 + C::VS, *V2 = V1 + C::VS;
+  double *FT = V2 + C::VS;         // [6][2][NN] own trace / normal derivative at face Gauss points
   double *NB = FT + 12 * NN;       // [2][4][NN] neighbour: trace, normal, two tangential derivatives
   double *NB2 = NB + 8 * NN;       // [2][2][NN] weighted tangential term2
   const int64_t ns = active ? a.nodal_stride[a.elem[ei]] : 0;

@@ -67,7 +67,8 @@ struct FlatCfg {
   static constexpr int THREADS = kThreads[N];
   static constexpr int EPB = THREADS / NN;
   // V0,V1,V2 + per-thread face results [6][2][NN] + 6 face metas (2 doubles each)
-  static constexpr int SH_PER_ELEM = 3 * N3 + 12 * NN + 12;
+  static constexpr int VS = VSize<N>::value;
+  static constexpr int SH_PER_ELEM = 3 * VS + 12 * NN + 12 + VLay<N>::PAD;
   static constexpr int MIN_BLOCKS = kMinBlocks[N];
 };
 
@@ -158,8 +159,8 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) f
   const int ei = a.first + blockIdx.x * C::EPB + slot;
   const bool active = (slot < C::EPB) && (ei < a.n_elem);
   double *V0 = smem + (size_t)(slot < C::EPB ? slot : 0) * C::SH_PER_ELEM;
-  double *V1 = V0 + N3, *V2 = V1 + N3;
-  double *FB = V2 + N3;                                   // [6][2][NN], thread-private columns
+  double *V1 = V0 + C::VS, *V2 = V1 + C::VS;
+  double *FB = V2 + C::VS;                                // [6][2][NN], thread-private columns
   FaceMeta *META = reinterpret_cast<FaceMeta *>(FB + 12 * NN);
   const int64_t ns = active ? a.nodal_stride[a.elem[ei]] : 0;
   const double wxy = T.w[lx] * T.w[ly];
