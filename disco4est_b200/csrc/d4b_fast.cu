@@ -110,7 +110,6 @@ __device__ __forceinline__ int vix(int a, int b, int c) {
 template <int N>
 struct Cfg {
   static constexpr int NN = N * N;
-  static constexpr int N3 = N * N * N;
   static constexpr int THREADS = (N == 7 || N == 6) ? 256 : 128;
   static constexpr int EPB = THREADS / NN;           // elements per CTA
 };
