@@ -3,6 +3,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <algorithm>
+#include <vector>
 #include "d4b_internal.h"
 
 namespace {
@@ -73,10 +74,60 @@ void d4b_apply_device(d4b_mesh *m, const double *du, double *dAu) {
 }
 
 namespace {
+// Host-pointer apply, pipelined: u goes up in chunks of consecutive elements, a chunk is applied as
+// soon as the chunks holding its face neighbours have arrived (their uh is computed on arrival), and
+// its part of Au goes down while later chunks are still going up -- the two copy engines run
+// concurrently instead of one after the other.
+void apply_host_pipelined(d4b_mesh *m, const double *u, double *Au) {
+  const int K = (int)m->chunk_dep.size();
+  if (!m->h2d_stream) {
+    D4B_CUDA(cudaStreamCreateWithFlags(&m->h2d_stream, cudaStreamNonBlocking));
+    D4B_CUDA(cudaStreamCreateWithFlags(&m->d2h_stream, cudaStreamNonBlocking));
+    m->ev_h2d.resize(K); m->ev_done.resize(K);
+    for (int k = 0; k < K; ++k) {
+      D4B_CUDA(cudaEventCreateWithFlags(&m->ev_h2d[k], cudaEventDisableTiming));
+      D4B_CUDA(cudaEventCreateWithFlags(&m->ev_done[k], cudaEventDisableTiming));
+    }
+  }
+  D4B_CUDA(cudaStreamSynchronize(m->stream));   // the staging vectors are free
+  m->epi = D4bEpilogue();
+  double *du = m->d_u_stage, *dAu = m->d_Au_stage;
+  for (int i = 0; i < K; ++i) {
+    const int k = m->chunk_order[i];
+    const int64_t n0 = m->chunk_node[k], n1 = m->chunk_node[k + 1];
+    if (n1 > n0)
+      D4B_CUDA(cudaMemcpyAsync(du + n0, u + n0, (size_t)(n1 - n0) * sizeof(double), cudaMemcpyHostToDevice, m->h2d_stream));
+    D4B_CUDA(cudaEventRecord(m->ev_h2d[i], m->h2d_stream));
+  }
+  std::vector<char> launched(K, 0);
+  for (int i = 0; i < K; ++i) {
+    const int k = m->chunk_order[i];
+    D4B_CUDA(cudaStreamWaitEvent(m->stream, m->ev_h2d[i], 0));
+    d4b_launch_fast_range(m, du, dAu, 0, m->chunk_elem[k], m->chunk_elem[k + 1]);
+    for (int j = 0; j <= i; ++j) {
+      const int c = m->chunk_order[j];
+      if (launched[c] || m->chunk_dep[c] > i) continue;
+      launched[c] = 1;
+      d4b_launch_fast_range(m, du, dAu, 1, m->chunk_elem[c], m->chunk_elem[c + 1]);
+      D4B_CUDA(cudaEventRecord(m->ev_done[c], m->stream));
+      D4B_CUDA(cudaStreamWaitEvent(m->d2h_stream, m->ev_done[c], 0));
+      const int64_t n0 = m->chunk_node[c], n1 = m->chunk_node[c + 1];
+      if (n1 > n0)
+        D4B_CUDA(cudaMemcpyAsync(Au + n0, dAu + n0, (size_t)(n1 - n0) * sizeof(double), cudaMemcpyDeviceToHost, m->d2h_stream));
+    }
+  }
+  D4B_CUDA(cudaStreamSynchronize(m->d2h_stream));
+  D4B_CUDA(cudaStreamSynchronize(m->stream));
+}
+
 void apply_impl(d4b_mesh *m, const double *u, double *Au, int stiffness_only) {
   D4B_CHECK(m && u && Au, "d4b_apply: NULL argument");
   D4B_CHECK(m->n_ghost == 0 || m->d_ughost, "d4b_apply: ghost buffer missing");
   bool u_dev = is_device_ptr(u), Au_dev = is_device_ptr(Au);
+  if (!u_dev && !Au_dev && !stiffness_only && !m->chunk_dep.empty() && u != Au) {
+    apply_host_pipelined(m, u, Au);
+    return;
+  }
   const double *du = u;
   double *dAu = Au;
   size_t bytes = (size_t)m->local_nodes * sizeof(double);

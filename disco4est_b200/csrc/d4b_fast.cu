@@ -650,6 +650,15 @@ void launch_fast(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, 
   D4B_CUDA(cudaGetLastError());
 }
 
+template <int N>
+void launch_interp_range(d4b_mesh *m, const D4bFastClass &cls, const double *d_u, int lo, int hi) {
+  using C = Cfg<N>;
+  if (hi <= lo) return;
+  interp_kernel<N><<<(hi - lo + C::EPB - 1) / C::EPB, C::THREADS, 0, m->stream>>>(cls.d_hat_elem + lo, hi - lo,
+                                                                                   m->d_nodal_stride, d_u, m->d_uhat);
+  D4B_CUDA(cudaGetLastError());
+}
+
 void build_fast_tab(int N, FastTab &T) {
   memset(&T, 0, sizeof(T));
   double xl[8], wl[8], xg[8], wg[8], E[64], ends[2] = {-1., 1.};
@@ -841,6 +850,7 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
       if (!hat_done) {
         c.n_hat = (int)hat_by_deg[p].size();
         c.d_hat_elem = d4b_dev_upload<int32_t>(m, hat_by_deg[p].data(), hat_by_deg[p].size());
+        c.h_hat = hat_by_deg[p];
         c.n_ghost_hat = (int)ghost_hat.size();
         c.d_ghost_hat = d4b_dev_upload<int32_t>(m, ghost_hat.data(), ghost_hat.size());
         hat_done = true;
@@ -896,6 +906,7 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
         }
       }
       c.d_elem = d4b_dev_upload<int32_t>(m, els.data(), els.size());
+      c.h_elem = els;
       c.d_FG = d4b_dev_upload<double>(m, FG.data(), FG.size());
       if (kind == 0) {
         c.d_face_rec = d4b_dev_upload<int64_t>(m, face_rec.data(), face_rec.size());
@@ -932,6 +943,7 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
       if (!hat_done) {
         c.n_hat = (int)hat_by_deg[p].size();
         c.d_hat_elem = d4b_dev_upload<int32_t>(m, hat_by_deg[p].data(), hat_by_deg[p].size());
+        c.h_hat = hat_by_deg[p];
         c.n_ghost_hat = (int)ghost_hat.size();
         c.d_ghost_hat = d4b_dev_upload<int32_t>(m, ghost_hat.data(), ghost_hat.size());
         hat_done = true;
@@ -939,6 +951,7 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
       c.n_elem = (int)els.size();
       c.n_interior = (int)(mid - els.begin());
       c.d_elem = d4b_dev_upload<int32_t>(m, els.data(), els.size());
+      c.h_elem = els;
       m->n_hp_elem += c.n_elem;
       m->fast.push_back(c);
     }
@@ -948,6 +961,26 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
   if (!FF.empty()) m->d_fast_FF = d4b_dev_upload<double>(m, FF.data(), FF.size());
   if (!FF3.empty()) m->d_flat_FF = d4b_dev_upload<double>(m, FF3.data(), FF3.size());
   m->d_uhat = d4b_dev_alloc<double>(m, (size_t)(d->local_nodes + d->ghost_nodes));
+}
+
+void d4b_launch_fast_range(d4b_mesh *m, const double *d_u, double *d_Au, int what, int e0, int e1) {
+  for (const D4bFastClass &c : m->fast) {
+    const std::vector<int32_t> &list = what == 0 ? c.h_hat : c.h_elem;
+    const int lo = (int)(std::lower_bound(list.begin(), list.end(), e0) - list.begin());
+    const int hi = (int)(std::lower_bound(list.begin(), list.end(), e1) - list.begin());
+    if (hi <= lo) continue;
+#define D4B_CASE(n) case n: \
+      if (what == 0) launch_interp_range<n>(m, c, d_u, lo, hi); \
+      else if (c.kind == 2) launch_hp<n>(m, c, d_Au, lo, hi); \
+      else if (c.kind) launch_flat<n>(m, c, d_Au, lo, hi); \
+      else launch_fast<n>(m, c, d_Au, lo, hi); \
+      break;
+    switch (c.deg + 1) {
+      D4B_CASE(2) D4B_CASE(3) D4B_CASE(4) D4B_CASE(5) D4B_CASE(6) D4B_CASE(7) D4B_CASE(8)
+      default: D4B_ABORT("fast path: unsupported degree %d", c.deg);
+    }
+#undef D4B_CASE
+  }
 }
 
 // part 0: uh of the local elements; part 1: elements without a ghost neighbour;

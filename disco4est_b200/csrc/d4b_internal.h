@@ -54,6 +54,7 @@ struct D4bFastClass {
   int64_t *d_face_rec = nullptr; // [6*n_elem] face record offset
   int64_t *d_face_nbr = nullptr; // [6*n_elem] neighbour nodal offset / -1
   int32_t *d_face_code = nullptr;
+  std::vector<int32_t> h_elem, h_hat;   // host copies of d_elem / d_hat_elem (chunked host-pointer applies)
   int kind = 0;                  // 0: general conforming kernel, 1: tangential-free faces (d4b_flat_kernel.cuh),
                                  // 2: hp mortar kernel (d4b_hp_kernel.cuh)
   void *d_face_meta = nullptr;   // kind 1: [6*n_elem] packed face descriptors
@@ -135,6 +136,12 @@ struct d4b_mesh {
 
   // staging for host-pointer calls
   double *d_u_stage = nullptr, *d_Au_stage = nullptr;
+  // pipelined host-pointer apply (d4b_capi.cu): contiguous element chunks [chunk_elem[k], chunk_elem[k+1]),
+  // sent in chunk_order; chunk_dep[k] = position in that order of the last chunk holding a face neighbour of k
+  std::vector<int32_t> chunk_elem, chunk_dep, chunk_order;
+  std::vector<int64_t> chunk_node;
+  cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;
+  std::vector<cudaEvent_t> ev_h2d, ev_done;
   // scratch for reductions / smoother
   double *d_red = nullptr;         // partial sums
   double *h_red = nullptr;         // pinned
@@ -179,6 +186,8 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *desc, const std::vector<
 // part 0: uh of local elements; 1: interior elements; 2 (after the halo exchange): uh of
 // ghost elements + elements with a ghost neighbour
 void d4b_launch_fast(d4b_mesh *m, const double *d_u, double *d_Au, int part);
+// one-rank meshes: what = 0: uh of the elements [e0, e1); what = 1: apply on the elements [e0, e1)
+void d4b_launch_fast_range(d4b_mesh *m, const double *d_u, double *d_Au, int what, int e0, int e1);
 
 // One smoothing of a multigrid level on device vectors (cg_eigs estimate when asked,
 // Chebyshev sweeps, r = rhs - A u), enqueued without any host synchronisation; the estimate

@@ -278,6 +278,69 @@ extern "C" d4b_mesh_t *d4b_mesh_create(const d4b_mesh_desc_t *d) {
   D4B_CHECK(m->generic_smem <= 227 * 1024, "generic kernel needs %d bytes of shared memory", m->generic_smem);
   d4b_generic_configure(m->generic_smem);
 
+  // chunks of the pipelined host-pointer apply: one rank, every element in a Gauss-basis kernel, class
+  // lists in element order (no interior / halo split)
+  const int pipe_min = getenv("D4B_PIPELINE_MIN_ELEMS") ? atoi(getenv("D4B_PIPELINE_MIN_ELEMS")) : 4096;   // 0 = never
+  if (d->mpisize <= 1 && m->n_generic == 0 && pipe_min > 0 && E >= pipe_min) {
+    const int K = E >= 32 * 64 ? 32 : (E >= 64 ? 8 : 1);
+    m->chunk_elem.assign(K + 1, E);
+    m->chunk_elem[0] = 0;
+    for (int k = 1, e = 0; k < K; ++k) {
+      const int64_t target = d->local_nodes * k / K;
+      while (e < E && d->nodal_stride[e] < target) ++e;
+      m->chunk_elem[k] = e;
+    }
+    auto chunk_of = [&](int e) {
+      return (int)(std::upper_bound(m->chunk_elem.begin(), m->chunk_elem.end(), e) - m->chunk_elem.begin()) - 1;
+    };
+    // chunk adjacency through the flux sides
+    std::vector<std::vector<char>> adj(K, std::vector<char>(K, 0));
+    for (int s = 0; s < d->n_sides; ++s)
+      for (int i = 0; i < d->side_faces_m[s]; ++i) {
+        const int32_t em = d->side_e_m[4 * s + i];
+        if (em < 0) continue;
+        const int km = chunk_of(em);
+        for (int j = 0; j < d->side_faces_p[s]; ++j) {
+          const int32_t ep = d->side_e_p[4 * s + j];
+          if (ep >= 0) { const int kp = chunk_of(ep); adj[km][kp] = adj[kp][km] = 1; }
+        }
+      }
+    // transfer order: Cuthill-McKee on the chunk graph, so that a chunk's neighbours arrive soon after
+    // it (Morton order would make half the mesh wait for the far octant)
+    std::vector<int> degc(K, 0), order;
+    for (int a = 0; a < K; ++a)
+      for (int b = 0; b < K; ++b) degc[a] += (a != b && adj[a][b]);
+    std::vector<char> seen(K, 0);
+    while ((int)order.size() < K) {
+      int start = -1;
+      for (int a = 0; a < K; ++a)
+        if (!seen[a] && (start < 0 || degc[a] < degc[start])) start = a;
+      seen[start] = 1;
+      size_t head = order.size();
+      order.push_back(start);
+      while (head < order.size()) {
+        const int a = order[head++];
+        std::vector<int> nb;
+        for (int b = 0; b < K; ++b)
+          if (!seen[b] && adj[a][b]) nb.push_back(b);
+        std::stable_sort(nb.begin(), nb.end(), [&](int x, int y) { return degc[x] < degc[y]; });
+        for (int b : nb) { seen[b] = 1; order.push_back(b); }
+      }
+    }
+    std::vector<int> pos(K);
+    for (int i = 0; i < K; ++i) pos[order[i]] = i;
+    m->chunk_order.assign(order.begin(), order.end());
+    m->chunk_dep.resize(K);   // position in the transfer order after which chunk k can be applied
+    for (int k = 0; k < K; ++k) {
+      int dp = pos[k];
+      for (int b = 0; b < K; ++b)
+        if (adj[k][b]) dp = std::max(dp, pos[b]);
+      m->chunk_dep[k] = dp;
+    }
+    m->chunk_node.resize(K + 1);
+    for (int k = 0; k <= K; ++k)
+      m->chunk_node[k] = m->chunk_elem[k] < E ? d->nodal_stride[m->chunk_elem[k]] : d->local_nodes;
+  }
   m->d_u_stage = d4b_dev_alloc<double>(m, (size_t)d->local_nodes);
   m->d_Au_stage = d4b_dev_alloc<double>(m, (size_t)d->local_nodes);
   m->d_red = d4b_dev_alloc<double>(m, 4096);
@@ -305,6 +368,10 @@ extern "C" void d4b_mesh_destroy(d4b_mesh_t *m) {
       if (p) cudaFree(p);
   }
   if (m->h_red) cudaFreeHost(m->h_red);
+  for (cudaEvent_t ev : m->ev_h2d) cudaEventDestroy(ev);
+  for (cudaEvent_t ev : m->ev_done) cudaEventDestroy(ev);
+  if (m->h2d_stream) cudaStreamDestroy(m->h2d_stream);
+  if (m->d2h_stream) cudaStreamDestroy(m->d2h_stream);
   d4b_comm_teardown(m);
   if (m->own_stream) cudaStreamDestroy(m->stream);
   delete m;

@@ -186,3 +186,50 @@ def test_flat_kernel_all_degrees_against_oracle(p):
     ref = Oracle(A).apply(u)
     assert rel(au, ref) < 1e-12
     m.close()
+
+
+@pytest.mark.parametrize("case", ["brick_l2_p3", "sphere_p2", "sphere_p_amr1", "sphere_p_amr1_robin"])
+def test_pipelined_host_apply_equals_device_apply(golden, case, monkeypatch):
+    """host-pointer applies on one-rank meshes go up / down in chunks overlapped with the kernels
+    (apply_host_pipelined); forced onto the small fixtures here: bit-identical to the device-pointer apply"""
+    import torch
+
+    from disco4est_b200 import Mesh
+
+    A = golden(case)
+    monkeypatch.setenv("D4B_PIPELINE_MIN_ELEMS", "1")
+    m = Mesh(A)
+    monkeypatch.delenv("D4B_PIPELINE_MIN_ELEMS")
+    u = np.ascontiguousarray(A["u"])
+    a_host = np.full_like(u, np.nan)
+    m.apply(u, a_host)
+    m.apply(u, a_host)                       # events and staging are re-used
+    du = torch.from_numpy(u).cuda()
+    dAu = torch.empty_like(du)
+    m.apply(du, dAu)
+    m.sync()
+    assert np.array_equal(a_host, dAu.cpu().numpy())
+    assert rel(a_host, A["Au_plain"]) < TOL
+    m.close()
+
+
+def test_pipelined_host_apply_at_size():
+    """16^3 p=2 brick (above the default threshold): pinned and pageable host buffers"""
+    import torch
+
+    from disco4est_b200 import Mesh
+    from disco4est_b200.brick import brick_desc
+
+    m = Mesh(brick_desc(4, 2))
+    u = np.random.default_rng(1).standard_normal(m.n)
+    du = torch.from_numpy(u).cuda()
+    dAu = torch.empty_like(du)
+    m.apply(du, dAu)
+    m.sync()
+    ref = dAu.cpu().numpy()
+    a1 = np.zeros_like(u)
+    m.apply(u, a1)
+    pu, pa = torch.from_numpy(u).pin_memory(), torch.empty(m.n, dtype=torch.float64).pin_memory()
+    m.apply(pu.numpy(), pa.numpy())
+    assert np.array_equal(a1, ref) and np.array_equal(pa.numpy(), ref)
+    m.close()
