@@ -860,11 +860,14 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
       std::vector<int64_t> face_rec((size_t)6 * els.size()), face_nbr((size_t)6 * els.size(), -1);
       std::vector<int32_t> face_code((size_t)6 * els.size(), 0);
       std::vector<double> FG((size_t)6 * N3 * els.size());
+#pragma omp parallel for schedule(static)
       for (size_t i = 0; i < els.size(); ++i) {
-        const int e = els[i];
-        const int64_t qs = d->quad_stride[e];
+        const int64_t qs = d->quad_stride[els[i]];
         for (int cpl = 0; cpl < 6; ++cpl)
           for (int k = 0; k < N3; ++k) FG[(i * 6 + cpl) * N3 + k] = G[(size_t)cpl * LQ + qs + k];
+      }
+      for (size_t i = 0; i < els.size(); ++i) {
+        const int e = els[i];
         for (int f = 0; f < 6; ++f) {
           const int s = elem_side[6 * e + f];
           const size_t fi = 6 * i + f;

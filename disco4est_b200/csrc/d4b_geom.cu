@@ -15,7 +15,10 @@
 // the reference evaluates machine-generated closed forms of the same derivatives
 // (d4est_geometry_cubed_sphere.c:847-1370), so the two agree to round-off, not bit for bit.
 #include <algorithm>
+#include <chrono>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 #include "d4b_internal.h"
@@ -504,7 +507,12 @@ extern "C" d4b_mesh_t *d4b_mesh_create_with_geometry(const d4b_mesh_desc_t *topo
   out.sj_m_mortar_quad = sj.data(); out.n_m_mortar_quad = n.data();
   out.drst_dxyz_m_mortar_quad = drm.data(); out.drst_dxyz_p_mortar_quad_porder = drp.data();
   out.hm_mortar_quad = hm.data(); out.hp_mortar_quad = hp.data();
+  const bool timing = getenv("D4B_TIMING") && atoi(getenv("D4B_TIMING"));
+  auto t0 = std::chrono::steady_clock::now();
   d4b_geom_compute(topo, geom, &out);
+  if (timing)
+    fprintf(stderr, "[d4b_mesh_create_with_geometry] generate + copy to host %8.3f s\n",
+            std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count());
   d4b_mesh_desc_t d = *topo;
   d.J_quad = J.data(); d.rst_xyz_quad = rst.data();
   d.sj_m_mortar_quad = sj.data(); d.n_m_mortar_quad = n.data();

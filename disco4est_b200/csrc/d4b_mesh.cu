@@ -2,6 +2,7 @@
 // description (d4b_mesh_desc_t).  Runs once per mesh (after d4est_mesh_update,
 // src/Mesh/d4est_mesh.c:2790-2890); nothing here is on the per-apply path.
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -94,7 +95,21 @@ void build_tables(d4b_mesh *m) {
 
 }  // namespace
 
+namespace {
+struct PhaseTimer {   // D4B_TIMING=1: wall time of the set-up phases on stderr
+  bool on = getenv("D4B_TIMING") && atoi(getenv("D4B_TIMING"));
+  std::chrono::steady_clock::time_point t = std::chrono::steady_clock::now();
+  void lap(const char *what) {
+    if (!on) return;
+    auto n = std::chrono::steady_clock::now();
+    fprintf(stderr, "[d4b_mesh_create] %-28s %8.3f s\n", what, std::chrono::duration<double>(n - t).count());
+    t = n;
+  }
+};
+}  // namespace
+
 extern "C" d4b_mesh_t *d4b_mesh_create(const d4b_mesh_desc_t *d) {
+  PhaseTimer pt;
   D4B_CHECK(d != nullptr, "d4b_mesh_create: NULL description");
   D4B_CHECK(d->abi_version == D4B_ABI_VERSION, "d4b_mesh_create: ABI version %d, library has %d",
             d->abi_version, D4B_ABI_VERSION);
@@ -137,11 +152,17 @@ extern "C" d4b_mesh_t *d4b_mesh_create(const d4b_mesh_desc_t *d) {
   std::vector<double> G((size_t)6 * d->local_nodes_quad);
   {
     const int64_t LQ = d->local_nodes_quad;
-    std::vector<double> xg(D4B_MAXNQ), wg(D4B_MAXNQ);
-    int cur_q = -1;
+    // Gauss weights per quadrature degree, then one element per loop iteration (host threads)
+    std::vector<std::vector<double>> wgs(D4B_MAXNQ + 1);
+    for (int q = 1; q <= m->max_deg_quad; ++q) {
+      std::vector<double> xg(q + 1);
+      wgs[q].resize(q + 1);
+      d4b_tab_gauss(q + 1, xg.data(), wgs[q].data());
+    }
+#pragma omp parallel for schedule(static)
     for (int e = 0; e < E; ++e) {
       int q = d->deg_quad[e], nq = q + 1;
-      if (q != cur_q) { d4b_tab_gauss(nq, xg.data(), wg.data()); cur_q = q; }
+      const std::vector<double> &wg = wgs[q];
       int64_t qs = d->quad_stride[e];
       for (int k = 0; k < nq * nq * nq; ++k) {
         int a = k % nq, b = (k / nq) % nq, c = k / (nq * nq);
@@ -160,6 +181,7 @@ extern "C" d4b_mesh_t *d4b_mesh_create(const d4b_mesh_desc_t *d) {
     m->d_G = d4b_dev_upload<double>(m, G.data(), G.size());
   }
 
+  pt.lap("tables, volume metric fold");
   // ---- element-face -> side record
   std::vector<int32_t> elem_side((size_t)6 * E, -1), elem_sub((size_t)6 * E, 0);
   for (int s = 0; s < d->n_sides; ++s) {
@@ -182,6 +204,7 @@ extern "C" d4b_mesh_t *d4b_mesh_create(const d4b_mesh_desc_t *d) {
   std::vector<double> mortar((size_t)8 * MP, 0.);
   auto degq_of = [&](int32_t r) { return r >= 0 ? d->deg_quad[r] : d->ghost_deg_quad[-r - 1]; };
   auto deg_of = [&](int32_t r) { return r >= 0 ? d->deg[r] : d->ghost_deg[-r - 1]; };
+#pragma omp parallel for schedule(static)
   for (int s = 0; s < d->n_sides; ++s) {
     int faces_m = d->side_faces_m[s], faces_p = d->side_faces_p[s], perm = d->side_perm[s];
     int M = std::max(faces_m, faces_p);
@@ -246,6 +269,7 @@ extern "C" d4b_mesh_t *d4b_mesh_create(const d4b_mesh_desc_t *d) {
     }
   }
 
+  pt.lap("mortar fold");
   m->d_side_faces_m = d4b_dev_upload<int32_t>(m, d->side_faces_m, d->n_sides);
   m->d_side_faces_p = d4b_dev_upload<int32_t>(m, d->side_faces_p, d->n_sides);
   m->d_side_f_m = d4b_dev_upload<int32_t>(m, d->side_f_m, d->n_sides);
@@ -261,6 +285,7 @@ extern "C" d4b_mesh_t *d4b_mesh_create(const d4b_mesh_desc_t *d) {
   std::vector<char> is_fast(E, 0);
   const char *force = getenv("D4B_FORCE_GENERIC");
   if (!(force && force[0] == '1')) d4b_fast_setup(m, d, mortar, G, elem_side, is_fast);
+  pt.lap("kernel classes, face records");
   std::vector<int32_t> generic;
   for (int e = 0; e < E; ++e)
     if (!is_fast[e]) generic.push_back(e);
@@ -341,6 +366,7 @@ extern "C" d4b_mesh_t *d4b_mesh_create(const d4b_mesh_desc_t *d) {
     for (int k = 0; k <= K; ++k)
       m->chunk_node[k] = m->chunk_elem[k] < E ? d->nodal_stride[m->chunk_elem[k]] : d->local_nodes;
   }
+  pt.lap("uploads, transfer chunks");
   m->d_u_stage = d4b_dev_alloc<double>(m, (size_t)d->local_nodes);
   m->d_Au_stage = d4b_dev_alloc<double>(m, (size_t)d->local_nodes);
   m->d_red = d4b_dev_alloc<double>(m, 4096);
