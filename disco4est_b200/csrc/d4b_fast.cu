@@ -762,7 +762,7 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
 
   // ---- face records, one per face, shared by both sides when consistent
   std::vector<double> FF, FF3;
-  std::map<int64_t, int64_t> rec_of, rec3_of;   // key of the owning (element, face) -> record
+  std::vector<int64_t> rec_of((size_t)6 * E, -1), rec3_of((size_t)6 * E, -1);   // owning (element, face) -> record
   auto write_record = [&](int s, int NN, bool boundary) -> int64_t {
     int64_t off = (int64_t)FF.size();
     FF.resize(FF.size() + (size_t)7 * NN);
@@ -887,17 +887,15 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
           face_nbr[fi] = d->nodal_stride[ep];
           const int64_t mykey = (int64_t)e * 6 + f, okey = (int64_t)ep * 6 + fp;
           const int s2 = elem_side[6 * ep + fp];
-          std::map<int64_t, int64_t> &recs = kind ? rec3_of : rec_of;
+          std::vector<int64_t> &recs = kind ? rec3_of : rec_of;
           bool i_own = mykey < okey;
           int64_t off;
           if (i_own) {
-            auto it = recs.find(mykey);
-            off = (it != recs.end()) ? it->second
-                                     : (recs[mykey] = kind ? write_record3(s, NN, false) : write_record(s, NN, false));
+            if (recs[mykey] < 0) recs[mykey] = kind ? write_record3(s, NN, false) : write_record(s, NN, false);
+            off = recs[mykey];
           } else if (consistent(s, s2, N, perm)) {
-            auto it = recs.find(okey);
-            off = (it != recs.end()) ? it->second
-                                     : (recs[okey] = kind ? write_record3(s2, NN, false) : write_record(s2, NN, false));
+            if (recs[okey] < 0) recs[okey] = kind ? write_record3(s2, NN, false) : write_record(s2, NN, false);
+            off = recs[okey];
             ++n_shared;
           } else {
             off = kind ? write_record3(s, NN, false) : write_record(s, NN, false);
