@@ -88,6 +88,8 @@ struct FastArgs {
   const double *W;              // MASS kernels: weighted diagonal at the quadrature points (d4b_mesh_set_mass_diag)
   const int64_t *quad_stride;
   int prefetch;                 // L2 prefetch of the block's volume metric and face records at kernel start
+  const unsigned char *has_extra;   // face split, see FlatArgs
+  const double *extra;
 };
 
 // Placement of the N^3 block in shared memory for the three line orientations: an XOR swizzle for
@@ -321,9 +323,11 @@ __global__ void __launch_bounds__(CurvedCfg<N>::THREADS, CurvedCfg<N>::MIN_BLOCK
     }
     // mass-type diagonal: in the Gauss basis V^T diag(W) V u is point-wise, r += W uh
     const double *Wd = MASS ? a.W + a.quad_stride[a.elem[ei]] + lt : nullptr;
+    const double *xtr = (a.has_extra && a.has_extra[ei]) ? a.extra + ns + lt : nullptr;
 #pragma unroll
     for (int c = 0; c < N; ++c) {
       double s = MASS ? Wd[NN * c] * V0[vix<N>(lx, ly, c)] : 0.;
+      if (xtr) s += xtr[NN * c];
 #pragma unroll
       for (int i = 0; i < N; ++i) s += T.Dg[i][c] * ft[i];
       V0[vix<N>(lx, ly, c)] = s;
@@ -534,6 +538,7 @@ void launch_flat(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, 
   a.uh = m->d_uhat; a.Au = d_Au; a.epi = m->epi;
   size_t smem = (size_t)C::EPB * C::SH_PER_ELEM * sizeof(double);
   a.W = m->d_W; a.quad_stride = m->d_quad_stride;
+  a.has_extra = cls.d_has_extra; a.extra = m->d_extra;
   static bool configured = false;
   if (!configured) {
     D4B_CUDA(cudaFuncSetAttribute(flat_apply_kernel<N, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -550,7 +555,7 @@ void launch_flat(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, 
 #include "d4b_hp_kernel.cuh"
 
 template <int N>
-void launch_hp(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, int last) {
+void launch_hp(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, int last, bool face_only = false) {
   if (last <= first) return;
   HpArgs a;
   a.elem = cls.d_elem; a.first = first; a.n_elem = last;
@@ -578,7 +583,15 @@ void launch_hp(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, in
     configured = smem;
   }
   const int grid = (last - first + warps - 1) / warps;
-  if (m->d_W) hp_apply_kernel<N, true><<<grid, 32 * warps, smem, m->stream>>>(a);
+  a.face_mask = cls.d_face_mask; a.extra = m->d_extra;
+  if (face_only) {
+    static size_t configured_f = 48 * 1024;
+    if (smem > configured_f) {
+      D4B_CUDA(cudaFuncSetAttribute(hp_apply_kernel<N, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      configured_f = smem;
+    }
+    hp_apply_kernel<N, false, true><<<grid, 32 * warps, smem, m->stream>>>(a);
+  } else if (m->d_W) hp_apply_kernel<N, true><<<grid, 32 * warps, smem, m->stream>>>(a);
   else hp_apply_kernel<N, false><<<grid, 32 * warps, smem, m->stream>>>(a);
   D4B_CUDA(cudaGetLastError());
 }
@@ -637,6 +650,7 @@ void launch_fast(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, 
   a.uh = m->d_uhat; a.Au = d_Au; a.epi = m->epi;
   size_t smem = (size_t)C::EPB * C::SH_PER_ELEM * sizeof(double);
   a.W = m->d_W; a.quad_stride = m->d_quad_stride;
+  a.has_extra = cls.d_has_extra; a.extra = m->d_extra;
   static bool configured = false;
   if (!configured) {
     D4B_CUDA(cudaFuncSetAttribute(fast_apply_kernel<N, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

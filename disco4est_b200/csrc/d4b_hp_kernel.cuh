@@ -49,6 +49,10 @@ struct HpArgs {
   const double *tabdata;
   int mM;                      // largest Gauss count per direction on any mortar of the mesh
   int smem_doubles;            // shared doubles per warp
+  // FACE_ONLY launches (face split): bit f of face_mask[class position] = face f is irregular;
+  // their Gauss-basis contributions go to extra[nodal_stride + k] instead of Au
+  const unsigned char *face_mask;
+  double *extra;
 };
 
 template <int N>
@@ -126,7 +130,9 @@ __device__ __forceinline__ void hp_project4(double *out, int ostride, const doub
   __syncwarp();
 }
 
-template <int N, bool MASS>
+// FACE_ONLY: the face split of DESIGN.md 4b -- only the faces in face_mask, no volume term, no
+// back-transform: the conforming kernels add the result to their accumulator.
+template <int N, bool MASS, bool FACE_ONLY = false>
 __global__ void __launch_bounds__(128) hp_apply_kernel(HpArgs a) {
   constexpr int NN = N * N, N3 = N * N * N;
   extern __shared__ double smem[];
@@ -211,8 +217,12 @@ __global__ void __launch_bounds__(128) hp_apply_kernel(HpArgs a) {
     FT[(1 * 2 + 0) * NN + lt] = t1; FT[(1 * 2 + 1) * NN + lt] = n1;
   }
   __syncwarp();
+  if (FACE_ONLY) {
+    for (int k = lane; k < N3; k += 32) V0[k] = 0.;
+    __syncwarp();
+  }
   // ---- stiffness metric, point-wise; V0 becomes the residual accumulator
-  {
+  if (!FACE_ONLY) {
     const double *G = a.G + a.quad_stride[e];
     const double *Wd = MASS ? a.W + a.quad_stride[e] : nullptr;
     for (int k = lane; k < N3; k += 32) {
@@ -226,6 +236,7 @@ __global__ void __launch_bounds__(128) hp_apply_kernel(HpArgs a) {
     }
   }
   __syncwarp();
+  if (!FACE_ONLY) {
   // ---- r += Dg^T F along c, b, a
   for (int lt = lane; lt < NN; lt += 32) {
     double f[N];
@@ -269,9 +280,12 @@ __global__ void __launch_bounds__(128) hp_apply_kernel(HpArgs a) {
   }
   __syncwarp();
 
+  }
+
   // ---- faces
 #pragma unroll 1
   for (int f = 0; f < 6; ++f) {
+    if (FACE_ONLY && !((a.face_mask[slot] >> f) & 1)) continue;
     const int nd = f >> 1, sd = f & 1;
     const int s = a.elem_side[6 * e + f], my = a.elem_sub[6 * e + f];
     const int faces_m = a.side_faces_m[s], faces_p = a.side_faces_p[s];
@@ -433,6 +447,10 @@ __global__ void __launch_bounds__(128) hp_apply_kernel(HpArgs a) {
     __syncwarp();
   }
 
+  if (FACE_ONLY) {
+    for (int k = lane; k < N3; k += 32) a.extra[ns + k] = V0[k];
+  }
+  if (!FACE_ONLY) {
   // ---- back to the LGL basis: I^T along a, b, c
   for (int lt = lane; lt < NN; lt += 32) {
     double l[N];
@@ -477,5 +495,6 @@ __global__ void __launch_bounds__(128) hp_apply_kernel(HpArgs a) {
         store_result(a.epi, ec, a.Au, ns + lt + NN * c, s);
       }
     }
+  }
   }
 }

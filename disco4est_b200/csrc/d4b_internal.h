@@ -56,8 +56,12 @@ struct D4bFastClass {
   int32_t *d_face_code = nullptr;
   std::vector<int32_t> h_elem, h_hat;   // host copies of d_elem / d_hat_elem (chunked host-pointer applies)
   int kind = 0;                  // 0: general conforming kernel, 1: tangential-free faces (d4b_flat_kernel.cuh),
-                                 // 2: hp mortar kernel (d4b_hp_kernel.cuh)
+                                 // 2: hp mortar kernel (d4b_hp_kernel.cuh), 3: its FACE_ONLY form (face split)
   void *d_face_meta = nullptr;   // kind 1: [6*n_elem] packed face descriptors
+  // face split: kinds 0/1: per class position, 1 = the element has irregular faces whose contributions
+  // arrive in m->d_extra; kind 3 (face class): per class position the 6-bit mask of those faces
+  unsigned char *d_has_extra = nullptr;
+  unsigned char *d_face_mask = nullptr;
 };
 
 // what the fast kernels do with a finished value s = (A u)[i] (fused smoother,
@@ -157,6 +161,7 @@ struct d4b_mesh {
   double *d_flat_FF = nullptr;         // compact face records [3][N^2] of the tangential-free class
   int64_t n_flat_elem = 0;
   int64_t n_hp_elem = 0;               // elements of the mortar kernel (d4b_hp_kernel.cuh)
+  double *d_extra = nullptr;           // face split: Gauss-basis contributions of irregular faces, nodal layout
   void *d_hp_tabs = nullptr;           // its table offsets / data
   double *d_hp_tabdata = nullptr;
   int64_t n_face_shared = 0, n_face_split = 0;
