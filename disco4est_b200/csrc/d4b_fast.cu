@@ -736,17 +736,49 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
   auto collocated = [&](int32_t r) {
     return r >= 0 ? d->deg_quad[r] == d->deg[r] : d->ghost_deg_quad[-r - 1] == d->ghost_deg[-r - 1];
   };
-  bool any_hp = false;
+  // Face split: such an element runs in the conforming kernels with its irregular faces
+  // switched off (an all-zero boundary record) and a FACE_ONLY launch of the mortar kernel supplies those
+  // faces' contributions through m->d_extra; split_mask[e] = the irregular faces.
+  std::vector<unsigned char> split_mask(E, 0);
+  std::vector<std::vector<int32_t>> split_by_deg(D4B_MAX_DEG + 1);
+  std::vector<int32_t> eligible;
+  int64_t n_irregular_faces = 0;
   for (int e = 0; e < E && allow_hp; ++e) {
     if (is_fast[e] || d->deg_quad[e] != d->deg[e]) continue;
     bool ok = true;
+    unsigned mask = 0;
     for (int f = 0; f < 6 && ok; ++f) {
       const int s = elem_side[6 * e + f];
       for (int i = 0; i < d->side_faces_m[s] && ok; ++i) ok = collocated(d->side_e_m[4 * s + i]);
       for (int i = 0; i < d->side_faces_p[s] && ok; ++i) ok = collocated(d->side_e_p[4 * s + i]);
+      bool regular = d->side_faces_m[s] == 1 && d->side_faces_p[s] <= 1;
+      if (regular && d->side_faces_p[s] == 1) {
+        const int32_t ep = d->side_e_p[4 * s];
+        regular = (ep >= 0 ? d->deg[ep] : d->ghost_deg[-ep - 1]) == d->deg[e];
+      }
+      if (!regular) { mask |= 1u << f; ++n_irregular_faces; }
     }
-    if (ok) { is_fast[e] = 1; hp_by_deg[d->deg[e]].push_back(e); any_hp = true; }
+    if (!ok) continue;
+    is_fast[e] = 1;
+    split_mask[e] = (unsigned char)mask;
+    eligible.push_back(e);
   }
+  const bool any_hp = !eligible.empty();
+  // element-wise mortar kernel or face split?  The split pays when an irregular element has few irregular
+  // faces (AMR interfaces: one or two); with most faces irregular it would process the element twice.
+  // D4B_SPLIT=0/1 overrides.
+  bool split = any_hp && n_irregular_faces <= (int64_t)(2.5 * (double)eligible.size());
+  if (getenv("D4B_SPLIT")) split = any_hp && atoi(getenv("D4B_SPLIT")) != 0;
+  for (int e : eligible) {
+    if (split) split_by_deg[d->deg[e]].push_back(e);
+    else { hp_by_deg[d->deg[e]].push_back(e); split_mask[e] = 0; }
+  }
+  if (split)
+    for (int p = 1; p <= D4B_MAX_DEG; ++p) {
+      std::vector<int32_t> merged(by_deg[p].size() + split_by_deg[p].size());
+      std::merge(by_deg[p].begin(), by_deg[p].end(), split_by_deg[p].begin(), split_by_deg[p].end(), merged.begin());
+      by_deg[p].swap(merged);
+    }
   bool any = any_hp;
   for (int p = 1; p <= D4B_MAX_DEG; ++p) any = any || !by_deg[p].empty();
   if (!any) return;
@@ -836,14 +868,16 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
     std::vector<int32_t> els_kind[2];
     for (int e : by_deg[p]) {
       bool flat = allow_flat;
-      for (int f = 0; f < 6 && flat; ++f) flat = face_is_flat(elem_side[6 * e + f], NN);
+      for (int f = 0; f < 6 && flat; ++f)
+        if (!((split_mask[e] >> f) & 1)) flat = face_is_flat(elem_side[6 * e + f], NN);
       els_kind[flat ? 1 : 0].push_back(e);
     }
     // elements without a ghost neighbour first: they run while the halo is in flight
     auto touches_ghost = [&](int e) {
       for (int f = 0; f < 6; ++f) {
         const int s = elem_side[6 * e + f];
-        if (d->side_faces_p[s] == 1 && d->side_e_p[4 * s] < 0) return true;
+        for (int i = 0; i < d->side_faces_m[s]; ++i) if (d->side_e_m[4 * s + i] < 0) return true;
+        for (int i = 0; i < d->side_faces_p[s]; ++i) if (d->side_e_p[4 * s + i] < 0) return true;
       }
       return false;
     };
@@ -855,6 +889,38 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
     }
     const std::vector<int32_t> &ghost_hat = ghost_hat_p;
     bool hat_done = false;
+    // compact records are addressed by index * 3 NN: keep the array a multiple of this degree's record
+    while (FF3.size() % ((size_t)3 * NN)) FF3.push_back(0.);
+    int64_t zero7 = -1, zero3 = -1;   // all-zero records that switch a face off
+    if (!split_by_deg[p].empty()) {
+      zero7 = (int64_t)FF.size();
+      FF.resize(FF.size() + (size_t)7 * NN, 0.);
+      zero3 = (int64_t)(FF3.size() / ((size_t)3 * NN));
+      FF3.resize(FF3.size() + (size_t)3 * NN, 0.);
+      // the FACE_ONLY class runs before this degree's conforming classes (same stream)
+      std::vector<int32_t> els = split_by_deg[p];
+      auto mid = std::stable_partition(els.begin(), els.end(), [&](int e) { return !touches_ghost(e); });
+      std::vector<unsigned char> masks(els.size());
+      for (size_t i = 0; i < els.size(); ++i) masks[i] = split_mask[els[i]];
+      D4bFastClass c;
+      c.deg = p;
+      c.kind = 3;
+      c.n_hat = (int)hat_by_deg[p].size();
+      c.d_hat_elem = d4b_dev_upload<int32_t>(m, hat_by_deg[p].data(), hat_by_deg[p].size());
+      c.h_hat = hat_by_deg[p];
+      c.n_ghost_hat = (int)ghost_hat.size();
+      c.d_ghost_hat = d4b_dev_upload<int32_t>(m, ghost_hat.data(), ghost_hat.size());
+      hat_done = true;
+      c.n_elem = (int)els.size();
+      c.n_interior = (int)(mid - els.begin());
+      c.d_elem = d4b_dev_upload<int32_t>(m, els.data(), els.size());
+      c.h_elem = els;
+      D4B_CUDA(cudaMalloc(&c.d_face_mask, masks.size()));
+      D4B_CUDA(cudaMemcpy(c.d_face_mask, masks.data(), masks.size(), cudaMemcpyHostToDevice));
+      m->n_hp_elem += c.n_elem;
+      if (!m->d_extra) m->d_extra = d4b_dev_alloc<double>(m, (size_t)d->local_nodes);
+      m->fast.push_back(c);
+    }
     for (int kind = 0; kind < 2; ++kind) {
       const std::vector<int32_t> &els = els_kind[kind];
       if (els.empty()) continue;
@@ -880,11 +946,20 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
         for (int cpl = 0; cpl < 6; ++cpl)
           for (int k = 0; k < N3; ++k) FG[(i * 6 + cpl) * N3 + k] = G[(size_t)cpl * LQ + qs + k];
       }
+      std::vector<unsigned char> has_extra(els.size(), 0);
+      bool any_extra = false;
       for (size_t i = 0; i < els.size(); ++i) {
         const int e = els[i];
+        has_extra[i] = split_mask[e] != 0;
+        any_extra = any_extra || has_extra[i];
         for (int f = 0; f < 6; ++f) {
           const int s = elem_side[6 * e + f];
           const size_t fi = 6 * i + f;
+          if ((split_mask[e] >> f) & 1) {   // irregular face: off here, supplied by the FACE_ONLY launch
+            face_rec[fi] = kind ? zero3 : zero7;
+            face_code[fi] = kOwn;
+            continue;
+          }
           if (d->side_faces_p[s] == 0) {
             face_rec[fi] = kind ? write_record3(s, NN, true) : write_record(s, NN, true);
             face_code[fi] = kOwn;
@@ -922,6 +997,10 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
       }
       c.d_elem = d4b_dev_upload<int32_t>(m, els.data(), els.size());
       c.h_elem = els;
+      if (any_extra) {
+        D4B_CUDA(cudaMalloc(&c.d_has_extra, has_extra.size()));
+        D4B_CUDA(cudaMemcpy(c.d_has_extra, has_extra.data(), has_extra.size(), cudaMemcpyHostToDevice));
+      }
       c.d_FG = d4b_dev_upload<double>(m, FG.data(), FG.size());
       if (kind == 0) {
         c.d_face_rec = d4b_dev_upload<int64_t>(m, face_rec.data(), face_rec.size());
@@ -986,7 +1065,7 @@ void d4b_launch_fast_range(d4b_mesh *m, const double *d_u, double *d_Au, int wha
     if (hi <= lo) continue;
 #define D4B_CASE(n) case n: \
       if (what == 0) launch_interp_range<n>(m, c, d_u, lo, hi); \
-      else if (c.kind == 2) launch_hp<n>(m, c, d_Au, lo, hi); \
+      else if (c.kind >= 2) launch_hp<n>(m, c, d_Au, lo, hi, c.kind == 3); \
       else if (c.kind) launch_flat<n>(m, c, d_Au, lo, hi); \
       else launch_fast<n>(m, c, d_Au, lo, hi); \
       break;
@@ -1016,7 +1095,7 @@ void d4b_launch_fast(d4b_mesh *m, const double *d_u, double *d_Au, int part) {
   if (part == 0) return;
   for (const D4bFastClass &c : m->fast) {
     const int first = part == 1 ? 0 : c.n_interior, last = part == 1 ? c.n_interior : c.n_elem;
-#define D4B_CASE(n) case n: if (c.kind == 2) launch_hp<n>(m, c, d_Au, first, last); else if (c.kind) launch_flat<n>(m, c, d_Au, first, last); else launch_fast<n>(m, c, d_Au, first, last); break;
+#define D4B_CASE(n) case n: if (c.kind >= 2) launch_hp<n>(m, c, d_Au, first, last, c.kind == 3); else if (c.kind) launch_flat<n>(m, c, d_Au, first, last); else launch_fast<n>(m, c, d_Au, first, last); break;
     switch (c.deg + 1) {
       D4B_CASE(2) D4B_CASE(3) D4B_CASE(4) D4B_CASE(5) D4B_CASE(6) D4B_CASE(7) D4B_CASE(8)
       default: D4B_ABORT("fast path: unsupported degree %d", c.deg);

@@ -233,3 +233,43 @@ def test_pipelined_host_apply_at_size():
     m.apply(pu.numpy(), pa.numpy())
     assert np.array_equal(a1, ref) and np.array_equal(pa.numpy(), ref)
     m.close()
+
+
+@pytest.mark.parametrize("case", ["sphere_p_amr1", "sphere_p_amr1_robin"])
+def test_face_split_equals_mortar_kernel(golden, case, monkeypatch):
+    """face split: irregular elements run in the conforming kernels with their irregular faces supplied by a
+    FACE_ONLY launch of the mortar kernel; same operator as the element-wise mortar kernel and the reference"""
+    from disco4est_b200 import Mesh
+
+    A = golden(case)
+    u = np.ascontiguousarray(A["u"])
+    monkeypatch.setenv("D4B_SPLIT", "1")
+    m1 = Mesh(A)
+    monkeypatch.setenv("D4B_SPLIT", "0")
+    m2 = Mesh(A)
+    monkeypatch.delenv("D4B_SPLIT")
+    assert m1.hp_elements() == m2.hp_elements() > 0
+    a1, a2 = np.zeros_like(u), np.zeros_like(u)
+    m1.apply(u, a1); m2.apply(u, a2)
+    m1.close(); m2.close()
+    assert rel(a1, a2) < 1e-13
+    assert rel(a1, A["Au_plain"]) < TOL
+
+
+@pytest.mark.parametrize("kw", [dict(pmax=2), dict(pmax=4), dict(p=3, graded=True)])
+def test_face_split_on_synthetic_spheres(kw, monkeypatch):
+    from disco4est_b200 import Mesh
+    from disco4est_b200.sphere import sphere_desc
+
+    B, g = sphere_desc(3, **kw)
+    u = np.random.default_rng(2).standard_normal(int(B["local_nodes"]))
+    out = []
+    for flag in ("1", "0"):
+        monkeypatch.setenv("D4B_SPLIT", flag)
+        m = Mesh(B, geom=g)
+        a = np.zeros_like(u)
+        m.apply(u, a)
+        m.close()
+        out.append(a)
+    monkeypatch.delenv("D4B_SPLIT")
+    assert rel(out[0], out[1]) < 1e-13

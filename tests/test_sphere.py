@@ -100,7 +100,7 @@ def test_operator_matches_oracle(kw):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("kw", [dict(p=3), dict(pmax=4)])
+@pytest.mark.parametrize("kw", [dict(p=3), dict(pmax=4), dict(pmax=2)])
 def test_properties_at_depth(kw):
     """level 3 (6656 elements): symmetry of the operator, linearity, the kernels agree"""
     import os
