@@ -283,6 +283,7 @@ def bench_sphere(args, rank, world, local_rank, torch, dist, dev):
         t = float(tt[0])
         out[name] = {"GDOF_per_s": total_dof / t / 1e9, "ms_per_apply": 1e3 * t, "level": lvl, "elements": E,
                      "dof": total_dof, "fast_kernel_elements_rank0": mesh.fast_elements(),
+                     "hp_irregular_elements_rank0": mesh.hp_elements(),
                      "flat_kernel_elements_rank0": mesh.flat_elements(),
                      "launches_per_apply": mesh.launches_per_apply(),
                      "frac_of_hbm_roofline": total_dof * algorithmic_bytes_per_dof(args.deg) / t / 1e9 / world / measured_peak()[0]
