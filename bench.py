@@ -292,6 +292,50 @@ def bench_sphere(args, rank, world, local_rank, torch, dist, dev):
                      "checksum_Au": float(Au.sum())}
         mesh.close()
         del u, Au
+    # BASELINE configs[0] in synthetic form: what one AMR step leaves behind -- the unit cube at --level with one
+    # octant refined once more (hanging faces on three interface planes), uniform degree
+    from disco4est_b200.brick import brick_amr_desc
+    t0 = time.perf_counter()
+    A, g = brick_amr_desc(args.level, args.deg)
+    E, total_dof = int(A["n_local"]), int(A["local_nodes"])
+    if world > 1:
+        B = partition_desc(A, rank, world)
+        g = partition_geom(g, B, rank, world, E)
+        A = B
+    t1 = time.perf_counter()
+    mesh = Mesh(A, device=local_rank, geom=g)
+    t2 = time.perf_counter()
+    del A, g
+    stream = torch.cuda.current_stream()
+    mesh.set_stream(stream.cuda_stream)
+    u = torch.rand(mesh.n, dtype=torch.float64, device=dev, generator=torch.Generator(device=dev).manual_seed(77 + rank))
+    Au = torch.empty_like(u)
+    for _ in range(3):
+        mesh.apply(u, Au)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    steps = max(args.steps // 2, 5)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(stream)
+    for _ in range(steps):
+        mesh.apply(u, Au)
+    ev1.record(stream)
+    torch.cuda.synchronize()
+    tt = torch.tensor([ev0.elapsed_time(ev1) * 1e-3 / steps], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    t = float(tt[0])
+    out["amr_brick"] = {"GDOF_per_s": total_dof / t / 1e9, "ms_per_apply": 1e3 * t, "base_level": args.level,
+                        "elements": E, "dof": total_dof, "hp_irregular_elements_rank0": mesh.hp_elements(),
+                        "flat_kernel_elements_rank0": mesh.flat_elements(),
+                        "launches_per_apply": mesh.launches_per_apply(),
+                        "setup_s": {"topology_numpy": t1 - t0, "device_geometry_and_mesh": t2 - t1},
+                        "workload": "unit cube, %d^3 elements with the octant [0,1/2]^3 refined once (hanging faces), p=%d, "
+                                    "face_h = volume/area, geometric factors generated on the device" % (1 << args.level, args.deg),
+                        "checksum_Au": float(Au.sum())}
+    mesh.close()
+    del u, Au
     out["scaling"] = "strong (fixed mesh split over the ranks)"
     out["workload"] = ("13-tree cubed sphere R = 1, 2, 3, SIPG prefactor 2 maxp_sqr_over_minh, face_h = J/sj, "
                        "deg_quad = deg, geometric factors generated on the device")

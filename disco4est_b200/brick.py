@@ -222,3 +222,99 @@ def brick_hierarchy(level, p, rank=0, world=1, trees=(1, 1, 1), **kw):
         E = descs[l]["n_local"]
         transfers.append((8 * np.arange(E, dtype=np.int32), np.full(E, 8, np.int32)))
     return descs, transfers
+
+
+def brick_amr_desc(level, p, prefactor=2.0, penalty_fcn=0, face_h_type="volume_div_area"):
+    """(topology, geom) of the unit cube refined uniformly to `level` with the octant [0,1/2]^3 refined once
+    more: a 2:1-balanced forest with hanging faces on the three interface planes, the kind of mesh one AMR
+    step of the reference produces (ConstantDensityStar driver, BASELINE.json configs[0]).  Elements in
+    Morton order like p4est (the refined octant is Morton-contiguous and comes first); flux side records as
+    the reference's face iteration emits them (src/Mesh/d4est_mortars.c:601-802): one per (element, face)
+    on conforming faces, one (1 -> 4) per coarse element and one (4 -> 1) per group of four fine elements
+    on hanging faces.  Geometric factors come from the device generator (Mesh(topology, geom=geom))."""
+    n = 1 << level                      # coarse cells per direction
+    nh = n // 2
+    root = 1 << 30
+    N2 = (p + 1) ** 2
+    n3 = (p + 1) ** 3
+    # --- elements: fine block (level + 1, coordinates in [0, n)^3 of the 2n grid), then the coarse rest
+    nf = n ** 3
+    fx, fy, fz = morton_decode(np.arange(nf, dtype=np.int64))
+    mc = np.arange(n ** 3 // 8, n ** 3, dtype=np.int64)
+    cx, cy, cz = morton_decode(mc)
+    ncz = mc.size
+    E = nf + ncz
+    fine_id = lambda x, y, z: morton_encode(x, y, z)
+    coarse_id = lambda x, y, z: nf + morton_encode(x, y, z) - n ** 3 // 8
+    sides = {k: [] for k in ("faces_m", "faces_p", "f_m", "f_p", "e_m", "e_p")}
+
+    def add(faces_m, faces_p, f_m, f_p, e_m, e_p):
+        k = len(f_m)
+        pad = np.full((k, 4), np.iinfo(np.int32).min, np.int64)
+        em, ep = pad.copy(), pad.copy()
+        em[:, :e_m.shape[1]] = e_m
+        if e_p is not None:
+            ep[:, :e_p.shape[1]] = e_p
+        sides["faces_m"].append(np.full(k, faces_m)); sides["faces_p"].append(np.full(k, faces_p))
+        sides["f_m"].append(f_m); sides["f_p"].append(f_p)
+        sides["e_m"].append(em); sides["e_p"].append(ep)
+
+    tang = {0: (1, 2), 1: (0, 2), 2: (0, 1)}
+    for f in range(6):
+        d, sg = f // 2, (1 if f % 2 else -1)
+        ta, tb = tang[d]
+        # fine cells: neighbour at the same level inside the block, domain boundary, or the coarse cell behind
+        c = np.stack([fx, fy, fz]); nb = c.copy(); nb[d] += sg
+        ids = np.arange(nf)
+        inside = (nb[d] >= 0) & (nb[d] < n)
+        add(1, 1, np.full(inside.sum(), f), np.full(inside.sum(), f ^ 1), ids[inside][:, None],
+            fine_id(nb[0][inside], nb[1][inside], nb[2][inside])[:, None])
+        bnd = nb[d] < 0
+        add(1, 0, np.full(bnd.sum(), f), np.full(bnd.sum(), -1), ids[bnd][:, None], None)
+        if sg > 0:   # + face on the interface plane: groups of four fine cells against one coarse cell
+            lead = (nb[d] >= n) & (c[ta] % 2 == 0) & (c[tb] % 2 == 0)
+            g = c[:, lead]
+            grp = []
+            for i in range(4):
+                q = g.copy(); q[ta] += i & 1; q[tb] += i >> 1
+                grp.append(fine_id(q[0], q[1], q[2]))
+            cc = g // 2; cc[d] = nh
+            add(4, 1, np.full(lead.sum(), f), np.full(lead.sum(), f ^ 1), np.stack(grp, axis=1),
+                coarse_id(cc[0], cc[1], cc[2])[:, None])
+        # coarse cells
+        c = np.stack([cx, cy, cz]); nb = c.copy(); nb[d] += sg
+        ids = nf + np.arange(ncz)
+        bnd = (nb[d] < 0) | (nb[d] >= n)
+        add(1, 0, np.full(bnd.sum(), f), np.full(bnd.sum(), -1), ids[bnd][:, None], None)
+        into_fine = ~bnd & (nb[0] < nh) & (nb[1] < nh) & (nb[2] < nh)
+        same = ~bnd & ~into_fine
+        add(1, 1, np.full(same.sum(), f), np.full(same.sum(), f ^ 1), ids[same][:, None],
+            coarse_id(nb[0][same], nb[1][same], nb[2][same])[:, None])
+        g = 2 * nb[:, into_fine]
+        g[d] = n - 1                                  # only reached with sg < 0: the fine layer below the plane
+        grp = []
+        for i in range(4):
+            q = g.copy(); q[ta] += i & 1; q[tb] += i >> 1
+            grp.append(fine_id(q[0], q[1], q[2]))
+        add(1, 4, np.full(into_fine.sum(), f), np.full(into_fine.sum(), f ^ 1), ids[into_fine][:, None],
+            np.stack(grp, axis=1) if into_fine.any() else np.zeros((0, 4), np.int64))
+    cat = {k: np.concatenate(v) for k, v in sides.items()}
+    S = cat["f_m"].size
+    mort = np.maximum(cat["faces_m"], cat["faces_p"]).astype(np.int64)
+    A = {"n_local": E, "n_ghost": 0, "n_sides": S, "local_nodes": E * n3, "local_nodes_quad": E * n3, "ghost_nodes": 0,
+         "deg": np.full(E, p, np.int32), "deg_quad": np.full(E, p, np.int32),
+         "nodal_stride": np.arange(E, dtype=np.int64) * n3, "quad_stride": np.arange(E, dtype=np.int64) * n3,
+         "side_faces_m": cat["faces_m"].astype(np.int32), "side_faces_p": cat["faces_p"].astype(np.int32),
+         "side_f_m": cat["f_m"].astype(np.int32), "side_f_p": cat["f_p"].astype(np.int32),
+         "side_e_m": cat["e_m"].astype(np.int32).reshape(-1), "side_e_p": cat["e_p"].astype(np.int32).reshape(-1),
+         "side_perm": np.zeros(S, np.int32), "side_sub_order": np.tile(np.arange(4, dtype=np.int32), S),
+         "side_mortar_stride": np.concatenate([[0], np.cumsum(mort * N2)[:-1]]).astype(np.int64),
+         "local_mortar_nodes_quad": int((mort * N2).sum()), "side_penalty_mult": np.ones(S),
+         "sipg_penalty_prefactor": prefactor, "sipg_penalty_fcn": penalty_fcn, "bc_type": 0,
+         "mpirank": 0, "mpisize": 1, "n_mirrors": 0}
+    dqf, dqc = root >> (level + 1), root >> level
+    geom = {"geom_type": "brick", "face_h_type": face_h_type, "X0": 0.0, "X1": 1.0, "Y0": 0.0, "Y1": 1.0, "Z0": 0.0, "Z1": 1.0,
+            "elem_tree": np.zeros(E, np.int32),
+            "elem_q": np.concatenate([np.stack([fx, fy, fz], axis=1) * dqf, np.stack([cx, cy, cz], axis=1) * dqc]).astype(np.int32).reshape(-1),
+            "elem_dq": np.concatenate([np.full(nf, dqf), np.full(ncz, dqc)]).astype(np.int32)}
+    return A, geom
