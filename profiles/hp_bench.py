@@ -1,5 +1,5 @@
 """Time one apply on the synthetic cubed sphere (uniform-p curved kernel, random-hp kernel).
-usage: python profiles/hp_bench.py [level] [deg] [mode ...]   mode: uniform | hp | generic (uniform mesh forced to the hp kernel)"""
+usage: python profiles/hp_bench.py [level] [deg] [mode ...]   mode: uniform | hp | graded | generic (uniform mesh forced to the general kernel) | amr (brick, one octant refined)"""
 import os
 import sys
 
@@ -18,7 +18,11 @@ for mode in modes:
     kw = dict(pmax=deg) if mode == "hp" else dict(p=deg, graded=True) if mode == "graded" else dict(p=deg)
     if mode == "generic":
         os.environ["D4B_FORCE_GENERIC"] = "1"
-    A, g = sphere_desc(level, **kw)
+    if mode == "amr":
+        from disco4est_b200.brick import brick_amr_desc
+        A, g = brick_amr_desc(level, deg)
+    else:
+        A, g = sphere_desc(level, **kw)
     m = Mesh(A, geom=g)
     os.environ.pop("D4B_FORCE_GENERIC", None)
     stream = torch.cuda.current_stream()
