@@ -77,3 +77,32 @@ def test_gpu_cheby_device_pointers(golden):
     assert rel(u.cpu().numpy(), A["cheby_u"]) < 1e-11
     assert rel(r.cpu().numpy(), A["cheby_r"]) < 1e-10
     m.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", ["sphere_p_amr1", "sphere_p_amr1_robin"])
+@pytest.mark.parametrize("split", ["0", "1"])
+def test_fused_smoother_on_hp_meshes(golden, case, split, monkeypatch):
+    """meshes whose irregular elements run in the mortar kernel (element-wise or face split) take the fused
+    Chebyshev epilogue like the conforming ones: same iterate and residual as the unfused sequence and as the
+    restatement on top of the oracle"""
+    from disco4est_b200 import Mesh
+
+    A = golden(case)
+    orc = Oracle(A)
+    rng = np.random.default_rng(8)
+    rhs, u0 = rng.standard_normal(orc.n), rng.standard_normal(orc.n)
+    lmax, _ = cg_eigs(orc.apply, u0.copy(), rhs, 6, use_new=0)
+    u_ref, r_ref = cheby(orc.apply, u0.copy(), rhs, 5, lmax / 30.0, lmax)
+    out = {}
+    monkeypatch.setenv("D4B_SPLIT", split)
+    for fused in ("0", "1"):
+        monkeypatch.setenv("D4B_NO_FUSED_CHEBY", "0" if fused == "1" else "1")
+        m = Mesh(A)
+        assert m.hp_elements() > 0
+        u, r = u0.copy(), np.zeros_like(u0)
+        m.cheby_smooth(u, rhs, r, 5, lmax / 30.0, lmax)
+        m.close()
+        out[fused] = (u, r)
+        assert rel(u, u_ref) < 1e-11 and rel(r, r_ref) < 1e-10
+    assert rel(out["1"][0], out["0"][0]) < 1e-13
