@@ -17,3 +17,9 @@ echo "== cubed sphere, random hp AMR (hanging faces, all orientations): one appl
 "$DRV" "$HERE/configs/sphere_hp.ini" - --amr 1 --b200 | tail -2
 echo "== cubed sphere uniform p=2 (curved conforming kernel): one apply"
 "$DRV" "$HERE/configs/sphere_p.ini" - --uniform-deg 2 --b200 | tail -2
+echo "== cubed sphere, random hp AMR with deg_quad = deg (mortar kernel / face split, fused smoother): preconditioner slot"
+"$DRV" "$HERE/configs/sphere_p_mg.ini" - --amr 1 --mg 3 --b200 | grep pc_vcycles
+echo "== Robin boundary (two-puncture-like), random hp AMR: one apply"
+"$DRV" "$HERE/configs/sphere_p.ini" - --amr 1 --bc robin --b200 | grep b200_apply_rel_l2
+echo "== inhomogeneous Dirichlet data, random hp AMR: right-hand side and estimator"
+"$DRV" "$HERE/configs/sphere_p.ini" - --amr 1 --bc poly --b200 | grep "build_rhs\|estimator"

@@ -90,11 +90,13 @@ def test_reference_multigrid_with_our_smoother_entry():
 
 
 @pytest.mark.parametrize("ini,args", [("brick_poisson_mg.ini", ["--uniform-deg", "3", "--mg", "4"]),
-                                      ("sphere_hp_mg.ini", ["--amr", "1", "--mg", "3"])])
+                                      ("sphere_hp_mg.ini", ["--amr", "1", "--mg", "3"]),
+                                      ("sphere_p_mg.ini", ["--amr", "1", "--mg", "3"])])
 def test_reference_preconditioner_slot(ini, args):
     """d4est_b200_pc_multigrid_create against d4est_krylov_pc_multigrid_create, both called as
     pc->pc_apply(pc, x, y): hierarchy recorded from the reference's own V-cycle, V-cycles on the device
-    (brick: fused smoother, bottom CG; hp sphere: general kernel, hp transfers, bottom Chebyshev)"""
+    (brick: fused smoother, bottom CG; hp sphere: general kernel, hp transfers, bottom Chebyshev; hp sphere with
+    deg_quad = deg: mortar kernel / face split with the fused smoother on every level)"""
     lines = run(ini, *args)
     res = [l for l in lines if "pc_y_rel_l2_diff" in l][0]
     assert res["pc_vcycles_b200"] == res["pc_vcycles_reference"]
