@@ -28,7 +28,7 @@ EXPORTS = [
     "d4b_mesh_create", "d4b_mesh_destroy", "d4b_mesh_local_nodes", "d4b_mesh_device_bytes", "d4b_mesh_fast_elements", "d4b_mesh_flat_elements", "d4b_mesh_hp_elements", "d4b_mesh_launches_per_apply",
     "d4b_apply", "d4b_apply_stiffness", "d4b_sync", "d4b_set_stream",
     "d4b_interp_to_quad", "d4b_apply_galerkin", "d4b_apply_mass", "d4b_mesh_set_mass_diag", "d4b_build_rhs", "d4b_estimator_bi",
-    "d4b_vec_dot", "d4b_vec_axpy", "d4b_vec_xpby", "d4b_vec_scale",
+    "d4b_vec_dot", "d4b_vec_axpy", "d4b_vec_xpby", "d4b_vec_scale", "d4b_vec_dot_noalloc",
     "d4b_cg_eigs", "d4b_cheby_smooth",
     "d4b_mg_create", "d4b_mg_destroy", "d4b_mg_vcycle", "d4b_mg_solve", "d4b_mg_get_eigs", "d4b_mg_restrict",
     "d4b_mg_prolong",
@@ -84,6 +84,9 @@ def load_library():
     L.d4b_set_stream.argtypes = [C.c_void_p, C.c_void_p]
     L.d4b_vec_dot.restype = C.c_double
     L.d4b_vec_dot.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]
+    L.d4b_vec_dot_noalloc.restype = C.c_int32
+    L.d4b_vec_dot_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p,
+                                      C.c_char_p, C.c_int64]
     L.d4b_vec_axpy.argtypes = [C.c_void_p, C.c_double, C.c_void_p, C.c_void_p, C.c_int64]
     L.d4b_vec_xpby.argtypes = [C.c_void_p, C.c_void_p, C.c_double, C.c_void_p, C.c_int64]
     L.d4b_vec_scale.argtypes = [C.c_void_p, C.c_double, C.c_void_p, C.c_int64]
@@ -215,6 +218,19 @@ def _ptr(x):
     # torch tensor
     assert x.dtype.is_floating_point and x.element_size() == 8 and x.is_contiguous()
     return x.data_ptr()
+
+
+def vec_dot_noalloc(x, y, n, nvec, out, stream=None):
+    """d4b_vec_dot_noalloc: out[v] = x[v*n:(v+1)*n] . y[v*n:(v+1)*n] for device tensors, enqueued on
+    `stream` (raw cudaStream_t as int, None = legacy default stream) with no allocation on the
+    path; raises ValueError (bad / too large arguments) or RuntimeError (CUDA) with the library's
+    message.  x, y, out may be None only where the C entry point accepts NULL."""
+    L = load_library()
+    err = C.create_string_buffer(512)
+    rc = L.d4b_vec_dot_noalloc(None if x is None else _ptr(x), None if y is None else _ptr(y), n, nvec,
+                               None if out is None else _ptr(out), stream, err, len(err))
+    if rc != 0:
+        raise (RuntimeError if rc == 3 else ValueError)(err.value.decode())
 
 
 def geom_compute(arrays, geom, want=None, device=0, out=None):

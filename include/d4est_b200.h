@@ -337,6 +337,39 @@ void   d4b_vec_axpy(d4b_mesh_t *mesh, double a, const double *x, double *y, int6
 void   d4b_vec_xpby(d4b_mesh_t *mesh, const double *x, double b, double *y, int64_t n);
 void   d4b_vec_scale(d4b_mesh_t *mesh, double a, double *x, int64_t n);
 
+/* d4b_vec_dot_noalloc has no counterpart in the reference; it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  It is d4b_vec_dot without a mesh
+ * and without any allocation: the per-block partial sums of the two-pass reduction live in a
+ * file-scope device array of the library (csrc/d4b_static.cu) instead of the mesh's
+ * cudaMalloc'ed buffer, and the path calls no cudaMalloc, cudaFree or allocating routine.
+ *
+ *   out[v] = sum_i x[v*n + i] * y[v*n + i],  v = 0 .. nvec-1
+ *
+ * x, y (nvec*n doubles each) and out (nvec doubles) are DEVICE pointers on the current
+ * device; the two kernels are enqueued on cuda_stream (a cudaStream_t passed as void*, NULL =
+ * the legacy default stream) and the call does not synchronise.  For one vector pair the sum
+ * is bit-identical to d4b_vec_dot on one rank (same grid, same reduction trees); there is no
+ * allreduce over ranks.
+ * Limit: nvec <= D4B_DOT_NOALLOC_MAX_VECS; more is rejected with D4B_NOALLOC_E_TOO_LARGE.
+ * The scratch is D4B_DOT_NOALLOC_MAX_VECS x 592 doubles = 303 104 bytes, held by every GPU
+ * that loads the library until the process exits.  n is not limited.
+ * Sharing: every call on a device uses the same array, which keeps the last call's partial
+ * sums; each call overwrites all it reads, so nothing needs clearing, but calls that overlap
+ * on the GPU (other streams, concurrent graph replays) RACE -- serialise them.
+ * Set-up (the device address of the array, once per device) happens on the first call with
+ * that device current; nvec = 0 does the set-up and launches nothing -- call it once before
+ * a stream capture.
+ * Returns D4B_NOALLOC_OK or an error code; never aborts.  On error a message is written to
+ * err (err_len bytes, NUL-terminated; err may be NULL) and nothing has been launched.        */
+#define D4B_DOT_NOALLOC_MAX_VECS 64
+#define D4B_NOALLOC_OK           0
+#define D4B_NOALLOC_E_ARG        1   /* negative size or NULL pointer             */
+#define D4B_NOALLOC_E_TOO_LARGE  2   /* nvec > D4B_DOT_NOALLOC_MAX_VECS           */
+#define D4B_NOALLOC_E_CUDA       3   /* a CUDA call failed; err has its message   */
+int32_t d4b_vec_dot_noalloc(const double *x, const double *y, int64_t n, int32_t nvec, double *out,
+                            void *cuda_stream, char *err, int64_t err_len);
+
 /* ---------------------------------------------------- Chebyshev smoother  */
 /* parameters of [mg_smoother_cheby], d4est_solver_multigrid_smoother_cheby.h:7-27 */
 typedef struct d4b_cheby_params
