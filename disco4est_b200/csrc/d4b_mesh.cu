@@ -307,7 +307,9 @@ extern "C" d4b_mesh_t *d4b_mesh_create(const d4b_mesh_desc_t *d) {
   // lists in element order (no interior / halo split)
   const int pipe_min = getenv("D4B_PIPELINE_MIN_ELEMS") ? atoi(getenv("D4B_PIPELINE_MIN_ELEMS")) : 4096;   // 0 = never
   if (d->mpisize <= 1 && m->n_generic == 0 && pipe_min > 0 && E >= pipe_min) {
-    const int K = E >= 32 * 64 ? 32 : (E >= 64 ? 8 : 1);
+    // 16 chunks: per-chunk cost (~7 us of DMA / event latency) against pipeline fill; profiles/r01_chunk_sweep.txt
+    int K = E >= 32 * 64 ? 16 : (E >= 64 ? 8 : 1);
+    if (const char *kc = getenv("D4B_PIPELINE_CHUNKS")) K = std::max(1, std::min(std::min(atoi(kc), 1024), E));
     m->chunk_elem.assign(K + 1, E);
     m->chunk_elem[0] = 0;
     for (int k = 1, e = 0; k < K; ++k) {
