@@ -378,14 +378,66 @@ d4est_b200_ctx_new (d4est_laplacian_flux_data_t * flux_data)
 }
 
 void
-d4est_b200_ctx_destroy (d4est_b200_ctx_t * ctx)
+d4est_b200_ctx_invalidate (d4est_b200_ctx_t * ctx)
 {
   if (ctx == NULL) return;
 #ifndef D4EST_B200_ADAPTER_NO_DEVICE
   for (int i = 0; i < D4EST_B200_CACHE; i++)
     if (ctx->cache[i].mesh) d4b_mesh_destroy (ctx->cache[i].mesh);
 #endif
+  memset (ctx->cache, 0, sizeof (ctx->cache));
+}
+
+void
+d4est_b200_ctx_destroy (d4est_b200_ctx_t * ctx)
+{
+  if (ctx == NULL) return;
+  d4est_b200_ctx_invalidate (ctx);
   free (ctx);
+}
+
+/* ---- identity of the reference's current mesh (see d4est_b200_cached_mesh_t) ---- */
+static uint64_t
+sig_words (const uint32_t * w, size_t n, uint64_t seed)
+{
+  /* four independent multiply-xorshift lanes: memory-bound on the stride records */
+  uint64_t h[4] = { seed ^ 0x9E3779B97F4A7C15ull, seed ^ 0xC2B2AE3D27D4EB4Full, seed ^ 0x165667B19E3779F9ull,
+                    seed ^ 0x27D4EB2F165667C5ull };
+  size_t i = 0;
+  for (; i + 4 <= n; i += 4)
+    for (int l = 0; l < 4; l++) {
+      h[l] = (h[l] ^ w[i + l]) * 0x100000001B3ull;
+      h[l] ^= h[l] >> 29;
+    }
+  for (; i < n; i++) { h[0] = (h[0] ^ w[i]) * 0x100000001B3ull; h[0] ^= h[0] >> 29; }
+  return (h[0] * 3) ^ (h[1] * 5) ^ (h[2] * 7) ^ (h[3] * 11) ^ (uint64_t) n;
+}
+
+static uint64_t
+stride_signature (p4est_t * p4est, d4est_mesh_data_t * d4est_factors)
+{
+  return sig_words ((const uint32_t *) d4est_factors->local_strides,
+                    (size_t) p4est->local_num_quadrants * (sizeof (d4est_mesh_local_strides_t) / sizeof (uint32_t)), 1);
+}
+
+static uint64_t
+forest_signature (p4est_t * p4est)
+{
+  uint64_t h = 0x5851F42D4C957F2Dull;
+  for (p4est_topidx_t tt = p4est->first_local_tree; tt <= p4est->last_local_tree; ++tt) {
+    p4est_tree_t *tree = p4est_tree_array_index (p4est->trees, tt);
+    sc_array_t *tq = &tree->quadrants;
+    h = (h ^ (uint64_t) tt) * 0x100000001B3ull;
+    for (size_t q = 0; q < tq->elem_count; ++q) {
+      const p4est_quadrant_t *quad = p4est_quadrant_array_index (tq, q);
+      h = (h ^ (uint32_t) quad->x) * 0x100000001B3ull;
+      h = (h ^ (uint32_t) quad->y) * 0x100000001B3ull;
+      h = (h ^ (uint32_t) quad->z) * 0x100000001B3ull;
+      h = (h ^ (uint32_t) quad->level) * 0x100000001B3ull;
+      h ^= h >> 31;
+    }
+  }
+  return h;
 }
 
 static void eval_dirichlet (d4est_b200_flat_t * fl, d4est_operators_t * d4est_ops, d4est_geometry_t * d4est_geom,
@@ -508,14 +560,34 @@ d4est_b200_get_mesh (d4est_b200_ctx_t * ctx, p4est_t * p4est, d4est_ghost_t * gh
                      d4est_mesh_data_t * d4est_factors)
 {
   const int ne = p4est->local_num_quadrants, nn = d4est_factors->local_sizes.local_nodes;
+  const int nq = d4est_factors->local_sizes.local_nodes_quad, nm = d4est_factors->local_sizes.local_mortar_nodes_quad;
+  const int has_bc = ctx->bc_ops != NULL;
   int victim = 0;
+  int have_stride_sig = 0, have_forest_sig = 0;
+  uint64_t ssig = 0, fsig = 0;
   ctx->clock++;
   for (int i = 0; i < D4EST_B200_CACHE; i++) {
     d4est_b200_cached_mesh_t *c = &ctx->cache[i];
-    if (c->mesh && c->factors == d4est_factors && c->local_elements == ne && c->local_nodes == nn) {
+    if (!(c->mesh && c->factors == d4est_factors && c->local_elements == ne && c->local_nodes == nn
+          && c->local_nodes_quad == nq && c->local_mortar_nodes_quad == nm)) continue;
+    /* same object and counts: is it still the same mesh?  degrees (every time) ... */
+    if (!have_stride_sig) { ssig = stride_signature (p4est, d4est_factors); have_stride_sig = 1; }
+    int same = (c->stride_sig == ssig);
+    /* ... and forest, whenever p4est changed since this entry was last confirmed (the reference's
+     * multigrid coarsens and refines one p4est in place, so a level comes back with a new revision) */
+    if (same && c->revision != p4est->revision) {
+      if (!have_forest_sig) { fsig = forest_signature (p4est); have_forest_sig = 1; }
+      same = (c->forest_sig == fsig);
+      if (same) c->revision = p4est->revision;
+    }
+    if (same && c->has_dirichlet_data == has_bc && c->device_geom == (void *) ctx->device_geom) {
       c->stamp = ctx->clock;
       return c->mesh;
     }
+    /* the reference reused this d4est_mesh_data_t for another mesh (AMR step with equal counts), or the
+     * context gained boundary data / device geometry: the cached operator is stale */
+    d4b_mesh_destroy (c->mesh);
+    memset (c, 0, sizeof (*c));
   }
   /* first free slot, else the least recently used one */
   victim = -1;
@@ -543,7 +615,15 @@ d4est_b200_get_mesh (d4est_b200_ctx_t * ctx, p4est_t * p4est, d4est_ghost_t * gh
   c->factors = d4est_factors;
   c->local_elements = ne;
   c->local_nodes = nn;
+  c->local_nodes_quad = nq;
+  c->local_mortar_nodes_quad = nm;
+  c->revision = p4est->revision;
+  c->forest_sig = have_forest_sig ? fsig : forest_signature (p4est);
+  c->stride_sig = have_stride_sig ? ssig : stride_signature (p4est, d4est_factors);
+  c->has_dirichlet_data = has_bc;
+  c->device_geom = (void *) ctx->device_geom;
   c->stamp = ctx->clock;
+  c->serial = ++ctx->serial;
   ctx->uploads++;
   return c->mesh;
 }
@@ -750,6 +830,9 @@ d4est_b200_pc_record_level (p4est_t * p4est, int level, double *r, int local_nod
     pcd->level_mesh[level] = d4est_b200_get_mesh (pcd->ctx, p4est, updater->current_d4est_ghost,
                                                   updater->current_d4est_factors);
     pcd->level_elements[level] = p4est->local_num_quadrants;
+    pcd->level_serial[level] = 0;
+    for (int i = 0; i < D4EST_B200_CACHE; i++)
+      if (pcd->ctx->cache[i].mesh == pcd->level_mesh[level]) pcd->level_serial[level] = pcd->ctx->cache[i].serial;
   }
   /* zero residual -> zero coarse right-hand sides, zero corrections: u is left as it was */
   memset (r, 0, sizeof (double) * (size_t) local_nodes);
@@ -878,6 +961,30 @@ d4est_b200_pc_build_hierarchy (d4est_b200_pc_multigrid_data_t * pcd, p4est_t * p
   pcd->builds++;
 }
 
+/* is the recorded hierarchy still the one of the reference's current mesh?  Every level's device mesh must
+ * still be the cached upload it was built from, and the top entry must still describe p4est (same test as
+ * d4est_b200_get_mesh: an AMR step can keep all counts) */
+static int
+d4est_b200_pc_hierarchy_current (d4est_b200_pc_multigrid_data_t * pcd, p4est_t * p4est, int local_nodes)
+{
+  if (pcd->mg == NULL || pcd->top_elements != p4est->local_num_quadrants || pcd->top_nodes != local_nodes) return 0;
+  d4est_b200_cached_mesh_t *top = NULL;
+  for (int l = 0; l < pcd->n_levels; l++) {
+    d4est_b200_cached_mesh_t *hit = NULL;
+    for (int i = 0; i < D4EST_B200_CACHE && !hit; i++)
+      if (pcd->ctx->cache[i].mesh == pcd->level_mesh[l] && pcd->ctx->cache[i].serial == pcd->level_serial[l])
+        hit = &pcd->ctx->cache[i];
+    if (!hit) return 0;
+    if (l == pcd->n_levels - 1) top = hit;
+  }
+  if (top->stride_sig != stride_signature (p4est, top->factors)) return 0;
+  if (top->revision != p4est->revision) {
+    if (top->forest_sig != forest_signature (p4est)) return 0;
+    top->revision = p4est->revision;
+  }
+  return 1;
+}
+
 static void
 d4est_b200_pc_multigrid_apply (d4est_krylov_pc_t * kpc, double *xp, double *yp)
 {
@@ -886,7 +993,7 @@ d4est_b200_pc_multigrid_apply (d4est_krylov_pc_t * kpc, double *xp, double *yp)
   const int local_nodes = kct->vecs->local_nodes;
   /* zero initial guess, d4est_krylov_pc_multigrid.c:52 */
   memset (yp, 0, sizeof (double) * (size_t) local_nodes);
-  if (pcd->mg == NULL || pcd->top_elements != kct->p4est->local_num_quadrants || pcd->top_nodes != local_nodes) {
+  if (!d4est_b200_pc_hierarchy_current (pcd, kct->p4est, local_nodes)) {
     double *Au = P4EST_ALLOC (double, local_nodes);
     d4est_elliptic_data_t mg_prob_vecs;
     d4est_elliptic_data_copy_ptrs (kct->vecs, &mg_prob_vecs);

@@ -50,16 +50,30 @@ typedef struct
 
 /* One uploaded mesh.  The reference re-runs d4est_mesh_update after AMR and keeps
  * one d4est_mesh_data_t per multigrid level alive for the whole solve
- * (d4est_solver_multigrid_element_data_updater.c:89-205), so (factors pointer,
- * element count, node count) identifies a mesh and a small cache makes every
- * level a one-time upload.                                                    */
+ * (d4est_solver_multigrid_element_data_updater.c:89-205); a small cache makes every
+ * level a one-time upload.  The reference also REUSES one d4est_mesh_data_t across
+ * d4est_mesh_update calls, and an AMR step can keep every count (refine one element and
+ * coarsen one family; a +1/-1 p-adapt), so a cached mesh is identified by
+ *   (factors pointer, element / node / quadrature-node / mortar-node counts)   O(1)
+ *   + a 64-bit hash of the per-element stride records (degrees)                O(n), every look-up
+ *   + a 64-bit hash of the forest (tree, x, y, z, level of every quadrant)     O(n), recomputed only
+ *     when p4est->revision differs from the one seen at the last look-up
+ *   + how the mesh was built: with / without evaluated Dirichlet data, copied / generated factors.
+ * d4est_b200_ctx_invalidate drops every cached mesh (for callers that overwrite factor arrays
+ * in place without changing the forest or the degrees).                        */
 #define D4EST_B200_CACHE 32
 typedef struct
 {
   d4b_mesh_t *mesh;
   d4est_mesh_data_t *factors;
-  int local_elements, local_nodes;
+  int local_elements, local_nodes, local_nodes_quad, local_mortar_nodes_quad;
+  long revision;                           /* p4est->revision at the last look-up that hashed the forest */
+  uint64_t forest_sig, stride_sig;
+  int has_dirichlet_data;                  /* built after bc_ops was set     */
+  void *device_geom;                       /* built with generated factors   */
   unsigned long stamp;                     /* last use, for eviction         */
+  unsigned long serial;                    /* unique per upload: holders of a d4b_mesh_t* (the pc hierarchy)
+                                              check it to notice that their mesh was replaced */
 } d4est_b200_cached_mesh_t;
 
 /* user context stored in d4est_elliptic_eqns_t.user */
@@ -67,7 +81,7 @@ typedef struct
 {
   d4est_laplacian_flux_data_t *flux_data;  /* as the reference callbacks use */
   d4est_b200_cached_mesh_t cache[D4EST_B200_CACHE];
-  unsigned long clock;
+  unsigned long clock, serial;
   long uploads, applies;                   /* statistics                     */
   /* device-generated geometric factors (d4est_b200_ctx_use_device_geometry) */
   d4est_geometry_t *device_geom;
@@ -155,6 +169,8 @@ void d4est_b200_apply_lhs(p4est_t *p4est, d4est_ghost_t *ghost,
 
 d4est_b200_ctx_t *d4est_b200_ctx_new(d4est_laplacian_flux_data_t *flux_data);
 void d4est_b200_ctx_destroy(d4est_b200_ctx_t *ctx);
+/* forget (and free) every cached device mesh: the next call re-flattens and uploads */
+void d4est_b200_ctx_invalidate(d4est_b200_ctx_t *ctx);
 
 /* Second entry point: the multigrid smoother.  Same factory signature, INI section
  * ([mg_smoother_cheby]) and behaviour as d4est_solver_multigrid_smoother_cheby_init
@@ -210,6 +226,7 @@ typedef struct
   d4b_mg_t *mg;                            /* NULL until the first apply     */
   int n_levels;
   d4b_mesh_t *level_mesh[D4EST_B200_MAX_LEVELS];
+  unsigned long level_serial[D4EST_B200_MAX_LEVELS];
   int level_elements[D4EST_B200_MAX_LEVELS];
   int top_elements, top_nodes;
   long builds, applies, vcycles;           /* statistics                     */

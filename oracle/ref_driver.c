@@ -118,6 +118,17 @@ apply_with_opt (p4est_t * p4est, d4est_ghost_t * ghost, d4est_ghost_data_t * gho
                                       d4est_ops, d4est_geom, d4est_quad, d4est_factors, 0);
 }
 
+/* count-preserving p-adapt for the stale-cache check: elements g_swap_a / g_swap_b exchange degrees */
+static int g_swap_a = -1, g_swap_b = -1, g_swap_deg_a, g_swap_deg_b;
+static void
+swap_deg_cb (d4est_element_data_t * elem_data, void *user_ctx)
+{
+  d4est_mesh_initial_extents_t *input = user_ctx;
+  if (elem_data->id == g_swap_a) elem_data->deg = g_swap_deg_b;
+  if (elem_data->id == g_swap_b) elem_data->deg = g_swap_deg_a;
+  elem_data->deg_quad = input->deg_quad_inc[elem_data->region] + elem_data->deg;
+}
+
 static int g_uniform_deg = -1;
 static void
 set_uniform_deg (d4est_element_data_t * elem_data, void *user_ctx)
@@ -656,6 +667,47 @@ main (int argc, char *argv[])
                 "\"t_fcg_reference_s\": %.4f, \"t_fcg_b200_pc_s\": %.4f}\n",
                 its[0], its[1], sqrt (fn / fd), tf[0], tf[1]);
         P4EST_FREE (fus[0]); P4EST_FREE (fus[1]);
+      }
+    }
+    if (amr_steps > 0) {
+      /* STALE-CACHE CHECK: the reference reuses one d4est_mesh_data_t across d4est_mesh_update calls, and a
+       * +1/-1 p-adapt keeps the element, node, quadrature-node and mortar-node counts.  Two elements of the
+       * same region with different degrees exchange them; the context must notice and upload a new mesh. */
+      for (p4est_topidx_t tt = p4est->first_local_tree; tt <= p4est->last_local_tree && g_swap_b < 0; ++tt) {
+        p4est_tree_t *tree = p4est_tree_array_index (p4est->trees, tt);
+        sc_array_t *tquadrants = &tree->quadrants;
+        g_swap_a = -1;
+        for (int q = 0; q < (int) tquadrants->elem_count && g_swap_b < 0; ++q) {
+          p4est_quadrant_t *quad = p4est_quadrant_array_index (tquadrants, q);
+          d4est_element_data_t *ed = quad->p.user_data;
+          if (g_swap_a < 0) { g_swap_a = ed->id; g_swap_deg_a = ed->deg; }
+          else if (ed->deg != g_swap_deg_a) { g_swap_b = ed->id; g_swap_deg_b = ed->deg; }
+        }
+      }
+      if (g_swap_b >= 0) {
+        const long uploads0 = bctx->uploads;
+        d4est_mesh_local_sizes_t ls2 =
+          d4est_mesh_update (p4est, &d4est_ghost, d4est_ops, d4est_geom, d4est_quad, d4est_factors,
+                             initial_grid_input, INITIALIZE_GHOST, INITIALIZE_QUADRATURE_DATA,
+                             INITIALIZE_GEOMETRY_DATA, INITIALIZE_GEOMETRY_ALIASES, swap_deg_cb,
+                             (void *) initial_grid_input);
+        double *Au_r2 = P4EST_ALLOC_ZERO (double, local_nodes), *Au_b2 = P4EST_ALLOC_ZERO (double, local_nodes);
+        vecs.Au = Au_r2;
+        d4est_elliptic_eqns_apply_lhs (p4est, d4est_ghost, d4est_ghost_data, &fcns_plain, &vecs,
+                                       d4est_ops, d4est_geom, d4est_quad, d4est_factors);
+        vecs.Au = Au_b2;
+        d4est_elliptic_eqns_apply_lhs (p4est, d4est_ghost, d4est_ghost_data, &fcns_b200, &vecs,
+                                       d4est_ops, d4est_geom, d4est_quad, d4est_factors);
+        double sn = 0., sd = 0., moved = 0.;
+        for (int i = 0; i < local_nodes; i++) {
+          sn += (Au_b2[i] - Au_r2[i]) * (Au_b2[i] - Au_r2[i]);
+          sd += Au_r2[i] * Au_r2[i];
+          moved += (Au_r2[i] - Au_plain[i]) * (Au_r2[i] - Au_plain[i]);
+        }
+        printf ("{\"b200_apply_after_degree_swap_rel_l2\": %.3e, \"same_counts\": %d, \"uploads_for_swapped_mesh\": %ld, "
+                "\"reference_change_rel_l2\": %.3e}\n", sqrt (sn / sd),
+                (int) (ls2.local_nodes == local_nodes), bctx->uploads - uploads0, sqrt (moved / sd));
+        P4EST_FREE (Au_r2); P4EST_FREE (Au_b2);
       }
     }
     vecs.Au = Au_tmp;

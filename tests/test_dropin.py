@@ -111,3 +111,15 @@ def test_reference_fcg_with_our_preconditioner():
     res = [l for l in lines if "fcg_iters_b200_pc" in l][0]
     assert res["fcg_iters_b200_pc"] == res["fcg_iters_reference"]
     assert res["fcg_u_rel_l2_diff"] < 1e-9
+
+
+@pytest.mark.parametrize("ini", ["sphere_p.ini", "sphere_hp.ini"])
+def test_cached_mesh_is_dropped_after_count_preserving_p_adapt(ini):
+    """The reference reuses one d4est_mesh_data_t across d4est_mesh_update; two elements exchanging their
+    degrees keep every count.  The adapter's cache key (stride hash + forest hash) must notice it."""
+    lines = run(ini, "--amr", "1")
+    res = [l for l in lines if "b200_apply_after_degree_swap_rel_l2" in l][0]
+    assert res["same_counts"] == 1
+    assert res["reference_change_rel_l2"] > 1e-6      # the operator really changed
+    assert res["uploads_for_swapped_mesh"] == 1
+    assert res["b200_apply_after_degree_swap_rel_l2"] < 1e-12
