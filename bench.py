@@ -44,9 +44,17 @@ def required_bytes_per_dof(p, flat):
     return 80.0 + (72.0 if flat else 168.0) / (p + 1)
 
 
-# DRAM bytes per apply from `ncu --set full` (dram__bytes_read.sum + dram__bytes_write.sum over
-# interp_kernel + flat_apply_kernel), only for the default workload; see profiles/
-NCU_TRAFFIC_BYTES = {(6, 3): 1.656e9}   # profiles/r01_ncu_full_flat_p3_64cube.txt
+def ncu_traffic_bytes(level, deg, world):
+    """DRAM bytes per apply of the dominant kernel from an `ncu --set full` capture of THIS workload
+    (dram__bytes_read.sum + dram__bytes_write.sum), kept in profiles/traffic.json next to the capture it
+    came from; None when no capture exists for (n_gpus, level, deg) -- never a constant carried over."""
+    path = os.path.join(ROOT, "profiles", "traffic.json")
+    if not os.path.exists(path):
+        return None
+    for rec in json.load(open(path)):
+        if rec["n_gpus"] == world and rec["level"] == level and rec["deg"] == deg:
+            return rec["dram_bytes_per_launch"]
+    return None
 
 
 def measured_peak():
@@ -121,8 +129,48 @@ def run_ref_driver(level, deg, reps, out="-"):
     return json.loads(res.stdout.strip().splitlines()[-1])
 
 
-def cpu_baseline(deg):
-    """Reference CPU apply on ONE host core, bounded sample (about 10-20 s)."""
+REF_DRIVER_B200 = os.path.join(ROOT, "oracle", "_ref", "ref_driver_b200")
+
+
+def run_ref_driver_b200(level, deg):
+    """The unmodified reference with eqns->apply_lhs = d4est_b200_apply_lhs on a 2^level cube: the
+    reference builds the mesh and applies its own CPU operator (plain and with_opt), then calls the
+    plugin through d4est_elliptic_eqns_apply_lhs with ITS OWN (pageable) host vectors.  Returns the
+    two JSON lines (reference timings, plugin parity + timing)."""
+    ini = "/tmp/d4b_bench_b200_%d_%d.ini" % (os.getpid(), level)
+    txt = open(BRICK_INI).read().replace("min_level = 2", "min_level = %d" % level)
+    open(ini, "w").write(txt)
+    env = dict(os.environ)
+    env["LD_LIBRARY_PATH"] = "/usr/local/cuda/lib64:" + env.get("LD_LIBRARY_PATH", "")
+    res = subprocess.run([REF_DRIVER_B200, ini, "-", "--uniform-deg", str(deg), "--b200-apply-only"],
+                         capture_output=True, text=True, check=True, env=env)
+    os.unlink(ini)
+    lines = [json.loads(l) for l in res.stdout.splitlines() if l.startswith("{")]
+    return lines[0], [l for l in lines if "b200_apply_rel_l2" in l][0]
+
+
+def cpu_baseline(deg, with_plugin=True):
+    """Reference CPU apply on ONE host core, bounded sample (about 10-20 s).  When the device-linked
+    reference binary is there, the same run also calls the plugin (d4est_b200_apply_lhs) from inside the
+    reference on that mesh: returns (cpu_baseline, plugin record or None)."""
+    level = 5 if deg <= 3 else 4
+    if with_plugin and os.path.exists(REF_DRIVER_B200):
+        r, b = run_ref_driver_b200(level, deg)
+        t = min(r["t_apply_plain_s"], r["t_apply_with_opt_s"])
+        cpu = {"value": r["local_nodes"] / t / 1e9, "unit": UNIT, "cores": 1, "kind": "reference",
+               "sample": "unmodified reference d4est_laplacian[_with_opt]_apply_aij, %d^3-element unit cube p=%d "
+                         "(%d DOF), one apply of each variant, the faster one, 1 core (serial build, no MPI)"
+                         % (1 << level, deg, r["local_nodes"])}
+        plugin = {"workload": "%d^3-element unit cube p=%d (%d DOF) built by the unmodified reference"
+                              % (1 << level, deg, r["local_nodes"]),
+                  "call": "d4est_elliptic_eqns_apply_lhs -> d4est_b200_apply_lhs (9-argument callback) with the "
+                          "reference's own P4EST_ALLOC'd (pageable) u / Au: H2D, apply, D2H inside the call",
+                  "parity_rel_l2_vs_reference_cpu_apply": b["b200_apply_rel_l2"],
+                  "e2e_GDOF_per_s": r["local_nodes"] / b["t_apply_b200_host_vectors_s"] / 1e9,
+                  "e2e_GDOF_per_s_best_of_5": r["local_nodes"] / b["t_apply_b200_host_vectors_best_s"] / 1e9,
+                  "ms_per_call": 1e3 * b["t_apply_b200_host_vectors_s"],
+                  "reference_cpu_ms_per_call": 1e3 * t}
+        return cpu, plugin
     level = 4 if deg <= 3 else 3
     if os.path.exists(REF_DRIVER):
         r = run_ref_driver(level, deg, 2)
@@ -130,7 +178,7 @@ def cpu_baseline(deg):
         return {"value": r["local_nodes"] / t / 1e9, "unit": UNIT, "cores": 1, "kind": "reference",
                 "sample": "unmodified reference d4est_laplacian[_with_opt]_apply_aij, %d^3-element unit cube p=%d "
                           "(%d DOF), best of 3 applies of the faster variant, 1 core (serial build, no MPI)"
-                          % (1 << level, deg, r["local_nodes"])}
+                          % (1 << level, deg, r["local_nodes"])}, None
     import numpy as np
     import oracle_lib
     from disco4est_b200.brick import brick_desc
@@ -139,7 +187,7 @@ def cpu_baseline(deg):
     u = np.random.default_rng(0).standard_normal(O.n)
     t0 = time.perf_counter(); O.apply(u); t = time.perf_counter() - t0
     return {"value": O.n / t / 1e9, "unit": UNIT, "cores": 1, "kind": "port",
-            "sample": "oracle/d4b_oracle C restatement, %d^3 cube p=%d, 1 apply, 1 core" % (1 << (level - 1), deg)}
+            "sample": "oracle/d4b_oracle C restatement, %d^3 cube p=%d, 1 apply, 1 core" % (1 << (level - 1), deg)}, None
 
 
 def bench_reference(args):
@@ -180,6 +228,103 @@ def bench_reference(args):
                    "sample": "bounded: %d^3 elements per core (cost per element is mesh-size independent)" % (1 << level)},
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+PARITY_FIXTURES = ("sphere_p_amr1", "brick_l2_p3")
+PARITY_TOL = 1e-12
+
+
+def nccl_parity(rank, world, local_rank, torch, dist, dev):
+    """Multi-GPU parity where the driver sees it (the reference's own gate is its 1-vs-N-rank
+    regression run, src/Tests/Regression/d4est_test_mpi.sh:3-12).  Fixtures written by the UNMODIFIED
+    reference on one rank (tests/golden/: a random-hp cubed sphere with hanging faces and all face
+    orientations, and a p=3 brick) are split over the N ranks the way p4est partitions them; every
+    rank applies its part through d4b_apply with the NCCL halo exchange inside, the parts are gathered
+    and compared with the reference's own Au (`Au_plain` of the fixture).  Returns one record per
+    fixture; the caller exits non-zero above 1e-12."""
+    import numpy as np
+
+    import d4bio
+    from disco4est_b200 import Mesh
+    from disco4est_b200.brick import partition_offsets
+    from disco4est_b200.partition import partition_desc
+
+    recs = []
+    for case in PARITY_FIXTURES:
+        full = d4bio.load(os.path.join(ROOT, "tests", "golden", case + ".d4b.gz"))
+        E = int(np.asarray(full["n_local"]).reshape(-1)[0])
+        LN = int(np.asarray(full["local_nodes"]).reshape(-1)[0])
+        eoffs = partition_offsets(E, world)
+        nend = np.concatenate([full["nodal_stride"], [LN]]).astype(np.int64)
+        offs = nend[eoffs]
+        A = partition_desc(full, rank, world)
+        m = Mesh(A, device=local_rank)
+        ul = torch.from_numpy(np.ascontiguousarray(full["u"][offs[rank]:offs[rank + 1]])).to(dev)
+        aul = torch.empty_like(ul)
+        m.apply(ul, aul)
+        m.sync()
+        # host-pointer call on the same partitioned mesh: bit-equal to the device-pointer call
+        hau = np.zeros(int(ul.numel()))
+        m.apply(np.ascontiguousarray(ul.cpu().numpy()), hau)
+        host_equal = bool(np.array_equal(hau, aul.cpu().numpy()))
+        sizes = [int(offs[r + 1] - offs[r]) for r in range(world)]
+        pad = torch.zeros(max(sizes), dtype=torch.float64, device=dev)
+        pad[:aul.numel()] = aul
+        parts = [torch.zeros_like(pad) for _ in range(world)]
+        dist.all_gather(parts, pad)
+        got = np.concatenate([parts[r][:sizes[r]].cpu().numpy() for r in range(world)])
+        ref = full["Au_plain"]
+        err = float(np.linalg.norm(got - ref) / np.linalg.norm(ref))
+        flag = torch.tensor([0 if host_equal else 1], device=dev)
+        dist.all_reduce(flag)
+        recs.append({"fixture": case, "ranks": world, "elements": E, "nccl_rel_l2": err,
+                     "ghost_elements_rank0": int(np.asarray(A["n_ghost"]).reshape(-1)[0]),
+                     "host_pointer_call_bit_equal_on_all_ranks": int(flag[0]) == 0,
+                     "against": "Au_plain written by the unmodified reference on one rank"})
+        m.close()
+    return recs
+
+
+def bench_degree_sweep(args, torch, dev):
+    """BASELINE.json metric `GDOF/s ... at p=1..7` (configs[1]): the device-resident apply at every degree on
+    one GPU, same timing as the headline (CUDA events on the launching stream, inputs larger than L2)."""
+    from disco4est_b200 import Mesh
+    from disco4est_b200.brick import brick_desc
+
+    out = []
+    peak = measured_peak()[0]
+    stream = torch.cuda.current_stream()
+    for p in range(1, 8):
+        level = args.level if p <= args.sweep_full_level_max_deg else args.level - 1
+        t0 = time.perf_counter()
+        A = brick_desc(level, p)
+        mesh = Mesh(A, device=dev.index)
+        t_setup = time.perf_counter() - t0
+        del A
+        n = mesh.n
+        mesh.set_stream(stream.cuda_stream)
+        u = torch.rand(n, dtype=torch.float64, device=dev, generator=torch.Generator(device=dev).manual_seed(11 + p))
+        Au = torch.empty_like(u)
+        for _ in range(max(args.warmup, 3)):
+            mesh.apply(u, Au)
+        torch.cuda.synchronize()
+        steps = max(args.steps // 2, 5)
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record(stream)
+        for _ in range(steps):
+            mesh.apply(u, Au)
+        ev1.record(stream)
+        torch.cuda.synchronize()
+        t = ev0.elapsed_time(ev1) * 1e-3 / steps
+        flat = mesh.flat_elements() == mesh.fast_elements() > 0
+        out.append({"p": p, "elements_per_direction": 1 << level, "dof": n, "GDOF_per_s": n / t / 1e9,
+                    "ms_per_apply": 1e3 * t, "bytes_per_dof": algorithmic_bytes_per_dof(p),
+                    "frac": n * algorithmic_bytes_per_dof(p) / t / 1e9 / peak,
+                    "frac_true_bytes": n * required_bytes_per_dof(p, flat) / t / 1e9 / peak,
+                    "vectors_larger_than_l2": 8 * n > 126e6, "setup_s": t_setup})
+        mesh.close()
+        del mesh, u, Au
+    return out
 
 
 def bench_vcycle(top_mesh, level, deg, rank, world, trees, torch, dev, cycles=3):
@@ -369,6 +514,14 @@ def bench_ours(args):
     trees = trees_for_world(world)
     if world > 1:
         comm_init_from_torch(local_rank)
+    parity = None
+    if world > 1 and not args.no_parity:
+        parity = nccl_parity(rank, world, local_rank, torch, dist, dev)
+        worst = max(r["nccl_rel_l2"] for r in parity)
+        if not (worst <= PARITY_TOL and all(r["host_pointer_call_bit_equal_on_all_ranks"] for r in parity)):
+            if rank == 0:
+                sys.stderr.write("bench.py: multi-GPU parity FAILED: %s\n" % json.dumps(parity))
+            sys.exit(3)
     A = brick_desc(level, deg, rank=rank, world=world, trees=trees)
     n_ghost = int(A["n_ghost"])
     mesh = Mesh(A, device=local_rank)
@@ -387,8 +540,9 @@ def bench_ours(args):
         torch.cuda.synchronize()
 
     # ---- device-resident timing (value) ----
-    # multi-rank runs get a longer untimed settling phase (NCCL channels, clocks of all GPUs)
-    n_warm = max(args.warmup, 3) + (20 if world > 1 else 0)
+    # W untimed warm-up applies, exactly as asked (at least the 3 the timing rules want); on N > 1 the
+    # NCCL channels have already carried the parity applies above
+    n_warm = max(args.warmup, 3)
     for _ in range(n_warm):
         mesh.apply(u, Au)
     barrier()
@@ -444,7 +598,7 @@ def bench_ours(args):
                     "h2d_bytes_per_step": 8 * n, "d2h_bytes_per_step": 8 * n},
             "gpu_launches": args.steps * mesh.launches_per_apply(),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": NCU_TRAFFIC_BYTES.get((level, deg)),
+                         "frac": achieved / peak, "traffic": ncu_traffic_bytes(level, deg, world),
                          "peak_source": peak_src,
                          "bytes_per_dof": algorithmic_bytes_per_dof(deg),
                          "bytes_per_dof_true": required_bytes_per_dof(deg, flat),
@@ -453,8 +607,19 @@ def bench_ours(args):
                                      else "interp_kernel + fast_apply_kernel (+ generic_kernel)")},
             "clocks": clocks,
         }
+        if parity is not None:
+            out["parity"] = {"nccl_rel_l2": max(r["nccl_rel_l2"] for r in parity), "ranks": world,
+                             "fixture": "+".join(r["fixture"] for r in parity), "tolerance": PARITY_TOL,
+                             "cases": parity}
         if world == 1 and not args.no_cpu:
-            out["cpu_baseline"] = cpu_baseline(deg)
+            out["cpu_baseline"], plugin = cpu_baseline(deg)
+            if plugin is not None:
+                # the plugin call the reference itself makes, on a mesh the reference built (32^3: the
+                # reference needs ~1 min of host time to set up and apply 64^3), checked against its CPU apply
+                out["e2e_apply_lhs"] = plugin
+                if not plugin["parity_rel_l2_vs_reference_cpu_apply"] <= PARITY_TOL:
+                    sys.stderr.write("bench.py: plugin parity FAILED: %s\n" % json.dumps(plugin))
+                    sys.exit(3)
     # second metric of BASELINE.json: seconds per multigrid V-cycle
     vc = None
     if not args.no_vcycle:
@@ -464,7 +629,12 @@ def bench_ours(args):
     sp = None
     if not args.no_sphere:
         sp = bench_sphere(args, rank, world, local_rank, torch, dist, dev)
+    sweep = None
+    if world == 1 and not args.no_sweep:
+        sweep = bench_degree_sweep(args, torch, dev)
     if rank == 0:
+        if sweep is not None:
+            out["degree_sweep"] = sweep
         if vc is not None:
             out["vcycle"] = vc
         if sp is not None:
@@ -488,6 +658,10 @@ def main():
     ap.add_argument("--no-vcycle", action="store_true", help="skip the V-cycle metric")
     ap.add_argument("--no-sphere", action="store_true", help="skip the cubed-sphere applies")
     ap.add_argument("--sphere-level", type=int, default=5, help="refinement level of each of the 13 sphere trees")
+    ap.add_argument("--no-sweep", action="store_true", help="skip the p=1..7 degree sweep (N=1 only)")
+    ap.add_argument("--no-parity", action="store_true", help="skip the multi-GPU parity check (N>1 only)")
+    ap.add_argument("--sweep-full-level-max-deg", type=int, default=3,
+                    help="degrees up to this one are swept at --level, higher ones at --level - 1")
     args = ap.parse_args()
     if args.impl == "reference":
         bench_reference(args)

@@ -24,6 +24,10 @@ geom() { # name ini args...: sidecar for the device geometry generator (element 
   rm -f /tmp/d4b_geom_$$.d4b
   gzip -9nf "$G/$name.geom.d4b"
 }
+variant() { # new.ini base.ini sed-expression...: derived configuration under /tmp (penalty function / multipliers)
+  local new=$1 base=$2; shift 2
+  sed "$@" "$HERE/configs/$base" > "$HERE/configs/$new"
+}
 geom brick_l2_p3 brick_poisson.ini --uniform-deg 3
 geom sphere_p2 sphere_p.ini --uniform-deg 2
 geom sphere_hp_amr1 sphere_hp.ini --amr 1 --bc poly
@@ -40,3 +44,14 @@ run brick_l2_p2_robin brick_poisson.ini --uniform-deg 2 --bc robin   # Robin bou
 run sphere_p_amr1_robin sphere_p.ini --amr 1 --bc robin               # Robin on the outer sphere, random hp refinement (two-puncture-like)
 run sphere_hp_amr1_zero sphere_hp.ini --amr 1 --cheby 8 10 --quad  # hanging faces, homogeneous BC, smoother outputs
 run brick_mg_l2_p2 brick_poisson_mg.ini --uniform-deg 2 --mg 4 --fcg 30   # + in-house FCG (multigrid-preconditioned and not) and CG: iterates, iteration counts; + the reference multigrid: residual and iterate after each of 4 V-cycles
+# the other three penalty functions (d4est_laplacian_flux_sipg.c:945-1005; meanp_sqr_over_meanh is what
+# src/Problems/Okendon/options.input and BoyenYorkModel/options.input select) and region multipliers != 1
+# (:1165-1199), on the 13-tree sphere with per-region degrees 1 / 2 / 1 (p-jumps and h-jumps on the region
+# interfaces, so the four functions and the averaged multipliers all differ) and inhomogeneous Dirichlet data
+variant _pen_maxpp1.ini sphere_p.ini -e 's/^sipg_penalty_fcn = .*/sipg_penalty_fcn = maxpp1_sqr_over_minh/'
+variant _pen_meanp_mult.ini sphere_p.ini -e 's/^sipg_penalty_fcn = .*/sipg_penalty_fcn = meanp_sqr_over_meanh\nsipg_use_region_multiplier = 1\nsipg_use_region_multipliers = 1\nsipg_number_of_regions = 3\nregion0_multiplier = 0.7\nregion1_multiplier = 1.9\nregion2_multiplier = 3.1\nsipg_region0_multiplier = 0.7\nsipg_region1_multiplier = 1.9\nsipg_region2_multiplier = 3.1/'
+variant _pen_meanph.ini sphere_p.ini -e 's/^sipg_penalty_fcn = .*/sipg_penalty_fcn = mean_p_sqr_over_h/'
+run sphere_p_pen_maxpp1 _pen_maxpp1.ini --bc poly --no-opt
+run sphere_p_pen_meanp_mult _pen_meanp_mult.ini --bc poly
+run sphere_p_pen_meanph _pen_meanph.ini --bc poly
+rm -f "$HERE"/configs/_pen_*.ini

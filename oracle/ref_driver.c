@@ -282,7 +282,7 @@ main (int argc, char *argv[])
   const char *ini = argv[1];
   const char *out = argv[2];
   int amr_steps = 0, time_reps = 0, bc_poly = 0, cheby_imax = 0, cheby_eigs_imax = 0, mg_vcycles = 0, use_b200 = 0;
-  int dump_quad = 0, fcg_imax = 0, bc_robin = 0;
+  int dump_quad = 0, fcg_imax = 0, bc_robin = 0, b200_apply_only = 0, no_opt = 0;
   const char *geom_out = NULL;
   for (int a = 3; a < argc; a++) {
     if (!strcmp (argv[a], "--amr")) amr_steps = atoi (argv[++a]);
@@ -294,7 +294,11 @@ main (int argc, char *argv[])
     else if (!strcmp (argv[a], "--quad")) { dump_quad = 1; }
     else if (!strcmp (argv[a], "--fcg")) { fcg_imax = atoi (argv[++a]); }
     else if (!strcmp (argv[a], "--b200")) { use_b200 = 1; }
+    else if (!strcmp (argv[a], "--b200-apply-only")) { use_b200 = 1; b200_apply_only = 1; }
     else if (!strcmp (argv[a], "--geom")) { geom_out = argv[++a]; }
+    /* the with_opt flux knows no maxpp1_sqr_over_minh (d4est_laplacian_with_opt_flux_sipg.c:1350-1366 aborts):
+     * both outputs then come from the plain operator */
+    else if (!strcmp (argv[a], "--no-opt")) { no_opt = 1; }
     else { fprintf (stderr, "unknown option %s\n", argv[a]); return 2; }
   }
 
@@ -380,12 +384,13 @@ main (int argc, char *argv[])
   d4est_laplacian_flux_data_t *flux_plain = bc_robin
     ? d4est_laplacian_flux_new (p4est, ini, BC_ROBIN, &bc_robin_data)
     : d4est_laplacian_flux_new (p4est, ini, BC_DIRICHLET, &bc_data_for_lhs);
-  d4est_laplacian_with_opt_flux_data_t *flux_opt = bc_robin
+  d4est_laplacian_with_opt_flux_data_t *flux_opt = no_opt ? NULL : bc_robin
     ? d4est_laplacian_with_opt_flux_new (p4est, ini, BC_ROBIN, &bc_robin_opt)
     : d4est_laplacian_with_opt_flux_new (p4est, ini, BC_DIRICHLET, &bc_data_for_lhs);
 
   d4est_elliptic_eqns_t fcns_plain = {.build_residual = NULL,.apply_lhs = apply_plain,.user = flux_plain };
   d4est_elliptic_eqns_t fcns_opt = {.build_residual = NULL,.apply_lhs = apply_with_opt,.user = flux_opt };
+  if (no_opt) fcns_opt = fcns_plain;
 
   double *u = P4EST_ALLOC (double, local_nodes);
   double *Au_plain = P4EST_ALLOC_ZERO (double, local_nodes);
@@ -452,19 +457,24 @@ main (int argc, char *argv[])
     vecs.Au = Au_b;
     d4est_elliptic_eqns_apply_lhs (p4est, d4est_ghost, d4est_ghost_data, &fcns_b200, &vecs,
                                    d4est_ops, d4est_geom, d4est_quad, d4est_factors);
-    double t1 = wall ();
-    for (int r = 0; r < 5; r++)
+    double t1 = wall (), t_b200_best = 1e30;
+    for (int r = 0; r < 5; r++) {
+      double t1r = wall ();
       d4est_elliptic_eqns_apply_lhs (p4est, d4est_ghost, d4est_ghost_data, &fcns_b200, &vecs,
                                      d4est_ops, d4est_geom, d4est_quad, d4est_factors);
+      t1r = wall () - t1r;
+      if (t1r < t_b200_best) t_b200_best = t1r;
+    }
     double t_b200 = (wall () - t1) / 5.;
     double num = 0., den = 0.;
     for (int i = 0; i < local_nodes; i++) {
       num += (Au_b[i] - Au_plain[i]) * (Au_b[i] - Au_plain[i]);
       den += Au_plain[i] * Au_plain[i];
     }
-    printf ("{\"b200_apply_rel_l2\": %.3e, \"t_apply_b200_host_vectors_s\": %.6f, \"t_apply_reference_s\": %.6f}\n",
-            sqrt (num / den), t_b200, best_plain < best_opt ? best_plain : best_opt);
-    {
+    printf ("{\"b200_apply_rel_l2\": %.3e, \"t_apply_b200_host_vectors_s\": %.6f, \"t_apply_b200_host_vectors_best_s\": %.6f, "
+            "\"t_apply_reference_s\": %.6f}\n",
+            sqrt (num / den), t_b200, t_b200_best, best_plain < best_opt ? best_plain : best_opt);
+    if (!b200_apply_only) {
       /* the same callback on a context that generates the geometric factors on the device
        * (d4est_b200_ctx_use_device_geometry) instead of copying the reference's arrays */
       d4est_b200_ctx_t *gctx = d4est_b200_ctx_new (flux_plain);
@@ -484,7 +494,7 @@ main (int argc, char *argv[])
       P4EST_FREE (Au_g);
       d4est_b200_ctx_destroy (gctx);
     }
-    {
+    if (!b200_apply_only) {
       /* Jacobian apply of a nonlinear problem: Laplacian + mass-type term.  Reference: the
        * problem files' loop over d4est_quadrature_apply_fofufofvlilj added to apply_aij
        * (constant_density_star_fcns.h:528-600); ours: d4est_b200_set_mass_term, then the same
@@ -1118,7 +1128,7 @@ main (int argc, char *argv[])
   P4EST_FREE (Au_opt);
   d4est_ghost_data_destroy (d4est_ghost_data);
   d4est_laplacian_flux_destroy (flux_plain);
-  d4est_laplacian_with_opt_flux_destroy (flux_opt);
+  if (flux_opt) d4est_laplacian_with_opt_flux_destroy (flux_opt);
   d4est_ghost_destroy (d4est_ghost);
   d4est_mesh_initial_extents_destroy (initial_grid_input);
   d4est_quadrature_destroy (p4est, d4est_ops, d4est_geom, d4est_quad);

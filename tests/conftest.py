@@ -13,6 +13,8 @@ GOLDEN_CASES = [
     "brick_l2_p1", "brick_l2_p2_bc", "brick_l2_p3", "brick_l2_p5", "brick_l2_p7",
     "sphere_p2", "sphere_hp_amr0", "sphere_hp_amr1", "sphere_hp_amr1_zero", "sphere_p_amr1",
     "brick_l2_p2_robin", "sphere_p_amr1_robin",
+    # the other three penalty functions (+ region multipliers != 1), d4est_laplacian_flux_sipg.c:945-1005, :1165-1199
+    "sphere_p_pen_maxpp1", "sphere_p_pen_meanp_mult", "sphere_p_pen_meanph",
 ]
 
 
