@@ -97,7 +97,35 @@ GEOM_ARRAY_FIELDS = ["xyz", "J_quad", "rst_xyz_quad", "sj_m_mortar_quad", "n_m_m
 class GeomArrays(C.Structure):
     """d4b_geom_arrays_t (addresses; host or device)"""
 
-    _fields_ = [(name, C.c_void_p) for name in GEOM_ARRAY_FIELDS]
+    _fields_ = [(name, C.c_void_p) for name in GEOM_ARRAY_FIELDS + ["xyz_quad"]]
+
+
+NL_KIND = {"punctures": 1, "constant_density_star": 2, "table": 3}
+MAX_PUNCTURES = 10
+
+
+class NonlinearDesc(C.Structure):
+    """d4b_nonlinear_desc_t"""
+
+    _fields_ = [("kind", C.c_int32), ("n_punctures", C.c_int32),
+                ("punctures", (C.c_double * 10) * MAX_PUNCTURES),
+                ("star_rho0", C.c_double), ("star_R", C.c_double), ("star_c", C.c_double * 3),
+                ("exponent", C.c_int32),
+                ("a_quad", C.c_void_p), ("b_quad", C.c_void_p), ("xyz_quad", C.c_void_p), ("jac_quad", C.c_void_p)]
+
+
+class NewtonParams(C.Structure):
+    """d4b_newton_params_t"""
+
+    _fields_ = [("atol", C.c_double), ("rtol", C.c_double), ("imin", C.c_int32), ("imax", C.c_int32),
+                ("fcg_atol", C.c_double), ("fcg_rtol", C.c_double), ("fcg_imax", C.c_int32), ("fcg_flags", C.c_int32)]
+
+
+class NewtonStats(C.Structure):
+    """d4b_newton_stats_t"""
+
+    _fields_ = [("steps", C.c_int32), ("fcg_iterations", C.c_int32 * 64), ("residual_norm", C.c_double * 65),
+                ("jacobian_applies", C.c_int64)]
 
 
 GEOM_TYPE = {"brick": 0, "cubed_sphere": 1}

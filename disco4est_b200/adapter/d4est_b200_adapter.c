@@ -396,48 +396,29 @@ d4est_b200_ctx_destroy (d4est_b200_ctx_t * ctx)
   free (ctx);
 }
 
-/* ---- identity of the reference's current mesh (see d4est_b200_cached_mesh_t) ---- */
+/* ---- identity of the reference's current mesh (see d4est_b200_cached_mesh_t) ----
+ * One walk over the local quadrants: position in the forest and the two degrees of every element.
+ * (d4est_mesh_data_t::local_strides is no substitute: its nodal / quadrature strides are never filled,
+ * src/Mesh/d4est_mesh.c:502-503, :962-963 set the mortar strides only.) */
 static uint64_t
-sig_words (const uint32_t * w, size_t n, uint64_t seed)
+mesh_signature (p4est_t * p4est)
 {
-  /* four independent multiply-xorshift lanes: memory-bound on the stride records */
-  uint64_t h[4] = { seed ^ 0x9E3779B97F4A7C15ull, seed ^ 0xC2B2AE3D27D4EB4Full, seed ^ 0x165667B19E3779F9ull,
-                    seed ^ 0x27D4EB2F165667C5ull };
-  size_t i = 0;
-  for (; i + 4 <= n; i += 4)
-    for (int l = 0; l < 4; l++) {
-      h[l] = (h[l] ^ w[i + l]) * 0x100000001B3ull;
-      h[l] ^= h[l] >> 29;
-    }
-  for (; i < n; i++) { h[0] = (h[0] ^ w[i]) * 0x100000001B3ull; h[0] ^= h[0] >> 29; }
-  return (h[0] * 3) ^ (h[1] * 5) ^ (h[2] * 7) ^ (h[3] * 11) ^ (uint64_t) n;
-}
-
-static uint64_t
-stride_signature (p4est_t * p4est, d4est_mesh_data_t * d4est_factors)
-{
-  return sig_words ((const uint32_t *) d4est_factors->local_strides,
-                    (size_t) p4est->local_num_quadrants * (sizeof (d4est_mesh_local_strides_t) / sizeof (uint32_t)), 1);
-}
-
-static uint64_t
-forest_signature (p4est_t * p4est)
-{
-  uint64_t h = 0x5851F42D4C957F2Dull;
+  uint64_t h[2] = { 0x5851F42D4C957F2Dull, 0x9E3779B97F4A7C15ull };
   for (p4est_topidx_t tt = p4est->first_local_tree; tt <= p4est->last_local_tree; ++tt) {
     p4est_tree_t *tree = p4est_tree_array_index (p4est->trees, tt);
     sc_array_t *tq = &tree->quadrants;
-    h = (h ^ (uint64_t) tt) * 0x100000001B3ull;
+    h[0] = (h[0] ^ (uint64_t) tt) * 0x100000001B3ull;
     for (size_t q = 0; q < tq->elem_count; ++q) {
       const p4est_quadrant_t *quad = p4est_quadrant_array_index (tq, q);
-      h = (h ^ (uint32_t) quad->x) * 0x100000001B3ull;
-      h = (h ^ (uint32_t) quad->y) * 0x100000001B3ull;
-      h = (h ^ (uint32_t) quad->z) * 0x100000001B3ull;
-      h = (h ^ (uint32_t) quad->level) * 0x100000001B3ull;
-      h ^= h >> 31;
+      const d4est_element_data_t *ed = (const d4est_element_data_t *) quad->p.user_data;
+      h[0] = (h[0] ^ (((uint64_t) (uint32_t) quad->x << 32) | (uint32_t) quad->y)) * 0x100000001B3ull;
+      h[0] ^= h[0] >> 29;
+      h[1] = (h[1] ^ (((uint64_t) (uint32_t) quad->z << 32) | ((uint32_t) quad->level << 16)
+                      | ((uint32_t) ed->deg << 8) | (uint32_t) ed->deg_quad)) * 0xC2B2AE3D27D4EB4Full;
+      h[1] ^= h[1] >> 31;
     }
   }
-  return h;
+  return h[0] * 3 ^ h[1] * 5;
 }
 
 static void eval_dirichlet (d4est_b200_flat_t * fl, d4est_operators_t * d4est_ops, d4est_geometry_t * d4est_geom,
@@ -563,23 +544,17 @@ d4est_b200_get_mesh (d4est_b200_ctx_t * ctx, p4est_t * p4est, d4est_ghost_t * gh
   const int nq = d4est_factors->local_sizes.local_nodes_quad, nm = d4est_factors->local_sizes.local_mortar_nodes_quad;
   const int has_bc = ctx->bc_ops != NULL;
   int victim = 0;
-  int have_stride_sig = 0, have_forest_sig = 0;
-  uint64_t ssig = 0, fsig = 0;
+  int have_sig = 0;
+  uint64_t sig = 0;
   ctx->clock++;
   for (int i = 0; i < D4EST_B200_CACHE; i++) {
     d4est_b200_cached_mesh_t *c = &ctx->cache[i];
     if (!(c->mesh && c->factors == d4est_factors && c->local_elements == ne && c->local_nodes == nn
           && c->local_nodes_quad == nq && c->local_mortar_nodes_quad == nm)) continue;
-    /* same object and counts: is it still the same mesh?  degrees (every time) ... */
-    if (!have_stride_sig) { ssig = stride_signature (p4est, d4est_factors); have_stride_sig = 1; }
-    int same = (c->stride_sig == ssig);
-    /* ... and forest, whenever p4est changed since this entry was last confirmed (the reference's
-     * multigrid coarsens and refines one p4est in place, so a level comes back with a new revision) */
-    if (same && c->revision != p4est->revision) {
-      if (!have_forest_sig) { fsig = forest_signature (p4est); have_forest_sig = 1; }
-      same = (c->forest_sig == fsig);
-      if (same) c->revision = p4est->revision;
-    }
+    /* same object and counts: is it still the same mesh?  (the reference's multigrid coarsens and
+     * refines one p4est in place and re-runs d4est_mesh_update on one d4est_mesh_data_t after AMR) */
+    if (!have_sig) { sig = mesh_signature (p4est); have_sig = 1; }
+    const int same = (c->mesh_sig == sig);
     if (same && c->has_dirichlet_data == has_bc && c->device_geom == (void *) ctx->device_geom) {
       c->stamp = ctx->clock;
       return c->mesh;
@@ -617,9 +592,7 @@ d4est_b200_get_mesh (d4est_b200_ctx_t * ctx, p4est_t * p4est, d4est_ghost_t * gh
   c->local_nodes = nn;
   c->local_nodes_quad = nq;
   c->local_mortar_nodes_quad = nm;
-  c->revision = p4est->revision;
-  c->forest_sig = have_forest_sig ? fsig : forest_signature (p4est);
-  c->stride_sig = have_stride_sig ? ssig : stride_signature (p4est, d4est_factors);
+  c->mesh_sig = have_sig ? sig : mesh_signature (p4est);
   c->has_dirichlet_data = has_bc;
   c->device_geom = (void *) ctx->device_geom;
   c->stamp = ctx->clock;
@@ -977,12 +950,7 @@ d4est_b200_pc_hierarchy_current (d4est_b200_pc_multigrid_data_t * pcd, p4est_t *
     if (!hit) return 0;
     if (l == pcd->n_levels - 1) top = hit;
   }
-  if (top->stride_sig != stride_signature (p4est, top->factors)) return 0;
-  if (top->revision != p4est->revision) {
-    if (top->forest_sig != forest_signature (p4est)) return 0;
-    top->revision = p4est->revision;
-  }
-  return 1;
+  return top->mesh_sig == mesh_signature (p4est);
 }
 
 static void

@@ -50,8 +50,19 @@ bool is_device_ptr(const void *p) {
 
 }  // namespace
 
+namespace {
+__global__ void add_k(const double *__restrict__ x, double *__restrict__ y, int64_t n) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    y[i] += x[i];
+}
+}  // namespace
+
 void d4b_apply_device(d4b_mesh *m, const double *du, double *dAu) {
   D4B_CHECK(m->epi.mode == 0 || m->n_generic == 0, "fused epilogue on a mesh with general-kernel elements");
+  // coarse multigrid level of a linearised problem: the Galerkin mass term of this input first
+  const bool add = m->pre_apply && m->pre_apply(m, du);
+  const bool add_after = add && (m->n_generic > 0 || m->fast.empty());
+  if (add && !add_after) m->epi.add = m->d_addterm;
   if (m->mpisize == 1) {
     d4b_launch_fast(m, du, dAu, 0);
     d4b_launch_fast(m, du, dAu, 1);
@@ -71,6 +82,11 @@ void d4b_apply_device(d4b_mesh *m, const double *du, double *dAu) {
     D4B_CUDA(cudaStreamWaitEvent(m->stream, m->ev_boundary, 0));
   }
   d4b_launch_generic(m, du, dAu, 0);
+  if (add_after) {
+    const int64_t n = m->local_nodes;
+    add_k<<<(int)std::min<int64_t>((n + 255) / 256, 148 * 8), 256, 0, m->stream>>>(m->d_addterm, dAu, n);
+  }
+  m->epi.add = nullptr;
 }
 
 namespace {
@@ -124,7 +140,7 @@ void apply_impl(d4b_mesh *m, const double *u, double *Au, int stiffness_only) {
   D4B_CHECK(m && u && Au, "d4b_apply: NULL argument");
   D4B_CHECK(m->n_ghost == 0 || m->d_ughost, "d4b_apply: ghost buffer missing");
   bool u_dev = is_device_ptr(u), Au_dev = is_device_ptr(Au);
-  if (!u_dev && !Au_dev && !stiffness_only && !m->chunk_dep.empty() && u != Au) {
+  if (!u_dev && !Au_dev && !stiffness_only && !m->chunk_dep.empty() && u != Au && !m->pre_apply) {
     apply_host_pipelined(m, u, Au);
     return;
   }

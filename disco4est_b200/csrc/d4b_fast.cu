@@ -64,6 +64,7 @@ __device__ __forceinline__ EpiCoef epi_coef(const D4bEpilogue &e) {
   return c;
 }
 __device__ __forceinline__ void store_result(const D4bEpilogue &e, const EpiCoef &c, double *Au, int64_t i, double s) {
+  if (e.add) s += e.add[i];
   if (e.mode == 0) { Au[i] = s; return; }
   if (e.mode == 2) { Au[i] = e.rhs[i] - s; return; }
   const double r = (e.rhs[i] - s) * c.alpha;

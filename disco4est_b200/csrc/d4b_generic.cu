@@ -489,7 +489,19 @@ struct QuadArgs {
   int mode, mQ;
   const double *in, *jac;
   double *out;
+  const double *wja, *nb;   // modes 5, 6: w J a(x) and b(x) of f = a (b + u)^k
+  int kexp;
 };
+
+// x^k for an integer exponent of either sign
+__device__ __forceinline__ double ipow(double x, int k) {
+  double r = 1., p = x;
+  for (int n = k < 0 ? -k : k; n; n >>= 1) {
+    if (n & 1) r *= p;
+    p *= p;
+  }
+  return k < 0 ? 1. / r : r;
+}
 
 __global__ void __launch_bounds__(128) quad_ops_kernel(QuadArgs a) {
   extern __shared__ double smem[];
@@ -508,7 +520,7 @@ __global__ void __launch_bounds__(128) quad_ops_kernel(QuadArgs a) {
     }
     return;
   }
-  if (a.mode == 0 || a.mode == 2) {
+  if (a.mode == 0 || a.mode == 2 || a.mode >= 4) {
     for (int i = threadIdx.x; i < n3; i += blockDim.x) s0[i] = a.in[ns + i];
     __syncthreads();
     sweep3<false>(s1, s0, E, N, 1, Nq, N, 0, N, N, N);
@@ -518,13 +530,21 @@ __global__ void __launch_bounds__(128) quad_ops_kernel(QuadArgs a) {
       for (int k = threadIdx.x; k < q3; k += blockDim.x) a.out[qs + k] = s0[k];
       return;
     }
+    if (a.mode == 6) {   // Newton linearisation: W = w J f_u(x, V u0) = k (w J a) (b + V u0)^(k-1)
+      for (int k = threadIdx.x; k < q3; k += blockDim.x)
+        a.out[qs + k] = (double)a.kexp * a.wja[qs + k] * ipow(a.nb[qs + k] + s0[k], a.kexp - 1);
+      return;
+    }
   } else {
     for (int k = threadIdx.x; k < q3; k += blockDim.x) s0[k] = a.in[qs + k];
     __syncthreads();
   }
+  __syncthreads();
   for (int k = threadIdx.x; k < q3; k += blockDim.x) {
     const int ia = k % Nq, ib = (k / Nq) % Nq, ic = k / (Nq * Nq);
-    s0[k] *= w[ic] * w[ib] * w[ia] * (a.jac ? a.jac[qs + k] : 1.);
+    if (a.mode == 4) s0[k] *= a.jac[qs + k];                                                   // weights folded in
+    else if (a.mode == 5) s0[k] = a.wja[qs + k] * ipow(a.nb[qs + k] + s0[k], a.kexp);          // w J f(x, V u)
+    else s0[k] *= w[ic] * w[ib] * w[ia] * (a.jac ? a.jac[qs + k] : 1.);
   }
   __syncthreads();
   sweep3<false>(s1, s0, E, 1, N, N, Nq, 2, Nq, Nq, Nq);
@@ -535,9 +555,27 @@ __global__ void __launch_bounds__(128) quad_ops_kernel(QuadArgs a) {
 
 }  // namespace
 
+void d4b_launch_quad_nl(d4b_mesh *m, int mode, const double *d_in, double *d_out) {
+  D4B_CHECK(m->d_nl_wja && m->d_nl_b, "no nonlinear term attached to this mesh (d4b_mesh_set_nonlinear_term)");
+  if (m->n_local == 0) return;
+  QuadArgs a;
+  a.tab = m->d_tab; a.tabdata = m->d_tabdata;
+  a.deg = m->d_deg; a.deg_quad = m->d_deg_quad;
+  a.nodal_stride = m->d_nodal_stride; a.quad_stride = m->d_quad_stride;
+  a.mode = mode;
+  a.mQ = m->max_deg_quad > m->max_deg ? m->max_deg_quad + 1 : m->max_deg + 1;
+  a.in = d_in; a.jac = nullptr; a.out = d_out;
+  a.wja = m->d_nl_wja; a.nb = m->d_nl_b; a.kexp = m->nl_k;
+  const size_t smem = (size_t)3 * a.mQ * a.mQ * a.mQ * sizeof(double);
+  D4B_CHECK(smem <= 48 * 1024, "quadrature operators: %zu bytes of shared memory", smem);
+  quad_ops_kernel<<<m->n_local, 128, smem, m->stream>>>(a);
+  D4B_CUDA(cudaGetLastError());
+}
+
 void d4b_launch_quad_op(d4b_mesh *m, int mode, const double *d_in, const double *d_jac, double *d_out) {
   if (m->n_local == 0) return;
   QuadArgs a;
+  a.wja = nullptr; a.nb = nullptr; a.kexp = 0;
   a.tab = m->d_tab; a.tabdata = m->d_tabdata;
   a.deg = m->d_deg; a.deg_quad = m->d_deg_quad;
   a.nodal_stride = m->d_nodal_stride; a.quad_stride = m->d_quad_stride;

@@ -183,7 +183,7 @@ struct GeomArgs {
   // element sizes [n_local + n_ghost] / [..][6]
   double *vol, *area, *jmin, *jmean, *jmax;
   // outputs
-  double *xyz, *J, *rst_xyz, *sj, *n, *drm, *drp, *hm, *hp;
+  double *xyz, *J, *rst_xyz, *sj, *n, *drm, *drp, *hm, *hp, *xyz_quad;
 };
 
 __device__ __forceinline__ ElemPos elem_pos(const GeomArgs &A, int32_t ref) {
@@ -203,13 +203,16 @@ __device__ __forceinline__ ElemPos elem_pos(const GeomArgs &A, int32_t ref) {
 __global__ void geom_volume_kernel(GeomArgs A) {
   const int e = blockIdx.x;
   const ElemPos pos = elem_pos(A, e);
-  if (A.J) {
+  if (A.J || A.xyz_quad) {
     const int dq = A.deg_quad[e], nq = dq + 1, n3 = nq * nq * nq;
     const int64_t qs = A.quad_stride[e];
     for (int k = threadIdx.x; k < n3; k += blockDim.x) {
       const double rst[3] = {c_gt.gx[dq][k % nq], c_gt.gx[dq][(k / nq) % nq], c_gt.gx[dq][k / (nq * nq)]};
-      double dx[3][3], cof[3][3];
-      geom_map(A.P, pos, rst, dx, nullptr);
+      double dx[3][3], cof[3][3], xq[3];
+      geom_map(A.P, pos, rst, dx, A.xyz_quad ? xq : nullptr);
+      if (A.xyz_quad)
+        for (int d = 0; d < 3; ++d) A.xyz_quad[(int64_t)d * A.LQ + qs + k] = xq[d];
+      if (!A.J) continue;
       const double J = cofactors(dx, cof);
       A.J[qs + k] = J;
       if (A.rst_xyz)
@@ -468,7 +471,7 @@ extern "C" void d4b_geom_compute(const d4b_mesh_desc_t *d, const d4b_geom_desc_t
   Out outs[] = {{out->xyz, &A.xyz, 3 * LN}, {out->J_quad, &A.J, LQ}, {out->rst_xyz_quad, &A.rst_xyz, 9 * LQ},
                 {out->sj_m_mortar_quad, &A.sj, MP}, {out->n_m_mortar_quad, &A.n, 3 * MP},
                 {out->drst_dxyz_m_mortar_quad, &A.drm, 9 * MP}, {out->drst_dxyz_p_mortar_quad_porder, &A.drp, 9 * MP},
-                {out->hm_mortar_quad, &A.hm, MP}, {out->hp_mortar_quad, &A.hp, MP}};
+                {out->hm_mortar_quad, &A.hm, MP}, {out->hp_mortar_quad, &A.hp, MP}, {out->xyz_quad, &A.xyz_quad, 3 * LQ}};
   for (Out &o : outs) {
     if (!o.user) continue;
     *o.slot = is_device_ptr(o.user) ? o.user : B.up<double>(nullptr, o.n);
@@ -484,7 +487,7 @@ extern "C" void d4b_geom_compute(const d4b_mesh_desc_t *d, const d4b_geom_desc_t
     geom_size_kernel<<<(unsigned)((nt + 127) / 128), 128>>>(A);
     D4B_CUDA(cudaGetLastError());
   }
-  if ((A.J || A.xyz) && E > 0) {
+  if ((A.J || A.xyz || A.xyz_quad) && E > 0) {
     geom_volume_kernel<<<E, 64>>>(A);
     D4B_CUDA(cudaGetLastError());
   }
@@ -518,5 +521,19 @@ extern "C" d4b_mesh_t *d4b_mesh_create_with_geometry(const d4b_mesh_desc_t *topo
   d.sj_m_mortar_quad = sj.data(); d.n_m_mortar_quad = n.data();
   d.drst_dxyz_m_mortar_quad = drm.data(); d.drst_dxyz_p_mortar_quad_porder = drp.data();
   d.hm_mortar_quad = hm.data(); d.hp_mortar_quad = hp.data();
-  return d4b_mesh_create(&d);
+  d4b_mesh *m = d4b_mesh_create(&d);
+  // what d4b_mesh_set_nonlinear_term needs to regenerate positions / J at the quadrature points
+  m->has_geom = true;
+  m->gdesc = *geom;
+  const size_t E = (size_t)topo->n_local;
+  m->g_tree.assign(geom->elem_tree, geom->elem_tree + E);
+  m->g_q.assign(geom->elem_q, geom->elem_q + 3 * E);
+  m->g_dq.assign(geom->elem_dq, geom->elem_dq + E);
+  m->h_deg.assign(topo->deg, topo->deg + E);
+  m->h_deg_quad.assign(topo->deg_quad, topo->deg_quad + E);
+  m->h_nodal_stride.assign(topo->nodal_stride, topo->nodal_stride + E);
+  m->h_quad_stride.assign(topo->quad_stride, topo->quad_stride + E);
+  m->gdesc.elem_tree = m->gdesc.elem_q = m->gdesc.elem_dq = nullptr;
+  m->gdesc.ghost_tree = m->gdesc.ghost_q = m->gdesc.ghost_dq = nullptr;
+  return m;
 }

@@ -7,6 +7,7 @@
 
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <functional>
 #include <vector>
 #include "d4est_b200.h"
 
@@ -76,6 +77,7 @@ struct D4bEpilogue {
   double *p = nullptr, *u = nullptr;
   double alpha = 0., beta = 0.;
   const double *coef = nullptr;   // mode 1: {alpha, beta} in device memory instead of the two arguments
+  const double *add = nullptr;    // every mode: s += add[i] first (the coarse-level Galerkin mass term, d4b_mg.cu)
 };
 
 // halo exchange with one neighbour rank; offsets / counts in doubles
@@ -151,6 +153,19 @@ struct d4b_mesh {
   double *h_red = nullptr;         // pinned
   double *d_work[4] = {nullptr, nullptr, nullptr, nullptr};
 
+  // nonlinear mass-type term f(x,u) = a(x) (b(x) + u)^k (d4b_nonlinear.cu): w J a and b at the quadrature points
+  double *d_nl_wja = nullptr, *d_nl_b = nullptr;
+  int nl_k = 0;
+  // coarse multigrid level under a linearised finest level: pre_apply(u) leaves the Galerkin mass term
+  // P^T M P u in d_addterm before every apply, the kernels' epilogue adds it (d4b_mg_set_coarse_mass)
+  std::function<bool(d4b_mesh *, const double *)> pre_apply;
+  double *d_addterm = nullptr;
+  // meshes created with device geometry keep what is needed to regenerate positions / J on demand
+  bool has_geom = false;
+  d4b_geom_desc_t gdesc;
+  std::vector<int32_t> h_deg, h_deg_quad, g_tree, g_q, g_dq;
+  std::vector<int64_t> h_nodal_stride, h_quad_stride;
+
   // fast path
   std::vector<D4bFastClass> fast;
   int n_generic = 0;
@@ -177,8 +192,10 @@ T *d4b_dev_upload(d4b_mesh *m, const T *h, size_t n);
 // kernels / launchers
 void d4b_launch_generic(d4b_mesh *m, const double *d_u, double *d_Au, int stiffness_only);
 // volume quadrature operators on device pointers (d4b_generic.cu): mode 0 interpolate,
-// 1 Galerkin integral, 2 mass matrix, 3 out_quad = w jac
+// 1 Galerkin integral, 2 mass matrix, 3 out_quad = w jac, 4 out = V^T diag(jac) V in (weights already in jac),
+// 5 out = V^T (wja (b + V in)^k), 6 out_quad = k wja (b + V in)^(k-1)   (5, 6: d4b_launch_quad_nl)
 void d4b_launch_quad_op(d4b_mesh *m, int mode, const double *d_in, const double *d_jac, double *d_out);
+void d4b_launch_quad_nl(d4b_mesh *m, int mode, const double *d_in, double *d_out);
 // d4est_estimator_bi_compute on device pointers (d4b_generic.cu); ghost values of u must be in m->d_ughost
 void d4b_launch_estimator(d4b_mesh *m, const double *d_u, const double *d_r, const double *d_jac, const double *d_diam,
                           const double *d_sj, const double *d_hm, const double *d_hp, const double *d_g, int family,

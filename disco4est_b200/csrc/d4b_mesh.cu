@@ -386,7 +386,7 @@ extern "C" void d4b_mesh_destroy(d4b_mesh_t *m) {
                   m->d_side_mortar_stride, m->d_mortar, m->d_ughost, m->d_u_stage, m->d_Au_stage,
                   m->d_red, m->d_work[0], m->d_work[1], m->d_work[2], m->d_work[3], m->d_generic_elem,
                   m->d_fast_FF, m->d_uhat, m->d_flat_FF, m->d_hp_tabs, m->d_hp_tabdata, m->d_extra, m->d_send_src, m->d_send_dst, m->d_send_cnt,
-                  m->d_sendbuf, m->d_W};
+                  m->d_sendbuf, m->d_W, m->d_nl_wja, m->d_nl_b, m->d_addterm};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   for (auto &c : m->fast) {

@@ -10,6 +10,7 @@
 // (eigenvalue re-use rules included) and the CG / Chebyshev bottom solvers.
 // All level vectors stay in HBM; the only host traffic is the scalars of the
 // dot products that steer CG and the stopping tests.
+#include <algorithm>
 #include <cmath>
 #include <cstring>
 #include <cstdlib>
@@ -41,6 +42,11 @@ struct d4b_mg {
   std::vector<CycleGraph> graphs;
   double *d_r2 = nullptr;        // squared residual of the last cycle
   cudaStream_t cap_stream = nullptr;
+  // Galerkin mass term of the coarse levels (d4b_mg_set_coarse_mass): per level l >= 1 a prolonged copy of the
+  // input and the weighted / restricted result on the way back
+  int coarse_mass = 0;
+  std::vector<double *> d_mw, d_mt;
+  double *d_W0 = nullptr;        // mode 1: w J f_u(x, 0) on the finest level (see d4b_mg_set_coarse_mass)
 };
 
 namespace {
@@ -70,6 +76,46 @@ __global__ void __launch_bounds__(128) transfer_kernel(int dir, int accumulate, 
   const int nH = deg_c[e] + 1, nH3 = nH * nH * nH;
   const int64_t sH = stride_c[e];
   const int first = child_first[e], count = child_count[e];
+  if (dir == 2 && count == 8) {
+    // What the reference's multigrid matrix operator EXECUTES for an h-coarsened family
+    // (d4est_operators_compute_PT_mat_P, src/dGMath/d4est_operators.c:608-661): it transposes the stacked
+    // prolongation [sum_i n_i x nH3] as a whole (:638) and then takes, for child i, the CONTIGUOUS slice
+    // PT[off_i nH3 ...) of that transpose as if it were P_i^T (:650) -- which it is only for a single child.
+    // The slice read as an [nH3 x n_i] row-major matrix is  Q_i[a][b] = Pstack[k][j]  with
+    // f = off_i nH3 + a n_i + b, j = f / total, k = f % total.  out_H = sum_i Q_i in_i.
+    int nh3[8], off[9];
+    off[0] = 0;
+    for (int c = 0; c < 8; ++c) {
+      const int nh = deg_f[first + c] + 1;
+      nh3[c] = nh * nh * nh;
+      off[c + 1] = off[c] + nh3[c];
+    }
+    const int total = off[8];
+    for (int a = threadIdx.x; a < nH3; a += blockDim.x) {
+      double acc = 0.;
+      for (int i = 0; i < 8; ++i) {
+        const double *y = in + stride_f[first + i];
+        const int64_t f0 = (int64_t)off[i] * nH3 + (int64_t)a * nh3[i];
+        for (int b = 0; b < nh3[i]; ++b) {
+          const int64_t f = f0 + b;
+          const int j = (int)(f / total), k = (int)(f % total);
+          int c = 0;
+          while (k >= off[c + 1]) ++c;
+          const int m = k - off[c];
+          const int nh = deg_f[first + c] + 1;
+          const int tb = ((nH - 2) * 7 + (nh - 2)) * 3;
+          const double *Px = P + P_off[tb + 1 + (c & 1)], *Py = P + P_off[tb + 1 + ((c >> 1) & 1)],
+                       *Pz = P + P_off[tb + 1 + ((c >> 2) & 1)];
+          const int mx = m % nh, my = (m / nh) % nh, mz = m / (nh * nh);
+          const int jx = j % nH, jy = (j / nH) % nH, jz = j / (nH * nH);
+          acc += Px[mx * nH + jx] * Py[my * nH + jy] * Pz[mz * nH + jz] * y[b];
+        }
+      }
+      out[sH + a] = acc;
+    }
+    return;
+  }
+  if (dir == 2) dir = 1;
   if (dir == 0) {
     for (int i = threadIdx.x; i < nH3; i += blockDim.x) sAcc[i] = in[sH + i];
   } else {
@@ -158,6 +204,35 @@ __global__ void resid_k(const double *__restrict__ rhs, const double *__restrict
 int grid_for(int64_t n) {
   int64_t b = (n + 255) / 256;
   return (int)(b < 148 * 8 ? (b > 0 ? b : 1) : 148 * 8);
+}
+
+// t = P_l^T ... P_{top-1}^T (V^T diag(W) V) P_{top-1} ... P_l u on coarse level l: what the reference's dense
+// per-element matrices PT_mat_P of the multigrid matrix operator apply
+// (d4est_solver_multigrid_matrix_operator.c:5-47; d4est_operators_compute_PT_mat_P), matrix-free.
+// Returns false (nothing to add) while the finest level is not linearised.
+bool coarse_mass_term(d4b_mg *g, int l, const double *u) {
+  const int top = g->n_levels - 1;
+  d4b_mesh *mt = g->mesh[top], *ml = g->mesh[l];
+  if (!g->coarse_mass || !mt->d_W) return false;
+  // every level shares the top stream inside a V-cycle; a stand-alone coarse apply runs on its own
+  // stream and the level vectors are ordered through it
+  cudaStream_t s = ml->stream;
+  std::vector<cudaStream_t> saved(g->n_levels);
+  for (int j = l; j <= top; ++j) {
+    saved[j] = g->mesh[j]->stream;
+    if (saved[j] != s) { D4B_CUDA(cudaStreamSynchronize(saved[j])); g->mesh[j]->stream = s; }
+  }
+  const double *in = u;
+  for (int j = l; j < top; ++j) {
+    transfer(g, 0, 0, j, in, g->d_mw[j + 1]);
+    in = g->d_mw[j + 1];
+  }
+  d4b_launch_quad_op(mt, 4, in, g->coarse_mass == 1 ? g->d_W0 : mt->d_W, g->d_mt[top]);
+  // mode 1: the slices the reference executes (transfer_kernel dir 2); mode 2: the Galerkin product P^T M P
+  const int back = g->coarse_mass == 1 ? 2 : 1;
+  for (int j = top - 1; j >= l; --j) transfer(g, back, 0, j, g->d_mt[j + 1], j == l ? ml->d_addterm : g->d_mt[j]);
+  for (int j = l; j <= top; ++j) g->mesh[j]->stream = saved[j];
+  return true;
 }
 
 // Chebyshev smoother of one level, d4est_solver_multigrid_smoother_cheby.c:264-376; the
@@ -386,6 +461,47 @@ extern "C" d4b_mg_t *d4b_mg_create(const d4b_mg_desc_t *desc) {
 
 d4b_mesh *d4b_mg_top_mesh(d4b_mg *g) { return g->mesh[g->n_levels - 1]; }
 
+extern "C" void d4b_mg_set_coarse_mass(d4b_mg_t *g, int32_t mode) {
+  D4B_CHECK(g && mode >= 0 && mode <= 2, "d4b_mg_set_coarse_mass: bad argument");
+  const int top = g->n_levels - 1;
+  for (d4b_mesh *m : g->mesh) D4B_CUDA(cudaStreamSynchronize(m->stream));
+  g->coarse_mass = mode;
+  if (mode == 1) {
+    // The reference builds the fine matrices of its matrix operator with the arguments of
+    // d4est_quadrature_apply_fofufofvlilj shifted by one (d4est_solver_multigrid_matrix_operator.c:215-240 passes
+    // u0 in the `vec` slot and NULL in the `u` slot), so f_u is evaluated at u = 0 whatever the linearisation
+    // point is (src/Quadrature/d4est_quadrature.c:663-671): the coarse mass term never changes during a Newton solve.
+    d4b_mesh *mt = g->mesh[top];
+    D4B_CHECK(mt->d_nl_wja, "d4b_mg_set_coarse_mass(REFERENCE): the finest mesh has no nonlinear term "
+                            "(d4b_mesh_set_nonlinear_term); use D4B_COARSE_MASS_GALERKIN with d4b_mesh_set_mass_diag");
+    if (!g->d_W0) g->d_W0 = d4b_dev_alloc<double>(mt, (size_t)mt->local_nodes_quad);
+    double *zero = nullptr;
+    D4B_CUDA(cudaMalloc(&zero, std::max<size_t>((size_t)mt->local_nodes, 1) * sizeof(double)));
+    D4B_CUDA(cudaMemsetAsync(zero, 0, (size_t)mt->local_nodes * sizeof(double), mt->stream));
+    d4b_launch_quad_nl(mt, 6, zero, g->d_W0);
+    D4B_CUDA(cudaStreamSynchronize(mt->stream));
+    cudaFree(zero);
+  }
+  if (mode && g->d_mw.empty()) {
+    g->d_mw.assign(g->n_levels, nullptr);
+    g->d_mt.assign(g->n_levels, nullptr);
+    for (int l = 1; l <= top; ++l) {
+      g->d_mw[l] = d4b_dev_alloc<double>(g->mesh[l], (size_t)g->mesh[l]->local_nodes);
+      g->d_mt[l] = d4b_dev_alloc<double>(g->mesh[l], (size_t)g->mesh[l]->local_nodes);
+    }
+  }
+  for (int l = 0; l < top; ++l) {
+    d4b_mesh *m = g->mesh[l];
+    m->config_epoch++;
+    if (mode) {
+      if (!m->d_addterm) m->d_addterm = d4b_dev_alloc<double>(m, (size_t)m->local_nodes);
+      m->pre_apply = [g, l](d4b_mesh *, const double *u) { return coarse_mass_term(g, l, u); };
+    } else {
+      m->pre_apply = nullptr;
+    }
+  }
+}
+
 extern "C" void d4b_mg_destroy(d4b_mg_t *g) {
   if (!g) return;
   for (d4b_mesh *m : g->mesh) cudaStreamSynchronize(m->stream);
@@ -394,6 +510,10 @@ extern "C" void d4b_mg_destroy(d4b_mg_t *g) {
   for (auto p : g->d_u) if (p) cudaFree(p);
   for (auto p : g->d_rhs) if (p) cudaFree(p);
   for (auto p : g->d_r) if (p) cudaFree(p);
+  for (auto p : g->d_mw) if (p) cudaFree(p);
+  for (auto p : g->d_mt) if (p) cudaFree(p);
+  if (g->d_W0) cudaFree(g->d_W0);
+  for (int l = 0; l + 1 < g->n_levels; ++l) g->mesh[l]->pre_apply = nullptr;
   if (g->d_top_u) cudaFree(g->d_top_u);
   if (g->d_top_rhs) cudaFree(g->d_top_rhs);
   cudaFree(g->d_P); cudaFree(g->d_P_off);

@@ -14,7 +14,8 @@ import os
 
 import numpy as np
 
-from .abi import EST_FAMILY, GEOM_ARRAY_FIELDS, ChebyParams, EstimatorDesc, GeomArrays, GeomDesc, MeshDesc, MgDesc, make_desc, make_geom_desc
+from .abi import (EST_FAMILY, GEOM_ARRAY_FIELDS, NL_KIND, ChebyParams, EstimatorDesc, GeomArrays, GeomDesc, MeshDesc, MgDesc,
+                  NewtonParams, NewtonStats, NonlinearDesc, make_desc, make_geom_desc)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 # D4B_LIBRARY_PATH lets profiling scripts A/B differently compiled builds of the same library
@@ -33,6 +34,7 @@ EXPORTS = [
     "d4b_mg_create", "d4b_mg_destroy", "d4b_mg_vcycle", "d4b_mg_solve", "d4b_mg_get_eigs", "d4b_mg_restrict",
     "d4b_mg_prolong",
     "d4b_cg_solve", "d4b_fcg_solve",
+    "d4b_mesh_set_nonlinear_term", "d4b_mesh_linearize", "d4b_build_residual", "d4b_mg_set_coarse_mass", "d4b_newton_solve",
     "d4b_comm_get_unique_id", "d4b_comm_init", "d4b_comm_destroy", "d4b_comm_size", "d4b_comm_rank",
 ]
 
@@ -109,6 +111,13 @@ def load_library():
     L.d4b_fcg_solve.restype = C.c_int32
     L.d4b_fcg_solve.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_double, C.c_double,
                                 C.c_int32, C.c_void_p]
+    L.d4b_mesh_set_nonlinear_term.argtypes = [C.c_void_p, C.POINTER(NonlinearDesc)]
+    L.d4b_mesh_linearize.argtypes = [C.c_void_p, C.c_void_p]
+    L.d4b_build_residual.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.d4b_mg_set_coarse_mass.argtypes = [C.c_void_p, C.c_int32]
+    L.d4b_newton_solve.restype = C.c_int32
+    L.d4b_newton_solve.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(NewtonParams),
+                                   C.POINTER(NewtonStats)]
     L.d4b_comm_get_unique_id.argtypes = [C.c_void_p]
     L.d4b_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int]
     L.d4b_comm_size.restype = C.c_int
@@ -158,6 +167,11 @@ class Multigrid:
         hist = np.zeros(self.vcycle_imax + 1)
         n = int(self.L.d4b_mg_solve(self.h, _ptr(u), _ptr(rhs), hist.ctypes.data))
         return n, hist[: n + 1]
+
+    def set_coarse_mass(self, mode="reference"):
+        """the reference's multigrid matrix operator on the coarse levels of a linearised problem: "reference" =
+        what it executes (d4b_mg_set_coarse_mass mode 1), "galerkin" = P^T M P (mode 2), None / False = off"""
+        self.L.d4b_mg_set_coarse_mass(self.h, {None: 0, False: 0, "off": 0, "reference": 1, True: 1, "galerkin": 2}[mode])
 
     def eigs(self):
         e = np.zeros(len(self.meshes))
@@ -335,6 +349,50 @@ class Mesh:
             eta2 = np.zeros(int(self.desc.n_local))
         self.L.d4b_estimator_bi(self.h, C.byref(d), _ptr(eta2), None if terms is None else _ptr(terms))
         return eta2
+
+    def set_nonlinear_term(self, kind=None, punctures=None, star=None, xyz_quad=None, jac_quad=None, a_quad=None,
+                           b_quad=None, exponent=0):
+        """attach f(x, u) = a(x) (b(x) + u)^k (d4b_mesh_set_nonlinear_term); kind None removes it.
+        punctures: array [n][10] = M, X, Y, Z, PX, PY, PZ, SX, SY, SZ; star: (rho0, R, cx, cy, cz)"""
+        if kind is None:
+            self.L.d4b_mesh_set_nonlinear_term(self.h, None)
+            return
+        d = NonlinearDesc()
+        d.kind = NL_KIND[kind]
+        if punctures is not None:
+            P = np.asarray(punctures, dtype=np.float64).reshape(-1, 10)
+            d.n_punctures = P.shape[0]
+            for i in range(P.shape[0]):
+                for j in range(10):
+                    d.punctures[i][j] = float(P[i, j])
+        if star is not None:
+            d.star_rho0, d.star_R = float(star[0]), float(star[1])
+            for j in range(3):
+                d.star_c[j] = float(star[2 + j])
+        d.exponent = int(exponent)
+        for name, val in (("a_quad", a_quad), ("b_quad", b_quad), ("xyz_quad", xyz_quad), ("jac_quad", jac_quad)):
+            setattr(d, name, None if val is None else _ptr(val))
+        self.L.d4b_mesh_set_nonlinear_term(self.h, C.byref(d))
+
+    def linearize(self, u0):
+        """every later apply is the Jacobian about u0 (None drops the mass-type term)"""
+        self.L.d4b_mesh_linearize(self.h, None if u0 is None else _ptr(u0))
+
+    def build_residual(self, u, F, rhs=None):
+        """F = A(u) + N(u) - rhs (d4b_build_residual)"""
+        self.L.d4b_build_residual(self.h, _ptr(u), None if rhs is None else _ptr(rhs), _ptr(F))
+
+    def newton_solve(self, u, pc=None, mesh_jac=None, atol=1e-15, rtol=1e-8, imin=1, imax=20, fcg_atol=1e-15,
+                     fcg_rtol=5e-2, fcg_imax=100, fcg_flags=0):
+        """d4est_solver_newton_solve + d4est_solver_fcg_solve + the V-cycle preconditioner on the device;
+        returns (ierr, steps, fcg iterations per step, residual norms, fine-level Jacobian applies)"""
+        prm = NewtonParams(atol, rtol, imin, imax, fcg_atol, fcg_rtol, fcg_imax, fcg_flags)
+        st = NewtonStats()
+        mj = mesh_jac if mesh_jac is not None else self
+        ierr = int(self.L.d4b_newton_solve(self.h, mj.h, pc.h if pc is not None else None, _ptr(u), C.byref(prm),
+                                           C.byref(st)))
+        n = int(st.steps)
+        return ierr, n, list(st.fcg_iterations[:n]), list(st.residual_norm[:n + 1]), int(st.jacobian_applies)
 
     def set_mass_diag(self, jac_quad):
         """every later apply adds V^T diag(w jac_quad) V u (None removes the term)"""

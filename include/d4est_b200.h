@@ -241,6 +241,8 @@ typedef struct d4b_geom_arrays
   double *sj_m_mortar_quad, *n_m_mortar_quad;
   double *drst_dxyz_m_mortar_quad, *drst_dxyz_p_mortar_quad_porder;
   double *hm_mortar_quad, *hp_mortar_quad;
+  double *xyz_quad;                   /* [3*local_nodes_quad]: d*local_nodes_quad + quad_stride + k
+                                         (d4est_mesh_data_t.xyz_quad) */
 } d4b_geom_arrays_t;
 
 /* `topo` supplies sizes, degrees, strides and side records; its geometric arrays are not read */
@@ -474,6 +476,98 @@ void      d4b_mg_prolong(d4b_mg_t *mg, int32_t coarse_level, const double *coars
 int32_t d4b_cg_solve(d4b_mesh_t *mesh, double *u, const double *rhs, int32_t imax, double rtol, double atol);
 int32_t d4b_fcg_solve(d4b_mesh_t *mesh, d4b_mg_t *pc, double *u, const double *rhs, int32_t imax,
                       double rtol, double atol, int32_t flags, double *r2_history);
+
+/* ------------------------------------------- nonlinear mass-type terms (Newton)  */
+/* The shipped nonlinear problems are  -lap u + f(x, u) = 0  with a point-wise f; the reference
+ * integrates f and f_u against the basis element by element on the host,
+ *   residual:  d4est_quadrature_apply_fofufofvlj   (src/Quadrature/d4est_quadrature.c:776-936)
+ *   Jacobian:  d4est_quadrature_apply_fofufofvlilj (:593-774, QUAD_APPLY_MATRIX)
+ * with f given as a d4est_xyzu_fcn_t callback.  Every shipped f has the form
+ *       f(x, u) = a(x) (b(x) + u)^k ,   f_u = k a(x) (b(x) + u)^(k-1) ,   k an integer:
+ *   two punctures     a = -K^2(x) / 8,  b = 1 + sum_n m_n / (2 r_n),  k = -7
+ *                     (multi_punctures_neg_1o8_K2_psi_neg7 / _plus_7o8_K2_psi_neg8,
+ *                      src/Problems/TwoPunctures/multi_punctures_fcns_with_opt.h:292-423)
+ *   constant density  a = -2 pi rho(x), b = 0, k = 5, rho = rho0 inside radius R of c, else 0
+ *   star              (neg_2pi_rho_up1_neg5 / neg_10pi_rho_up1_neg4,
+ *                      src/Problems/ConstantDensityStar/constant_density_star_fcns.h:334-360)
+ * These are DEVICE FUNCTORS here: a(x), b(x) are evaluated once per mesh by a kernel at the
+ * quadrature points, (b + V u)^k inside the residual / linearisation kernels; no callback is
+ * evaluated on the host and only u crosses the bus.                                              */
+typedef enum {
+  D4B_NL_PUNCTURES = 1,              /* a, b from the puncture list                              */
+  D4B_NL_CONSTANT_DENSITY_STAR = 2,  /* a from the density step                                  */
+  D4B_NL_TABLE = 3                   /* a_quad, b_quad, exponent supplied by the caller           */
+} d4b_nonlinear_kind_t;
+#define D4B_MAX_PUNCTURES 10
+typedef struct d4b_nonlinear_desc
+{
+  int32_t kind;
+  int32_t n_punctures;
+  double  punctures[D4B_MAX_PUNCTURES][10];  /* M, X, Y, Z, PX, PY, PZ, SX, SY, SZ (black_hole_data_t) */
+  double  star_rho0, star_R, star_c[3];
+  int32_t exponent;                  /* D4B_NL_TABLE only                                         */
+  const double *a_quad, *b_quad;     /* D4B_NL_TABLE only, [local_nodes_quad]                     */
+  const double *xyz_quad;            /* [3*local_nodes_quad] d4est_mesh_data_t.xyz_quad; NULL for a mesh
+                                        created by d4b_mesh_create_with_geometry (positions kept)  */
+  const double *jac_quad;            /* [local_nodes_quad] J_quad; NULL likewise                  */
+} d4b_nonlinear_desc_t;
+/* attach f to the mesh (desc == NULL removes it); host or device arrays                          */
+void d4b_mesh_set_nonlinear_term(d4b_mesh_t *mesh, const d4b_nonlinear_desc_t *desc);
+/* Newton linearisation about u0: from now on every apply of `mesh` (d4b_apply, smoother, Krylov)
+ * is the Jacobian  A + V^T diag(w J f_u(x, V u0)) V  -- what multi_punctures_apply_jac computes
+ * (multi_punctures_fcns_with_opt.h:546-624).  u0 host or device; u0 == NULL drops the term.       */
+void d4b_mesh_linearize(d4b_mesh_t *mesh, const double *u0);
+/* the build_residual callback of d4est_elliptic_eqns_t (src/EllipticSystem/d4est_elliptic_eqns.h:26-37)
+ * on the device:  F = A(u) + V^T (w J f(x, V u)) - rhs   with A(u) the operator of `mesh` INCLUDING its
+ * boundary data, the middle term only when a nonlinear term is attached, rhs == NULL meaning 0:
+ *   Poisson  F = A u - rhs            (poisson_build_residual, src/Problems/Poisson/poisson_sinx_fcns.h:133-149)
+ *   punctures F = A u + N(u)          (multi_punctures_build_residual, ...with_opt.h:706-750)
+ * Any linearisation of `mesh` is ignored here.  Host or device pointers.                          */
+void d4b_build_residual(d4b_mesh_t *mesh, const double *u, const double *rhs, double *F);
+
+/* The reference's multigrid "matrix operator" for such Jacobians
+ * (src/Solver/d4est_solver_multigrid_matrix_operator.c:5-47, :170-250): below the finest level the mass-type
+ * term is meant to be the Galerkin product  M_l = P^T M_{l+1} P  of the finest level's V^T diag(W) V, element
+ * family by element family, stored as dense matrices.  Applied here matrix-free on every coarse level of `mg`
+ * whenever the finest mesh is linearised (prolong to the finest level, weight, come back down):
+ *   mode 0 (default): coarse levels are plain Laplacians
+ *   mode 1: what the reference EXECUTES.  d4est_operators_compute_PT_mat_P (src/dGMath/d4est_operators.c:608-661)
+ *           transposes the stacked prolongation of a family as a whole and then uses a contiguous slice of that
+ *           transpose as "P_i^T" (:638, :650), which is the transpose only for a single child (p-coarsening);
+ *           for an h-coarsened family of 8 the slice is another matrix Q_i, so M_l = sum_i Q_i M_i P_i.
+ *           And its fine matrices are built with the arguments of d4est_quadrature_apply_fofufofvlilj shifted by
+ *           one (d4est_solver_multigrid_matrix_operator.c:215-240: u0 lands in the unused `vec` slot, NULL in `u`),
+ *           so f_u is evaluated at u = 0 for every linearisation point: W = w J f_u(x, 0) on the coarse levels.
+ *           Needs the nonlinear term on the finest mesh.  Iterates and iteration counts of the reference's Newton-Krylov runs are reproduced only with this.
+ *   mode 2: the Galerkin product the reference's comments describe.                                          */
+#define D4B_COARSE_MASS_OFF 0
+#define D4B_COARSE_MASS_REFERENCE 1
+#define D4B_COARSE_MASS_GALERKIN 2
+void d4b_mg_set_coarse_mass(d4b_mg_t *mg, int32_t mode);
+
+/* d4est_solver_newton_solve (src/Solver/d4est_solver_newton.c:136-367) with d4est_solver_fcg_solve as the
+ * Krylov callback and the V-cycle hierarchy `pc` (may be NULL) as preconditioner, device-resident:
+ *   F_0 = F(u); while (|F| > atol + rtol |F_0| or it < imin) and it < imax:
+ *     linearise about u; solve J step = -F with FCG from a zero guess; u += step; F = F(u).
+ * mesh_res supplies the residual (its boundary data included), mesh_jac the Jacobian (boundary data zeroed,
+ * as the reference asks of flux_data_for_jac); they may be the same handle.  Both need the nonlinear term.
+ * u: initial guess in, solution out (host or device).  Returns 0 when converged, 1 otherwise (ierr).    */
+typedef struct d4b_newton_params
+{
+  double  atol, rtol;                /* [d4est_solver_newton]                                     */
+  int32_t imin, imax;
+  double  fcg_atol, fcg_rtol;        /* [d4est_solver_fcg]                                        */
+  int32_t fcg_imax, fcg_flags;
+} d4b_newton_params_t;
+typedef struct d4b_newton_stats
+{
+  int32_t steps;                     /* Newton steps taken                                        */
+  int32_t fcg_iterations[64];        /* per step                                                  */
+  double  residual_norm[65];         /* |F| before the first and after every step                 */
+  int64_t jacobian_applies;          /* fine-level operator applies inside FCG (not the V-cycles)  */
+} d4b_newton_stats_t;
+int32_t d4b_newton_solve(d4b_mesh_t *mesh_res, d4b_mesh_t *mesh_jac, d4b_mg_t *pc, double *u,
+                         const d4b_newton_params_t *params, d4b_newton_stats_t *stats);
 
 #ifdef __cplusplus
 }

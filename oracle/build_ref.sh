@@ -80,6 +80,7 @@ Solver/d4est_solver_multigrid_mesh_analyzer.c Solver/d4est_solver_multigrid_smoo
 Solver/d4est_solver_multigrid_smoother_none.c Solver/d4est_solver_multigrid_bottom_solver_reuse_smoother.c
 Solver/d4est_solver_cg_eigs.c Solver/d4est_krylov_pc_multigrid.c
 Solver/d4est_solver_fcg_improved.c Solver/d4est_solver_cg.c
+Solver/d4est_solver_newton.c Solver/d4est_solver_multigrid_matrix_operator.c
 Estimators/d4est_estimator_bi.c
 "
 for s in $D8SRCS; do
@@ -89,11 +90,11 @@ emit $HERE/refbuild/miniblas.c obj/d8/miniblas.o "$OPT -fPIC"
 emit $HERE/refbuild/ref_stubs.c obj/d8/ref_stubs.o "$DFLAGS"
 emit $HERE/../disco4est_b200/adapter/d4est_b200_adapter.c obj/d8/d4est_b200_adapter.o \
      "$DFLAGS -DD4EST_B200_ADAPTER_NO_DEVICE -I$HERE/../include -I$HERE/../disco4est_b200/adapter"
-emit $HERE/ref_driver.c obj/d8/ref_driver.o "$DFLAGS -I$HERE -I$HERE/../include -I$HERE/../disco4est_b200/adapter"
+emit $HERE/ref_driver.c obj/d8/ref_driver.o "$DFLAGS -I$REF/src/Problems/TwoPunctures -I$HERE -I$HERE/../include -I$HERE/../disco4est_b200/adapter"
 # device-linked variant: the same driver and adapter with the C ABI library behind them
 emit $HERE/../disco4est_b200/adapter/d4est_b200_adapter.c obj/d8/d4est_b200_adapter_dev.o \
      "$DFLAGS -I$HERE/../include -I$HERE/../disco4est_b200/adapter"
-emit $HERE/ref_driver.c obj/d8/ref_driver_dev.o "$DFLAGS -DD4B_WITH_DEVICE -I$HERE -I$HERE/../include -I$HERE/../disco4est_b200/adapter"
+emit $HERE/ref_driver.c obj/d8/ref_driver_dev.o "$DFLAGS -DD4B_WITH_DEVICE -I$REF/src/Problems/TwoPunctures -I$HERE -I$HERE/../include -I$HERE/../disco4est_b200/adapter"
 
 if [ -s "$CMDS" ]; then
   echo "build_ref.sh: compiling $(wc -l < "$CMDS") files"

@@ -55,3 +55,9 @@ run sphere_p_pen_maxpp1 _pen_maxpp1.ini --bc poly --no-opt
 run sphere_p_pen_meanp_mult _pen_meanp_mult.ini --bc poly
 run sphere_p_pen_meanph _pen_meanph.ini --bc poly
 rm -f "$HERE"/configs/_pen_*.ini
+# BASELINE configs[4] in small: two punctures on the 13-tree sphere (Robin outer boundary), the reference's in-house
+# Newton -> FCG -> multigrid (matrix operator for the mass-type term): Newton steps, FCG iterations per step,
+# residual norms, final u; residual F(u) and Jacobian J(u0) v samples with the unmodified puncture callbacks
+"$DRV" "$HERE/configs/sphere_punctures.ini" "$G/sphere_punctures_newton.d4b" --newton | tail -1 > "$G/sphere_punctures_newton.json"
+gzip -9nf "$G/sphere_punctures_newton.d4b"
+echo "sphere_punctures_newton: $(cat "$G/sphere_punctures_newton.json")"

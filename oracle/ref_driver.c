@@ -31,7 +31,12 @@
 #include <d4est_solver_fcg_improved.h>
 #include <d4est_solver_cg.h>
 #include <d4est_estimator_bi.h>
+#include <d4est_solver_newton.h>
+#include <d4est_solver_multigrid_matrix_operator.h>
 #include <d4est_util.h>
+/* the two-puncture problem callbacks of the reference, used as they are
+ * (src/Problems/TwoPunctures/multi_punctures_fcns_with_opt.h; found through -I src/Problems/TwoPunctures) */
+#include <multi_punctures_fcns_with_opt.h>
 #include <zlog.h>
 #include <time.h>
 #include <sys/time.h>
@@ -229,12 +234,16 @@ static d4est_krylov_pc_apply_fcn_t fcg_inner_pc_apply;
 static int fcg_pc_calls, fcg_nodes;
 static double fcg_r2_hist[512];
 
+static double *fcg_first_pc_x, *fcg_first_pc_y;   /* when set: input / output of the first preconditioner call */
+
 static void
 fcg_counting_pc_apply (d4est_krylov_pc_t * kpc, double *x, double *y)
 {
   if (fcg_pc_calls < 512) fcg_r2_hist[fcg_pc_calls] = d4est_linalg_vec_dot (x, x, fcg_nodes);
+  if (fcg_pc_calls == 0 && fcg_first_pc_x) memcpy (fcg_first_pc_x, x, sizeof (double) * fcg_nodes);
   fcg_pc_calls++;
   fcg_inner_pc_apply (kpc, x, y);
+  if (fcg_pc_calls == 1 && fcg_first_pc_y) memcpy (fcg_first_pc_y, y, sizeof (double) * fcg_nodes);
 }
 
 static d4est_apply_operator_fcn_t cg_inner_apply_lhs;
@@ -271,6 +280,198 @@ star_like_res_fcn (double x, double y, double z, double u, void *user)
   return -2. * M_PI * star_like_rho (x, y, z) * (1. + u) * (1. + u) * (1. + u) * (1. + u) * (1. + u);
 }
 
+/* ---- BASELINE configs[4]: the reference's in-house Newton-Krylov-multigrid stack on the two-puncture problem,
+ * wired as src/Problems/TwoPunctures/multi_punctures_anares_inhouse.c:849-964 does, with recording wrappers
+ * around the callbacks (the solvers report through zlog only). */
+#define NEWTON_MAX_STEPS 64
+static d4est_apply_operator_fcn_t nw_inner_build_residual;
+static int nw_res_calls, nw_nodes;
+static double nw_fnrm[NEWTON_MAX_STEPS + 1];
+static int nw_pc_calls_at_res[NEWTON_MAX_STEPS + 1];
+
+static void
+nw_recording_build_residual (p4est_t * p4est, d4est_ghost_t * ghost, d4est_ghost_data_t * ghost_data,
+                             d4est_elliptic_data_t * prob_vecs, d4est_operators_t * d4est_ops,
+                             d4est_geometry_t * d4est_geom, d4est_quadrature_t * d4est_quad,
+                             d4est_mesh_data_t * d4est_factors, void *user)
+{
+  nw_inner_build_residual (p4est, ghost, ghost_data, prob_vecs, d4est_ops, d4est_geom, d4est_quad, d4est_factors, user);
+  if (nw_res_calls <= NEWTON_MAX_STEPS) {
+    nw_fnrm[nw_res_calls] = sqrt (d4est_linalg_vec_dot (prob_vecs->Au, prob_vecs->Au, nw_nodes));
+    nw_pc_calls_at_res[nw_res_calls] = fcg_pc_calls;
+  }
+  nw_res_calls++;
+}
+
+/* D4B_NW_TRACE=1: one line per operator application during the first preconditioner call (debugging aid) */
+static d4est_apply_operator_fcn_t nw_inner_apply_lhs;
+static void
+nw_tracing_apply_lhs (p4est_t * p4est, d4est_ghost_t * ghost, d4est_ghost_data_t * ghost_data,
+                      d4est_elliptic_data_t * prob_vecs, d4est_operators_t * d4est_ops,
+                      d4est_geometry_t * d4est_geom, d4est_quadrature_t * d4est_quad,
+                      d4est_mesh_data_t * d4est_factors, void *user)
+{
+  nw_inner_apply_lhs (p4est, ghost, ghost_data, prob_vecs, d4est_ops, d4est_geom, d4est_quad, d4est_factors, user);
+  if (getenv ("D4B_NW_TRACE") && fcg_pc_calls == atoi (getenv ("D4B_NW_TRACE")))
+    fprintf (stderr, "APPLY pc_calls=%d n=%d |u|=%.15e |Au|=%.15e\n", fcg_pc_calls, prob_vecs->local_nodes,
+             sqrt (d4est_linalg_vec_dot (prob_vecs->u, prob_vecs->u, prob_vecs->local_nodes)),
+             sqrt (d4est_linalg_vec_dot (prob_vecs->Au, prob_vecs->Au, prob_vecs->local_nodes)));
+}
+
+static void
+run_newton (p4est_t * p4est, d4est_ghost_t ** d4est_ghost, d4est_ghost_data_t ** d4est_ghost_data,
+            d4est_operators_t * d4est_ops, d4est_geometry_t * d4est_geom, d4est_quadrature_t * d4est_quad,
+            d4est_mesh_data_t * d4est_factors, d4est_mesh_initial_extents_t * initial_grid_input,
+            const char *ini, const char *out, int local_nodes)
+{
+  d4est_field_type_t field_type = NODAL;
+  multi_punctures_params_t *mp = multi_punctures_params_init (p4est, ini);
+  problem_ctx_t ctx;
+  memset (&ctx, 0, sizeof (ctx));
+  ctx.multi_punctures_params = mp;
+
+  /* Robin outer boundary exactly as the problem file sets it up (multi_punctures_anares_inhouse.c:640-668) */
+  d4est_laplacian_with_opt_robin_bc_t bc_robin;
+  bc_robin.robin_coeff = multi_punctures_robin_coeff_sphere_fcn;
+  bc_robin.robin_rhs = multi_punctures_robin_bc_rhs_fcn;
+  bc_robin.user = NULL;
+  d4est_laplacian_with_opt_flux_data_t *flux_jac = d4est_laplacian_with_opt_flux_new (p4est, ini, BC_ROBIN, &bc_robin);
+  d4est_laplacian_with_opt_flux_data_t *flux_res = d4est_laplacian_with_opt_flux_new (p4est, ini, BC_ROBIN, &bc_robin);
+  ctx.flux_data_for_jac = flux_jac;
+  ctx.flux_data_for_res = flux_res;
+  /* the same boundary through the plain flux: only used to flatten the mesh for the fixture */
+  d4est_laplacian_robin_bc_t bc_plain;
+  bc_plain.robin_coeff = (d4est_laplacian_mortar_xyz_fcn_t) multi_punctures_robin_coeff_sphere_fcn;
+  bc_plain.robin_rhs = (d4est_laplacian_mortar_xyz_fcn_t) multi_punctures_robin_bc_rhs_fcn;
+  bc_plain.user = NULL;
+  d4est_laplacian_flux_data_t *flux_plain = d4est_laplacian_flux_new (p4est, ini, BC_ROBIN, &bc_plain);
+
+  d4est_elliptic_eqns_t prob_fcns;
+  prob_fcns.build_residual = multi_punctures_build_residual;
+  prob_fcns.apply_lhs = multi_punctures_apply_jac;
+  prob_fcns.user = &ctx;
+
+  double *u = P4EST_ALLOC_ZERO (double, local_nodes);
+  double *Au = P4EST_ALLOC_ZERO (double, local_nodes);
+  double *rhs = P4EST_ALLOC_ZERO (double, local_nodes);
+  d4est_elliptic_data_t vecs;
+  memset (&vecs, 0, sizeof (vecs));
+  vecs.u = u; vecs.Au = Au; vecs.rhs = rhs; vecs.local_nodes = local_nodes;
+  vecs.field_types = &field_type; vecs.num_of_fields = 1;
+
+  /* operator-level samples before the solve: residual F(us) and Jacobian J(us) v for seeded us, v
+   * (matrix operator off: the fine level evaluates the quadrature form, multi_punctures_apply_jac) */
+  double *us = P4EST_ALLOC (double, local_nodes), *v = P4EST_ALLOC (double, local_nodes);
+  double *Fus = P4EST_ALLOC_ZERO (double, local_nodes), *Jv = P4EST_ALLOC_ZERO (double, local_nodes);
+  srand (102321);
+  for (int i = 0; i < local_nodes; i++) us[i] = 0.2 * (double) rand () / (double) RAND_MAX - 0.05;
+  for (int i = 0; i < local_nodes; i++) v[i] = (double) rand () / (double) RAND_MAX - 0.5;
+  ctx.use_matrix_operator = 0;
+  {
+    d4est_elliptic_data_t sv = vecs;
+    sv.u = us; sv.Au = Fus;
+    d4est_elliptic_eqns_build_residual (p4est, *d4est_ghost, *d4est_ghost_data, &prob_fcns, &sv, d4est_ops, d4est_geom,
+                                        d4est_quad, d4est_factors);
+    sv.u = v; sv.u0 = us; sv.Au = Jv;
+    d4est_elliptic_eqns_apply_lhs (p4est, *d4est_ghost, *d4est_ghost_data, &prob_fcns, &sv, d4est_ops, d4est_geom,
+                                   d4est_quad, d4est_factors);
+  }
+
+  d4est_solver_multigrid_t *mg_data =
+    d4est_solver_multigrid_data_init (p4est, d4est_ops, d4est_geom, d4est_quad, d4est_ghost, d4est_ghost_data,
+                                      d4est_factors, initial_grid_input, ini);
+  d4est_solver_multigrid_user_callbacks_t *user_callbacks =
+    d4est_solver_multigrid_matrix_operator_init (p4est, mg_data->num_of_levels, 0);
+  d4est_solver_multigrid_set_user_callbacks (mg_data, user_callbacks);
+  d4est_krylov_pc_t *pc = d4est_krylov_pc_multigrid_create (mg_data, multi_punctures_d4est_krylov_pc_setup_fcn);
+  ctx.use_matrix_operator = 1;
+  ctx.mg_data = mg_data;
+
+  d4est_solver_fcg_params_t fcg_params;
+  d4est_solver_fcg_input (p4est, ini, "d4est_solver_fcg", &fcg_params);
+  d4est_solver_newton_params_t np = d4est_solver_newton_input (p4est, ini);
+
+  /* recording wrappers */
+  fcg_inner_pc_apply = pc->pc_apply;
+  pc->pc_apply = fcg_counting_pc_apply;
+  fcg_pc_calls = 0; fcg_nodes = local_nodes;
+  nw_inner_build_residual = prob_fcns.build_residual;
+  prob_fcns.build_residual = nw_recording_build_residual;
+  nw_inner_apply_lhs = prob_fcns.apply_lhs;
+  prob_fcns.apply_lhs = nw_tracing_apply_lhs;
+  nw_res_calls = 0; nw_nodes = local_nodes;
+  fcg_first_pc_x = P4EST_ALLOC_ZERO (double, local_nodes);
+  fcg_first_pc_y = P4EST_ALLOC_ZERO (double, local_nodes);
+
+  double t0 = wall ();
+  int ierr = d4est_solver_newton_solve (p4est, &vecs, &prob_fcns, d4est_ghost, d4est_ghost_data, d4est_ops, d4est_geom,
+                                        d4est_quad, d4est_factors, (char *) ini, d4est_solver_fcg_solve, &fcg_params,
+                                        (mg_data->num_of_levels <= 1) ? NULL : pc, 0);
+  double t_newton = wall () - t0;
+  const int steps = nw_res_calls - 1;
+  double fcg_its[NEWTON_MAX_STEPS];
+  for (int k = 0; k < steps && k < NEWTON_MAX_STEPS; k++)
+    fcg_its[k] = (double) (nw_pc_calls_at_res[k + 1] - nw_pc_calls_at_res[k]);
+  printf ("{\"elements\": %d, \"local_nodes\": %d, \"mg_levels\": %d, \"newton_steps\": %d, \"newton_ierr\": %d, "
+          "\"fcg_iterations_per_step\": [", (int) p4est->local_num_quadrants, local_nodes, mg_data->num_of_levels, steps, ierr);
+  for (int k = 0; k < steps; k++) printf ("%s%d", k ? ", " : "", (int) fcg_its[k]);
+  printf ("], \"residual_norms\": [");
+  for (int k = 0; k <= steps; k++) printf ("%s%.17g", k ? ", " : "", nw_fnrm[k]);
+  printf ("], \"t_newton_s\": %.3f}\n", t_newton);
+
+  if (strcmp (out, "-")) {
+    d4est_b200_flat_t *flat = d4est_b200_flatten (p4est, *d4est_ghost, d4est_factors, flux_plain);
+    FILE *f = d4b_dump_open (out);
+    dump_desc (f, &flat->desc);
+    const int64_t lnq = d4est_factors->local_sizes.local_nodes_quad;
+    d4b_dump_put1 (f, "xyz", D4B_F64, 3 * (uint64_t) local_nodes, d4est_factors->xyz);
+    d4b_dump_put1 (f, "xyz_quad", D4B_F64, 3 * (uint64_t) lnq, d4est_factors->xyz_quad);
+    double pun[MAX_PUNCTURES * 10];
+    for (int i = 0; i < mp->number_of_punctures; i++) {
+      pun[10 * i] = mp->bh[i].M;
+      for (int d = 0; d < 3; d++) {
+        pun[10 * i + 1 + d] = mp->bh[i].XYZ[d];
+        pun[10 * i + 4 + d] = mp->bh[i].P[d];
+        pun[10 * i + 7 + d] = mp->bh[i].S[d];
+      }
+    }
+    d4b_dump_put1 (f, "punctures", D4B_F64, 10 * (uint64_t) mp->number_of_punctures, pun);
+    d4b_dump_put1 (f, "nw_us", D4B_F64, local_nodes, us);
+    d4b_dump_put1 (f, "nw_v", D4B_F64, local_nodes, v);
+    d4b_dump_put1 (f, "nw_F_us", D4B_F64, local_nodes, Fus);
+    d4b_dump_put1 (f, "nw_J_us_v", D4B_F64, local_nodes, Jv);
+    double prm[8] = { np.atol, np.rtol, (double) np.imin, (double) np.imax, fcg_params.atol, fcg_params.rtol,
+                      (double) fcg_params.imax, (double) mg_data->num_of_levels };
+    d4b_dump_put1 (f, "nw_params", D4B_F64, 8, prm);
+    d4b_dump_put1 (f, "nw_residual_norms", D4B_F64, steps + 1, nw_fnrm);
+    d4b_dump_put1 (f, "nw_fcg_iterations", D4B_F64, steps, fcg_its);
+    d4b_dump_put1 (f, "nw_fcg_r2", D4B_F64, fcg_pc_calls < 512 ? fcg_pc_calls : 512, fcg_r2_hist);
+    d4b_dump_put1 (f, "nw_u", D4B_F64, local_nodes, vecs.u);
+    /* the first preconditioner application of the first Newton step (linearised about u = 0): x -> y */
+    d4b_dump_put1 (f, "nw_pc_x0", D4B_F64, local_nodes, fcg_first_pc_x);
+    d4b_dump_put1 (f, "nw_pc_y0", D4B_F64, local_nodes, fcg_first_pc_y);
+    d4est_solver_multigrid_smoother_cheby_t *cheby = mg_data->smoother->user;
+    double cprm[5] = { (double) cheby->cheby_imax, (double) cheby->cheby_eigs_cg_imax,
+                       cheby->cheby_eigs_lmax_lmin_ratio, cheby->cheby_eigs_max_multiplier,
+                       (double) cheby->cheby_use_new_cg_eigs };
+    d4b_dump_put1 (f, "mg_cheby_params", D4B_F64, 5, cprm);
+    fclose (f);
+    d4est_b200_flat_destroy (flat);
+  }
+  pc->pc_apply = fcg_inner_pc_apply;
+  P4EST_FREE (fcg_first_pc_x); P4EST_FREE (fcg_first_pc_y);
+  fcg_first_pc_x = fcg_first_pc_y = NULL;
+  d4est_krylov_pc_multigrid_destroy (pc);
+  d4est_solver_multigrid_matrix_operator_destroy (user_callbacks);
+  d4est_solver_multigrid_data_destroy (mg_data);
+  P4EST_FREE (us); P4EST_FREE (v); P4EST_FREE (Fus); P4EST_FREE (Jv);
+  P4EST_FREE (u); P4EST_FREE (Au); P4EST_FREE (rhs);
+  d4est_laplacian_flux_destroy (flux_plain);
+  d4est_laplacian_with_opt_flux_destroy (flux_jac);
+  d4est_laplacian_with_opt_flux_destroy (flux_res);
+  multi_punctures_params_destroy (mp);
+}
+
 int
 main (int argc, char *argv[])
 {
@@ -282,7 +483,7 @@ main (int argc, char *argv[])
   const char *ini = argv[1];
   const char *out = argv[2];
   int amr_steps = 0, time_reps = 0, bc_poly = 0, cheby_imax = 0, cheby_eigs_imax = 0, mg_vcycles = 0, use_b200 = 0;
-  int dump_quad = 0, fcg_imax = 0, bc_robin = 0, b200_apply_only = 0, no_opt = 0;
+  int dump_quad = 0, fcg_imax = 0, bc_robin = 0, b200_apply_only = 0, no_opt = 0, newton = 0;
   const char *geom_out = NULL;
   for (int a = 3; a < argc; a++) {
     if (!strcmp (argv[a], "--amr")) amr_steps = atoi (argv[++a]);
@@ -299,6 +500,7 @@ main (int argc, char *argv[])
     /* the with_opt flux knows no maxpp1_sqr_over_minh (d4est_laplacian_with_opt_flux_sipg.c:1350-1366 aborts):
      * both outputs then come from the plain operator */
     else if (!strcmp (argv[a], "--no-opt")) { no_opt = 1; }
+    else if (!strcmp (argv[a], "--newton")) { newton = 1; }
     else { fprintf (stderr, "unknown option %s\n", argv[a]); return 2; }
   }
 
@@ -367,6 +569,21 @@ main (int argc, char *argv[])
     d4est_ghost_data_init (p4est, d4est_ghost, &field_type, 1);
   int local_nodes = local_sizes.local_nodes;
 
+  if (newton) {
+    run_newton (p4est, &d4est_ghost, &d4est_ghost_data, d4est_ops, d4est_geom, d4est_quad, d4est_factors,
+                initial_grid_input, ini, out, local_nodes);
+    d4est_ghost_data_destroy (d4est_ghost_data);
+    d4est_ghost_destroy (d4est_ghost);
+    d4est_mesh_initial_extents_destroy (initial_grid_input);
+    d4est_quadrature_destroy (p4est, d4est_ops, d4est_geom, d4est_quad);
+    d4est_mesh_data_destroy (d4est_factors);
+    d4est_ops_destroy (d4est_ops);
+    p4est_destroy (p4est);
+    d4est_geometry_destroy (d4est_geom);
+    zlog_fini ();
+    sc_finalize ();
+    return 0;
+  }
   d4est_laplacian_dirichlet_bc_t bc_data_for_lhs;
   bc_data_for_lhs.dirichlet_fcn = bc_poly ? drv_poly_fcn : drv_zero_fcn;
   bc_data_for_lhs.eval_method = EVAL_BNDRY_FCN_ON_LOBATTO;

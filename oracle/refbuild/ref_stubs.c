@@ -20,6 +20,8 @@ STUB (d4est_geometry_cubed_sphere_vtk_new)
 STUB (d4est_amr_smooth_pred_init)
 STUB (mpsort_mpi)
 STUB (d4est_checkpoint_save)
+STUB (d4est_solver_krylov_petsc_solve)
+STUB (d4est_hessian_compute_hessian_trace_of_field_on_quadrature_points)
 
 double
 d4est_power_method ()

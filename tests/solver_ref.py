@@ -79,12 +79,27 @@ def cheby(apply, u, rhs, iters, lmin, lmax):
 
 
 # ---- multigrid -------------------------------------------------------------------
+_LGL = {}
+
+
 def lgl_nodes(N):
-    from disco4est_b200.brick import lgl_nodes as f
-    return f(N)
+    if N not in _LGL:
+        from disco4est_b200.brick import lgl_nodes as f
+        _LGL[N] = f(N)
+    return _LGL[N]
+
+
+_P1D = {}
 
 
 def prolong_1d(degH, degh, half):
+    key = (degH, degh, half)
+    if key not in _P1D:
+        _P1D[key] = _prolong_1d(degH, degh, half)
+    return _P1D[key]
+
+
+def _prolong_1d(degH, degh, half):
     """[nh x nH] Lagrange basis on LGL(degH) at the LGL(degh) nodes of the whole
     interval (half 0: build_p_prolong_1d, d4est_operators.c:995-1012) or of its lower /
     upper half (half 1, 2: build_hp_prolong_1d :944-993)."""
@@ -234,3 +249,41 @@ def fcg(apply, pc, u, rhs, imax, rtol, atol=0.0, textbook=False):
         if k > 0 and np.sqrt(rr) <= tol:
             break
     return u, len(hist), hist
+
+
+# ---- Newton-Krylov-multigrid on a mass-type nonlinearity -----------------------------
+def vcycle2(ap1, ap0, transfer, rhs, cheby_imax, eigs_imax, ratio, use_new=0, bottom=(15, 15, 30.0)):
+    """One two-level V-cycle from a zero guess with a Chebyshev bottom solver
+    (d4est_solver_multigrid_bottom_solver_cheby.c:60-115): what d4est_krylov_pc_multigrid_apply does with
+    vcycle_imax = 1.  Returns u."""
+    def smooth(ap, u, b, imax, eimax, rat):
+        e, u = cg_eigs(ap, u, b, eimax, use_new)
+        return cheby(ap, u, b, imax, e / rat, e)
+
+    u, r = smooth(ap1, np.zeros_like(rhs), rhs, cheby_imax, eigs_imax, ratio)
+    rc = transfer.restrict(r)
+    uc, _ = smooth(ap0, np.zeros_like(rc), rc, bottom[0], bottom[1], bottom[2])
+    u, r = smooth(ap1, u + transfer.prolong(uc), rhs, cheby_imax, eigs_imax, ratio)
+    return u
+
+
+def newton(residual, linearize, u, atol, rtol, imin, imax, fcg_rtol, fcg_atol, fcg_imax):
+    """d4est_solver_newton_solve (src/Solver/d4est_solver_newton.c:136-367) with d4est_solver_fcg_solve as the
+    Krylov callback.  residual(u) -> F; linearize(u0) -> (apply, pc).  Returns (u, FCG iterations per step,
+    residual norms)."""
+    x = u.copy()
+    f0 = residual(x)
+    fnrm = float(np.sqrt(f0 @ f0))
+    norms, its = [fnrm], []
+    stop = atol + rtol * fnrm
+    itc = 0
+    while (fnrm > stop or itc < imin) and itc < imax:
+        ap, pc = linearize(x)
+        step, n, _ = fcg(ap, pc, np.zeros_like(x), -f0, fcg_imax, fcg_rtol, fcg_atol)
+        its.append(n)
+        x = x + step
+        f0 = residual(x)
+        fnrm = float(np.sqrt(f0 @ f0))
+        norms.append(fnrm)
+        itc += 1
+    return x, its, norms
