@@ -587,6 +587,12 @@ d4est_b200_get_mesh (d4est_b200_ctx_t * ctx, p4est_t * p4est, d4est_ghost_t * gh
   else
     c->mesh = d4b_mesh_create (&fl->desc);
   d4est_b200_flat_destroy (fl);
+  if (ctx->has_nonlinear) {
+    d4b_nonlinear_desc_t nl = ctx->nonlinear;
+    nl.xyz_quad = d4est_factors->xyz_quad;
+    nl.jac_quad = d4est_factors->J_quad;
+    d4b_mesh_set_nonlinear_term (c->mesh, &nl);
+  }
   c->factors = d4est_factors;
   c->local_elements = ne;
   c->local_nodes = nn;
@@ -602,6 +608,43 @@ d4est_b200_get_mesh (d4est_b200_ctx_t * ctx, p4est_t * p4est, d4est_ghost_t * gh
 }
 
 void
+d4est_b200_set_nonlinear_term (d4est_b200_ctx_t * ctx, const d4b_nonlinear_desc_t * desc, d4est_b200_ctx_t * residual_ctx)
+{
+  d4est_b200_ctx_invalidate (ctx);
+  ctx->has_nonlinear = (desc != NULL);
+  if (desc) ctx->nonlinear = *desc;
+  ctx->residual_ctx = residual_ctx;
+  ctx->lin_u0 = NULL; ctx->lin_mesh = NULL;
+  if (residual_ctx && residual_ctx != ctx) {
+    d4est_b200_ctx_invalidate (residual_ctx);
+    residual_ctx->has_nonlinear = ctx->has_nonlinear;
+    residual_ctx->nonlinear = ctx->nonlinear;
+  }
+}
+
+/* strided checksum of a linearisation point: <= 4096 samples, position-weighted */
+static double
+u0_signature (const double *u0, int n)
+{
+  const int stride = n > 4096 ? n / 4096 : 1;
+  double s = 0.;
+  for (int i = 0, k = 1; i < n; i += stride, k++) s += u0[i] * (1. + 1e-3 * (k % 97));
+  return s + u0[n - 1];
+}
+
+/* Newton: make `mesh` the Jacobian about u0 unless it already is (same address, size and checksum) */
+static void
+d4est_b200_ensure_linearised (d4est_b200_ctx_t * ctx, d4b_mesh_t * mesh, const double *u0, int n)
+{
+  if (!ctx->has_nonlinear || u0 == NULL || n <= 0) return;
+  const double sig = u0_signature (u0, n);
+  if (ctx->lin_mesh == mesh && ctx->lin_u0 == u0 && ctx->lin_nodes == n && ctx->lin_sig == sig) return;
+  d4b_mesh_linearize (mesh, u0);
+  ctx->lin_mesh = mesh; ctx->lin_u0 = u0; ctx->lin_nodes = n; ctx->lin_sig = sig;
+  ctx->linearisations++;
+}
+
+void
 d4est_b200_apply_lhs (p4est_t * p4est, d4est_ghost_t * ghost,
                       d4est_ghost_data_t * ghost_data,
                       d4est_elliptic_data_t * prob_vecs,
@@ -613,7 +656,26 @@ d4est_b200_apply_lhs (p4est_t * p4est, d4est_ghost_t * ghost,
   d4est_b200_ctx_t *ctx = (d4est_b200_ctx_t *) user;
   d4b_mesh_t *mesh = d4est_b200_get_mesh (ctx, p4est, ghost, d4est_factors);
   ctx->applies++;
+  /* the Jacobian of a nonlinear problem: only the mesh the Newton iterate lives on carries u0 */
+  /* (inside the reference's own multigrid the coarse levels see the fine level's u0 pointer: skipped) */
+  if (ctx->has_nonlinear && prob_vecs->u0 != NULL
+      && (ctx->newton_nodes == 0 || ctx->newton_nodes == prob_vecs->local_nodes))
+    d4est_b200_ensure_linearised (ctx, mesh, prob_vecs->u0, prob_vecs->local_nodes);
   d4b_apply (mesh, prob_vecs->u, prob_vecs->Au);
+}
+
+void
+d4est_b200_build_residual (p4est_t * p4est, d4est_ghost_t * ghost, d4est_ghost_data_t * ghost_data,
+                           d4est_elliptic_data_t * prob_vecs, d4est_operators_t * d4est_ops,
+                           d4est_geometry_t * d4est_geom, d4est_quadrature_t * d4est_quad,
+                           d4est_mesh_data_t * d4est_factors, void *user)
+{
+  d4est_b200_ctx_t *ctx = (d4est_b200_ctx_t *) user;
+  d4est_b200_ctx_t *rctx = ctx->residual_ctx ? ctx->residual_ctx : ctx;
+  d4b_mesh_t *mesh = d4est_b200_get_mesh (rctx, p4est, ghost, d4est_factors);
+  (void) ghost_data; (void) d4est_ops; (void) d4est_geom; (void) d4est_quad;
+  ctx->newton_nodes = prob_vecs->local_nodes;
+  d4b_build_residual (mesh, prob_vecs->u, ctx->has_nonlinear ? NULL : prob_vecs->rhs, prob_vecs->Au);
 }
 
 /* ------------------------------------------------------------ right-hand side */
@@ -927,6 +989,7 @@ d4est_b200_pc_build_hierarchy (d4est_b200_pc_multigrid_data_t * pcd, p4est_t * p
   else
     D4EST_ABORT ("d4est_b200_pc_multigrid needs mg_bottom_solver_cg or mg_bottom_solver_cheby");
   pcd->mg = d4b_mg_create (&D);
+  if (pcd->ctx->has_nonlinear) d4b_mg_set_coarse_mass (pcd->mg, D4B_COARSE_MASS_REFERENCE);
   for (int l = 0; l < top; l++) { free (first[l]); free (count[l]); }
   pcd->n_levels = nl;
   pcd->top_elements = p4est->local_num_quadrants;
@@ -971,6 +1034,8 @@ d4est_b200_pc_multigrid_apply (d4est_krylov_pc_t * kpc, double *xp, double *yp)
     d4est_b200_pc_build_hierarchy (pcd, kct->p4est, &mg_prob_vecs, kct->fcns);
     P4EST_FREE (Au);
   }
+  if (pcd->ctx->has_nonlinear)
+    d4est_b200_ensure_linearised (pcd->ctx, pcd->level_mesh[pcd->n_levels - 1], kct->vecs->u0, local_nodes);
   pcd->vcycles += d4b_mg_solve (pcd->mg, yp, xp, NULL);
   pcd->applies++;
 }

@@ -75,7 +75,7 @@ typedef struct
 } d4est_b200_cached_mesh_t;
 
 /* user context stored in d4est_elliptic_eqns_t.user */
-typedef struct
+typedef struct d4est_b200_ctx
 {
   d4est_laplacian_flux_data_t *flux_data;  /* as the reference callbacks use */
   d4est_b200_cached_mesh_t cache[D4EST_B200_CACHE];
@@ -88,6 +88,19 @@ typedef struct
   d4est_operators_t *bc_ops;
   d4est_geometry_t *bc_geom;
   d4est_quadrature_t *bc_quad;
+  /* nonlinear mass-type term (d4est_b200_set_nonlinear_term): attached to every mesh this context uploads */
+  int has_nonlinear;
+  d4b_nonlinear_desc_t nonlinear;
+  /* the context whose operator build_residual applies (flux_data_for_res of the problem files: same faces,
+   * boundary data NOT zeroed); NULL = this context */
+  struct d4est_b200_ctx *residual_ctx;
+  /* linearisation point last uploaded for the top mesh (d4est_b200_apply_lhs with prob_vecs->u0) */
+  const double *lin_u0;
+  double lin_sig;
+  int lin_nodes;
+  int newton_nodes;                        /* local_nodes of the mesh build_residual ran on last (0 = unknown) */
+  d4b_mesh_t *lin_mesh;
+  long linearisations;                     /* statistics: u0 uploads          */
 } d4est_b200_ctx_t;
 
 /* Dirichlet data of flux_data->bc_data at the boundary-face quadrature points, evaluated the way
@@ -164,6 +177,30 @@ void d4est_b200_apply_lhs(p4est_t *p4est, d4est_ghost_t *ghost,
                           d4est_geometry_t *d4est_geom,
                           d4est_quadrature_t *d4est_quad,
                           d4est_mesh_data_t *d4est_factors, void *user);
+
+/* drop-in for d4est_elliptic_eqns_t.build_residual (src/EllipticSystem/d4est_elliptic_eqns.h:26-37), same nine
+ * arguments, user = the d4est_b200_ctx_t of apply_lhs:  prob_vecs->Au = A(u) + N(u) - rhs  on the device, with
+ * A the operator of ctx->residual_ctx (or ctx) INCLUDING its boundary data, N the nonlinear term of the context
+ * if one is set, and rhs = prob_vecs->rhs unless ctx->has_nonlinear (the nonlinear problem files put no rhs
+ * into their residual, multi_punctures_build_residual; the linear ones do, poisson_build_residual,
+ * src/Problems/Poisson/poisson_sinx_fcns.h:133-149).                                                    */
+void d4est_b200_build_residual(p4est_t *p4est, d4est_ghost_t *ghost, d4est_ghost_data_t *ghost_data,
+                               d4est_elliptic_data_t *prob_vecs, d4est_operators_t *d4est_ops,
+                               d4est_geometry_t *d4est_geom, d4est_quadrature_t *d4est_quad,
+                               d4est_mesh_data_t *d4est_factors, void *user);
+
+/* Nonlinear mass-type term f(x, u) = a(x) (b(x) + u)^k as a DEVICE functor (include/d4est_b200.h,
+ * d4b_nonlinear_desc_t): `desc` carries the kind and its parameters (puncture list / star); xyz_quad and jac_quad
+ * are filled in from the reference's d4est_mesh_data_t whenever a mesh is uploaded.  From then on
+ *   d4est_b200_build_residual adds V^T w J f(x, V u)                  (d4est_quadrature_apply_fofufofvlj),
+ *   d4est_b200_apply_lhs applies the Jacobian about prob_vecs->u0      (..._fofufofvlilj); u0 is uploaded
+ *     once per linearisation point -- recognised by its address and a strided checksum -- and f, f_u are
+ *     evaluated on the device,
+ *   d4est_b200_pc_multigrid_create's hierarchy applies the reference's multigrid matrix operator on its coarse
+ *     levels (d4b_mg_set_coarse_mass, as the reference executes it).
+ * residual_ctx: the context of the problem's flux_data_for_res (may be NULL = same operator).                */
+void d4est_b200_set_nonlinear_term(d4est_b200_ctx_t *ctx, const d4b_nonlinear_desc_t *desc,
+                                   d4est_b200_ctx_t *residual_ctx);
 
 d4est_b200_ctx_t *d4est_b200_ctx_new(d4est_laplacian_flux_data_t *flux_data);
 void d4est_b200_ctx_destroy(d4est_b200_ctx_t *ctx);

@@ -322,7 +322,7 @@ static void
 run_newton (p4est_t * p4est, d4est_ghost_t ** d4est_ghost, d4est_ghost_data_t ** d4est_ghost_data,
             d4est_operators_t * d4est_ops, d4est_geometry_t * d4est_geom, d4est_quadrature_t * d4est_quad,
             d4est_mesh_data_t * d4est_factors, d4est_mesh_initial_extents_t * initial_grid_input,
-            const char *ini, const char *out, int local_nodes)
+            const char *ini, const char *out, int local_nodes, int use_b200)
 {
   d4est_field_type_t field_type = NODAL;
   multi_punctures_params_t *mp = multi_punctures_params_init (p4est, ini);
@@ -418,6 +418,81 @@ run_newton (p4est_t * p4est, d4est_ghost_t ** d4est_ghost, d4est_ghost_data_t **
   printf ("], \"residual_norms\": [");
   for (int k = 0; k <= steps; k++) printf ("%s%.17g", k ? ", " : "", nw_fnrm[k]);
   printf ("], \"t_newton_s\": %.3f}\n", t_newton);
+
+#ifdef D4B_WITH_DEVICE
+  if (use_b200) {
+    /* DROP-IN CHECK: the same UNMODIFIED d4est_solver_newton_solve + d4est_solver_fcg_solve, with
+     * build_residual = d4est_b200_build_residual, apply_lhs = d4est_b200_apply_lhs and
+     * pc = d4est_b200_pc_multigrid_create; the puncture terms are device functors, f is never evaluated on the host */
+    d4est_laplacian_flux_data_t *flux_plain_res = d4est_laplacian_flux_new (p4est, ini, BC_ROBIN, &bc_plain);
+    d4est_b200_ctx_t *jctx = d4est_b200_ctx_new (flux_plain), *rctx = d4est_b200_ctx_new (flux_plain_res);
+    d4b_nonlinear_desc_t nl;
+    memset (&nl, 0, sizeof (nl));
+    nl.kind = D4B_NL_PUNCTURES;
+    nl.n_punctures = mp->number_of_punctures;
+    for (int i = 0; i < mp->number_of_punctures; i++) {
+      nl.punctures[i][0] = mp->bh[i].M;
+      for (int d = 0; d < 3; d++) {
+        nl.punctures[i][1 + d] = mp->bh[i].XYZ[d];
+        nl.punctures[i][4 + d] = mp->bh[i].P[d];
+        nl.punctures[i][7 + d] = mp->bh[i].S[d];
+      }
+    }
+    d4est_b200_set_nonlinear_term (jctx, &nl, rctx);
+    d4est_elliptic_eqns_t b_fcns;
+    b_fcns.build_residual = d4est_b200_build_residual;
+    b_fcns.apply_lhs = d4est_b200_apply_lhs;
+    b_fcns.user = jctx;
+    d4est_solver_multigrid_t *bmg =
+      d4est_solver_multigrid_data_init (p4est, d4est_ops, d4est_geom, d4est_quad, d4est_ghost, d4est_ghost_data,
+                                        d4est_factors, initial_grid_input, ini);
+    d4est_krylov_pc_t *bpc = d4est_b200_pc_multigrid_create (bmg, jctx, NULL);
+    const int ref_steps = steps;
+    int ref_its[NEWTON_MAX_STEPS];
+    double ref_fnrm[NEWTON_MAX_STEPS + 1];
+    for (int k = 0; k < steps; k++) ref_its[k] = (int) fcg_its[k];
+    for (int k = 0; k <= steps; k++) ref_fnrm[k] = nw_fnrm[k];
+    fcg_inner_pc_apply = bpc->pc_apply;
+    bpc->pc_apply = fcg_counting_pc_apply;
+    fcg_pc_calls = 0;
+    nw_inner_build_residual = b_fcns.build_residual;
+    b_fcns.build_residual = nw_recording_build_residual;
+    nw_res_calls = 0;
+    double *bu = P4EST_ALLOC_ZERO (double, local_nodes), *bAu = P4EST_ALLOC_ZERO (double, local_nodes);
+    d4est_elliptic_data_t bv = vecs;
+    bv.u = bu; bv.Au = bAu;
+    double tb = wall ();
+    int bierr = d4est_solver_newton_solve (p4est, &bv, &b_fcns, d4est_ghost, d4est_ghost_data, d4est_ops, d4est_geom,
+                                           d4est_quad, d4est_factors, (char *) ini, d4est_solver_fcg_solve, &fcg_params,
+                                           bpc, 0);
+    tb = wall () - tb;
+    const int bsteps = nw_res_calls - 1;
+    int same_its = (bsteps == ref_steps), k;
+    double worst_norm = 0., un = 0., ud = 0.;
+    printf ("{\"b200_newton_steps\": %d, \"reference_newton_steps\": %d, \"b200_newton_ierr\": %d, "
+            "\"b200_fcg_iterations_per_step\": [", bsteps, ref_steps, bierr);
+    for (k = 0; k < bsteps; k++) {
+      const int its_k = nw_pc_calls_at_res[k + 1] - nw_pc_calls_at_res[k];
+      printf ("%s%d", k ? ", " : "", its_k);
+      if (k >= ref_steps || its_k != ref_its[k]) same_its = 0;
+    }
+    for (k = 0; k <= bsteps && k <= ref_steps; k++) {
+      /* relative, with a floor at 1e-8 of the initial residual (the last norms are round-off of the first) */
+      const double d = fabs (nw_fnrm[k] - ref_fnrm[k]) / (ref_fnrm[k] + 1e-8 * ref_fnrm[0]);
+      if (d > worst_norm) worst_norm = d;
+    }
+    for (k = 0; k < local_nodes; k++) { un += (bu[k] - vecs.u[k]) * (bu[k] - vecs.u[k]); ud += vecs.u[k] * vecs.u[k]; }
+    printf ("], \"same_iteration_counts\": %d, \"residual_norm_worst_rel_diff\": %.3e, \"newton_u_rel_l2_diff\": %.3e, "
+            "\"u0_uploads\": %ld, \"device_mesh_uploads\": %ld, \"t_newton_reference_s\": %.3f, \"t_newton_b200_s\": %.3f}\n",
+            same_its, worst_norm, sqrt (un / ud), jctx->linearisations, jctx->uploads + rctx->uploads, t_newton, tb);
+    bpc->pc_apply = fcg_inner_pc_apply;
+    d4est_b200_pc_multigrid_destroy (bpc);
+    d4est_solver_multigrid_data_destroy (bmg);
+    d4est_b200_ctx_destroy (jctx); d4est_b200_ctx_destroy (rctx);
+    d4est_laplacian_flux_destroy (flux_plain_res);
+    P4EST_FREE (bu); P4EST_FREE (bAu);
+  }
+#endif
 
   if (strcmp (out, "-")) {
     d4est_b200_flat_t *flat = d4est_b200_flatten (p4est, *d4est_ghost, d4est_factors, flux_plain);
@@ -571,7 +646,7 @@ main (int argc, char *argv[])
 
   if (newton) {
     run_newton (p4est, &d4est_ghost, &d4est_ghost_data, d4est_ops, d4est_geom, d4est_quad, d4est_factors,
-                initial_grid_input, ini, out, local_nodes);
+                initial_grid_input, ini, out, local_nodes, use_b200);
     d4est_ghost_data_destroy (d4est_ghost_data);
     d4est_ghost_destroy (d4est_ghost);
     d4est_mesh_initial_extents_destroy (initial_grid_input);

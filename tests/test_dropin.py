@@ -123,3 +123,20 @@ def test_cached_mesh_is_dropped_after_count_preserving_p_adapt(ini):
     assert res["reference_change_rel_l2"] > 1e-6      # the operator really changed
     assert res["uploads_for_swapped_mesh"] == 1
     assert res["b200_apply_after_degree_swap_rel_l2"] < 1e-12
+
+
+def test_reference_newton_with_device_residual_jacobian_and_preconditioner():
+    """BASELINE configs[4] in small, INSIDE the reference: its unmodified d4est_solver_newton_solve and
+    d4est_solver_fcg_solve run with build_residual = d4est_b200_build_residual, apply_lhs = d4est_b200_apply_lhs
+    (Jacobian about prob_vecs->u0) and pc = d4est_b200_pc_multigrid_create; puncture terms are device functors.
+    Same Newton steps and FCG iterations per step as the stock run, one upload of u0 per Newton step."""
+    lines = run("sphere_punctures.ini", "--newton")
+    ref = [l for l in lines if "newton_steps" in l][0]
+    res = [l for l in lines if "b200_newton_steps" in l][0]
+    assert res["b200_newton_ierr"] == 0
+    assert res["b200_newton_steps"] == ref["newton_steps"]
+    assert res["b200_fcg_iterations_per_step"] == ref["fcg_iterations_per_step"]
+    assert res["same_iteration_counts"] == 1
+    assert res["residual_norm_worst_rel_diff"] < 1e-6
+    assert res["newton_u_rel_l2_diff"] < 1e-9
+    assert res["u0_uploads"] == res["b200_newton_steps"]
