@@ -61,3 +61,18 @@ rm -f "$HERE"/configs/_pen_*.ini
 "$DRV" "$HERE/configs/sphere_punctures.ini" "$G/sphere_punctures_newton.d4b" --newton | tail -1 > "$G/sphere_punctures_newton.json"
 gzip -9nf "$G/sphere_punctures_newton.d4b"
 echo "sphere_punctures_newton: $(cat "$G/sphere_punctures_newton.json")"
+# the bench V-cycle's exact configuration: Chebyshev bottom solver (d4est_solver_multigrid_bottom_solver_cheby.c:60-115)
+variant _mg_cheby.ini brick_poisson_mg.ini -e 's/^bottom_solver_name = .*/bottom_solver_name = mg_bottom_solver_cheby/'
+cat >> "$HERE/configs/_mg_cheby.ini" <<'INI'
+
+[mg_bottom_solver_cheby]
+cheby_imax = 15
+cheby_eigs_cg_imax = 15
+cheby_eigs_lmax_lmin_ratio = 30.
+cheby_eigs_max_multiplier = 1.
+cheby_print_residual_norm = 0
+cheby_print_spectral_bound = 0
+cheby_print_spectral_bound_iterations = 0
+INI
+run brick_mg_l2_p2_cheby _mg_cheby.ini --uniform-deg 2 --mg 4 --fcg 30
+rm -f "$HERE"/configs/_mg_cheby.ini

@@ -169,9 +169,11 @@ def bottom_cg(apply, rhs, imax, rtol, atol):
 
 
 def vcycle(applies, transfers, u, rhs, cheby_imax, eigs_imax, ratio, mult=1.0, use_new=0,
-           bottom=(100, 1e-10, 0.0)):
+           bottom=(100, 1e-10, 0.0), bottom_cheby=None):
     """One V-cycle, d4est_solver_multigrid.c:751-1349 (eigenvalues recomputed on both legs).
-    applies[l], transfers[l] (between l and l+1), coarsest first.  Returns (u, r2, eigs)."""
+    applies[l], transfers[l] (between l and l+1), coarsest first.  Returns (u, r2, eigs).
+    bottom = (imax, rtol, atol) of mg_bottom_solver_cg, or bottom_cheby = (cheby_imax, eigs_cg_imax, ratio)
+    of mg_bottom_solver_cheby (d4est_solver_multigrid_bottom_solver_cheby.c:60-115)."""
     top = len(applies) - 1
     us, rhss, eigs = [None] * (top + 1), [None] * (top + 1), [0.0] * (top + 1)
     us[top], rhss[top] = u.copy(), rhs
@@ -188,7 +190,11 @@ def vcycle(applies, transfers, u, rhs, cheby_imax, eigs_imax, ratio, mult=1.0, u
             us[l] = np.zeros_like(rhss[l])
         r = smooth(l)
         rhss[l - 1] = transfers[l - 1].restrict(r)
-    us[0], _ = bottom_cg(applies[0], rhss[0], *bottom)
+    if bottom_cheby is None:
+        us[0], _ = bottom_cg(applies[0], rhss[0], *bottom)
+    else:
+        e0, u0 = cg_eigs(applies[0], np.zeros_like(rhss[0]), rhss[0], bottom_cheby[1], use_new)
+        us[0], _ = cheby(applies[0], u0, rhss[0], bottom_cheby[0], e0 / bottom_cheby[2], e0)
     for l in range(0, top):
         us[l + 1] = us[l + 1] + transfers[l].prolong(us[l])
         r = smooth(l + 1)

@@ -8,6 +8,9 @@ from oracle_lib import Oracle
 from solver_ref import Transfer, prolong_1d, vcycle
 
 CASE = "brick_mg_l2_p2"
+# same mesh and right-hand side with mg_bottom_solver_cheby (cheby_imax 15, cheby_eigs_cg_imax 15, ratio 30): the
+# configuration of the bench V-cycle and of the shipped nonlinear problems' input files
+CASES = [("brick_mg_l2_p2", None), ("brick_mg_l2_p2_cheby", (15, 15, 30.0))]
 
 
 def rel(a, b):
@@ -38,9 +41,10 @@ def test_prolong_tables_match_reference(golden):
             assert np.abs(prolong_1d(p, q, 0) - ref).max() < 1e-13
 
 
-def test_restatement_matches_reference_multigrid(golden):
+@pytest.mark.parametrize("case,bottom_cheby", CASES)
+def test_restatement_matches_reference_multigrid(golden, case, bottom_cheby):
     """pins tests/solver_ref.py:vcycle (and the synthetic hierarchy) to the reference"""
-    A = golden(CASE)
+    A = golden(case)
     descs, transfers = hierarchy(A)
     assert len(descs) == int(A["mg_num_levels"][0])
     orcs = [Oracle(d) for d in descs]
@@ -53,7 +57,8 @@ def test_restatement_matches_reference_multigrid(golden):
     assert abs(float(rhs @ rhs) - r2_ref[0]) <= 1e-12 * r2_ref[0]
     hist = np.asarray(A["mg_u_hist"]).reshape(-1, n)
     for k in range(hist.shape[0]):
-        u, r2, eigs = vcycle([o.apply for o in orcs], trs, u, rhs, int(imax), int(eigs_imax), ratio, mult, int(use_new))
+        u, r2, eigs = vcycle([o.apply for o in orcs], trs, u, rhs, int(imax), int(eigs_imax), ratio, mult, int(use_new),
+                             bottom_cheby=bottom_cheby)
         # relative to the initial residual: the last cycles sit at round-off level
         assert abs(r2 - r2_ref[k + 1]) <= 1e-6 * r2_ref[k + 1] + 1e-25 * r2_ref[0]
         assert rel(u, hist[k]) < 1e-9
@@ -99,9 +104,14 @@ def test_gpu_transfers_match_restatement(gpu_mg):
 
 
 @pytest.mark.gpu
-def test_gpu_vcycles_match_reference(gpu_mg):
-    A, descs, transfers, make = gpu_mg
-    mg = make()
+@pytest.mark.parametrize("case,bottom_cheby", CASES)
+def test_gpu_vcycles_match_reference(gpu_mg, golden, case, bottom_cheby):
+    from disco4est_b200.runtime import cheby_params
+
+    _, descs, transfers, make = gpu_mg
+    A = golden(case)
+    mg = make() if bottom_cheby is None else make(bottom_solver="cheby",
+                                                  bottom_cheby=cheby_params(bottom_cheby[0], bottom_cheby[1], bottom_cheby[2]))
     rhs = np.ascontiguousarray(A["mg_rhs"])
     n = rhs.size
     u = np.zeros(n)
