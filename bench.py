@@ -487,6 +487,124 @@ def bench_sphere(args, rank, world, local_rank, torch, dist, dev):
     return out
 
 
+# the two punctures of oracle/configs/sphere_punctures.ini (M, X, Y, Z, PX, PY, PZ, SX, SY, SZ)
+PUNCTURES = [[0.5, -0.37, 0.11, 0.05, 0.0, -0.2, 0.0, 0.0, 0.0, 0.1],
+             [0.5, 0.41, -0.07, -0.03, 0.0, 0.2, 0.0, 0.0, 0.05, -0.1]]
+
+
+def bench_punctures(args, rank, world, local_rank, torch, dist, dev):
+    """BASELINE.json configs[4] in synthetic form: two-puncture initial data on the 13-tree cubed sphere with a
+    Robin outer boundary (src/Problems/TwoPunctures/multi_punctures_anares_inhouse.c), geometric factors and the
+    puncture terms generated on the device.  (i) GDOF/s of the Jacobian apply (Laplacian + linearised mass-type
+    term, what FCG and the smoothers call) and of the residual evaluation, mesh split over the ranks like p4est;
+    (ii) on one GPU the whole in-house Newton -> FCG -> multigrid solve (d4b_newton_solve, matrix operator on the
+    coarse levels as the reference executes it) on the next coarser sphere, with its iteration counts."""
+    import numpy as np
+
+    from disco4est_b200 import Mesh
+    from disco4est_b200.partition import partition_desc
+    from disco4est_b200.runtime import Multigrid, cheby_params
+    from disco4est_b200.sphere import partition_geom, sphere_desc
+
+    R2 = 3.0
+
+    def robin(A):
+        mp = int(np.asarray(A["local_mortar_nodes_quad"]).reshape(-1)[0])
+        A = dict(A)
+        A["bc_type"] = 1
+        A["robin_coeff_mortar_quad"] = np.full(mp, 1.0 / R2)   # multi_punctures_robin_coeff_sphere_fcn: 1 / r
+        A["robin_rhs_mortar_quad"] = np.zeros(mp)
+        return A
+
+    out = {}
+    lvl = args.sphere_level
+    A, g = sphere_desc(lvl, p=args.deg, prefactor=2.0, radii=(1.0, 2.0, R2))
+    A = robin(A)
+    E, total_dof = int(A["n_local"]), int(A["local_nodes"])
+    if world > 1:
+        B = partition_desc(A, rank, world)
+        g = partition_geom(g, B, rank, world, E)
+        A = B
+    mesh = Mesh(A, device=local_rank, geom=g)
+    del A, g
+    mesh.set_nonlinear_term("punctures", punctures=PUNCTURES)
+    stream = torch.cuda.current_stream()
+    mesh.set_stream(stream.cuda_stream)
+    gen = torch.Generator(device=dev).manual_seed(99 + rank)
+    u0 = 0.05 * torch.rand(mesh.n, dtype=torch.float64, device=dev, generator=gen)
+    v = torch.rand(mesh.n, dtype=torch.float64, device=dev, generator=gen)
+    Jv = torch.empty_like(v)
+    mesh.linearize(u0)
+    steps = max(args.steps // 2, 5)
+
+    def timed(fn):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record(stream)
+        for _ in range(steps):
+            fn()
+        ev1.record(stream)
+        torch.cuda.synchronize()
+        tt = torch.tensor([ev0.elapsed_time(ev1) * 1e-3 / steps], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        return float(tt[0])
+
+    t_jac = timed(lambda: mesh.apply(v, Jv))
+    t_res = timed(lambda: mesh.build_residual(u0, Jv))
+    out["jacobian_apply"] = {"GDOF_per_s": total_dof / t_jac / 1e9, "ms_per_apply": 1e3 * t_jac, "level": lvl,
+                             "elements": E, "dof": total_dof, "checksum": float(Jv.sum())}
+    out["residual"] = {"GDOF_per_s": total_dof / t_res / 1e9, "ms_per_evaluation": 1e3 * t_res,
+                       "note": "apply + a quadrature kernel for V^T w J f(x, V u)"}
+    mesh.close()
+    del u0, v, Jv
+    if world == 1:
+        nl = min(lvl, args.newton_level)
+        t0 = time.perf_counter()
+        meshes = []
+        for l in range(nl + 1):
+            A, g = sphere_desc(l, p=args.deg, prefactor=2.0, radii=(1.0, 2.0, R2))
+            meshes.append(Mesh(robin(A), device=local_rank, geom=g))
+        transfers = [(8 * np.arange(13 * 8 ** l, dtype=np.int32), np.full(13 * 8 ** l, 8, np.int32)) for l in range(nl)]
+        top = meshes[-1]
+        top.set_nonlinear_term("punctures", punctures=PUNCTURES)
+        mg = Multigrid(meshes, transfers, cheby_params(8, 10, 30.0, 1.0), vcycle_imax=1, vcycle_rtol=1e-9,
+                       bottom_solver="cheby", bottom_cheby=cheby_params(15, 15, 30.0, 1.0))
+        mg.set_coarse_mass("reference")
+        t_setup = time.perf_counter() - t0
+        # (a) what the reference's in-house stack executes: FCG with d_k = (1 + c) v_k and the matrix operator
+        #     linearised about u = 0 with the sliced transposes (parity mode: pinned against the reference at small size,
+        #     tests/test_newton.py; on larger meshes that FCG is erratic, as it is in the reference);
+        # (b) what its comments state: Notay's FCG recurrence and the Galerkin product P^T M(u0) P
+        for key, cm, flags in (("newton_solve", "reference", 0), ("newton_solve_textbook", "galerkin", 1)):
+            mg.set_coarse_mass(cm)
+            u = torch.zeros(top.n, dtype=torch.float64, device=dev)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            ierr, nsteps, its, norms, japplies = top.newton_solve(u, pc=mg, atol=1e-15, rtol=1e-8, imin=1, imax=20,
+                                                                  fcg_atol=1e-15, fcg_rtol=5e-2, fcg_imax=100, fcg_flags=flags)
+            torch.cuda.synchronize()
+            t_newton = time.perf_counter() - t0
+            out[key] = {"seconds": t_newton, "ierr": ierr, "newton_steps": nsteps, "fcg_iterations_per_step": its,
+                        "residual_norms": norms, "level": nl, "elements": 13 * 8 ** nl, "dof": top.n,
+                        "mg_levels": nl + 1, "preconditioner_vcycles": int(sum(its)),
+                        "seconds_per_preconditioned_fcg_iteration": t_newton / max(sum(its), 1),
+                        "setup_s": t_setup, "fcg": "reference arithmetic" if flags == 0 else "D4B_FCG_TEXTBOOK",
+                        "coarse_mass": cm,
+                        "settings": "[d4est_solver_newton] rtol 1e-8 imin 1; [d4est_solver_fcg] rtol 5e-2 imax 100; V-cycle: "
+                                    "Chebyshev(8), 10 cg_eigs steps, ratio 30, Chebyshev(15) bottom solver"}
+        mg.close()
+        for m in meshes:
+            m.close()
+    out["workload"] = ("two punctures (oracle/configs/sphere_punctures.ini) on the 13-tree cubed sphere R = 1, 2, 3, Robin outer "
+                       "boundary 1/r, p=%d, deg_quad = deg; f = -K^2/8 psi^-7 and f_u as device functors" % args.deg)
+    return out
+
+
 def bench_ours(args):
     import numpy as np
     import torch
@@ -629,12 +747,17 @@ def bench_ours(args):
     sp = None
     if not args.no_sphere:
         sp = bench_sphere(args, rank, world, local_rank, torch, dist, dev)
+    pun = None
+    if not args.no_punctures:
+        pun = bench_punctures(args, rank, world, local_rank, torch, dist, dev)
     sweep = None
     if world == 1 and not args.no_sweep:
         sweep = bench_degree_sweep(args, torch, dev)
     if rank == 0:
         if sweep is not None:
             out["degree_sweep"] = sweep
+        if pun is not None:
+            out["two_punctures"] = pun
         if vc is not None:
             out["vcycle"] = vc
         if sp is not None:
@@ -658,6 +781,8 @@ def main():
     ap.add_argument("--no-vcycle", action="store_true", help="skip the V-cycle metric")
     ap.add_argument("--no-sphere", action="store_true", help="skip the cubed-sphere applies")
     ap.add_argument("--sphere-level", type=int, default=5, help="refinement level of each of the 13 sphere trees")
+    ap.add_argument("--no-punctures", action="store_true", help="skip the two-puncture Newton-Krylov block")
+    ap.add_argument("--newton-level", type=int, default=4, help="sphere level of the Newton solve (N=1)")
     ap.add_argument("--no-sweep", action="store_true", help="skip the p=1..7 degree sweep (N=1 only)")
     ap.add_argument("--no-parity", action="store_true", help="skip the multi-GPU parity check (N>1 only)")
     ap.add_argument("--sweep-full-level-max-deg", type=int, default=3,

@@ -47,6 +47,10 @@ struct d4b_mg {
   int coarse_mass = 0;
   std::vector<double *> d_mw, d_mt;
   double *d_W0 = nullptr;        // mode 1: w J f_u(x, 0) on the finest level (see d4b_mg_set_coarse_mass)
+  // mode 1, levels whose families all have 8 children of one degree: the slices Q_i as a table
+  // Qt[(i nh3 + b) nH3 + a] (transposed for coalesced reads), per coarse level, else nullptr
+  std::vector<double *> d_Qt;
+  std::vector<int> q_nH3, q_nh3;
 };
 
 namespace {
@@ -188,7 +192,55 @@ __global__ void __launch_bounds__(128) transfer_kernel(int dir, int accumulate, 
     for (int i = threadIdx.x; i < nH3; i += blockDim.x) out[sH + i] = sAcc[i];
 }
 
+// out_H[a] = sum_i sum_b Qt[(i nh3 + b) nH3 + a] in_i[b] for uniform families (see transfer_kernel dir 2 for what
+// Q is); kQEpb coarse elements per block share one pass over the table
+constexpr int kQEpb = 8;
+__global__ void __launch_bounds__(128) qtable_restrict_kernel(int n_coarse, int nH3, int nh3,
+                                                              const int32_t *__restrict__ child_first,
+                                                              const int64_t *__restrict__ stride_c,
+                                                              const int64_t *__restrict__ stride_f,
+                                                              const double *__restrict__ Qt,
+                                                              const double *__restrict__ in, double *__restrict__ out) {
+  extern __shared__ double sy[];   // [kQEpb][8 nh3]
+  const int e0 = blockIdx.x * kQEpb;
+  const int ne = min(kQEpb, n_coarse - e0);
+  const int tot = 8 * nh3;
+  for (int k = 0; k < ne; ++k) {
+    const int first = child_first[e0 + k];
+    for (int j = threadIdx.x; j < tot; j += blockDim.x) sy[k * tot + j] = in[stride_f[first + j / nh3] + j % nh3];
+  }
+  __syncthreads();
+  for (int a = threadIdx.x; a < nH3; a += blockDim.x) {
+    double acc[kQEpb];
+#pragma unroll
+    for (int k = 0; k < kQEpb; ++k) acc[k] = 0.;
+    for (int j = 0; j < tot; ++j) {
+      const double q = Qt[(size_t)j * nH3 + a];
+#pragma unroll
+      for (int k = 0; k < kQEpb; ++k)
+        if (k < ne) acc[k] += q * sy[k * tot + j];
+    }
+#pragma unroll
+    for (int k = 0; k < kQEpb; ++k)
+      if (k < ne) out[stride_c[e0 + k] + a] = acc[k];
+  }
+}
+
 void transfer(d4b_mg *g, int dir, int accumulate, int lc, const double *in, double *out) {
+  if (dir == 2 && lc < (int)g->d_Qt.size() && g->d_Qt[lc]) {
+    d4b_mesh *mc = g->mesh[lc], *mf = g->mesh[lc + 1];
+    const size_t smem = (size_t)kQEpb * 8 * g->q_nh3[lc] * sizeof(double);
+    static size_t configured = 48 * 1024;
+    if (smem > configured) {
+      D4B_CUDA(cudaFuncSetAttribute(qtable_restrict_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      configured = smem;
+    }
+    qtable_restrict_kernel<<<(mc->n_local + kQEpb - 1) / kQEpb, 128, smem, mf->stream>>>(
+        mc->n_local, g->q_nH3[lc], g->q_nh3[lc], g->d_child_first[lc], mc->d_nodal_stride, mf->d_nodal_stride,
+        g->d_Qt[lc], in, out);
+    D4B_CUDA(cudaGetLastError());
+    return;
+  }
   d4b_mesh *mc = g->mesh[lc], *mf = g->mesh[lc + 1];
   transfer_kernel<<<mc->n_local, 128, 0, mf->stream>>>(dir, accumulate, mc->n_local, g->d_child_first[lc],
                                                        g->d_child_count[lc], mc->d_deg, mc->d_nodal_stride,
@@ -481,6 +533,48 @@ extern "C" void d4b_mg_set_coarse_mass(d4b_mg_t *g, int32_t mode) {
     d4b_launch_quad_nl(mt, 6, zero, g->d_W0);
     D4B_CUDA(cudaStreamSynchronize(mt->stream));
     cudaFree(zero);
+    // table form of the slices for levels with uniform families
+    const bool tables = !(getenv("D4B_MG_QTABLE") && atoi(getenv("D4B_MG_QTABLE")) == 0);   // 0: general path everywhere (tests)
+    if (g->d_Qt.empty() && tables) {
+      g->d_Qt.assign(top, nullptr); g->q_nH3.assign(top, 0); g->q_nh3.assign(top, 0);
+      for (int l = 0; l < top; ++l) {
+        d4b_mesh *mc = g->mesh[l], *mf = g->mesh[l + 1];
+        std::vector<int32_t> dc(mc->n_local), df(mf->n_local), cnt(mc->n_local);
+        D4B_CUDA(cudaMemcpy(dc.data(), mc->d_deg, dc.size() * sizeof(int32_t), cudaMemcpyDeviceToHost));
+        D4B_CUDA(cudaMemcpy(df.data(), mf->d_deg, df.size() * sizeof(int32_t), cudaMemcpyDeviceToHost));
+        D4B_CUDA(cudaMemcpy(cnt.data(), g->d_child_count[l], cnt.size() * sizeof(int32_t), cudaMemcpyDeviceToHost));
+        bool uniform = !dc.empty();
+        for (int32_t c : cnt) uniform = uniform && c == 8;
+        for (int32_t d : dc) uniform = uniform && d == dc[0];
+        for (int32_t d : df) uniform = uniform && d == df[0];
+        if (!uniform || (size_t)kQEpb * 8 * (df[0] + 1) * (df[0] + 1) * (df[0] + 1) * sizeof(double) > 200 * 1024) continue;
+        const int nH = dc[0] + 1, nh = df[0] + 1, nH3 = nH * nH * nH, nh3 = nh * nh * nh, total = 8 * nh3;
+        // 1-D half-interval prolongations [nh x nH] (the same tables d_P holds)
+        double xH[kMaxN], wH[kMaxN], xh[kMaxN], wh[kMaxN], y[kMaxN];
+        std::vector<double> P1[2];
+        d4b_tab_lobatto(nH, xH, wH);
+        d4b_tab_lobatto(nh, xh, wh);
+        for (int half = 0; half < 2; ++half) {
+          for (int i = 0; i < nh; ++i) y[i] = half == 0 ? 0.5 * (xh[i] - 1.) : 0.5 * (xh[i] + 1.);
+          P1[half].resize((size_t)nh * nH);
+          d4b_tab_eval(nH, xH, nh, y, P1[half].data());
+        }
+        auto Pstack = [&](int k, int j) {   // stacked prolongation entry: row k = (child, fine node), column j
+          const int c = k / nh3, m = k % nh3;
+          const int mx = m % nh, my = (m / nh) % nh, mz = m / (nh * nh), jx = j % nH, jy = (j / nH) % nH, jz = j / (nH * nH);
+          return P1[c & 1][mx * nH + jx] * P1[(c >> 1) & 1][my * nH + jy] * P1[(c >> 2) & 1][mz * nH + jz];
+        };
+        std::vector<double> Qt((size_t)total * nH3);
+        for (int i = 0; i < 8; ++i)
+          for (int a = 0; a < nH3; ++a)
+            for (int b = 0; b < nh3; ++b) {
+              const int64_t f = (int64_t)i * nh3 * nH3 + (int64_t)a * nh3 + b;
+              Qt[((size_t)i * nh3 + b) * nH3 + a] = Pstack((int)(f % total), (int)(f / total));
+            }
+        g->d_Qt[l] = d4b_dev_upload<double>(mc, Qt.data(), Qt.size());
+        g->q_nH3[l] = nH3; g->q_nh3[l] = nh3;
+      }
+    }
   }
   if (mode && g->d_mw.empty()) {
     g->d_mw.assign(g->n_levels, nullptr);
@@ -513,6 +607,7 @@ extern "C" void d4b_mg_destroy(d4b_mg_t *g) {
   for (auto p : g->d_mw) if (p) cudaFree(p);
   for (auto p : g->d_mt) if (p) cudaFree(p);
   if (g->d_W0) cudaFree(g->d_W0);
+  for (auto p : g->d_Qt) if (p) cudaFree(p);
   for (int l = 0; l + 1 < g->n_levels; ++l) g->mesh[l]->pre_apply = nullptr;
   if (g->d_top_u) cudaFree(g->d_top_u);
   if (g->d_top_rhs) cudaFree(g->d_top_rhs);

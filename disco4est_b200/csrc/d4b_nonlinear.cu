@@ -219,14 +219,18 @@ extern "C" void d4b_build_residual(d4b_mesh_t *m, const double *u, const double 
   const size_t n = (size_t)m->local_nodes;
   DevTmp du(m, u, n), dr(m, rhs, n);
   double *dF = F, *own = nullptr, *tmp = nullptr;
-  if (!is_dev(F)) { D4B_CUDA(cudaMalloc(&own, std::max<size_t>(n, 1) * sizeof(double))); dF = own; }
-  if (m->d_nl_wja) D4B_CUDA(cudaMalloc(&tmp, std::max<size_t>(n, 1) * sizeof(double)));
+  const bool F_dev = is_dev(F);
+  if (!F_dev) { D4B_CUDA(cudaMalloc(&own, std::max<size_t>(n, 1) * sizeof(double))); dF = own; }
+  if (m->d_nl_wja) {   // scratch of the mesh (shared with the smoother, never live at the same time)
+    if (!m->d_work[2]) m->d_work[2] = d4b_dev_alloc<double>(m, n);
+    tmp = m->d_work[2];
+  }
   if (m->mpisize > 1) D4B_CHECK(m->d_ughost || m->n_ghost == 0, "d4b_build_residual: ghost buffer missing");
   residual_device(m, du.p, dr.p, dF, tmp);
   if (own) D4B_CUDA(cudaMemcpyAsync(F, own, n * sizeof(double), cudaMemcpyDeviceToHost, m->stream));
-  D4B_CUDA(cudaStreamSynchronize(m->stream));
+  // stream-ordered for device pointers (d4b_sync to wait), synchronous otherwise
+  if (own || du.own || dr.own) D4B_CUDA(cudaStreamSynchronize(m->stream));
   if (own) cudaFree(own);
-  if (tmp) cudaFree(tmp);
 }
 
 extern "C" int32_t d4b_newton_solve(d4b_mesh_t *mr, d4b_mesh_t *mj, d4b_mg_t *pc, double *u,

@@ -522,7 +522,8 @@ void d4b_mesh_linearize(d4b_mesh_t *mesh, const double *u0);
  * boundary data, the middle term only when a nonlinear term is attached, rhs == NULL meaning 0:
  *   Poisson  F = A u - rhs            (poisson_build_residual, src/Problems/Poisson/poisson_sinx_fcns.h:133-149)
  *   punctures F = A u + N(u)          (multi_punctures_build_residual, ...with_opt.h:706-750)
- * Any linearisation of `mesh` is ignored here.  Host or device pointers.                          */
+ * Any linearisation of `mesh` is ignored here.  Host or device pointers; stream-ordered when all are device
+ * pointers (d4b_sync to wait), synchronous otherwise.                                               */
 void d4b_build_residual(d4b_mesh_t *mesh, const double *u, const double *rhs, double *F);
 
 /* The reference's multigrid "matrix operator" for such Jacobians

@@ -143,10 +143,13 @@ def _hierarchy(A, m1):
     return m0, mg
 
 
-def test_first_preconditioner_application_matches_reference(problem):
+@pytest.mark.parametrize("qtable", ["1", "0"])
+def test_first_preconditioner_application_matches_reference(problem, qtable, monkeypatch):
     """y = B(x): input and output of the reference's first d4est_krylov_pc_multigrid_apply of the Newton solve
     (matrix operator on the coarse level as the reference EXECUTES it, mode "reference"); the Galerkin product
     gives another preconditioner"""
+    # D4B_MG_QTABLE=0: the general (mixed-degree) form of the reference's slices instead of the per-level table
+    monkeypatch.setenv("D4B_MG_QTABLE", qtable)
     A, m1 = problem
     m0, mg = _hierarchy(A, m1)
     m1.linearize(np.zeros(m1.n))
