@@ -553,6 +553,38 @@ void launch_flat(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, 
   D4B_CUDA(cudaGetLastError());
 }
 
+#include "d4b_curved_kernel.cuh"
+
+// curved conforming elements, N <= 5: the shuffle kernel (D4B_CURVED_SHFL=0 selects the general conforming kernel)
+inline bool use_curved_shfl(int N) {
+  static const int on = getenv("D4B_CURVED_SHFL") ? atoi(getenv("D4B_CURVED_SHFL")) : 1;
+  return on != 0 && N <= 5;
+}
+
+template <int N>
+void launch_curved(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, int last) {
+  using C = CurvedShflCfg<N>;
+  if (last <= first) return;
+  CurvedArgs a;
+  a.elem = cls.d_elem; a.first = first; a.n_elem = last;
+  a.nodal_stride = m->d_nodal_stride;
+  a.FG = cls.d_FG; a.FF = m->d_fast_FF;
+  a.meta = static_cast<const FaceMeta *>(cls.d_face_meta);
+  a.uh = m->d_uhat; a.Au = d_Au; a.epi = m->epi;
+  a.W = m->d_W; a.quad_stride = m->d_quad_stride;
+  a.has_extra = cls.d_has_extra; a.extra = m->d_extra;
+  static const int prefetch = getenv("D4B_PREFETCH") ? atoi(getenv("D4B_PREFETCH")) : 1;
+  a.prefetch = prefetch;
+  const size_t smem = (size_t)C::EPB * C::SH_PER_ELEM * sizeof(double);
+  const int grid = (last - first + C::EPB - 1) / C::EPB;
+  if (m->d_W) curved_apply_kernel<N, true><<<grid, C::THREADS, smem, m->stream>>>(a);
+  else curved_apply_kernel<N, false><<<grid, C::THREADS, smem, m->stream>>>(a);
+  D4B_CUDA(cudaGetLastError());
+}
+template <> void launch_curved<6>(d4b_mesh *, const D4bFastClass &, double *, int, int) {}
+template <> void launch_curved<7>(d4b_mesh *, const D4bFastClass &, double *, int, int) {}
+template <> void launch_curved<8>(d4b_mesh *, const D4bFastClass &, double *, int, int) {}
+
 #include "d4b_hp_kernel.cuh"
 
 template <int N>
@@ -1007,6 +1039,16 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
         c.d_face_rec = d4b_dev_upload<int64_t>(m, face_rec.data(), face_rec.size());
         c.d_face_nbr = d4b_dev_upload<int64_t>(m, face_nbr.data(), face_nbr.size());
         c.d_face_code = d4b_dev_upload<int32_t>(m, face_code.data(), face_code.size());
+        if (N <= 5) {   // packed descriptors of the shuffle kernel (d4b_curved_kernel.cuh): rec = offset in doubles
+          std::vector<FaceMeta> meta(face_rec.size());
+          for (size_t j = 0; j < meta.size(); ++j) {
+            D4B_CHECK(face_rec[j] < INT32_MAX, "curved path: face records exceed 2^31 doubles");
+            meta[j].nbr = face_nbr[j];
+            meta[j].rec = (int32_t)face_rec[j];
+            meta[j].code = face_code[j];
+          }
+          c.d_face_meta = d4b_dev_upload<int64_t>(m, reinterpret_cast<const int64_t *>(meta.data()), meta.size() * 2);
+        }
       } else {
         std::vector<FaceMeta> meta(face_rec.size());
         for (size_t j = 0; j < meta.size(); ++j) {
@@ -1068,6 +1110,7 @@ void d4b_launch_fast_range(d4b_mesh *m, const double *d_u, double *d_Au, int wha
       if (what == 0) launch_interp_range<n>(m, c, d_u, lo, hi); \
       else if (c.kind >= 2) launch_hp<n>(m, c, d_Au, lo, hi, c.kind == 3); \
       else if (c.kind) launch_flat<n>(m, c, d_Au, lo, hi); \
+      else if (use_curved_shfl(n) && c.d_face_meta) launch_curved<n>(m, c, d_Au, lo, hi); \
       else launch_fast<n>(m, c, d_Au, lo, hi); \
       break;
     switch (c.deg + 1) {
@@ -1096,7 +1139,7 @@ void d4b_launch_fast(d4b_mesh *m, const double *d_u, double *d_Au, int part) {
   if (part == 0) return;
   for (const D4bFastClass &c : m->fast) {
     const int first = part == 1 ? 0 : c.n_interior, last = part == 1 ? c.n_interior : c.n_elem;
-#define D4B_CASE(n) case n: if (c.kind >= 2) launch_hp<n>(m, c, d_Au, first, last, c.kind == 3); else if (c.kind) launch_flat<n>(m, c, d_Au, first, last); else launch_fast<n>(m, c, d_Au, first, last); break;
+#define D4B_CASE(n) case n: if (c.kind >= 2) launch_hp<n>(m, c, d_Au, first, last, c.kind == 3); else if (c.kind) launch_flat<n>(m, c, d_Au, first, last); else if (use_curved_shfl(n) && c.d_face_meta) launch_curved<n>(m, c, d_Au, first, last); else launch_fast<n>(m, c, d_Au, first, last); break;
     switch (c.deg + 1) {
       D4B_CASE(2) D4B_CASE(3) D4B_CASE(4) D4B_CASE(5) D4B_CASE(6) D4B_CASE(7) D4B_CASE(8)
       default: D4B_ABORT("fast path: unsupported degree %d", c.deg);
