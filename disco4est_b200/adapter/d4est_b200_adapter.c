@@ -369,6 +369,27 @@ d4est_b200_flat_destroy (d4est_b200_flat_t * fl)
 
 /* ------------------------------------------------------------ apply_lhs */
 
+#ifndef D4EST_B200_ADAPTER_NO_DEVICE
+void
+d4est_b200_comm_init_from_p4est (p4est_t * p4est, int device)
+{
+  char id[128];
+  d4b_init (device);
+  if (p4est->mpisize <= 1) return;
+  memset (id, 0, sizeof (id));
+  if (p4est->mpirank == 0) d4b_comm_get_unique_id (id);
+  int mpiret = sc_MPI_Bcast (id, (int) sizeof (id), sc_MPI_BYTE, 0, p4est->mpicomm);
+  SC_CHECK_MPI (mpiret);
+  d4b_comm_init (id, p4est->mpirank, p4est->mpisize);
+}
+
+void
+d4est_b200_comm_finalize (void)
+{
+  d4b_comm_destroy ();
+}
+#endif
+
 d4est_b200_ctx_t *
 d4est_b200_ctx_new (d4est_laplacian_flux_data_t * flux_data)
 {

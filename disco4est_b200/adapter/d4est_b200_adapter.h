@@ -202,6 +202,14 @@ void d4est_b200_build_residual(p4est_t *p4est, d4est_ghost_t *ghost, d4est_ghost
 void d4est_b200_set_nonlinear_term(d4est_b200_ctx_t *ctx, const d4b_nonlinear_desc_t *desc,
                                    d4est_b200_ctx_t *residual_ctx);
 
+/* Collective context from the reference side: one NCCL communicator over the ranks of
+ * p4est->mpicomm.  Rank 0 draws the id (d4b_comm_get_unique_id), sc_MPI_Bcast carries its 128 bytes, every rank
+ * selects `device` (e.g. local rank) and calls d4b_comm_init; the neighbour lists of the halo exchange come with
+ * every flattened mesh (mirror / ghost offsets of d4est_ghost_t, src/Mesh/d4est_ghost_data.c:171-199).  Call once
+ * after p4est_new_ext; a no-op on one rank.  d4est_b200_comm_finalize before sc_MPI_Finalize.                  */
+void d4est_b200_comm_init_from_p4est(p4est_t *p4est, int device);
+void d4est_b200_comm_finalize(void);
+
 d4est_b200_ctx_t *d4est_b200_ctx_new(d4est_laplacian_flux_data_t *flux_data);
 void d4est_b200_ctx_destroy(d4est_b200_ctx_t *ctx);
 /* forget (and free) every cached device mesh: the next call re-flattens and uploads */

@@ -534,7 +534,7 @@ void launch_flat(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, 
   FlatArgs a;
   a.elem = cls.d_elem; a.first = first; a.n_elem = last;
   a.nodal_stride = m->d_nodal_stride;
-  a.FG = cls.d_FG; a.FF3 = m->d_flat_FF;
+  a.FG = cls.d_FG; a.FGc = cls.d_FGc; a.FF3 = m->d_flat_FF;
   a.meta = static_cast<const FaceMeta *>(cls.d_face_meta);
   a.uh = m->d_uhat; a.Au = d_Au; a.epi = m->epi;
   size_t smem = (size_t)C::EPB * C::SH_PER_ELEM * sizeof(double);
@@ -544,11 +544,17 @@ void launch_flat(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, 
   if (!configured) {
     D4B_CUDA(cudaFuncSetAttribute(flat_apply_kernel<N, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     D4B_CUDA(cudaFuncSetAttribute(flat_apply_kernel<N, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    D4B_CUDA(cudaFuncSetAttribute(flat_apply_kernel<N, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    D4B_CUDA(cudaFuncSetAttribute(flat_apply_kernel<N, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = true;
   }
-  a.prefetch = getenv("D4B_PREFETCH") ? atoi(getenv("D4B_PREFETCH")) : 2;
+  static const int prefetch = getenv("D4B_PREFETCH") ? atoi(getenv("D4B_PREFETCH")) : 2;
+  a.prefetch = prefetch;
   int grid = (last - first + C::EPB - 1) / C::EPB;
-  if (m->d_W) flat_apply_kernel<N, true><<<grid, C::THREADS, smem, m->stream>>>(a);
+  if (cls.d_FGc) {
+    if (m->d_W) flat_apply_kernel<N, true, true><<<grid, C::THREADS, smem, m->stream>>>(a);
+    else flat_apply_kernel<N, false, true><<<grid, C::THREADS, smem, m->stream>>>(a);
+  } else if (m->d_W) flat_apply_kernel<N, true><<<grid, C::THREADS, smem, m->stream>>>(a);
   else flat_apply_kernel<N, false><<<grid, C::THREADS, smem, m->stream>>>(a);
   D4B_CUDA(cudaGetLastError());
 }
@@ -1034,7 +1040,34 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
         D4B_CUDA(cudaMalloc(&c.d_has_extra, has_extra.size()));
         D4B_CUDA(cudaMemcpy(c.d_has_extra, has_extra.data(), has_extra.size(), cudaMemcpyHostToDevice));
       }
-      c.d_FG = d4b_dev_upload<double>(m, FG.data(), FG.size());
+      // tangential-free class whose elements are all affine (J and d(rst)/d(xyz) constant over the element, so
+      // G / (w_a w_b w_c) is one number per component): six doubles per element instead of 6 N^3.  Exact up to
+      // 1e-14 of the largest component (the reference computes J numerically point by point); D4B_AFFINE=0 keeps
+      // the per-point metric.
+      bool affine = kind == 1 && !(getenv("D4B_AFFINE") && atoi(getenv("D4B_AFFINE")) == 0);
+      std::vector<double> FGc;
+      if (affine) {
+        FGc.resize((size_t)6 * els.size());
+        const double *w = tabs[N].w;
+        int bad = 0;
+#pragma omp parallel for schedule(static) reduction(+ : bad)
+        for (size_t i = 0; i < els.size(); ++i) {
+          double scale = 0.;
+          for (int cpl = 0; cpl < 6; ++cpl) {
+            const double gc0 = FG[(i * 6 + cpl) * N3] / (w[0] * w[0] * w[0]);
+            FGc[i * 6 + cpl] = gc0;
+            scale = fmax(scale, fabs(gc0));
+          }
+          for (int cpl = 0; cpl < 6 && !bad; ++cpl)
+            for (int k = 0; k < N3; ++k) {
+              const double w3 = w[k % N] * w[(k / N) % N] * w[k / NN];
+              if (fabs(FG[(i * 6 + cpl) * N3 + k] - FGc[i * 6 + cpl] * w3) > 1e-14 * scale * w3) { ++bad; break; }
+            }
+        }
+        affine = bad == 0;
+      }
+      if (affine) c.d_FGc = d4b_dev_upload<double>(m, FGc.data(), FGc.size());
+      else c.d_FG = d4b_dev_upload<double>(m, FG.data(), FG.size());
       if (kind == 0) {
         c.d_face_rec = d4b_dev_upload<int64_t>(m, face_rec.data(), face_rec.size());
         c.d_face_nbr = d4b_dev_upload<int64_t>(m, face_nbr.data(), face_nbr.size());

@@ -30,6 +30,7 @@ struct FlatArgs {
   int n_elem;
   const int64_t *nodal_stride;
   const double *FG;             // [n_elem][6][N^3]
+  const double *FGc;            // CG kernels: [n_elem][6], metric of an affine element without the weights
   const double *FF3;            // compact face records: A_m[n], A_p[n] (g on the boundary), sj*sigma
   const FaceMeta *meta;         // [6*n_elem]
   const double *uh;
@@ -151,7 +152,9 @@ __device__ __forceinline__ void flat_face(const FlatArgs &a, const FastTab &T, c
   vd = -wxy * cm * Amn * du;
 }
 
-template <int N, bool MASS>
+// CG: every element of the class is affine (J and d(rst)/d(xyz) constant over the element, exact test at
+// set-up): the six metric components are one number each per element, times the Gauss weights
+template <int N, bool MASS, bool CG = false>
 __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) flat_apply_kernel(FlatArgs a) {
   using C = FlatCfg<N>;
   constexpr int NN = C::NN, N3 = C::N3;
@@ -173,7 +176,7 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) f
 
   // the volume metric is the largest stream and is first needed half-way
   // through the kernel: ask the L2 for this block's share now
-  if (threadIdx.x == 0 && a.prefetch) {
+  if (!CG && threadIdx.x == 0 && a.prefetch) {
     constexpr unsigned kBlockBytes = C::EPB * 6 * N3 * sizeof(double);
     const int e0 = a.first + (int)blockIdx.x * C::EPB, left = a.n_elem - e0;
     l2_prefetch(a.FG + (size_t)e0 * (6 * N3), left >= C::EPB ? kBlockBytes : left * 6 * N3 * 8);
@@ -270,13 +273,24 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) f
   block_sync<C::THREADS>();
   if (active) {   // T-orientation: metric, Dg^T along c + faces 4/5; V0 becomes the residual
     double ft[N];
-    const double *G = a.FG + (size_t)ei * (6 * N3) + lt;
+    const double *G = CG ? nullptr : a.FG + (size_t)ei * (6 * N3) + lt;
+    double gc[6];
+    if (CG) {
+#pragma unroll
+      for (int q = 0; q < 6; ++q) gc[q] = a.FGc[(size_t)ei * 6 + q] * wxy;
+    }
 #pragma unroll
     for (int c = 0; c < N; ++c) {
       const int idx = vix<N>(lx, ly, c);
       double gr = V1[idx], gs = V2[idx];
-      double G00 = G[0 * N3 + NN * c], G01 = G[1 * N3 + NN * c], G02 = G[2 * N3 + NN * c];
-      double G11 = G[3 * N3 + NN * c], G12 = G[4 * N3 + NN * c], G22 = G[5 * N3 + NN * c];
+      double G00, G01, G02, G11, G12, G22;
+      if (CG) {
+        const double wc = T.w[c];
+        G00 = gc[0] * wc; G01 = gc[1] * wc; G02 = gc[2] * wc; G11 = gc[3] * wc; G12 = gc[4] * wc; G22 = gc[5] * wc;
+      } else {
+        G00 = G[0 * N3 + NN * c]; G01 = G[1 * N3 + NN * c]; G02 = G[2 * N3 + NN * c];
+        G11 = G[3 * N3 + NN * c]; G12 = G[4 * N3 + NN * c]; G22 = G[5 * N3 + NN * c];
+      }
       V1[idx] = G00 * gr + G01 * gs + G02 * gt[c];
       V2[idx] = G01 * gr + G11 * gs + G12 * gt[c];
       ft[c] = G02 * gr + G12 * gs + G22 * gt[c];

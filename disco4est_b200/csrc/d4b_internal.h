@@ -52,6 +52,8 @@ struct D4bFastClass {
   int n_hat = 0;                 // elements of this degree with deg_quad == deg (uh is computed for all)
   int32_t *d_hat_elem = nullptr;
   double *d_FG = nullptr;        // [n_elem][6][N^3] volume metric
+  double *d_FGc = nullptr;       // kind 1, every element affine: [n_elem][6] metric without the quadrature weights
+                                 // (G = w_a w_b w_c Gc at every point); d_FG is then not stored
   int64_t *d_face_rec = nullptr; // [6*n_elem] face record offset
   int64_t *d_face_nbr = nullptr; // [6*n_elem] neighbour nodal offset / -1
   int32_t *d_face_code = nullptr;

@@ -390,7 +390,7 @@ extern "C" void d4b_mesh_destroy(d4b_mesh_t *m) {
   for (void *p : ptrs)
     if (p) cudaFree(p);
   for (auto &c : m->fast) {
-    void *cp[] = {c.d_elem, c.d_hat_elem, c.d_FG, c.d_face_rec, c.d_face_nbr, c.d_face_code, c.d_face_meta,
+    void *cp[] = {c.d_elem, c.d_hat_elem, c.d_FG, c.d_FGc, c.d_face_rec, c.d_face_nbr, c.d_face_code, c.d_face_meta,
                   c.d_ghost_hat, c.d_has_extra, c.d_face_mask};
     for (void *p : cp)
       if (p) cudaFree(p);

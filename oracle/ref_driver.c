@@ -606,6 +606,11 @@ main (int argc, char *argv[])
                                   sizeof (d4est_element_data_t), NULL, NULL);
   p4est_partition (p4est, 1, NULL);
   p4est_balance (p4est, P4EST_CONNECT_FULL, NULL);
+#ifdef D4B_WITH_DEVICE
+  /* the reference-side bootstrap of the collective context: device selection + (on > 1 rank) the NCCL id over
+   * p4est->mpicomm; this serial build has one rank */
+  if (use_b200) d4est_b200_comm_init_from_p4est (p4est, 0);
+#endif
 
   d4est_ghost_t *d4est_ghost = d4est_ghost_init (p4est);
   d4est_operators_t *d4est_ops = d4est_ops_init (20);

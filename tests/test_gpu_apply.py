@@ -273,3 +273,24 @@ def test_face_split_on_synthetic_spheres(kw, monkeypatch):
         out.append(a)
     monkeypatch.delenv("D4B_SPLIT")
     assert rel(out[0], out[1]) < 1e-13
+
+
+@pytest.mark.parametrize("case", ["brick_l2_p1", "brick_l2_p3", "brick_l2_p5", "brick_l2_p7", "brick_l2_p2_bc"])
+def test_affine_path_matches_per_point_metric(golden, case, monkeypatch):
+    """bricks: every element is affine, the tangential-free kernel then reads the volume metric once per element
+    (flat_apply_kernel<N, MASS, CG = true>); D4B_AFFINE=0 keeps the per-point metric.  Same operator."""
+    from disco4est_b200 import Mesh
+
+    A = golden(case)
+    u = np.ascontiguousarray(A["u"])
+    out = {}
+    for flag in ("0", "1"):
+        monkeypatch.setenv("D4B_AFFINE", flag)
+        m = Mesh(A)
+        assert m.flat_elements() == int(A["n_local"][0])
+        out[flag] = np.zeros_like(u)
+        m.apply(u, out[flag])
+        m.close()
+    assert rel(out["1"], A["Au_plain"]) < TOL
+    assert rel(out["0"], A["Au_plain"]) < TOL
+    assert rel(out["1"], out["0"]) < 1e-13
