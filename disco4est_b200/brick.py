@@ -60,6 +60,9 @@ def lgl_nodes(N):
     return x
 
 
+ROOT_LEN = 1 << 30   # P4EST_ROOT_LEN
+
+
 def partition_offsets(E, world):
     """Equal-count Morton-curve partition, the same rule as p4est_partition with
     uniform weights: rank r owns global elements [E*r//world, E*(r+1)//world)."""
@@ -84,7 +87,7 @@ def _global_coords(g, n, trees):
     return (t % a) * n + ix, ((t // a) % b) * n + iy, (t // (a * b)) * n + iz
 
 
-def brick_desc(level, p, prefactor=2.0, penalty_fcn=0, rank=0, world=1, trees=(1, 1, 1)):
+def brick_desc(level, p, prefactor=2.0, penalty_fcn=0, rank=0, world=1, trees=(1, 1, 1), geometry=True):
     """dict of arrays for make_desc()/Mesh() describing rank `rank`'s part of a
     brick of trees[0] x trees[1] x trees[2] unit-cube trees (p4est_connectivity_new_brick),
     each refined uniformly to `level` (element size h = 2**-level everywhere), elements
@@ -93,7 +96,11 @@ def brick_desc(level, p, prefactor=2.0, penalty_fcn=0, rank=0, world=1, trees=(1
     Ghost elements are the face neighbours owned by other ranks, numbered by
     (owner, global id) like p4est's ghost layer; mirrors are the local elements
     other ranks see as ghosts (src/Mesh/d4est_ghost.c:47-90,
-    d4est_ghost_data.c:142-255 for the exchange the plan describes)."""
+    d4est_ghost_data.c:142-255 for the exchange the plan describes).
+
+    geometry=False: returns (topology, geom) for Mesh(topology, geom=geom) instead -- no per-point array is
+    built on the host, the factors are generated and folded on the device (face_h = tree h, which is the
+    element width 2**-level exactly, like the hm = hp = h of the full description)."""
     n = 1 << level
     Eg = n ** 3 * trees[0] * trees[1] * trees[2]
     N = p + 1
@@ -116,11 +123,12 @@ def brick_desc(level, p, prefactor=2.0, penalty_fcn=0, rank=0, world=1, trees=(1
     A["nodal_stride"] = e * n3
     A["quad_stride"] = e * n3
     LQ = E * n3
-    A["J_quad"] = np.full(LQ, (0.5 * h) ** 3)
-    rst = np.zeros((9, LQ))
-    for i in range(3):
-        rst[i * 3 + i, :] = 2.0 / h
-    A["rst_xyz_quad"] = rst.reshape(-1)
+    if geometry:
+        A["J_quad"] = np.full(LQ, (0.5 * h) ** 3)
+        rst = np.zeros((9, LQ))
+        for i in range(3):
+            rst[i * 3 + i, :] = 2.0 / h
+        A["rst_xyz_quad"] = rst.reshape(-1)
     # sides: s = 6*e + f
     S = 6 * E
     f = np.tile(np.arange(6, dtype=np.int32), E)
@@ -173,6 +181,21 @@ def brick_desc(level, p, prefactor=2.0, penalty_fcn=0, rank=0, world=1, trees=(1
     A["mirror_proc_offsets"] = np.concatenate([[0], np.cumsum([a.size for a in per_peer])]).astype(np.int32)
     A["mirror_proc_mirrors"] = (np.searchsorted(mirror_elem, np.concatenate(per_peer)).astype(np.int32)
                                 if world > 1 else np.zeros(0, np.int32))
+    A["sipg_penalty_prefactor"] = prefactor
+    A["sipg_penalty_fcn"] = penalty_fcn
+    A["bc_type"] = 0
+    if not geometry:
+        dq = ROOT_LEN >> level
+        gx, gy, gz = _global_coords(ghost_gid, n, trees)
+        geom = {"geom_type": "brick", "face_h_type": "tree_h", "X0": 0.0, "X1": 1.0, "Y0": 0.0, "Y1": 1.0,
+                "Z0": 0.0, "Z1": 1.0,
+                "elem_tree": ((e + start) // n ** 3).astype(np.int32),
+                "elem_q": (np.stack([ix % n, iy % n, iz % n], axis=1) * dq).astype(np.int32).reshape(-1),
+                "elem_dq": np.full(E, dq, np.int32),
+                "ghost_tree": (ghost_gid // n ** 3).astype(np.int32),
+                "ghost_q": (np.stack([gx % n, gy % n, gz % n], axis=1) * dq).astype(np.int32).reshape(-1),
+                "ghost_dq": np.full(n_ghost, dq, np.int32)}
+        return A, geom
     MP = S * n2
     A["sj_m_mortar_quad"] = np.full(MP, (0.5 * h) ** 2)
     nvec = np.zeros((S, 3, n2))

@@ -738,17 +738,135 @@ void build_fast_tab(int N, FastTab &T) {
   for (int j = 0; j < N; ++j) T.w[j] = wg[j];
 }
 
-inline int perm_index_host(int n, int perm, int a, int b) {
-  int row = (perm & 4) ? a : b, col = (perm & 4) ? b : a;
-  if (perm & 2) row = n - 1 - row;
-  if (perm & 1) col = n - 1 - col;
-  return row * n + col;
+
+// ---- set-up on the device: everything that touches per-point data reads m->d_mortar / m->d_G where they already
+// are (uploaded or, with device geometry, generated there); only flags and index lists cross the bus ----
+struct RecSrc { int32_t side, boundary, NN, nd, ndp, pad; int64_t dst; };
+
+// per conforming side: bit 0 = tangential-free (face_is_flat), bit 1 = consistent with the record of the other side
+__global__ void side_flags_kernel(int n_sides, int64_t MP, const double *__restrict__ mortar,
+                                  const int32_t *__restrict__ faces_m, const int32_t *__restrict__ faces_p,
+                                  const int32_t *__restrict__ f_m, const int32_t *__restrict__ f_p,
+                                  const int32_t *__restrict__ e_m, const int32_t *__restrict__ e_p,
+                                  const int32_t *__restrict__ perm, const int64_t *__restrict__ mstride,
+                                  const int32_t *__restrict__ deg_quad, const int32_t *__restrict__ elem_side,
+                                  unsigned char *__restrict__ flags) {
+  const int s = blockIdx.x;
+  if (s >= n_sides) return;
+  __shared__ int not_flat;
+  __shared__ double sh_scale[64], sh_err[64];
+  if (threadIdx.x == 0) not_flat = 0;
+  __syncthreads();
+  if (faces_m[s] != 1 || faces_p[s] > 1) { if (threadIdx.x == 0) flags[s] = 0; return; }
+  const int32_t em = e_m[4 * s];
+  if (em < 0) { if (threadIdx.x == 0) flags[s] = 0; return; }
+  const int N = deg_quad[em] + 1, NN = N * N;
+  const int64_t S = mstride[s];
+  const int nd = f_m[s] >> 1;
+  const bool has_p = faces_p[s] == 1;
+  const int ndp = has_p ? (f_p[s] >> 1) : 0;
+  for (int k = threadIdx.x; k < NN; k += blockDim.x) {
+    for (int l = 0; l < 3; ++l) {
+      if (l != nd && mortar[(size_t)l * MP + S + k] != 0.) not_flat = 1;
+      if (has_p && l != ndp && mortar[(size_t)(3 + l) * MP + S + k] != 0.) not_flat = 1;
+    }
+  }
+  // consistency with the other side's record (only sides with a local neighbour of the same size)
+  double scale = 0., err = 0.;
+  bool cons_valid = false;
+  if (has_p && e_p[4 * s] >= 0) {
+    const int32_t ep = e_p[4 * s];
+    const int s2 = elem_side[6 * ep + f_p[s]];
+    if (s2 >= 0 && deg_quad[ep] + 1 == N && faces_m[s2] == 1 && faces_p[s2] == 1) {
+      cons_valid = true;
+      const int64_t S2 = mstride[s2];
+      const int pm = perm[s];
+      for (int k = threadIdx.x; k < NN; k += blockDim.x) {
+        const int kp = perm_xy(N, pm, k % N, k / N);
+        for (int l = 0; l < 3; ++l) {
+          const double am = mortar[(size_t)l * MP + S + k], ap = mortar[(size_t)(3 + l) * MP + S + k];
+          const double oam = mortar[(size_t)l * MP + S2 + kp], oap = mortar[(size_t)(3 + l) * MP + S2 + kp];
+          scale = fmax(scale, fmax(fabs(am), fabs(ap)));
+          err = fmax(err, fmax(fabs(am + oap), fabs(ap + oam)));
+        }
+        const double sg = mortar[(size_t)6 * MP + S + k], osg = mortar[(size_t)6 * MP + S2 + kp];
+        scale = fmax(scale, fabs(sg));
+        err = fmax(err, fabs(sg - osg));
+      }
+    }
+  }
+  sh_scale[threadIdx.x] = scale; sh_err[threadIdx.x] = err;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int t = 1; t < blockDim.x; ++t) { scale = fmax(scale, sh_scale[t]); err = fmax(err, sh_err[t]); }
+    flags[s] = (unsigned char)((not_flat ? 0 : 1) | ((cons_valid && err <= 1e-12 * scale) ? 2 : 0));
+  }
+}
+
+// face records from the folded mortar planes: 7 planes (+ g in the A_p[0] slot of boundary faces), or the
+// compact 3 planes (A_m[n], A_p[n'] or g, sj sigma)
+__global__ void gather_records_kernel(int n, const RecSrc *__restrict__ src, int compact, int64_t MP,
+                                      const double *__restrict__ mortar, const int64_t *__restrict__ mstride,
+                                      double *__restrict__ out) {
+  const int r = blockIdx.x;
+  if (r >= n) return;
+  const RecSrc q = src[r];
+  const int64_t S = mstride[q.side];
+  double *o = out + q.dst;
+  for (int k = threadIdx.x; k < q.NN; k += blockDim.x) {
+    if (compact) {
+      o[k] = mortar[(size_t)q.nd * MP + S + k];
+      o[q.NN + k] = q.boundary ? mortar[(size_t)7 * MP + S + k] : mortar[(size_t)(3 + q.ndp) * MP + S + k];
+      o[2 * q.NN + k] = mortar[(size_t)6 * MP + S + k];
+    } else {
+      for (int pl = 0; pl < 7; ++pl) o[pl * q.NN + k] = mortar[(size_t)pl * MP + S + k];
+      if (q.boundary) o[3 * q.NN + k] = mortar[(size_t)7 * MP + S + k];
+    }
+  }
+}
+
+// FG[i][cpl][k] = G[cpl][quad_stride[elem[i]] + k]
+__global__ void gather_fg_kernel(int n_elem, int N3, int64_t LQ, const int32_t *__restrict__ elem,
+                                 const int64_t *__restrict__ quad_stride, const double *__restrict__ G,
+                                 double *__restrict__ FG) {
+  const int i = blockIdx.x;
+  if (i >= n_elem) return;
+  const int64_t qs = quad_stride[elem[i]];
+  for (int j = threadIdx.x; j < 6 * N3; j += blockDim.x)
+    FG[(size_t)i * 6 * N3 + j] = G[(size_t)(j / N3) * LQ + qs + j % N3];
+}
+
+// affine test of a class: Gc[i][cpl] = G / (w_a w_b w_c) at point 0, *bad += 1 if some point deviates
+__global__ void affine_kernel(int n_elem, int N, int64_t LQ, const int32_t *__restrict__ elem,
+                              const int64_t *__restrict__ quad_stride, const double *__restrict__ G,
+                              double *__restrict__ Gc, int *__restrict__ bad) {
+  const int i = blockIdx.x;
+  if (i >= n_elem) return;
+  const FastTab &T = c_tab[N];
+  const int NN = N * N, N3 = N * NN;
+  const int64_t qs = quad_stride[elem[i]];
+  __shared__ double gc[6];
+  __shared__ double scale;
+  if (threadIdx.x == 0) {
+    double sc = 0.;
+    for (int cpl = 0; cpl < 6; ++cpl) {
+      gc[cpl] = G[(size_t)cpl * LQ + qs] / (T.w[0] * T.w[0] * T.w[0]);
+      Gc[(size_t)i * 6 + cpl] = gc[cpl];
+      sc = fmax(sc, fabs(gc[cpl]));
+    }
+    scale = sc;
+  }
+  __syncthreads();
+  for (int j = threadIdx.x; j < 6 * N3; j += blockDim.x) {
+    const int cpl = j / N3, k = j % N3;
+    const double w3 = T.w[k % N] * T.w[(k / N) % N] * T.w[k / NN];
+    if (fabs(G[(size_t)cpl * LQ + qs + k] - gc[cpl] * w3) > 1e-14 * scale * w3) atomicAdd(bad, 1);
+  }
 }
 
 }  // namespace
 
-void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<double> &mortar,
-                    const std::vector<double> &G, const std::vector<int32_t> &elem_side,
+void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<int32_t> &elem_side,
                     std::vector<char> &is_fast) {
   const int E = d->n_local;
   const int64_t MP = d->local_mortar_nodes_quad, LQ = d->local_nodes_quad;
@@ -824,72 +942,43 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
   if (any_hp) build_hp_tabs(m);
   const bool allow_flat = !(getenv("D4B_NO_FLAT") && atoi(getenv("D4B_NO_FLAT")) != 0);
 
-  // a face is tangential-free when A_m[l] (l != its normal direction) and
-  // A_p[l] (l != the neighbour's normal direction) vanish at every face point
-  auto face_is_flat = [&](int s, int NN) -> bool {
-    const int64_t S = d->side_mortar_stride[s];
-    const int nd = d->side_f_m[s] >> 1;
-    for (int l = 0; l < 3; ++l) {
-      if (l == nd) continue;
-      for (int k = 0; k < NN; ++k)
-        if (mortar[(size_t)l * MP + S + k] != 0.) return false;
-    }
-    if (d->side_faces_p[s] == 1) {
-      const int ndp = d->side_f_p[s] >> 1;
-      for (int l = 0; l < 3; ++l) {
-        if (l == ndp) continue;
-        for (int k = 0; k < NN; ++k)
-          if (mortar[(size_t)(3 + l) * MP + S + k] != 0.) return false;
-      }
-    }
-    return true;
-  };
+  // per-side flags from the folded mortar planes where they lie (device): tangential-free, and -- for a side
+  // with a local neighbour -- consistent with the record written from the other side (n_p sj_p = -n_m sj_m)
+  std::vector<unsigned char> side_flags((size_t)std::max(d->n_sides, 1), 0);
+  if (d->n_sides > 0) {
+    unsigned char *d_flags = nullptr;
+    D4B_CUDA(cudaMalloc(&d_flags, (size_t)d->n_sides));
+    side_flags_kernel<<<d->n_sides, 64, 0, m->stream>>>(d->n_sides, MP, m->d_mortar, m->d_side_faces_m, m->d_side_faces_p,
+                                                        m->d_side_f_m, m->d_side_f_p, m->d_side_e_m, m->d_side_e_p,
+                                                        m->d_side_perm, m->d_side_mortar_stride, m->d_deg_quad,
+                                                        m->d_elem_side, d_flags);
+    D4B_CUDA(cudaGetLastError());
+    D4B_CUDA(cudaMemcpyAsync(side_flags.data(), d_flags, (size_t)d->n_sides, cudaMemcpyDeviceToHost, m->stream));
+    D4B_CUDA(cudaStreamSynchronize(m->stream));
+    cudaFree(d_flags);
+  }
+  auto face_is_flat = [&](int s, int) -> bool { return side_flags[s] & 1; };
 
-  // ---- face records, one per face, shared by both sides when consistent
-  std::vector<double> FF, FF3;
+  // ---- face records, one per face, shared by both sides when consistent.  Only their places are decided
+  // here; gather_records_kernel fills them from m->d_mortar afterwards.
+  int64_t ff_size = 0, ff3_size = 0;
+  std::vector<RecSrc> src7, src3;
   std::vector<int64_t> rec_of((size_t)6 * E, -1), rec3_of((size_t)6 * E, -1);   // owning (element, face) -> record
   auto write_record = [&](int s, int NN, bool boundary) -> int64_t {
-    int64_t off = (int64_t)FF.size();
-    FF.resize(FF.size() + (size_t)7 * NN);
-    int64_t S = d->side_mortar_stride[s];
-    for (int q = 0; q < 7; ++q)
-      for (int k = 0; k < NN; ++k) FF[off + q * NN + k] = mortar[(size_t)q * MP + S + k];
-    if (boundary)
-      for (int k = 0; k < NN; ++k) FF[off + 3 * NN + k] = mortar[(size_t)7 * MP + S + k];   // g
+    const int64_t off = ff_size;
+    ff_size += (int64_t)7 * NN;
+    src7.push_back(RecSrc{s, boundary ? 1 : 0, NN, 0, 0, 0, off});
     return off;
   };
   auto write_record3 = [&](int s, int NN, bool boundary) -> int64_t {
-    int64_t idx = (int64_t)(FF3.size() / ((size_t)3 * NN));
-    size_t off = FF3.size();
-    FF3.resize(off + (size_t)3 * NN);
-    const int64_t S = d->side_mortar_stride[s];
+    const int64_t idx = ff3_size / ((int64_t)3 * NN);
     const int nd = d->side_f_m[s] >> 1, ndp = boundary ? 0 : (d->side_f_p[s] >> 1);
-    for (int k = 0; k < NN; ++k) {
-      FF3[off + k] = mortar[(size_t)nd * MP + S + k];
-      FF3[off + NN + k] = boundary ? mortar[(size_t)7 * MP + S + k] : mortar[(size_t)(3 + ndp) * MP + S + k];
-      FF3[off + 2 * NN + k] = mortar[(size_t)6 * MP + S + k];
-    }
+    src3.push_back(RecSrc{s, boundary ? 1 : 0, NN, nd, ndp, 0, ff3_size});
+    ff3_size += (int64_t)3 * NN;
     return idx;
   };
-  // can side s use the record written from the other side s2?
-  auto consistent = [&](int s, int s2, int N, int perm) -> bool {
-    const int NN = N * N;
-    const int64_t S1 = d->side_mortar_stride[s], S2 = d->side_mortar_stride[s2];
-    double scale = 0., err = 0.;
-    for (int k = 0; k < NN; ++k) {
-      int kp = perm_index_host(N, perm, k % N, k / N);
-      for (int l = 0; l < 3; ++l) {
-        double am = mortar[(size_t)l * MP + S1 + k], ap = mortar[(size_t)(3 + l) * MP + S1 + k];
-        double oam = mortar[(size_t)l * MP + S2 + kp], oap = mortar[(size_t)(3 + l) * MP + S2 + kp];
-        scale = fmax(scale, fmax(fabs(am), fabs(ap)));
-        err = fmax(err, fmax(fabs(am + oap), fabs(ap + oam)));
-      }
-      double sg = mortar[(size_t)6 * MP + S1 + k], osg = mortar[(size_t)6 * MP + S2 + kp];
-      scale = fmax(scale, fabs(sg));
-      err = fmax(err, fabs(sg - osg));
-    }
-    return err <= 1e-12 * scale;
-  };
+  // can side s use the record written from the other side?
+  auto consistent = [&](int s, int, int, int) -> bool { return side_flags[s] & 2; };
 
   FastTab tabs[9];
   memset(tabs, 0, sizeof(tabs));
@@ -929,13 +1018,13 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
     const std::vector<int32_t> &ghost_hat = ghost_hat_p;
     bool hat_done = false;
     // compact records are addressed by index * 3 NN: keep the array a multiple of this degree's record
-    while (FF3.size() % ((size_t)3 * NN)) FF3.push_back(0.);
-    int64_t zero7 = -1, zero3 = -1;   // all-zero records that switch a face off
+    while (ff3_size % ((int64_t)3 * NN)) ++ff3_size;
+    int64_t zero7 = -1, zero3 = -1;   // all-zero records that switch a face off (the arrays start zeroed)
     if (!split_by_deg[p].empty()) {
-      zero7 = (int64_t)FF.size();
-      FF.resize(FF.size() + (size_t)7 * NN, 0.);
-      zero3 = (int64_t)(FF3.size() / ((size_t)3 * NN));
-      FF3.resize(FF3.size() + (size_t)3 * NN, 0.);
+      zero7 = ff_size;
+      ff_size += (int64_t)7 * NN;
+      zero3 = ff3_size / ((int64_t)3 * NN);
+      ff3_size += (int64_t)3 * NN;
       // the FACE_ONLY class runs before this degree's conforming classes (same stream)
       std::vector<int32_t> els = split_by_deg[p];
       auto mid = std::stable_partition(els.begin(), els.end(), [&](int e) { return !touches_ghost(e); });
@@ -976,15 +1065,9 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
       }
       c.n_elem = (int)els.size();
       c.n_interior = n_interior_kind[kind];
+      c.d_elem = d4b_dev_upload<int32_t>(m, els.data(), els.size());
       std::vector<int64_t> face_rec((size_t)6 * els.size()), face_nbr((size_t)6 * els.size(), -1);
       std::vector<int32_t> face_code((size_t)6 * els.size(), 0);
-      std::vector<double> FG((size_t)6 * N3 * els.size());
-#pragma omp parallel for schedule(static)
-      for (size_t i = 0; i < els.size(); ++i) {
-        const int64_t qs = d->quad_stride[els[i]];
-        for (int cpl = 0; cpl < 6; ++cpl)
-          for (int k = 0; k < N3; ++k) FG[(i * 6 + cpl) * N3 + k] = G[(size_t)cpl * LQ + qs + k];
-      }
       std::vector<unsigned char> has_extra(els.size(), 0);
       bool any_extra = false;
       for (size_t i = 0; i < els.size(); ++i) {
@@ -1034,7 +1117,6 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
           face_code[fi] = fp | (perm << 3) | (i_own ? kOwn : 0);
         }
       }
-      c.d_elem = d4b_dev_upload<int32_t>(m, els.data(), els.size());
       c.h_elem = els;
       if (any_extra) {
         D4B_CUDA(cudaMalloc(&c.d_has_extra, has_extra.size()));
@@ -1045,29 +1127,27 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
       // 1e-14 of the largest component (the reference computes J numerically point by point); D4B_AFFINE=0 keeps
       // the per-point metric.
       bool affine = kind == 1 && !(getenv("D4B_AFFINE") && atoi(getenv("D4B_AFFINE")) == 0);
-      std::vector<double> FGc;
       if (affine) {
-        FGc.resize((size_t)6 * els.size());
-        const double *w = tabs[N].w;
-        int bad = 0;
-#pragma omp parallel for schedule(static) reduction(+ : bad)
-        for (size_t i = 0; i < els.size(); ++i) {
-          double scale = 0.;
-          for (int cpl = 0; cpl < 6; ++cpl) {
-            const double gc0 = FG[(i * 6 + cpl) * N3] / (w[0] * w[0] * w[0]);
-            FGc[i * 6 + cpl] = gc0;
-            scale = fmax(scale, fabs(gc0));
-          }
-          for (int cpl = 0; cpl < 6 && !bad; ++cpl)
-            for (int k = 0; k < N3; ++k) {
-              const double w3 = w[k % N] * w[(k / N) % N] * w[k / NN];
-              if (fabs(FG[(i * 6 + cpl) * N3 + k] - FGc[i * 6 + cpl] * w3) > 1e-14 * scale * w3) { ++bad; break; }
-            }
-        }
+        double *d_Gc = d4b_dev_alloc<double>(m, (size_t)6 * els.size());
+        int *d_bad = nullptr, bad = 0;
+        D4B_CUDA(cudaMalloc(&d_bad, sizeof(int)));
+        D4B_CUDA(cudaMemsetAsync(d_bad, 0, sizeof(int), m->stream));
+        affine_kernel<<<(int)els.size(), 64, 0, m->stream>>>((int)els.size(), N, LQ, c.d_elem, m->d_quad_stride, m->d_G,
+                                                             d_Gc, d_bad);
+        D4B_CUDA(cudaGetLastError());
+        D4B_CUDA(cudaMemcpyAsync(&bad, d_bad, sizeof(int), cudaMemcpyDeviceToHost, m->stream));
+        D4B_CUDA(cudaStreamSynchronize(m->stream));
+        cudaFree(d_bad);
         affine = bad == 0;
+        if (affine) c.d_FGc = d_Gc;
+        else { cudaFree(d_Gc); m->device_bytes -= (int64_t)(6 * els.size() * sizeof(double)); }
       }
-      if (affine) c.d_FGc = d4b_dev_upload<double>(m, FGc.data(), FGc.size());
-      else c.d_FG = d4b_dev_upload<double>(m, FG.data(), FG.size());
+      if (!affine) {
+        c.d_FG = d4b_dev_alloc<double>(m, (size_t)6 * N3 * els.size());
+        gather_fg_kernel<<<(int)els.size(), 128, 0, m->stream>>>((int)els.size(), N3, LQ, c.d_elem, m->d_quad_stride,
+                                                                 m->d_G, c.d_FG);
+        D4B_CUDA(cudaGetLastError());
+      }
       if (kind == 0) {
         c.d_face_rec = d4b_dev_upload<int64_t>(m, face_rec.data(), face_rec.size());
         c.d_face_nbr = d4b_dev_upload<int64_t>(m, face_nbr.data(), face_nbr.size());
@@ -1128,8 +1208,25 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<dou
   }
   m->n_face_shared = n_shared;
   m->n_face_split = n_split;
-  if (!FF.empty()) m->d_fast_FF = d4b_dev_upload<double>(m, FF.data(), FF.size());
-  if (!FF3.empty()) m->d_flat_FF = d4b_dev_upload<double>(m, FF3.data(), FF3.size());
+  auto fill = [&](int64_t size, const std::vector<RecSrc> &src, int compact) -> double * {
+    if (size == 0) return nullptr;
+    double *out = d4b_dev_alloc<double>(m, (size_t)size);
+    D4B_CUDA(cudaMemsetAsync(out, 0, (size_t)size * sizeof(double), m->stream));
+    if (!src.empty()) {
+      RecSrc *d_src = nullptr;
+      D4B_CUDA(cudaMalloc(&d_src, src.size() * sizeof(RecSrc)));
+      D4B_CUDA(cudaMemcpyAsync(d_src, src.data(), src.size() * sizeof(RecSrc), cudaMemcpyHostToDevice, m->stream));
+      gather_records_kernel<<<(int)src.size(), 64, 0, m->stream>>>((int)src.size(), d_src, compact, MP, m->d_mortar,
+                                                                   m->d_side_mortar_stride, out);
+      D4B_CUDA(cudaGetLastError());
+      D4B_CUDA(cudaStreamSynchronize(m->stream));
+      cudaFree(d_src);
+    }
+    return out;
+  };
+  m->d_fast_FF = fill(ff_size, src7, 0);
+  m->d_flat_FF = fill(ff3_size, src3, 1);
+  D4B_CUDA(cudaStreamSynchronize(m->stream));
   m->d_uhat = d4b_dev_alloc<double>(m, (size_t)(d->local_nodes + d->ghost_nodes));
 }
 

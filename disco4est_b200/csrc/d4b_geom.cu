@@ -503,6 +503,38 @@ extern "C" void d4b_geom_compute(const d4b_mesh_desc_t *d, const d4b_geom_desc_t
 extern "C" d4b_mesh_t *d4b_mesh_create_with_geometry(const d4b_mesh_desc_t *topo, const d4b_geom_desc_t *geom) {
   D4B_CHECK(topo && geom, "d4b_mesh_create_with_geometry: NULL argument");
   const size_t LQ = (size_t)topo->local_nodes_quad, MP = (size_t)topo->local_mortar_nodes_quad;
+  // the generated factors stay on the device: 10 doubles per volume point and 24 per mortar point of scratch, folded
+  // to 6 + 8 by kernels (d4b_mesh_create_impl) and freed; nothing of per-point size crosses the bus
+  // (D4B_HOST_FOLD=1: the round-1 path through host arrays, kept for A/B checks)
+  const bool host_fold = getenv("D4B_HOST_FOLD") && atoi(getenv("D4B_HOST_FOLD")) != 0;
+  const bool timing = getenv("D4B_TIMING") && atoi(getenv("D4B_TIMING"));
+  auto t0 = std::chrono::steady_clock::now();
+  d4b_mesh *m = nullptr;
+  if (!host_fold) {
+    d4b_geom_arrays_t out;
+    memset(&out, 0, sizeof(out));
+    double *raw = nullptr;
+    const size_t total = 10 * LQ + 24 * MP;
+    D4B_CUDA(cudaMalloc(&raw, std::max<size_t>(total, 1) * sizeof(double)));
+    double *p = raw;
+    out.J_quad = p; p += LQ;
+    out.rst_xyz_quad = p; p += 9 * LQ;
+    out.sj_m_mortar_quad = p; p += MP;
+    out.n_m_mortar_quad = p; p += 3 * MP;
+    out.drst_dxyz_m_mortar_quad = p; p += 9 * MP;
+    out.drst_dxyz_p_mortar_quad_porder = p; p += 9 * MP;
+    out.hm_mortar_quad = p; p += MP;
+    out.hp_mortar_quad = p; p += MP;
+    // boundary sides are never written by the generator (the reference leaves hp / drst_p stale there)
+    D4B_CUDA(cudaMemset(raw, 0, std::max<size_t>(total, 1) * sizeof(double)));
+    d4b_geom_compute(topo, geom, &out);
+    if (timing)
+      fprintf(stderr, "[d4b_mesh_create_with_geometry] generate on the device        %8.3f s\n",
+              std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count());
+    m = d4b_mesh_create_impl(topo, &out);
+    D4B_CUDA(cudaStreamSynchronize(m->stream));
+    cudaFree(raw);
+  } else {
   std::vector<double> J(LQ), rst(9 * LQ), sj(MP), n(3 * MP), drm(9 * MP), drp(9 * MP), hm(MP), hp(MP);
   d4b_geom_arrays_t out;
   memset(&out, 0, sizeof(out));
@@ -510,8 +542,6 @@ extern "C" d4b_mesh_t *d4b_mesh_create_with_geometry(const d4b_mesh_desc_t *topo
   out.sj_m_mortar_quad = sj.data(); out.n_m_mortar_quad = n.data();
   out.drst_dxyz_m_mortar_quad = drm.data(); out.drst_dxyz_p_mortar_quad_porder = drp.data();
   out.hm_mortar_quad = hm.data(); out.hp_mortar_quad = hp.data();
-  const bool timing = getenv("D4B_TIMING") && atoi(getenv("D4B_TIMING"));
-  auto t0 = std::chrono::steady_clock::now();
   d4b_geom_compute(topo, geom, &out);
   if (timing)
     fprintf(stderr, "[d4b_mesh_create_with_geometry] generate + copy to host %8.3f s\n",
@@ -521,7 +551,9 @@ extern "C" d4b_mesh_t *d4b_mesh_create_with_geometry(const d4b_mesh_desc_t *topo
   d.sj_m_mortar_quad = sj.data(); d.n_m_mortar_quad = n.data();
   d.drst_dxyz_m_mortar_quad = drm.data(); d.drst_dxyz_p_mortar_quad_porder = drp.data();
   d.hm_mortar_quad = hm.data(); d.hp_mortar_quad = hp.data();
-  d4b_mesh *m = d4b_mesh_create(&d);
+  m = d4b_mesh_create(&d);
+  }
+
   // what d4b_mesh_set_nonlinear_term needs to regenerate positions / J at the quadrature points
   m->has_geom = true;
   m->gdesc = *geom;

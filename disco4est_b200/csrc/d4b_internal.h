@@ -204,8 +204,10 @@ void d4b_launch_estimator(d4b_mesh *m, const double *d_u, const double *d_r, con
                           double prefactor, double *d_eta2, double *d_terms);
 // the whole apply on device pointers (halo exchange, fast kernels with m->epi, generic kernel)
 void d4b_apply_device(d4b_mesh *m, const double *d_u, double *d_Au);
-void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *desc, const std::vector<double> &mortar,
-                    const std::vector<double> &G, const std::vector<int32_t> &elem_side,
+// d4b_mesh_create with the geometric factors given as DEVICE arrays (dg != nullptr; d4b_geom.cu) or taken from `d`
+d4b_mesh *d4b_mesh_create_impl(const d4b_mesh_desc_t *d, const d4b_geom_arrays_t *dg);
+// reads m->d_G, m->d_mortar and the side arrays on the device: they must be in place
+void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *desc, const std::vector<int32_t> &elem_side,
                     std::vector<char> &is_fast);
 // part 0: uh of local elements; 1: interior elements; 2 (after the halo exchange): uh of
 // ghost elements + elements with a ghost neighbour

@@ -294,3 +294,25 @@ def test_affine_path_matches_per_point_metric(golden, case, monkeypatch):
     assert rel(out["1"], A["Au_plain"]) < TOL
     assert rel(out["0"], A["Au_plain"]) < TOL
     assert rel(out["1"], out["0"]) < 1e-13
+
+
+@pytest.mark.parametrize("level,p", [(2, 1), (2, 3), (1, 4), (1, 7)])
+def test_device_generated_and_folded_brick_matches_host_arrays(level, p):
+    """brick_desc(geometry=False): topology only, factors generated AND folded on the device
+    (d4b_mesh_create_with_geometry -> fold_volume_kernel / fold_mortar_kernel, face records and class metrics
+    gathered by kernels) against the same mesh described with host arrays (host fold)"""
+    from disco4est_b200 import Mesh
+    from disco4est_b200.brick import brick_desc
+
+    A = brick_desc(level, p)
+    T, g = brick_desc(level, p, geometry=False)
+    ma, mt = Mesh(A), Mesh(T, geom=g)
+    assert mt.fast_elements() == ma.fast_elements() == int(A["n_local"])
+    assert mt.flat_elements() == ma.flat_elements()
+    u = np.random.default_rng(5).standard_normal(ma.n)
+    a, b = np.zeros_like(u), np.zeros_like(u)
+    ma.apply(u, a)
+    mt.apply(u, b)
+    ma.close()
+    mt.close()
+    assert rel(b, a) < 1e-13
