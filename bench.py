@@ -297,10 +297,10 @@ def bench_degree_sweep(args, torch, dev):
     for p in range(1, 8):
         level = args.level if p <= args.sweep_full_level_max_deg else args.level - 1
         t0 = time.perf_counter()
-        A = brick_desc(level, p)
-        mesh = Mesh(A, device=dev.index)
+        A, gm = brick_desc(level, p, geometry=False)
+        mesh = Mesh(A, device=dev.index, geom=gm)
         t_setup = time.perf_counter() - t0
-        del A
+        del A, gm
         n = mesh.n
         mesh.set_stream(stream.cuda_stream)
         u = torch.rand(n, dtype=torch.float64, device=dev, generator=torch.Generator(device=dev).manual_seed(11 + p))
@@ -332,14 +332,18 @@ def bench_vcycle(top_mesh, level, deg, rank, world, trees, torch, dev, cycles=3)
     smoother with lambda_max from 15 CG steps recomputed on both legs, Chebyshev bottom
     solver (the [multigrid] settings of src/Problems/ConstantDensityStar/options.input),
     rhs = random, zero initial guess.  Whole-job seconds, max over ranks."""
+    import numpy as np
     import torch.distributed as dist
     from disco4est_b200 import Mesh
     from disco4est_b200.brick import brick_hierarchy
     from disco4est_b200.runtime import Multigrid, cheby_params
 
-    descs, transfers = brick_hierarchy(level, deg, rank=rank, world=world, trees=trees)
-    meshes = [Mesh(d, device=dev.index) for d in descs[:-1]] + [top_mesh]
-    nodes = [int(d["local_nodes"]) for d in descs]
+    # topology only: the factors of every level are generated and folded on the device
+    descs, transfers = brick_hierarchy(level - 1, deg, rank=rank, world=world, trees=trees, geometry=False)
+    meshes = [Mesh(d, device=dev.index, geom=g) for d, g in descs] + [top_mesh]
+    nodes = [int(d["local_nodes"]) for d, g in descs] + [top_mesh.n]
+    transfers.append((8 * np.arange(int(descs[-1][0]["n_local"]), dtype=np.int32),
+                      np.full(int(descs[-1][0]["n_local"]), 8, np.int32)))
     del descs
     sm = cheby_params(15, 15, 30.0, 1.0)
     mg = Multigrid(meshes, transfers, sm, vcycle_imax=1, bottom_solver="cheby", bottom_cheby=cheby_params(15, 30, 30.0, 1.0))
@@ -645,10 +649,12 @@ def bench_ours(args):
             if rank == 0:
                 sys.stderr.write("bench.py: multi-GPU parity FAILED: %s\n" % json.dumps(parity))
             sys.exit(3)
-    A = brick_desc(level, deg, rank=rank, world=world, trees=trees)
+    t_setup0 = time.perf_counter()
+    A, gm = brick_desc(level, deg, rank=rank, world=world, trees=trees, geometry=False)
     n_ghost = int(A["n_ghost"])
-    mesh = Mesh(A, device=local_rank)
-    del A
+    mesh = Mesh(A, device=local_rank, geom=gm)
+    t_setup = time.perf_counter() - t_setup0
+    del A, gm
     n = mesh.n
     stream = torch.cuda.current_stream()
     mesh.set_stream(stream.cuda_stream)
@@ -716,7 +722,9 @@ def bench_ours(args):
                        "halo": ("none (one rank)" if world == 1 else
                                 "NCCL send/recv of mirror elements inside every apply, overlapped with interior elements"),
                        "l2": "inputs larger than L2 (no flush needed)",
-                       "fast_kernel_elements": mesh.fast_elements(), "checksum_Au": checksum},
+                       "fast_kernel_elements": mesh.fast_elements(), "checksum_Au": checksum,
+                       "setup_s": t_setup,
+                       "setup": "topology from numpy; geometric factors generated, folded and laid out on the device"},
             "e2e": {"value": total_dof / t_e2e / 1e9, "unit": UNIT,
                     "h2d_bytes_per_step": 8 * n, "d2h_bytes_per_step": 8 * n},
             "gpu_launches": args.steps * mesh.launches_per_apply(),
@@ -754,9 +762,9 @@ def bench_ours(args):
     aff = None
     if not args.no_affine:
         os.environ["D4B_AFFINE"] = "1"
-        A = brick_desc(level, deg, rank=rank, world=world, trees=trees)
-        mesh = Mesh(A, device=local_rank)
-        del A
+        A, gm = brick_desc(level, deg, rank=rank, world=world, trees=trees, geometry=False)
+        mesh = Mesh(A, device=local_rank, geom=gm)
+        del A, gm
         mesh.set_stream(stream.cuda_stream)
         u = torch.rand(n, dtype=torch.float64, device=dev, generator=g)
         Au = torch.empty_like(u)
@@ -826,7 +834,7 @@ def main():
     ap.add_argument("--newton-level", type=int, default=4, help="sphere level of the Newton solve (N=1)")
     ap.add_argument("--no-sweep", action="store_true", help="skip the p=1..7 degree sweep (N=1 only)")
     ap.add_argument("--no-parity", action="store_true", help="skip the multi-GPU parity check (N>1 only)")
-    ap.add_argument("--sweep-full-level-max-deg", type=int, default=3,
+    ap.add_argument("--sweep-full-level-max-deg", type=int, default=7,
                     help="degrees up to this one are swept at --level, higher ones at --level - 1")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -242,7 +242,7 @@ def brick_hierarchy(level, p, rank=0, world=1, trees=(1, 1, 1), **kw):
     descs = [brick_desc(l, p, rank=rank, world=world, trees=trees, **kw) for l in range(level + 1)]
     transfers = []
     for l in range(level):
-        E = descs[l]["n_local"]
+        E = (descs[l][0] if isinstance(descs[l], tuple) else descs[l])["n_local"]   # geometry=False: (topology, geom)
         transfers.append((8 * np.arange(E, dtype=np.int32), np.full(E, 8, np.int32)))
     return descs, transfers
 
