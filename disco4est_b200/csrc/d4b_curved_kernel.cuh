@@ -153,21 +153,14 @@ __global__ void __launch_bounds__(CurvedShflCfg<N>::THREADS, CurvedShflCfg<N>::M
   FaceMeta *META = reinterpret_cast<FaceMeta *>(FB + 12 * NN);
   const int64_t ns = active ? a.nodal_stride[a.elem[ei]] : 0;
   const double wxy = T.w[lx] * T.w[ly];
-  double gt[N];
-  double tr4 = 0., dn4 = 0., tr5 = 0., dn5 = 0.;
-#pragma unroll
-  for (int c = 0; c < N; ++c) gt[c] = 0.;
-
   if (threadIdx.x == 0 && a.prefetch) {
     constexpr unsigned kBlockBytes = C::EPB * 6 * N3 * sizeof(double);
     const int e0 = a.first + (int)blockIdx.x * C::EPB, left = a.n_elem - e0;
     l2_prefetch(a.FG + (size_t)e0 * (6 * N3), left >= C::EPB ? kBlockBytes : left * 6 * N3 * 8);
   }
-  // ---- T-orientation (a,b) = (lx,ly), line along c ----
+  // ---- T-orientation (a,b) = (lx,ly), line along c: only stage uh; its c-derivative and the traces of faces 4/5
+  // are taken in the metric phase from the staged copy (keeps them out of the registers during the S / R faces)
   if (active) {
-    double uh[N];
-#pragma unroll
-    for (int c = 0; c < N; ++c) uh[c] = a.uh[ns + lt + NN * c];
     for (int j = lt; j < 6; j += NN) {
       const FaceMeta fm = a.meta[6 * (size_t)ei + j];
       META[j] = fm;
@@ -177,18 +170,7 @@ __global__ void __launch_bounds__(CurvedShflCfg<N>::THREADS, CurvedShflCfg<N>::M
       }
     }
 #pragma unroll
-    for (int i = 0; i < N; ++i) {
-      V0[vix<N>(lx, ly, i)] = uh[i];
-      tr4 += T.e[0][i] * uh[i]; dn4 += T.d[0][i] * uh[i];
-      tr5 += T.e[1][i] * uh[i]; dn5 += T.d[1][i] * uh[i];
-    }
-#pragma unroll
-    for (int c = 0; c < N; ++c) {
-      double s = 0.;
-#pragma unroll
-      for (int i = 0; i < N; ++i) s += T.Dg[c][i] * uh[i];
-      gt[c] = s;
-    }
+    for (int c = 0; c < N; ++c) V0[vix<N>(lx, ly, c)] = a.uh[ns + lt + NN * c];
   }
   __syncwarp();
   const FaceMeta zero_meta = {-1, 0, kOwn};
@@ -248,17 +230,27 @@ __global__ void __launch_bounds__(CurvedShflCfg<N>::THREADS, CurvedShflCfg<N>::M
   // at faces 4/5 are traces of d_r u, d_s u along that line and the tangential test weights go straight
   // into the flux lines F_r, F_s: no shuffles for the own side of this face pair.
   {
-    double gr[N], gs[N];
-    double d14 = 0., d24 = 0., d15 = 0., d25 = 0.;
+    double gr[N], gs[N], gt[N];
+    double d14 = 0., d24 = 0., d15 = 0., d25 = 0., tr4 = 0., dn4 = 0., tr5 = 0., dn5 = 0.;
 #pragma unroll
-    for (int c = 0; c < N; ++c) { gr[c] = 0.; gs[c] = 0.; }
+    for (int c = 0; c < N; ++c) { gr[c] = 0.; gs[c] = 0.; gt[c] = 0.; }
     if (active) {
+      double uh[N];
 #pragma unroll
       for (int c = 0; c < N; ++c) {
         const int idx = vix<N>(lx, ly, c);
-        gr[c] = V1[idx]; gs[c] = V2[idx];
+        uh[c] = V0[idx]; gr[c] = V1[idx]; gs[c] = V2[idx];
         d14 += T.e[0][c] * gr[c]; d24 += T.e[0][c] * gs[c];
         d15 += T.e[1][c] * gr[c]; d25 += T.e[1][c] * gs[c];
+        tr4 += T.e[0][c] * uh[c]; dn4 += T.d[0][c] * uh[c];
+        tr5 += T.e[1][c] * uh[c]; dn5 += T.d[1][c] * uh[c];
+      }
+#pragma unroll
+      for (int c = 0; c < N; ++c) {
+        double sd = 0.;
+#pragma unroll
+        for (int i = 0; i < N; ++i) sd += T.Dg[c][i] * uh[i];
+        gt[c] = sd;
       }
     }
     double ve0, vd0, ve1, vd1, w14, w24, w15, w25;

@@ -191,6 +191,6 @@ def test_newton_iteration_counts_match_reference(problem):
     assert its == ref_its
     ref_norms = A["nw_residual_norms"]
     for a, b in zip(norms, ref_norms):
-        assert abs(a - b) <= 1e-6 * b + 1e-16
+        assert abs(a - b) <= 1e-6 * b + 1e-11 * ref_norms[0]   # the last norms are round-off of the first
     assert rel(u, A["nw_u"]) < 1e-9
     assert japplies == sum(ref_its) + len(ref_its)
