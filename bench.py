@@ -32,6 +32,15 @@ REF_DRIVER = os.path.join(ROOT, "oracle", "_ref", "ref_driver")
 BRICK_INI = os.path.join(ROOT, "oracle", "configs", "brick_poisson.ini")
 
 
+HALO_TEXT = {
+    "none": "none (one rank)",
+    "nccl": "NCCL send/recv of mirror elements inside every apply, overlapped with interior elements",
+    "peer": "peer memory: boundary elements read the neighbour ranks' Gauss-collocated vectors over NVLink (CUDA IPC "
+            "mappings, flag per neighbour and apply), overlapped with interior elements; no pack / send / recv",
+    "undecided": "undecided",
+}
+
+
 def algorithmic_bytes_per_dof(p):
     """8 (u) + 8 (Au) + 48 (6 metric comps) + 168/N (7 face doubles x 3 faces)."""
     return 64.0 + 168.0 / (p + 1)
@@ -277,7 +286,7 @@ def nccl_parity(rank, world, local_rank, torch, dist, dev):
         err = float(np.linalg.norm(got - ref) / np.linalg.norm(ref))
         flag = torch.tensor([0 if host_equal else 1], device=dev)
         dist.all_reduce(flag)
-        recs.append({"fixture": case, "ranks": world, "elements": E, "nccl_rel_l2": err,
+        recs.append({"fixture": case, "ranks": world, "elements": E, "nccl_rel_l2": err, "halo_rank0": m.halo_mode(),
                      "ghost_elements_rank0": int(np.asarray(A["n_ghost"]).reshape(-1)[0]),
                      "host_pointer_call_bit_equal_on_all_ranks": int(flag[0]) == 0,
                      "against": "Au_plain written by the unmodified reference on one rank"})
@@ -722,8 +731,7 @@ def bench_ours(args):
                                    "Gauss quadrature, SIPG prefactor 2 maxp_sqr_over_minh, homogeneous Dirichlet"
                                    % (1 << level, deg),
                        "dof_per_gpu": n, "trees": list(trees), "ghost_elements_rank0": n_ghost,
-                       "halo": ("none (one rank)" if world == 1 else
-                                "NCCL send/recv of mirror elements inside every apply, overlapped with interior elements"),
+                       "halo": HALO_TEXT[mesh.halo_mode()],
                        "l2": "inputs larger than L2 (no flush needed)",
                        "fast_kernel_elements": mesh.fast_elements(), "checksum_Au": checksum,
                        "setup_s": t_setup,
@@ -754,6 +762,61 @@ def bench_ours(args):
                 if not plugin["parity_rel_l2_vs_reference_cpu_apply"] <= PARITY_TOL:
                     sys.stderr.write("bench.py: plugin parity FAILED: %s\n" % json.dumps(plugin))
                     sys.exit(3)
+    # the same apply with the NCCL send/recv halo (the fallback when peers cannot be mapped), for comparison
+    halo_ab = None
+    if world > 1 and not args.no_halo_ab:
+        modes = torch.tensor([1 if mesh.halo_mode() == "peer" else 0], dtype=torch.int64, device=dev)
+        dist.all_reduce(modes, op=dist.ReduceOp.MIN)
+        if int(modes[0]) == 1:
+            os.environ["D4B_PEER_HALO"] = "0"
+            A, gm = brick_desc(level, deg, rank=rank, world=world, trees=trees, geometry=False)
+            mesh2 = Mesh(A, device=local_rank, geom=gm)
+            del A, gm
+            mesh2.set_stream(stream.cuda_stream)
+            Au2 = torch.empty_like(u)
+            for _ in range(n_warm):
+                mesh2.apply(u, Au2)
+            barrier()
+            ev0.record(stream)
+            for _ in range(args.steps):
+                mesh2.apply(u, Au2)
+            ev1.record(stream)
+            barrier()
+            tt = torch.tensor([ev0.elapsed_time(ev1) * 1e-3 / args.steps], dtype=torch.float64, device=dev)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            same = torch.tensor([1 if torch.equal(Au, Au2) else 0], dtype=torch.int64, device=dev)
+            dist.all_reduce(same, op=dist.ReduceOp.MIN)
+            halo_ab = {"nccl_halo_GDOF_per_s": total_dof / float(tt[0]) / 1e9, "nccl_halo_ms_per_apply": 1e3 * float(tt[0]),
+                       "peer_halo_ms_per_apply": 1e3 * t_dev, "halo_mode_checked": mesh2.halo_mode(),
+                       "results_bit_equal_on_all_ranks": bool(int(same[0]))}
+            mesh2.close()
+            del mesh2, Au2
+            os.environ.pop("D4B_PEER_HALO", None)
+            # and with no halo at all: every rank applies a one-rank cube of the same size at the same time
+            # (what the GPUs of this box do independently; max / min over the ranks)
+            A, gm = brick_desc(level, deg, geometry=False)
+            mesh2 = Mesh(A, device=local_rank, geom=gm)
+            del A, gm
+            mesh2.set_stream(stream.cuda_stream)
+            Au2 = torch.empty_like(u)
+            for _ in range(n_warm):
+                mesh2.apply(u, Au2)
+            barrier()
+            ev0.record(stream)
+            for _ in range(args.steps):
+                mesh2.apply(u, Au2)
+            ev1.record(stream)
+            barrier()
+            t1 = ev0.elapsed_time(ev1) * 1e-3 / args.steps
+            tt = torch.tensor([t1, -t1], dtype=torch.float64, device=dev)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            halo_ab["independent_one_rank_cubes_ms_per_apply"] = {"slowest_gpu": 1e3 * float(tt[0]), "fastest_gpu": -1e3 * float(tt[1])}
+            mesh2.close()
+            del mesh2, Au2
+            if not halo_ab["results_bit_equal_on_all_ranks"]:
+                if rank == 0:
+                    sys.stderr.write("bench.py: peer-memory halo and NCCL halo differ: %s\n" % json.dumps(halo_ab))
+                sys.exit(3)
     # second metric of BASELINE.json: seconds per multigrid V-cycle
     vc = None
     if not args.no_vcycle:
@@ -811,6 +874,8 @@ def bench_ours(args):
             out["two_punctures"] = pun
         if vc is not None:
             out["vcycle"] = vc
+        if halo_ab is not None:
+            out["halo_comparison"] = halo_ab
         if sp is not None:
             out["cubed_sphere"] = sp
         sys.stdout.flush()
@@ -839,6 +904,7 @@ def main():
                     help="also run the Newton solve with the FCG / matrix operator arithmetic the reference executes")
     ap.add_argument("--no-sweep", action="store_true", help="skip the p=1..7 degree sweep (N=1 only)")
     ap.add_argument("--no-parity", action="store_true", help="skip the multi-GPU parity check (N>1 only)")
+    ap.add_argument("--no-halo-ab", action="store_true", help="skip the NCCL-halo comparison run (N>1 only)")
     ap.add_argument("--sweep-full-level-max-deg", type=int, default=7,
                     help="degrees up to this one are swept at --level, higher ones at --level - 1")
     args = ap.parse_args()

@@ -66,6 +66,24 @@ void d4b_apply_device(d4b_mesh *m, const double *du, double *dAu) {
   if (m->mpisize == 1) {
     d4b_launch_fast(m, du, dAu, 0);
     d4b_launch_fast(m, du, dAu, 1);
+  } else if (d4b_comm_peer_ready(m)) {
+    // halo over peer memory (d4b_comm.cu): nothing is packed or sent; the boundary elements read the
+    // neighbour ranks' uh over NVLink once those ranks have signalled that it is complete
+    // compute stream:  uh(local) | interior elements ........................... | join
+    // halo stream   :        wait uh(local) | signal neighbours | wait for theirs | boundary elements
+    d4b_comm_peer_begin(m);
+    d4b_launch_fast(m, du, dAu, 0);
+    D4B_CUDA(cudaEventRecord(m->ev_interp, m->stream));
+    D4B_CUDA(cudaStreamWaitEvent(m->comm_stream, m->ev_interp, 0));
+    d4b_comm_peer_signal(m);
+    d4b_launch_fast(m, du, dAu, 1);
+    d4b_comm_peer_wait(m);
+    cudaStream_t compute = m->stream;
+    m->stream = m->comm_stream;
+    d4b_launch_fast(m, du, dAu, 2);
+    D4B_CUDA(cudaEventRecord(m->ev_boundary, m->comm_stream));
+    m->stream = compute;
+    D4B_CUDA(cudaStreamWaitEvent(m->stream, m->ev_boundary, 0));
   } else {
     // compute stream:  pack | uh(local) | interior elements ............ | join
     // halo stream   :       wait pack | send/recv | wait uh(local) | uh(ghosts) | boundary elements

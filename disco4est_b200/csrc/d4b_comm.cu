@@ -10,6 +10,8 @@
 // multi-rank mesh without an initialised communicator aborts.
 #include <dlfcn.h>
 #include <nccl.h>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include "d4b_internal.h"
 
@@ -25,6 +27,7 @@ struct NcclApi {
   decltype(&ncclGroupStart) GroupStart = nullptr;
   decltype(&ncclGroupEnd) GroupEnd = nullptr;
   decltype(&ncclAllReduce) AllReduce = nullptr;
+  decltype(&ncclAllGather) AllGather = nullptr;
   decltype(&ncclGetErrorString) GetErrorString = nullptr;
 };
 
@@ -54,6 +57,7 @@ void load_nccl() {
   D4B_SYM(GroupStart, "ncclGroupStart");
   D4B_SYM(GroupEnd, "ncclGroupEnd");
   D4B_SYM(AllReduce, "ncclAllReduce");
+  D4B_SYM(AllGather, "ncclAllGather");
   D4B_SYM(GetErrorString, "ncclGetErrorString");
 #undef D4B_SYM
 }
@@ -112,6 +116,7 @@ void d4b_comm_setup(d4b_mesh *m, const d4b_mesh_desc_t *d) {
     D4bPeer p;
     p.rank = q;
     p.send_off = send_total;
+    p.send_elem_off = (int32_t)src.size();
     for (int i = d->mirror_proc_offsets[q]; i < d->mirror_proc_offsets[q + 1]; ++i) {
       const int e = d->mirror_elem[d->mirror_proc_mirrors[i]];
       D4B_CHECK(e >= 0 && e < d->n_local, "mirror element out of range");
@@ -120,9 +125,11 @@ void d4b_comm_setup(d4b_mesh *m, const d4b_mesh_desc_t *d) {
       send_total += n;
     }
     p.send_cnt = send_total - p.send_off;
+    p.send_elem_cnt = (int32_t)src.size() - p.send_elem_off;
     const int g0 = d->ghost_proc_offsets[q], g1 = d->ghost_proc_offsets[q + 1];
     p.recv_off = (g0 < d->n_ghost) ? d->ghost_nodal_stride[g0] : d->ghost_nodes;
     p.recv_cnt = 0;
+    p.ghost_first = g0; p.ghost_cnt = g1 - g0;
     for (int g = g0; g < g1; ++g) {
       const int n = (d->ghost_deg[g] + 1) * (d->ghost_deg[g] + 1) * (d->ghost_deg[g] + 1);
       // the receive lands in place: ghosts of one rank must be contiguous in ghost-id order
@@ -190,4 +197,218 @@ void d4b_comm_allreduce_sum(d4b_mesh *m, double *d_x, int n) {
   if (m->mpisize == 1) return;
   D4B_CHECK(g_comm, "d4b_comm_init was not called");
   D4B_NCCL(g_nccl.AllReduce(d_x, d_x, (size_t)n, ncclDouble, ncclSum, g_comm, m->stream));
+}
+
+// ---- halo over peer memory -------------------------------------------------------
+// No counterpart in the reference (its exchange is MPI point-to-point of nodal values,
+// d4est_ghost_data.c:142-255).  On one node every rank maps the Gauss-collocated vector uhat of
+// its neighbour ranks (cudaIpc*, NVLink) and the kernels of its boundary elements read the
+// neighbours' lines where they lie: pack kernel, send/recv and the interpolation of the ghost
+// elements leave the critical path of an apply.  Synchronisation per apply k:
+//   every rank   : uhat of its own elements -> copy (k & 1) of its buffer; flags[me] on every neighbour := k
+//   before the boundary elements: wait until flags[q] >= k for every neighbour q
+// Two copies suffice: a rank can only reach apply k + 2 (and overwrite copy k & 1) after its
+// neighbours signalled k + 1, which they do after their boundary elements of apply k are done.
+namespace {
+
+__global__ void peer_signal_k(unsigned long long *const *__restrict__ dst, int n, unsigned long long epoch) {
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    __threadfence_system();
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(dst[i]), "l"(epoch) : "memory");
+  }
+}
+
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+__global__ void peer_wait_k(const unsigned long long *__restrict__ flags, const int32_t *__restrict__ ranks, int n,
+                            unsigned long long epoch, int rank) {
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const unsigned long long *p = flags + ranks[i];
+    const unsigned long long t0 = global_ns();
+    for (;;) {
+      unsigned long long v;
+      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+      if (v >= epoch) break;
+      if (global_ns() - t0 > 30000000000ull) {   // 30 s: a neighbour never produced this apply
+        printf("[d4b] rank %d: peer halo timed out waiting for rank %d (have %llu, need %llu)\n", rank, ranks[i], v, epoch);
+        __trap();
+      }
+      __nanosleep(64);
+    }
+  }
+}
+
+struct PeerXchg {
+  cudaIpcMemHandle_t uh, flags;
+  int64_t ok;
+};
+
+// min over the ranks of a local 0/1
+int all_agree(d4b_mesh *m, int64_t *d_scratch, int local_ok) {
+  int64_t v = local_ok;
+  D4B_CUDA(cudaMemcpyAsync(d_scratch, &v, sizeof(v), cudaMemcpyHostToDevice, m->stream));
+  D4B_NCCL(g_nccl.AllReduce(d_scratch, d_scratch, 1, ncclInt64, ncclMin, g_comm, m->stream));
+  D4B_CUDA(cudaMemcpyAsync(&v, d_scratch, sizeof(v), cudaMemcpyDeviceToHost, m->stream));
+  D4B_CUDA(cudaStreamSynchronize(m->stream));
+  return (int)v;
+}
+
+void peer_release(d4b_mesh *m) {
+  D4bPeerHalo &P = m->peer;
+  for (void *p : P.mapped) cudaIpcCloseMemHandle(p);
+  P.mapped.clear();
+  if (P.uh2) { if (m->d_uhat >= P.uh2 && m->d_uhat < P.uh2 + 2 * P.H) m->d_uhat = nullptr; cudaFree(P.uh2); P.uh2 = nullptr; }
+  if (P.flags) { cudaFree(P.flags); P.flags = nullptr; }
+  if (P.d_signal) { cudaFree(P.d_signal); P.d_signal = nullptr; }
+  if (P.d_wait) { cudaFree(P.d_wait); P.d_wait = nullptr; }
+  if (P.d_ghost_uh_off) { cudaFree(P.d_ghost_uh_off); P.d_ghost_uh_off = nullptr; }
+  cudaGetLastError();
+}
+
+}  // namespace
+
+// Collective over the communicator (every rank reaches it in its first apply on this mesh).
+// D4B_PEER_HALO=0 keeps the NCCL exchange.
+bool d4b_comm_peer_ready(d4b_mesh *m) {
+  D4bPeerHalo &P = m->peer;
+  if (P.state) return P.state > 0;
+  P.state = -1;
+  if (m->mpisize == 1) return false;
+  D4B_CHECK(g_comm && g_size == m->mpisize && g_rank == m->mpirank,
+            "mesh of rank %d/%d but d4b_comm_init was %s", m->mpirank, m->mpisize,
+            g_comm ? "called with another rank/size" : "not called");
+  const char *env = getenv("D4B_PEER_HALO");
+  // the general kernel reads nodal ghost values: such meshes keep the nodal exchange
+  int ok = !(env && atoi(env) == 0) && m->n_generic == 0 && !m->fast.empty() && m->d_uhat != nullptr;
+  const int R = m->mpisize;
+  int64_t *d_sc = nullptr;
+  D4B_CUDA(cudaMalloc(&d_sc, 4 * sizeof(int64_t)));
+  int64_t H = (m->local_nodes + 31) / 32 * 32;
+  D4B_CUDA(cudaMemcpyAsync(d_sc + 1, &H, sizeof(H), cudaMemcpyHostToDevice, m->stream));
+  D4B_NCCL(g_nccl.AllReduce(d_sc + 1, d_sc + 1, 1, ncclInt64, ncclMax, g_comm, m->stream));
+  D4B_CUDA(cudaMemcpyAsync(&H, d_sc + 1, sizeof(H), cudaMemcpyDeviceToHost, m->stream));
+  if (!all_agree(m, d_sc, ok)) { cudaFree(d_sc); return false; }
+
+  // buffers and their IPC handles
+  P.H = H;
+  PeerXchg mine;
+  memset(&mine, 0, sizeof(mine));
+  ok = cudaMalloc(&P.uh2, (size_t)2 * H * sizeof(double)) == cudaSuccess &&
+       cudaMalloc(&P.flags, (size_t)R * sizeof(unsigned long long)) == cudaSuccess;
+  if (ok) {
+    D4B_CUDA(cudaMemsetAsync(P.uh2, 0, (size_t)2 * H * sizeof(double), m->stream));
+    D4B_CUDA(cudaMemsetAsync(P.flags, 0, (size_t)R * sizeof(unsigned long long), m->stream));
+    ok = cudaIpcGetMemHandle(&mine.uh, P.uh2) == cudaSuccess && cudaIpcGetMemHandle(&mine.flags, P.flags) == cudaSuccess;
+  }
+  cudaGetLastError();
+  mine.ok = ok;
+  char *d_x = nullptr;
+  D4B_CUDA(cudaMalloc(&d_x, (size_t)(R + 1) * sizeof(PeerXchg)));
+  D4B_CUDA(cudaMemcpyAsync(d_x + (size_t)R * sizeof(PeerXchg), &mine, sizeof(mine), cudaMemcpyHostToDevice, m->stream));
+  D4B_NCCL(g_nccl.AllGather(d_x + (size_t)R * sizeof(PeerXchg), d_x, sizeof(PeerXchg), ncclChar, g_comm, m->stream));
+  std::vector<PeerXchg> all(R);
+  D4B_CUDA(cudaMemcpyAsync(all.data(), d_x, (size_t)R * sizeof(PeerXchg), cudaMemcpyDeviceToHost, m->stream));
+  D4B_CUDA(cudaStreamSynchronize(m->stream));   // also: every rank's flags are zero before anybody can signal
+  cudaFree(d_x);
+  for (int q = 0; q < R; ++q) ok = ok && all[q].ok;
+
+  // map the neighbours, learn where their mirrors' lines are (the nodal offset of each of my ghosts on its owner)
+  std::vector<double *> puh(m->peers.size(), nullptr);
+  std::vector<unsigned long long *> pfl(m->peers.size(), nullptr);
+  for (size_t i = 0; i < m->peers.size() && ok; ++i) {
+    const int q = m->peers[i].rank;
+    void *a = nullptr, *b = nullptr;
+    ok = cudaIpcOpenMemHandle(&a, all[q].uh, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+    if (ok) P.mapped.push_back(a);
+    ok = ok && cudaIpcOpenMemHandle(&b, all[q].flags, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+    if (ok) P.mapped.push_back(b);
+    puh[i] = static_cast<double *>(a); pfl[i] = static_cast<unsigned long long *>(b);
+  }
+  cudaGetLastError();
+  int64_t *d_remote = nullptr;
+  D4B_CUDA(cudaMalloc(&d_remote, (size_t)(m->n_ghost > 0 ? m->n_ghost : 1) * sizeof(int64_t)));
+  D4B_NCCL(g_nccl.GroupStart());
+  for (const D4bPeer &p : m->peers) {
+    if (p.send_elem_cnt > 0)
+      D4B_NCCL(g_nccl.Send(m->d_send_src + p.send_elem_off, (size_t)p.send_elem_cnt, ncclInt64, p.rank, g_comm, m->stream));
+    if (p.ghost_cnt > 0)
+      D4B_NCCL(g_nccl.Recv(d_remote + p.ghost_first, (size_t)p.ghost_cnt, ncclInt64, p.rank, g_comm, m->stream));
+  }
+  D4B_NCCL(g_nccl.GroupEnd());
+  std::vector<int64_t> off((size_t)(m->n_ghost > 0 ? m->n_ghost : 1), 0);
+  D4B_CUDA(cudaMemcpyAsync(off.data(), d_remote, (size_t)m->n_ghost * sizeof(int64_t), cudaMemcpyDeviceToHost, m->stream));
+  const int agreed = all_agree(m, d_sc, ok);
+  cudaFree(d_sc);
+  if (!agreed) { cudaFree(d_remote); peer_release(m); return false; }
+
+  for (size_t i = 0; i < m->peers.size(); ++i) {
+    const D4bPeer &p = m->peers[i];
+    const intptr_t delta = reinterpret_cast<intptr_t>(puh[i]) - reinterpret_cast<intptr_t>(P.uh2);
+    D4B_CHECK(delta % (intptr_t)sizeof(double) == 0, "peer mapping is not 8-byte aligned");
+    for (int g = p.ghost_first; g < p.ghost_first + p.ghost_cnt; ++g) {
+      D4B_CHECK(off[g] >= 0 && off[g] < H, "peer halo: remote offset of ghost %d out of range", g);
+      off[g] += delta / (intptr_t)sizeof(double);
+    }
+  }
+  D4B_CUDA(cudaMemcpyAsync(d_remote, off.data(), (size_t)m->n_ghost * sizeof(int64_t), cudaMemcpyHostToDevice, m->stream));
+  d4b_fast_patch_ghost_offsets(m, d_remote);          // conforming classes: neighbour offsets in their face descriptors
+  for (int64_t &o : off) o -= m->local_nodes;         // mortar kernel: uhat + local_nodes + d_ghost_uh_off[g]
+  D4B_CUDA(cudaMalloc(&P.d_ghost_uh_off, off.size() * sizeof(int64_t)));
+  D4B_CUDA(cudaMemcpyAsync(P.d_ghost_uh_off, off.data(), off.size() * sizeof(int64_t), cudaMemcpyHostToDevice, m->stream));
+  P.n_nbr = (int)m->peers.size();
+  std::vector<unsigned long long *> sig(P.n_nbr > 0 ? P.n_nbr : 1, nullptr);
+  std::vector<int32_t> wr(P.n_nbr > 0 ? P.n_nbr : 1, 0);
+  for (int i = 0; i < P.n_nbr; ++i) { sig[i] = pfl[i] + m->mpirank; wr[i] = m->peers[i].rank; }
+  D4B_CUDA(cudaMalloc(&P.d_signal, sig.size() * sizeof(void *)));
+  D4B_CUDA(cudaMalloc(&P.d_wait, wr.size() * sizeof(int32_t)));
+  D4B_CUDA(cudaMemcpyAsync(P.d_signal, sig.data(), sig.size() * sizeof(void *), cudaMemcpyHostToDevice, m->stream));
+  D4B_CUDA(cudaMemcpyAsync(P.d_wait, wr.data(), wr.size() * sizeof(int32_t), cudaMemcpyHostToDevice, m->stream));
+  D4B_CUDA(cudaStreamSynchronize(m->stream));
+  cudaFree(d_remote);
+  // the one-copy buffer of d4b_fast_setup is no longer used
+  cudaFree(m->d_uhat);
+  m->device_bytes += (int64_t)(2 * H - (m->local_nodes + m->ghost_nodes)) * (int64_t)sizeof(double);
+  m->d_uhat = P.uh2;
+  P.state = 1;
+  return true;
+}
+
+void d4b_comm_peer_begin(d4b_mesh *m) {
+  D4bPeerHalo &P = m->peer;
+  ++P.epoch;
+  m->d_uhat = P.uh2 + (P.epoch & 1) * P.H;
+}
+
+void d4b_comm_peer_signal(d4b_mesh *m) {
+  const D4bPeerHalo &P = m->peer;
+  if (P.n_nbr == 0) return;
+  peer_signal_k<<<1, 32, 0, m->comm_stream>>>(P.d_signal, P.n_nbr, P.epoch);
+  D4B_CUDA(cudaGetLastError());
+}
+
+void d4b_comm_peer_wait(d4b_mesh *m) {
+  const D4bPeerHalo &P = m->peer;
+  if (P.n_nbr == 0) return;
+  peer_wait_k<<<1, 32, 0, m->comm_stream>>>(P.flags, P.d_wait, P.n_nbr, P.epoch, m->mpirank);
+  D4B_CUDA(cudaGetLastError());
+}
+
+// Neighbours may still be reading this rank's uhat: meshes with an active peer halo are destroyed
+// collectively (every rank drains its own device, then all meet before anything is unmapped or freed).
+void d4b_comm_peer_teardown(d4b_mesh *m) {
+  if (m->peer.state != 1) return;
+  cudaDeviceSynchronize();
+  if (g_comm && g_size == m->mpisize) {
+    int64_t *d_sc = nullptr;
+    if (cudaMalloc(&d_sc, sizeof(int64_t)) == cudaSuccess) {
+      all_agree(m, d_sc, 1);
+      cudaFree(d_sc);
+    }
+  }
+  peer_release(m);
+  m->peer.state = -1;
 }

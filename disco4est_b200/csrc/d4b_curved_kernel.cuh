@@ -86,7 +86,7 @@ __device__ __forceinline__ void curved_face(const CurvedArgs &a, const FastTab &
   constexpr int NN = N * N;
   constexpr int T1 = (ND == 0) ? 1 : 0, T2 = (ND == 2) ? 1 : 2;   // my tangential directions, x <-> T1, y <-> T2
   const int code = fm.code;
-  const bool own = code & kOwn, interior = fm.nbr >= 0;
+  const bool own = code & kOwn, interior = fm.nbr != kNoNbr;
   const bool swp = code & (4 << 3), frow = code & (2 << 3), fcol = code & (1 << 3);
   int row = swp ? x : y, col = swp ? y : x;
   row = frow ? N - 1 - row : row;

@@ -52,6 +52,7 @@ __constant__ FastTab c_tab[9];   // indexed by N
 
 // code bits of an element face
 constexpr int kOwn = 1 << 6;     // this element owns the face record
+constexpr int64_t kNoNbr = INT64_MIN;   // neighbour offset of a boundary face (offsets into a peer's uhat may be negative)
 
 // what to do with a finished entry of A u (D4bEpilogue, d4b_internal.h)
 struct EpiCoef { double alpha, beta; };
@@ -81,7 +82,7 @@ struct FastArgs {
   const double *FG;             // [n_elem][6][N^3] volume metric
   const double *FF;             // face records, [7][N^2] each
   const int64_t *face_rec;      // [6*n_elem] offset of the face record in FF
-  const int64_t *face_nbr;      // [6*n_elem] nodal offset of the neighbour or -1
+  const int64_t *face_nbr;      // [6*n_elem] nodal offset of the neighbour or kNoNbr
   const int32_t *face_code;     // [6*n_elem] f_p | perm << 3 | own << 6
   const double *uh;             // Gauss-collocated input
   double *Au;
@@ -350,7 +351,7 @@ __global__ void __launch_bounds__(CurvedCfg<N>::THREADS, CurvedCfg<N>::MIN_BLOCK
         const int f = 2 * nd + sd;
         const int64_t nb = a.face_nbr[6 * ei + f];
         code[sd] = a.face_code[6 * ei + f];
-        interior[sd] = nb >= 0;
+        interior[sd] = nb != kNoNbr;
         const double *rec = a.FF + a.face_rec[6 * ei + f];
         const int perm = (code[sd] >> 3) & 7;
         const bool own = code[sd] & kOwn;
@@ -600,7 +601,7 @@ void launch_hp(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, in
   a.elem = cls.d_elem; a.first = first; a.n_elem = last;
   a.deg = m->d_deg; a.ghost_deg = m->d_ghost_deg;
   a.nodal_stride = m->d_nodal_stride; a.quad_stride = m->d_quad_stride;
-  a.ghost_nodal_stride = m->d_ghost_nodal_stride;
+  a.ghost_nodal_stride = m->peer.state == 1 ? m->peer.d_ghost_uh_off : m->d_ghost_nodal_stride;
   a.G = m->d_G; a.LQ = m->local_nodes_quad; a.W = m->d_W;
   a.elem_side = m->d_elem_side; a.elem_sub = m->d_elem_sub;
   a.side_faces_m = m->d_side_faces_m; a.side_faces_p = m->d_side_faces_p; a.side_f_p = m->d_side_f_p;
@@ -1066,7 +1067,7 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<int
       c.n_elem = (int)els.size();
       c.n_interior = n_interior_kind[kind];
       c.d_elem = d4b_dev_upload<int32_t>(m, els.data(), els.size());
-      std::vector<int64_t> face_rec((size_t)6 * els.size()), face_nbr((size_t)6 * els.size(), -1);
+      std::vector<int64_t> face_rec((size_t)6 * els.size()), face_nbr((size_t)6 * els.size(), kNoNbr);
       std::vector<int32_t> face_code((size_t)6 * els.size(), 0);
       std::vector<unsigned char> has_extra(els.size(), 0);
       bool any_extra = false;
@@ -1230,6 +1231,42 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<int
   m->d_uhat = d4b_dev_alloc<double>(m, (size_t)(d->local_nodes + d->ghost_nodes));
 }
 
+namespace {
+// neighbour offsets >= local_nodes address a ghost's lines behind the local block of uhat: replace them by the
+// offset of the same lines in the owner's uhat (peer memory), relative to this rank's uhat
+__global__ void patch_ghost_nbr_k(int64_t *__restrict__ nbr, int step, int64_t n, int64_t local_nodes,
+                                  const int64_t *__restrict__ ghost_stride, int n_ghost,
+                                  const int64_t *__restrict__ ghost_off) {
+  for (int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; j < n; j += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t v = nbr[j * step];
+    if (v == kNoNbr || v < local_nodes) continue;
+    const int64_t key = v - local_nodes;
+    int lo = 0, hi = n_ghost - 1;   // the last ghost whose first node is <= key
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (ghost_stride[mid] <= key) lo = mid; else hi = mid - 1;
+    }
+    nbr[j * step] = ghost_off[lo] + (key - ghost_stride[lo]);
+  }
+}
+}  // namespace
+
+void d4b_fast_patch_ghost_offsets(d4b_mesh *m, const int64_t *d_ghost_off) {
+  if (m->n_ghost == 0) return;
+  for (const D4bFastClass &c : m->fast) {
+    const int64_t n = (int64_t)6 * c.n_elem;
+    if (n == 0) continue;
+    const int grid = (int)std::min<int64_t>((n + 255) / 256, 1184);
+    if (c.d_face_nbr)
+      patch_ghost_nbr_k<<<grid, 256, 0, m->stream>>>(c.d_face_nbr, 1, n, m->local_nodes, m->d_ghost_nodal_stride,
+                                                     m->n_ghost, d_ghost_off);
+    if (c.d_face_meta)
+      patch_ghost_nbr_k<<<grid, 256, 0, m->stream>>>(static_cast<int64_t *>(c.d_face_meta), 2, n, m->local_nodes,
+                                                     m->d_ghost_nodal_stride, m->n_ghost, d_ghost_off);
+    D4B_CUDA(cudaGetLastError());
+  }
+}
+
 void d4b_launch_fast_range(d4b_mesh *m, const double *d_u, double *d_Au, int what, int e0, int e1) {
   for (const D4bFastClass &c : m->fast) {
     const std::vector<int32_t> &list = what == 0 ? c.h_hat : c.h_elem;
@@ -1255,7 +1292,7 @@ void d4b_launch_fast_range(d4b_mesh *m, const double *d_u, double *d_Au, int wha
 // part 2 (after the halo arrived): uh of the ghost elements + elements with a ghost neighbour.
 // Launches go to m->stream (d4b_apply_device points it at the high-priority halo stream for part 2).
 void d4b_launch_fast(d4b_mesh *m, const double *d_u, double *d_Au, int part) {
-  if (part != 1) {
+  if (part == 0 || (part == 2 && m->peer.state != 1)) {   // (peer halo: the ghosts' uh is read where its owner wrote it)
     const int phase = part == 0 ? 0 : 1;
     for (const D4bFastClass &c : m->fast) {
 #define D4B_CASE(n) case n: launch_interp<n>(m, c, d_u, phase); break;

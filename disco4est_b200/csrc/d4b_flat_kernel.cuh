@@ -19,7 +19,7 @@
 // Included by d4b_fast.cu (shares its constant tables and helpers).
 
 struct FaceMeta {     // 16 bytes per element face
-  int64_t nbr;        // offset of the neighbour's uh block, -1 on the boundary
+  int64_t nbr;        // offset of the neighbour's uh block, kNoNbr on the boundary
   int32_t rec;        // record index into FF3 (records of 3 planes [NN])
   int32_t code;       // f_p | perm << 3 | own << 6
 };
@@ -94,7 +94,7 @@ __device__ __forceinline__ void flat_face(const FlatArgs &a, const FastTab &T, c
                                           int y, double trm, double dnm, double wxy, double &ve, double &vd) {
   constexpr int NN = N * N;
   const int code = fm.code;
-  const bool own = code & kOwn, interior = fm.nbr >= 0;
+  const bool own = code & kOwn, interior = fm.nbr != kNoNbr;
   int row = (code & (4 << 3)) ? x : y, col = (code & (4 << 3)) ? y : x;
   row = (code & (2 << 3)) ? N - 1 - row : row;
   col = (code & (1 << 3)) ? N - 1 - col : col;

@@ -87,6 +87,24 @@ struct D4bPeer {
   int rank = 0;
   int64_t send_off = 0, send_cnt = 0;   // into d_sendbuf
   int64_t recv_off = 0, recv_cnt = 0;   // into d_ughost
+  int32_t send_elem_off = 0, send_elem_cnt = 0;   // its mirrors in d_send_src
+  int32_t ghost_first = 0, ghost_cnt = 0;         // its ghosts (ghost ids are contiguous per owner)
+};
+
+// Halo over peer memory (d4b_comm.cu): instead of exchanging the mirrors' nodal values, every rank maps
+// the Gauss-collocated vectors of its neighbour ranks (CUDA IPC over NVLink) and its boundary elements
+// read the neighbours' lines where they lie.
+struct D4bPeerHalo {
+  int state = 0;                     // 0 not tried yet, 1 active, -1 unavailable (NCCL exchange is used)
+  double *uh2 = nullptr;             // two copies of uhat, H doubles apart (IPC-exported); apply k writes copy k & 1
+  int64_t H = 0;                     // the same on every rank, so that peer - local offsets hold for both copies
+  unsigned long long *flags = nullptr;        // [mpisize]: flags[q] = last apply whose uhat rank q has finished
+  std::vector<void *> mapped;                 // IPC mappings to close
+  unsigned long long **d_signal = nullptr;    // per neighbour rank: address of its flags[my rank]
+  int32_t *d_wait = nullptr;                  // neighbour ranks
+  int n_nbr = 0;
+  unsigned long long epoch = 0;
+  int64_t *d_ghost_uh_off = nullptr; // per ghost: offset of its uhat lines relative to (uhat + local_nodes)
 };
 
 struct d4b_mesh {
@@ -141,6 +159,7 @@ struct d4b_mesh {
   double *d_sendbuf = nullptr;
   cudaStream_t comm_stream = nullptr;
   cudaEvent_t ev_packed = nullptr, ev_recv = nullptr, ev_interp = nullptr, ev_boundary = nullptr;
+  D4bPeerHalo peer;
 
   // staging for host-pointer calls
   double *d_u_stage = nullptr, *d_Au_stage = nullptr;
@@ -234,5 +253,13 @@ void d4b_comm_teardown(d4b_mesh *m);
 void d4b_comm_exchange_begin(d4b_mesh *m, const double *d_u);
 void d4b_comm_exchange_wait(d4b_mesh *m);
 void d4b_comm_allreduce_sum(d4b_mesh *m, double *d_x, int n);
+// peer-memory halo: collective set-up on first use (true when active), per-apply signal / wait
+bool d4b_comm_peer_ready(d4b_mesh *m);
+void d4b_comm_peer_begin(d4b_mesh *m);    // next epoch: points m->d_uhat at this apply's copy
+void d4b_comm_peer_signal(d4b_mesh *m);   // on m->comm_stream: tell the neighbours this rank's uhat is complete
+void d4b_comm_peer_teardown(d4b_mesh *m); // collective; before anything of the mesh is freed
+void d4b_comm_peer_wait(d4b_mesh *m);     // on m->comm_stream: until every neighbour has signalled this epoch
+// d4b_fast.cu: ghost neighbours of the conforming classes addressed through d_ghost_off (offsets relative to uhat)
+void d4b_fast_patch_ghost_offsets(d4b_mesh *m, const int64_t *d_ghost_off);
 
 #endif

@@ -26,7 +26,7 @@ _I32P_T = C.POINTER(C.c_int32)
 EXPORTS = [
     "d4b_set_abort_hook", "d4b_abi_version", "d4b_device_count", "d4b_init",
     "d4b_geom_compute", "d4b_mesh_create_with_geometry",
-    "d4b_mesh_create", "d4b_mesh_destroy", "d4b_mesh_local_nodes", "d4b_mesh_device_bytes", "d4b_mesh_fast_elements", "d4b_mesh_flat_elements", "d4b_mesh_hp_elements", "d4b_mesh_launches_per_apply",
+    "d4b_mesh_create", "d4b_mesh_destroy", "d4b_mesh_local_nodes", "d4b_mesh_device_bytes", "d4b_mesh_fast_elements", "d4b_mesh_flat_elements", "d4b_mesh_hp_elements", "d4b_mesh_launches_per_apply", "d4b_mesh_halo_mode",
     "d4b_apply", "d4b_apply_stiffness", "d4b_sync", "d4b_set_stream",
     "d4b_interp_to_quad", "d4b_apply_galerkin", "d4b_apply_mass", "d4b_mesh_set_mass_diag", "d4b_build_rhs", "d4b_estimator_bi",
     "d4b_vec_dot", "d4b_vec_axpy", "d4b_vec_xpby", "d4b_vec_scale", "d4b_vec_dot_noalloc",
@@ -73,6 +73,8 @@ def load_library():
     L.d4b_mesh_hp_elements.argtypes = [C.c_void_p]
     L.d4b_mesh_launches_per_apply.restype = C.c_int32
     L.d4b_mesh_launches_per_apply.argtypes = [C.c_void_p]
+    L.d4b_mesh_halo_mode.restype = C.c_int32
+    L.d4b_mesh_halo_mode.argtypes = [C.c_void_p]
     for fn in (L.d4b_apply, L.d4b_apply_stiffness):
         fn.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         fn.restype = None
@@ -309,6 +311,10 @@ class Mesh:
 
     def launches_per_apply(self):
         return int(self.L.d4b_mesh_launches_per_apply(self.h))
+
+    def halo_mode(self):
+        """"none" (one rank), "nccl", "peer" (neighbours' memory over NVLink) or "undecided" (before the first apply)"""
+        return {0: "none", 1: "nccl", 2: "peer", -1: "undecided"}[int(self.L.d4b_mesh_halo_mode(self.h))]
 
     def device_bytes(self):
         return int(self.L.d4b_mesh_device_bytes(self.h))

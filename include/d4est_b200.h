@@ -190,6 +190,12 @@ int64_t     d4b_mesh_flat_elements(const d4b_mesh_t *mesh);
 int64_t     d4b_mesh_hp_elements(const d4b_mesh_t *mesh);
 /* CUDA kernels one d4b_apply launches on this mesh (for launch accounting)  */
 int32_t     d4b_mesh_launches_per_apply(const d4b_mesh_t *mesh);
+/* How this mesh's applies obtain ghost data (replaces d4est_ghost_data_exchange, src/Mesh/d4est_ghost_data.c:142-255):
+ * 0 one rank, no exchange; 1 NCCL send/recv of the mirrors' nodal values; 2 peer memory -- the boundary elements read
+ * the neighbour ranks' Gauss-collocated vectors over NVLink (CUDA IPC mappings, one node; chosen in the first apply
+ * when every rank can map its neighbours and no element needs the general kernel; D4B_PEER_HALO=0 keeps mode 1);
+ * -1 multi-rank mesh that has not been applied yet.  With mode 2 d4b_mesh_destroy is collective.              */
+int32_t     d4b_mesh_halo_mode(const d4b_mesh_t *mesh);
 
 /* --------------------------------------------- geometric factors on device */
 /* Replaces the geometry half of d4est_mesh_data_compute (src/Mesh/d4est_mesh.c:2543-2755)

@@ -11,7 +11,9 @@ single-rank oracle on the whole mesh.  This checks the partition, the ghost
 numbering and the plan the CUDA library consumes.
 
 mode "nccl": one GPU per rank.  The same mesh through the C ABI: d4b_comm_init
-from a torch-broadcast NCCL id, d4b_apply with the halo exchange inside, plus
+from a torch-broadcast NCCL id, d4b_apply with the halo inside -- once over NCCL
+send/recv and once over peer memory (the neighbours' vectors mapped with CUDA IPC),
+compared bit for bit, also over back-to-back applies and the fused smoother -- plus
 the all-reduced dot product; rank 0 compares with the oracle.
 """
 import os
@@ -108,11 +110,25 @@ def main():
         from disco4est_b200.runtime import comm_init_from_torch, comm_destroy
 
         comm_init_from_torch(rank)
+        # two meshes of the same description: halo over NCCL send/recv, and over peer memory (the default on one node)
+        os.environ["D4B_PEER_HALO"] = "0"
+        m_nccl = Mesh(A, device=rank)
+        au_nccl = np.zeros_like(ul)
+        m_nccl.apply(ul, au_nccl)
+        assert m_nccl.halo_mode() == "nccl", m_nccl.halo_mode()
+        os.environ["D4B_PEER_HALO"] = "1"
         m = Mesh(A, device=rank)
         if not mesh_arg.startswith("golden:"):
             assert m.fast_elements() == A["n_local"], "every brick element must take a fast kernel, ghosts included"
         au = np.zeros_like(ul)
         m.apply(ul, au)
+        # when no rank needs the general kernel, the peer halo must be what ran (on every rank or on none)
+        t = torch.tensor([1 if m.fast_elements() == _i(A["n_local"]) else 0, 1 if m.halo_mode() == "peer" else 0,
+                          -(1 if m.halo_mode() == "peer" else 0)], dtype=torch.int64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        assert int(t[1]) == -int(t[2]), "ranks disagree about the halo mode"
+        assert int(t[0]) == 0 or int(t[1]) == 1, "peer halo was not activated: %s" % m.halo_mode()
+        assert np.array_equal(au, au_nccl), "peer-memory halo and NCCL halo differ"
         # device-pointer path + all-reduced dot
         du = torch.from_numpy(ul).cuda(rank)
         dau = torch.empty_like(du)
@@ -120,6 +136,32 @@ def main():
         m.sync()
         assert np.array_equal(dau.cpu().numpy(), au)
         gdot = m.dot(du, dau)
+        # back-to-back applies on alternating inputs without a host synchronisation in between: the two copies
+        # of uhat and the epoch flags must keep them apart
+        du2 = torch.from_numpy(np.random.default_rng(11 + rank).standard_normal(ul.size)).cuda(rank)
+        ref2 = torch.empty_like(du)
+        m_nccl.apply(du2, ref2)
+        m_nccl.sync()
+        outs = [torch.empty_like(du) for _ in range(7)]
+        for k in range(7):
+            m.apply(du if k % 2 == 0 else du2, outs[k])
+        m.sync()
+        for k in range(7):
+            assert torch.equal(outs[k], dau if k % 2 == 0 else ref2), "apply %d of the back-to-back sequence differs" % k
+        # fused Chebyshev smoother (u updated in place by the apply's epilogue) and the lambda_max estimate
+        if m.fast_elements() == _i(A["n_local"]):
+            res = []
+            for mm in (m_nccl, m):
+                us = torch.zeros_like(du)
+                rs = torch.empty_like(du)
+                lam = mm.cg_eigs(us, du, 5)
+                us.zero_()
+                mm.cheby_smooth(us, du, rs, 4, lam / 30.0, lam)
+                mm.sync()
+                res.append((lam, us.clone(), rs.clone()))
+            assert res[0][0] == res[1][0], "cg_eigs differs between the two halos: %r %r" % (res[0][0], res[1][0])
+            assert torch.equal(res[0][1], res[1][1]) and torch.equal(res[0][2], res[1][2]), "smoother differs"
+        m_nccl.close()
         m.close()
         comm_destroy()
 
