@@ -73,17 +73,27 @@ void d4b_apply_device(d4b_mesh *m, const double *du, double *dAu) {
     // halo stream   :        wait uh(local) | signal neighbours | wait for theirs | boundary elements
     d4b_comm_peer_begin(m);
     d4b_launch_fast(m, du, dAu, 0);
-    D4B_CUDA(cudaEventRecord(m->ev_interp, m->stream));
-    D4B_CUDA(cudaStreamWaitEvent(m->comm_stream, m->ev_interp, 0));
-    d4b_comm_peer_signal(m);
-    d4b_launch_fast(m, du, dAu, 1);
-    d4b_comm_peer_wait(m);
-    cudaStream_t compute = m->stream;
-    m->stream = m->comm_stream;
-    d4b_launch_fast(m, du, dAu, 2);
-    D4B_CUDA(cudaEventRecord(m->ev_boundary, m->comm_stream));
-    m->stream = compute;
-    D4B_CUDA(cudaStreamWaitEvent(m->stream, m->ev_boundary, 0));
+    // small meshes (coarse multigrid levels): an interior launch of a few microseconds hides nothing, and the two
+    // cross-stream dependencies cost more than it runs -- everything in order on the compute stream
+    static const int64_t split_min = getenv("D4B_PEER_SPLIT_MIN_NODES") ? atoll(getenv("D4B_PEER_SPLIT_MIN_NODES")) : (int64_t)1 << 20;
+    if (m->local_nodes < split_min) {
+      d4b_comm_peer_signal(m, m->stream);
+      d4b_launch_fast(m, du, dAu, 1);
+      d4b_comm_peer_wait(m, m->stream);
+      d4b_launch_fast(m, du, dAu, 2);
+    } else {
+      D4B_CUDA(cudaEventRecord(m->ev_interp, m->stream));
+      D4B_CUDA(cudaStreamWaitEvent(m->comm_stream, m->ev_interp, 0));
+      d4b_comm_peer_signal(m, m->comm_stream);
+      d4b_launch_fast(m, du, dAu, 1);
+      d4b_comm_peer_wait(m, m->comm_stream);
+      cudaStream_t compute = m->stream;
+      m->stream = m->comm_stream;
+      d4b_launch_fast(m, du, dAu, 2);
+      D4B_CUDA(cudaEventRecord(m->ev_boundary, m->comm_stream));
+      m->stream = compute;
+      D4B_CUDA(cudaStreamWaitEvent(m->stream, m->ev_boundary, 0));
+    }
   } else {
     // compute stream:  pack | uh(local) | interior elements ............ | join
     // halo stream   :       wait pack | send/recv | wait uh(local) | uh(ghosts) | boundary elements

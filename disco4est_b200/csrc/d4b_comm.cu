@@ -13,6 +13,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <vector>
 #include "d4b_internal.h"
 
 namespace {
@@ -92,7 +93,9 @@ extern "C" void d4b_comm_init(const void *id_in, int rank, int size) {
   D4B_NCCL(g_nccl.CommInitRank(&g_comm, size, id, rank));
 }
 
+static void d4b_comm_release_allreduce();
 extern "C" void d4b_comm_destroy(void) {
+  d4b_comm_release_allreduce();
   if (g_comm) { g_nccl.CommDestroy(g_comm); g_comm = nullptr; }
   g_rank = 0; g_size = 1;
 }
@@ -192,10 +195,149 @@ void d4b_comm_exchange_wait(d4b_mesh *m) {
   D4B_CUDA(cudaStreamWaitEvent(m->stream, m->ev_recv, 0));
 }
 
+namespace {
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+}  // namespace
+
+// ---- all-reduce of a few doubles over peer memory ------------------------------------------
+// The solvers' dot products end in a sum of ONE double over the ranks (sc_allreduce in the reference,
+// d4est_solver_cg_eigs.c:181-245), two per CG iteration on every multigrid level: pure latency.  On one node every
+// rank maps a small slot array of every other rank (CUDA IPC) and one kernel does the whole exchange: it writes this
+// rank's values into slot [rank] of every rank -- each 8-byte store carries 4 bytes of data and the 4-byte epoch
+// of the call, so a value is complete when both of its words show the epoch (no flag, no fence) -- then polls its
+// own R slots and adds them in rank order: every rank gets the same bits.  Two slot sets alternate: a rank can only
+// be two calls ahead of a peer that has not yet read.  Falls back to ncclAllReduce when the mappings cannot be made.
+namespace {
+
+constexpr int kArMax = 4;   // doubles per call
+
+struct PeerAllreduce {
+  int state = 0;                         // 0 not tried, 1 active, -1 unavailable
+  unsigned long long *slots = nullptr;   // [2][R][kArMax][2]
+  unsigned long long **d_peer = nullptr; // [R] slot arrays of all ranks (own included)
+  std::vector<void *> mapped;
+  unsigned epoch = 0;
+  cudaStream_t last_stream = nullptr;    // calls must execute in issue order: a call on another stream waits for the last
+  cudaEvent_t ev = nullptr;
+} g_ar;
+
+__global__ void peer_allreduce_k(double *__restrict__ x, int n, unsigned long long *__restrict__ mine,
+                                 unsigned long long *const *__restrict__ peer, int rank, int R, unsigned epoch) {
+  __shared__ double got[64 * kArMax];
+  const int t = threadIdx.x;
+  const size_t set = (size_t)(epoch & 1) * R * kArMax * 2;
+  if (t < R * n) {
+    const int q = t / n, j = t % n;
+    const unsigned long long bits = (unsigned long long)__double_as_longlong(x[j]);
+    unsigned long long *dst = peer[q] + set + ((size_t)rank * kArMax + j) * 2;
+    const unsigned long long w0 = (bits & 0xffffffffull) | ((unsigned long long)epoch << 32);
+    const unsigned long long w1 = (bits >> 32) | ((unsigned long long)epoch << 32);
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(dst), "l"(w0) : "memory");
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(dst + 1), "l"(w1) : "memory");
+    const unsigned long long *src = mine + set + ((size_t)q * kArMax + j) * 2;
+    const unsigned long long t0 = global_ns();
+    unsigned long long a, b;
+    for (;;) {
+      asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(a) : "l"(src) : "memory");
+      asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(b) : "l"(src + 1) : "memory");
+      if ((unsigned)(a >> 32) == epoch && (unsigned)(b >> 32) == epoch) break;
+      if (global_ns() - t0 > 30000000000ull) {
+        printf("[d4b] rank %d: all-reduce %u timed out waiting for rank %d\n", rank, epoch, q);
+        __trap();
+      }
+    }
+    got[q * kArMax + j] = __longlong_as_double((long long)((a & 0xffffffffull) | (b << 32)));
+  }
+  __syncthreads();
+  if (t < n) {
+    double s = 0.;
+    for (int q = 0; q < R; ++q) s += got[q * kArMax + t];
+    x[t] = s;
+  }
+}
+
+void peer_allreduce_release() {
+  for (void *p : g_ar.mapped) cudaIpcCloseMemHandle(p);
+  g_ar.mapped.clear();
+  if (g_ar.slots) { cudaFree(g_ar.slots); g_ar.slots = nullptr; }
+  if (g_ar.d_peer) { cudaFree(g_ar.d_peer); g_ar.d_peer = nullptr; }
+  if (g_ar.ev) { cudaEventDestroy(g_ar.ev); g_ar.ev = nullptr; }
+  g_ar.last_stream = nullptr;
+  cudaGetLastError();
+}
+
+// collective; every rank reaches it in its first all-reduce
+bool peer_allreduce_ready(cudaStream_t st) {
+  if (g_ar.state) return g_ar.state > 0;
+  g_ar.state = -1;
+  const char *env = getenv("D4B_PEER_ALLREDUCE");
+  const int R = g_size;
+  int ok = !(env && atoi(env) == 0) && R <= 64;
+  struct X { cudaIpcMemHandle_t h; int64_t ok; } mine;
+  memset(&mine, 0, sizeof(mine));
+  const size_t bytes = (size_t)2 * R * kArMax * 2 * sizeof(unsigned long long);
+  if (ok) ok = cudaMalloc(&g_ar.slots, bytes) == cudaSuccess;
+  if (ok) {
+    D4B_CUDA(cudaMemsetAsync(g_ar.slots, 0, bytes, st));   // epoch 0 is never used
+    ok = cudaIpcGetMemHandle(&mine.h, g_ar.slots) == cudaSuccess;
+  }
+  cudaGetLastError();
+  mine.ok = ok;
+  char *d_x = nullptr;
+  D4B_CUDA(cudaMalloc(&d_x, (size_t)(R + 1) * sizeof(X)));
+  D4B_CUDA(cudaMemcpyAsync(d_x + (size_t)R * sizeof(X), &mine, sizeof(mine), cudaMemcpyHostToDevice, st));
+  D4B_NCCL(g_nccl.AllGather(d_x + (size_t)R * sizeof(X), d_x, sizeof(X), ncclChar, g_comm, st));
+  std::vector<X> all(R);
+  D4B_CUDA(cudaMemcpyAsync(all.data(), d_x, (size_t)R * sizeof(X), cudaMemcpyDeviceToHost, st));
+  D4B_CUDA(cudaStreamSynchronize(st));
+  for (int q = 0; q < R; ++q) ok = ok && all[q].ok;
+  std::vector<unsigned long long *> ptr(R, nullptr);
+  for (int q = 0; q < R && ok; ++q) {
+    if (q == g_rank) { ptr[q] = g_ar.slots; continue; }
+    void *a = nullptr;
+    ok = cudaIpcOpenMemHandle(&a, all[q].h, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+    if (ok) { g_ar.mapped.push_back(a); ptr[q] = static_cast<unsigned long long *>(a); }
+  }
+  cudaGetLastError();
+  // agree (over NCCL, which always works here)
+  int64_t v = ok, *d_v = reinterpret_cast<int64_t *>(d_x);
+  D4B_CUDA(cudaMemcpyAsync(d_v, &v, sizeof(v), cudaMemcpyHostToDevice, st));
+  D4B_NCCL(g_nccl.AllReduce(d_v, d_v, 1, ncclInt64, ncclMin, g_comm, st));
+  D4B_CUDA(cudaMemcpyAsync(&v, d_v, sizeof(v), cudaMemcpyDeviceToHost, st));
+  D4B_CUDA(cudaStreamSynchronize(st));
+  cudaFree(d_x);
+  if (!v) { peer_allreduce_release(); return false; }
+  D4B_CUDA(cudaMalloc(&g_ar.d_peer, (size_t)R * sizeof(void *)));
+  D4B_CUDA(cudaMemcpy(g_ar.d_peer, ptr.data(), (size_t)R * sizeof(void *), cudaMemcpyHostToDevice));
+  D4B_CUDA(cudaEventCreateWithFlags(&g_ar.ev, cudaEventDisableTiming));
+  g_ar.last_stream = nullptr;
+  g_ar.epoch = 0;
+  g_ar.state = 1;
+  return true;
+}
+
+}  // namespace
+
 // sum n doubles (n <= 4) over the ranks, in place on the device, on the mesh's stream
 void d4b_comm_allreduce_sum(d4b_mesh *m, double *d_x, int n) {
   if (m->mpisize == 1) return;
   D4B_CHECK(g_comm, "d4b_comm_init was not called");
+  D4B_CHECK(n >= 1 && n <= kArMax, "all-reduce of %d doubles", n);
+  if (peer_allreduce_ready(m->stream)) {
+    ++g_ar.epoch;
+    if (g_ar.epoch == 0) ++g_ar.epoch;   // 0 marks an empty slot
+    if (g_ar.last_stream && g_ar.last_stream != m->stream) D4B_CUDA(cudaStreamWaitEvent(m->stream, g_ar.ev, 0));
+    peer_allreduce_k<<<1, 64 * kArMax, 0, m->stream>>>(d_x, n, g_ar.slots, g_ar.d_peer, g_rank, g_size, g_ar.epoch);
+    D4B_CUDA(cudaGetLastError());
+    D4B_CUDA(cudaEventRecord(g_ar.ev, m->stream));
+    g_ar.last_stream = m->stream;
+    return;
+  }
   D4B_NCCL(g_nccl.AllReduce(d_x, d_x, (size_t)n, ncclDouble, ncclSum, g_comm, m->stream));
 }
 
@@ -216,12 +358,6 @@ __global__ void peer_signal_k(unsigned long long *const *__restrict__ dst, int n
     __threadfence_system();
     asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(dst[i]), "l"(epoch) : "memory");
   }
-}
-
-__device__ __forceinline__ unsigned long long global_ns() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-  return t;
 }
 
 __global__ void peer_wait_k(const unsigned long long *__restrict__ flags, const int32_t *__restrict__ ranks, int n,
@@ -383,17 +519,17 @@ void d4b_comm_peer_begin(d4b_mesh *m) {
   m->d_uhat = P.uh2 + (P.epoch & 1) * P.H;
 }
 
-void d4b_comm_peer_signal(d4b_mesh *m) {
+void d4b_comm_peer_signal(d4b_mesh *m, cudaStream_t st) {
   const D4bPeerHalo &P = m->peer;
   if (P.n_nbr == 0) return;
-  peer_signal_k<<<1, 32, 0, m->comm_stream>>>(P.d_signal, P.n_nbr, P.epoch);
+  peer_signal_k<<<1, 32, 0, st>>>(P.d_signal, P.n_nbr, P.epoch);
   D4B_CUDA(cudaGetLastError());
 }
 
-void d4b_comm_peer_wait(d4b_mesh *m) {
+void d4b_comm_peer_wait(d4b_mesh *m, cudaStream_t st) {
   const D4bPeerHalo &P = m->peer;
   if (P.n_nbr == 0) return;
-  peer_wait_k<<<1, 32, 0, m->comm_stream>>>(P.flags, P.d_wait, P.n_nbr, P.epoch, m->mpirank);
+  peer_wait_k<<<1, 32, 0, st>>>(P.flags, P.d_wait, P.n_nbr, P.epoch, m->mpirank);
   D4B_CUDA(cudaGetLastError());
 }
 
@@ -411,4 +547,23 @@ void d4b_comm_peer_teardown(d4b_mesh *m) {
   }
   peer_release(m);
   m->peer.state = -1;
+}
+
+// d4b_comm_destroy is collective like d4b_comm_init: every rank drains its device, all meet, then unmap
+static void d4b_comm_release_allreduce() {
+  if (g_ar.state == 1) {
+    cudaDeviceSynchronize();
+    if (g_comm) {
+      int64_t *d_v = nullptr;
+      if (cudaMalloc(&d_v, sizeof(int64_t)) == cudaSuccess) {
+        cudaMemset(d_v, 0, sizeof(int64_t));
+        g_nccl.AllReduce(d_v, d_v, 1, ncclInt64, ncclMin, g_comm, (cudaStream_t)0);
+        cudaStreamSynchronize((cudaStream_t)0);
+        cudaFree(d_v);
+      }
+    }
+    peer_allreduce_release();
+  }
+  g_ar.state = 0;
+  g_ar.epoch = 0;
 }

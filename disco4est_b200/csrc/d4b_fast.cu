@@ -46,6 +46,8 @@ struct FastTab {
   double e[2][8];    // Gauss basis evaluated at -1 / +1
   double d[2][8];    // Gauss basis derivative at -1 / +1
   double w[8];       // Gauss weights
+  double B[8][8];    // I I^T (Gauss x Gauss): the back-transform of the Gauss-resident smoother (HAT kernels)
+  double Iinv[8][8]; // Gauss -> LGL, [lgl][gauss]: u = (Iinv x Iinv x Iinv) uh
 };
 
 __constant__ FastTab c_tab[9];   // indexed by N
@@ -60,7 +62,7 @@ struct EpiCoef { double alpha, beta; };
 // estimate never left the device (d4b_solver.cu) -- a pair in device memory
 __device__ __forceinline__ EpiCoef epi_coef(const D4bEpilogue &e) {
   EpiCoef c;
-  if (e.mode == 1 && e.coef) { c.alpha = e.coef[0]; c.beta = e.coef[1]; }
+  if ((e.mode == 1 || e.mode == 3) && e.coef) { c.alpha = e.coef[0]; c.beta = e.coef[1]; }
   else { c.alpha = e.alpha; c.beta = e.beta; }
   return c;
 }
@@ -157,29 +159,47 @@ __device__ __forceinline__ int perm_xy(int n, int perm, int a, int b) {
 
 
 // ---- kernel 1: uh = (I x I x I) u ---------------------------------------------
-template <int N>
-__global__ void __launch_bounds__(Cfg<N>::THREADS) interp_kernel(const int32_t *__restrict__ elem, int n_elem,
-                                                                 const int64_t *__restrict__ nodal_stride,
-                                                                 const double *__restrict__ u,
-                                                                 double *__restrict__ uh) {
+// MODE 0: uh = (I x I x I) u
+// MODE 1: the direction update of CG fused in: d = r + (bnum / bden) d is written back and interpolated
+//         (d4est_linalg_vec_xpby of d4est_solver_cg_eigs.c:257 followed by the next apply's first step)
+// MODE 2: the way back, out = (Iinv x Iinv x Iinv) in
+struct InterpArgs {
+  const int32_t *elem;
+  int n_elem;
+  const int64_t *nodal_stride;
+  const double *in;
+  double *out;
+  const double *r, *bnum, *bden;   // MODE 1
+  double *d;                       // MODE 1: = in, written
+};
+template <int N, int MODE>
+__global__ void __launch_bounds__(Cfg<N>::THREADS) interp_kernel(InterpArgs a) {
   using C = Cfg<N>;
   constexpr int NN = C::NN;
   __shared__ double sm[C::EPB * VSize<N>::value];
   const FastTab &T = c_tab[N];
   const int slot = threadIdx.x / NN, lt = threadIdx.x % NN, lx = lt % N, ly = lt / N;
   const int ei = blockIdx.x * C::EPB + slot;
-  const bool active = (slot < C::EPB) && (ei < n_elem);
+  const bool active = (slot < C::EPB) && (ei < a.n_elem);
   double *V = sm + (slot < C::EPB ? slot : 0) * VSize<N>::value;
-  const int64_t ns = active ? nodal_stride[elem[ei]] : 0;
+  const int64_t ns = active ? a.nodal_stride[a.elem[ei]] : 0;
   if (active) {
     double l[N];
 #pragma unroll
-    for (int c = 0; c < N; ++c) l[c] = u[ns + lx + N * ly + NN * c];
+    for (int c = 0; c < N; ++c) l[c] = a.in[ns + lx + N * ly + NN * c];
+    if (MODE == 1) {
+      const double beta = *a.bnum / *a.bden;
+#pragma unroll
+      for (int c = 0; c < N; ++c) {
+        l[c] = a.r[ns + lx + N * ly + NN * c] + beta * l[c];
+        a.d[ns + lx + N * ly + NN * c] = l[c];
+      }
+    }
 #pragma unroll
     for (int c2 = 0; c2 < N; ++c2) {
       double s = 0.;
 #pragma unroll
-      for (int c = 0; c < N; ++c) s += T.I[c2][c] * l[c];
+      for (int c = 0; c < N; ++c) s += (MODE == 2 ? T.Iinv[c2][c] : T.I[c2][c]) * l[c];
       V[vix<N>(lx, ly, c2)] = s;
     }
   }
@@ -192,7 +212,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) interp_kernel(const int32_t *
     for (int i2 = 0; i2 < N; ++i2) {
       double s = 0.;
 #pragma unroll
-      for (int i = 0; i < N; ++i) s += T.I[i2][i] * l[i];
+      for (int i = 0; i < N; ++i) s += (MODE == 2 ? T.Iinv[i2][i] : T.I[i2][i]) * l[i];
       V[vix<N>(i2, lx, ly)] = s;
     }
   }
@@ -205,8 +225,8 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) interp_kernel(const int32_t *
     for (int i2 = 0; i2 < N; ++i2) {
       double s = 0.;
 #pragma unroll
-      for (int i = 0; i < N; ++i) s += T.I[i2][i] * l[i];
-      uh[ns + lx + N * i2 + NN * ly] = s;
+      for (int i = 0; i < N; ++i) s += (MODE == 2 ? T.Iinv[i2][i] : T.I[i2][i]) * l[i];
+      a.out[ns + lx + N * i2 + NN * ly] = s;
     }
   }
 }
@@ -547,12 +567,24 @@ void launch_flat(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, 
     D4B_CUDA(cudaFuncSetAttribute(flat_apply_kernel<N, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     D4B_CUDA(cudaFuncSetAttribute(flat_apply_kernel<N, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     D4B_CUDA(cudaFuncSetAttribute(flat_apply_kernel<N, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    D4B_CUDA(cudaFuncSetAttribute(flat_apply_kernel<N, false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    D4B_CUDA(cudaFuncSetAttribute(flat_apply_kernel<N, false, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = true;
   }
   static const int prefetch = getenv("D4B_PREFETCH") ? atoi(getenv("D4B_PREFETCH")) : 2;
   a.prefetch = prefetch;
   int grid = (last - first + C::EPB - 1) / C::EPB;
-  if (cls.d_FGc) {
+  if (m->epi.dot_part) {   // this launch's partial sums follow those of the apply's earlier launches
+    a.epi.dot_part = m->epi.dot_part + m->dot_count;
+    m->dot_count += (int64_t)grid * (C::THREADS / 32);
+    D4B_CHECK(m->dot_count <= m->dot_capacity, "energy dot: %lld partial sums, room for %lld", (long long)m->dot_count,
+              (long long)m->dot_capacity);
+  }
+  if (m->epi.mode == 3) {
+    D4B_CHECK(!m->d_W && m->epi.uh_out && m->epi.rhs && m->epi.p, "Gauss-resident smoother: bad epilogue");
+    if (cls.d_FGc) flat_apply_kernel<N, false, true, true><<<grid, C::THREADS, smem, m->stream>>>(a);
+    else flat_apply_kernel<N, false, false, true><<<grid, C::THREADS, smem, m->stream>>>(a);
+  } else if (cls.d_FGc) {
     if (m->d_W) flat_apply_kernel<N, true, true><<<grid, C::THREADS, smem, m->stream>>>(a);
     else flat_apply_kernel<N, false, true><<<grid, C::THREADS, smem, m->stream>>>(a);
   } else if (m->d_W) flat_apply_kernel<N, true><<<grid, C::THREADS, smem, m->stream>>>(a);
@@ -665,16 +697,39 @@ void build_hp_tabs(d4b_mesh *m) {
 template <int N>
 void launch_interp(d4b_mesh *m, const D4bFastClass &cls, const double *d_u, int phase) {
   using C = Cfg<N>;
+  InterpArgs a;
+  memset(&a, 0, sizeof(a));
   if (phase == 0) {   // local elements
     if (cls.n_hat == 0) return;
     int grid = (cls.n_hat + C::EPB - 1) / C::EPB;
-    interp_kernel<N><<<grid, C::THREADS, 0, m->stream>>>(cls.d_hat_elem, cls.n_hat, m->d_nodal_stride, d_u, m->d_uhat);
+    a.elem = cls.d_hat_elem; a.n_elem = cls.n_hat; a.nodal_stride = m->d_nodal_stride; a.in = d_u; a.out = m->d_uhat;
+    if (m->epi.xpby_r) {   // CG: d = r + beta d on the way (d4b_solver.cu)
+      a.r = m->epi.xpby_r; a.bnum = m->epi.xpby_num; a.bden = m->epi.xpby_den; a.d = const_cast<double *>(d_u);
+      interp_kernel<N, 1><<<grid, C::THREADS, 0, m->stream>>>(a);
+    } else {
+      interp_kernel<N, 0><<<grid, C::THREADS, 0, m->stream>>>(a);
+    }
   } else {            // ghost elements, from the receive buffer to the tail of uhat
     if (cls.n_ghost_hat == 0) return;
     int grid = (cls.n_ghost_hat + C::EPB - 1) / C::EPB;
-    interp_kernel<N><<<grid, C::THREADS, 0, m->stream>>>(cls.d_ghost_hat, cls.n_ghost_hat, m->d_ghost_nodal_stride,
-                                                        m->d_ughost, m->d_uhat + m->local_nodes);
+    a.elem = cls.d_ghost_hat; a.n_elem = cls.n_ghost_hat; a.nodal_stride = m->d_ghost_nodal_stride;
+    a.in = m->d_ughost; a.out = m->d_uhat + m->local_nodes;
+    interp_kernel<N, 0><<<grid, C::THREADS, 0, m->stream>>>(a);
   }
+  D4B_CUDA(cudaGetLastError());
+}
+
+// out = (M x M x M) in over every collocated element of the class: M = I (to the Gauss basis) or its inverse
+template <int N>
+void launch_basis_change(d4b_mesh *m, const D4bFastClass &cls, const double *in, double *out, bool to_gauss) {
+  using C = Cfg<N>;
+  if (cls.n_hat == 0) return;
+  InterpArgs a;
+  memset(&a, 0, sizeof(a));
+  a.elem = cls.d_hat_elem; a.n_elem = cls.n_hat; a.nodal_stride = m->d_nodal_stride; a.in = in; a.out = out;
+  const int grid = (cls.n_hat + C::EPB - 1) / C::EPB;
+  if (to_gauss) interp_kernel<N, 0><<<grid, C::THREADS, 0, m->stream>>>(a);
+  else interp_kernel<N, 2><<<grid, C::THREADS, 0, m->stream>>>(a);
   D4B_CUDA(cudaGetLastError());
 }
 
@@ -708,8 +763,10 @@ template <int N>
 void launch_interp_range(d4b_mesh *m, const D4bFastClass &cls, const double *d_u, int lo, int hi) {
   using C = Cfg<N>;
   if (hi <= lo) return;
-  interp_kernel<N><<<(hi - lo + C::EPB - 1) / C::EPB, C::THREADS, 0, m->stream>>>(cls.d_hat_elem + lo, hi - lo,
-                                                                                   m->d_nodal_stride, d_u, m->d_uhat);
+  InterpArgs a;
+  memset(&a, 0, sizeof(a));
+  a.elem = cls.d_hat_elem + lo; a.n_elem = hi - lo; a.nodal_stride = m->d_nodal_stride; a.in = d_u; a.out = m->d_uhat;
+  interp_kernel<N, 0><<<(hi - lo + C::EPB - 1) / C::EPB, C::THREADS, 0, m->stream>>>(a);
   D4B_CUDA(cudaGetLastError());
 }
 
@@ -737,6 +794,30 @@ void build_fast_tab(int N, FastTab &T) {
       T.d[s][j] = v;
     }
   for (int j = 0; j < N; ++j) T.w[j] = wg[j];
+  for (int i = 0; i < N; ++i)
+    for (int j = 0; j < N; ++j) {
+      long double v = 0.L;
+      for (int k = 0; k < N; ++k) v += (long double)T.I[i][k] * (long double)T.I[j][k];
+      T.B[i][j] = (double)v;
+    }
+  // Iinv = I^-1 (Gauss-Jordan with partial pivoting in long double; N <= 8, well conditioned)
+  long double A[8][16];
+  for (int i = 0; i < N; ++i)
+    for (int j = 0; j < N; ++j) { A[i][j] = T.I[i][j]; A[i][N + j] = (i == j) ? 1.L : 0.L; }
+  for (int c = 0; c < N; ++c) {
+    int piv = c;
+    for (int r = c + 1; r < N; ++r) if (fabsl(A[r][c]) > fabsl(A[piv][c])) piv = r;
+    for (int j = 0; j < 2 * N; ++j) std::swap(A[c][j], A[piv][j]);
+    const long double inv = 1.L / A[c][c];
+    for (int j = 0; j < 2 * N; ++j) A[c][j] *= inv;
+    for (int r = 0; r < N; ++r) {
+      if (r == c) continue;
+      const long double f = A[r][c];
+      for (int j = 0; j < 2 * N; ++j) A[r][j] -= f * A[c][j];
+    }
+  }
+  for (int i = 0; i < N; ++i)
+    for (int j = 0; j < N; ++j) T.Iinv[i][j] = (double)A[i][N + j];
 }
 
 
@@ -1229,6 +1310,22 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<int
   m->d_flat_FF = fill(ff3_size, src3, 1);
   D4B_CUDA(cudaStreamSynchronize(m->stream));
   m->d_uhat = d4b_dev_alloc<double>(m, (size_t)(d->local_nodes + d->ghost_nodes));
+  // every element in the tangential-free kernel: the solvers may use its energy dot and Gauss-resident smoother
+  int64_t n_flat = 0;
+  for (const D4bFastClass &c : m->fast) if (c.kind == 1) n_flat += c.n_elem;
+  m->all_flat = m->n_generic == 0 && n_flat == d->n_local && d->n_local > 0;
+  for (const D4bFastClass &c : m->fast) m->all_flat = m->all_flat && (c.kind == 1 || c.n_elem == 0);
+}
+
+void d4b_launch_basis_change(d4b_mesh *m, const double *in, double *out, bool to_gauss) {
+  for (const D4bFastClass &c : m->fast) {
+#define D4B_CASE(n) case n: launch_basis_change<n>(m, c, in, out, to_gauss); break;
+    switch (c.deg + 1) {
+      D4B_CASE(2) D4B_CASE(3) D4B_CASE(4) D4B_CASE(5) D4B_CASE(6) D4B_CASE(7) D4B_CASE(8)
+      default: D4B_ABORT("fast path: unsupported degree %d", c.deg);
+    }
+#undef D4B_CASE
+  }
 }
 
 namespace {

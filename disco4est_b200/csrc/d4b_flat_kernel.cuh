@@ -71,9 +71,9 @@ struct FlatCfg {
   static constexpr int kMinBlocks[9] = D4B_FLAT_MINB;   // resident blocks per SM the register budget is cut for
   static constexpr int THREADS = kThreads[N];
   static constexpr int EPB = THREADS / NN;
-  // V0,V1,V2 + per-thread face results [6][2][NN] + 6 face metas (2 doubles each)
+  // V0,V1,V2 + per-thread face results [6][2][NN] + 6 face metas (2 doubles each) + per-thread energy sums [NN]
   static constexpr int VS = VSize<N>::value;
-  static constexpr int SH_PER_ELEM = 3 * VS + 12 * NN + 12 + VLay<N>::PAD;
+  static constexpr int SH_PER_ELEM = 3 * VS + 13 * NN + 12 + VLay<N>::PAD;
   static constexpr int MIN_BLOCKS = kMinBlocks[N];
 };
 
@@ -154,7 +154,9 @@ __device__ __forceinline__ void flat_face(const FlatArgs &a, const FastTab &T, c
 
 // CG: every element of the class is affine (J and d(rst)/d(xyz) constant over the element, exact test at
 // set-up): the six metric components are one number each per element, times the Gauss weights
-template <int N, bool MASS, bool CG = false>
+// HAT: the smoother recurrence carried in the Gauss basis (D4bEpilogue mode 3): back-transform with B = I I^T,
+// rhs / p / the updated iterate are Gauss-basis vectors, the new uh goes to epi.uh_out (neighbours still read a.uh)
+template <int N, bool MASS, bool CG = false, bool HAT = false>
 __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) flat_apply_kernel(FlatArgs a) {
   using C = FlatCfg<N>;
   constexpr int NN = C::NN, N3 = C::N3;
@@ -169,6 +171,8 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) f
   double *V1 = V0 + C::VS, *V2 = V1 + C::VS;
   double *FB = V2 + C::VS;                                // [6][2][NN], thread-private columns
   FaceMeta *META = reinterpret_cast<FaceMeta *>(FB + 12 * NN);
+  double *ACC = FB + 12 * NN + 12;                        // [NN] thread-private: u . A u in its energy form
+  const bool dot = a.epi.dot_part != nullptr;
   const int64_t ns = active ? a.nodal_stride[a.elem[ei]] : 0;
   const double wxy = T.w[lx] * T.w[ly];
   double gt[N];
@@ -183,11 +187,11 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) f
   }
   // fused smoother: its three operand streams are only touched by the very last
   // phase; have them in L2 by then
-  if (active && a.epi.mode == 1 && a.prefetch) {
+  if (active && (a.epi.mode == 1 || HAT) && a.prefetch) {
     for (int off = lt * 16; off < N3; off += NN * 16) {
       l2_prefetch_line(a.epi.rhs + ns + off);
       l2_prefetch_line(a.epi.p + ns + off);
-      l2_prefetch_line(a.epi.u + ns + off);
+      if (!HAT) l2_prefetch_line(a.epi.u + ns + off);
     }
   }
   // ---- T-orientation (a,b) = (lx,ly), line along c ----
@@ -216,12 +220,16 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) f
   }
   block_sync<C::THREADS>();
   if (active) {
+    // the lifted face term tested with the element's own polynomial: sum_c uh_c (e_c ve + d_c vd) = tr ve + dn vd
+    double dacc = 0.;
     {   // faces 4/5 (normal c), face point (a,b)
       double ve, vd;
       flat_face<N>(a, T, META[4], ns, lx, ly, tr4, dn4, wxy, ve, vd);
       FB[(4 * 2 + 0) * NN + lt] = ve; FB[(4 * 2 + 1) * NN + lt] = vd;
+      if (dot) dacc += tr4 * ve + dn4 * vd;
       flat_face<N>(a, T, META[5], ns, lx, ly, tr5, dn5, wxy, ve, vd);
       FB[(5 * 2 + 0) * NN + lt] = ve; FB[(5 * 2 + 1) * NN + lt] = vd;
+      if (dot) dacc += tr5 * ve + dn5 * vd;
     }
     {   // S-orientation: (a,c) = (lx,ly), line along b: gradient, faces 2/3
       double uh[N];
@@ -243,8 +251,10 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) f
       double ve, vd;
       flat_face<N>(a, T, META[2], ns, lx, ly, t2, n2, wxy, ve, vd);
       FB[(2 * 2 + 0) * NN + lt] = ve; FB[(2 * 2 + 1) * NN + lt] = vd;
+      if (dot) dacc += t2 * ve + n2 * vd;
       flat_face<N>(a, T, META[3], ns, lx, ly, t3, n3, wxy, ve, vd);
       FB[(3 * 2 + 0) * NN + lt] = ve; FB[(3 * 2 + 1) * NN + lt] = vd;
+      if (dot) dacc += t3 * ve + n3 * vd;
     }
     {   // R-orientation: (b,c) = (lx,ly), line along a: gradient, faces 0/1
       double uh[N];
@@ -266,11 +276,15 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) f
       double ve, vd;
       flat_face<N>(a, T, META[0], ns, lx, ly, t0, n0, wxy, ve, vd);
       FB[(0 * 2 + 0) * NN + lt] = ve; FB[(0 * 2 + 1) * NN + lt] = vd;
+      if (dot) dacc += t0 * ve + n0 * vd;
       flat_face<N>(a, T, META[1], ns, lx, ly, t1, n1, wxy, ve, vd);
       FB[(1 * 2 + 0) * NN + lt] = ve; FB[(1 * 2 + 1) * NN + lt] = vd;
+      if (dot) dacc += t1 * ve + n1 * vd;
     }
+    if (dot) ACC[lt] = dacc;
   }
   block_sync<C::THREADS>();
+  double dsum = 0.;   // this thread's share of u . A u (dot): volume energy grad . F (+ mass, + irregular faces) + faces
   if (active) {   // T-orientation: metric, Dg^T along c + faces 4/5; V0 becomes the residual
     double ft[N];
     const double *G = CG ? nullptr : a.FG + (size_t)ei * (6 * N3) + lt;
@@ -291,9 +305,12 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) f
         G00 = G[0 * N3 + NN * c]; G01 = G[1 * N3 + NN * c]; G02 = G[2 * N3 + NN * c];
         G11 = G[3 * N3 + NN * c]; G12 = G[4 * N3 + NN * c]; G22 = G[5 * N3 + NN * c];
       }
-      V1[idx] = G00 * gr + G01 * gs + G02 * gt[c];
-      V2[idx] = G01 * gr + G11 * gs + G12 * gt[c];
+      const double Fr = G00 * gr + G01 * gs + G02 * gt[c];
+      const double Fs = G01 * gr + G11 * gs + G12 * gt[c];
+      V1[idx] = Fr;
+      V2[idx] = Fs;
       ft[c] = G02 * gr + G12 * gs + G22 * gt[c];
+      if (dot) dsum += gr * Fr + gs * Fs + gt[c] * ft[c];
     }
     const double ve0 = FB[(4 * 2 + 0) * NN + lt], vd0 = FB[(4 * 2 + 1) * NN + lt];
     const double ve1 = FB[(5 * 2 + 0) * NN + lt], vd1 = FB[(5 * 2 + 1) * NN + lt];
@@ -303,12 +320,25 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) f
 #pragma unroll
     for (int c = 0; c < N; ++c) {
       double s = T.e[0][c] * ve0 + T.d[0][c] * vd0 + T.e[1][c] * ve1 + T.d[1][c] * vd1;
-      if (MASS) s += Wd[NN * c] * V0[vix<N>(lx, ly, c)];
-      if (xtr) s += xtr[NN * c];
+      if (MASS) {
+        const double uc = V0[vix<N>(lx, ly, c)], wu = Wd[NN * c] * uc;
+        s += wu;
+        if (dot) dsum += wu * uc;
+      }
+      if (xtr) {
+        s += xtr[NN * c];
+        if (dot) dsum += xtr[NN * c] * V0[vix<N>(lx, ly, c)];
+      }
 #pragma unroll
       for (int i = 0; i < N; ++i) s += T.Dg[i][c] * ft[i];
       V0[vix<N>(lx, ly, c)] = s;
     }
+    if (dot) dsum += ACC[lt];
+  }
+  if (dot) {   // one partial sum per warp, fixed order (deterministic)
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) dsum += __shfl_xor_sync(0xffffffffu, dsum, o);
+    if ((threadIdx.x & 31) == 0) a.epi.dot_part[(size_t)blockIdx.x * (C::THREADS / 32) + (threadIdx.x >> 5)] = dsum;
   }
   block_sync<C::THREADS>();
   if (active) {   // S-orientation: + Dg^T F_s + faces 2/3
@@ -343,7 +373,7 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) f
     for (int i2 = 0; i2 < N; ++i2) {
       double s = 0.;
 #pragma unroll
-      for (int i = 0; i < N; ++i) s += T.I[i][i2] * tot[i];
+      for (int i = 0; i < N; ++i) s += (HAT ? T.B[i][i2] : T.I[i][i2]) * tot[i];
       V0[vix<N>(i2, lx, ly)] = s;
     }
   }
@@ -356,7 +386,7 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) f
     for (int i2 = 0; i2 < N; ++i2) {
       double s = 0.;
 #pragma unroll
-      for (int i = 0; i < N; ++i) s += T.I[i][i2] * l[i];
+      for (int i = 0; i < N; ++i) s += (HAT ? T.B[i][i2] : T.I[i][i2]) * l[i];
       V0[vix<N>(lx, i2, ly)] = s;
     }
   }
@@ -370,8 +400,16 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) f
     for (int c = 0; c < N; ++c) {
       double s = 0.;
 #pragma unroll
-      for (int i = 0; i < N; ++i) s += T.I[i][c] * l[i];
-      store_result(a.epi, ec, a.Au, ns + lt + NN * c, s);
+      for (int i = 0; i < N; ++i) s += (HAT ? T.B[i][c] : T.I[i][c]) * l[i];
+      if (HAT) {
+        const int64_t i = ns + lt + NN * c;
+        const double r = (a.epi.rhs[i] - s) * ec.alpha;
+        const double pn = r + ec.beta * a.epi.p[i];
+        a.epi.p[i] = pn;
+        a.epi.uh_out[i] = a.uh[i] + pn;
+      } else {
+        store_result(a.epi, ec, a.Au, ns + lt + NN * c, s);
+      }
     }
   }
 }

@@ -73,6 +73,9 @@ struct D4bFastClass {
 //   mode 1: r = alpha (rhs[i] - s); p[i] = r + beta p[i]; u[i] += p[i]   (u is updated in place:
 //           the kernels read the Gauss-collocated copy uhat, never u)
 //   mode 2: Au[i] = rhs[i] - s
+//   mode 3 (tangential-free kernel, HAT instantiation): the same recurrence as mode 1 carried in the Gauss basis --
+//           s = (B x B x B) rh with B = I I^T, rhs / p are Gauss-basis vectors, uh_out[i] = uh[i] + p[i] -- so that
+//           the next sweep needs no interpolation kernel (d4b_solver.cu, cheby_enqueue)
 struct D4bEpilogue {
   int mode = 0;
   const double *rhs = nullptr;
@@ -80,6 +83,12 @@ struct D4bEpilogue {
   double alpha = 0., beta = 0.;
   const double *coef = nullptr;   // mode 1: {alpha, beta} in device memory instead of the two arguments
   const double *add = nullptr;    // every mode: s += add[i] first (the coarse-level Galerkin mass term, d4b_mg.cu)
+  double *uh_out = nullptr;       // mode 3
+  // u . A u of this apply in its energy form, sum over quadrature points of grad . F + face terms (tangential-free
+  // kernel): one partial sum per warp, launch after launch from dot_part[*dot_count] (d4b_launch_fast advances it)
+  double *dot_part = nullptr;
+  // interpolation kernel of this apply: the input vector is first updated, d = xpby_r + (*xpby_num / *xpby_den) d
+  const double *xpby_r = nullptr, *xpby_num = nullptr, *xpby_den = nullptr;
 };
 
 // halo exchange with one neighbour rank; offsets / counts in doubles
@@ -203,6 +212,11 @@ struct d4b_mesh {
   int64_t n_face_shared = 0, n_face_split = 0;
   int generic_smem = 0;
   D4bEpilogue epi;                     // epilogue of the next fast-kernel launches
+  int64_t dot_count = 0;               // partial sums the launches of the current apply have claimed in epi.dot_part
+  double *d_dot_part = nullptr;        // [dot_capacity]
+  int64_t dot_capacity = 0;
+  double *d_uhat_alt = nullptr, *d_rhs_hat = nullptr;   // Gauss-resident smoother: second copy of uhat, (I x I x I) rhs
+  bool all_flat = false;               // every element runs in the tangential-free kernel
 };
 
 template <typename T>
@@ -233,6 +247,8 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *desc, const std::vector<
 void d4b_launch_fast(d4b_mesh *m, const double *d_u, double *d_Au, int part);
 // one-rank meshes: what = 0: uh of the elements [e0, e1); what = 1: apply on the elements [e0, e1)
 void d4b_launch_fast_range(d4b_mesh *m, const double *d_u, double *d_Au, int what, int e0, int e1);
+// out = (I x I x I) in (to_gauss) or its inverse, over every collocated element
+void d4b_launch_basis_change(d4b_mesh *m, const double *in, double *out, bool to_gauss);
 
 // One smoothing of a multigrid level on device vectors (cg_eigs estimate when asked,
 // Chebyshev sweeps, r = rhs - A u), enqueued without any host synchronisation; the estimate
@@ -256,9 +272,9 @@ void d4b_comm_allreduce_sum(d4b_mesh *m, double *d_x, int n);
 // peer-memory halo: collective set-up on first use (true when active), per-apply signal / wait
 bool d4b_comm_peer_ready(d4b_mesh *m);
 void d4b_comm_peer_begin(d4b_mesh *m);    // next epoch: points m->d_uhat at this apply's copy
-void d4b_comm_peer_signal(d4b_mesh *m);   // on m->comm_stream: tell the neighbours this rank's uhat is complete
+void d4b_comm_peer_signal(d4b_mesh *m, cudaStream_t st);   // tell the neighbours this rank's uhat is complete
 void d4b_comm_peer_teardown(d4b_mesh *m); // collective; before anything of the mesh is freed
-void d4b_comm_peer_wait(d4b_mesh *m);     // on m->comm_stream: until every neighbour has signalled this epoch
+void d4b_comm_peer_wait(d4b_mesh *m, cudaStream_t st);     // until every neighbour has signalled this epoch
 // d4b_fast.cu: ghost neighbours of the conforming classes addressed through d_ghost_off (offsets relative to uhat)
 void d4b_fast_patch_ghost_offsets(d4b_mesh *m, const int64_t *d_ghost_off);
 

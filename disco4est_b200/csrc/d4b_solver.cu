@@ -6,14 +6,15 @@
 //   ..._smoother_cheby_iterate_aux         src/Solver/d4est_solver_multigrid_smoother_cheby.c:81-176
 // Reductions are deterministic: fixed grid, fixed-shape tree, no atomics.
 #include <cmath>
+#include <algorithm>
 #include <cstdlib>
 #include <vector>
 #include "d4b_internal.h"
+#include "d4b_reduce_cfg.h"
 
 namespace {
 
-constexpr int kRedBlocks = 592;    // 4 x 148 SMs
-constexpr int kRedThreads = 256;
+constexpr int kRedBlocks = kD4bRedBlocks, kRedThreads = kD4bRedThreads;
 
 __global__ void __launch_bounds__(kRedThreads) dot_partial(const double *__restrict__ x,
                                                            const double *__restrict__ y, int64_t n,
@@ -42,6 +43,23 @@ __global__ void __launch_bounds__(1024) dot_final(const double *__restrict__ par
     __syncthreads();
   }
   if (threadIdx.x == 0) *out = sh[0];
+}
+
+// sum of n partial sums (the energy dot of the apply kernels): stage 1 of 2 for large n
+__global__ void __launch_bounds__(kRedThreads) sum_partial(const double *__restrict__ x, int64_t n,
+                                                           double *__restrict__ part) {
+  __shared__ double sh[kRedThreads];
+  int64_t chunk = (n + gridDim.x - 1) / gridDim.x;
+  int64_t lo = (int64_t)blockIdx.x * chunk, hi = lo + chunk < n ? lo + chunk : n;
+  double s = 0.;
+  for (int64_t i = lo + threadIdx.x; i < hi; i += kRedThreads) s += x[i];
+  sh[threadIdx.x] = s;
+  __syncthreads();
+  for (int w = kRedThreads / 2; w > 0; w >>= 1) {
+    if (threadIdx.x < w) sh[threadIdx.x] += sh[threadIdx.x + w];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) part[blockIdx.x] = sh[0];
 }
 
 __global__ void axpy_k(double a, const double *__restrict__ x, double *__restrict__ y, int64_t n) {
@@ -181,6 +199,9 @@ void dot_to(d4b_mesh *m, const double *x, const double *y, int64_t n, double *d_
 }
 
 // u += alpha d ; r -= alpha Ad with alpha = *delta / *dAd ; block partials of r.r
+// (six streams, 48 B per node: 6 blocks of 256 threads per SM and two independent nodes per thread and trip
+//  keep enough loads in flight; kUpdBlocks <= 1024 = what dot_final sums)
+constexpr int kUpdBlocks = 888;
 __global__ void __launch_bounds__(kRedThreads) cg_update_dot_k(const double *__restrict__ delta,
                                                                const double *__restrict__ dAd,
                                                                const double *__restrict__ d,
@@ -191,14 +212,26 @@ __global__ void __launch_bounds__(kRedThreads) cg_update_dot_k(const double *__r
   const double alpha = *delta / *dAd;
   int64_t chunk = (n + gridDim.x - 1) / gridDim.x;
   int64_t lo = (int64_t)blockIdx.x * chunk, hi = lo + chunk < n ? lo + chunk : n;
-  double s = 0.;
-  for (int64_t i = lo + threadIdx.x; i < hi; i += kRedThreads) {
+  double s0 = 0., s1 = 0.;
+  int64_t i = lo + threadIdx.x;
+  for (; i + kRedThreads < hi; i += 2 * kRedThreads) {
+    const int64_t j = i + kRedThreads;
+    const double di = d[i], dj = d[j], ai = Ad[i], aj = Ad[j], ui = u[i], uj = u[j], ri0 = r[i], rj0 = r[j];
+    u[i] = ui + alpha * di;
+    u[j] = uj + alpha * dj;
+    const double ri = ri0 - alpha * ai, rj = rj0 - alpha * aj;
+    r[i] = ri;
+    r[j] = rj;
+    s0 += ri * ri;
+    s1 += rj * rj;
+  }
+  if (i < hi) {
     u[i] += alpha * d[i];
     const double ri = r[i] - alpha * Ad[i];
     r[i] = ri;
-    s += ri * ri;
+    s0 += ri * ri;
   }
-  sh[threadIdx.x] = s;
+  sh[threadIdx.x] = s0 + s1;
   __syncthreads();
   for (int w = kRedThreads / 2; w > 0; w >>= 1) {
     if (threadIdx.x < w) sh[threadIdx.x] += sh[threadIdx.x + w];
@@ -227,9 +260,42 @@ __global__ void cheby_update_dev_k(const double *__restrict__ coef, const double
   }
 }
 
+// the partial sums epi.dot_part collected during the last apply -> one device scalar (all-reduced)
+void energy_dot_finish(d4b_mesh *m, double *d_out) {
+  const int64_t n = m->dot_count;
+  if (n <= 1024) {
+    dot_final<<<1, 1024, 0, m->stream>>>(m->d_dot_part, (int)n, d_out);
+  } else {
+    const int blocks = (int)std::min<int64_t>((n + 4 * kRedThreads - 1) / (4 * kRedThreads), 256);
+    sum_partial<<<blocks, kRedThreads, 0, m->stream>>>(m->d_dot_part, n, m->d_red);
+    dot_final<<<1, 1024, 0, m->stream>>>(m->d_red, blocks, d_out);
+  }
+  d4b_comm_allreduce_sum(m, d_out, 1);
+}
+
+void energy_dot_reserve(d4b_mesh *m) {
+  if (m->d_dot_part) return;
+  m->dot_capacity = 2 * (int64_t)m->n_local + 64;   // at most two warps per element, one launch tail per class and part
+  for (const auto &c : m->fast) m->dot_capacity += 8;
+  m->d_dot_part = d4b_dev_alloc<double>(m, (size_t)m->dot_capacity);
+}
+
+// D4B_FUSED_SOLVERS=0: cg_eigs and the smoother as separate apply + vector kernels
+bool fused_solvers_allowed(const d4b_mesh *m) {
+  const char *e = getenv("D4B_FUSED_SOLVERS");
+  return m->all_flat && !m->pre_apply && !(e && e[0] == '0');
+}
+
 // cg_eigs on device vectors, enqueued without a host round trip: kernel i reads
 // alpha_i = delta_i / (d.Ad)_i and beta_i = delta_{i+1} / delta_i from the slots earlier
 // reductions filled.  Leaves delta[0..imax], dAd[0..imax) in d_red.
+//
+// On meshes whose elements all run in the tangential-free kernel an iteration is three passes instead of six:
+//   interpolation kernel   d = r + beta d (written back), dh = (I x I x I) d
+//   apply kernel           Ad, and d.Ad in its energy form from the registers of the kernel (D4bEpilogue::dot_part)
+//   cg_update_dot_k        u += alpha d, r -= alpha Ad, r.r
+// (the same recurrences as d4est_solver_cg_eigs.c:181-257; d.Ad differs from the dot product of the two vectors
+//  in the last bits only).
 void cg_eigs_enqueue(d4b_mesh *m, double *du, const double *drhs, int imax, int use_zero_guess) {
   D4B_CHECK(imax >= 1 && imax <= kMaxCgIter, "cg_eigs: imax %d out of range", imax);
   const int64_t n = m->local_nodes;
@@ -242,21 +308,50 @@ void cg_eigs_enqueue(d4b_mesh *m, double *du, const double *drhs, int imax, int 
   double *Au = m->d_Au_stage, *d = work(m, 0), *r = work(m, 1);
   double *delta = m->d_red + kScalOff, *dAd = delta + kMaxCgIter + 1;
   const int g = grid_for(n);
+  const bool fused = fused_solvers_allowed(m);
+  // the packed halo (NCCL send/recv of nodal values) is taken from d before the interpolation kernel runs:
+  // the direction update can only ride on that kernel when no nodal values are sent
+  const bool fuse_xpby = fused && (m->mpisize == 1 || d4b_comm_peer_ready(m));
+  if (fused) energy_dot_reserve(m);
+  m->epi = D4bEpilogue();
   d4b_apply(m, du, Au);
   residual2_k<<<g, 256, 0, m->stream>>>(drhs, Au, r, d, n);
   dot_to(m, r, r, n, delta);
   for (int i = 0; i < imax; ++i) {
-    d4b_apply(m, d, Au);
-    dot_to(m, d, Au, n, dAd + i);
-    cg_update_dot_k<<<kRedBlocks, kRedThreads, 0, m->stream>>>(delta + i, dAd + i, d, Au, du, r, n, m->d_red);
-    dot_final<<<1, 1024, 0, m->stream>>>(m->d_red, kRedBlocks, delta + i + 1);
+    if (fused) {
+      m->epi = D4bEpilogue();
+      m->epi.dot_part = m->d_dot_part;
+      m->dot_count = 0;
+      if (i > 0) {
+        if (fuse_xpby) { m->epi.xpby_r = r; m->epi.xpby_num = delta + i; m->epi.xpby_den = delta + i - 1; }
+        else xpby_dev_k<<<g, 256, 0, m->stream>>>(r, delta + i, delta + i - 1, d, n);
+      }
+      d4b_apply_device(m, d, Au);
+      m->epi = D4bEpilogue();
+      energy_dot_finish(m, dAd + i);
+    } else {
+      d4b_apply(m, d, Au);
+      dot_to(m, d, Au, n, dAd + i);
+    }
+    cg_update_dot_k<<<kUpdBlocks, kRedThreads, 0, m->stream>>>(delta + i, dAd + i, d, Au, du, r, n, m->d_red);
+    dot_final<<<1, 1024, 0, m->stream>>>(m->d_red, kUpdBlocks, delta + i + 1);
     d4b_comm_allreduce_sum(m, delta + i + 1, 1);
-    xpby_dev_k<<<g, 256, 0, m->stream>>>(r, delta + i + 1, delta + i, d, n);
+    // (the reference also forms the next direction after its last iteration; nothing reads it)
+    if (!fused) xpby_dev_k<<<g, 256, 0, m->stream>>>(r, delta + i + 1, delta + i, d, n);
   }
 }
 
 // Chebyshev recurrence on device vectors.  Coefficients: host arrays (alpha/beta as kernel
 // arguments) or, when d_coef is given, pairs in device memory.
+//
+// Three forms, fastest applicable first:
+//  (a) Gauss-resident (one-rank meshes whose elements all run in the tangential-free kernel): the recurrence
+//      is carried in the Gauss basis, uh <- uh + ph, ph <- alpha (I3 rhs - (B x B x B) rh) + beta ph with B = I I^T,
+//      so a sweep is ONE kernel (no interpolation kernel, no nodal vectors); I3 rhs before the first sweep,
+//      u = I3^-1 uh after the last, and the closing residual apply starts from the uh already there.
+//      Same numbers as (b) up to round-off of the basis change.
+//  (b) the recurrence in the apply's epilogue on nodal vectors (every element in a fast kernel)
+//  (c) apply + one vector kernel
 void cheby_enqueue(d4b_mesh *m, double *du, const double *drhs, double *dr, int iter, const double *h_alpha,
                    const double *h_beta, const double *d_coef) {
   const int64_t n = m->local_nodes;
@@ -267,6 +362,34 @@ void cheby_enqueue(d4b_mesh *m, double *du, const double *drhs, double *dr, int 
   // (u updated in place, no Au vector); otherwise apply + one vector kernel
   const char *nf = getenv("D4B_NO_FUSED_CHEBY");
   const bool fused = m->n_generic == 0 && !m->fast.empty() && !(nf && nf[0] == '1');
+  const bool hat = fused && iter > 0 && m->mpisize == 1 && !m->d_W && fused_solvers_allowed(m);
+  if (hat) {
+    if (!m->d_uhat_alt) {
+      m->d_uhat_alt = d4b_dev_alloc<double>(m, (size_t)n);
+      m->d_rhs_hat = d4b_dev_alloc<double>(m, (size_t)n);
+    }
+    double *uh_own = m->d_uhat, *cur = m->d_uhat, *nxt = m->d_uhat_alt;
+    d4b_launch_basis_change(m, du, cur, true);
+    d4b_launch_basis_change(m, drhs, m->d_rhs_hat, true);
+    for (int i = 0; i < iter; ++i) {
+      m->epi = D4bEpilogue();
+      m->epi.mode = 3; m->epi.rhs = m->d_rhs_hat; m->epi.p = p; m->epi.uh_out = nxt;
+      if (d_coef) m->epi.coef = d_coef + 2 * i;
+      else { m->epi.alpha = h_alpha[i]; m->epi.beta = h_beta[i]; }
+      m->d_uhat = cur;
+      d4b_launch_fast(m, nullptr, nullptr, 1);   // the apply kernels only: uh is already there
+      std::swap(cur, nxt);
+    }
+    d4b_launch_basis_change(m, cur, du, false);
+    // r = rhs - A u from the uh of the last sweep
+    m->epi = D4bEpilogue();
+    m->epi.mode = 2; m->epi.rhs = drhs;
+    m->d_uhat = cur;
+    d4b_launch_fast(m, nullptr, dr, 1);
+    m->epi = D4bEpilogue();
+    m->d_uhat = uh_own;
+    return;
+  }
   for (int i = 0; i < iter; ++i) {
     if (fused) {
       m->epi = D4bEpilogue();

@@ -22,11 +22,12 @@
 #include <mutex>
 #include <cuda_runtime.h>
 #include "d4est_b200.h"
+#include "d4b_reduce_cfg.h"
 
 namespace {
 
-constexpr int kBlocks = 592;     // 4 x 148 SMs; must stay equal to kRedBlocks of d4b_solver.cu
-constexpr int kThreads = 256;
+constexpr int kBlocks = kD4bRedBlocks;     // the geometry of d4b_vec_dot (d4b_reduce_cfg.h)
+constexpr int kThreads = kD4bRedThreads;
 constexpr int kMaxDevices = 64;
 
 // The scratch.  In host code this name is only a stand-in for the symbol: its device address
@@ -121,6 +122,9 @@ extern "C" int32_t d4b_vec_dot_noalloc(const double *x, const double *y, int64_t
                 (const void *)y, (void *)out);
   cudaStream_t st = (cudaStream_t)cuda_stream;
   dot_partial_static<<<dim3(kBlocks, nvec), kThreads, 0, st>>>(x, y, n, scratch);
+  const cudaError_t e1 = cudaGetLastError();
+  if (e1 != cudaSuccess)   // nothing else has been enqueued
+    return fail(err, err_len, D4B_NOALLOC_E_CUDA, "d4b_vec_dot_noalloc: kernel launch: %s", cudaGetErrorString(e1));
   dot_final_static<<<nvec, 1024, 0, st>>>(scratch, out);
   const cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess)

@@ -369,7 +369,9 @@ void   d4b_vec_scale(d4b_mesh_t *mesh, double a, double *x, int64_t n);
  * that device current; nvec = 0 does the set-up and launches nothing -- call it once before
  * a stream capture.
  * Returns D4B_NOALLOC_OK or an error code; never aborts.  On error a message is written to
- * err (err_len bytes, NUL-terminated; err may be NULL) and nothing has been launched.        */
+ * err (err_len bytes, NUL-terminated; err may be NULL); for E_ARG / E_TOO_LARGE / a failed
+ * set-up nothing has been launched, E_CUDA reports a failed kernel launch (`out` is then
+ * undefined).                                                                                */
 #define D4B_DOT_NOALLOC_MAX_VECS 64
 #define D4B_NOALLOC_OK           0
 #define D4B_NOALLOC_E_ARG        1   /* negative size or NULL pointer             */

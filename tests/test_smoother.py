@@ -106,3 +106,38 @@ def test_fused_smoother_on_hp_meshes(golden, case, split, monkeypatch):
         out[fused] = (u, r)
         assert rel(u, u_ref) < 1e-11 and rel(r, r_ref) < 1e-10
     assert rel(out["1"][0], out["0"][0]) < 1e-13
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("p", [1, 2, 3, 4, 5, 6, 7])
+def test_fused_solvers_on_bricks(p, monkeypatch):
+    """meshes whose elements all run in the tangential-free kernel: cg_eigs with d.Ad taken from the apply
+    kernel (energy form) and the direction update riding on the interpolation kernel, and the Chebyshev
+    recurrence carried in the Gauss basis (one kernel per sweep) -- against the unfused sequence of apply +
+    vector kernels (D4B_FUSED_SOLVERS=0) and the restatement on top of the oracle"""
+    from disco4est_b200 import Mesh
+    from disco4est_b200.brick import brick_desc
+
+    A = brick_desc(1 if p > 4 else 2, p)
+    orc = Oracle(A)
+    rng = np.random.default_rng(80 + p)
+    rhs, u0 = rng.standard_normal(orc.n), rng.standard_normal(orc.n)
+    lmax_ref, u1_ref = cg_eigs(orc.apply, u0.copy(), rhs, 8, use_new=0)
+    u_ref, r_ref = cheby(orc.apply, u0.copy(), rhs, 6, lmax_ref / 30.0, lmax_ref)
+    out = {}
+    for fused in ("0", "1"):
+        monkeypatch.setenv("D4B_FUSED_SOLVERS", fused)
+        m = Mesh(A)
+        assert m.flat_elements() == int(A["n_local"])
+        u = u0.copy()
+        lmax = m.cg_eigs(u, rhs, 8, use_new=0)
+        assert abs(lmax - lmax_ref) <= 1e-10 * lmax_ref
+        assert rel(u, u1_ref) < 1e-10
+        us, r = u0.copy(), np.zeros_like(u0)
+        m.cheby_smooth(us, rhs, r, 6, lmax_ref / 30.0, lmax_ref)
+        assert rel(us, u_ref) < 1e-11 and rel(r, r_ref) < 1e-10
+        m.close()
+        out[fused] = (lmax, u, us, r)
+    assert abs(out["1"][0] - out["0"][0]) <= 1e-12 * out["0"][0]
+    assert rel(out["1"][1], out["0"][1]) < 1e-12 and rel(out["1"][2], out["0"][2]) < 1e-12
+    assert rel(out["1"][3], out["0"][3]) < 1e-11
