@@ -561,7 +561,8 @@ void launch_flat(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, 
   size_t smem = (size_t)C::EPB * C::SH_PER_ELEM * sizeof(double);
   a.W = m->d_W; a.quad_stride = m->d_quad_stride;
   a.has_extra = cls.d_has_extra; a.extra = m->d_extra;
-  static bool configured = false;
+  static bool configured_dev[kD4bMaxDevices] = {};   // the attribute is per device
+  bool &configured = configured_dev[m->device];
   if (!configured) {
     D4B_CUDA(cudaFuncSetAttribute(flat_apply_kernel<N, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     D4B_CUDA(cudaFuncSetAttribute(flat_apply_kernel<N, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -569,18 +570,25 @@ void launch_flat(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, 
     D4B_CUDA(cudaFuncSetAttribute(flat_apply_kernel<N, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     D4B_CUDA(cudaFuncSetAttribute(flat_apply_kernel<N, false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     D4B_CUDA(cudaFuncSetAttribute(flat_apply_kernel<N, false, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    D4B_CUDA(cudaFuncSetAttribute(flat_apply_kernel<N, false, false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    D4B_CUDA(cudaFuncSetAttribute(flat_apply_kernel<N, false, true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = true;
   }
   static const int prefetch = getenv("D4B_PREFETCH") ? atoi(getenv("D4B_PREFETCH")) : 2;
   a.prefetch = prefetch;
   int grid = (last - first + C::EPB - 1) / C::EPB;
+  const int groups = grid;
   if (m->epi.dot_part) {   // this launch's partial sums follow those of the apply's earlier launches
     a.epi.dot_part = m->epi.dot_part + m->dot_count;
-    m->dot_count += (int64_t)grid * (C::THREADS / 32);
+    m->dot_count += (int64_t)groups * (C::THREADS / 32);
     D4B_CHECK(m->dot_count <= m->dot_capacity, "energy dot: %lld partial sums, room for %lld", (long long)m->dot_count,
               (long long)m->dot_capacity);
   }
-  if (m->epi.mode == 3) {
+  if (m->epi.dot_part) {
+    D4B_CHECK(!m->d_W && m->epi.mode != 3, "energy dot: not with a mass term or the Gauss-resident smoother");
+    if (cls.d_FGc) flat_apply_kernel<N, false, true, false, true><<<grid, C::THREADS, smem, m->stream>>>(a);
+    else flat_apply_kernel<N, false, false, false, true><<<grid, C::THREADS, smem, m->stream>>>(a);
+  } else if (m->epi.mode == 3) {
     D4B_CHECK(!m->d_W && m->epi.uh_out && m->epi.rhs && m->epi.p, "Gauss-resident smoother: bad epilogue");
     if (cls.d_FGc) flat_apply_kernel<N, false, true, true><<<grid, C::THREADS, smem, m->stream>>>(a);
     else flat_apply_kernel<N, false, false, true><<<grid, C::THREADS, smem, m->stream>>>(a);
@@ -648,8 +656,9 @@ void launch_hp(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, in
   int warps = (int)((200 * 1024) / per_warp);
   warps = warps < 1 ? 1 : warps > 4 ? 4 : warps;
   const size_t smem = per_warp * warps;
-  static size_t configured = 48 * 1024;
-  if (smem > configured) {
+  static size_t configured_dev[kD4bMaxDevices] = {};   // per device; 0 = the 48 KB default
+  size_t &configured = configured_dev[m->device];
+  if (smem > 48 * 1024 && smem > configured) {
     D4B_CUDA(cudaFuncSetAttribute(hp_apply_kernel<N, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     D4B_CUDA(cudaFuncSetAttribute(hp_apply_kernel<N, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = smem;
@@ -657,8 +666,9 @@ void launch_hp(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, in
   const int grid = (last - first + warps - 1) / warps;
   a.face_mask = cls.d_face_mask; a.extra = m->d_extra;
   if (face_only) {
-    static size_t configured_f = 48 * 1024;
-    if (smem > configured_f) {
+    static size_t configured_f_dev[kD4bMaxDevices] = {};
+    size_t &configured_f = configured_f_dev[m->device];
+    if (smem > 48 * 1024 && smem > configured_f) {
       D4B_CUDA(cudaFuncSetAttribute(hp_apply_kernel<N, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
       configured_f = smem;
     }
@@ -746,7 +756,8 @@ void launch_fast(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, 
   size_t smem = (size_t)C::EPB * C::SH_PER_ELEM * sizeof(double);
   a.W = m->d_W; a.quad_stride = m->d_quad_stride;
   a.has_extra = cls.d_has_extra; a.extra = m->d_extra;
-  static bool configured = false;
+  static bool configured_dev[kD4bMaxDevices] = {};
+  bool &configured = configured_dev[m->device];
   if (!configured) {
     D4B_CUDA(cudaFuncSetAttribute(fast_apply_kernel<N, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     D4B_CUDA(cudaFuncSetAttribute(fast_apply_kernel<N, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

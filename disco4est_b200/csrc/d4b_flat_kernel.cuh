@@ -71,9 +71,10 @@ struct FlatCfg {
   static constexpr int kMinBlocks[9] = D4B_FLAT_MINB;   // resident blocks per SM the register budget is cut for
   static constexpr int THREADS = kThreads[N];
   static constexpr int EPB = THREADS / NN;
-  // V0,V1,V2 + per-thread face results [6][2][NN] + 6 face metas (2 doubles each) + per-thread energy sums [NN]
+  // V0,V1,V2 + per-thread face results [6][2][NN] + 6 face metas (2 doubles each)
+  // (the element stride is part of the tuned layouts of VLay: do not grow it)
   static constexpr int VS = VSize<N>::value;
-  static constexpr int SH_PER_ELEM = 3 * VS + 13 * NN + 12 + VLay<N>::PAD;
+  static constexpr int SH_PER_ELEM = 3 * VS + 12 * NN + 12 + VLay<N>::PAD;
   static constexpr int MIN_BLOCKS = kMinBlocks[N];
 };
 
@@ -108,42 +109,20 @@ __device__ __forceinline__ void flat_face(const FlatArgs &a, const FastTab &T, c
   const int stride = (ndp == 0) ? 1 : ((ndp == 1) ? N : NN);
   const int base = (ndp == 0) ? (N * col + NN * row) : ((ndp == 1) ? (col + NN * row) : (col + N * row));
   double v[N];
-#ifdef D4B_FLAT_VECTOR_LINES
-  // a line along the neighbour's fastest index is N contiguous doubles: 16-byte loads
-  // quarter the number of L1 requests (each 8-byte lane load is its own 32-byte sector)
+  double trp = 0., dnp = 0.;
   const double *p0 = a.uh + (interior ? fm.nbr : ns) + base;
-  if (N % 2 == 0 && ndp == 0) {
-    const double2 *q = reinterpret_cast<const double2 *>(p0);
+  {
+    const double *p = p0 + (sp ? (N - 1) * stride : 0);
+    const int step = sp ? -stride : stride;
 #pragma unroll
-    for (int l = 0; l < N / 2; ++l) {
-      const double2 t = q[l];
-      v[2 * l] = t.x; v[2 * l + 1] = t.y;
+    for (int l = 0; l < N; ++l) v[l] = p[l * step];
+#pragma unroll
+    for (int l = 0; l < N; ++l) {
+      trp += T.e[0][l] * v[l];
+      dnp += T.d[0][l] * v[l];
     }
-  } else {
-#pragma unroll
-    for (int l = 0; l < N; ++l) v[l] = p0[l * stride];
+    dnp = sp ? -dnp : dnp;
   }
-  double trp = 0., dnp = 0.;
-  if (sp) {
-#pragma unroll
-    for (int l = 0; l < N; ++l) { trp += T.e[1][l] * v[l]; dnp += T.d[1][l] * v[l]; }
-  } else {
-#pragma unroll
-    for (int l = 0; l < N; ++l) { trp += T.e[0][l] * v[l]; dnp += T.d[0][l] * v[l]; }
-  }
-#else
-  const double *p = a.uh + (interior ? fm.nbr : ns) + base + (sp ? (N - 1) * stride : 0);
-  const int step = sp ? -stride : stride;
-#pragma unroll
-  for (int l = 0; l < N; ++l) v[l] = p[l * step];
-  double trp = 0., dnp = 0.;
-#pragma unroll
-  for (int l = 0; l < N; ++l) {
-    trp += T.e[0][l] * v[l];
-    dnp += T.d[0][l] * v[l];
-  }
-  dnp = sp ? -dnp : dnp;
-#endif
   const double Amn = own ? r0 : -r1;
   const double Apn = own ? r1 : -r0;
   const double du = trm - (interior ? trp : r1);   // boundary: Dirichlet data in the A_p slot
@@ -156,7 +135,8 @@ __device__ __forceinline__ void flat_face(const FlatArgs &a, const FastTab &T, c
 // set-up): the six metric components are one number each per element, times the Gauss weights
 // HAT: the smoother recurrence carried in the Gauss basis (D4bEpilogue mode 3): back-transform with B = I I^T,
 // rhs / p / the updated iterate are Gauss-basis vectors, the new uh goes to epi.uh_out (neighbours still read a.uh)
-template <int N, bool MASS, bool CG = false, bool HAT = false>
+// DOT: u . A u of the launch in its energy form, one partial sum per warp in epi.dot_part (cg_eigs, d4b_solver.cu)
+template <int N, bool MASS, bool CG = false, bool HAT = false, bool DOT = false>
 __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) flat_apply_kernel(FlatArgs a) {
   using C = FlatCfg<N>;
   constexpr int NN = C::NN, N3 = C::N3;
@@ -165,14 +145,16 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) f
   const int slot = threadIdx.x / NN;
   const int lt = threadIdx.x % NN;
   const int lx = lt % N, ly = lt / N;
-  const int ei = a.first + blockIdx.x * C::EPB + slot;
+  {
+  const int blk = blockIdx.x;
+  const int ei = a.first + blk * C::EPB + slot;
   const bool active = (slot < C::EPB) && (ei < a.n_elem);
   double *V0 = smem + (size_t)(slot < C::EPB ? slot : 0) * C::SH_PER_ELEM;
   double *V1 = V0 + C::VS, *V2 = V1 + C::VS;
   double *FB = V2 + C::VS;                                // [6][2][NN], thread-private columns
   FaceMeta *META = reinterpret_cast<FaceMeta *>(FB + 12 * NN);
-  double *ACC = FB + 12 * NN + 12;                        // [NN] thread-private: u . A u in its energy form
-  const bool dot = a.epi.dot_part != nullptr;
+  constexpr bool dot = DOT;
+  double dsum = 0.;   // dot: this thread's share of u . A u in its energy form, grad . F (+ mass, irregular faces) + faces
   const int64_t ns = active ? a.nodal_stride[a.elem[ei]] : 0;
   const double wxy = T.w[lx] * T.w[ly];
   double gt[N];
@@ -221,15 +203,14 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) f
   block_sync<C::THREADS>();
   if (active) {
     // the lifted face term tested with the element's own polynomial: sum_c uh_c (e_c ve + d_c vd) = tr ve + dn vd
-    double dacc = 0.;
     {   // faces 4/5 (normal c), face point (a,b)
       double ve, vd;
       flat_face<N>(a, T, META[4], ns, lx, ly, tr4, dn4, wxy, ve, vd);
       FB[(4 * 2 + 0) * NN + lt] = ve; FB[(4 * 2 + 1) * NN + lt] = vd;
-      if (dot) dacc += tr4 * ve + dn4 * vd;
+      if (dot) dsum += tr4 * ve + dn4 * vd;
       flat_face<N>(a, T, META[5], ns, lx, ly, tr5, dn5, wxy, ve, vd);
       FB[(5 * 2 + 0) * NN + lt] = ve; FB[(5 * 2 + 1) * NN + lt] = vd;
-      if (dot) dacc += tr5 * ve + dn5 * vd;
+      if (dot) dsum += tr5 * ve + dn5 * vd;
     }
     {   // S-orientation: (a,c) = (lx,ly), line along b: gradient, faces 2/3
       double uh[N];
@@ -251,10 +232,10 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) f
       double ve, vd;
       flat_face<N>(a, T, META[2], ns, lx, ly, t2, n2, wxy, ve, vd);
       FB[(2 * 2 + 0) * NN + lt] = ve; FB[(2 * 2 + 1) * NN + lt] = vd;
-      if (dot) dacc += t2 * ve + n2 * vd;
+      if (dot) dsum += t2 * ve + n2 * vd;
       flat_face<N>(a, T, META[3], ns, lx, ly, t3, n3, wxy, ve, vd);
       FB[(3 * 2 + 0) * NN + lt] = ve; FB[(3 * 2 + 1) * NN + lt] = vd;
-      if (dot) dacc += t3 * ve + n3 * vd;
+      if (dot) dsum += t3 * ve + n3 * vd;
     }
     {   // R-orientation: (b,c) = (lx,ly), line along a: gradient, faces 0/1
       double uh[N];
@@ -276,15 +257,13 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) f
       double ve, vd;
       flat_face<N>(a, T, META[0], ns, lx, ly, t0, n0, wxy, ve, vd);
       FB[(0 * 2 + 0) * NN + lt] = ve; FB[(0 * 2 + 1) * NN + lt] = vd;
-      if (dot) dacc += t0 * ve + n0 * vd;
+      if (dot) dsum += t0 * ve + n0 * vd;
       flat_face<N>(a, T, META[1], ns, lx, ly, t1, n1, wxy, ve, vd);
       FB[(1 * 2 + 0) * NN + lt] = ve; FB[(1 * 2 + 1) * NN + lt] = vd;
-      if (dot) dacc += t1 * ve + n1 * vd;
+      if (dot) dsum += t1 * ve + n1 * vd;
     }
-    if (dot) ACC[lt] = dacc;
   }
   block_sync<C::THREADS>();
-  double dsum = 0.;   // this thread's share of u . A u (dot): volume energy grad . F (+ mass, + irregular faces) + faces
   if (active) {   // T-orientation: metric, Dg^T along c + faces 4/5; V0 becomes the residual
     double ft[N];
     const double *G = CG ? nullptr : a.FG + (size_t)ei * (6 * N3) + lt;
@@ -333,12 +312,11 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) f
       for (int i = 0; i < N; ++i) s += T.Dg[i][c] * ft[i];
       V0[vix<N>(lx, ly, c)] = s;
     }
-    if (dot) dsum += ACC[lt];
   }
   if (dot) {   // one partial sum per warp, fixed order (deterministic)
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) dsum += __shfl_xor_sync(0xffffffffu, dsum, o);
-    if ((threadIdx.x & 31) == 0) a.epi.dot_part[(size_t)blockIdx.x * (C::THREADS / 32) + (threadIdx.x >> 5)] = dsum;
+    if ((threadIdx.x & 31) == 0) a.epi.dot_part[(size_t)blk * (C::THREADS / 32) + (threadIdx.x >> 5)] = dsum;
   }
   block_sync<C::THREADS>();
   if (active) {   // S-orientation: + Dg^T F_s + faces 2/3
@@ -412,4 +390,5 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) f
       }
     }
   }
+  }   // element group
 }

@@ -588,7 +588,7 @@ void d4b_launch_quad_op(d4b_mesh *m, int mode, const double *d_in, const double 
   D4B_CUDA(cudaGetLastError());
 }
 
-void d4b_generic_configure(int smem_bytes);
+void d4b_generic_configure(int device, int smem_bytes);
 
 void d4b_launch_generic(d4b_mesh *m, const double *d_u, double *d_Au, int stiffness_only) {
   bool force_all = (stiffness_only != 0) || (m->fast.empty());
@@ -618,7 +618,7 @@ void d4b_launch_generic(d4b_mesh *m, const double *d_u, double *d_Au, int stiffn
   int warps = (200 * 1024) / per_warp;
   warps = warps < 1 ? 1 : warps > kMaxWarps ? kMaxWarps : warps;
   a.smem_doubles = per_warp / (int)sizeof(double);
-  d4b_generic_configure(per_warp * warps);
+  d4b_generic_configure(m->device, per_warp * warps);
   generic_apply_kernel<<<(n_elem + warps - 1) / warps, 32 * warps, (size_t)per_warp * warps, m->stream>>>(a);
   D4B_CUDA(cudaGetLastError());
 }
@@ -649,8 +649,9 @@ void d4b_launch_estimator(d4b_mesh *m, const double *d_u, const double *d_r, con
   int warps = (200 * 1024) / per_warp;
   warps = warps < 1 ? 1 : warps > kMaxWarps ? kMaxWarps : warps;
   a.smem_doubles = per_warp / (int)sizeof(double);
-  static int configured = 48 * 1024;
-  if (per_warp * warps > configured) {
+  static int configured_dev[kD4bMaxDevices] = {};   // per device; 0 = the 48 KB default
+  int &configured = configured_dev[m->device];
+  if (per_warp * warps > 48 * 1024 && per_warp * warps > configured) {
     D4B_CUDA(cudaFuncSetAttribute(estimator_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, per_warp * warps));
     configured = per_warp * warps;
   }
@@ -669,10 +670,11 @@ int d4b_generic_smem_bytes(int maxN, int maxNq) {
   return (int)(d * sizeof(double));   // per warp (= per element in flight)
 }
 
-void d4b_generic_configure(int smem_bytes) {
-  // the attribute is per function, not per mesh: only ever raise it
-  static int configured = 48 * 1024;
-  if (smem_bytes <= configured) return;
+void d4b_generic_configure(int device, int smem_bytes) {
+  // the attribute is per function and device, not per mesh: only ever raise it
+  static int configured_dev[kD4bMaxDevices] = {};
+  int &configured = configured_dev[device];
+  if (smem_bytes <= 48 * 1024 || smem_bytes <= configured) return;
   D4B_CUDA(cudaFuncSetAttribute(generic_apply_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 smem_bytes));
   configured = smem_bytes;

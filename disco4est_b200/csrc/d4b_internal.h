@@ -13,6 +13,7 @@
 
 #define D4B_MAXN 8     // max LGL nodes per direction (deg <= 7)
 #define D4B_MAXNQ 12   // max Gauss nodes per direction handled by the generic kernel
+constexpr int kD4bMaxDevices = 64;   // per-device kernel attributes (dynamic shared memory) are tracked up to here
 
 void d4b_abort_impl(const char *file, int line, const char *fmt, ...);
 #define D4B_ABORT(...) d4b_abort_impl(__FILE__, __LINE__, __VA_ARGS__)

@@ -159,8 +159,11 @@ int d4b_cg_run(d4b_mesh *m, double *u, const double *rhs, double *r, double *d, 
   d4b_dot_async(m, r, r, n, &s->rr);
   cg_begin_k<<<1, 1, 0, m->stream>>>(s, atol, rtol, imax);
   h->iters = 0;
-  for (int i0 = 0; i0 < imax; i0 += kCgChunk) {
-    for (int i = i0; i < imax && i < i0 + kCgChunk; ++i) {
+  // iterations are enqueued in chunks between two looks at the done flag; the chunk grows 1, 2, 4, ... kCgChunk so that
+  // a solve that converges in a few iterations (multigrid bottom solver) does not run a whole chunk of dead
+  // applies, halo exchanges and reductions past its end
+  for (int i0 = 0, chunk = 1; i0 < imax; i0 += chunk, chunk = chunk < kCgChunk ? 2 * chunk : kCgChunk) {
+    for (int i = i0; i < imax && i < i0 + chunk; ++i) {
       d4b_apply(m, d, Au);
       d4b_dot_async(m, d, Au, n, &s->dAd);
       cg_alpha_k<<<1, 1, 0, m->stream>>>(s);

@@ -283,7 +283,7 @@ void energy_dot_reserve(d4b_mesh *m) {
 // D4B_FUSED_SOLVERS=0: cg_eigs and the smoother as separate apply + vector kernels
 bool fused_solvers_allowed(const d4b_mesh *m) {
   const char *e = getenv("D4B_FUSED_SOLVERS");
-  return m->all_flat && !m->pre_apply && !(e && e[0] == '0');
+  return m->all_flat && !m->pre_apply && !m->d_W && !(e && e[0] == '0');
 }
 
 // cg_eigs on device vectors, enqueued without a host round trip: kernel i reads
@@ -362,7 +362,7 @@ void cheby_enqueue(d4b_mesh *m, double *du, const double *drhs, double *dr, int 
   // (u updated in place, no Au vector); otherwise apply + one vector kernel
   const char *nf = getenv("D4B_NO_FUSED_CHEBY");
   const bool fused = m->n_generic == 0 && !m->fast.empty() && !(nf && nf[0] == '1');
-  const bool hat = fused && iter > 0 && m->mpisize == 1 && !m->d_W && fused_solvers_allowed(m);
+  const bool hat = fused && iter > 0 && m->mpisize == 1 && fused_solvers_allowed(m);
   if (hat) {
     if (!m->d_uhat_alt) {
       m->d_uhat_alt = d4b_dev_alloc<double>(m, (size_t)n);

@@ -73,8 +73,9 @@ def load_library():
     L.d4b_mesh_hp_elements.argtypes = [C.c_void_p]
     L.d4b_mesh_launches_per_apply.restype = C.c_int32
     L.d4b_mesh_launches_per_apply.argtypes = [C.c_void_p]
-    L.d4b_mesh_halo_mode.restype = C.c_int32
-    L.d4b_mesh_halo_mode.argtypes = [C.c_void_p]
+    if hasattr(L, "d4b_mesh_halo_mode"):   # (older builds of the library are still loadable for A/B runs)
+        L.d4b_mesh_halo_mode.restype = C.c_int32
+        L.d4b_mesh_halo_mode.argtypes = [C.c_void_p]
     for fn in (L.d4b_apply, L.d4b_apply_stiffness):
         fn.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         fn.restype = None
