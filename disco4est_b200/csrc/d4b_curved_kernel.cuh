@@ -21,7 +21,9 @@
 struct CurvedArgs {
   const int32_t *elem;
   int first, n_elem;
-  const int64_t *nodal_stride;
+  const int64_t *elem_ns;       // [n_elem] nodal offset of each class position
+  int64_t ns0;                  // ns_linear: elem_ns[i] = ns0 + i N^3, no load needed (see FlatArgs)
+  int ns_linear;
   const double *FG;             // [n_elem][6][N^3]
   const double *FF;             // 7-plane face records [7][NN]; meta.rec = offset in doubles
   const FaceMeta *meta;         // [6*n_elem]
@@ -151,7 +153,7 @@ __global__ void __launch_bounds__(CurvedShflCfg<N>::THREADS, CurvedShflCfg<N>::M
   double *V1 = V0 + C::VS, *V2 = V1 + C::VS;
   double *FB = V2 + C::VS;                                // [6][2][NN], thread-private columns
   FaceMeta *META = reinterpret_cast<FaceMeta *>(FB + 12 * NN);
-  const int64_t ns = active ? a.nodal_stride[a.elem[ei]] : 0;
+  const int64_t ns = !active ? 0 : a.ns_linear ? a.ns0 + (int64_t)ei * N3 : a.elem_ns[ei];
   const double wxy = T.w[lx] * T.w[ly];
   if (threadIdx.x == 0 && a.prefetch) {
     constexpr unsigned kBlockBytes = C::EPB * 6 * N3 * sizeof(double);

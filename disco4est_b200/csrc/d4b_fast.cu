@@ -80,7 +80,7 @@ struct FastArgs {
   const int32_t *elem;          // [n_elem] element ids of this class
   int first;                    // this launch covers class positions [first, n_elem)
   int n_elem;
-  const int64_t *nodal_stride;
+  const int64_t *elem_ns;       // [n_elem] nodal offset of each class position (one load instead of elem -> stride)
   const double *FG;             // [n_elem][6][N^3] volume metric
   const double *FF;             // face records, [7][N^2] each
   const int64_t *face_rec;      // [6*n_elem] offset of the face record in FF
@@ -164,9 +164,10 @@ __device__ __forceinline__ int perm_xy(int n, int perm, int a, int b) {
 //         (d4est_linalg_vec_xpby of d4est_solver_cg_eigs.c:257 followed by the next apply's first step)
 // MODE 2: the way back, out = (Iinv x Iinv x Iinv) in
 struct InterpArgs {
-  const int32_t *elem;
   int n_elem;
-  const int64_t *nodal_stride;
+  const int64_t *elem_ns;          // [n_elem] nodal offset of each listed element
+  int64_t ns0;                     // ns_linear: elem_ns[i] = ns0 + i N^3
+  int ns_linear;
   const double *in;
   double *out;
   const double *r, *bnum, *bden;   // MODE 1
@@ -182,7 +183,7 @@ __global__ void __launch_bounds__(Cfg<N>::THREADS) interp_kernel(InterpArgs a) {
   const int ei = blockIdx.x * C::EPB + slot;
   const bool active = (slot < C::EPB) && (ei < a.n_elem);
   double *V = sm + (slot < C::EPB ? slot : 0) * VSize<N>::value;
-  const int64_t ns = active ? a.nodal_stride[a.elem[ei]] : 0;
+  const int64_t ns = !active ? 0 : a.ns_linear ? a.ns0 + (int64_t)ei * (N * NN) : a.elem_ns[ei];
   if (active) {
     double l[N];
 #pragma unroll
@@ -248,7 +249,7 @@ __global__ void __launch_bounds__(CurvedCfg<N>::THREADS, CurvedCfg<N>::MIN_BLOCK
   double *FT = V2 + C::VS;         // [6][2][NN] own trace / normal derivative at face Gauss points
   double *NB = FT + 12 * NN;       // [2][4][NN] neighbour: trace, normal, two tangential derivatives
   double *NB2 = NB + 8 * NN;       // [2][2][NN] weighted tangential term2
-  const int64_t ns = active ? a.nodal_stride[a.elem[ei]] : 0;
+  const int64_t ns = active ? a.elem_ns[ei] : 0;
   double gt[N];
   // the volume metric and the face records are first needed after the forward sweeps: ask the L2 now
   if (a.prefetch) {
@@ -554,7 +555,7 @@ void launch_flat(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, 
   if (last <= first) return;
   FlatArgs a;
   a.elem = cls.d_elem; a.first = first; a.n_elem = last;
-  a.nodal_stride = m->d_nodal_stride;
+  a.elem_ns = cls.d_elem_ns; a.ns0 = cls.ns0; a.ns_linear = cls.ns_linear;
   a.FG = cls.d_FG; a.FGc = cls.d_FGc; a.FF3 = m->d_flat_FF;
   a.meta = static_cast<const FaceMeta *>(cls.d_face_meta);
   a.uh = m->d_uhat; a.Au = d_Au; a.epi = m->epi;
@@ -614,7 +615,7 @@ void launch_curved(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first
   if (last <= first) return;
   CurvedArgs a;
   a.elem = cls.d_elem; a.first = first; a.n_elem = last;
-  a.nodal_stride = m->d_nodal_stride;
+  a.elem_ns = cls.d_elem_ns; a.ns0 = cls.ns0; a.ns_linear = cls.ns_linear;
   a.FG = cls.d_FG; a.FF = m->d_fast_FF;
   a.meta = static_cast<const FaceMeta *>(cls.d_face_meta);
   a.uh = m->d_uhat; a.Au = d_Au; a.epi = m->epi;
@@ -712,7 +713,8 @@ void launch_interp(d4b_mesh *m, const D4bFastClass &cls, const double *d_u, int 
   if (phase == 0) {   // local elements
     if (cls.n_hat == 0) return;
     int grid = (cls.n_hat + C::EPB - 1) / C::EPB;
-    a.elem = cls.d_hat_elem; a.n_elem = cls.n_hat; a.nodal_stride = m->d_nodal_stride; a.in = d_u; a.out = m->d_uhat;
+    a.elem_ns = cls.d_hat_ns; a.n_elem = cls.n_hat; a.in = d_u; a.out = m->d_uhat;
+    a.ns0 = cls.hat_ns0; a.ns_linear = cls.hat_linear;
     if (m->epi.xpby_r) {   // CG: d = r + beta d on the way (d4b_solver.cu)
       a.r = m->epi.xpby_r; a.bnum = m->epi.xpby_num; a.bden = m->epi.xpby_den; a.d = const_cast<double *>(d_u);
       interp_kernel<N, 1><<<grid, C::THREADS, 0, m->stream>>>(a);
@@ -722,7 +724,7 @@ void launch_interp(d4b_mesh *m, const D4bFastClass &cls, const double *d_u, int 
   } else {            // ghost elements, from the receive buffer to the tail of uhat
     if (cls.n_ghost_hat == 0) return;
     int grid = (cls.n_ghost_hat + C::EPB - 1) / C::EPB;
-    a.elem = cls.d_ghost_hat; a.n_elem = cls.n_ghost_hat; a.nodal_stride = m->d_ghost_nodal_stride;
+    a.elem_ns = cls.d_ghost_hat_ns; a.n_elem = cls.n_ghost_hat;
     a.in = m->d_ughost; a.out = m->d_uhat + m->local_nodes;
     interp_kernel<N, 0><<<grid, C::THREADS, 0, m->stream>>>(a);
   }
@@ -736,7 +738,8 @@ void launch_basis_change(d4b_mesh *m, const D4bFastClass &cls, const double *in,
   if (cls.n_hat == 0) return;
   InterpArgs a;
   memset(&a, 0, sizeof(a));
-  a.elem = cls.d_hat_elem; a.n_elem = cls.n_hat; a.nodal_stride = m->d_nodal_stride; a.in = in; a.out = out;
+  a.elem_ns = cls.d_hat_ns; a.n_elem = cls.n_hat; a.in = in; a.out = out;
+  a.ns0 = cls.hat_ns0; a.ns_linear = cls.hat_linear;
   const int grid = (cls.n_hat + C::EPB - 1) / C::EPB;
   if (to_gauss) interp_kernel<N, 0><<<grid, C::THREADS, 0, m->stream>>>(a);
   else interp_kernel<N, 2><<<grid, C::THREADS, 0, m->stream>>>(a);
@@ -749,7 +752,7 @@ void launch_fast(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, 
   if (last <= first) return;
   FastArgs a;
   a.elem = cls.d_elem; a.first = first; a.n_elem = last;
-  a.nodal_stride = m->d_nodal_stride;
+  a.elem_ns = cls.d_elem_ns;
   a.FG = cls.d_FG; a.FF = m->d_fast_FF;
   a.face_rec = cls.d_face_rec; a.face_nbr = cls.d_face_nbr; a.face_code = cls.d_face_code;
   a.uh = m->d_uhat; a.Au = d_Au; a.epi = m->epi;
@@ -763,7 +766,8 @@ void launch_fast(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, 
     D4B_CUDA(cudaFuncSetAttribute(fast_apply_kernel<N, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = true;
   }
-  a.prefetch = getenv("D4B_PREFETCH") ? atoi(getenv("D4B_PREFETCH")) : 1;
+  static const int prefetch = getenv("D4B_PREFETCH") ? atoi(getenv("D4B_PREFETCH")) : 1;
+  a.prefetch = prefetch;
   int grid = (last - first + C::EPB - 1) / C::EPB;
   if (m->d_W) fast_apply_kernel<N, true><<<grid, C::THREADS, smem, m->stream>>>(a);
   else fast_apply_kernel<N, false><<<grid, C::THREADS, smem, m->stream>>>(a);
@@ -776,7 +780,8 @@ void launch_interp_range(d4b_mesh *m, const D4bFastClass &cls, const double *d_u
   if (hi <= lo) return;
   InterpArgs a;
   memset(&a, 0, sizeof(a));
-  a.elem = cls.d_hat_elem + lo; a.n_elem = hi - lo; a.nodal_stride = m->d_nodal_stride; a.in = d_u; a.out = m->d_uhat;
+  a.elem_ns = cls.d_hat_ns + lo; a.n_elem = hi - lo; a.in = d_u; a.out = m->d_uhat;
+  a.ns0 = cls.hat_ns0 + (int64_t)lo * (N * N * N); a.ns_linear = cls.hat_linear;
   interp_kernel<N, 0><<<(hi - lo + C::EPB - 1) / C::EPB, C::THREADS, 0, m->stream>>>(a);
   D4B_CUDA(cudaGetLastError());
 }
@@ -1073,6 +1078,18 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<int
   // can side s use the record written from the other side?
   auto consistent = [&](int s, int, int, int) -> bool { return side_flags[s] & 2; };
 
+  // nodal offsets of a list of elements (the kernels' first load: one array instead of list -> stride table)
+  auto upload_ns = [&](const std::vector<int32_t> &els, const int64_t *stride) -> int64_t * {
+    std::vector<int64_t> ns(els.size());
+    for (size_t i = 0; i < els.size(); ++i) ns[i] = stride[els[i]];
+    return d4b_dev_upload<int64_t>(m, ns.data(), ns.size());
+  };
+  auto set_hat_linear = [&](D4bFastClass &c, const std::vector<int32_t> &els, int n3) {
+    c.hat_linear = !els.empty();
+    c.hat_ns0 = els.empty() ? 0 : d->nodal_stride[els[0]];
+    for (size_t i = 0; i < els.size() && c.hat_linear; ++i)
+      c.hat_linear = d->nodal_stride[els[i]] == c.hat_ns0 + (int64_t)i * n3;
+  };
   FastTab tabs[9];
   memset(tabs, 0, sizeof(tabs));
   int64_t n_shared = 0, n_split = 0;
@@ -1128,13 +1145,16 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<int
       c.kind = 3;
       c.n_hat = (int)hat_by_deg[p].size();
       c.d_hat_elem = d4b_dev_upload<int32_t>(m, hat_by_deg[p].data(), hat_by_deg[p].size());
+      c.d_hat_ns = upload_ns(hat_by_deg[p], d->nodal_stride); set_hat_linear(c, hat_by_deg[p], N3);
       c.h_hat = hat_by_deg[p];
       c.n_ghost_hat = (int)ghost_hat.size();
       c.d_ghost_hat = d4b_dev_upload<int32_t>(m, ghost_hat.data(), ghost_hat.size());
+      c.d_ghost_hat_ns = upload_ns(ghost_hat, d->ghost_nodal_stride);
       hat_done = true;
       c.n_elem = (int)els.size();
       c.n_interior = (int)(mid - els.begin());
       c.d_elem = d4b_dev_upload<int32_t>(m, els.data(), els.size());
+      c.d_elem_ns = upload_ns(els, d->nodal_stride);
       c.h_elem = els;
       D4B_CUDA(cudaMalloc(&c.d_face_mask, masks.size()));
       D4B_CUDA(cudaMemcpy(c.d_face_mask, masks.data(), masks.size(), cudaMemcpyHostToDevice));
@@ -1151,14 +1171,21 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<int
       if (!hat_done) {
         c.n_hat = (int)hat_by_deg[p].size();
         c.d_hat_elem = d4b_dev_upload<int32_t>(m, hat_by_deg[p].data(), hat_by_deg[p].size());
+        c.d_hat_ns = upload_ns(hat_by_deg[p], d->nodal_stride); set_hat_linear(c, hat_by_deg[p], N3);
         c.h_hat = hat_by_deg[p];
         c.n_ghost_hat = (int)ghost_hat.size();
         c.d_ghost_hat = d4b_dev_upload<int32_t>(m, ghost_hat.data(), ghost_hat.size());
+        c.d_ghost_hat_ns = upload_ns(ghost_hat, d->ghost_nodal_stride);
         hat_done = true;
       }
       c.n_elem = (int)els.size();
       c.n_interior = n_interior_kind[kind];
       c.d_elem = d4b_dev_upload<int32_t>(m, els.data(), els.size());
+      c.d_elem_ns = upload_ns(els, d->nodal_stride);
+      c.ns0 = d->nodal_stride[els[0]];
+      c.ns_linear = 1;
+      for (size_t i = 0; i < els.size() && c.ns_linear; ++i)
+        c.ns_linear = d->nodal_stride[els[i]] == c.ns0 + (int64_t)i * N3;
       std::vector<int64_t> face_rec((size_t)6 * els.size()), face_nbr((size_t)6 * els.size(), kNoNbr);
       std::vector<int32_t> face_code((size_t)6 * els.size(), 0);
       std::vector<unsigned char> has_extra(els.size(), 0);
@@ -1286,14 +1313,17 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<int
       if (!hat_done) {
         c.n_hat = (int)hat_by_deg[p].size();
         c.d_hat_elem = d4b_dev_upload<int32_t>(m, hat_by_deg[p].data(), hat_by_deg[p].size());
+        c.d_hat_ns = upload_ns(hat_by_deg[p], d->nodal_stride); set_hat_linear(c, hat_by_deg[p], N3);
         c.h_hat = hat_by_deg[p];
         c.n_ghost_hat = (int)ghost_hat.size();
         c.d_ghost_hat = d4b_dev_upload<int32_t>(m, ghost_hat.data(), ghost_hat.size());
+        c.d_ghost_hat_ns = upload_ns(ghost_hat, d->ghost_nodal_stride);
         hat_done = true;
       }
       c.n_elem = (int)els.size();
       c.n_interior = (int)(mid - els.begin());
       c.d_elem = d4b_dev_upload<int32_t>(m, els.data(), els.size());
+      c.d_elem_ns = upload_ns(els, d->nodal_stride);
       c.h_elem = els;
       m->n_hp_elem += c.n_elem;
       m->fast.push_back(c);

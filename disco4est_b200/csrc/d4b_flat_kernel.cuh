@@ -28,7 +28,9 @@ struct FlatArgs {
   const int32_t *elem;
   int first;                    // this launch covers class positions [first, n_elem)
   int n_elem;
-  const int64_t *nodal_stride;
+  const int64_t *elem_ns;       // [n_elem] nodal offset of each class position
+  int64_t ns0;                  // ns_linear: elem_ns[i] = ns0 + i N^3 (the class is a run of consecutive elements):
+  int ns_linear;                //   the kernel's first dependent load is not needed at all
   const double *FG;             // [n_elem][6][N^3]
   const double *FGc;            // CG kernels: [n_elem][6], metric of an affine element without the weights
   const double *FF3;            // compact face records: A_m[n], A_p[n] (g on the boundary), sj*sigma
@@ -155,7 +157,7 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) f
   FaceMeta *META = reinterpret_cast<FaceMeta *>(FB + 12 * NN);
   constexpr bool dot = DOT;
   double dsum = 0.;   // dot: this thread's share of u . A u in its energy form, grad . F (+ mass, irregular faces) + faces
-  const int64_t ns = active ? a.nodal_stride[a.elem[ei]] : 0;
+  const int64_t ns = !active ? 0 : a.ns_linear ? a.ns0 + (int64_t)ei * N3 : a.elem_ns[ei];
   const double wxy = T.w[lx] * T.w[ly];
   double gt[N];
   double tr4 = 0., dn4 = 0., tr5 = 0., dn5 = 0.;
@@ -185,6 +187,8 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) f
       const FaceMeta fm = a.meta[6 * (size_t)ei + j];
       META[j] = fm;
       if ((3 * NN * 8) % 16 == 0 && a.prefetch > 1) l2_prefetch(a.FF3 + (size_t)fm.rec * (3 * NN), 3 * NN * 8);
+      if (a.prefetch > 2 && fm.nbr != kNoNbr)   // the neighbour's uh block: its lines are read two phases later
+        for (int off = 0; off < N3; off += 16) l2_prefetch_line(a.uh + fm.nbr + off);
     }
 #pragma unroll
     for (int i = 0; i < N; ++i) {

@@ -49,7 +49,12 @@ struct D4bFastClass {
   int n_interior = 0;            // the first n_interior of them have no ghost neighbour
   int n_ghost_hat = 0;           // ghost elements of this degree whose uh the class needs
   int32_t *d_ghost_hat = nullptr;
+  int64_t ns0 = 0;               // ns_linear: the class is a run of consecutive elements, nodal offset of position i
+  int ns_linear = 0;             //   = ns0 + i N^3
+  int64_t hat_ns0 = 0;           // the same for d_hat_elem
+  int hat_linear = 0;
   int32_t *d_elem = nullptr;     // [n_elem] element ids
+  int64_t *d_elem_ns = nullptr, *d_hat_ns = nullptr, *d_ghost_hat_ns = nullptr;   // nodal offsets of d_elem / d_hat_elem / d_ghost_hat
   int n_hat = 0;                 // elements of this degree with deg_quad == deg (uh is computed for all)
   int32_t *d_hat_elem = nullptr;
   double *d_FG = nullptr;        // [n_elem][6][N^3] volume metric
