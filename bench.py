@@ -686,10 +686,13 @@ def bench_ours(args):
     n_warm = max(args.warmup, 3)
     for _ in range(n_warm):
         mesh.apply(u, Au)
-    barrier()
+    # the clock sampler (an nvidia-smi child process on rank 0) starts BEFORE the barrier: started after it, rank 0
+    # entered the timed region about a millisecond after the others, who then waited for its halo -- at N > 1 the
+    # max over ranks carried that delay (0.02-0.04 ms per apply at 20 steps; found in round 2)
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
+    barrier()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record(stream)
     for _ in range(args.steps):
@@ -762,61 +765,73 @@ def bench_ours(args):
                 if not plugin["parity_rel_l2_vs_reference_cpu_apply"] <= PARITY_TOL:
                     sys.stderr.write("bench.py: plugin parity FAILED: %s\n" % json.dumps(plugin))
                     sys.exit(3)
-    # the same apply with the NCCL send/recv halo (the fallback when peers cannot be mapped), for comparison
+    # the same apply with the other halo (NCCL send/recv <-> neighbours' memory read in place), for comparison
     halo_ab = None
     if world > 1 and not args.no_halo_ab:
-        modes = torch.tensor([1 if mesh.halo_mode() == "peer" else 0], dtype=torch.int64, device=dev)
-        dist.all_reduce(modes, op=dist.ReduceOp.MIN)
-        if int(modes[0]) == 1:
-            os.environ["D4B_PEER_HALO"] = "0"
-            A, gm = brick_desc(level, deg, rank=rank, world=world, trees=trees, geometry=False)
-            mesh2 = Mesh(A, device=local_rank, geom=gm)
-            del A, gm
-            mesh2.set_stream(stream.cuda_stream)
-            Au2 = torch.empty_like(u)
-            for _ in range(n_warm):
-                mesh2.apply(u, Au2)
-            barrier()
-            ev0.record(stream)
-            for _ in range(args.steps):
-                mesh2.apply(u, Au2)
-            ev1.record(stream)
-            barrier()
-            tt = torch.tensor([ev0.elapsed_time(ev1) * 1e-3 / args.steps], dtype=torch.float64, device=dev)
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-            same = torch.tensor([1 if torch.equal(Au, Au2) else 0], dtype=torch.int64, device=dev)
-            dist.all_reduce(same, op=dist.ReduceOp.MIN)
-            halo_ab = {"nccl_halo_GDOF_per_s": total_dof / float(tt[0]) / 1e9, "nccl_halo_ms_per_apply": 1e3 * float(tt[0]),
-                       "peer_halo_ms_per_apply": 1e3 * t_dev, "halo_mode_checked": mesh2.halo_mode(),
-                       "results_bit_equal_on_all_ranks": bool(int(same[0]))}
-            mesh2.close()
-            del mesh2, Au2
-            os.environ.pop("D4B_PEER_HALO", None)
-            # and with no halo at all: every rank applies a one-rank cube of the same size at the same time
-            # (what the GPUs of this box do independently; max / min over the ranks)
-            A, gm = brick_desc(level, deg, geometry=False)
-            mesh2 = Mesh(A, device=local_rank, geom=gm)
-            del A, gm
-            mesh2.set_stream(stream.cuda_stream)
-            Au2 = torch.empty_like(u)
-            for _ in range(n_warm):
-                mesh2.apply(u, Au2)
-            barrier()
-            ev0.record(stream)
-            for _ in range(args.steps):
-                mesh2.apply(u, Au2)
-            ev1.record(stream)
-            barrier()
-            t1 = ev0.elapsed_time(ev1) * 1e-3 / args.steps
-            tt = torch.tensor([t1, -t1], dtype=torch.float64, device=dev)
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-            halo_ab["independent_one_rank_cubes_ms_per_apply"] = {"slowest_gpu": 1e3 * float(tt[0]), "fastest_gpu": -1e3 * float(tt[1])}
-            mesh2.close()
-            del mesh2, Au2
-            if not halo_ab["results_bit_equal_on_all_ranks"]:
-                if rank == 0:
-                    sys.stderr.write("bench.py: peer-memory halo and NCCL halo differ: %s\n" % json.dumps(halo_ab))
-                sys.exit(3)
+        mine = mesh.halo_mode()
+        other = "peer" if mine == "nccl" else "nccl"
+        os.environ["D4B_PEER_HALO"] = "1" if other == "peer" else "0"
+        A, gm = brick_desc(level, deg, rank=rank, world=world, trees=trees, geometry=False)
+        mesh2 = Mesh(A, device=local_rank, geom=gm)
+        del A, gm
+        mesh2.set_stream(stream.cuda_stream)
+        Au2 = torch.empty_like(u)
+        for _ in range(n_warm):
+            mesh2.apply(u, Au2)
+        barrier()
+        ev0.record(stream)
+        for _ in range(args.steps):
+            mesh2.apply(u, Au2)
+        ev1.record(stream)
+        barrier()
+        tt = torch.tensor([ev0.elapsed_time(ev1) * 1e-3 / args.steps], dtype=torch.float64, device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        same = torch.tensor([1 if torch.equal(Au, Au2) else 0], dtype=torch.int64, device=dev)
+        dist.all_reduce(same, op=dist.ReduceOp.MIN)
+        halo_ab = {"headline_halo": mine, mine + "_halo_ms_per_apply": 1e3 * t_dev,
+                   other + "_halo_ms_per_apply": 1e3 * float(tt[0]),
+                   other + "_halo_GDOF_per_s": total_dof / float(tt[0]) / 1e9,
+                   "halo_mode_checked": mesh2.halo_mode(),
+                   "results_bit_equal_on_all_ranks": bool(int(same[0])),
+                   "order": "headline halo, the other one, the headline halo again (same mesh size, same vectors)"}
+        mesh2.close()
+        del mesh2, Au2
+        os.environ.pop("D4B_PEER_HALO", None)
+        # the headline mesh once more, after the other one (order effects)
+        barrier()
+        ev0.record(stream)
+        for _ in range(args.steps):
+            mesh.apply(u, Au)
+        ev1.record(stream)
+        barrier()
+        tt = torch.tensor([ev0.elapsed_time(ev1) * 1e-3 / args.steps], dtype=torch.float64, device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        halo_ab[mine + "_halo_ms_per_apply_second_run"] = 1e3 * float(tt[0])
+        # and with no halo at all: every rank applies a one-rank cube of the same size at the same time
+        # (what the GPUs of this box do independently; max / min over the ranks)
+        A, gm = brick_desc(level, deg, geometry=False)
+        mesh2 = Mesh(A, device=local_rank, geom=gm)
+        del A, gm
+        mesh2.set_stream(stream.cuda_stream)
+        Au2 = torch.empty_like(u)
+        for _ in range(n_warm):
+            mesh2.apply(u, Au2)
+        barrier()
+        ev0.record(stream)
+        for _ in range(args.steps):
+            mesh2.apply(u, Au2)
+        ev1.record(stream)
+        barrier()
+        t1 = ev0.elapsed_time(ev1) * 1e-3 / args.steps
+        tt = torch.tensor([t1, -t1], dtype=torch.float64, device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        halo_ab["independent_one_rank_cubes_ms_per_apply"] = {"slowest_gpu": 1e3 * float(tt[0]), "fastest_gpu": -1e3 * float(tt[1])}
+        mesh2.close()
+        del mesh2, Au2
+        if not halo_ab["results_bit_equal_on_all_ranks"]:
+            if rank == 0:
+                sys.stderr.write("bench.py: peer-memory halo and NCCL halo differ: %s\n" % json.dumps(halo_ab))
+            sys.exit(3)
     # second metric of BASELINE.json: seconds per multigrid V-cycle
     vc = None
     if not args.no_vcycle:

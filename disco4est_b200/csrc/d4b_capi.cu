@@ -72,27 +72,55 @@ void d4b_apply_device(d4b_mesh *m, const double *du, double *dAu) {
     // compute stream:  uh(local) | interior elements ........................... | join
     // halo stream   :        wait uh(local) | signal neighbours | wait for theirs | boundary elements
     d4b_comm_peer_begin(m);
-    d4b_launch_fast(m, du, dAu, 0);
     // small meshes (coarse multigrid levels): an interior launch of a few microseconds hides nothing, and the two
     // cross-stream dependencies cost more than it runs -- everything in order on the compute stream
     static const int64_t split_min = getenv("D4B_PEER_SPLIT_MIN_NODES") ? atoll(getenv("D4B_PEER_SPLIT_MIN_NODES")) : (int64_t)1 << 20;
-    if (m->local_nodes < split_min) {
+    if (m->local_nodes < split_min && d4b_fast_can_merge_halo(m)) {
+      // every class in a kernel that waits by itself: ONE launch per class on the compute stream; the element groups
+      // with a ghost neighbour come last in the class order and find the neighbours' flags set when they run
+      // (no second stream, no event, no wait kernel, no extra launch)
+      d4b_launch_fast(m, du, dAu, 0);
+      d4b_comm_peer_signal(m, m->stream);
+      d4b_launch_fast(m, du, dAu, 3);
+    } else if (m->local_nodes < split_min) {
+      d4b_launch_fast(m, du, dAu, 0);
       d4b_comm_peer_signal(m, m->stream);
       d4b_launch_fast(m, du, dAu, 1);
       d4b_comm_peer_wait(m, m->stream);
       d4b_launch_fast(m, du, dAu, 2);
     } else {
+      // D4B_HALO_TIMING=1: event time stamps of the phases of every apply, averages printed by d4b_mesh_destroy
+      static const bool timing = getenv("D4B_HALO_TIMING") && atoi(getenv("D4B_HALO_TIMING")) != 0;
+      if (timing && m->halo_ev.empty()) {
+        m->halo_ev.resize(6);
+        for (cudaEvent_t &e : m->halo_ev) D4B_CUDA(cudaEventCreate(&e));
+      } else if (timing) {   // the previous apply's stamps
+        D4B_CUDA(cudaEventSynchronize(m->halo_ev[5]));
+        for (int i = 0; i < 5; ++i) {
+          float ms = 0.f;
+          D4B_CUDA(cudaEventElapsedTime(&ms, m->halo_ev[0], m->halo_ev[i + 1]));
+          m->halo_t[i] += ms;
+        }
+        ++m->halo_n;
+      }
+      if (timing) D4B_CUDA(cudaEventRecord(m->halo_ev[0], m->stream));      // 0: apply begins
+      d4b_launch_fast(m, du, dAu, 0);
       D4B_CUDA(cudaEventRecord(m->ev_interp, m->stream));
+      if (timing) D4B_CUDA(cudaEventRecord(m->halo_ev[1], m->stream));      // 1: uh(local) done
       D4B_CUDA(cudaStreamWaitEvent(m->comm_stream, m->ev_interp, 0));
       d4b_comm_peer_signal(m, m->comm_stream);
       d4b_launch_fast(m, du, dAu, 1);
+      if (timing) D4B_CUDA(cudaEventRecord(m->halo_ev[2], m->stream));      // 2: interior elements done
       d4b_comm_peer_wait(m, m->comm_stream);
+      if (timing) D4B_CUDA(cudaEventRecord(m->halo_ev[3], m->comm_stream)); // 3: neighbours have signalled
       cudaStream_t compute = m->stream;
       m->stream = m->comm_stream;
       d4b_launch_fast(m, du, dAu, 2);
       D4B_CUDA(cudaEventRecord(m->ev_boundary, m->comm_stream));
+      if (timing) D4B_CUDA(cudaEventRecord(m->halo_ev[4], m->comm_stream)); // 4: boundary elements done
       m->stream = compute;
       D4B_CUDA(cudaStreamWaitEvent(m->stream, m->ev_boundary, 0));
+      if (timing) D4B_CUDA(cudaEventRecord(m->halo_ev[5], m->stream));      // 5: joined
     }
   } else {
     // compute stream:  pack | uh(local) | interior elements ............ | join

@@ -417,7 +417,7 @@ bool d4b_comm_peer_ready(d4b_mesh *m) {
   D4B_CHECK(g_comm && g_size == m->mpisize && g_rank == m->mpirank,
             "mesh of rank %d/%d but d4b_comm_init was %s", m->mpirank, m->mpisize,
             g_comm ? "called with another rank/size" : "not called");
-  const char *env = getenv("D4B_PEER_HALO");
+  const char *env = getenv("D4B_PEER_HALO");   // 0: keep the NCCL exchange
   // the general kernel reads nodal ghost values: such meshes keep the nodal exchange
   int ok = !(env && atoi(env) == 0) && m->n_generic == 0 && !m->fast.empty() && m->d_uhat != nullptr;
   const int R = m->mpisize;

@@ -35,6 +35,7 @@ struct CurvedArgs {
   const int64_t *quad_stride;
   const unsigned char *has_extra;
   const double *extra;
+  D4bHaloWait halo;
 };
 
 template <int N>
@@ -147,7 +148,8 @@ __global__ void __launch_bounds__(CurvedShflCfg<N>::THREADS, CurvedShflCfg<N>::M
   const int lt = threadIdx.x % NN;
   const int lx = lt % N, ly = lt / N;
   const int base = (slot < C::EPB ? slot : 0) * NN;          // first lane of my element
-  const int ei = a.first + blockIdx.x * C::EPB + slot;
+  const int blk = blockIdx.x;
+  const int ei = a.first + blk * C::EPB + slot;
   const bool active = (slot < C::EPB) && (ei < a.n_elem);
   double *V0 = smem + (size_t)(slot < C::EPB ? slot : 0) * C::SH_PER_ELEM;
   double *V1 = V0 + C::VS, *V2 = V1 + C::VS;
@@ -157,7 +159,7 @@ __global__ void __launch_bounds__(CurvedShflCfg<N>::THREADS, CurvedShflCfg<N>::M
   const double wxy = T.w[lx] * T.w[ly];
   if (threadIdx.x == 0 && a.prefetch) {
     constexpr unsigned kBlockBytes = C::EPB * 6 * N3 * sizeof(double);
-    const int e0 = a.first + (int)blockIdx.x * C::EPB, left = a.n_elem - e0;
+    const int e0 = a.first + blk * C::EPB, left = a.n_elem - e0;
     l2_prefetch(a.FG + (size_t)e0 * (6 * N3), left >= C::EPB ? kBlockBytes : left * 6 * N3 * 8);
   }
   // ---- T-orientation (a,b) = (lx,ly), line along c: only stage uh; its c-derivative and the traces of faces 4/5
@@ -174,8 +176,9 @@ __global__ void __launch_bounds__(CurvedShflCfg<N>::THREADS, CurvedShflCfg<N>::M
 #pragma unroll
     for (int c = 0; c < N; ++c) V0[vix<N>(lx, ly, c)] = a.uh[ns + lt + NN * c];
   }
+  if (a.halo.n > 0 && a.first + (blk + 1) * C::EPB > a.halo.from) halo_wait(a.halo);   // see d4b_flat_kernel.cuh
   __syncwarp();
-  const FaceMeta zero_meta = {-1, 0, kOwn};
+  const FaceMeta zero_meta = {kNoNbr, 0, kOwn};
   {   // S-orientation: (a,c) = (lx,ly), line along b: gradient, faces 2/3
     double t2 = 0., n2 = 0., t3 = 0., n3 = 0.;
     if (active) {

@@ -550,10 +550,11 @@ __global__ void __launch_bounds__(CurvedCfg<N>::THREADS, CurvedCfg<N>::MIN_BLOCK
 #include "d4b_flat_kernel.cuh"
 
 template <int N>
-void launch_flat(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, int last) {
+void launch_flat(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, int last, const D4bHaloWait *halo = nullptr) {
   using C = FlatCfg<N>;
   if (last <= first) return;
   FlatArgs a;
+  if (halo) a.halo = *halo;
   a.elem = cls.d_elem; a.first = first; a.n_elem = last;
   a.elem_ns = cls.d_elem_ns; a.ns0 = cls.ns0; a.ns_linear = cls.ns_linear;
   a.FG = cls.d_FG; a.FGc = cls.d_FGc; a.FF3 = m->d_flat_FF;
@@ -610,10 +611,11 @@ inline bool use_curved_shfl(int N) {
 }
 
 template <int N>
-void launch_curved(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, int last) {
+void launch_curved(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, int last, const D4bHaloWait *halo = nullptr) {
   using C = CurvedShflCfg<N>;
   if (last <= first) return;
   CurvedArgs a;
+  if (halo) a.halo = *halo;
   a.elem = cls.d_elem; a.first = first; a.n_elem = last;
   a.elem_ns = cls.d_elem_ns; a.ns0 = cls.ns0; a.ns_linear = cls.ns_linear;
   a.FG = cls.d_FG; a.FF = m->d_fast_FF;
@@ -629,9 +631,9 @@ void launch_curved(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first
   else curved_apply_kernel<N, false><<<grid, C::THREADS, smem, m->stream>>>(a);
   D4B_CUDA(cudaGetLastError());
 }
-template <> void launch_curved<6>(d4b_mesh *, const D4bFastClass &, double *, int, int) {}
-template <> void launch_curved<7>(d4b_mesh *, const D4bFastClass &, double *, int, int) {}
-template <> void launch_curved<8>(d4b_mesh *, const D4bFastClass &, double *, int, int) {}
+template <> void launch_curved<6>(d4b_mesh *, const D4bFastClass &, double *, int, int, const D4bHaloWait *) {}
+template <> void launch_curved<7>(d4b_mesh *, const D4bFastClass &, double *, int, int, const D4bHaloWait *) {}
+template <> void launch_curved<8>(d4b_mesh *, const D4bFastClass &, double *, int, int, const D4bHaloWait *) {}
 
 #include "d4b_hp_kernel.cuh"
 
@@ -1358,6 +1360,19 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *d, const std::vector<int
   for (const D4bFastClass &c : m->fast) m->all_flat = m->all_flat && (c.kind == 1 || c.n_elem == 0);
 }
 
+// every class runs in a kernel with the in-kernel halo wait (tangential-free or the curved shuffle kernel)
+bool d4b_fast_can_merge_halo(const d4b_mesh *m) {
+  static const bool off = getenv("D4B_PEER_MERGED") && atoi(getenv("D4B_PEER_MERGED")) == 0;
+  if (off || m->n_generic > 0 || m->fast.empty()) return false;
+  for (const D4bFastClass &c : m->fast) {
+    if (c.n_elem == 0) continue;
+    if (c.kind == 1) continue;
+    if (c.kind == 0 && use_curved_shfl(c.deg + 1) && c.d_face_meta) continue;
+    return false;
+  }
+  return true;
+}
+
 void d4b_launch_basis_change(d4b_mesh *m, const double *in, double *out, bool to_gauss) {
   for (const D4bFastClass &c : m->fast) {
 #define D4B_CASE(n) case n: launch_basis_change<n>(m, c, in, out, to_gauss); break;
@@ -1442,6 +1457,20 @@ void d4b_launch_fast(d4b_mesh *m, const double *d_u, double *d_Au, int part) {
     }
   }
   if (part == 0) return;
+  if (part == 3) {   // one launch per class; the groups from n_interior on wait for the neighbour ranks by themselves
+    for (const D4bFastClass &c : m->fast) {
+      D4bHaloWait h;
+      h.flags = m->peer.flags; h.ranks = m->peer.d_wait; h.n = c.n_elem > c.n_interior ? m->peer.n_nbr : 0;
+      h.from = c.n_interior; h.epoch = m->peer.epoch;
+#define D4B_CASE(n) case n: if (c.kind == 1) launch_flat<n>(m, c, d_Au, 0, c.n_elem, &h); else launch_curved<n>(m, c, d_Au, 0, c.n_elem, &h); break;
+      switch (c.deg + 1) {
+        D4B_CASE(2) D4B_CASE(3) D4B_CASE(4) D4B_CASE(5) D4B_CASE(6) D4B_CASE(7) D4B_CASE(8)
+        default: D4B_ABORT("fast path: unsupported degree %d", c.deg);
+      }
+#undef D4B_CASE
+    }
+    return;
+  }
   for (const D4bFastClass &c : m->fast) {
     const int first = part == 1 ? 0 : c.n_interior, last = part == 1 ? c.n_interior : c.n_elem;
 #define D4B_CASE(n) case n: if (c.kind >= 2) launch_hp<n>(m, c, d_Au, first, last, c.kind == 3); else if (c.kind) launch_flat<n>(m, c, d_Au, first, last); else if (use_curved_shfl(n) && c.d_face_meta) launch_curved<n>(m, c, d_Au, first, last); else launch_fast<n>(m, c, d_Au, first, last); break;

@@ -24,6 +24,24 @@ struct FaceMeta {     // 16 bytes per element face
   int32_t code;       // f_p | perm << 3 | own << 6
 };
 
+// the first lanes of the block poll the neighbour ranks' flags (see D4bHaloWait); the caller synchronises the block
+__device__ __forceinline__ void halo_wait(const D4bHaloWait &h) {
+  for (int i = threadIdx.x; i < h.n; i += blockDim.x) {
+    const unsigned long long *p = h.flags + h.ranks[i];
+    unsigned long long v, t0 = 0;
+    for (int spin = 0;; ++spin) {
+      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+      if (v >= h.epoch) break;
+      unsigned long long now;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+      if (spin == 0) t0 = now;
+      if (now - t0 > 30000000000ull) __trap();   // 30 s: a neighbour never produced this apply (no printf: it would
+                                                 // put a stack frame into every instantiation of the apply kernels)
+      __nanosleep(64);
+    }
+  }
+}
+
 struct FlatArgs {
   const int32_t *elem;
   int first;                    // this launch covers class positions [first, n_elem)
@@ -45,6 +63,7 @@ struct FlatArgs {
   // contributions of their irregular faces from hp_apply_kernel<.., FACE_ONLY>) to the accumulator
   const unsigned char *has_extra;
   const double *extra;
+  D4bHaloWait halo;
 };
 
 // ask the L2 for `bytes` (multiple of 16) at a 16-byte aligned global address
@@ -166,7 +185,7 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) f
   // through the kernel: ask the L2 for this block's share now
   if (!CG && threadIdx.x == 0 && a.prefetch) {
     constexpr unsigned kBlockBytes = C::EPB * 6 * N3 * sizeof(double);
-    const int e0 = a.first + (int)blockIdx.x * C::EPB, left = a.n_elem - e0;
+    const int e0 = a.first + blk * C::EPB, left = a.n_elem - e0;
     l2_prefetch(a.FG + (size_t)e0 * (6 * N3), left >= C::EPB ? kBlockBytes : left * 6 * N3 * 8);
   }
   // fused smoother: its three operand streams are only touched by the very last
@@ -204,6 +223,13 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) f
       gt[c] = s;
     }
   }
+  // merged launch with the peer-memory halo (small meshes): the groups holding elements with a ghost neighbour --
+  // the last ones of the class order -- wait for the neighbours' uh here (their own loads are already in flight);
+  // nothing before this point reads a neighbour.  On large meshes these groups are a launch of their own on the
+  // halo stream instead (d4b_capi.cu): at the end of one big launch their NVLink latency is the tail of the kernel
+  // (0.375 vs 0.368 ms at 2 GPUs), moved forward they spin for a neighbour that may be most of an apply behind and
+  // hold SM slots meanwhile (0.418 ms) -- profiles/r02_peer_merged_launch_ab.txt
+  if (a.halo.n > 0 && a.first + (blk + 1) * C::EPB > a.halo.from) halo_wait(a.halo);
   block_sync<C::THREADS>();
   if (active) {
     // the lifted face term tested with the element's own polynomial: sum_c uh_c (e_c ve + d_c vd) = tr ve + dn vd

@@ -122,6 +122,16 @@ struct D4bPeerHalo {
   int64_t *d_ghost_uh_off = nullptr; // per ghost: offset of its uhat lines relative to (uhat + local_nodes)
 };
 
+// Peer-memory halo inside the apply kernels (merged launch): element groups that reach class positions >= from
+// hold elements with a ghost neighbour; before they read neighbour lines they wait until every neighbour rank has
+// signalled this apply (flags[ranks[i]] >= epoch).  n == 0: no wait (one rank, NCCL halo, interior-only launches).
+struct D4bHaloWait {
+  const unsigned long long *flags = nullptr;
+  const int32_t *ranks = nullptr;
+  int n = 0, from = 0;
+  unsigned long long epoch = 0;
+};
+
 struct d4b_mesh {
   int device = 0;
   cudaStream_t stream = nullptr;
@@ -175,6 +185,9 @@ struct d4b_mesh {
   cudaStream_t comm_stream = nullptr;
   cudaEvent_t ev_packed = nullptr, ev_recv = nullptr, ev_interp = nullptr, ev_boundary = nullptr;
   D4bPeerHalo peer;
+  std::vector<cudaEvent_t> halo_ev;   // D4B_HALO_TIMING (d4b_capi.cu)
+  double halo_t[5] = {0., 0., 0., 0., 0.};
+  int64_t halo_n = 0;
 
   // staging for host-pointer calls
   double *d_u_stage = nullptr, *d_Au_stage = nullptr;
@@ -250,7 +263,9 @@ void d4b_fast_setup(d4b_mesh *m, const d4b_mesh_desc_t *desc, const std::vector<
                     std::vector<char> &is_fast);
 // part 0: uh of local elements; 1: interior elements; 2 (after the halo exchange): uh of
 // ghost elements + elements with a ghost neighbour
+// part 3 (peer halo, every class in a kernel that can wait by itself): all elements in one launch per class
 void d4b_launch_fast(d4b_mesh *m, const double *d_u, double *d_Au, int part);
+bool d4b_fast_can_merge_halo(const d4b_mesh *m);
 // one-rank meshes: what = 0: uh of the elements [e0, e1); what = 1: apply on the elements [e0, e1)
 void d4b_launch_fast_range(d4b_mesh *m, const double *d_u, double *d_Au, int what, int e0, int e1);
 // out = (I x I x I) in (to_gauss) or its inverse, over every collocated element
