@@ -57,21 +57,25 @@ __global__ void add_k(const double *__restrict__ x, double *__restrict__ y, int6
 }
 }  // namespace
 
+// du == nullptr: the Gauss-collocated input is already in m->d_uhat (the Gauss-resident smoother, d4b_solver.cu); with
+// the peer halo the caller has also begun this apply's epoch (d4b_comm_peer_begin)
 void d4b_apply_device(d4b_mesh *m, const double *du, double *dAu) {
   D4B_CHECK(m->epi.mode == 0 || m->n_generic == 0, "fused epilogue on a mesh with general-kernel elements");
+  const bool have_uh = du == nullptr;
+  D4B_CHECK(!have_uh || (m->n_generic == 0 && !m->pre_apply), "apply from uh on a mesh that needs the nodal input");
   // coarse multigrid level of a linearised problem: the Galerkin mass term of this input first
   const bool add = m->pre_apply && m->pre_apply(m, du);
   const bool add_after = add && (m->n_generic > 0 || m->fast.empty());
   if (add && !add_after) m->epi.add = m->d_addterm;
   if (m->mpisize == 1) {
-    d4b_launch_fast(m, du, dAu, 0);
+    if (!have_uh) d4b_launch_fast(m, du, dAu, 0);
     d4b_launch_fast(m, du, dAu, 1);
   } else if (d4b_comm_peer_ready(m)) {
     // halo over peer memory (d4b_comm.cu): nothing is packed or sent; the boundary elements read the
     // neighbour ranks' uh over NVLink once those ranks have signalled that it is complete
     // compute stream:  uh(local) | interior elements ........................... | join
     // halo stream   :        wait uh(local) | signal neighbours | wait for theirs | boundary elements
-    d4b_comm_peer_begin(m);
+    if (!have_uh) d4b_comm_peer_begin(m);
     // small meshes (coarse multigrid levels): an interior launch of a few microseconds hides nothing, and the two
     // cross-stream dependencies cost more than it runs -- everything in order on the compute stream
     static const int64_t split_min = getenv("D4B_PEER_SPLIT_MIN_NODES") ? atoll(getenv("D4B_PEER_SPLIT_MIN_NODES")) : (int64_t)1 << 20;
@@ -79,11 +83,11 @@ void d4b_apply_device(d4b_mesh *m, const double *du, double *dAu) {
       // every class in a kernel that waits by itself: ONE launch per class on the compute stream; the element groups
       // with a ghost neighbour come last in the class order and find the neighbours' flags set when they run
       // (no second stream, no event, no wait kernel, no extra launch)
-      d4b_launch_fast(m, du, dAu, 0);
+      if (!have_uh) d4b_launch_fast(m, du, dAu, 0);
       d4b_comm_peer_signal(m, m->stream);
       d4b_launch_fast(m, du, dAu, 3);
     } else if (m->local_nodes < split_min) {
-      d4b_launch_fast(m, du, dAu, 0);
+      if (!have_uh) d4b_launch_fast(m, du, dAu, 0);
       d4b_comm_peer_signal(m, m->stream);
       d4b_launch_fast(m, du, dAu, 1);
       d4b_comm_peer_wait(m, m->stream);
@@ -104,7 +108,7 @@ void d4b_apply_device(d4b_mesh *m, const double *du, double *dAu) {
         ++m->halo_n;
       }
       if (timing) D4B_CUDA(cudaEventRecord(m->halo_ev[0], m->stream));      // 0: apply begins
-      d4b_launch_fast(m, du, dAu, 0);
+      if (!have_uh) d4b_launch_fast(m, du, dAu, 0);
       D4B_CUDA(cudaEventRecord(m->ev_interp, m->stream));
       if (timing) D4B_CUDA(cudaEventRecord(m->halo_ev[1], m->stream));      // 1: uh(local) done
       D4B_CUDA(cudaStreamWaitEvent(m->comm_stream, m->ev_interp, 0));
@@ -125,6 +129,7 @@ void d4b_apply_device(d4b_mesh *m, const double *du, double *dAu) {
   } else {
     // compute stream:  pack | uh(local) | interior elements ............ | join
     // halo stream   :       wait pack | send/recv | wait uh(local) | uh(ghosts) | boundary elements
+    D4B_CHECK(!have_uh, "apply from uh needs the peer-memory halo");
     d4b_comm_exchange_begin(m, du);
     d4b_launch_fast(m, du, dAu, 0);
     D4B_CUDA(cudaEventRecord(m->ev_interp, m->stream));

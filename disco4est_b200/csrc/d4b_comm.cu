@@ -519,6 +519,12 @@ void d4b_comm_peer_begin(d4b_mesh *m) {
   m->d_uhat = P.uh2 + (P.epoch & 1) * P.H;
 }
 
+// the copy of uhat the NEXT epoch will use (the Gauss-resident smoother writes its new iterate there)
+double *d4b_comm_peer_next_copy(d4b_mesh *m) {
+  const D4bPeerHalo &P = m->peer;
+  return P.uh2 + ((P.epoch + 1) & 1) * P.H;
+}
+
 void d4b_comm_peer_signal(d4b_mesh *m, cudaStream_t st) {
   const D4bPeerHalo &P = m->peer;
   if (P.n_nbr == 0) return;

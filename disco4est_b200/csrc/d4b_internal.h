@@ -294,6 +294,7 @@ void d4b_comm_allreduce_sum(d4b_mesh *m, double *d_x, int n);
 bool d4b_comm_peer_ready(d4b_mesh *m);
 void d4b_comm_peer_begin(d4b_mesh *m);    // next epoch: points m->d_uhat at this apply's copy
 void d4b_comm_peer_signal(d4b_mesh *m, cudaStream_t st);   // tell the neighbours this rank's uhat is complete
+double *d4b_comm_peer_next_copy(d4b_mesh *m);
 void d4b_comm_peer_teardown(d4b_mesh *m); // collective; before anything of the mesh is freed
 void d4b_comm_peer_wait(d4b_mesh *m, cudaStream_t st);     // until every neighbour has signalled this epoch
 // d4b_fast.cu: ghost neighbours of the conforming classes addressed through d_ghost_off (offsets relative to uhat)

@@ -362,32 +362,38 @@ void cheby_enqueue(d4b_mesh *m, double *du, const double *drhs, double *dr, int 
   // (u updated in place, no Au vector); otherwise apply + one vector kernel
   const char *nf = getenv("D4B_NO_FUSED_CHEBY");
   const bool fused = m->n_generic == 0 && !m->fast.empty() && !(nf && nf[0] == '1');
-  const bool hat = fused && iter > 0 && m->mpisize == 1 && fused_solvers_allowed(m);
+  // (multi-rank: only with the peer-memory halo -- the neighbours read each other's uh, nodal values never exist)
+  const bool multi = m->mpisize > 1;
+  const bool hat = fused && iter > 0 && fused_solvers_allowed(m) && (!multi || d4b_comm_peer_ready(m));
   if (hat) {
-    if (!m->d_uhat_alt) {
-      m->d_uhat_alt = d4b_dev_alloc<double>(m, (size_t)n);
-      m->d_rhs_hat = d4b_dev_alloc<double>(m, (size_t)n);
-    }
-    double *uh_own = m->d_uhat, *cur = m->d_uhat, *nxt = m->d_uhat_alt;
+    if (!m->d_rhs_hat) m->d_rhs_hat = d4b_dev_alloc<double>(m, (size_t)n);
+    if (!multi && !m->d_uhat_alt) m->d_uhat_alt = d4b_dev_alloc<double>(m, (size_t)n);
+    double *const uh_own = m->d_uhat;
+    // one rank: two private buffers.  Peer halo: the two copies of uhat the neighbours have mapped; every sweep is
+    // one epoch of the flag protocol (signal = "the copy of this epoch is complete", sent when the previous sweep is)
+    if (multi) d4b_comm_peer_begin(m);
+    double *cur = m->d_uhat;
     d4b_launch_basis_change(m, du, cur, true);
     d4b_launch_basis_change(m, drhs, m->d_rhs_hat, true);
     for (int i = 0; i < iter; ++i) {
+      double *nxt = multi ? d4b_comm_peer_next_copy(m) : (cur == uh_own ? m->d_uhat_alt : uh_own);
       m->epi = D4bEpilogue();
       m->epi.mode = 3; m->epi.rhs = m->d_rhs_hat; m->epi.p = p; m->epi.uh_out = nxt;
       if (d_coef) m->epi.coef = d_coef + 2 * i;
       else { m->epi.alpha = h_alpha[i]; m->epi.beta = h_beta[i]; }
       m->d_uhat = cur;
-      d4b_launch_fast(m, nullptr, nullptr, 1);   // the apply kernels only: uh is already there
-      std::swap(cur, nxt);
+      d4b_apply_device(m, nullptr, nullptr);   // the apply kernels only: uh is already there
+      if (multi) { d4b_comm_peer_begin(m); cur = m->d_uhat; }
+      else cur = nxt;
     }
     d4b_launch_basis_change(m, cur, du, false);
     // r = rhs - A u from the uh of the last sweep
     m->epi = D4bEpilogue();
     m->epi.mode = 2; m->epi.rhs = drhs;
     m->d_uhat = cur;
-    d4b_launch_fast(m, nullptr, dr, 1);
+    d4b_apply_device(m, nullptr, dr);
     m->epi = D4bEpilogue();
-    m->d_uhat = uh_own;
+    if (!multi) m->d_uhat = uh_own;
     return;
   }
   for (int i = 0; i < iter; ++i) {
