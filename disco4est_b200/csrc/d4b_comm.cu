@@ -221,15 +221,19 @@ struct PeerAllreduce {
   unsigned long long *slots = nullptr;   // [2][R][kArMax][2]
   unsigned long long **d_peer = nullptr; // [R] slot arrays of all ranks (own included)
   std::vector<void *> mapped;
-  unsigned epoch = 0;
+  unsigned *d_epoch = nullptr;           // call counter, advanced by the kernel itself (a replayed CUDA graph of a
+                                         // V-cycle must not carry the epochs of the cycle it was captured from)
   cudaStream_t last_stream = nullptr;    // calls must execute in issue order: a call on another stream waits for the last
   cudaEvent_t ev = nullptr;
 } g_ar;
 
 __global__ void peer_allreduce_k(double *__restrict__ x, int n, unsigned long long *__restrict__ mine,
-                                 unsigned long long *const *__restrict__ peer, int rank, int R, unsigned epoch) {
+                                 unsigned long long *const *__restrict__ peer, int rank, int R,
+                                 unsigned *__restrict__ epoch_ctr) {
   __shared__ double got[64 * kArMax];
   const int t = threadIdx.x;
+  unsigned epoch = *epoch_ctr + 1;
+  if (epoch == 0) epoch = 1;   // 0 marks an empty slot
   const size_t set = (size_t)(epoch & 1) * R * kArMax * 2;
   if (t < R * n) {
     const int q = t / n, j = t % n;
@@ -254,6 +258,7 @@ __global__ void peer_allreduce_k(double *__restrict__ x, int n, unsigned long lo
     got[q * kArMax + j] = __longlong_as_double((long long)((a & 0xffffffffull) | (b << 32)));
   }
   __syncthreads();
+  if (t == 0) *epoch_ctr = epoch;
   if (t < n) {
     double s = 0.;
     for (int q = 0; q < R; ++q) s += got[q * kArMax + t];
@@ -266,6 +271,7 @@ void peer_allreduce_release() {
   g_ar.mapped.clear();
   if (g_ar.slots) { cudaFree(g_ar.slots); g_ar.slots = nullptr; }
   if (g_ar.d_peer) { cudaFree(g_ar.d_peer); g_ar.d_peer = nullptr; }
+  if (g_ar.d_epoch) { cudaFree(g_ar.d_epoch); g_ar.d_epoch = nullptr; }
   if (g_ar.ev) { cudaEventDestroy(g_ar.ev); g_ar.ev = nullptr; }
   g_ar.last_stream = nullptr;
   cudaGetLastError();
@@ -315,8 +321,9 @@ bool peer_allreduce_ready(cudaStream_t st) {
   D4B_CUDA(cudaMalloc(&g_ar.d_peer, (size_t)R * sizeof(void *)));
   D4B_CUDA(cudaMemcpy(g_ar.d_peer, ptr.data(), (size_t)R * sizeof(void *), cudaMemcpyHostToDevice));
   D4B_CUDA(cudaEventCreateWithFlags(&g_ar.ev, cudaEventDisableTiming));
+  D4B_CUDA(cudaMalloc(&g_ar.d_epoch, sizeof(unsigned)));
+  D4B_CUDA(cudaMemset(g_ar.d_epoch, 0, sizeof(unsigned)));
   g_ar.last_stream = nullptr;
-  g_ar.epoch = 0;
   g_ar.state = 1;
   return true;
 }
@@ -329,10 +336,8 @@ void d4b_comm_allreduce_sum(d4b_mesh *m, double *d_x, int n) {
   D4B_CHECK(g_comm, "d4b_comm_init was not called");
   D4B_CHECK(n >= 1 && n <= kArMax, "all-reduce of %d doubles", n);
   if (peer_allreduce_ready(m->stream)) {
-    ++g_ar.epoch;
-    if (g_ar.epoch == 0) ++g_ar.epoch;   // 0 marks an empty slot
     if (g_ar.last_stream && g_ar.last_stream != m->stream) D4B_CUDA(cudaStreamWaitEvent(m->stream, g_ar.ev, 0));
-    peer_allreduce_k<<<1, 64 * kArMax, 0, m->stream>>>(d_x, n, g_ar.slots, g_ar.d_peer, g_rank, g_size, g_ar.epoch);
+    peer_allreduce_k<<<1, 64 * kArMax, 0, m->stream>>>(d_x, n, g_ar.slots, g_ar.d_peer, g_rank, g_size, g_ar.d_epoch);
     D4B_CUDA(cudaGetLastError());
     D4B_CUDA(cudaEventRecord(g_ar.ev, m->stream));
     g_ar.last_stream = m->stream;
@@ -353,7 +358,12 @@ void d4b_comm_allreduce_sum(d4b_mesh *m, double *d_x, int n) {
 // neighbours signalled k + 1, which they do after their boundary elements of apply k are done.
 namespace {
 
-__global__ void peer_signal_k(unsigned long long *const *__restrict__ dst, int n, unsigned long long epoch) {
+// the epoch is a device counter advanced here, once per apply (or smoother sweep): waits read it back.  Kernel
+// arguments would freeze the epochs of the V-cycle a CUDA graph was captured from into its replays.
+__global__ void peer_signal_k(unsigned long long *const *__restrict__ dst, int n, unsigned long long *__restrict__ ctr) {
+  const unsigned long long epoch = *ctr + 1;
+  __syncthreads();
+  if (threadIdx.x == 0) *ctr = epoch;
   for (int i = threadIdx.x; i < n; i += blockDim.x) {
     __threadfence_system();
     asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(dst[i]), "l"(epoch) : "memory");
@@ -361,7 +371,8 @@ __global__ void peer_signal_k(unsigned long long *const *__restrict__ dst, int n
 }
 
 __global__ void peer_wait_k(const unsigned long long *__restrict__ flags, const int32_t *__restrict__ ranks, int n,
-                            unsigned long long epoch, int rank) {
+                            const unsigned long long *__restrict__ ctr, int rank) {
+  const unsigned long long epoch = *ctr;
   for (int i = threadIdx.x; i < n; i += blockDim.x) {
     const unsigned long long *p = flags + ranks[i];
     const unsigned long long t0 = global_ns();
@@ -402,6 +413,7 @@ void peer_release(d4b_mesh *m) {
   if (P.d_signal) { cudaFree(P.d_signal); P.d_signal = nullptr; }
   if (P.d_wait) { cudaFree(P.d_wait); P.d_wait = nullptr; }
   if (P.d_ghost_uh_off) { cudaFree(P.d_ghost_uh_off); P.d_ghost_uh_off = nullptr; }
+  if (P.d_epoch) { cudaFree(P.d_epoch); P.d_epoch = nullptr; }
   cudaGetLastError();
 }
 
@@ -495,6 +507,8 @@ bool d4b_comm_peer_ready(d4b_mesh *m) {
   for (int64_t &o : off) o -= m->local_nodes;         // mortar kernel: uhat + local_nodes + d_ghost_uh_off[g]
   D4B_CUDA(cudaMalloc(&P.d_ghost_uh_off, off.size() * sizeof(int64_t)));
   D4B_CUDA(cudaMemcpyAsync(P.d_ghost_uh_off, off.data(), off.size() * sizeof(int64_t), cudaMemcpyHostToDevice, m->stream));
+  D4B_CUDA(cudaMalloc(&P.d_epoch, sizeof(unsigned long long)));
+  D4B_CUDA(cudaMemsetAsync(P.d_epoch, 0, sizeof(unsigned long long), m->stream));
   P.n_nbr = (int)m->peers.size();
   std::vector<unsigned long long *> sig(P.n_nbr > 0 ? P.n_nbr : 1, nullptr);
   std::vector<int32_t> wr(P.n_nbr > 0 ? P.n_nbr : 1, 0);
@@ -528,14 +542,14 @@ double *d4b_comm_peer_next_copy(d4b_mesh *m) {
 void d4b_comm_peer_signal(d4b_mesh *m, cudaStream_t st) {
   const D4bPeerHalo &P = m->peer;
   if (P.n_nbr == 0) return;
-  peer_signal_k<<<1, 32, 0, st>>>(P.d_signal, P.n_nbr, P.epoch);
+  peer_signal_k<<<1, 32, 0, st>>>(P.d_signal, P.n_nbr, P.d_epoch);
   D4B_CUDA(cudaGetLastError());
 }
 
 void d4b_comm_peer_wait(d4b_mesh *m, cudaStream_t st) {
   const D4bPeerHalo &P = m->peer;
   if (P.n_nbr == 0) return;
-  peer_wait_k<<<1, 32, 0, st>>>(P.flags, P.d_wait, P.n_nbr, P.epoch, m->mpirank);
+  peer_wait_k<<<1, 32, 0, st>>>(P.flags, P.d_wait, P.n_nbr, P.d_epoch, m->mpirank);
   D4B_CUDA(cudaGetLastError());
 }
 
@@ -571,5 +585,27 @@ static void d4b_comm_release_allreduce() {
     peer_allreduce_release();
   }
   g_ar.state = 0;
-  g_ar.epoch = 0;
 }
+
+// ---- CUDA-graph capture of solver sequences on multi-rank meshes (d4b_mg.cu) --------------------
+// A mesh's applies can be captured when nothing in them calls NCCL and nothing is a kernel argument that must change
+// from replay to replay: peer halo and peer all-reduce active (their epochs are device counters), no phase timing.
+bool d4b_comm_graph_safe(d4b_mesh *m) {
+  if (m->mpisize == 1) return true;
+  static const bool timing = getenv("D4B_HALO_TIMING") && atoi(getenv("D4B_HALO_TIMING")) != 0;
+  return m->peer.state == 1 && g_ar.state == 1 && !timing;
+}
+// the all-reduce orders itself across streams with an event: a capture must neither wait for an event recorded
+// outside it nor leave one behind that is waited for outside (call before BeginCapture and after EndCapture,
+// with the streams involved idle or ordered otherwise)
+void d4b_comm_allreduce_reset_order() { g_ar.last_stream = nullptr; }
+// which copy of uhat the mesh's next apply writes (0 / 1): part of the key of a captured sequence, whose kernels carry
+// the pointers of the copies they were captured with
+int d4b_comm_peer_parity(const d4b_mesh *m) { return m->peer.state == 1 ? (int)((m->peer.epoch + 1) & 1) : 0; }
+// a replayed sequence has advanced the mesh by `epochs` applies
+void d4b_comm_peer_advance(d4b_mesh *m, unsigned long long epochs) {
+  if (m->peer.state != 1 || epochs == 0) return;
+  m->peer.epoch += epochs;
+  m->d_uhat = m->peer.uh2 + (m->peer.epoch & 1) * m->peer.H;
+}
+unsigned long long d4b_comm_peer_epoch(const d4b_mesh *m) { return m->peer.state == 1 ? m->peer.epoch : 0; }

@@ -1461,7 +1461,7 @@ void d4b_launch_fast(d4b_mesh *m, const double *d_u, double *d_Au, int part) {
     for (const D4bFastClass &c : m->fast) {
       D4bHaloWait h;
       h.flags = m->peer.flags; h.ranks = m->peer.d_wait; h.n = c.n_elem > c.n_interior ? m->peer.n_nbr : 0;
-      h.from = c.n_interior; h.epoch = m->peer.epoch;
+      h.from = c.n_interior; h.epoch = m->peer.d_epoch;
 #define D4B_CASE(n) case n: if (c.kind == 1) launch_flat<n>(m, c, d_Au, 0, c.n_elem, &h); else launch_curved<n>(m, c, d_Au, 0, c.n_elem, &h); break;
       switch (c.deg + 1) {
         D4B_CASE(2) D4B_CASE(3) D4B_CASE(4) D4B_CASE(5) D4B_CASE(6) D4B_CASE(7) D4B_CASE(8)

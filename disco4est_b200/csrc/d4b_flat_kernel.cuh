@@ -28,10 +28,11 @@ struct FaceMeta {     // 16 bytes per element face
 __device__ __forceinline__ void halo_wait(const D4bHaloWait &h) {
   for (int i = threadIdx.x; i < h.n; i += blockDim.x) {
     const unsigned long long *p = h.flags + h.ranks[i];
+    const unsigned long long epoch = *h.epoch;
     unsigned long long v, t0 = 0;
     for (int spin = 0;; ++spin) {
       asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-      if (v >= h.epoch) break;
+      if (v >= epoch) break;
       unsigned long long now;
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
       if (spin == 0) t0 = now;

@@ -118,7 +118,8 @@ struct D4bPeerHalo {
   unsigned long long **d_signal = nullptr;    // per neighbour rank: address of its flags[my rank]
   int32_t *d_wait = nullptr;                  // neighbour ranks
   int n_nbr = 0;
-  unsigned long long epoch = 0;
+  unsigned long long epoch = 0;             // host count of applies: which copy is current (parity)
+  unsigned long long *d_epoch = nullptr;    // device count, advanced by the signal kernel, read by the waits
   int64_t *d_ghost_uh_off = nullptr; // per ghost: offset of its uhat lines relative to (uhat + local_nodes)
 };
 
@@ -129,7 +130,7 @@ struct D4bHaloWait {
   const unsigned long long *flags = nullptr;
   const int32_t *ranks = nullptr;
   int n = 0, from = 0;
-  unsigned long long epoch = 0;
+  const unsigned long long *epoch = nullptr;   // device counter of the mesh (advanced by this apply's signal kernel)
 };
 
 struct d4b_mesh {
@@ -295,6 +296,11 @@ bool d4b_comm_peer_ready(d4b_mesh *m);
 void d4b_comm_peer_begin(d4b_mesh *m);    // next epoch: points m->d_uhat at this apply's copy
 void d4b_comm_peer_signal(d4b_mesh *m, cudaStream_t st);   // tell the neighbours this rank's uhat is complete
 double *d4b_comm_peer_next_copy(d4b_mesh *m);
+bool d4b_comm_graph_safe(d4b_mesh *m);
+void d4b_comm_allreduce_reset_order();
+int d4b_comm_peer_parity(const d4b_mesh *m);
+void d4b_comm_peer_advance(d4b_mesh *m, unsigned long long epochs);
+unsigned long long d4b_comm_peer_epoch(const d4b_mesh *m);
 void d4b_comm_peer_teardown(d4b_mesh *m); // collective; before anything of the mesh is freed
 void d4b_comm_peer_wait(d4b_mesh *m, cudaStream_t st);     // until every neighbour has signalled this epoch
 // d4b_fast.cu: ghost neighbours of the conforming classes addressed through d_ghost_off (offsets relative to uhat)

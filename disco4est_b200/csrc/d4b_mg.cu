@@ -14,6 +14,7 @@
 #include <cmath>
 #include <cstring>
 #include <cstdlib>
+#include <cstdio>
 #include "d4b_internal.h"
 
 struct d4b_mg {
@@ -36,10 +37,14 @@ struct d4b_mg {
     double *u = nullptr; const double *rhs = nullptr;
     bool eigs_down = false, eigs_up = false;
     int64_t epoch = 0;             // sum of the levels' config_epoch when the key was created
+    uint64_t parity = 0;           // multi-rank: bit l = which copy of uhat level l writes next (the captured kernels
+                                   // carry the pointers of the copies; d4b_comm_peer_parity)
+    std::vector<unsigned long long> advance;   // multi-rank: applies per level in one cycle (host-side epoch bookkeeping)
     int seen = 0;
     cudaGraphExec_t exec = nullptr;
   };
   std::vector<CycleGraph> graphs;
+  int64_t n_replays = 0;
   double *d_r2 = nullptr;        // squared residual of the last cycle
   cudaStream_t cap_stream = nullptr;
   // Galerkin mass term of the coarse levels (d4b_mg_set_coarse_mass): per level l >= 1 a prolonged copy of the
@@ -360,16 +365,25 @@ double vcycle_device(d4b_mg *g, double *u_top, const double *rhs_top) {
     }
     d4b_dot_async(mt, g->d_r[top], g->d_r[top], mt->local_nodes, g->d_r2);
   };
-  // graph replay: only when the sequence is static (no host polling, no second stream)
+  // graph replay: only when the sequence is static (no host polling).  Multi-rank meshes qualify when the halo
+  // and the all-reduces run over peer memory: no NCCL call in the sequence, the epochs of both flag protocols are
+  // device counters, and the second stream of the large levels is forked from and joined to the captured one
   bool graphable = g->prm.bottom_solver == 1 && !(getenv("D4B_MG_GRAPH") && atoi(getenv("D4B_MG_GRAPH")) == 0);
-  for (int l = 0; l <= top && graphable; ++l) graphable = g->mesh[l]->mpisize == 1;
+  for (int l = 0; l <= top && graphable; ++l) graphable = d4b_comm_graph_safe(g->mesh[l]);
+  bool multi = false;
+  for (int l = 0; l <= top; ++l) multi = multi || g->mesh[l]->mpisize > 1;
+  if (multi && getenv("D4B_MG_GRAPH_MULTI") && atoi(getenv("D4B_MG_GRAPH_MULTI")) == 0) graphable = false;
   d4b_mg::CycleGraph *cg = nullptr;
   int64_t epoch = 0;
-  for (int l = 0; l <= top; ++l) epoch += g->mesh[l]->config_epoch;
+  uint64_t parity = 0;
+  for (int l = 0; l <= top; ++l) {
+    epoch += g->mesh[l]->config_epoch;
+    parity |= (uint64_t)d4b_comm_peer_parity(g->mesh[l]) << l;
+  }
   if (graphable) {
     for (auto &c2 : g->graphs)
       if (c2.u == u_top && c2.rhs == rhs_top && c2.eigs_down == eigs_down && c2.eigs_up == eigs_up &&
-          c2.epoch == epoch) cg = &c2;
+          c2.epoch == epoch && c2.parity == parity) cg = &c2;
     if (!cg) {
       if (g->graphs.size() >= 8) {   // vectors keep changing: stop caching
         for (auto &c2 : g->graphs) if (c2.exec) cudaGraphExecDestroy(c2.exec);
@@ -378,10 +392,19 @@ double vcycle_device(d4b_mg *g, double *u_top, const double *rhs_top) {
       g->graphs.emplace_back();
       cg = &g->graphs.back();
       cg->u = u_top; cg->rhs = rhs_top; cg->eigs_down = eigs_down; cg->eigs_up = eigs_up; cg->epoch = epoch;
+      cg->parity = parity;
     }
   }
+  if (getenv("D4B_MG_DEBUG"))
+    fprintf(stderr, "[d4b mg] cycle %d: graphable %d key parity %llx config %lld -> %s (cached keys %zu)\n", vc, (int)graphable,
+            (unsigned long long)parity, (long long)epoch,
+            !cg ? "eager (not graphable)" : cg->exec ? "replay" : cg->seen >= 1 ? "record" : "eager (first time)", g->graphs.size());
+  std::vector<unsigned long long> e0(g->n_levels);
+  for (int l = 0; l <= top; ++l) e0[l] = d4b_comm_peer_epoch(g->mesh[l]);
   if (cg && cg->exec) {
     D4B_CUDA(cudaGraphLaunch(cg->exec, s));
+    ++g->n_replays;
+    for (int l = 0; l <= top; ++l) d4b_comm_peer_advance(g->mesh[l], cg->advance[l]);   // what the eager cycle does on the host
   } else if (cg && cg->seen >= 1) {
     // every lazy allocation and kernel attribute was set by the first, eager cycle with this key
     // captured on a private stream (the caller's may be the legacy default stream, which cannot be
@@ -390,10 +413,14 @@ double vcycle_device(d4b_mg *g, double *u_top, const double *rhs_top) {
     if (!g->cap_stream) D4B_CUDA(cudaStreamCreateWithFlags(&g->cap_stream, cudaStreamNonBlocking));
     D4B_CUDA(cudaStreamSynchronize(s));
     for (int l = 0; l <= top; ++l) g->mesh[l]->stream = g->cap_stream;
+    d4b_comm_allreduce_reset_order();
     D4B_CUDA(cudaStreamBeginCapture(g->cap_stream, cudaStreamCaptureModeThreadLocal));
     enqueue(g->cap_stream);
     D4B_CUDA(cudaStreamEndCapture(g->cap_stream, &graph));
+    d4b_comm_allreduce_reset_order();
     for (int l = 0; l <= top; ++l) g->mesh[l]->stream = s;
+    cg->advance.resize(g->n_levels);   // the capture ran the host-side bookkeeping of one cycle
+    for (int l = 0; l <= top; ++l) cg->advance[l] = d4b_comm_peer_epoch(g->mesh[l]) - e0[l];
     D4B_CUDA(cudaGraphInstantiate(&cg->exec, graph, 0));
     D4B_CUDA(cudaGraphDestroy(graph));
     D4B_CUDA(cudaGraphLaunch(cg->exec, s));
@@ -652,6 +679,7 @@ extern "C" int32_t d4b_mg_solve(d4b_mg_t *g, double *u, const double *rhs, doubl
   return g->vcycle_num_finished;
 }
 
+extern "C" int64_t d4b_mg_graph_replays(const d4b_mg_t *g) { return g->n_replays; }
 extern "C" void d4b_mg_get_eigs(const d4b_mg_t *g, double *eigs_out) {
   D4B_CUDA(cudaMemcpy(eigs_out, g->d_eigs, (size_t)g->n_levels * sizeof(double), cudaMemcpyDeviceToHost));
 }

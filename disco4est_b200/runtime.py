@@ -31,7 +31,7 @@ EXPORTS = [
     "d4b_interp_to_quad", "d4b_apply_galerkin", "d4b_apply_mass", "d4b_mesh_set_mass_diag", "d4b_build_rhs", "d4b_estimator_bi",
     "d4b_vec_dot", "d4b_vec_axpy", "d4b_vec_xpby", "d4b_vec_scale", "d4b_vec_dot_noalloc",
     "d4b_cg_eigs", "d4b_cheby_smooth",
-    "d4b_mg_create", "d4b_mg_destroy", "d4b_mg_vcycle", "d4b_mg_solve", "d4b_mg_get_eigs", "d4b_mg_restrict",
+    "d4b_mg_create", "d4b_mg_destroy", "d4b_mg_vcycle", "d4b_mg_solve", "d4b_mg_get_eigs", "d4b_mg_graph_replays", "d4b_mg_restrict",
     "d4b_mg_prolong",
     "d4b_cg_solve", "d4b_fcg_solve",
     "d4b_mesh_set_nonlinear_term", "d4b_mesh_linearize", "d4b_build_residual", "d4b_mg_set_coarse_mass", "d4b_newton_solve",
@@ -107,6 +107,9 @@ def load_library():
     L.d4b_mg_solve.restype = C.c_int32
     L.d4b_mg_solve.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     L.d4b_mg_get_eigs.argtypes = [C.c_void_p, C.c_void_p]
+    if hasattr(L, "d4b_mg_graph_replays"):
+        L.d4b_mg_graph_replays.restype = C.c_int64
+        L.d4b_mg_graph_replays.argtypes = [C.c_void_p]
     L.d4b_mg_restrict.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]
     L.d4b_mg_prolong.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]
     L.d4b_cg_solve.restype = C.c_int32
@@ -180,6 +183,10 @@ class Multigrid:
         e = np.zeros(len(self.meshes))
         self.L.d4b_mg_get_eigs(self.h, e.ctypes.data)
         return e
+
+    def graph_replays(self):
+        """V-cycles replayed from a recorded CUDA graph so far"""
+        return int(self.L.d4b_mg_graph_replays(self.h))
 
     def restrict(self, coarse_level, fine, coarse):
         self.L.d4b_mg_restrict(self.h, coarse_level, _ptr(fine), _ptr(coarse))

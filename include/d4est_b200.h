@@ -457,6 +457,11 @@ double    d4b_mg_vcycle(d4b_mg_t *mg, double *u, const double *rhs);
 int32_t   d4b_mg_solve(d4b_mg_t *mg, double *u, const double *rhs, double *r2_history);
 /* largest-eigenvalue estimates the smoother used last, [n_levels]           */
 void      d4b_mg_get_eigs(const d4b_mg_t *mg, double *eigs_out);
+/* V-cycles that were replayed from a recorded CUDA graph instead of being enqueued kernel by kernel (a cycle is
+ * recorded the second time it is asked for with the same vectors; device plumbing of d4est_solver_multigrid_vcycle,
+ * src/Solver/d4est_solver_multigrid.c:751-1349; D4B_MG_GRAPH=0 / D4B_MG_GRAPH_MULTI=0 switch it off for all /
+ * multi-rank hierarchies)                                                                                     */
+int64_t   d4b_mg_graph_replays(const d4b_mg_t *mg);
 /* inter-grid transfer alone (tests): coarse level l <- / -> fine level l+1;
  * device or host pointers                                                    */
 void      d4b_mg_restrict(d4b_mg_t *mg, int32_t coarse_level, const double *fine, double *coarse);

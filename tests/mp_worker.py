@@ -60,8 +60,60 @@ def exchange_host(A, ul, dist, torch):
     return ug
 
 
+def multigrid_main(level, p):
+    """mode "mg", one GPU per rank: a brick hierarchy split over the ranks; V-cycles enqueued kernel by kernel against
+    V-cycles replayed from a CUDA graph recorded on every rank (peer-memory halo and all-reduce: nothing in the
+    sequence calls NCCL, the epochs of the flag protocols are device counters) -- bit-equal residual histories and
+    iterates, and the replays must actually have happened."""
+    import torch
+    import torch.distributed as dist
+    from disco4est_b200 import Mesh
+    from disco4est_b200.brick import brick_hierarchy, trees_for_world
+    from disco4est_b200.runtime import Multigrid, cheby_params, comm_init_from_torch, comm_destroy
+
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", rank))
+    comm_init_from_torch(rank)
+    trees = trees_for_world(world)
+    out = {}
+    for graph in ("0", "1"):
+        os.environ["D4B_MG_GRAPH"] = graph
+        descs, transfers = brick_hierarchy(level, p, rank=rank, world=world, trees=trees, geometry=False)
+        meshes = [Mesh(d, device=rank, geom=g) for d, g in descs]
+        mg = Multigrid(meshes, transfers, cheby_params(4, 5, 30.0, 1.0), vcycle_imax=1, bottom_solver="cheby",
+                       bottom_cheby=cheby_params(5, 6, 30.0, 1.0))
+        n = meshes[-1].n
+        rhs = torch.rand(n, dtype=torch.float64, device="cuda", generator=torch.Generator(device="cuda").manual_seed(5 + rank))
+        u = torch.zeros_like(rhs)
+        v = torch.empty_like(rhs)
+        hist = []
+        for k in range(12):
+            hist.append(mg.vcycle(u, rhs))
+            if k == 7:
+                meshes[-1].apply(u, v)   # an apply between two cycles flips the parity of the top level's uhat copies
+        meshes[-1].sync()
+        assert all(mm.halo_mode() == "peer" for mm in meshes), [mm.halo_mode() for mm in meshes]
+        replays = mg.graph_replays()
+        assert (replays > 0) == (graph == "1"), "graph=%s but %d replays" % (graph, replays)
+        out[graph] = (hist, u.clone())
+        mg.close()
+        for mm in meshes:
+            mm.close()
+    assert out["0"][0] == out["1"][0], "residual histories differ: %r %r" % (out["0"][0], out["1"][0])
+    assert torch.equal(out["0"][1], out["1"][1])
+    assert out["0"][0][-1] < 1e-3 * out["0"][0][0]
+    if rank == 0:
+        print("MP_RESULT mode=mg world=%d r2 %.3e -> %.3e" % (world, out["0"][0][0], out["0"][0][-1]), flush=True)
+    comm_destroy()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
 def main():
     mode, mesh_arg, p = sys.argv[1], sys.argv[2], int(sys.argv[3])
+    if mode == "mg":
+        return multigrid_main(int(mesh_arg), p)
     import torch
     import torch.distributed as dist
     from disco4est_b200.brick import brick_desc, partition_offsets, trees_for_world

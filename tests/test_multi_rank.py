@@ -75,3 +75,13 @@ def test_two_gpu_hp_mesh_matches_oracle(case):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     run_ranks("nccl", 2, "golden:" + case, 0)
+
+
+@pytest.mark.gpu
+def test_two_gpu_vcycle_graph_replay():
+    """multi-rank V-cycles replayed from a CUDA graph == enqueued kernel by kernel, bit for bit"""
+    import torch
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    run_ranks("mg", 2, 3, 3)
