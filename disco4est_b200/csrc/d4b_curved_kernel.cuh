@@ -77,35 +77,35 @@ __device__ __forceinline__ double face_grad_t(const FastTab &T, double a, double
   return s;
 }
 
-// One face at this thread's face Gauss point (x, y); ND = my normal direction (compile time).  Every lane of
-// the warp must call it (shuffles); lanes without an element carry zeros.
-// OWN_T: the caller supplies the own tangential derivatives (dmx, dmy in) and takes the two tangential test
-// weights back (w1, w2 out) instead of their transposed face derivative being folded into ve.
-template <int N, int ND, bool OWN_T = false>
-__device__ __forceinline__ void curved_face(const CurvedArgs &a, const FastTab &T, const FaceMeta &fm, bool active,
-                                            int64_t ns, int base, int x, int y, double trm, double dnm, double wxy,
-                                            double &ve, double &vd, double dmx = 0., double dmy = 0.,
-                                            double *w1 = nullptr, double *w2 = nullptr) {
+// What one face needs from memory at this thread's face Gauss point (x, y): its record (own view) and the neighbour's
+// trace / normal derivative.  Split from the arithmetic so that the loads of BOTH faces of a pair are in flight
+// before the first shuffle: the shuffles are convergence points, and with load and use in one function the six
+// faces' L2 latencies were paid one after the other (a quarter of the kernel's stall samples, profiles/
+// r02_ncu_curved_p3_sphere_stalls.txt).
+struct CurvedFaceData {
+  double Am[3], Ap[3], S, trp, dnp;
+};
+template <int N>
+__device__ __forceinline__ void curved_face_load(const CurvedArgs &a, const FastTab &T, const FaceMeta &fm, bool active,
+                                                 int64_t ns, int x, int y, CurvedFaceData &d) {
   constexpr int NN = N * N;
-  constexpr int T1 = (ND == 0) ? 1 : 0, T2 = (ND == 2) ? 1 : 2;   // my tangential directions, x <-> T1, y <-> T2
   const int code = fm.code;
   const bool own = code & kOwn, interior = fm.nbr != kNoNbr;
   const bool swp = code & (4 << 3), frow = code & (2 << 3), fcol = code & (1 << 3);
   int row = swp ? x : y, col = swp ? y : x;
   row = frow ? N - 1 - row : row;
   col = fcol ? N - 1 - col : col;
-  double Am[3] = {0., 0., 0.}, Ap[3] = {0., 0., 0.}, S = 0., trp = 0., dnp = 0.;
+#pragma unroll
+  for (int l = 0; l < 3; ++l) { d.Am[l] = 0.; d.Ap[l] = 0.; }
+  d.S = 0.; d.trp = 0.; d.dnp = 0.;
   const int ndp = (code >> 1) & 3, sp = code & 1;
   if (active) {
     const int k = own ? (x + N * y) : (col + N * row);
     const double *r = a.FF + (size_t)fm.rec + k;
+    double rp[3], rq[3];
 #pragma unroll
-    for (int l = 0; l < 3; ++l) {
-      const double p = r[l * NN], q = r[(3 + l) * NN];
-      Am[l] = own ? p : -q;
-      Ap[l] = own ? q : -p;
-    }
-    S = r[6 * NN];
+    for (int l = 0; l < 3; ++l) { rp[l] = r[l * NN]; rq[l] = r[(3 + l) * NN]; }
+    d.S = r[6 * NN];
     // neighbour line normal to its face through its point (col, row), read from the face inwards
     const int stride = (ndp == 0) ? 1 : ((ndp == 1) ? N : NN);
     const int b0 = (ndp == 0) ? (N * col + NN * row) : ((ndp == 1) ? (col + NN * row) : (col + N * row));
@@ -115,9 +115,31 @@ __device__ __forceinline__ void curved_face(const CurvedArgs &a, const FastTab &
 #pragma unroll
     for (int l = 0; l < N; ++l) v[l] = p[l * step];
 #pragma unroll
-    for (int l = 0; l < N; ++l) { trp += T.e[0][l] * v[l]; dnp += T.d[0][l] * v[l]; }
-    dnp = sp ? -dnp : dnp;
+    for (int l = 0; l < 3; ++l) {
+      d.Am[l] = own ? rp[l] : -rq[l];
+      d.Ap[l] = own ? rq[l] : -rp[l];
+    }
+#pragma unroll
+    for (int l = 0; l < N; ++l) { d.trp += T.e[0][l] * v[l]; d.dnp += T.d[0][l] * v[l]; }
+    d.dnp = sp ? -d.dnp : d.dnp;
   }
+}
+
+// The arithmetic of one face; ND = my normal direction (compile time).  Every lane of the warp must call it
+// (shuffles); lanes without an element carry zeros.
+// OWN_T: the caller supplies the own tangential derivatives (dmx, dmy in) and takes the two tangential test
+// weights back (w1, w2 out) instead of their transposed face derivative being folded into ve.
+template <int N, int ND, bool OWN_T = false>
+__device__ __forceinline__ void curved_face(const FastTab &T, const FaceMeta &fm, const CurvedFaceData &d, int base, int x,
+                                            int y, double trm, double dnm, double wxy, double &ve, double &vd,
+                                            double dmx = 0., double dmy = 0., double *w1 = nullptr, double *w2 = nullptr) {
+  constexpr int T1 = (ND == 0) ? 1 : 0, T2 = (ND == 2) ? 1 : 2;   // my tangential directions, x <-> T1, y <-> T2
+  const int code = fm.code;
+  const bool interior = fm.nbr != kNoNbr;
+  const bool swp = code & (4 << 3), frow = code & (2 << 3), fcol = code & (1 << 3);
+  const int ndp = (code >> 1) & 3;
+  const double *Am = d.Am, *Ap = d.Ap;
+  const double S = d.S, trp = d.trp, dnp = d.dnp;
   // tangential derivatives on the face, both traces, in my frame
   double dpx, dpy;
   if (!OWN_T) face_grad<N>(T, trm, base, x, y, dmx, dmy);
@@ -157,6 +179,10 @@ __global__ void __launch_bounds__(CurvedShflCfg<N>::THREADS, CurvedShflCfg<N>::M
   FaceMeta *META = reinterpret_cast<FaceMeta *>(FB + 12 * NN);
   const int64_t ns = !active ? 0 : a.ns_linear ? a.ns0 + (int64_t)ei * N3 : a.elem_ns[ei];
   const double wxy = T.w[lx] * T.w[ly];
+  // both faces of a pair loaded before the first is used: +3 % at N = 2, 3, 5; at N = 4 the 18 extra live registers
+  // spill under the 128-register cap of 16 blocks per SM and fewer blocks cost more than the latency
+  // (profiles/r02_curved_hoist_ab.txt)
+  constexpr bool kHoist = N != 4;
   if (threadIdx.x == 0 && a.prefetch) {
     constexpr unsigned kBlockBytes = C::EPB * 6 * N3 * sizeof(double);
     const int e0 = a.first + blk * C::EPB, left = a.n_elem - e0;
@@ -199,9 +225,14 @@ __global__ void __launch_bounds__(CurvedShflCfg<N>::THREADS, CurvedShflCfg<N>::M
       }
     }
     double ve, vd;
-    curved_face<N, 1>(a, T, active ? META[2] : zero_meta, active, ns, base, lx, ly, t2, n2, wxy, ve, vd);
+    const FaceMeta fa = active ? META[2] : zero_meta, fb = active ? META[3] : zero_meta;
+    CurvedFaceData da, db;
+    curved_face_load<N>(a, T, fa, active, ns, lx, ly, da);
+    if (kHoist) curved_face_load<N>(a, T, fb, active, ns, lx, ly, db);
+    curved_face<N, 1>(T, fa, da, base, lx, ly, t2, n2, wxy, ve, vd);
     if (active) { FB[(2 * 2 + 0) * NN + lt] = ve; FB[(2 * 2 + 1) * NN + lt] = vd; }
-    curved_face<N, 1>(a, T, active ? META[3] : zero_meta, active, ns, base, lx, ly, t3, n3, wxy, ve, vd);
+    if (!kHoist) curved_face_load<N>(a, T, fb, active, ns, lx, ly, db);
+    curved_face<N, 1>(T, fb, db, base, lx, ly, t3, n3, wxy, ve, vd);
     if (active) { FB[(3 * 2 + 0) * NN + lt] = ve; FB[(3 * 2 + 1) * NN + lt] = vd; }
   }
   {   // R-orientation: (b,c) = (lx,ly), line along a: gradient, faces 0/1
@@ -224,9 +255,14 @@ __global__ void __launch_bounds__(CurvedShflCfg<N>::THREADS, CurvedShflCfg<N>::M
       }
     }
     double ve, vd;
-    curved_face<N, 0>(a, T, active ? META[0] : zero_meta, active, ns, base, lx, ly, t0, n0, wxy, ve, vd);
+    const FaceMeta fa = active ? META[0] : zero_meta, fb = active ? META[1] : zero_meta;
+    CurvedFaceData da, db;
+    curved_face_load<N>(a, T, fa, active, ns, lx, ly, da);
+    if (kHoist) curved_face_load<N>(a, T, fb, active, ns, lx, ly, db);
+    curved_face<N, 0>(T, fa, da, base, lx, ly, t0, n0, wxy, ve, vd);
     if (active) { FB[(0 * 2 + 0) * NN + lt] = ve; FB[(0 * 2 + 1) * NN + lt] = vd; }
-    curved_face<N, 0>(a, T, active ? META[1] : zero_meta, active, ns, base, lx, ly, t1, n1, wxy, ve, vd);
+    if (!kHoist) curved_face_load<N>(a, T, fb, active, ns, lx, ly, db);
+    curved_face<N, 0>(T, fb, db, base, lx, ly, t1, n1, wxy, ve, vd);
     if (active) { FB[(1 * 2 + 0) * NN + lt] = ve; FB[(1 * 2 + 1) * NN + lt] = vd; }
   }
   __syncwarp();
@@ -259,10 +295,13 @@ __global__ void __launch_bounds__(CurvedShflCfg<N>::THREADS, CurvedShflCfg<N>::M
       }
     }
     double ve0, vd0, ve1, vd1, w14, w24, w15, w25;
-    curved_face<N, 2, true>(a, T, active ? META[4] : zero_meta, active, ns, base, lx, ly, tr4, dn4, wxy, ve0, vd0, d14, d24,
-                            &w14, &w24);
-    curved_face<N, 2, true>(a, T, active ? META[5] : zero_meta, active, ns, base, lx, ly, tr5, dn5, wxy, ve1, vd1, d15, d25,
-                            &w15, &w25);
+    const FaceMeta fa = active ? META[4] : zero_meta, fb = active ? META[5] : zero_meta;
+    CurvedFaceData da, db;
+    curved_face_load<N>(a, T, fa, active, ns, lx, ly, da);
+    if (kHoist) curved_face_load<N>(a, T, fb, active, ns, lx, ly, db);
+    curved_face<N, 2, true>(T, fa, da, base, lx, ly, tr4, dn4, wxy, ve0, vd0, d14, d24, &w14, &w24);
+    if (!kHoist) curved_face_load<N>(a, T, fb, active, ns, lx, ly, db);
+    curved_face<N, 2, true>(T, fb, db, base, lx, ly, tr5, dn5, wxy, ve1, vd1, d15, d25, &w15, &w25);
     if (active) {
       double ft[N];
       const double *G = a.FG + (size_t)ei * (6 * N3) + lt;
