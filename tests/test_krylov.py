@@ -111,3 +111,35 @@ def test_gpu_fcg_matches_reference(gpu_case):
     du = torch.zeros(rhs.size, dtype=torch.float64, device="cuda")
     its2, _ = mesh.fcg_solve(du, torch.from_numpy(rhs).cuda(), int(imax), rtol, atol, pc=mg)
     assert its2 == its and np.array_equal(du.cpu().numpy(), u)
+
+
+@pytest.mark.gpu
+def test_blas1_kernels_direct(golden):
+    """d4b_vec_axpy / xpby / scale / dot against numpy (d4est_linalg_vec_axpy: y += a x; _xpby: y = x + b y;
+    _scale: x *= a; src/LinearAlgebra/d4est_linalg.c:179-236), a length that is not a multiple of any block size"""
+    import ctypes as C
+
+    import torch
+    from disco4est_b200 import Mesh
+
+    m = Mesh(golden(CASE))
+    n = 100003
+    rng = np.random.default_rng(3)
+    x, y = rng.standard_normal(n), rng.standard_normal(n)
+    dx, dy = torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda()
+    L, h = m.L, m.h
+    L.d4b_vec_axpy(h, 0.37, C.c_void_p(dx.data_ptr()), C.c_void_p(dy.data_ptr()), n)
+    m.sync()
+    y = y + 0.37 * x
+    assert np.allclose(dy.cpu().numpy(), y, rtol=1e-15, atol=1e-15)
+    L.d4b_vec_xpby(h, C.c_void_p(dx.data_ptr()), -1.25, C.c_void_p(dy.data_ptr()), n)
+    m.sync()
+    y = x - 1.25 * y
+    assert np.allclose(dy.cpu().numpy(), y, rtol=1e-15, atol=1e-15)
+    L.d4b_vec_scale(h, 3.0, C.c_void_p(dy.data_ptr()), n)
+    m.sync()
+    y = 3.0 * y
+    assert np.allclose(dy.cpu().numpy(), y, rtol=1e-15, atol=1e-15)
+    d = float(L.d4b_vec_dot(h, C.c_void_p(dx.data_ptr()), C.c_void_p(dy.data_ptr()), n))
+    assert abs(d - float(x @ y)) <= 1e-12 * float(np.abs(x) @ np.abs(y))
+    m.close()
