@@ -179,6 +179,11 @@ def cpu_baseline(deg, with_plugin=True):
                   "e2e_GDOF_per_s_best_of_5": r["local_nodes"] / b["t_apply_b200_host_vectors_best_s"] / 1e9,
                   "ms_per_call": 1e3 * b["t_apply_b200_host_vectors_s"],
                   "reference_cpu_ms_per_call": 1e3 * t}
+        if "t_apply_b200_pinned_vectors_s" in b:   # the same vectors page-locked once (d4est_b200_pin_vectors)
+            plugin["pinned_vectors"] = {"e2e_GDOF_per_s": r["local_nodes"] / b["t_apply_b200_pinned_vectors_s"] / 1e9,
+                                        "e2e_GDOF_per_s_best_of_5": r["local_nodes"] / b["t_apply_b200_pinned_vectors_best_s"] / 1e9,
+                                        "ms_per_call": 1e3 * b["t_apply_b200_pinned_vectors_s"],
+                                        "parity_rel_l2_vs_reference_cpu_apply": b["b200_apply_pinned_rel_l2"]}
         return cpu, plugin
     level = 4 if deg <= 3 else 3
     if os.path.exists(REF_DRIVER):

@@ -390,6 +390,26 @@ d4est_b200_comm_finalize (void)
 }
 #endif
 
+#ifndef D4EST_B200_ADAPTER_NO_DEVICE
+void
+d4est_b200_pin_vectors (d4est_elliptic_data_t * prob_vecs)
+{
+  double *v[3] = { prob_vecs->u, prob_vecs->Au, prob_vecs->rhs };
+  for (int i = 0; i < 3; i++)
+    if (v[i] != NULL && (i == 0 || (v[i] != v[0] && (i == 1 || v[i] != v[1]))))
+      (void) d4b_host_pin (v[i], (int64_t) prob_vecs->local_nodes * (int64_t) sizeof (double));
+}
+
+void
+d4est_b200_unpin_vectors (d4est_elliptic_data_t * prob_vecs)
+{
+  double *v[3] = { prob_vecs->u, prob_vecs->Au, prob_vecs->rhs };
+  for (int i = 0; i < 3; i++)
+    if (v[i] != NULL && (i == 0 || (v[i] != v[0] && (i == 1 || v[i] != v[1]))))
+      (void) d4b_host_unpin (v[i]);
+}
+#endif
+
 d4est_b200_ctx_t *
 d4est_b200_ctx_new (d4est_laplacian_flux_data_t * flux_data)
 {

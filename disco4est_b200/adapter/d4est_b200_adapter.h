@@ -210,6 +210,13 @@ void d4est_b200_set_nonlinear_term(d4est_b200_ctx_t *ctx, const d4b_nonlinear_de
 void d4est_b200_comm_init_from_p4est(p4est_t *p4est, int device);
 void d4est_b200_comm_finalize(void);
 
+/* The solver vectors of the reference are P4EST_ALLOC'd (pageable): page-lock prob_vecs->u / Au / rhs (those that are
+ * set, local_nodes doubles each) once after they are allocated, so that d4est_b200_apply_lhs moves them at link speed
+ * and can overlap the two directions (d4b_host_pin).  d4est_b200_unpin_vectors before they are freed.  Optional:
+ * without it everything works on pageable memory, more slowly.                                                   */
+void d4est_b200_pin_vectors(d4est_elliptic_data_t *prob_vecs);
+void d4est_b200_unpin_vectors(d4est_elliptic_data_t *prob_vecs);
+
 d4est_b200_ctx_t *d4est_b200_ctx_new(d4est_laplacian_flux_data_t *flux_data);
 void d4est_b200_ctx_destroy(d4est_b200_ctx_t *ctx);
 /* forget (and free) every cached device mesh: the next call re-flattens and uploads */

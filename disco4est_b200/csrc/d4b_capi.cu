@@ -343,6 +343,18 @@ extern "C" void d4b_mesh_set_mass_diag(d4b_mesh_t *m, const double *jac_quad) {
   D4B_CUDA(cudaStreamSynchronize(m->stream));
 }
 
+extern "C" int32_t d4b_host_pin(void *ptr, int64_t bytes) {
+  if (!ptr || bytes <= 0) return (int32_t)cudaErrorInvalidValue;
+  const cudaError_t e = cudaHostRegister(ptr, (size_t)bytes, cudaHostRegisterPortable);
+  if (e != cudaSuccess) cudaGetLastError();
+  return (int32_t)e;
+}
+extern "C" int32_t d4b_host_unpin(void *ptr) {
+  const cudaError_t e = cudaHostUnregister(ptr);
+  if (e != cudaSuccess) cudaGetLastError();
+  return (int32_t)e;
+}
+
 extern "C" void d4b_sync(d4b_mesh_t *m) { D4B_CUDA(cudaStreamSynchronize(m->stream)); }
 extern "C" void d4b_set_stream(d4b_mesh_t *m, void *cuda_stream) {
   D4B_CUDA(cudaStreamSynchronize(m->stream));

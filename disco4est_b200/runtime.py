@@ -26,7 +26,7 @@ _I32P_T = C.POINTER(C.c_int32)
 EXPORTS = [
     "d4b_set_abort_hook", "d4b_abi_version", "d4b_device_count", "d4b_init",
     "d4b_geom_compute", "d4b_mesh_create_with_geometry",
-    "d4b_mesh_create", "d4b_mesh_destroy", "d4b_mesh_local_nodes", "d4b_mesh_device_bytes", "d4b_mesh_fast_elements", "d4b_mesh_flat_elements", "d4b_mesh_hp_elements", "d4b_mesh_launches_per_apply", "d4b_mesh_halo_mode",
+    "d4b_mesh_create", "d4b_mesh_destroy", "d4b_mesh_local_nodes", "d4b_mesh_device_bytes", "d4b_mesh_fast_elements", "d4b_mesh_flat_elements", "d4b_mesh_hp_elements", "d4b_mesh_launches_per_apply", "d4b_mesh_halo_mode", "d4b_host_pin", "d4b_host_unpin",
     "d4b_apply", "d4b_apply_stiffness", "d4b_sync", "d4b_set_stream",
     "d4b_interp_to_quad", "d4b_apply_galerkin", "d4b_apply_mass", "d4b_mesh_set_mass_diag", "d4b_build_rhs", "d4b_estimator_bi",
     "d4b_vec_dot", "d4b_vec_axpy", "d4b_vec_xpby", "d4b_vec_scale", "d4b_vec_dot_noalloc",

@@ -188,6 +188,13 @@ int64_t     d4b_mesh_flat_elements(const d4b_mesh_t *mesh);
 /* elements taken by the hp mortar kernel: collocated quadrature (deg_quad == deg) on the element
  * and its face neighbours, faces between unequal degrees and / or hanging faces             */
 int64_t     d4b_mesh_hp_elements(const d4b_mesh_t *mesh);
+/* Page-lock `bytes` of host memory at `ptr` (cudaHostRegister) / release it again.  The reference's solver vectors are
+ * P4EST_ALLOC'd, i.e. pageable (d4est_elliptic_data_t, src/EllipticSystem/d4est_elliptic_data.h): a host-pointer
+ * d4b_apply then stages every copy through the driver's bounce buffer and the chunked host apply cannot overlap its
+ * transfers.  Pinned once after allocation they go at link speed.  Returns 0 on success, a CUDA error code otherwise
+ * (the vectors then simply stay pageable); d4b_host_unpin before the memory is freed.                             */
+int32_t     d4b_host_pin(void *ptr, int64_t bytes);
+int32_t     d4b_host_unpin(void *ptr);
 /* CUDA kernels one d4b_apply launches on this mesh (for launch accounting)  */
 int32_t     d4b_mesh_launches_per_apply(const d4b_mesh_t *mesh);
 /* How this mesh's applies obtain ghost data (replaces d4est_ghost_data_exchange, src/Mesh/d4est_ghost_data.c:142-255):

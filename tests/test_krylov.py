@@ -131,15 +131,15 @@ def test_blas1_kernels_direct(golden):
     L.d4b_vec_axpy(h, 0.37, C.c_void_p(dx.data_ptr()), C.c_void_p(dy.data_ptr()), n)
     m.sync()
     y = y + 0.37 * x
-    assert np.allclose(dy.cpu().numpy(), y, rtol=1e-15, atol=1e-15)
+    assert np.allclose(dy.cpu().numpy(), y, rtol=1e-14, atol=1e-14)   # (FMA on the device, separate multiply and add in numpy)
     L.d4b_vec_xpby(h, C.c_void_p(dx.data_ptr()), -1.25, C.c_void_p(dy.data_ptr()), n)
     m.sync()
     y = x - 1.25 * y
-    assert np.allclose(dy.cpu().numpy(), y, rtol=1e-15, atol=1e-15)
+    assert np.allclose(dy.cpu().numpy(), y, rtol=1e-14, atol=1e-14)   # (FMA on the device, separate multiply and add in numpy)
     L.d4b_vec_scale(h, 3.0, C.c_void_p(dy.data_ptr()), n)
     m.sync()
     y = 3.0 * y
-    assert np.allclose(dy.cpu().numpy(), y, rtol=1e-15, atol=1e-15)
+    assert np.allclose(dy.cpu().numpy(), y, rtol=1e-14, atol=1e-14)   # (FMA on the device, separate multiply and add in numpy)
     d = float(L.d4b_vec_dot(h, C.c_void_p(dx.data_ptr()), C.c_void_p(dy.data_ptr()), n))
     assert abs(d - float(x @ y)) <= 1e-12 * float(np.abs(x) @ np.abs(y))
     m.close()
