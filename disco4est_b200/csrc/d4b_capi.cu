@@ -169,6 +169,14 @@ void apply_host_pipelined(d4b_mesh *m, const double *u, double *Au) {
   D4B_CUDA(cudaStreamSynchronize(m->stream));   // the staging vectors are free
   m->epi = D4bEpilogue();
   double *du = m->d_u_stage, *dAu = m->d_Au_stage;
+  // D4B_PIPE_TIMING=1: when the upload ended, when the first / last part of Au went down (ms after the first copy began)
+  static const bool timing = getenv("D4B_PIPE_TIMING") && atoi(getenv("D4B_PIPE_TIMING")) != 0;
+  static cudaEvent_t tev[4] = {nullptr, nullptr, nullptr, nullptr};
+  if (timing && !tev[0]) for (cudaEvent_t &e : tev) D4B_CUDA(cudaEventCreate(&e));
+  if (timing) D4B_CUDA(cudaEventRecord(tev[0], m->h2d_stream));
+  bool first_down = true;
+  // (one stream per direction: alternating the chunks between two streams per direction, so that the next copy is
+  //  already queued at the copy engine when the current one ends, is slower -- 4.25 vs 3.96 ms)
   for (int i = 0; i < K; ++i) {
     const int k = m->chunk_order[i];
     const int64_t n0 = m->chunk_node[k], n1 = m->chunk_node[k + 1];
@@ -176,6 +184,7 @@ void apply_host_pipelined(d4b_mesh *m, const double *u, double *Au) {
       D4B_CUDA(cudaMemcpyAsync(du + n0, u + n0, (size_t)(n1 - n0) * sizeof(double), cudaMemcpyHostToDevice, m->h2d_stream));
     D4B_CUDA(cudaEventRecord(m->ev_h2d[i], m->h2d_stream));
   }
+  if (timing) D4B_CUDA(cudaEventRecord(tev[1], m->h2d_stream));
   std::vector<char> launched(K, 0);
   for (int i = 0; i < K; ++i) {
     const int k = m->chunk_order[i];
@@ -187,14 +196,23 @@ void apply_host_pipelined(d4b_mesh *m, const double *u, double *Au) {
       launched[c] = 1;
       d4b_launch_fast_range(m, du, dAu, 1, m->chunk_elem[c], m->chunk_elem[c + 1]);
       D4B_CUDA(cudaEventRecord(m->ev_done[c], m->stream));
-      D4B_CUDA(cudaStreamWaitEvent(m->d2h_stream, m->ev_done[c], 0));
+      cudaStream_t ds = m->d2h_stream;
+      D4B_CUDA(cudaStreamWaitEvent(ds, m->ev_done[c], 0));
       const int64_t n0 = m->chunk_node[c], n1 = m->chunk_node[c + 1];
+      if (timing && first_down) { D4B_CUDA(cudaEventRecord(tev[2], ds)); first_down = false; }
       if (n1 > n0)
-        D4B_CUDA(cudaMemcpyAsync(Au + n0, dAu + n0, (size_t)(n1 - n0) * sizeof(double), cudaMemcpyDeviceToHost, m->d2h_stream));
+        D4B_CUDA(cudaMemcpyAsync(Au + n0, dAu + n0, (size_t)(n1 - n0) * sizeof(double), cudaMemcpyDeviceToHost, ds));
     }
   }
+  if (timing) D4B_CUDA(cudaEventRecord(tev[3], m->d2h_stream));
   D4B_CUDA(cudaStreamSynchronize(m->d2h_stream));
   D4B_CUDA(cudaStreamSynchronize(m->stream));
+  if (timing) {
+    float t1 = 0.f, t2 = 0.f, t3 = 0.f;
+    cudaEventElapsedTime(&t1, tev[0], tev[1]); cudaEventElapsedTime(&t2, tev[0], tev[2]); cudaEventElapsedTime(&t3, tev[0], tev[3]);
+    fprintf(stderr, "[d4b] pipelined host apply, %d chunks: upload done %.3f ms | first download starts %.3f | last download done %.3f\n",
+            K, t1, t2, t3);
+  }
 }
 
 void apply_impl(d4b_mesh *m, const double *u, double *Au, int stiffness_only) {
