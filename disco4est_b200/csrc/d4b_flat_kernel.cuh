@@ -80,14 +80,16 @@ __device__ __forceinline__ void l2_prefetch_line(const void *ptr) {
 template <int N>
 struct FlatCfg {
   static constexpr int NN = N * N, N3 = N * N * N;
-  // threads per block by N = 2..8, from an A/B sweep on B200 (profiles/): small
-  // blocks keep barriers cheap, a one-warp block needs none
+  // threads per block by N = 2..8, from A/B sweeps on B200 (profiles/): small
+  // blocks keep barriers cheap, a one-warp block needs none; N = 6, 7 take 256-thread blocks because N^2 = 36, 49
+  // threads per element fill 252 / 245 of 256 lanes but only 108 of 128 / 49 of 64 (N = 7: +23 %, N = 6: +2 %,
+  // profiles/r02_flat_256thread_ab.txt)
   // (D4B_FLAT_THREADS / D4B_FLAT_MINB: compile-time overrides for those sweeps, profiles/build_variants.sh)
 #ifndef D4B_FLAT_THREADS
-#define D4B_FLAT_THREADS {0, 0, 32, 64, 32, 128, 128, 64, 64}
+#define D4B_FLAT_THREADS {0, 0, 32, 64, 32, 128, 256, 256, 64}
 #endif
 #ifndef D4B_FLAT_MINB
-#define D4B_FLAT_MINB {0, 0, 1, 12, 24, 5, 4, 1, 8}
+#define D4B_FLAT_MINB {0, 0, 1, 12, 24, 5, 2, 3, 8}
 #endif
   static constexpr int kThreads[9] = D4B_FLAT_THREADS;
   static constexpr int kMinBlocks[9] = D4B_FLAT_MINB;   // resident blocks per SM the register budget is cut for
