@@ -123,10 +123,10 @@ struct Cfg {
 // launch geometry of fast_apply_kernel by N = 2..8 (D4B_FAST_THREADS / D4B_FAST_MINB: compile-time
 // overrides for A/B sweeps, profiles/build_variants.sh); a one-warp block synchronises with __syncwarp
 #ifndef D4B_FAST_THREADS
-#define D4B_FAST_THREADS {0, 0, 32, 128, 32, 128, 128, 64, 64}
+#define D4B_FAST_THREADS {0, 0, 32, 128, 32, 128, 128, 256, 64}   // N = 7: 245 of 256 lanes instead of 49 of 64 (+6 %, profiles/r02_curved_256thread_ab.txt)
 #endif
 #ifndef D4B_FAST_MINB
-#define D4B_FAST_MINB {0, 0, 16, 5, 20, 4, 4, 5, 5}
+#define D4B_FAST_MINB {0, 0, 16, 5, 20, 4, 4, 2, 5}
 #endif
 template <int N>
 struct CurvedCfg {
