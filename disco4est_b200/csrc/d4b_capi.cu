@@ -217,6 +217,7 @@ void apply_host_pipelined(d4b_mesh *m, const double *u, double *Au) {
 
 void apply_impl(d4b_mesh *m, const double *u, double *Au, int stiffness_only) {
   D4B_CHECK(m && u && Au, "d4b_apply: NULL argument");
+  d4b_check_device(m);
   D4B_CHECK(m->n_ghost == 0 || m->d_ughost, "d4b_apply: ghost buffer missing");
   bool u_dev = is_device_ptr(u), Au_dev = is_device_ptr(Au);
   if (!u_dev && !Au_dev && !stiffness_only && !m->chunk_dep.empty() && u != Au && !m->pre_apply) {

@@ -239,6 +239,14 @@ struct d4b_mesh {
   bool all_flat = false;               // every element runs in the tangential-free kernel
 };
 
+// the entry points launch on the mesh's stream: the mesh's device must be the caller's current one
+inline void d4b_check_device(const d4b_mesh *m) {
+  int cur = -1;
+  cudaGetDevice(&cur);
+  D4B_CHECK(cur == m->device, "mesh lives on device %d but the current device is %d (cudaSetDevice before the call)",
+            m->device, cur);
+}
+
 template <typename T>
 T *d4b_dev_alloc(d4b_mesh *m, size_t n);
 template <typename T>

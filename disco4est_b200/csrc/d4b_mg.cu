@@ -321,6 +321,7 @@ void bottom_cheby(d4b_mg *g, double *u, const double *rhs, double *r) {
 // levels, so their launch latencies are hidden.
 double vcycle_device(d4b_mg *g, double *u_top, const double *rhs_top) {
   const int top = g->n_levels - 1;
+  d4b_check_device(g->mesh[top]);
   const d4b_cheby_params_t &c = g->prm.smoother;
   const int vc = g->vcycle_num_finished;
   // ..._smoother_cheby_update (:222-262): decided at PRE_V for the whole down leg,

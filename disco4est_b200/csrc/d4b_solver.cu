@@ -450,6 +450,7 @@ static double d4b_smooth_eig(d4b_mesh *m) {
 
 extern "C" double d4b_cg_eigs(d4b_mesh_t *m, double *u, const double *rhs, int32_t imax,
                               int32_t use_new, int32_t use_zero_guess) {
+  d4b_check_device(m);
   const int64_t n = m->local_nodes;
   const size_t bytes = (size_t)n * sizeof(double);
   bool u_dev = is_dev(u), rhs_dev = is_dev(rhs);
@@ -472,6 +473,7 @@ extern "C" double d4b_cg_eigs(d4b_mesh_t *m, double *u, const double *rhs, int32
 extern "C" void d4b_cheby_smooth(d4b_mesh_t *m, double *u, const double *rhs, double *r, int32_t iter,
                                  double lmin, double lmax) {
   D4B_CHECK(iter >= 0 && iter <= kMaxCheby, "d4b_cheby_smooth: iter %d out of range", iter);
+  d4b_check_device(m);
   const int64_t n = m->local_nodes;
   const size_t bytes = (size_t)n * sizeof(double);
   bool u_dev = is_dev(u), rhs_dev = is_dev(rhs), r_dev = is_dev(r);
