@@ -73,6 +73,11 @@ def load_library():
     L.d4b_mesh_hp_elements.argtypes = [C.c_void_p]
     L.d4b_mesh_launches_per_apply.restype = C.c_int32
     L.d4b_mesh_launches_per_apply.argtypes = [C.c_void_p]
+    if hasattr(L, "d4b_host_pin"):
+        L.d4b_host_pin.restype = C.c_int32
+        L.d4b_host_pin.argtypes = [C.c_void_p, C.c_int64]
+        L.d4b_host_unpin.restype = C.c_int32
+        L.d4b_host_unpin.argtypes = [C.c_void_p]
     if hasattr(L, "d4b_mesh_halo_mode"):   # (older builds of the library are still loadable for A/B runs)
         L.d4b_mesh_halo_mode.restype = C.c_int32
         L.d4b_mesh_halo_mode.argtypes = [C.c_void_p]

@@ -232,6 +232,13 @@ def test_pipelined_host_apply_at_size():
     pu, pa = torch.from_numpy(u).pin_memory(), torch.empty(m.n, dtype=torch.float64).pin_memory()
     m.apply(pu.numpy(), pa.numpy())
     assert np.array_equal(a1, ref) and np.array_equal(pa.numpy(), ref)
+    # pageable vectors page-locked by the library (what d4est_b200_pin_vectors does for the reference's vectors)
+    u2, a2 = u.copy(), np.zeros_like(u)
+    assert m.L.d4b_host_pin(u2.ctypes.data, u2.nbytes) == 0 and m.L.d4b_host_pin(a2.ctypes.data, a2.nbytes) == 0
+    m.apply(u2, a2)
+    assert np.array_equal(a2, ref)
+    assert m.L.d4b_host_unpin(u2.ctypes.data) == 0 and m.L.d4b_host_unpin(a2.ctypes.data) == 0
+    assert m.L.d4b_host_unpin(a2.ctypes.data) != 0   # (not pinned any more: an error code, no abort)
     m.close()
 
 
