@@ -351,12 +351,18 @@ extern "C" void d4b_estimator_bi(d4b_mesh_t *m, const d4b_estimator_desc_t *d, d
 extern "C" void d4b_mesh_set_mass_diag(d4b_mesh_t *m, const double *jac_quad) {
   D4B_CHECK(m, "d4b_mesh_set_mass_diag: NULL mesh");
   D4B_CUDA(cudaStreamSynchronize(m->stream));
-  m->config_epoch++;   // recorded V-cycle graphs of this mesh are stale
+  // recorded V-cycle graphs of this mesh go stale when the term appears or disappears (other kernel variants, another
+  // pointer); new values in the same array leave them valid
   if (!jac_quad) {
-    if (m->d_W) { cudaFree(m->d_W); m->d_W = nullptr; m->device_bytes -= m->local_nodes_quad * (int64_t)sizeof(double); }
+    if (m->d_W) {
+      cudaFree(m->d_W); m->d_W = nullptr; m->device_bytes -= m->local_nodes_quad * (int64_t)sizeof(double);
+      m->config_epoch++;
+      m->w_version++;
+    }
     return;
   }
-  if (!m->d_W) m->d_W = d4b_dev_alloc<double>(m, (size_t)m->local_nodes_quad);
+  if (!m->d_W) { m->d_W = d4b_dev_alloc<double>(m, (size_t)m->local_nodes_quad); m->config_epoch++; }
+  m->w_version++;
   DevIn jac(m, jac_quad, m->local_nodes_quad);
   d4b_launch_quad_op(m, 3, nullptr, jac.p, m->d_W);
   D4B_CUDA(cudaStreamSynchronize(m->stream));

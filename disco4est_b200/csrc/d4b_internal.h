@@ -142,6 +142,7 @@ struct d4b_mesh {
   int max_deg = 0, max_deg_quad = 0;
   int64_t device_bytes = 0;
   int64_t config_epoch = 0;      // bumped whenever a later launch sequence would differ (d4b_mesh_set_mass_diag)
+  int64_t w_version = 0;         // bumped whenever the CONTENTS of d_W change (new linearisation point)
 
   // tables
   D4bTables tab;                 // host copy of offsets

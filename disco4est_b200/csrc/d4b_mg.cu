@@ -52,6 +52,14 @@ struct d4b_mg {
   int coarse_mass = 0;
   std::vector<double *> d_mw, d_mt;
   double *d_W0 = nullptr;        // mode 1: w J f_u(x, 0) on the finest level (see d4b_mg_set_coarse_mass)
+  // the same operator as dense per-element matrices of the coarse levels (uniform degree, what the reference's
+  // PT_mat_P stores): column-major, Mc[l][(e n3 + k) n3 + i]; built level by level from the one above whenever the
+  // fine weights change (build_coarse_matrices), applied by one kernel instead of the prolong / weight / restrict chain
+  std::vector<double *> d_Mc;
+  std::vector<int> mc_n3;        // 0: level not available in dense form (chain)
+  int mc_mode = 0;               // what d_Mc was built for
+  int64_t mc_version = -1;       // ... and for which contents of the finest level's W (mode 2)
+  double *d_unit = nullptr;      // unit vectors of the build
   // mode 1, levels whose families all have 8 children of one degree: the slices Q_i as a table
   // Qt[(i nh3 + b) nH3 + a] (transposed for coalesced reads), per coarse level, else nullptr
   std::vector<double *> d_Qt;
@@ -263,6 +271,95 @@ int grid_for(int64_t n) {
   return (int)(b < 148 * 8 ? (b > 0 ? b : 1) : 148 * 8);
 }
 
+// out_e = Mc_e in_e, one block per element, thread i one row (column-major storage: coalesced)
+__global__ void dense_elem_matvec_k(int n3, const double *__restrict__ Mc, const double *__restrict__ in,
+                                    double *__restrict__ out) {
+  extern __shared__ double su[];
+  const size_t e = blockIdx.x;
+  for (int k = threadIdx.x; k < n3; k += blockDim.x) su[k] = in[e * n3 + k];
+  __syncthreads();
+  const double *M = Mc + e * (size_t)n3 * n3;
+  for (int i = threadIdx.x; i < n3; i += blockDim.x) {
+    double acc = 0.;
+    for (int k = 0; k < n3; ++k) acc += M[(size_t)k * n3 + i] * su[k];
+    out[e * n3 + i] = acc;
+  }
+}
+__global__ void unit_vector_k(int64_t n, int n3, int k, double *__restrict__ u) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    u[i] = (i % n3 == k) ? 1. : 0.;
+}
+__global__ void store_column_k(int64_t n, int n3, int k, const double *__restrict__ col, double *__restrict__ Mc) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    Mc[((i / n3) * n3 + k) * (int64_t)n3 + i % n3] = col[i];
+}
+
+void dense_coarse_apply(d4b_mg *g, int l, const double *in, double *out) {
+  d4b_mesh *m = g->mesh[l];
+  const int n3 = g->mc_n3[l];
+  dense_elem_matvec_k<<<m->n_local, n3 <= 64 ? 64 : 128, (size_t)n3 * sizeof(double), m->stream>>>(n3, g->d_Mc[l], in, out);
+  D4B_CUDA(cudaGetLastError());
+}
+
+void transfer(d4b_mg *g, int dir, int accumulate, int lc, const double *in, double *out);
+
+// The coarse-level mass term as dense per-element matrices, M_l = L_l M_{l+1} P_l with L = P^T (Galerkin) or the
+// reference's slices, column by column: the chain of ONE level applied to the unit vector k of every element at once
+// gives column k of every element's matrix (the operator is block diagonal over the elements).  Levels must have a
+// uniform degree N <= 5 and fit D4B_MG_DENSE_COARSE_MB (default 4096) together; D4B_MG_DENSE_COARSE=0 keeps the chain.
+// Not inside a stream capture: called at the start of every V-cycle and of every stand-alone coarse apply.
+void build_coarse_matrices(d4b_mg *g) {
+  const int top = g->n_levels - 1;
+  d4b_mesh *mt = g->mesh[top];
+  if (!g->coarse_mass || !mt->d_W) return;
+  if (g->mc_mode == g->coarse_mass && (g->coarse_mass == 1 || g->mc_version == mt->w_version)) return;
+  static const bool off = getenv("D4B_MG_DENSE_COARSE") && atoi(getenv("D4B_MG_DENSE_COARSE")) == 0;
+  static const double budget_mb = getenv("D4B_MG_DENSE_COARSE_MB") ? atof(getenv("D4B_MG_DENSE_COARSE_MB")) : 4096.;
+  g->mc_mode = g->coarse_mass;
+  g->mc_version = mt->w_version;
+  if (g->d_Mc.empty()) { g->d_Mc.assign(g->n_levels, nullptr); g->mc_n3.assign(g->n_levels, 0); }
+  cudaStream_t s = mt->stream;
+  std::vector<cudaStream_t> saved(g->n_levels);
+  for (int j = 0; j <= top; ++j) {
+    saved[j] = g->mesh[j]->stream;
+    if (saved[j] != s) { D4B_CUDA(cudaStreamSynchronize(saved[j])); g->mesh[j]->stream = s; }
+  }
+  const double *Wfine = g->coarse_mass == 1 ? g->d_W0 : mt->d_W;
+  const int back = g->coarse_mass == 1 ? 2 : 1;
+  double used_mb = 0.;
+  bool chain_from_here = off;
+  for (int l = top - 1; l >= 0; --l) {
+    d4b_mesh *ml = g->mesh[l];
+    const int N = ml->max_deg + 1, n3 = N * N * N;
+    const double mb = (double)ml->n_local * n3 * n3 * 8. / 1048576.;
+    const bool uniform = ml->n_local > 0 && ml->local_nodes == (int64_t)ml->n_local * n3 && N <= 5 && ml->mpisize >= 1;
+    if (chain_from_here || !uniform || used_mb + mb > budget_mb) {   // this level and everything below: the chain
+      chain_from_here = true;
+      g->mc_n3[l] = 0;
+      continue;
+    }
+    used_mb += mb;
+    if (!g->d_Mc[l]) g->d_Mc[l] = d4b_dev_alloc<double>(ml, (size_t)ml->n_local * n3 * n3);
+    if (!g->d_unit) {
+      int64_t mx = 1;
+      for (int j = 0; j < top; ++j) mx = std::max(mx, g->mesh[j]->local_nodes);
+      g->d_unit = d4b_dev_alloc<double>(mt, (size_t)mx);
+    }
+    const int64_t n = ml->local_nodes;
+    for (int k = 0; k < n3; ++k) {
+      unit_vector_k<<<grid_for(n), 256, 0, s>>>(n, n3, k, g->d_unit);
+      transfer(g, 0, 0, l, g->d_unit, g->d_mw[l + 1]);
+      if (l + 1 == top) d4b_launch_quad_op(mt, 4, g->d_mw[top], Wfine, g->d_mt[top]);
+      else dense_coarse_apply(g, l + 1, g->d_mw[l + 1], g->d_mt[l + 1]);
+      transfer(g, back, 0, l, g->d_mt[l + 1], ml->d_addterm);
+      store_column_k<<<grid_for(n), 256, 0, s>>>(n, n3, k, ml->d_addterm, g->d_Mc[l]);
+    }
+    D4B_CUDA(cudaGetLastError());
+    g->mc_n3[l] = n3;
+  }
+  for (int j = 0; j <= top; ++j) g->mesh[j]->stream = saved[j];
+}
+
 // t = P_l^T ... P_{top-1}^T (V^T diag(W) V) P_{top-1} ... P_l u on coarse level l: what the reference's dense
 // per-element matrices PT_mat_P of the multigrid matrix operator apply
 // (d4est_solver_multigrid_matrix_operator.c:5-47; d4est_operators_compute_PT_mat_P), matrix-free.
@@ -271,6 +368,11 @@ bool coarse_mass_term(d4b_mg *g, int l, const double *u) {
   const int top = g->n_levels - 1;
   d4b_mesh *mt = g->mesh[top], *ml = g->mesh[l];
   if (!g->coarse_mass || !mt->d_W) return false;
+  if (!g->d_Mc.empty() && g->mc_n3[l] && g->mc_mode == g->coarse_mass &&
+      (g->coarse_mass == 1 || g->mc_version == mt->w_version)) {
+    dense_coarse_apply(g, l, u, ml->d_addterm);
+    return true;
+  }
   // every level shares the top stream inside a V-cycle; a stand-alone coarse apply runs on its own
   // stream and the level vectors are ordered through it
   cudaStream_t s = ml->stream;
@@ -322,6 +424,7 @@ void bottom_cheby(d4b_mg *g, double *u, const double *rhs, double *r) {
 double vcycle_device(d4b_mg *g, double *u_top, const double *rhs_top) {
   const int top = g->n_levels - 1;
   d4b_check_device(g->mesh[top]);
+  build_coarse_matrices(g);   // (a no-op unless the coarse-level mass term is on and the fine weights changed)
   const d4b_cheby_params_t &c = g->prm.smoother;
   const int vc = g->vcycle_num_finished;
   // ..._smoother_cheby_update (:222-262): decided at PRE_V for the whole down leg,
@@ -546,6 +649,7 @@ extern "C" void d4b_mg_set_coarse_mass(d4b_mg_t *g, int32_t mode) {
   const int top = g->n_levels - 1;
   for (d4b_mesh *m : g->mesh) D4B_CUDA(cudaStreamSynchronize(m->stream));
   g->coarse_mass = mode;
+  g->mc_mode = 0;   // dense coarse matrices (build_coarse_matrices) are rebuilt before the next V-cycle
   if (mode == 1) {
     // The reference builds the fine matrices of its matrix operator with the arguments of
     // d4est_quadrature_apply_fofufofvlilj shifted by one (d4est_solver_multigrid_matrix_operator.c:215-240 passes
@@ -635,6 +739,8 @@ extern "C" void d4b_mg_destroy(d4b_mg_t *g) {
   for (auto p : g->d_mw) if (p) cudaFree(p);
   for (auto p : g->d_mt) if (p) cudaFree(p);
   if (g->d_W0) cudaFree(g->d_W0);
+  for (auto p : g->d_Mc) if (p) cudaFree(p);
+  if (g->d_unit) cudaFree(g->d_unit);
   for (auto p : g->d_Qt) if (p) cudaFree(p);
   for (int l = 0; l + 1 < g->n_levels; ++l) g->mesh[l]->pre_apply = nullptr;
   if (g->d_top_u) cudaFree(g->d_top_u);

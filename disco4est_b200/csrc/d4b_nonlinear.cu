@@ -131,9 +131,11 @@ void residual_device(d4b_mesh *m, const double *du, const double *drhs, double *
 
 void linearize_device(d4b_mesh *m, const double *du0) {
   D4B_CHECK(m->d_nl_wja, "d4b_mesh_linearize: no nonlinear term attached to this mesh");
-  if (!m->d_W) m->d_W = d4b_dev_alloc<double>(m, (size_t)m->local_nodes_quad);
+  // recorded V-cycle graphs carry the POINTER of W and the kernel variants chosen for a mesh with a mass term: a new
+  // linearisation point changes the contents only, the graphs stay valid (a Newton solve re-linearises every step)
+  if (!m->d_W) { m->d_W = d4b_dev_alloc<double>(m, (size_t)m->local_nodes_quad); m->config_epoch++; }
   d4b_launch_quad_nl(m, 6, du0, m->d_W);
-  m->config_epoch++;   // recorded V-cycle graphs are keyed on it
+  m->w_version++;
 }
 
 }  // namespace

@@ -173,6 +173,13 @@ def test_graph_replay_equals_eager_cycles(monkeypatch):
         jac = torch.full((int(descs[-1]["local_nodes_quad"]),), 0.7, dtype=torch.float64, device=dev)
         meshes[-1].set_mass_diag(jac)                    # the operator changes: A + 0.7 M-like term
         r2 += [mg.vcycle(u, rhs) for _ in range(3)]
+        # new values in the same array (a Newton solve re-linearises every step): the recorded graphs stay valid and
+        # must see them
+        jac2 = torch.full((int(descs[-1]["local_nodes_quad"]),), 0.2, dtype=torch.float64, device=dev)
+        replays = mg.graph_replays()
+        meshes[-1].set_mass_diag(jac2)
+        r2 += [mg.vcycle(u, rhs) for _ in range(2)]
+        assert (mg.graph_replays() - replays == 2) == graph
         out = u.cpu().numpy().copy()
         mg.close()
         for m in meshes:
