@@ -587,7 +587,8 @@ def bench_punctures(args, rank, world, local_rank, torch, dist, dev):
     out["jacobian_apply"] = {"GDOF_per_s": total_dof / t_jac / 1e9, "ms_per_apply": 1e3 * t_jac, "level": lvl,
                              "elements": E, "dof": total_dof, "checksum": float(Jv.sum())}
     out["residual"] = {"GDOF_per_s": total_dof / t_res / 1e9, "ms_per_evaluation": 1e3 * t_res,
-                       "note": "apply + a quadrature kernel for V^T w J f(x, V u)"}
+                       "note": "one pass: f(x, V u) is evaluated at the quadrature points inside the apply kernels "
+                               "(uh is already there), like the linearised term of the Jacobian"}
     mesh.close()
     del u0, v, Jv
     if world == 1:

@@ -32,6 +32,8 @@ struct CurvedArgs {
   D4bEpilogue epi;
   int prefetch;
   const double *W;
+  const double *nlB;            // residual: the functor's b (mass_point, d4b_fast.cu)
+  int nlK;
   const int64_t *quad_stride;
   const unsigned char *has_extra;
   const double *extra;
@@ -315,11 +317,12 @@ __global__ void __launch_bounds__(CurvedShflCfg<N>::THREADS, CurvedShflCfg<N>::M
         ft[c] = G02 * gr[c] + G12 * gs[c] + G22 * gt[c];
       }
       const double *Wd = MASS ? a.W + a.quad_stride[a.elem[ei]] + lt : nullptr;
+      const double *Bd = (MASS && a.nlB) ? a.nlB + a.quad_stride[a.elem[ei]] + lt : nullptr;
       const double *xtr = (a.has_extra && a.has_extra[ei]) ? a.extra + ns + lt : nullptr;
 #pragma unroll
       for (int c = 0; c < N; ++c) {
         double s = T.e[0][c] * ve0 + T.d[0][c] * vd0 + T.e[1][c] * ve1 + T.d[1][c] * vd1;
-        if (MASS) s += Wd[NN * c] * V0[vix<N>(lx, ly, c)];
+        if (MASS) s += mass_point(Wd, Bd, a.nlK, NN * c, V0[vix<N>(lx, ly, c)]);
         if (xtr) s += xtr[NN * c];
 #pragma unroll
         for (int i = 0; i < N; ++i) s += T.Dg[i][c] * ft[i];

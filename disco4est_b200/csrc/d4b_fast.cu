@@ -76,6 +76,23 @@ __device__ __forceinline__ void store_result(const D4bEpilogue &e, const EpiCoef
   e.u[i] += pn;
 }
 
+// MASS kernels: the mass-type term of one quadrature point in the Gauss basis (point-wise there).  Linear, W uh -- the
+// Jacobian of a nonlinear problem about u0, W = w J f_u(x, V u0) (d4b_mesh_linearize / d4b_mesh_set_mass_diag) -- or,
+// with B set, the nonlinear functor itself, W (B + uh)^k with W = w J a (d4b_build_residual: the term
+// d4est_quadrature_apply_fofufofvlj adds, src/Quadrature/d4est_quadrature.c:776-936, for f = a (b + u)^k)
+__device__ __forceinline__ double mass_point(const double *__restrict__ W, const double *__restrict__ B, int k, int64_t q,
+                                             double uh) {
+  const double w = W[q];
+  if (!B) return w * uh;
+  const double x = B[q] + uh;
+  double r = 1., p = x;
+  for (int n = k < 0 ? -k : k; n; n >>= 1) {
+    if (n & 1) r *= p;
+    p *= p;
+  }
+  return w * (k < 0 ? 1. / r : r);
+}
+
 struct FastArgs {
   const int32_t *elem;          // [n_elem] element ids of this class
   int first;                    // this launch covers class positions [first, n_elem)
@@ -90,6 +107,8 @@ struct FastArgs {
   double *Au;
   D4bEpilogue epi;
   const double *W;              // MASS kernels: weighted diagonal at the quadrature points (d4b_mesh_set_mass_diag)
+  const double *nlB;            // MASS kernels, residual: the functor's b at the quadrature points (see mass_point)
+  int nlK;
   const int64_t *quad_stride;
   int prefetch;                 // L2 prefetch of the block's volume metric and face records at kernel start
   const unsigned char *has_extra;   // face split, see FlatArgs
@@ -346,10 +365,11 @@ __global__ void __launch_bounds__(CurvedCfg<N>::THREADS, CurvedCfg<N>::MIN_BLOCK
     }
     // mass-type diagonal: in the Gauss basis V^T diag(W) V u is point-wise, r += W uh
     const double *Wd = MASS ? a.W + a.quad_stride[a.elem[ei]] + lt : nullptr;
+    const double *Bd = (MASS && a.nlB) ? a.nlB + a.quad_stride[a.elem[ei]] + lt : nullptr;
     const double *xtr = (a.has_extra && a.has_extra[ei]) ? a.extra + ns + lt : nullptr;
 #pragma unroll
     for (int c = 0; c < N; ++c) {
-      double s = MASS ? Wd[NN * c] * V0[vix<N>(lx, ly, c)] : 0.;
+      double s = MASS ? mass_point(Wd, Bd, a.nlK, NN * c, V0[vix<N>(lx, ly, c)]) : 0.;
       if (xtr) s += xtr[NN * c];
 #pragma unroll
       for (int i = 0; i < N; ++i) s += T.Dg[i][c] * ft[i];
@@ -561,7 +581,8 @@ void launch_flat(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, 
   a.meta = static_cast<const FaceMeta *>(cls.d_face_meta);
   a.uh = m->d_uhat; a.Au = d_Au; a.epi = m->epi;
   size_t smem = (size_t)C::EPB * C::SH_PER_ELEM * sizeof(double);
-  a.W = m->d_W; a.quad_stride = m->d_quad_stride;
+  const double *Wsrc = m->nl_fused ? m->d_nl_wja : m->d_W;
+  a.W = Wsrc; a.nlB = m->nl_fused ? m->d_nl_b : nullptr; a.nlK = m->nl_k; a.quad_stride = m->d_quad_stride;
   a.has_extra = cls.d_has_extra; a.extra = m->d_extra;
   static bool configured_dev[kD4bMaxDevices] = {};   // the attribute is per device
   bool &configured = configured_dev[m->device];
@@ -587,17 +608,17 @@ void launch_flat(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, 
               (long long)m->dot_capacity);
   }
   if (m->epi.dot_part) {
-    D4B_CHECK(!m->d_W && m->epi.mode != 3, "energy dot: not with a mass term or the Gauss-resident smoother");
+    D4B_CHECK(!Wsrc && m->epi.mode != 3, "energy dot: not with a mass term or the Gauss-resident smoother");
     if (cls.d_FGc) flat_apply_kernel<N, false, true, false, true><<<grid, C::THREADS, smem, m->stream>>>(a);
     else flat_apply_kernel<N, false, false, false, true><<<grid, C::THREADS, smem, m->stream>>>(a);
   } else if (m->epi.mode == 3) {
-    D4B_CHECK(!m->d_W && m->epi.uh_out && m->epi.rhs && m->epi.p, "Gauss-resident smoother: bad epilogue");
+    D4B_CHECK(!Wsrc && m->epi.uh_out && m->epi.rhs && m->epi.p, "Gauss-resident smoother: bad epilogue");
     if (cls.d_FGc) flat_apply_kernel<N, false, true, true><<<grid, C::THREADS, smem, m->stream>>>(a);
     else flat_apply_kernel<N, false, false, true><<<grid, C::THREADS, smem, m->stream>>>(a);
   } else if (cls.d_FGc) {
-    if (m->d_W) flat_apply_kernel<N, true, true><<<grid, C::THREADS, smem, m->stream>>>(a);
+    if (Wsrc) flat_apply_kernel<N, true, true><<<grid, C::THREADS, smem, m->stream>>>(a);
     else flat_apply_kernel<N, false, true><<<grid, C::THREADS, smem, m->stream>>>(a);
-  } else if (m->d_W) flat_apply_kernel<N, true><<<grid, C::THREADS, smem, m->stream>>>(a);
+  } else if (Wsrc) flat_apply_kernel<N, true><<<grid, C::THREADS, smem, m->stream>>>(a);
   else flat_apply_kernel<N, false><<<grid, C::THREADS, smem, m->stream>>>(a);
   D4B_CUDA(cudaGetLastError());
 }
@@ -621,13 +642,14 @@ void launch_curved(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first
   a.FG = cls.d_FG; a.FF = m->d_fast_FF;
   a.meta = static_cast<const FaceMeta *>(cls.d_face_meta);
   a.uh = m->d_uhat; a.Au = d_Au; a.epi = m->epi;
-  a.W = m->d_W; a.quad_stride = m->d_quad_stride;
+  const double *Wsrc = m->nl_fused ? m->d_nl_wja : m->d_W;
+  a.W = Wsrc; a.nlB = m->nl_fused ? m->d_nl_b : nullptr; a.nlK = m->nl_k; a.quad_stride = m->d_quad_stride;
   a.has_extra = cls.d_has_extra; a.extra = m->d_extra;
   static const int prefetch = getenv("D4B_PREFETCH") ? atoi(getenv("D4B_PREFETCH")) : 1;
   a.prefetch = prefetch;
   const size_t smem = (size_t)C::EPB * C::SH_PER_ELEM * sizeof(double);
   const int grid = (last - first + C::EPB - 1) / C::EPB;
-  if (m->d_W) curved_apply_kernel<N, true><<<grid, C::THREADS, smem, m->stream>>>(a);
+  if (Wsrc) curved_apply_kernel<N, true><<<grid, C::THREADS, smem, m->stream>>>(a);
   else curved_apply_kernel<N, false><<<grid, C::THREADS, smem, m->stream>>>(a);
   D4B_CUDA(cudaGetLastError());
 }
@@ -645,7 +667,8 @@ void launch_hp(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, in
   a.deg = m->d_deg; a.ghost_deg = m->d_ghost_deg;
   a.nodal_stride = m->d_nodal_stride; a.quad_stride = m->d_quad_stride;
   a.ghost_nodal_stride = m->peer.state == 1 ? m->peer.d_ghost_uh_off : m->d_ghost_nodal_stride;
-  a.G = m->d_G; a.LQ = m->local_nodes_quad; a.W = m->d_W;
+  const double *Wsrc = m->nl_fused ? m->d_nl_wja : m->d_W;
+  a.G = m->d_G; a.LQ = m->local_nodes_quad; a.W = Wsrc; a.nlB = m->nl_fused ? m->d_nl_b : nullptr; a.nlK = m->nl_k;
   a.elem_side = m->d_elem_side; a.elem_sub = m->d_elem_sub;
   a.side_faces_m = m->d_side_faces_m; a.side_faces_p = m->d_side_faces_p; a.side_f_p = m->d_side_f_p;
   a.side_e_m = m->d_side_e_m; a.side_e_p = m->d_side_e_p; a.side_perm = m->d_side_perm;
@@ -676,7 +699,7 @@ void launch_hp(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, in
       configured_f = smem;
     }
     hp_apply_kernel<N, false, true><<<grid, 32 * warps, smem, m->stream>>>(a);
-  } else if (m->d_W) hp_apply_kernel<N, true><<<grid, 32 * warps, smem, m->stream>>>(a);
+  } else if (Wsrc) hp_apply_kernel<N, true><<<grid, 32 * warps, smem, m->stream>>>(a);
   else hp_apply_kernel<N, false><<<grid, 32 * warps, smem, m->stream>>>(a);
   D4B_CUDA(cudaGetLastError());
 }
@@ -759,7 +782,8 @@ void launch_fast(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, 
   a.face_rec = cls.d_face_rec; a.face_nbr = cls.d_face_nbr; a.face_code = cls.d_face_code;
   a.uh = m->d_uhat; a.Au = d_Au; a.epi = m->epi;
   size_t smem = (size_t)C::EPB * C::SH_PER_ELEM * sizeof(double);
-  a.W = m->d_W; a.quad_stride = m->d_quad_stride;
+  const double *Wsrc = m->nl_fused ? m->d_nl_wja : m->d_W;
+  a.W = Wsrc; a.nlB = m->nl_fused ? m->d_nl_b : nullptr; a.nlK = m->nl_k; a.quad_stride = m->d_quad_stride;
   a.has_extra = cls.d_has_extra; a.extra = m->d_extra;
   static bool configured_dev[kD4bMaxDevices] = {};
   bool &configured = configured_dev[m->device];
@@ -771,7 +795,7 @@ void launch_fast(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, 
   static const int prefetch = getenv("D4B_PREFETCH") ? atoi(getenv("D4B_PREFETCH")) : 1;
   a.prefetch = prefetch;
   int grid = (last - first + C::EPB - 1) / C::EPB;
-  if (m->d_W) fast_apply_kernel<N, true><<<grid, C::THREADS, smem, m->stream>>>(a);
+  if (Wsrc) fast_apply_kernel<N, true><<<grid, C::THREADS, smem, m->stream>>>(a);
   else fast_apply_kernel<N, false><<<grid, C::THREADS, smem, m->stream>>>(a);
   D4B_CUDA(cudaGetLastError());
 }

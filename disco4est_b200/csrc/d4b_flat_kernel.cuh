@@ -59,6 +59,8 @@ struct FlatArgs {
   D4bEpilogue epi;
   int prefetch;                 // 1: bulk-prefetch the block's volume metric into L2 at kernel start
   const double *W;              // MASS kernels: weighted diagonal at the quadrature points (d4b_mesh_set_mass_diag)
+  const double *nlB;            // MASS kernels, residual: the functor's b at the quadrature points (mass_point, d4b_fast.cu)
+  int nlK;
   const int64_t *quad_stride;
   // face split: elements with has_extra[class position] add extra[nodal_stride + k] (Gauss basis, the
   // contributions of their irregular faces from hp_apply_kernel<.., FACE_ONLY>) to the accumulator
@@ -328,12 +330,13 @@ __global__ void __launch_bounds__(FlatCfg<N>::THREADS, FlatCfg<N>::MIN_BLOCKS) f
     const double ve1 = FB[(5 * 2 + 0) * NN + lt], vd1 = FB[(5 * 2 + 1) * NN + lt];
     // mass-type diagonal: in the Gauss basis V^T diag(W) V u is point-wise, r += W uh
     const double *Wd = MASS ? a.W + a.quad_stride[a.elem[ei]] + lt : nullptr;
+    const double *Bd = (MASS && a.nlB) ? a.nlB + a.quad_stride[a.elem[ei]] + lt : nullptr;
     const double *xtr = (a.has_extra && a.has_extra[ei]) ? a.extra + ns + lt : nullptr;
 #pragma unroll
     for (int c = 0; c < N; ++c) {
       double s = T.e[0][c] * ve0 + T.d[0][c] * vd0 + T.e[1][c] * ve1 + T.d[1][c] * vd1;
       if (MASS) {
-        const double uc = V0[vix<N>(lx, ly, c)], wu = Wd[NN * c] * uc;
+        const double uc = V0[vix<N>(lx, ly, c)], wu = mass_point(Wd, Bd, a.nlK, NN * c, uc);
         s += wu;
         if (dot) dsum += wu * uc;
       }

@@ -36,6 +36,8 @@ struct HpArgs {
   const double *G;             // 6 planes of LQ
   int64_t LQ;
   const double *W;
+  const double *nlB;           // residual: the functor's b (mass_point, d4b_fast.cu)
+  int nlK;
   const int32_t *elem_side, *elem_sub;
   const int32_t *side_faces_m, *side_faces_p, *side_f_p, *side_e_m, *side_e_p, *side_perm, *side_sub_order;
   const int64_t *side_mortar_stride;
@@ -225,6 +227,7 @@ __global__ void __launch_bounds__(128) hp_apply_kernel(HpArgs a) {
   if (!FACE_ONLY) {
     const double *G = a.G + a.quad_stride[e];
     const double *Wd = MASS ? a.W + a.quad_stride[e] : nullptr;
+    const double *Bd = (MASS && a.nlB) ? a.nlB + a.quad_stride[e] : nullptr;
     for (int k = lane; k < N3; k += 32) {
       const double gr = V1[k], gs = V2[k], gt = V3[k];
       const double G00 = G[k], G01 = G[a.LQ + k], G02 = G[2 * a.LQ + k], G11 = G[3 * a.LQ + k],
@@ -232,7 +235,7 @@ __global__ void __launch_bounds__(128) hp_apply_kernel(HpArgs a) {
       V1[k] = G00 * gr + G01 * gs + G02 * gt;
       V2[k] = G01 * gr + G11 * gs + G12 * gt;
       V3[k] = G02 * gr + G12 * gs + G22 * gt;
-      V0[k] = MASS ? Wd[k] * V0[k] : 0.;
+      V0[k] = MASS ? mass_point(Wd, Bd, a.nlK, k, V0[k]) : 0.;
     }
   }
   __syncwarp();

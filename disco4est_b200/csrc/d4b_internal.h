@@ -207,6 +207,7 @@ struct d4b_mesh {
   // nonlinear mass-type term f(x,u) = a(x) (b(x) + u)^k (d4b_nonlinear.cu): w J a and b at the quadrature points
   double *d_nl_wja = nullptr, *d_nl_b = nullptr;
   int nl_k = 0;
+  bool nl_fused = false;   // the next apply adds the functor itself (residual) instead of the linear term W u
   // coarse multigrid level under a linearised finest level: pre_apply(u) leaves the Galerkin mass term
   // P^T M P u in d_addterm before every apply, the kernels' epilogue adds it (d4b_mg_set_coarse_mass)
   std::function<bool(d4b_mesh *, const double *)> pre_apply;

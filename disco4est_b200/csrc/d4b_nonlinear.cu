@@ -119,12 +119,24 @@ void drop_nonlinear(d4b_mesh *m) {
 
 // F = A(u) + N(u) - rhs on device pointers, stream-ordered; the mesh's linearisation is masked
 void residual_device(d4b_mesh *m, const double *du, const double *drhs, double *dF, double *dtmp) {
+  const int64_t n = m->local_nodes;
+  // every element in a Gauss-basis kernel: the functor is evaluated at the quadrature points INSIDE the apply (uh is
+  // already there), like the linear term of the Jacobian -- one pass, no quadrature kernel.  D4B_FUSED_RESIDUAL=0 or
+  // elements in the general kernel: apply + quadrature kernel.
+  static const bool fuse = !(getenv("D4B_FUSED_RESIDUAL") && atoi(getenv("D4B_FUSED_RESIDUAL")) == 0);
+  if (fuse && m->d_nl_wja && m->n_generic == 0 && !m->fast.empty() && !m->pre_apply) {
+    m->epi = D4bEpilogue();
+    m->nl_fused = true;
+    d4b_apply_device(m, du, dF);
+    m->nl_fused = false;
+    if (drhs) resid_sum_k<<<grid_for(n), 256, 0, m->stream>>>(nullptr, drhs, dF, n);
+    return;
+  }
   double *W = m->d_W;
   m->d_W = nullptr;
   m->epi = D4bEpilogue();
   d4b_apply_device(m, du, dF);
   m->d_W = W;
-  const int64_t n = m->local_nodes;
   if (m->d_nl_wja) d4b_launch_quad_nl(m, 5, du, dtmp);
   if (m->d_nl_wja || drhs) resid_sum_k<<<grid_for(n), 256, 0, m->stream>>>(m->d_nl_wja ? dtmp : nullptr, drhs, dF, n);
 }
