@@ -659,6 +659,28 @@ template <> void launch_curved<8>(d4b_mesh *, const D4bFastClass &, double *, in
 
 #include "d4b_hp_kernel.cuh"
 
+template <int N, int GS>
+void launch_hp_gs(d4b_mesh *m, const HpArgs &a, int first, int last, bool mass, bool face_only) {
+  constexpr int EPW = 32 / GS;   // elements per warp
+  const size_t per_warp = (size_t)EPW * a.smem_doubles * sizeof(double);
+  int warps = (int)((200 * 1024) / per_warp);
+  warps = warps < 1 ? 1 : warps > 4 ? 4 : warps;
+  const size_t smem = per_warp * warps;
+  static size_t configured_dev[kD4bMaxDevices] = {};   // per device; 0 = the 48 KB default
+  size_t &configured = configured_dev[m->device];
+  if (smem > 48 * 1024 && smem > configured) {
+    D4B_CUDA(cudaFuncSetAttribute(hp_apply_kernel<N, false, false, GS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    D4B_CUDA(cudaFuncSetAttribute(hp_apply_kernel<N, true, false, GS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    D4B_CUDA(cudaFuncSetAttribute(hp_apply_kernel<N, false, true, GS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = smem;
+  }
+  const int grid = (last - first + warps * EPW - 1) / (warps * EPW);
+  if (face_only) hp_apply_kernel<N, false, true, GS><<<grid, 32 * warps, smem, m->stream>>>(a);
+  else if (mass) hp_apply_kernel<N, true, false, GS><<<grid, 32 * warps, smem, m->stream>>>(a);
+  else hp_apply_kernel<N, false, false, GS><<<grid, 32 * warps, smem, m->stream>>>(a);
+  D4B_CUDA(cudaGetLastError());
+}
+
 template <int N>
 void launch_hp(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, int last, bool face_only = false) {
   if (last <= first) return;
@@ -678,30 +700,14 @@ void launch_hp(d4b_mesh *m, const D4bFastClass &cls, double *d_Au, int first, in
   a.tabs = static_cast<const HpTabs *>(m->d_hp_tabs); a.tabdata = m->d_hp_tabdata;
   a.mM = m->max_deg + 1;
   a.smem_doubles = hp_smem_doubles<N>(a.mM);
-  const size_t per_warp = (size_t)a.smem_doubles * sizeof(double);
-  int warps = (int)((200 * 1024) / per_warp);
-  warps = warps < 1 ? 1 : warps > 4 ? 4 : warps;
-  const size_t smem = per_warp * warps;
-  static size_t configured_dev[kD4bMaxDevices] = {};   // per device; 0 = the 48 KB default
-  size_t &configured = configured_dev[m->device];
-  if (smem > 48 * 1024 && smem > configured) {
-    D4B_CUDA(cudaFuncSetAttribute(hp_apply_kernel<N, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    D4B_CUDA(cudaFuncSetAttribute(hp_apply_kernel<N, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
-  }
-  const int grid = (last - first + warps - 1) / warps;
   a.face_mask = cls.d_face_mask; a.extra = m->d_extra;
-  if (face_only) {
-    static size_t configured_f_dev[kD4bMaxDevices] = {};
-    size_t &configured_f = configured_f_dev[m->device];
-    if (smem > 48 * 1024 && smem > configured_f) {
-      D4B_CUDA(cudaFuncSetAttribute(hp_apply_kernel<N, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      configured_f = smem;
-    }
-    hp_apply_kernel<N, false, true><<<grid, 32 * warps, smem, m->stream>>>(a);
-  } else if (Wsrc) hp_apply_kernel<N, true><<<grid, 32 * warps, smem, m->stream>>>(a);
-  else hp_apply_kernel<N, false><<<grid, 32 * warps, smem, m->stream>>>(a);
-  D4B_CUDA(cudaGetLastError());
+  // Lanes per element: HpGroup<N> (8 at N = 2, 16 at N = 3) as long as four CTAs of an SM still fit their shared memory,
+  // else a whole warp -- the lane groups of one warp run their mortar loops one after the other where they differ, and
+  // with few resident warps nothing covers that (profiles/r02_hp_kernel.md: a gain up to max degree 3, a loss at 5).
+  constexpr int GSmin = HpGroup<N>::size;
+  const bool pack = GSmin < 32 && 4 * (4 * (size_t)(32 / GSmin) * a.smem_doubles * sizeof(double) + 1024) <= 228 * 1024;
+  if (pack) launch_hp_gs<N, GSmin>(m, a, first, last, Wsrc != nullptr, face_only);
+  else launch_hp_gs<N, 32>(m, a, first, last, Wsrc != nullptr, face_only);
 }
 
 void build_hp_tabs(d4b_mesh *m) {
