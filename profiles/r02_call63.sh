@@ -1,5 +1,5 @@
 #!/bin/bash
-# hp mortar kernel: table offsets in constant memory (committed) against the pointer in the arguments (gtabs); hp tests
+# hp mortar kernel: table offsets in constant memory (working tree of that call, not kept) against the pointer in the arguments (gtabs); hp tests
 mkdir -p gpurun_out
 {
 for lp in "5 3" "4 5"; do
